@@ -1,0 +1,196 @@
+/*
+ * ibl.h -- C ABI of libibl.so: the B200 (sm_100a) implementation of the per-frame
+ * object-localisation hot path of instance-based-loc.
+ *
+ * The reference has no FFI on this path: its "operator API" is the Python signatures of
+ * utils/depth_utils.py, utils/similarity_volume.py, utils/fpfh_register.py and the Open3D 0.17
+ * calls they make.  Each entry point below names the reference call (file:line) it replaces.
+ * The Python mirror in instance_based_loc_b200/ binds these through ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name starts with h_ ; plain C types only
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), except where a
+ *     count must be returned to the host (documented per function: "syncs")
+ *   - return value: >= 0 success (sometimes a count), < 0 an IBL_E_* code;
+ *     ibl_last_error_string() gives detail for the calling thread
+ *   - points / colours / normals are row-major double[n][3] (Open3D stores f64; exact f64
+ *     arithmetic in nanoflann accumulation order is what makes counts and index sets bit-exact)
+ *   - all floating-point arithmetic is compiled with FMA contraction disabled
+ */
+#ifndef IBL_H_
+#define IBL_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IBL_OK 0
+#define IBL_E_CUDA (-1)
+#define IBL_E_ARG (-2)
+#define IBL_E_NOMEM (-3)
+#define IBL_E_RANGE (-4)
+
+const char *ibl_last_error_string(void);
+int ibl_version(void);
+
+/* ---------------------------------------------------------------- depth -> clouds ----------- */
+/* utils/depth_utils.py:46-90 + :176-206 (get_mask_coloured_pointclouds_from_depth): ONE pass over
+ * the frame for all masks.  depth is float32[H*W] (depth_is_f64==0) or float64[H*W]; rgb uint8
+ * [H*W*3] or NULL; masks uint8[n_masks][H*W] (0/1); hor float32[W], ver float32[H] are the
+ * reference's np.linspace vectors.  Points of mask i are written, in row-major pixel order, to
+ * out_pts/out_cols rows [h_offsets[i], h_offsets[i+1]).  out_* must hold n_masks*H*W rows
+ * (or pass out_pts==NULL to only count).  h_offsets: host int64[n_masks+1].  Syncs. */
+int ibl_backproject_masks(const void *depth, int depth_is_f64, const uint8_t *rgb, const uint8_t *masks,
+                          int n_masks, int H, int W, const float *hor, const float *ver, double fx, double fy,
+                          double *out_pts, double *out_cols, int64_t *h_offsets, void *stream);
+
+/* utils/depth_utils.py:211-265 voxel_down_sample_with_colors.  vox_id (optional) receives, per
+ * input point, the rank of its voxel in first-occurrence order; h_voxel_keys (optional, host
+ * int64[n][3]) is not written by the device path.  cols / nrm may be NULL.  Returns the number of
+ * voxels (syncs).  Outputs must hold n rows. */
+int64_t ibl_voxel_downsample(const double *pts, const double *cols, const double *nrm, int64_t n, double voxel,
+                             double *out_pts, double *out_cols, double *out_nrm, int32_t *vox_id,
+                             int64_t *out_keys /* int64[n][3] floor(p/voxel), may be NULL */, void *stream);
+
+/* order-preserving row selection (Open3D SelectByIndex used by remove_radius_outlier).
+ * keep: uint8[n]; a/b/c are optional double[n][3] arrays compacted identically; out_index
+ * (optional int32) receives the kept indices.  Returns kept count (syncs). */
+int64_t ibl_select_rows(const uint8_t *keep, int64_t n, const double *a, const double *b, const double *c,
+                        double *out_a, double *out_b, double *out_c, int32_t *out_index, void *stream);
+
+/* Open3D PointCloud::Transform / translate (object_memory.py:1033-1034, fpfh_register ICP):
+ * out = ((T00*x + T01*y) + T02*z) + T03 per row; T is HOST row-major double[16]. rotate_only=1
+ * applies R only (normals). in==out allowed. */
+int ibl_transform_points(const double *h_T16, const double *in, int64_t n, int rotate_only, double *out,
+                         void *stream);
+/* sequential-order-independent column means (np.mean(points, axis=0), object_memory.py:1030):
+ * pairwise f64 reduction; h_mean host double[3]. Syncs. */
+int ibl_mean3(const double *pts, int64_t n, double *h_mean, void *stream);
+
+/* ---------------------------------------------------------------- uniform grid -------------- */
+typedef struct ibl_grid ibl_grid_t;
+/* Cell-sorted uniform grid over pts (replaces Open3D KDTreeFlann construction at every call
+ * site).  cell is a request: it is enlarged until nx*ny*nz <= max_cells (0 -> 2^24).  Syncs. */
+int ibl_grid_create(const double *pts, int64_t n, double cell, int64_t max_cells, ibl_grid_t **out, void *stream);
+void ibl_grid_destroy(ibl_grid_t *g);
+double ibl_grid_cell(const ibl_grid_t *g);
+int64_t ibl_grid_occupied(const ibl_grid_t *g);
+/* Chebyshev ring-distance field (uint8 per cell, capped) used to skip empty space in nn queries */
+int ibl_grid_build_ringfield(ibl_grid_t *g, int max_ring, void *stream);
+
+/* KDTreeFlann::SearchRadius count for every grid point against the grid (A.2):
+ * count[i] = #{j : d2(i,j) < r*r}.  depth_utils.py:41,87, object_memory.py:994. */
+int ibl_radius_count(const ibl_grid_t *g, double radius, int32_t *count, void *stream);
+/* keep[i] = count[i] > nb_points fused variant */
+int ibl_radius_outlier_mask(const ibl_grid_t *g, double radius, int32_t nb_points, uint8_t *keep, void *stream);
+
+/* KDTreeFlann::SearchHybrid(q, radius, max_nn) (A.1) for nq queries; queries==NULL means the
+ * grid's own points (row i of the output = point i).  idx int32[nq][max_nn] (-1 padded), d2
+ * double[nq][max_nn] (may be NULL), cnt int32[nq].  Ascending (d2, index). */
+int ibl_knn_hybrid(const ibl_grid_t *g, const double *queries, int64_t nq, double radius, int32_t max_nn,
+                   int32_t *idx, double *d2, int32_t *cnt, void *stream);
+
+/* SearchHybrid(q, max_d, 1) for every row of T*src (h_T16 may be NULL = identity): the body of
+ * GetRegistrationResultAndCorrespondences (A.6), used by evaluate_registration
+ * (fpfh_register.py:145-150) and each ICP iteration.  nn_idx int32[n] (-1 = none) and nn_d2
+ * optional.  h_result: host {int64 n_inliers; double err2}.  Syncs. */
+typedef struct { int64_t n_inliers; double err2; } ibl_score_t;
+int ibl_nn_score(const ibl_grid_t *g, const double *src, int64_t n, const double *h_T16, double max_d,
+                 int32_t *nn_idx, double *nn_d2, ibl_score_t *h_result, void *stream);
+
+/* ---------------------------------------------------------------- normals / FPFH ------------ */
+/* PointCloud::EstimateNormals(Hybrid) covariance + FastEigen3x3 (A.3), fpfh_register.py:90-92 */
+int ibl_normals(const double *pts, int64_t n, const int32_t *nbr_idx, const int32_t *nbr_cnt, int32_t max_nn,
+                double *normals, void *stream);
+/* ComputeSPFHFeature / ComputeFPFHFeature (A.4), fpfh_register.py:94-97.  Device layout is
+ * POINT-MAJOR: spfh, fpfh double[n][33] (the Python mirror exposes Open3D's [33][n] view). */
+int ibl_spfh(const double *pts, const double *nrm, int64_t n, const int32_t *nbr_idx, const int32_t *nbr_cnt,
+             int32_t max_nn, double *spfh, void *stream);
+int ibl_fpfh(int64_t n, const int32_t *nbr_idx, const double *nbr_d2, const int32_t *nbr_cnt, int32_t max_nn,
+             const double *spfh, double *fpfh, void *stream);
+/* exact 33-d nearest neighbour of every column of fa among the columns of fb (A.5 KDTreeFlann on
+ * features, SearchKNN k=1); lowest index wins ties.  fa double[na][33], fb double[nb][33]. */
+int ibl_feature_nn(const double *fa, int64_t na, const double *fb, int64_t nb, int32_t *nn, void *stream);
+/* mutual filter + fallback (A.5). ij int32[ns], ji int32[nt] -> corres int32[<=ns][2]; returns C. Syncs. */
+int64_t ibl_mutual_corres(const int32_t *ij, int64_t ns, const int32_t *ji, int64_t nt, int32_t ransac_n,
+                          int32_t *corres, void *stream);
+
+/* ---------------------------------------------------------------- RANSAC -------------------- */
+typedef struct {
+    double T[16];          /* row-major 4x4 */
+    double fitness;        /* n_inliers / n_src */
+    double inlier_rmse;    /* sqrt(err2 / n_inliers) */
+    int64_t n_inliers;
+    double err2;
+    int64_t best_hyp;      /* index of the winning hypothesis in the sample stream (-1 none) */
+    int64_t drawn;         /* hypotheses consumed before the adaptive stop */
+    int64_t validated;     /* hypotheses that passed the cheap checkers and were scored */
+    int64_t n_corres;
+    int32_t iterations;    /* ICP iterations performed */
+    int32_t status;        /* 0 ok; 1 = empty result (too few correspondences etc.) */
+} ibl_reg_result_t;
+
+/* Hypothesis samples: either an explicit host-seeded array samples int32[.][3] (device), or
+ * samples==NULL and the counter-based stream ibl_sample(seed, h, j, C) (rigid.cuh; restated in
+ * oracle/sampler.py so the oracle consumes identical draws). */
+
+/* A.7 hypothesis generation + EdgeLength/Distance checkers for hypotheses [h0, h0+H).
+ * pass uint8[H]; T_out double[H][16] optional (written only where pass, or everywhere when
+ * use_checkers==0).  fpfh_register.py:110-119. */
+int ibl_ransac_check(const double *src, const double *tgt, const int32_t *corres, int64_t n_corres,
+                     const int32_t *samples, uint64_t seed, int64_t h0, int64_t H, double edge_thr, double dist_thr,
+                     int use_checkers, uint8_t *pass, double *T_out, void *stream);
+/* Score hypotheses hyp_ids int64[nh] over the whole source (A.6): inliers int32[nh], err2
+ * double[nh], corres_inliers int32[nh] (EvaluateInlierCorrespondenceRatio numerator), T_out
+ * double[nh][16].  Source is tiled over CTAs; partials are combined in a fixed order. */
+int ibl_ransac_score(const ibl_grid_t *tgt_grid, const double *src, int64_t n_src, const double *tgt,
+                     const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
+                     const int64_t *hyp_ids, int64_t nh, double max_d, int32_t *inliers, double *err2,
+                     int32_t *corres_inliers, double *T_out, void *stream);
+/* Whole RegistrationRANSACBasedOnCorrespondence loop with sequential semantics (A.7): blocks of
+ * `block` hypotheses are checked, the survivors scored, and the ordered update / adaptive stop
+ * applied on the host.  Syncs. */
+int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_t n_src, const double *tgt,
+                   const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
+                   int64_t max_iteration, double confidence, double max_d, double edge_thr, int use_checkers,
+                   int early_exit, int64_t block, ibl_reg_result_t *h_result, void *stream);
+
+/* ---------------------------------------------------------------- ICP ----------------------- */
+/* InitializePointCloudForColoredICP (A.8): grad double[n][3] */
+int ibl_color_gradient(const double *pts, const double *nrm, const double *col, int64_t n, const int32_t *nbr_idx,
+                       const int32_t *nbr_cnt, int32_t max_nn, double *grad, void *stream);
+/* TransformationEstimationPointToPoint::ComputeTransformation over (i, nn_idx[i]>=0) pairs
+ * (A.9; Eigen::umeyama restated as Jacobi-Kabsch).  h_T16 host out.  Syncs. */
+int ibl_p2p_update(const double *src, const int32_t *nn_idx, int64_t n, const double *tgt, double *h_T16,
+                   void *stream);
+/* TransformationEstimationForColoredICP (A.8) over (i, nn_idx[i]>=0): h_out27 = 21 upper-triangle
+ * JTJ (row-major) + 6 JTr; h_T16 (optional) = the solved update.  Deterministic tree reduction. Syncs. */
+int ibl_colored_update(const double *src, const double *scol, const int32_t *nn_idx, int64_t n, const double *tgt,
+                       const double *tnrm, const double *tcol, const double *tgrad, double lambda_geometric,
+                       double *h_out27, double *h_T16, void *stream);
+/* RegistrationICP loop (A.9), fpfh_register.py:132-141.  mode 0 = point-to-point, 1 = coloured
+ * (scol/tnrm/tcol/tgrad required).  src is not modified.  Syncs every iteration (27 doubles). */
+int ibl_icp(const ibl_grid_t *tgt_grid, const double *src, const double *scol, int64_t n_src, const double *tgt,
+            const double *tnrm, const double *tcol, const double *tgrad, int mode, double max_d,
+            const double *h_T_init, int max_iteration, double rel_fitness, double rel_rmse, double lambda_geometric,
+            ibl_reg_result_t *h_result, void *stream);
+
+/* ---------------------------------------------------------------- similarity ---------------- */
+/* object_memory.py:922-936: S[i][j] = max over stored embeddings e of object j of <mem_e/|mem_e|,
+ * det_i/|det_i|>.  det float32[nd][D]; mem float32[E][D]; seg int32[m+1] CSR offsets. */
+int ibl_cosine_segmax(const float *det, int32_t nd, const float *mem, int64_t E, int32_t D, const int32_t *seg,
+                      int32_t m, float *S, void *stream);
+/* utils/similarity_volume.py:102-164,213-270 without materialising (m+1)^3: for every chosen
+ * combination of s=min(nd,3) detections, the k best masked fp16 products in (value desc, flat
+ * index asc) order.  S float32[nd][m] -> out_flat int64[n_comb][k], out_val float32[n_comb][k]
+ * (value = the fp16 product widened, -inf when exhausted with flat index 0). */
+int ibl_simvolume_topk(const float *S, int32_t nd, int32_t m, int32_t k, int64_t *out_flat, float *out_val,
+                       void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IBL_H_ */

@@ -1,0 +1,257 @@
+// cloud.cu -- depth -> per-mask clouds, order-preserving selection, voxel down-sampling, rigid
+// transforms (reference: utils/depth_utils.py:12-116,146-265).
+#include <cub/cub.cuh>
+
+#include "ibl_common.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// back-projection: each thread owns 4 consecutive pixels of one mask (float4 / uchar4 loads when
+// H*W % 4 == 0); pass 1 counts, pass 2 scatters at scanned offsets (row-major order preserved).
+template <typename DT>
+__device__ __forceinline__ void load4(const DT *__restrict__ depth, const uint8_t *__restrict__ mask, int64_t p0,
+                                      int64_t P, bool vec, DT d[4], uint8_t m[4]) {
+    if (vec && p0 + 3 < P) {
+        if constexpr (sizeof(DT) == 4) {
+            float4 v = *reinterpret_cast<const float4 *>(depth + p0);
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        } else {
+            double2 a = *reinterpret_cast<const double2 *>(depth + p0);
+            double2 b = *reinterpret_cast<const double2 *>(depth + p0 + 2);
+            d[0] = a.x; d[1] = a.y; d[2] = b.x; d[3] = b.y;
+        }
+        uchar4 mm = *reinterpret_cast<const uchar4 *>(mask + p0);
+        m[0] = mm.x; m[1] = mm.y; m[2] = mm.z; m[3] = mm.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            bool in = p0 + k < P;
+            d[k] = in ? depth[p0 + k] : (DT)0;
+            m[k] = in ? mask[p0 + k] : 0;
+        }
+    }
+}
+
+// depth * mask exactly as numpy: d*1 or d*0 (NaN*0 stays NaN and counts as != 0)
+template <typename DT>
+__device__ __forceinline__ DT masked(DT d, uint8_t m) { return m ? d : d * (DT)0; }
+
+template <typename DT>
+__global__ void __launch_bounds__(256) bp_count_kernel(const DT *__restrict__ depth, const uint8_t *__restrict__ masks,
+                                                       int64_t P, int ntiles, bool vec, int *__restrict__ counts) {
+    int mi = blockIdx.y, tile = blockIdx.x;
+    int64_t p0 = ((int64_t)tile * 256 + threadIdx.x) * 4;
+    DT d[4]; uint8_t m[4];
+    load4<DT>(depth, masks + (size_t)mi * P, p0, P, vec, d, m);
+    int c = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) c += (p0 + k < P) && (masked<DT>(d[k], m[k]) != (DT)0);
+    typedef cub::BlockReduce<int, 256> BR;
+    __shared__ typename BR::TempStorage ts;
+    int tot = BR(ts).Sum(c);
+    if (threadIdx.x == 0) counts[(size_t)mi * ntiles + tile] = tot;
+}
+
+template <typename DT>
+__global__ void __launch_bounds__(256) bp_write_kernel(const DT *__restrict__ depth, const uint8_t *__restrict__ rgb,
+                                                       const uint8_t *__restrict__ masks, int64_t P, int W, int ntiles,
+                                                       bool vec, const float *__restrict__ hor,
+                                                       const float *__restrict__ ver, double fx, double fy,
+                                                       const int64_t *__restrict__ offs, double *__restrict__ out_pts,
+                                                       double *__restrict__ out_cols) {
+    int mi = blockIdx.y, tile = blockIdx.x;
+    int64_t p0 = ((int64_t)tile * 256 + threadIdx.x) * 4;
+    DT d[4]; uint8_t m[4];
+    load4<DT>(depth, masks + (size_t)mi * P, p0, P, vec, d, m);
+    bool ok[4];
+    int c = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { d[k] = masked<DT>(d[k], m[k]); ok[k] = (p0 + k < P) && (d[k] != (DT)0); c += ok[k]; }
+    typedef cub::BlockScan<int, 256> BS;
+    __shared__ typename BS::TempStorage ts;
+    int pre;
+    BS(ts).ExclusiveSum(c, pre);
+    int64_t o = offs[(size_t)mi * ntiles + tile] + pre;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (!ok[k]) continue;
+        int64_t p = p0 + k;
+        int row = (int)(p / W), col = (int)(p - (int64_t)row * W);
+        double X, Y, Z;
+        if constexpr (sizeof(DT) == 4) {
+            // numpy: (f32 * f32) / f32(fx)  -- two roundings in float32
+            X = (double)__fdiv_rn(__fmul_rn(hor[col], d[k]), (float)fx);
+            Y = (double)__fdiv_rn(__fmul_rn(ver[row], d[k]), (float)fy);
+            Z = (double)d[k];
+        } else {
+            X = __ddiv_rn(__dmul_rn((double)hor[col], d[k]), fx);
+            Y = __ddiv_rn(__dmul_rn((double)ver[row], d[k]), fy);
+            Z = d[k];
+        }
+        out_pts[3 * o] = X; out_pts[3 * o + 1] = Y; out_pts[3 * o + 2] = Z;
+        if (out_cols) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) out_cols[3 * o + a] = (double)__fdiv_rn((float)rgb[3 * p + a], 255.0f);
+        }
+        ++o;
+    }
+}
+
+template <typename DT>
+static int backproject_impl(const DT *depth, const uint8_t *rgb, const uint8_t *masks, int n_masks, int H, int W,
+                            const float *hor, const float *ver, double fx, double fy, double *out_pts, double *out_cols,
+                            int64_t *h_offsets, cudaStream_t st) {
+    int64_t P = (int64_t)H * W;
+    int ntiles = (int)((P + 1023) / 1024);
+    bool vec = (P % 4 == 0) && ((uintptr_t)depth % 16 == 0) && ((uintptr_t)masks % 4 == 0);
+    size_t nc = (size_t)n_masks * ntiles;
+    int *counts = nullptr; int64_t *offs = nullptr;
+    IBL_CUDA(ibl_alloc(&counts, nc + 1, st));
+    IBL_CUDA(ibl_alloc(&offs, nc + 1, st));
+    IBL_CUDA(cudaMemsetAsync(counts + nc, 0, sizeof(int), st));
+    dim3 grid(ntiles, n_masks);
+    bp_count_kernel<DT><<<grid, 256, 0, st>>>(depth, masks, P, ntiles, vec, counts);
+    IBL_LAUNCH_CHECK();
+    size_t tb = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tb, counts, offs, (int)(nc + 1), st);
+    void *tmp = nullptr;
+    IBL_CUDA(cudaMallocAsync(&tmp, tb ? tb : 1, st));
+    IBL_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, counts, offs, (int)(nc + 1), st));
+    if (out_pts) {
+        bp_write_kernel<DT><<<grid, 256, 0, st>>>(depth, rgb, masks, P, W, ntiles, vec, hor, ver, fx, fy, offs, out_pts,
+                                                  rgb ? out_cols : nullptr);
+        IBL_LAUNCH_CHECK();
+    }
+    // per-mask offsets = offs[mi*ntiles]
+    int64_t *hall = (int64_t *)malloc(sizeof(int64_t) * (nc + 1));
+    IBL_CUDA(cudaMemcpyAsync(hall, offs, sizeof(int64_t) * (nc + 1), cudaMemcpyDeviceToHost, st));
+    IBL_CUDA(cudaStreamSynchronize(st));
+    for (int i = 0; i <= n_masks; ++i) h_offsets[i] = hall[(size_t)i * ntiles];
+    free(hall);
+    ibl_free(tmp, st); ibl_free(counts, st); ibl_free(offs, st);
+    return IBL_OK;
+}
+
+IBL_API int ibl_backproject_masks(const void *depth, int depth_is_f64, const uint8_t *rgb, const uint8_t *masks,
+                                  int n_masks, int H, int W, const float *hor, const float *ver, double fx, double fy,
+                                  double *out_pts, double *out_cols, int64_t *h_offsets, void *stream) {
+    IBL_ARG(depth && masks && hor && ver && h_offsets && n_masks >= 0 && H > 0 && W > 0);
+    if (n_masks == 0) { h_offsets[0] = 0; return IBL_OK; }
+    cudaStream_t st = ibl_stream(stream);
+    if (depth_is_f64)
+        return backproject_impl<double>((const double *)depth, rgb, masks, n_masks, H, W, hor, ver, fx, fy, out_pts,
+                                        out_cols, h_offsets, st);
+    return backproject_impl<float>((const float *)depth, rgb, masks, n_masks, H, W, hor, ver, fx, fy, out_pts, out_cols,
+                                   h_offsets, st);
+}
+
+// ------------------------------------------------------------------------------------------------
+// order-preserving selection
+struct U8ToInt {
+    __host__ __device__ int operator()(uint8_t v) const { return v ? 1 : 0; }
+};
+
+__global__ void select_scatter_kernel(const uint8_t *__restrict__ keep, const int *__restrict__ pos, int64_t n,
+                                      const double *__restrict__ a, const double *__restrict__ b,
+                                      const double *__restrict__ c, double *__restrict__ oa, double *__restrict__ ob,
+                                      double *__restrict__ oc, int32_t *__restrict__ oidx) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n || !keep[i]) return;
+    int64_t o = pos[i];
+    if (a) { oa[3 * o] = a[3 * i]; oa[3 * o + 1] = a[3 * i + 1]; oa[3 * o + 2] = a[3 * i + 2]; }
+    if (b) { ob[3 * o] = b[3 * i]; ob[3 * o + 1] = b[3 * i + 1]; ob[3 * o + 2] = b[3 * i + 2]; }
+    if (c) { oc[3 * o] = c[3 * i]; oc[3 * o + 1] = c[3 * i + 1]; oc[3 * o + 2] = c[3 * i + 2]; }
+    if (oidx) oidx[o] = (int32_t)i;
+}
+
+IBL_API int64_t ibl_select_rows(const uint8_t *keep, int64_t n, const double *a, const double *b, const double *c,
+                                double *out_a, double *out_b, double *out_c, int32_t *out_index, void *stream) {
+    IBL_ARG(n >= 0 && n < (1ll << 31));
+    if (n == 0) return 0;
+    IBL_ARG(keep != nullptr);
+    cudaStream_t st = ibl_stream(stream);
+    int *pos = nullptr;
+    IBL_CUDA(ibl_alloc(&pos, (size_t)n + 1, st));
+    cub::TransformInputIterator<int, U8ToInt, const uint8_t *> it(keep, U8ToInt());
+    size_t tb = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tb, it, pos, (int)n, st);
+    void *tmp = nullptr;
+    IBL_CUDA(cudaMallocAsync(&tmp, tb ? tb : 1, st));
+    IBL_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, it, pos, (int)n, st));
+    int nb = (int)((n + 255) / 256);
+    select_scatter_kernel<<<nb, 256, 0, st>>>(keep, pos, n, a, b, c, out_a, out_b, out_c, out_index);
+    IBL_LAUNCH_CHECK();
+    int last_pos = 0; uint8_t last_keep = 0;
+    IBL_CUDA(cudaMemcpyAsync(&last_pos, pos + (n - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+    IBL_CUDA(cudaMemcpyAsync(&last_keep, keep + (n - 1), 1, cudaMemcpyDeviceToHost, st));
+    IBL_CUDA(cudaStreamSynchronize(st));
+    ibl_free(tmp, st); ibl_free(pos, st);
+    return (int64_t)last_pos + (last_keep ? 1 : 0);
+}
+
+// ------------------------------------------------------------------------------------------------
+struct Mat16c { double v[16]; };
+__global__ void transform_kernel(Mat16c T, const double *__restrict__ in, int64_t n, int rotate_only,
+                                 double *__restrict__ out) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double x = in[3 * i], y = in[3 * i + 1], z = in[3 * i + 2], a, b, c;
+    if (rotate_only) {
+        a = __dadd_rn(__dadd_rn(__dmul_rn(T.v[0], x), __dmul_rn(T.v[1], y)), __dmul_rn(T.v[2], z));
+        b = __dadd_rn(__dadd_rn(__dmul_rn(T.v[4], x), __dmul_rn(T.v[5], y)), __dmul_rn(T.v[6], z));
+        c = __dadd_rn(__dadd_rn(__dmul_rn(T.v[8], x), __dmul_rn(T.v[9], y)), __dmul_rn(T.v[10], z));
+    } else {
+        ibl_xform(T.v, x, y, z, a, b, c);
+    }
+    out[3 * i] = a; out[3 * i + 1] = b; out[3 * i + 2] = c;
+}
+IBL_API int ibl_transform_points(const double *h_T16, const double *in, int64_t n, int rotate_only, double *out,
+                                 void *stream) {
+    IBL_ARG(h_T16 && n >= 0);
+    if (n == 0) return IBL_OK;
+    Mat16c T;
+    memcpy(T.v, h_T16, sizeof(T.v));
+    int nb = (int)((n + 255) / 256);
+    transform_kernel<<<nb, 256, 0, ibl_stream(stream)>>>(T, in, n, rotate_only, out);
+    IBL_LAUNCH_CHECK();
+    return IBL_OK;
+}
+
+// column sums: per-block fixed tree, partials finished on host in index order
+__global__ void __launch_bounds__(256) sum3_kernel(const double *__restrict__ pts, int64_t n, double *__restrict__ part) {
+    double s[3] = {0, 0, 0};
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        s[0] += pts[3 * i]; s[1] += pts[3 * i + 1]; s[2] += pts[3 * i + 2];
+    }
+    __shared__ double sm[3][8];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        for (int o = 16; o; o >>= 1) s[a] += __shfl_down_sync(0xffffffffu, s[a], o);
+        if (lane == 0) sm[a][w] = s[a];
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        double t = 0;
+        for (int k = 0; k < 8; ++k) t += sm[threadIdx.x][k];
+        part[blockIdx.x * 3 + threadIdx.x] = t;
+    }
+}
+IBL_API int ibl_mean3(const double *pts, int64_t n, double *h_mean, void *stream) {
+    IBL_ARG(h_mean && n >= 0);
+    h_mean[0] = h_mean[1] = h_mean[2] = 0.0;
+    if (n == 0) return IBL_OK;
+    cudaStream_t st = ibl_stream(stream);
+    int nb = (int)((n + 2047) / 2048);
+    if (nb > IBL_SMS * 2) nb = IBL_SMS * 2;
+    double *part = nullptr;
+    IBL_CUDA(ibl_alloc(&part, (size_t)nb * 3, st));
+    sum3_kernel<<<nb, 256, 0, st>>>(pts, n, part);
+    IBL_LAUNCH_CHECK();
+    double hp[IBL_SMS * 2 * 3];
+    IBL_CUDA(cudaMemcpyAsync(hp, part, sizeof(double) * nb * 3, cudaMemcpyDeviceToHost, st));
+    IBL_CUDA(cudaStreamSynchronize(st));
+    ibl_free(part, st);
+    for (int b = 0; b < nb; ++b) for (int a = 0; a < 3; ++a) h_mean[a] += hp[b * 3 + a];
+    for (int a = 0; a < 3; ++a) h_mean[a] /= (double)n;
+    return IBL_OK;
+}

@@ -1,0 +1,312 @@
+// grid_query.cu -- exact neighbour queries on the cell-sorted grid.
+//   radius count  : warp per query, contiguous x-rows of cells streamed with coalesced 32 B loads
+//   hybrid k-NN   : warp per query, Chebyshev ring expansion, shared-memory candidate buffer,
+//                   warp bitonic sort on (d2 bits, index) -> ascending (d2, index) like the oracle
+//   1-NN + score  : thread per query (ring field skips empty space), deterministic block reduce
+#include "ibl_common.cuh"
+
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) radius_count_kernel(GridView g, int64_t n, double r2, int S, int32_t nb_points,
+                                                           int32_t *__restrict__ count, uint8_t *__restrict__ keep) {
+    int lane = threadIdx.x & 31;
+    int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t qi = warp; qi < n; qi += nwarps) {
+        double4 q = g.sorted[qi];
+        int cx = ibl_clampi(ibl_cell_coord(q.x, g.ox, g.inv_cell, g.nx), 0, g.nx - 1);
+        int cy = ibl_clampi(ibl_cell_coord(q.y, g.oy, g.inv_cell, g.ny), 0, g.ny - 1);
+        int cz = ibl_clampi(ibl_cell_coord(q.z, g.oz, g.inv_cell, g.nz), 0, g.nz - 1);
+        int x0 = max(cx - S, 0), x1 = min(cx + S, g.nx - 1);
+        int y0 = max(cy - S, 0), y1 = min(cy + S, g.ny - 1);
+        int z0 = max(cz - S, 0), z1 = min(cz + S, g.nz - 1);
+        int c = 0;
+        for (int z = z0; z <= z1; ++z)
+            for (int y = y0; y <= y1; ++y) {
+                size_t rb = ((size_t)z * g.ny + y) * g.nx;
+                int p0 = g.cell_start[rb + x0], p1 = g.cell_start[rb + x1 + 1];
+                for (int p = p0 + lane; p < p1; p += 32) {
+                    double4 t = g.sorted[p];
+                    c += ibl_d2(t.x, t.y, t.z, q.x, q.y, q.z) < r2;
+                }
+            }
+        for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        if (lane == 0) {
+            int oi = (int)__double_as_longlong(q.w);
+            if (count) count[oi] = c;
+            if (keep) keep[oi] = c > nb_points;
+        }
+    }
+}
+
+static int radius_launch(const ibl_grid_t *g, double radius, int32_t nb, int32_t *count, uint8_t *keep, void *stream) {
+    IBL_ARG(g != nullptr && radius > 0);
+    if (g->n == 0) return IBL_OK;
+    int S = (int)ceil(radius * g->inv_cell + 1e-6);
+    int64_t warps_needed = g->n;
+    int blocks = (int)((warps_needed * 32 + 255) / 256);
+    int maxb = IBL_SMS * 16;
+    if (blocks > maxb) blocks = maxb;
+    radius_count_kernel<<<blocks, 256, 0, ibl_stream(stream)>>>(ibl_view(g), g->n, radius * radius, S, nb, count, keep);
+    IBL_LAUNCH_CHECK();
+    return IBL_OK;
+}
+IBL_API int ibl_radius_count(const ibl_grid_t *g, double radius, int32_t *count, void *stream) {
+    return radius_launch(g, radius, 0, count, nullptr, stream);
+}
+IBL_API int ibl_radius_outlier_mask(const ibl_grid_t *g, double radius, int32_t nb_points, uint8_t *keep, void *stream) {
+    return radius_launch(g, radius, nb_points, nullptr, keep, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// hybrid k-NN
+struct KnnBuf {
+    unsigned long long *key;   // d2 bit pattern (non-negative doubles order like uint64)
+    int *val;                  // original index
+};
+
+__device__ __forceinline__ bool knn_less(unsigned long long ka, int va, unsigned long long kb, int vb) {
+    return ka < kb || (ka == kb && va < vb);
+}
+
+// warp-cooperative bitonic sort of buf[0..n2) (n2 power of two >= 32)
+__device__ void knn_sort(KnnBuf b, int n2, int lane) {
+    for (int k = 2; k <= n2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = lane; t < (n2 >> 1); t += 32) {
+                int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                int p = i | j;
+                bool up = (i & k) == 0;
+                unsigned long long ka = b.key[i], kb = b.key[p];
+                int va = b.val[i], vb = b.val[p];
+                bool gt = knn_less(kb, vb, ka, va);
+                if (gt == up) { b.key[i] = kb; b.val[i] = vb; b.key[p] = ka; b.val[p] = va; }
+            }
+            __syncwarp();
+        }
+    }
+}
+
+__device__ __forceinline__ int next_pow2_ge32(int c) {
+    int n2 = 32;
+    while (n2 < c) n2 <<= 1;
+    return n2;
+}
+
+template <int CAP>
+__global__ void __launch_bounds__(128) knn_kernel(GridView g, const double *__restrict__ queries, int64_t nq,
+                                                  double radius, double r2, int max_nn, int32_t *__restrict__ idx,
+                                                  double *__restrict__ d2out, int32_t *__restrict__ cnt) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    KnnBuf b;
+    b.key = reinterpret_cast<unsigned long long *>(smem_raw) + (size_t)wib * CAP;
+    b.val = reinterpret_cast<int *>(smem_raw + sizeof(unsigned long long) * CAP * (blockDim.x >> 5)) + (size_t)wib * CAP;
+    int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    int s_rad = isfinite(radius) ? (int)ceil(radius * g.inv_cell + 1e-6) : 0x3fffffff;
+    for (int64_t qi = warp; qi < nq; qi += nwarps) {
+        double qx, qy, qz;
+        int64_t row;
+        if (queries == nullptr) {
+            double4 q = g.sorted[qi];
+            qx = q.x; qy = q.y; qz = q.z;
+            row = (int64_t)__double_as_longlong(q.w);
+        } else {
+            qx = queries[3 * qi]; qy = queries[3 * qi + 1]; qz = queries[3 * qi + 2];
+            row = qi;
+        }
+        int cx = ibl_cell_coord(qx, g.ox, g.inv_cell, g.nx);
+        int cy = ibl_cell_coord(qy, g.oy, g.inv_cell, g.ny);
+        int cz = ibl_cell_coord(qz, g.oz, g.inv_cell, g.nz);
+        int count = 0;
+        bool have_tau = false;
+        unsigned long long tau_k = ~0ull;
+        int tau_v = 0x7fffffff;
+        // rings needed to reach the grid box from an outside query
+        int s_begin;
+        {
+            int kx = ibl_clampi(cx, 0, g.nx - 1), ky = ibl_clampi(cy, 0, g.ny - 1), kz = ibl_clampi(cz, 0, g.nz - 1);
+            s_begin = max(max(abs(cx - kx), abs(cy - ky)), abs(cz - kz));
+        }
+        for (int s = s_begin;; ++s) {
+            int z0 = max(cz - s, 0), z1 = min(cz + s, g.nz - 1);
+            int y0 = max(cy - s, 0), y1 = min(cy + s, g.ny - 1);
+            for (int z = z0; z <= z1; ++z) {
+                bool zedge = (z == cz - s) || (z == cz + s);
+                for (int y = y0; y <= y1; ++y) {
+                    bool edge = zedge || (y == cy - s) || (y == cy + s);
+                    size_t rb = ((size_t)z * g.ny + y) * g.nx;
+                    int nseg = edge ? 1 : 2;
+                    for (int seg = 0; seg < nseg; ++seg) {
+                        int xa, xb;
+                        if (edge) { xa = cx - s; xb = cx + s; }
+                        else if (seg == 0) { xa = xb = cx - s; }
+                        else { xa = xb = cx + s; }
+                        xa = max(xa, 0); xb = min(xb, g.nx - 1);
+                        if (xa > xb) continue;
+                        int p0 = g.cell_start[rb + xa], p1 = g.cell_start[rb + xb + 1];
+                        for (int pb = p0; pb < p1; pb += 32) {
+                            if (count + 32 > CAP) {   // compact: keep the max_nn best, remember threshold
+                                int n2 = next_pow2_ge32(count);
+                                for (int t = count + lane; t < n2; t += 32) { b.key[t] = ~0ull; b.val[t] = 0x7fffffff; }
+                                __syncwarp();
+                                knn_sort(b, n2, lane);
+                                if (count >= max_nn) {
+                                    count = max_nn;
+                                    have_tau = true;
+                                    tau_k = b.key[max_nn - 1];
+                                    tau_v = b.val[max_nn - 1];
+                                }
+                                __syncwarp();
+                            }
+                            int p = pb + lane;
+                            bool ok = false;
+                            unsigned long long kk = 0;
+                            int vv = 0;
+                            if (p < p1) {
+                                double4 t = g.sorted[p];
+                                double d2 = ibl_d2(t.x, t.y, t.z, qx, qy, qz);
+                                kk = (unsigned long long)__double_as_longlong(d2);
+                                vv = (int)__double_as_longlong(t.w);
+                                ok = d2 < r2 && (!have_tau || knn_less(kk, vv, tau_k, tau_v));
+                            }
+                            unsigned m = __ballot_sync(0xffffffffu, ok);
+                            if (ok) {
+                                int pos = count + __popc(m & lt_mask);
+                                b.key[pos] = kk;
+                                b.val[pos] = vv;
+                            }
+                            count += __popc(m);
+                            __syncwarp();
+                        }
+                    }
+                }
+            }
+            // termination tests
+            bool covers = (cx - s <= 0) && (cx + s >= g.nx - 1) && (cy - s <= 0) && (cy + s >= g.ny - 1) &&
+                          (cz - s <= 0) && (cz + s >= g.nz - 1);
+            if (covers || s >= s_rad) break;
+            if (count >= max_nn) {
+                double gr = ((double)s - 1e-6) * g.cell;
+                if (gr > 0) {
+                    unsigned long long gk = (unsigned long long)__double_as_longlong(gr * gr);
+                    int inside = 0;
+                    for (int t = lane; t < count; t += 32) inside += b.key[t] <= gk;
+                    for (int o = 16; o; o >>= 1) inside += __shfl_xor_sync(0xffffffffu, inside, o);
+                    if (inside >= max_nn) break;
+                }
+            }
+        }
+        // final ordering
+        int n2 = next_pow2_ge32(count);
+        for (int t = count + lane; t < n2; t += 32) { b.key[t] = ~0ull; b.val[t] = 0x7fffffff; }
+        __syncwarp();
+        knn_sort(b, n2, lane);
+        int outc = min(count, max_nn);
+        for (int t = lane; t < max_nn; t += 32) {
+            bool v = t < outc;
+            idx[row * max_nn + t] = v ? b.val[t] : -1;
+            if (d2out) d2out[row * max_nn + t] = v ? __longlong_as_double((long long)b.key[t]) : INFINITY;
+        }
+        if (lane == 0) cnt[row] = outc;
+        __syncwarp();
+    }
+}
+
+IBL_API int ibl_knn_hybrid(const ibl_grid_t *g, const double *queries, int64_t nq, double radius, int32_t max_nn,
+                           int32_t *idx, double *d2, int32_t *cnt, void *stream) {
+    IBL_ARG(g != nullptr && max_nn >= 1 && max_nn <= 224 && idx != nullptr && cnt != nullptr && radius > 0);
+    if (queries == nullptr) nq = g->n;
+    if (nq == 0) return IBL_OK;
+    cudaStream_t st = ibl_stream(stream);
+    const int threads = 128, wpb = threads / 32;
+    int64_t blocks64 = (nq + wpb - 1) / wpb;
+    int blocks = (int)(blocks64 > IBL_SMS * 32 ? IBL_SMS * 32 : blocks64);
+    double r2 = isfinite(radius) ? radius * radius : INFINITY;
+    if (max_nn <= 96) {
+        constexpr int CAP = 256;
+        size_t sm = (size_t)wpb * CAP * 12;
+        knn_kernel<CAP><<<blocks, threads, sm, st>>>(ibl_view(g), queries, nq, radius, r2, max_nn, idx, d2, cnt);
+    } else {
+        constexpr int CAP = 512;
+        size_t sm = (size_t)wpb * CAP * 12;
+        knn_kernel<CAP><<<blocks, threads, sm, st>>>(ibl_view(g), queries, nq, radius, r2, max_nn, idx, d2, cnt);
+    }
+    IBL_LAUNCH_CHECK();
+    return IBL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// 1-NN + registration score
+struct Mat16 { double v[16]; };
+
+__global__ void __launch_bounds__(256) nn_score_kernel(GridView g, const double *__restrict__ src, int64_t n, Mat16 T,
+                                                       int has_T, double max_d, double max_d2,
+                                                       int32_t *__restrict__ nn_idx, double *__restrict__ nn_d2,
+                                                       long long *__restrict__ part_cnt, double *__restrict__ part_err) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int hit = 0;
+    double e = 0.0;
+    if (i < n) {
+        double x = src[3 * i], y = src[3 * i + 1], z = src[3 * i + 2];
+        if (has_T) { double a, b, c; ibl_xform(T.v, x, y, z, a, b, c); x = a; y = b; z = c; }
+        double bd;
+        int j = ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd);
+        if (nn_idx) nn_idx[i] = j;
+        if (nn_d2) nn_d2[i] = j >= 0 ? bd : INFINITY;
+        if (j >= 0) { hit = 1; e = bd; }
+    }
+    // deterministic block reduction (fixed shuffle tree, then warp 0 in index order)
+    __shared__ double se[8];
+    __shared__ int sc[8];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int o = 16; o; o >>= 1) { e += __shfl_down_sync(0xffffffffu, e, o); hit += __shfl_down_sync(0xffffffffu, hit, o); }
+    if (lane == 0) { se[w] = e; sc[w] = hit; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double te = 0; long long tc = 0;
+        for (int k = 0; k < 8; ++k) { te += se[k]; tc += sc[k]; }
+        part_cnt[blockIdx.x] = tc;
+        part_err[blockIdx.x] = te;
+    }
+}
+
+__global__ void score_final_kernel(const long long *part_cnt, const double *part_err, int nb, ibl_score_t *out) {
+    // single warp, fixed order: lane-strided partial sums then shuffle tree
+    int lane = threadIdx.x;
+    double e = 0; long long c = 0;
+    for (int k = lane; k < nb; k += 32) { e += part_err[k]; c += part_cnt[k]; }
+    for (int o = 16; o; o >>= 1) { e += __shfl_down_sync(0xffffffffu, e, o); c += __shfl_down_sync(0xffffffffu, c, o); }
+    if (lane == 0) { out->n_inliers = c; out->err2 = e; }
+}
+
+IBL_API int ibl_nn_score(const ibl_grid_t *g, const double *src, int64_t n, const double *h_T16, double max_d,
+                         int32_t *nn_idx, double *nn_d2, ibl_score_t *h_result, void *stream) {
+    IBL_ARG(g != nullptr && n >= 0 && max_d > 0);
+    cudaStream_t st = ibl_stream(stream);
+    ibl_score_t res = {0, 0.0};
+    if (n > 0 && g->n > 0) {
+        Mat16 T;
+        int has_T = h_T16 != nullptr;
+        for (int k = 0; k < 16; ++k) T.v[k] = has_T ? h_T16[k] : ((k % 5 == 0) ? 1.0 : 0.0);
+        int nb = (int)((n + 255) / 256);
+        long long *pc = nullptr; double *pe = nullptr; ibl_score_t *dres = nullptr;
+        IBL_CUDA(ibl_alloc(&pc, (size_t)nb, st));
+        IBL_CUDA(ibl_alloc(&pe, (size_t)nb, st));
+        IBL_CUDA(ibl_alloc(&dres, 1, st));
+        nn_score_kernel<<<nb, 256, 0, st>>>(ibl_view(g), src, n, T, has_T, max_d, max_d * max_d, nn_idx, nn_d2, pc, pe);
+        IBL_LAUNCH_CHECK();
+        score_final_kernel<<<1, 32, 0, st>>>(pc, pe, nb, dres);
+        IBL_LAUNCH_CHECK();
+        if (h_result) {
+            IBL_CUDA(cudaMemcpyAsync(&res, dres, sizeof(res), cudaMemcpyDeviceToHost, st));
+            IBL_CUDA(cudaStreamSynchronize(st));
+        }
+        ibl_free(pc, st); ibl_free(pe, st); ibl_free(dres, st);
+    } else if (n > 0 && nn_idx) {
+        IBL_CUDA(cudaMemsetAsync(nn_idx, 0xff, sizeof(int32_t) * (size_t)n, st));
+    }
+    if (h_result) *h_result = res;
+    return IBL_OK;
+}

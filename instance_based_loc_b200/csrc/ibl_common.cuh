@@ -1,0 +1,197 @@
+// ibl_common.cuh -- shared device/host helpers for libibl.so (sm_100a).
+// All f64 arithmetic that decides a count or an index uses explicit _rn intrinsics so the result
+// does not depend on FMA contraction (the library is also built with -fmad=false).
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/ibl.h"
+
+#define IBL_API extern "C" __attribute__((visibility("default")))
+
+void ibl_set_error(const char *fmt, ...);
+
+#define IBL_CUDA(call)                                                                          \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess) {                                                               \
+            ibl_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+            return IBL_E_CUDA;                                                                  \
+        }                                                                                       \
+    } while (0)
+
+#define IBL_ARG(cond)                                                            \
+    do {                                                                         \
+        if (!(cond)) {                                                           \
+            ibl_set_error("%s:%d bad argument: %s", __FILE__, __LINE__, #cond);  \
+            return IBL_E_ARG;                                                    \
+        }                                                                        \
+    } while (0)
+
+#define IBL_LAUNCH_CHECK() IBL_CUDA(cudaGetLastError())
+
+static inline cudaStream_t ibl_stream(void *s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// number of SMs on B200; grids of grid-stride kernels are sized in multiples of this
+#define IBL_SMS 148
+
+// stream-ordered scratch allocation (cudaMallocAsync pool: no device sync on free)
+template <class T>
+static inline cudaError_t ibl_alloc(T **p, size_t count, cudaStream_t st) {
+    if (count == 0) count = 1;
+    return cudaMallocAsync(reinterpret_cast<void **>(p), count * sizeof(T), st);
+}
+static inline void ibl_free(void *p, cudaStream_t st) {
+    if (p) cudaFreeAsync(p, st);
+}
+
+// ------------------------------------------------------------------------------------------------
+struct ibl_grid {
+    int64_t n;            // points
+    double ox, oy, oz;    // origin (min corner)
+    double cell, inv_cell;
+    int nx, ny, nz;
+    int64_t ncells;
+    int64_t n_occupied;
+    const double *pts;    // caller's points (original order), not owned
+    int *cell_start;      // [ncells+1]
+    double4 *sorted;      // cell-sorted (x, y, z, bits(orig index))
+    int *order;           // sorted position -> original index
+    uint8_t *ring;        // optional Chebyshev ring-distance field [ncells]
+    int ring_cap;
+};
+
+// device view passed by value to kernels
+struct GridView {
+    double ox, oy, oz, cell, inv_cell;
+    int nx, ny, nz;
+    const int *cell_start;
+    const double4 *sorted;
+    const uint8_t *ring;
+    int ring_cap;
+};
+
+static inline GridView ibl_view(const ibl_grid *g) {
+    GridView v;
+    v.ox = g->ox; v.oy = g->oy; v.oz = g->oz; v.cell = g->cell; v.inv_cell = g->inv_cell;
+    v.nx = g->nx; v.ny = g->ny; v.nz = g->nz;
+    v.cell_start = g->cell_start; v.sorted = g->sorted; v.ring = g->ring; v.ring_cap = g->ring_cap;
+    return v;
+}
+
+// exact nanoflann L2: (dx*dx + dy*dy) + dz*dz, every op rounded once
+__device__ __forceinline__ double ibl_d2(double ax, double ay, double az, double bx, double by, double bz) {
+    double dx = __dsub_rn(ax, bx), dy = __dsub_rn(ay, by), dz = __dsub_rn(az, bz);
+    return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+}
+
+__device__ __forceinline__ int ibl_cell_coord(double p, double o, double inv, int /*n*/) {
+    double c = floor((p - o) * inv);
+    c = fmin(fmax(c, -1.0e9), 1.0e9);
+    return (int)c;
+}
+
+__device__ __forceinline__ int ibl_clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// Transform one point with the Open3D/Eigen (non-FMA) order ((T0*x + T1*y) + T2*z) + T3
+__device__ __forceinline__ void ibl_xform(const double *T, double x, double y, double z, double &ox, double &oy,
+                                          double &oz) {
+    ox = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(T[0], x), __dmul_rn(T[1], y)), __dmul_rn(T[2], z)), T[3]);
+    oy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(T[4], x), __dmul_rn(T[5], y)), __dmul_rn(T[6], z)), T[7]);
+    oz = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(T[8], x), __dmul_rn(T[9], y)), __dmul_rn(T[10], z)), T[11]);
+}
+
+// Nearest neighbour of q within max_d (strict d2 < max_d2) by expanding Chebyshev rings.
+// Returns original index or -1; best_d2 out.  Single-thread version (one query per thread).
+__device__ __forceinline__ int ibl_nn1_thread(const GridView &g, double qx, double qy, double qz, double max_d,
+                                              double max_d2, double &best_d2) {
+    int cx = ibl_cell_coord(qx, g.ox, g.inv_cell, g.nx);
+    int cy = ibl_cell_coord(qy, g.oy, g.inv_cell, g.ny);
+    int cz = ibl_cell_coord(qz, g.oz, g.inv_cell, g.nz);
+    double best = max_d2;
+    long long best_key = -1;   // original index
+    int s_max = (int)ceil(max_d * g.inv_cell) + 1;
+    int s0 = 0;
+    // quick reject / ring skip through the ring-distance field
+    if (g.ring != nullptr) {
+        int kx = ibl_clampi(cx, 0, g.nx - 1), ky = ibl_clampi(cy, 0, g.ny - 1), kz = ibl_clampi(cz, 0, g.nz - 1);
+        int out = max(max(abs(cx - kx), abs(cy - ky)), abs(cz - kz));   // rings to reach the grid box
+        int rf = g.ring[((size_t)kz * g.ny + ky) * g.nx + kx];          // rings from clamped cell to data
+        // nearest occupied cell is at Chebyshev distance >= max(out, rf - out) from (cx,cy,cz)
+        int lb = max(out, rf - out);
+        if (rf >= g.ring_cap && out == 0) lb = max(lb, g.ring_cap);
+        s0 = max(lb, 0);
+    } else {
+        int kx = ibl_clampi(cx, 0, g.nx - 1), ky = ibl_clampi(cy, 0, g.ny - 1), kz = ibl_clampi(cz, 0, g.nz - 1);
+        s0 = max(max(abs(cx - kx), abs(cy - ky)), abs(cz - kz));
+    }
+    for (int s = s0; s <= s_max; ++s) {
+        // everything in rings >= s is farther than (s-1)*cell (minus fp margin)
+        if (s > 0) {
+            double gr = ((double)(s - 1) - 1e-6) * g.cell;
+            if (gr > 0 && gr * gr >= best) break;
+        }
+        int z0 = max(cz - s, 0), z1 = min(cz + s, g.nz - 1);
+        int y0 = max(cy - s, 0), y1 = min(cy + s, g.ny - 1);
+        for (int z = z0; z <= z1; ++z) {
+            bool zedge = (z == cz - s) || (z == cz + s);
+            for (int y = y0; y <= y1; ++y) {
+                bool edge = zedge || (y == cy - s) || (y == cy + s);
+                size_t rowbase = ((size_t)z * g.ny + y) * g.nx;
+                int nseg = edge ? 1 : (s == 0 ? 1 : 2);
+                for (int seg = 0; seg < nseg; ++seg) {
+                    int xa, xb;
+                    if (edge || s == 0) { xa = cx - s; xb = cx + s; }
+                    else if (seg == 0) { xa = xb = cx - s; }
+                    else { xa = xb = cx + s; }
+                    xa = max(xa, 0); xb = min(xb, g.nx - 1);
+                    if (xa > xb) continue;
+                    int p0 = g.cell_start[rowbase + xa], p1 = g.cell_start[rowbase + xb + 1];
+                    for (int p = p0; p < p1; ++p) {
+                        double4 t = g.sorted[p];
+                        double d2 = ibl_d2(t.x, t.y, t.z, qx, qy, qz);
+                        long long oi = (long long)__double_as_longlong(t.w);
+                        if (d2 < best || (d2 == best && best_key >= 0 && oi < best_key)) { best = d2; best_key = oi; }
+                    }
+                }
+            }
+        }
+    }
+    best_d2 = best;
+    return (int)best_key;
+}
+
+// ------------------------------------------------------------------------------------------------
+// bounding box: per-block partial min/max (fixed tree), finished on the host
+static __global__ void bbox_kernel(const double *__restrict__ pts, int64_t n, double *__restrict__ part) {
+    double mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            double v = pts[3 * i + a];
+            mn[a] = fmin(mn[a], v);
+            mx[a] = fmax(mx[a], v);
+        }
+    }
+    __shared__ double sm[6][32];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        for (int o = 16; o; o >>= 1) {
+            mn[a] = fmin(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+            mx[a] = fmax(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+        }
+        if (lane == 0) { sm[a][w] = mn[a]; sm[3 + a][w] = mx[a]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        int nw = blockDim.x >> 5;
+        double v = sm[threadIdx.x][0];
+        for (int k = 1; k < nw; ++k) v = threadIdx.x < 3 ? fmin(v, sm[threadIdx.x][k]) : fmax(v, sm[threadIdx.x][k]);
+        part[blockIdx.x * 6 + threadIdx.x] = v;
+    }
+}
+

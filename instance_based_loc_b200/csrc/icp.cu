@@ -1,0 +1,276 @@
+// icp.cu -- RegistrationICP loop, point-to-point and coloured estimators, colour-gradient
+// initialisation (Open3D Registration.cpp / ColoredICP.cpp as called from
+// utils/fpfh_register.py:132-141).
+// Normal equations are reduced with warp shuffles (fixed tree) -> CTA -> per-CTA partials that the
+// host adds in index order: deterministic run to run.
+#include <vector>
+
+#include "ibl_common.cuh"
+#include "rigid.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// generic K-wide deterministic reduction: f(i, v[K]) fills the contribution of element i
+template <int K, class F>
+__global__ void __launch_bounds__(256) reduceK_kernel(int64_t n, F f, double *__restrict__ part) {
+    double acc[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) acc[k] = 0.0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        double v[K];
+        if (f(i, v)) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) acc[k] += v[k];
+        }
+    }
+    __shared__ double sm[8][K];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        double x = acc[k];
+        for (int o = 16; o; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+        if (lane == 0) sm[w][k] = x;
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        double t = 0;
+        for (int ww = 0; ww < 8; ++ww) t += sm[ww][k];
+        part[(size_t)blockIdx.x * K + k] = t;
+    }
+}
+
+template <int K, class F>
+static int reduceK(int64_t n, F f, double *h_out, cudaStream_t st) {
+    for (int k = 0; k < K; ++k) h_out[k] = 0.0;
+    if (n == 0) return IBL_OK;
+    int nb = (int)((n + 1023) / 1024);
+    if (nb > IBL_SMS * 2) nb = IBL_SMS * 2;
+    double *part = nullptr;
+    IBL_CUDA(ibl_alloc(&part, (size_t)nb * K, st));
+    reduceK_kernel<K, F><<<nb, 256, 0, st>>>(n, f, part);
+    IBL_LAUNCH_CHECK();
+    std::vector<double> hp((size_t)nb * K);
+    IBL_CUDA(cudaMemcpyAsync(hp.data(), part, sizeof(double) * nb * K, cudaMemcpyDeviceToHost, st));
+    IBL_CUDA(cudaStreamSynchronize(st));
+    ibl_free(part, st);
+    for (int b = 0; b < nb; ++b)
+        for (int k = 0; k < K; ++k) h_out[k] += hp[(size_t)b * K + k];
+    return IBL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+struct P2PSums {   // count, sum s(3), sum t(3)
+    const double *src; const int32_t *nn; const double *tgt;
+    __device__ bool operator()(int64_t i, double *v) const {
+        int j = nn[i];
+        if (j < 0) return false;
+        v[0] = 1.0;
+        for (int a = 0; a < 3; ++a) { v[1 + a] = src[3 * i + a]; v[4 + a] = tgt[3 * (size_t)j + a]; }
+        return true;
+    }
+};
+struct P2PCov {    // sum (t-mt)(s-ms)^T
+    const double *src; const int32_t *nn; const double *tgt; double ms[3], mt[3];
+    __device__ bool operator()(int64_t i, double *v) const {
+        int j = nn[i];
+        if (j < 0) return false;
+        double ds[3], dt[3];
+        for (int a = 0; a < 3; ++a) { ds[a] = src[3 * i + a] - ms[a]; dt[a] = tgt[3 * (size_t)j + a] - mt[a]; }
+        for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) v[3 * a + b] = dt[a] * ds[b];
+        return true;
+    }
+};
+
+IBL_API int ibl_p2p_update(const double *src, const int32_t *nn_idx, int64_t n, const double *tgt, double *h_T16,
+                           void *stream) {
+    IBL_ARG(h_T16 && n >= 0);
+    for (int k = 0; k < 16; ++k) h_T16[k] = (k % 5 == 0) ? 1.0 : 0.0;
+    if (n == 0) return IBL_OK;
+    cudaStream_t st = ibl_stream(stream);
+    double s7[7];
+    P2PSums f1{src, nn_idx, tgt};
+    int rc = reduceK<7>(n, f1, s7, st);
+    if (rc < 0) return rc;
+    if (s7[0] == 0.0) return IBL_OK;   // corres.empty() -> Identity
+    P2PCov f2{src, nn_idx, tgt, {0, 0, 0}, {0, 0, 0}};
+    for (int a = 0; a < 3; ++a) { f2.ms[a] = s7[1 + a] / s7[0]; f2.mt[a] = s7[4 + a] / s7[0]; }
+    double c9[9];
+    rc = reduceK<9>(n, f2, c9, st);
+    if (rc < 0) return rc;
+    double sg[3][3];
+    for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) sg[a][b] = c9[3 * a + b] / s7[0];
+    ibl_kabsch_finish(sg, f2.ms, f2.mt, h_T16);
+    return IBL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// A.8 colour gradient: thread per target point, rows accumulated in neighbour-list order
+__global__ void __launch_bounds__(128) color_gradient_kernel(const double *__restrict__ pts, const double *__restrict__ nrm,
+                                                             const double *__restrict__ col, int64_t n,
+                                                             const int32_t *__restrict__ nbr_idx,
+                                                             const int32_t *__restrict__ nbr_cnt, int max_nn,
+                                                             double *__restrict__ grad) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    double g[3] = {0, 0, 0};
+    int nn = nbr_cnt[k];
+    if (nn >= 4) {
+        double vt[3] = {pts[3 * k], pts[3 * k + 1], pts[3 * k + 2]};
+        double nt[3] = {nrm[3 * k], nrm[3 * k + 1], nrm[3 * k + 2]};
+        double it = (col[3 * k] + col[3 * k + 1] + col[3 * k + 2]) / 3.0;
+        double AtA[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Atb[3] = {0, 0, 0};
+        for (int i = 1; i < nn; ++i) {
+            size_t adj = (size_t)nbr_idx[k * max_nn + i];
+            double va[3] = {pts[3 * adj], pts[3 * adj + 1], pts[3 * adj + 2]};
+            double d[3] = {va[0] - vt[0], va[1] - vt[1], va[2] - vt[2]};
+            double pr = ibl_dot(d, nt);
+            double row[3] = {(va[0] - pr * nt[0]) - vt[0], (va[1] - pr * nt[1]) - vt[1], (va[2] - pr * nt[2]) - vt[2]};
+            double ia = (col[3 * adj] + col[3 * adj + 1] + col[3 * adj + 2]) / 3.0;
+            double bi = ia - it;
+            for (int a = 0; a < 3; ++a) {
+                for (int b = 0; b < 3; ++b) AtA[3 * a + b] += row[a] * row[b];
+                Atb[a] += row[a] * bi;
+            }
+        }
+        double w = (double)(nn - 1);
+        double row[3] = {w * nt[0], w * nt[1], w * nt[2]};
+        for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) AtA[3 * a + b] += row[a] * row[b];
+        double x[3];
+        if (ibl_ldlt_solve<3>(AtA, Atb, x)) { g[0] = x[0]; g[1] = x[1]; g[2] = x[2]; }
+    }
+    grad[3 * k] = g[0]; grad[3 * k + 1] = g[1]; grad[3 * k + 2] = g[2];
+}
+
+IBL_API int ibl_color_gradient(const double *pts, const double *nrm, const double *col, int64_t n, const int32_t *nbr_idx,
+                               const int32_t *nbr_cnt, int32_t max_nn, double *grad, void *stream) {
+    IBL_ARG(n >= 0);
+    if (n == 0) return IBL_OK;
+    IBL_ARG(pts && nrm && col && nbr_idx && nbr_cnt && grad);
+    color_gradient_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ibl_stream(stream)>>>(pts, nrm, col, n, nbr_idx, nbr_cnt, max_nn, grad);
+    IBL_LAUNCH_CHECK();
+    return IBL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+struct ColoredJTJ {   // 21 upper-triangle JTJ + 6 JTr
+    const double *src, *scol; const int32_t *nn; const double *tgt, *tnrm, *tcol, *tgrad; double sg, sp;
+    __device__ bool operator()(int64_t i, double *v) const {
+        int j = nn[i];
+        if (j < 0) return false;
+        size_t ct = (size_t)j;
+        double vs[3] = {src[3 * i], src[3 * i + 1], src[3 * i + 2]};
+        double vt[3] = {tgt[3 * ct], tgt[3 * ct + 1], tgt[3 * ct + 2]};
+        double nt[3] = {tnrm[3 * ct], tnrm[3 * ct + 1], tnrm[3 * ct + 2]};
+        double J[2][6], r[2], cr[3];
+        ibl_cross(vs, nt, cr);
+        for (int a = 0; a < 3; ++a) { J[0][a] = sg * cr[a]; J[0][3 + a] = sg * nt[a]; }
+        double d[3] = {vs[0] - vt[0], vs[1] - vt[1], vs[2] - vt[2]};
+        double dn = ibl_dot(d, nt);
+        r[0] = sg * dn;
+        double vp[3] = {vs[0] - dn * nt[0], vs[1] - dn * nt[1], vs[2] - dn * nt[2]};
+        double is = (scol[3 * i] + scol[3 * i + 1] + scol[3 * i + 2]) / 3.0;
+        double it = (tcol[3 * ct] + tcol[3 * ct + 1] + tcol[3 * ct + 2]) / 3.0;
+        double dit[3] = {tgrad[3 * ct], tgrad[3 * ct + 1], tgrad[3 * ct + 2]};
+        double dv[3] = {vp[0] - vt[0], vp[1] - vt[1], vp[2] - vt[2]};
+        double is0 = ibl_dot(dit, dv) + it;
+        double dm[3];
+        for (int b = 0; b < 3; ++b) {
+            double s = 0.0;
+            for (int a = 0; a < 3; ++a) s += dit[a] * ((a == b ? 1.0 : 0.0) - nt[a] * nt[b]);
+            dm[b] = -s;
+        }
+        ibl_cross(vs, dm, cr);
+        for (int a = 0; a < 3; ++a) { J[1][a] = sp * cr[a]; J[1][3 + a] = sp * dm[a]; }
+        r[1] = sp * (is - is0);
+        int o = 0;
+        for (int a = 0; a < 6; ++a)
+            for (int b = a; b < 6; ++b) v[o++] = J[0][a] * J[0][b] + J[1][a] * J[1][b];
+        for (int a = 0; a < 6; ++a) v[21 + a] = J[0][a] * r[0] + J[1][a] * r[1];
+        return true;
+    }
+};
+
+static void solve_update_host(const double *v27, double *T16) {
+    double A[36], nb[6], x[6];
+    int o = 0;
+    for (int a = 0; a < 6; ++a)
+        for (int b = a; b < 6; ++b) { A[6 * a + b] = v27[o]; A[6 * b + a] = v27[o]; ++o; }
+    for (int a = 0; a < 6; ++a) nb[a] = -v27[21 + a];
+    for (int k = 0; k < 16; ++k) T16[k] = (k % 5 == 0) ? 1.0 : 0.0;
+    if (!ibl_ldlt_solve<6>(A, nb, x)) return;
+    double cx = cos(x[0]), sx = sin(x[0]), cy = cos(x[1]), sy = sin(x[1]), cz = cos(x[2]), sz = sin(x[2]);
+    T16[0] = cz * cy; T16[1] = cz * sy * sx - sz * cx; T16[2] = cz * sy * cx + sz * sx; T16[3] = x[3];
+    T16[4] = sz * cy; T16[5] = sz * sy * sx + cz * cx; T16[6] = sz * sy * cx - cz * sx; T16[7] = x[4];
+    T16[8] = -sy;     T16[9] = cy * sx;                T16[10] = cy * cx;               T16[11] = x[5];
+}
+
+IBL_API int ibl_colored_update(const double *src, const double *scol, const int32_t *nn_idx, int64_t n, const double *tgt,
+                               const double *tnrm, const double *tcol, const double *tgrad, double lambda_geometric,
+                               double *h_out27, double *h_T16, void *stream) {
+    IBL_ARG(n >= 0 && h_out27);
+    ColoredJTJ f{src, scol, nn_idx, tgt, tnrm, tcol, tgrad, sqrt(lambda_geometric), sqrt(1.0 - lambda_geometric)};
+    int rc = reduceK<27>(n, f, h_out27, ibl_stream(stream));
+    if (rc < 0) return rc;
+    if (h_T16) solve_update_host(h_out27, h_T16);
+    return IBL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+static void matmul4(const double *A, const double *B, double *C) {
+    double t[16];
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) {
+            double s = 0;
+            for (int k = 0; k < 4; ++k) s += A[4 * i + k] * B[4 * k + j];
+            t[4 * i + j] = s;
+        }
+    memcpy(C, t, sizeof(t));
+}
+static bool is_identity(const double *T) {
+    for (int k = 0; k < 16; ++k) if (T[k] != ((k % 5 == 0) ? 1.0 : 0.0)) return false;
+    return true;
+}
+
+IBL_API int ibl_icp(const ibl_grid_t *tgt_grid, const double *src, const double *scol, int64_t n_src, const double *tgt,
+                    const double *tnrm, const double *tcol, const double *tgrad, int mode, double max_d,
+                    const double *h_T_init, int max_iteration, double rel_fitness, double rel_rmse, double lambda_geometric,
+                    ibl_reg_result_t *h_result, void *stream) {
+    IBL_ARG(tgt_grid && h_result && n_src >= 0 && max_d > 0 && (mode == 0 || (scol && tnrm && tcol && tgrad)));
+    cudaStream_t st = ibl_stream(stream);
+    memset(h_result, 0, sizeof(*h_result));
+    double T[16];
+    for (int k = 0; k < 16; ++k) T[k] = h_T_init ? h_T_init[k] : ((k % 5 == 0) ? 1.0 : 0.0);
+    memcpy(h_result->T, T, sizeof(T));
+    h_result->best_hyp = -1;
+    if (n_src == 0) { h_result->status = 1; return IBL_OK; }
+    double *pcd = nullptr; int32_t *nn = nullptr;
+    IBL_CUDA(ibl_alloc(&pcd, (size_t)n_src * 3, st));
+    IBL_CUDA(ibl_alloc(&nn, (size_t)n_src, st));
+    int rc;
+    if (is_identity(T)) {
+        IBL_CUDA(cudaMemcpyAsync(pcd, src, sizeof(double) * 3 * n_src, cudaMemcpyDeviceToDevice, st));
+    } else if ((rc = ibl_transform_points(T, src, n_src, 0, pcd, stream)) < 0) return rc;
+    ibl_score_t sc;
+    if ((rc = ibl_nn_score(tgt_grid, pcd, n_src, nullptr, max_d, nn, nullptr, &sc, stream)) < 0) return rc;
+    double fit = (double)sc.n_inliers / (double)n_src;
+    double rmse = sc.n_inliers > 0 ? sqrt(sc.err2 / (double)sc.n_inliers) : 0.0;
+    int it = 0;
+    for (; it < max_iteration;) {
+        double upd[16], v27[27];
+        if (mode == 0) rc = ibl_p2p_update(pcd, nn, n_src, tgt, upd, stream);
+        else rc = ibl_colored_update(pcd, scol, nn, n_src, tgt, tnrm, tcol, tgrad, lambda_geometric, v27, upd, stream);
+        if (rc < 0) return rc;
+        matmul4(upd, T, T);
+        if ((rc = ibl_transform_points(upd, pcd, n_src, 0, pcd, stream)) < 0) return rc;
+        double pf = fit, pr = rmse;
+        if ((rc = ibl_nn_score(tgt_grid, pcd, n_src, nullptr, max_d, nn, nullptr, &sc, stream)) < 0) return rc;
+        fit = (double)sc.n_inliers / (double)n_src;
+        rmse = sc.n_inliers > 0 ? sqrt(sc.err2 / (double)sc.n_inliers) : 0.0;
+        ++it;
+        if (fabs(pf - fit) < rel_fitness && fabs(pr - rmse) < rel_rmse) break;
+    }
+    memcpy(h_result->T, T, sizeof(T));
+    h_result->fitness = fit; h_result->inlier_rmse = rmse;
+    h_result->n_inliers = sc.n_inliers; h_result->err2 = sc.err2; h_result->iterations = it;
+    ibl_free(pcd, st); ibl_free(nn, st);
+    return IBL_OK;
+}

@@ -1,0 +1,274 @@
+// ransac.cu -- RegistrationRANSACBasedOnCorrespondence (utils/fpfh_register.py:110-119; A.6/A.7).
+//   check  : thread per hypothesis -- gather 3 correspondences, EdgeLength test first (needs no
+//            transform), Jacobi-Kabsch, Distance test
+//   score  : grid (source tiles x hypotheses); thread per source point does an exact 1-NN within
+//            max_d on the target grid (ring field skips empty space); integer inlier counts and a
+//            fixed-order err2 reduction (warp shuffles -> CTA -> tile partials)
+//   run    : host loop applying the ordered best-update / adaptive-stop rule
+#include <cub/cub.cuh>
+#include <vector>
+
+#include "ibl_common.cuh"
+#include "rigid.cuh"
+
+__device__ __forceinline__ void gather_sample(const double *__restrict__ src, const double *__restrict__ tgt,
+                                              const int32_t *__restrict__ corres, int64_t n_corres,
+                                              const int32_t *__restrict__ samples, uint64_t seed, int64_t h, double *s,
+                                              double *t) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        int c = samples ? samples[3 * h + j] : (int)ibl_sample(seed, (uint64_t)h, (uint32_t)j, (uint32_t)n_corres);
+        size_t cs = (size_t)corres[2 * c], ct = (size_t)corres[2 * c + 1];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { s[3 * j + a] = src[3 * cs + a]; t[3 * j + a] = tgt[3 * ct + a]; }
+    }
+}
+
+__global__ void __launch_bounds__(128) ransac_check_kernel(const double *__restrict__ src, const double *__restrict__ tgt,
+                                                           const int32_t *__restrict__ corres, int64_t n_corres,
+                                                           const int32_t *__restrict__ samples, uint64_t seed, int64_t h0,
+                                                           int64_t H, double edge_thr, double dist_thr, int use_checkers,
+                                                           uint8_t *__restrict__ pass, double *__restrict__ T_out) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= H) return;
+    int64_t h = h0 + k;
+    double s[9], t[9], T[16];
+    gather_sample(src, tgt, corres, n_corres, samples, seed, h, s, t);
+    bool ok = true;
+    if (use_checkers) {
+        for (int i = 0; i < 3 && ok; ++i)
+            for (int j = i + 1; j < 3; ++j) {
+                double a[3] = {s[3 * i] - s[3 * j], s[3 * i + 1] - s[3 * j + 1], s[3 * i + 2] - s[3 * j + 2]};
+                double b[3] = {t[3 * i] - t[3 * j], t[3 * i + 1] - t[3 * j + 1], t[3 * i + 2] - t[3 * j + 2]};
+                double ds = sqrt(ibl_dot(a, a)), dt = sqrt(ibl_dot(b, b));
+                if (ds < dt * edge_thr || dt < ds * edge_thr) { ok = false; break; }
+            }
+    }
+    if (ok) {
+        ibl_kabsch3(s, t, T);
+        if (use_checkers) {
+            for (int j = 0; j < 3; ++j) {
+                double qx, qy, qz;
+                ibl_xform(T, s[3 * j], s[3 * j + 1], s[3 * j + 2], qx, qy, qz);
+                double d[3] = {t[3 * j] - qx, t[3 * j + 1] - qy, t[3 * j + 2] - qz};
+                if (sqrt(ibl_dot(d, d)) > dist_thr) { ok = false; break; }
+            }
+        }
+        if (ok && T_out) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) T_out[16 * k + e] = T[e];
+        }
+    }
+    pass[k] = ok;
+}
+
+IBL_API int ibl_ransac_check(const double *src, const double *tgt, const int32_t *corres, int64_t n_corres,
+                             const int32_t *samples, uint64_t seed, int64_t h0, int64_t H, double edge_thr,
+                             double dist_thr, int use_checkers, uint8_t *pass, double *T_out, void *stream) {
+    IBL_ARG(H >= 0 && n_corres >= 1 && n_corres < (1ll << 31));
+    if (H == 0) return IBL_OK;
+    IBL_ARG(src && tgt && corres && pass);
+    ransac_check_kernel<<<(unsigned)((H + 127) / 128), 128, 0, ibl_stream(stream)>>>(
+        src, tgt, corres, n_corres, samples, seed, h0, H, edge_thr, dist_thr, use_checkers, pass, T_out);
+    IBL_LAUNCH_CHECK();
+    return IBL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void hyp_transform_kernel(const double *__restrict__ src, const double *__restrict__ tgt,
+                                     const int32_t *__restrict__ corres, int64_t n_corres,
+                                     const int32_t *__restrict__ samples, uint64_t seed,
+                                     const int64_t *__restrict__ hyp_ids, int64_t nh, double *__restrict__ T_out) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= nh) return;
+    double s[9], t[9], T[16];
+    gather_sample(src, tgt, corres, n_corres, samples, seed, hyp_ids[k], s, t);
+    ibl_kabsch3(s, t, T);
+#pragma unroll
+    for (int e = 0; e < 16; ++e) T_out[16 * k + e] = T[e];
+}
+
+#define SCORE_TILE 2048
+#define SCORE_THREADS 256
+
+__global__ void __launch_bounds__(SCORE_THREADS) ransac_score_kernel(GridView g, const double *__restrict__ src,
+                                                                     int64_t n_src, const double *__restrict__ T_all,
+                                                                     double max_d, double max_d2, int ntiles,
+                                                                     int *__restrict__ part_cnt,
+                                                                     double *__restrict__ part_err) {
+    __shared__ double T[16];
+    __shared__ double se[SCORE_THREADS / 32];
+    __shared__ int sc[SCORE_THREADS / 32];
+    int tile = blockIdx.x;
+    int64_t hyp = blockIdx.y;
+    if (threadIdx.x < 16) T[threadIdx.x] = T_all[16 * hyp + threadIdx.x];
+    __syncthreads();
+    int cnt = 0;
+    double err = 0.0;
+    int64_t base = (int64_t)tile * SCORE_TILE;
+#pragma unroll 1
+    for (int r = 0; r < SCORE_TILE / SCORE_THREADS; ++r) {
+        int64_t i = base + r * SCORE_THREADS + threadIdx.x;
+        if (i < n_src) {
+            double x, y, z, bd;
+            ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
+            int j = ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd);
+            if (j >= 0) { ++cnt; err = __dadd_rn(err, bd); }
+        }
+    }
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int o = 16; o; o >>= 1) { err += __shfl_down_sync(0xffffffffu, err, o); cnt += __shfl_down_sync(0xffffffffu, cnt, o); }
+    if (lane == 0) { se[w] = err; sc[w] = cnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double te = 0; int tc = 0;
+        for (int k = 0; k < SCORE_THREADS / 32; ++k) { te += se[k]; tc += sc[k]; }
+        part_cnt[hyp * ntiles + tile] = tc;
+        part_err[hyp * ntiles + tile] = te;
+    }
+}
+
+// one warp per hypothesis: tile partials in index order + correspondence inlier count
+__global__ void __launch_bounds__(128) ransac_finalize_kernel(const int *__restrict__ part_cnt,
+                                                              const double *__restrict__ part_err, int ntiles,
+                                                              int64_t nh, const double *__restrict__ T_all,
+                                                              const double *__restrict__ src,
+                                                              const double *__restrict__ tgt,
+                                                              const int32_t *__restrict__ corres, int64_t n_corres,
+                                                              double max_d, int32_t *__restrict__ inliers,
+                                                              double *__restrict__ err2,
+                                                              int32_t *__restrict__ corres_inliers) {
+    int lane = threadIdx.x & 31;
+    int64_t hyp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (hyp >= nh) return;
+    double e = 0; int c = 0;
+    for (int k = lane; k < ntiles; k += 32) { e += part_err[hyp * ntiles + k]; c += part_cnt[hyp * ntiles + k]; }
+    for (int o = 16; o; o >>= 1) { e += __shfl_down_sync(0xffffffffu, e, o); c += __shfl_down_sync(0xffffffffu, c, o); }
+    double T[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) T[k] = T_all[16 * hyp + k];
+    int ci = 0;
+    for (int64_t k = lane; k < n_corres; k += 32) {
+        size_t cs = (size_t)corres[2 * k], ct = (size_t)corres[2 * k + 1];
+        double x, y, z;
+        ibl_xform(T, src[3 * cs], src[3 * cs + 1], src[3 * cs + 2], x, y, z);
+        double d[3] = {x - tgt[3 * ct], y - tgt[3 * ct + 1], z - tgt[3 * ct + 2]};
+        ci += sqrt(ibl_dot(d, d)) < max_d;
+    }
+    for (int o = 16; o; o >>= 1) ci += __shfl_down_sync(0xffffffffu, ci, o);
+    if (lane == 0) { inliers[hyp] = c; err2[hyp] = e; if (corres_inliers) corres_inliers[hyp] = ci; }
+}
+
+IBL_API int ibl_ransac_score(const ibl_grid_t *tgt_grid, const double *src, int64_t n_src, const double *tgt,
+                             const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
+                             const int64_t *hyp_ids, int64_t nh, double max_d, int32_t *inliers, double *err2,
+                             int32_t *corres_inliers, double *T_out, void *stream) {
+    IBL_ARG(tgt_grid && nh >= 0 && n_src >= 0 && max_d > 0 && nh <= 65535);
+    if (nh == 0) return IBL_OK;
+    IBL_ARG(src && tgt && corres && hyp_ids && inliers && err2 && T_out);
+    cudaStream_t st = ibl_stream(stream);
+    hyp_transform_kernel<<<(unsigned)((nh + 63) / 64), 64, 0, st>>>(src, tgt, corres, n_corres, samples, seed, hyp_ids, nh, T_out);
+    IBL_LAUNCH_CHECK();
+    int ntiles = (int)((n_src + SCORE_TILE - 1) / SCORE_TILE);
+    if (ntiles < 1) ntiles = 1;
+    int *pc = nullptr; double *pe = nullptr;
+    IBL_CUDA(ibl_alloc(&pc, (size_t)nh * ntiles, st));
+    IBL_CUDA(ibl_alloc(&pe, (size_t)nh * ntiles, st));
+    dim3 grid(ntiles, (unsigned)nh);
+    ransac_score_kernel<<<grid, SCORE_THREADS, 0, st>>>(ibl_view(tgt_grid), src, n_src, T_out, max_d, max_d * max_d, ntiles, pc, pe);
+    IBL_LAUNCH_CHECK();
+    ransac_finalize_kernel<<<(unsigned)((nh * 32 + 127) / 128), 128, 0, st>>>(pc, pe, ntiles, nh, T_out, src, tgt, corres, n_corres,
+                                                                               max_d, inliers, err2, corres_inliers);
+    IBL_LAUNCH_CHECK();
+    ibl_free(pc, st); ibl_free(pe, st);
+    return IBL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+struct IotaPlus {
+    int64_t h0;
+    __host__ __device__ int64_t operator()(int64_t k) const { return h0 + k; }
+};
+
+IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_t n_src, const double *tgt,
+                           const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
+                           int64_t max_iteration, double confidence, double max_d, double edge_thr, int use_checkers,
+                           int early_exit, int64_t block, ibl_reg_result_t *h_result, void *stream) {
+    IBL_ARG(h_result != nullptr && tgt_grid != nullptr);
+    memset(h_result, 0, sizeof(*h_result));
+    for (int k = 0; k < 16; ++k) h_result->T[k] = (k % 5 == 0) ? 1.0 : 0.0;
+    h_result->best_hyp = -1;
+    h_result->n_corres = n_corres;
+    if (n_corres < 3 || max_d <= 0 || max_iteration <= 0 || n_src <= 0) { h_result->status = 1; return IBL_OK; }
+    cudaStream_t st = ibl_stream(stream);
+    if (block <= 0) block = 1 << 16;
+    const int64_t SCORE_CHUNK = 1024;
+    uint8_t *pass = nullptr; int64_t *ids = nullptr; int *dcount = nullptr;
+    int32_t *inl = nullptr, *cinl = nullptr; double *err = nullptr, *Ts = nullptr;
+    IBL_CUDA(ibl_alloc(&pass, (size_t)block, st));
+    IBL_CUDA(ibl_alloc(&ids, (size_t)block, st));
+    IBL_CUDA(ibl_alloc(&dcount, 1, st));
+    IBL_CUDA(ibl_alloc(&inl, (size_t)SCORE_CHUNK, st));
+    IBL_CUDA(ibl_alloc(&cinl, (size_t)SCORE_CHUNK, st));
+    IBL_CUDA(ibl_alloc(&err, (size_t)SCORE_CHUNK, st));
+    IBL_CUDA(ibl_alloc(&Ts, (size_t)SCORE_CHUNK * 16, st));
+    size_t tb = 0;
+    {
+        cub::CountingInputIterator<int64_t> cit(0);
+        cub::DeviceSelect::Flagged(nullptr, tb, cit, pass, ids, dcount, (int)block, st);
+    }
+    void *tmp = nullptr;
+    IBL_CUDA(cudaMallocAsync(&tmp, tb ? tb : 1, st));
+    std::vector<int64_t> h_ids(SCORE_CHUNK);
+    std::vector<int32_t> h_inl(SCORE_CHUNK), h_cinl(SCORE_CHUNK);
+    std::vector<double> h_err(SCORE_CHUNK), h_T(SCORE_CHUNK * 16);
+    int64_t est_k = max_iteration;
+    double best_fit = 0.0, best_rmse = 0.0;
+    int rc = IBL_OK;
+    for (int64_t h0 = 0; h0 < max_iteration && h0 < est_k; h0 += block) {
+        int64_t H = std::min(block, std::min(max_iteration, est_k) - h0);
+        if ((rc = ibl_ransac_check(src, tgt, corres, n_corres, samples, seed, h0, H, edge_thr, max_d, use_checkers, pass,
+                                   nullptr, stream)) < 0) break;
+        cub::CountingInputIterator<int64_t> cit(h0);
+        IBL_CUDA(cub::DeviceSelect::Flagged(tmp, tb, cit, pass, ids, dcount, (int)H, st));
+        int npass = 0;
+        IBL_CUDA(cudaMemcpyAsync(&npass, dcount, sizeof(int), cudaMemcpyDeviceToHost, st));
+        IBL_CUDA(cudaStreamSynchronize(st));
+        bool stop = false;
+        for (int64_t c0 = 0; c0 < npass && !stop; c0 += SCORE_CHUNK) {
+            int64_t nc = std::min<int64_t>(SCORE_CHUNK, npass - c0);
+            if ((rc = ibl_ransac_score(tgt_grid, src, n_src, tgt, corres, n_corres, samples, seed, ids + c0, nc, max_d, inl, err,
+                                       cinl, Ts, stream)) < 0) { stop = true; break; }
+            IBL_CUDA(cudaMemcpyAsync(h_ids.data(), ids + c0, sizeof(int64_t) * nc, cudaMemcpyDeviceToHost, st));
+            IBL_CUDA(cudaMemcpyAsync(h_inl.data(), inl, sizeof(int32_t) * nc, cudaMemcpyDeviceToHost, st));
+            IBL_CUDA(cudaMemcpyAsync(h_cinl.data(), cinl, sizeof(int32_t) * nc, cudaMemcpyDeviceToHost, st));
+            IBL_CUDA(cudaMemcpyAsync(h_err.data(), err, sizeof(double) * nc, cudaMemcpyDeviceToHost, st));
+            IBL_CUDA(cudaMemcpyAsync(h_T.data(), Ts, sizeof(double) * 16 * nc, cudaMemcpyDeviceToHost, st));
+            IBL_CUDA(cudaStreamSynchronize(st));
+            for (int64_t k = 0; k < nc; ++k) {
+                if (h_ids[k] >= est_k) { stop = true; break; }
+                h_result->validated++;
+                double fit = (double)h_inl[k] / (double)n_src;
+                double rmse = h_inl[k] > 0 ? sqrt(h_err[k] / (double)h_inl[k]) : 0.0;
+                if (fit > best_fit || (fit == best_fit && rmse < best_rmse)) {
+                    best_fit = fit; best_rmse = rmse;
+                    h_result->fitness = fit; h_result->inlier_rmse = rmse;
+                    h_result->n_inliers = h_inl[k]; h_result->err2 = h_err[k];
+                    h_result->best_hyp = h_ids[k];
+                    memcpy(h_result->T, &h_T[16 * k], sizeof(double) * 16);
+                    if (early_exit) {
+                        double rho = (double)h_cinl[k] / (double)n_corres;
+                        double den = rho < 1.0 ? log(1.0 - rho * rho * rho) : -INFINITY;
+                        double kk = den == 0.0 ? INFINITY : log(1.0 - confidence) / den;
+                        if (kk < (double)max_iteration) est_k = (int64_t)ceil(kk);
+                    }
+                }
+            }
+        }
+        if (rc < 0) break;
+    }
+    h_result->drawn = std::min(max_iteration, std::max<int64_t>(est_k, 0));
+    ibl_free(tmp, st); ibl_free(pass, st); ibl_free(ids, st); ibl_free(dcount, st);
+    ibl_free(inl, st); ibl_free(cinl, st); ibl_free(err, st); ibl_free(Ts, st);
+    return rc;
+}

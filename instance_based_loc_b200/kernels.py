@@ -1,0 +1,308 @@
+"""Torch-tensor wrappers over the C ABI (include/ibl.h).  PyTorch is only plumbing here: device
+memory, the current CUDA stream and host<->device copies.  Every function takes / returns CUDA
+tensors and raises if the CUDA library or a GPU is missing."""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_double, c_int64
+
+import numpy as np
+import torch
+
+from ._lib import IblError, RegResultT, ScoreT, check, lib
+
+F64 = torch.float64
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        raise IblError("instance_based_loc_b200 needs a CUDA device (no CPU fallback)")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def to_dev(a, dtype=F64):
+    """numpy / tensor -> contiguous CUDA tensor of dtype."""
+    if isinstance(a, torch.Tensor):
+        return a.to(device=_dev(), dtype=dtype).contiguous()
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).to(_dev())
+
+
+def _T16(T):
+    if T is None:
+        return None
+    arr = np.ascontiguousarray(np.asarray(T, dtype=np.float64).reshape(16))
+    return (c_double * 16)(*arr.tolist())
+
+
+# ---------------------------------------------------------------------------------------- clouds
+def backproject_masks(depth, rgb, masks, fx, fy, want_colors=True):
+    """depth [H,W] f32|f64 CUDA, rgb [H,W,3] u8 CUDA or None, masks [n,H,W] u8/bool CUDA.
+    -> (pts [N,3] f64, cols [N,3] f64 | None, offsets list[int] of len n+1)."""
+    H, W = depth.shape
+    n = int(masks.shape[0])
+    is64 = depth.dtype == torch.float64
+    if not is64 and depth.dtype != torch.float32:
+        raise IblError("depth must be float32 or float64")
+    masks = masks.reshape(n, H * W)
+    if masks.dtype == torch.bool:
+        masks = masks.view(torch.uint8)
+    masks = masks.contiguous()
+    depth = depth.contiguous()
+    hor = torch.from_numpy(np.linspace(-W / 2, W / 2, W, dtype=np.float32)).to(depth.device)
+    ver = torch.from_numpy(np.linspace(H / 2, -H / 2, H, dtype=np.float32)).to(depth.device)
+    offs = (c_int64 * (n + 1))()
+    L = lib()
+    args = (_p(depth), int(is64), _p(rgb) if rgb is not None else None, _p(masks), n, H, W, _p(hor), _p(ver),
+            float(fx), float(fy))
+    check(L.ibl_backproject_masks(*args, None, None, offs, _stream()), "backproject(count)")
+    total = int(offs[n])
+    pts = torch.empty((total, 3), dtype=F64, device=depth.device)
+    cols = torch.empty((total, 3), dtype=F64, device=depth.device) if (rgb is not None and want_colors) else None
+    if total:
+        check(L.ibl_backproject_masks(*args, _p(pts), _p(cols), offs, _stream()), "backproject")
+    return pts, cols, [int(o) for o in offs]
+
+
+def voxel_downsample(pts, cols=None, nrm=None, voxel=0.01, want_ids=False, want_keys=False):
+    n = pts.shape[0]
+    dev = pts.device
+    op = torch.empty_like(pts)
+    oc = torch.empty_like(pts) if cols is not None else None
+    on = torch.empty_like(pts) if nrm is not None else None
+    vid = torch.empty(n, dtype=torch.int32, device=dev) if want_ids else None
+    keys = torch.empty((n, 3), dtype=torch.int64, device=dev) if want_keys else None
+    nv = check(lib().ibl_voxel_downsample(_p(pts), _p(cols), _p(nrm), n, float(voxel), _p(op), _p(oc), _p(on), _p(vid),
+                                          _p(keys), _stream()), "voxel_downsample")
+    return (op[:nv], oc[:nv] if oc is not None else None, on[:nv] if on is not None else None, vid, keys)
+
+
+def select_rows(keep, a=None, b=None, c=None, want_index=False):
+    n = keep.shape[0]
+    dev = keep.device
+    if keep.dtype == torch.bool:
+        keep = keep.view(torch.uint8)
+    oa = torch.empty_like(a) if a is not None else None
+    ob = torch.empty_like(b) if b is not None else None
+    oc = torch.empty_like(c) if c is not None else None
+    oi = torch.empty(n, dtype=torch.int32, device=dev) if want_index else None
+    k = check(lib().ibl_select_rows(_p(keep), n, _p(a), _p(b), _p(c), _p(oa), _p(ob), _p(oc), _p(oi), _stream()),
+              "select_rows")
+    cut = lambda t: t[:k] if t is not None else None  # noqa: E731
+    return cut(oa), cut(ob), cut(oc), cut(oi)
+
+
+def transform_points(T, pts, rotate_only=False, inplace=False):
+    out = pts if inplace else torch.empty_like(pts)
+    check(lib().ibl_transform_points(_T16(T), _p(pts), pts.shape[0], int(rotate_only), _p(out), _stream()), "transform")
+    return out
+
+
+def mean3(pts):
+    m = (c_double * 3)()
+    check(lib().ibl_mean3(_p(pts), pts.shape[0], m, _stream()), "mean3")
+    return np.array([m[0], m[1], m[2]])
+
+
+# ------------------------------------------------------------------------------------------ grid
+class Grid:
+    """Owns an ibl_grid_t; keeps the point tensor alive."""
+
+    def __init__(self, pts, cell, max_cells=0, ring=0):
+        self.pts = pts
+        self.h = ctypes.c_void_p()
+        check(lib().ibl_grid_create(_p(pts), pts.shape[0], float(cell), int(max_cells), ctypes.byref(self.h), _stream()),
+              "grid_create")
+        if ring:
+            check(lib().ibl_grid_build_ringfield(self.h, int(ring), _stream()), "ringfield")
+
+    @property
+    def cell(self):
+        return lib().ibl_grid_cell(self.h)
+
+    @property
+    def occupied(self):
+        return lib().ibl_grid_occupied(self.h)
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().ibl_grid_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+def knn_cell_for(pts, k, radius):
+    """Pick a grid cell for a k-NN search from the cloud's surface density (two coarse counts)."""
+    n = pts.shape[0]
+    if n == 0:
+        return radius
+    g0 = Grid(pts, max(radius / 4.0, 1e-4))
+    occ = max(1, g0.occupied)
+    c0 = g0.cell
+    del g0
+    # surface model: n points over ~occ * c0^2 area -> spacing; k points within ~sqrt(k/pi)*spacing
+    spacing = c0 * (occ / n) ** 0.5
+    rk = (k / np.pi) ** 0.5 * spacing
+    return float(min(max(rk * 0.6, 1e-4), radius))
+
+
+def radius_count(grid, radius):
+    out = torch.empty(grid.pts.shape[0], dtype=torch.int32, device=grid.pts.device)
+    check(lib().ibl_radius_count(grid.h, float(radius), _p(out), _stream()), "radius_count")
+    return out
+
+
+def radius_outlier_mask(grid, radius, nb_points):
+    out = torch.empty(grid.pts.shape[0], dtype=torch.uint8, device=grid.pts.device)
+    check(lib().ibl_radius_outlier_mask(grid.h, float(radius), int(nb_points), _p(out), _stream()), "radius_outlier")
+    return out
+
+
+def knn_hybrid(grid, radius, max_nn, queries=None, want_d2=True):
+    nq = grid.pts.shape[0] if queries is None else queries.shape[0]
+    dev = grid.pts.device
+    idx = torch.empty((nq, max_nn), dtype=torch.int32, device=dev)
+    d2 = torch.empty((nq, max_nn), dtype=F64, device=dev) if want_d2 else None
+    cnt = torch.empty(nq, dtype=torch.int32, device=dev)
+    check(lib().ibl_knn_hybrid(grid.h, _p(queries), nq, float(radius), int(max_nn), _p(idx), _p(d2), _p(cnt), _stream()),
+          "knn_hybrid")
+    return idx, d2, cnt
+
+
+def nn_score(grid, src, max_d, T=None, want_idx=False, want_d2=False):
+    n = src.shape[0]
+    nn = torch.empty(n, dtype=torch.int32, device=src.device) if want_idx else None
+    d2 = torch.empty(n, dtype=F64, device=src.device) if want_d2 else None
+    res = ScoreT()
+    check(lib().ibl_nn_score(grid.h, _p(src), n, _T16(T), float(max_d), _p(nn), _p(d2), ctypes.byref(res), _stream()),
+          "nn_score")
+    return int(res.n_inliers), float(res.err2), nn, d2
+
+
+# -------------------------------------------------------------------------------------- features
+def normals(pts, idx, cnt):
+    out = torch.empty_like(pts)
+    check(lib().ibl_normals(_p(pts), pts.shape[0], _p(idx), _p(cnt), idx.shape[1], _p(out), _stream()), "normals")
+    return out
+
+
+def spfh(pts, nrm, idx, cnt):
+    out = torch.empty((pts.shape[0], 33), dtype=F64, device=pts.device)
+    check(lib().ibl_spfh(_p(pts), _p(nrm), pts.shape[0], _p(idx), _p(cnt), idx.shape[1], _p(out), _stream()), "spfh")
+    return out
+
+
+def fpfh(idx, d2, cnt, spfh_t):
+    out = torch.empty_like(spfh_t)
+    check(lib().ibl_fpfh(spfh_t.shape[0], _p(idx), _p(d2), _p(cnt), idx.shape[1], _p(spfh_t), _p(out), _stream()), "fpfh")
+    return out
+
+
+def feature_nn(fa, fb):
+    out = torch.empty(fa.shape[0], dtype=torch.int32, device=fa.device)
+    check(lib().ibl_feature_nn(_p(fa), fa.shape[0], _p(fb), fb.shape[0], _p(out), _stream()), "feature_nn")
+    return out
+
+
+def mutual_corres(ij, ji, ransac_n=3):
+    cor = torch.empty((ij.shape[0], 2), dtype=torch.int32, device=ij.device)
+    c = check(lib().ibl_mutual_corres(_p(ij), ij.shape[0], _p(ji), ji.shape[0], int(ransac_n), _p(cor), _stream()),
+              "mutual_corres")
+    return cor[:c]
+
+
+# ---------------------------------------------------------------------------------------- ransac
+def ransac_check(src, tgt, corres, H, edge_thr, dist_thr, samples=None, seed=0, h0=0, use_checkers=True, want_T=False):
+    ok = torch.empty(H, dtype=torch.uint8, device=src.device)
+    Ts = torch.zeros((H, 16), dtype=F64, device=src.device) if want_T else None
+    check(lib().ibl_ransac_check(_p(src), _p(tgt), _p(corres), corres.shape[0], _p(samples), int(seed), int(h0), int(H),
+                                 float(edge_thr), float(dist_thr), int(use_checkers), _p(ok), _p(Ts), _stream()),
+          "ransac_check")
+    return ok, Ts
+
+
+def ransac_score(grid, src, tgt, corres, hyp_ids, max_d, samples=None, seed=0):
+    nh = hyp_ids.shape[0]
+    dev = src.device
+    inl = torch.empty(nh, dtype=torch.int32, device=dev)
+    err = torch.empty(nh, dtype=F64, device=dev)
+    cin = torch.empty(nh, dtype=torch.int32, device=dev)
+    Ts = torch.empty((nh, 16), dtype=F64, device=dev)
+    check(lib().ibl_ransac_score(grid.h, _p(src), src.shape[0], _p(tgt), _p(corres), corres.shape[0], _p(samples),
+                                 int(seed), _p(hyp_ids), nh, float(max_d), _p(inl), _p(err), _p(cin), _p(Ts), _stream()),
+          "ransac_score")
+    return inl, err, cin, Ts
+
+
+def _reg_dict(r):
+    return {"T": np.array(list(r.T)).reshape(4, 4), "fitness": r.fitness, "inlier_rmse": r.inlier_rmse,
+            "n_inliers": r.n_inliers, "err2": r.err2, "best_hyp": r.best_hyp, "drawn": r.drawn,
+            "validated": r.validated, "n_corres": r.n_corres, "iterations": r.iterations, "status": r.status}
+
+
+def ransac_run(grid, src, tgt, corres, max_iteration, confidence, max_d, edge_thr=0.9, samples=None, seed=0,
+               use_checkers=True, early_exit=True, block=1 << 16):
+    r = RegResultT()
+    check(lib().ibl_ransac_run(grid.h, _p(src), src.shape[0], _p(tgt), _p(corres), corres.shape[0], _p(samples),
+                               int(seed), int(max_iteration), float(confidence), float(max_d), float(edge_thr),
+                               int(use_checkers), int(early_exit), int(block), ctypes.byref(r), _stream()), "ransac_run")
+    return _reg_dict(r)
+
+
+# ------------------------------------------------------------------------------------------- icp
+def color_gradient(pts, nrm, col, idx, cnt):
+    out = torch.empty_like(pts)
+    check(lib().ibl_color_gradient(_p(pts), _p(nrm), _p(col), pts.shape[0], _p(idx), _p(cnt), idx.shape[1], _p(out),
+                                   _stream()), "color_gradient")
+    return out
+
+
+def p2p_update(src, nn, tgt):
+    T = (c_double * 16)()
+    check(lib().ibl_p2p_update(_p(src), _p(nn), src.shape[0], _p(tgt), T, _stream()), "p2p_update")
+    return np.array(list(T)).reshape(4, 4)
+
+
+def colored_update(src, scol, nn, tgt, tnrm, tcol, tgrad, lambda_geometric=0.968):
+    v = (c_double * 27)()
+    T = (c_double * 16)()
+    check(lib().ibl_colored_update(_p(src), _p(scol), _p(nn), src.shape[0], _p(tgt), _p(tnrm), _p(tcol), _p(tgrad),
+                                   float(lambda_geometric), v, T, _stream()), "colored_update")
+    return np.array(list(T)).reshape(4, 4), np.array(list(v))
+
+
+def icp(grid, src, tgt, max_d, init=None, mode=0, scol=None, tnrm=None, tcol=None, tgrad=None, max_iteration=30,
+        rel_fitness=1e-6, rel_rmse=1e-6, lambda_geometric=0.968):
+    r = RegResultT()
+    check(lib().ibl_icp(grid.h, _p(src), _p(scol), src.shape[0], _p(tgt), _p(tnrm), _p(tcol), _p(tgrad), int(mode),
+                        float(max_d), _T16(init), int(max_iteration), float(rel_fitness), float(rel_rmse),
+                        float(lambda_geometric), ctypes.byref(r), _stream()), "icp")
+    return _reg_dict(r)
+
+
+# ------------------------------------------------------------------------------------ similarity
+def cosine_segmax(det, mem, seg):
+    nd, D = det.shape
+    m = seg.shape[0] - 1
+    S = torch.empty((nd, m), dtype=torch.float32, device=det.device)
+    check(lib().ibl_cosine_segmax(_p(det), nd, _p(mem), mem.shape[0], D, _p(seg), m, _p(S), _stream()), "cosine_segmax")
+    return S
+
+
+def simvolume_topk(S, k):
+    nd, m = S.shape
+    s = min(nd, 3)
+    ncomb = 1 if nd == 1 else int(round(np.prod([nd - i for i in range(s)]) / np.prod(range(1, s + 1))))
+    flat = torch.empty((ncomb, k), dtype=torch.int64, device=S.device)
+    val = torch.empty((ncomb, k), dtype=torch.float32, device=S.device)
+    check(lib().ibl_simvolume_topk(_p(S), nd, m, int(k), _p(flat), _p(val), _stream()), "simvolume_topk")
+    return flat, val

@@ -66,8 +66,8 @@ int64_t ibl_select_rows(const uint8_t *keep, int64_t n, const double *a, const d
  * applies R only (normals). in==out allowed. */
 int ibl_transform_points(const double *h_T16, const double *in, int64_t n, int rotate_only, double *out,
                          void *stream);
-/* sequential-order-independent column means (np.mean(points, axis=0), object_memory.py:1030):
- * pairwise f64 reduction; h_mean host double[3]. Syncs. */
+/* column means in numpy's exact order (np.mean(points, axis=0), object_memory.py:1030-1031, adds the rows
+ * one by one): bit-identical to the reference's detected_mean / memory_mean.  h_mean host double[3]. Syncs. */
 int ibl_mean3(const double *pts, int64_t n, double *h_mean, void *stream);
 
 /* ---------------------------------------------------------------- uniform grid -------------- */

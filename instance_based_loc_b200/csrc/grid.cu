@@ -55,7 +55,7 @@ IBL_API int ibl_grid_create(const double *pts, int64_t n, double cell, int64_t m
     if (max_cells <= 0) max_cells = 1ll << 24;
     ibl_grid *g = new ibl_grid();
     memset(g, 0, sizeof(*g));
-    g->n = n; g->pts = pts;
+    g->n = n; g->pts = pts; g->stream = st;
     double mn[3] = {0, 0, 0}, mx[3] = {0, 0, 0};
     if (n > 0) {
         int nb = (int)((n + 255) / 256);
@@ -134,10 +134,13 @@ IBL_API int ibl_grid_create(const double *pts, int64_t n, double cell, int64_t m
 
 IBL_API void ibl_grid_destroy(ibl_grid_t *g) {
     if (!g) return;
-    cudaFree(g->cell_start);
-    cudaFree(g->sorted);
-    cudaFree(g->order);
-    cudaFree(g->ring);
+    // stream-ordered frees on the creating stream: queries already enqueued there finish first.  (cudaFree on a
+    // cudaMallocAsync allocation does NOT synchronise, so it must not be used while kernels may be in flight.)
+    cudaStream_t st = g->stream;
+    ibl_free(g->cell_start, st);
+    ibl_free(g->sorted, st);
+    ibl_free(g->order, st);
+    ibl_free(g->ring, st);
     delete g;
 }
 IBL_API double ibl_grid_cell(const ibl_grid_t *g) { return g ? g->cell : 0.0; }
@@ -169,7 +172,7 @@ __global__ void ring_step_kernel(uint8_t *ring, int nx, int ny, int nz, uint8_t 
 IBL_API int ibl_grid_build_ringfield(ibl_grid_t *g, int max_ring, void *stream) {
     IBL_ARG(g != nullptr && max_ring >= 1 && max_ring <= 255);
     cudaStream_t st = ibl_stream(stream);
-    if (g->ring) { cudaFree(g->ring); g->ring = nullptr; }
+    if (g->ring) { ibl_free(g->ring, st); g->ring = nullptr; }
     IBL_CUDA(ibl_alloc(&g->ring, (size_t)g->ncells, st));
     g->ring_cap = max_ring;
     int64_t nb = (g->ncells + 255) / 256;

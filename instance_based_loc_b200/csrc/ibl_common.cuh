@@ -62,6 +62,7 @@ struct ibl_grid {
     int *order;           // sorted position -> original index
     uint8_t *ring;        // optional Chebyshev ring-distance field [ncells]
     int ring_cap;
+    cudaStream_t stream;  // stream the grid was built on (frees are ordered on it)
 };
 
 // device view passed by value to kernels

@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(128) ransac_finalize_kernel(const int *__restr
         double x, y, z;
         ibl_xform(T, src[3 * cs], src[3 * cs + 1], src[3 * cs + 2], x, y, z);
         double d[3] = {x - tgt[3 * ct], y - tgt[3 * ct + 1], z - tgt[3 * ct + 2]};
-        ci += sqrt(ibl_dot(d, d)) < max_d;
+        ci += ibl_dot(d, d) < max_d * max_d;
     }
     for (int o = 16; o; o >>= 1) ci += __shfl_down_sync(0xffffffffu, ci, o);
     if (lane == 0) { inliers[hyp] = c; err2[hyp] = e; if (corres_inliers) corres_inliers[hyp] = ci; }
@@ -260,7 +260,7 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
                         double rho = (double)h_cinl[k] / (double)n_corres;
                         double den = rho < 1.0 ? log(1.0 - rho * rho * rho) : -INFINITY;
                         double kk = den == 0.0 ? INFINITY : log(1.0 - confidence) / den;
-                        if (kk < (double)max_iteration) est_k = (int64_t)ceil(kk);
+                        if (kk < (double)est_k) est_k = (int64_t)ceil(kk);
                     }
                 }
             }

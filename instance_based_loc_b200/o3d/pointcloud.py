@@ -1,0 +1,282 @@
+"""Device-resident PointCloud with the open3d 0.17 surface the reference's localisation path uses
+(call sites utils/depth_utils.py:36-44,80-90, utils/fpfh_register.py:86-98,
+object_memory/object_memory.py:992-1034, object_memory/object_info.py:63-76).
+
+Points / colours / normals are CUDA float64 [N,3] tensors.  Every geometric method is a libibl.so
+kernel (include/ibl.h); numpy only appears where the caller asks for host data (np.asarray).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .. import kernels as K
+
+F64 = torch.float64
+
+
+class KDTreeSearchParamHybrid:
+    def __init__(self, radius, max_nn):
+        self.radius = float(radius)
+        self.max_nn = int(max_nn)
+
+
+class KDTreeSearchParamKNN:
+    def __init__(self, knn=30):
+        self.radius = float("inf")
+        self.max_nn = int(knn)
+
+
+class KDTreeSearchParamRadius:
+    def __init__(self, radius):
+        self.radius = float(radius)
+        self.max_nn = 0
+
+
+class DeviceVec:
+    """Read view of a device [N,c] tensor that quacks like open3d.utility.Vector3dVector:
+    np.asarray(v) (one D2H copy, cached), len(v), v[i]."""
+
+    __slots__ = ("t", "_host")
+
+    def __init__(self, t):
+        self.t = t
+        self._host = None
+
+    def _h(self):
+        if self._host is None:
+            self._host = self.t.detach().cpu().numpy()
+        return self._host
+
+    def __array__(self, dtype=None, copy=None):
+        h = self._h()
+        return h if dtype is None else h.astype(dtype, copy=False)
+
+    def __len__(self):
+        return int(self.t.shape[0])
+
+    def __getitem__(self, i):
+        return self._h()[i]
+
+    def __iter__(self):
+        return iter(self._h())
+
+    @property
+    def shape(self):
+        return tuple(self.t.shape)
+
+    def __repr__(self):
+        return f"DeviceVec({tuple(self.t.shape)}, {self.t.dtype}, {self.t.device})"
+
+
+def Vector3dVector(arr=None):
+    """Host staging object: assignment to PointCloud.points/colors/normals uploads it once."""
+    if arr is None:
+        return np.zeros((0, 3), np.float64)
+    if isinstance(arr, (DeviceVec, torch.Tensor)):
+        return arr
+    return np.array(arr, dtype=np.float64).reshape(-1, 3)
+
+
+def Vector2iVector(arr=None):
+    if arr is None:
+        return np.zeros((0, 2), np.int32)
+    return np.array(arr, dtype=np.int32).reshape(-1, 2)
+
+
+def _as_dev(v):
+    if isinstance(v, DeviceVec):
+        return v.t
+    if isinstance(v, torch.Tensor):
+        return K.to_dev(v).reshape(-1, 3)
+    return K.to_dev(np.asarray(v, dtype=np.float64).reshape(-1, 3))
+
+
+class PointCloud:
+    def __init__(self, points=None):
+        self._p = None
+        self._c = None
+        self._n = None
+        self._grids = {}
+        self._color_grad = None
+        if points is not None:
+            self.points = points
+
+    # ------------------------------------------------------------------ storage
+    @staticmethod
+    def from_tensors(p, c=None, n=None):
+        r = PointCloud()
+        r._p, r._c, r._n = p, c, n
+        return r
+
+
+    def _empty(self):
+        return torch.zeros((0, 3), dtype=F64, device=K._dev())
+
+    def _invalidate(self):
+        self._grids = {}
+        self._color_grad = None
+
+    @property
+    def points(self):
+        return DeviceVec(self._p if self._p is not None else self._empty())
+
+    @points.setter
+    def points(self, v):
+        self._p = _as_dev(v)
+        self._invalidate()
+
+    @property
+    def colors(self):
+        return DeviceVec(self._c if self._c is not None else self._empty())
+
+    @colors.setter
+    def colors(self, v):
+        self._c = _as_dev(v)
+        self._color_grad = None
+
+    @property
+    def normals(self):
+        return DeviceVec(self._n if self._n is not None else self._empty())
+
+    @normals.setter
+    def normals(self, v):
+        self._n = _as_dev(v)
+        self._color_grad = None
+
+    def n(self):
+        return 0 if self._p is None else int(self._p.shape[0])
+
+    def has_points(self):
+        return self.n() > 0
+
+    def has_colors(self):
+        return self.n() > 0 and self._c is not None and self._c.shape[0] == self.n()
+
+    def has_normals(self):
+        return self.n() > 0 and self._n is not None and self._n.shape[0] == self.n()
+
+    def is_empty(self):
+        return self.n() == 0
+
+    def __repr__(self):
+        return f"PointCloud with {self.n()} points."
+
+    # ------------------------------------------------------------------ open3d A.10
+    def __iadd__(self, o):
+        if o.is_empty():
+            return self
+        if (self.is_empty() or self.has_normals()) and o.has_normals():
+            self._n = o._n if self.is_empty() else torch.cat([self._n, o._n])
+        else:
+            self._n = None
+        if (self.is_empty() or self.has_colors()) and o.has_colors():
+            self._c = o._c if self.is_empty() else torch.cat([self._c, o._c])
+        else:
+            self._c = None
+        self._p = o._p if self.is_empty() else torch.cat([self._p, o._p])
+        self._invalidate()
+        return self
+
+    def __add__(self, o):
+        r = PointCloud()
+        r += self
+        r += o
+        return r
+
+    def translate(self, v, relative=True):
+        if self.is_empty():
+            return self
+        v = np.asarray(v, np.float64).reshape(3)
+        if not relative:
+            v = v - self.get_center()
+        self._p = self._p + torch.from_numpy(v).to(self._p.device)   # one rounded f64 add per coordinate
+        self._invalidate()
+        return self
+
+    def transform(self, T):
+        if self.is_empty():
+            return self
+        T = np.asarray(T, np.float64)
+        self._p = K.transform_points(T, self._p)
+        if self.has_normals():
+            self._n = K.transform_points(T, self._n, rotate_only=True)
+        self._invalidate()
+        return self
+
+    def get_center(self):
+        return K.mean3(self._p) if self.n() else np.zeros(3)
+
+    def select_by_index(self, idx, invert=False):
+        n = self.n()
+        keep = torch.zeros(n, dtype=torch.uint8, device=K._dev())
+        it = idx.t.long() if isinstance(idx, DeviceVec) else torch.as_tensor(np.asarray(idx, np.int64)).to(keep.device)
+        keep[it] = 1
+        if invert:
+            keep = 1 - keep
+        return self._select_mask(keep)[0]
+
+    def _select_mask(self, keep, want_index=False):
+        p, c, nn, oi = K.select_rows(keep, self._p, self._c if self.has_colors() else None,
+                                     self._n if self.has_normals() else None, want_index=want_index)
+        return PointCloud.from_tensors(p, c, nn), oi
+
+    def remove_radius_outlier(self, nb_points, radius, print_progress=False):
+        """A.2: keep i iff #{j: d2(i,j) < r^2} (self included) > nb_points; order preserved."""
+        if nb_points < 1 or radius <= 0:
+            raise RuntimeError("Illegal input parameters, number of points and radius must be positive")
+        if self.is_empty():
+            return PointCloud(), []
+        keep = K.radius_outlier_mask(self.grid(radius), radius, nb_points)
+        out, oi = self._select_mask(keep, want_index=True)
+        return out, DeviceVec(oi)
+
+    def estimate_normals(self, search_param=None, fast_normal_computation=True):
+        sp = search_param or KDTreeSearchParamKNN(30)
+        if self.is_empty():
+            return
+        idx, _, cnt = self.knn(sp.radius, sp.max_nn, want_d2=False)
+        self._n = K.normals(self._p, idx, cnt)
+        self._color_grad = None
+
+    def paint_uniform_color(self, c):
+        c = torch.as_tensor(np.asarray(c, np.float64).reshape(1, 3)).to(K._dev())
+        self._c = c.expand(self.n(), 3).contiguous()
+        return self
+
+    def voxel_down_sample(self, voxel_size):
+        """open3d's own voxel_down_sample (map build only; output order is unspecified upstream)."""
+        from ..utils.depth_utils import voxel_down_sample_with_colors
+        return voxel_down_sample_with_colors(self, voxel_size)
+
+    def cluster_dbscan(self, *a, **k):
+        raise NotImplementedError("cluster_dbscan is memory-build only (SURVEY.md section 8(f) row N2): out of scope")
+
+    # ------------------------------------------------------------------ neighbour plumbing
+    def grid(self, cell, ring=0, max_cells=0):
+        """Cached cell-sorted grid for this cloud (invalidated on any mutation)."""
+        key = (float(cell), int(ring), int(max_cells))
+        g = self._grids.get(key)
+        if g is None:
+            g = K.Grid(self._p, cell, max_cells=max_cells, ring=ring)
+            self._grids[key] = g
+        return g
+
+    def knn(self, radius, max_nn, want_d2=True):
+        cell = K.knn_cell_for(self._p, max_nn, radius if np.isfinite(radius) else 1e30)
+        return K.knn_hybrid(self.grid(cell), radius, max_nn, want_d2=want_d2)
+
+    # ------------------------------------------------------------------ copy / pickle
+    def __deepcopy__(self, memo):
+        cl = lambda t: None if t is None else t.clone()  # noqa: E731
+        return PointCloud.from_tensors(cl(self._p), cl(self._c), cl(self._n))
+
+    def __getstate__(self):
+        h = lambda t: None if t is None else t.cpu().numpy()  # noqa: E731
+        return {"points": h(self._p), "colors": h(self._c), "normals": h(self._n)}
+
+    def __setstate__(self, st):
+        self._grids = {}
+        self._color_grad = None
+        d = lambda a: None if a is None else K.to_dev(a)  # noqa: E731
+        self._p, self._c, self._n = d(st["points"]), d(st["colors"]), d(st["normals"])

@@ -1,0 +1,313 @@
+"""Mirror of the reference's ``ObjectMemory`` query path (object_memory/object_memory.py:60-161, 779-846,
+852-1169): same constructor / ``localise`` / ``load`` / ``save_to_pkl`` signatures and the same result-affecting
+behaviour (including the two bugs SURVEY.md section 0 lists, behind ``bug_compatible=True``), with the whole per-frame
+computation on libibl.so kernels.
+
+What is new relative to the reference (none of it changes results):
+  * ``localise_arrays`` -- the same computation from in-memory rgb / depth / masks / embeddings (the detector and
+    encoder are out of scope; benchmarks and tests inject synthetic masks and embeddings here);
+  * memory-side caches: the normalised embedding bank, the union of all memory clouds with its search grid, and per
+    (memory-object tuple) the centred union cloud with its normals, FPFH features, grids and colour gradients.  The
+    reference recomputes all of these for every frame and every assignment.
+"""
+from __future__ import annotations
+
+import copy
+import os
+import pickle
+
+import numpy as np
+import torch
+from scipy.spatial.transform import Rotation
+
+from .. import kernels as K
+from ..o3d.pointcloud import PointCloud
+from ..utils.depth_utils import get_mask_coloured_pointclouds_from_depth
+from ..utils.fpfh_register import downsample_and_compute_fpfh, evaluate_transform, register_point_clouds
+from ..utils.similarity_volume import SimVolume
+from .object_info import ObjectInfo
+
+
+def default_load_rgb(path):
+    """object_memory.py:31-32 (imageio there; PIL here -- imageio is not in this image)."""
+    from PIL import Image
+    return np.asarray(Image.open(path))
+
+
+def default_load_depth(path):
+    """object_memory.py:34-40."""
+    if path.split('.')[-1] == 'npy':
+        return np.load(path)
+    from PIL import Image
+    return np.asarray(Image.open(path))
+
+
+class ObjectMemory():
+    def __init__(self, device, ram_pretrained_path, sam_checkpoint_path, camera_focal_lenth_x, camera_focal_lenth_y,
+                 get_embeddings_func, log_enabled=True, mem_formation_bounding_box_threshold=0.3,
+                 mem_formation_occlusion_overlap_threshold=0.9, object_info_max_embeddings_num=1000000,
+                 load_rgb_image_func=default_load_rgb, load_depth_image_func=default_load_depth,
+                 dataset_floor_thickness=0.1, lora_path=None, object_finder=None, bug_compatible=True):
+        self.device = device
+        self.ram_pretrained_path = ram_pretrained_path
+        self.sam_checkpoint_path = sam_checkpoint_path
+        self.camera_focal_lenth_x = camera_focal_lenth_x
+        self.camera_focal_lenth_y = camera_focal_lenth_y
+        self.log_enabled = log_enabled
+        self.mem_formation_bounding_box_threshold = mem_formation_bounding_box_threshold
+        self.mem_formation_occlusion_overlap_threshold = mem_formation_occlusion_overlap_threshold
+        self.object_info_max_embeddings_num = object_info_max_embeddings_num
+        self.get_embeddings_func = get_embeddings_func
+        self.load_rgb_image_func = load_rgb_image_func
+        self.load_depth_image_func = load_depth_image_func
+        self.dataset_floor_thickness = dataset_floor_thickness
+        # The detector (RAM + GroundingDINO + SAM, object_memory/object_finder.py) is out of scope: any object with
+        # find(rgb_path, consider_floor) -> (crops, boxes, masks[n,1,H,W], phrases) can be injected.
+        self.object_finder = object_finder
+        self.bug_compatible = bug_compatible
+        if self.get_embeddings_func is None and object_finder is not None:
+            raise NotImplementedError("Need to pass in get_embeddings_func")
+        self.memory: list[ObjectInfo] = []
+        self.floors = None
+        self._cache_key = None
+        self._cache = {}
+        self.last_localise_info = {}
+
+    def _log(self, statement):
+        if self.log_enabled:
+            print(f"\033[34m{statement}\033[0m")
+
+    def __repr__(self):
+        r = "".join(f"\t{o}\n" for o in self.memory)
+        return r if r else "\tNo objects in memory yet."
+
+    # ------------------------------------------------------------------------------------------ memory I/O
+    def add_object(self, name, emb, pointcloud, embeddings=None):
+        """Append one ObjectInfo (what process_image does after transform_pointcloud, :239-256)."""
+        info = ObjectInfo(len(self.memory), name, np.asarray(emb), pointcloud, self.object_info_max_embeddings_num)
+        if embeddings is not None:
+            info.embeddings = [np.asarray(e) for e in embeddings]
+            info._compute_means()
+        self.memory.append(info)
+        return info
+
+    def downsample_all_objects(self, voxel_size):
+        for o in self.memory:
+            o.downsample(voxel_size)
+
+    def save_to_pkl(self, save_directory):
+        """:779-826 -- [(ObjectInfo-without-cloud, points f64[N,3], colors f64[N,3]), ...], floors tuple.  The
+        reference builds the floors tuple from the LAST object (bug, :804-824); reproduced."""
+        def strip(o):
+            b = copy.copy(o)
+            b.pointcloud = None
+            return (b, np.asarray(o.pointcloud.points), np.asarray(o.pointcloud.colors))
+        mem = [strip(o) for o in self.memory]
+        with open(save_directory, "wb") as f:
+            pickle.dump((mem, mem[-1] if mem else None), f)
+
+    def load(self, load_directory):
+        """:831-846."""
+        with open(load_directory, "rb") as f:
+            pklable_memory, pklable_floors = pickle.load(f)
+
+        def conv(info_tuple):
+            if info_tuple is None:
+                return None
+            blank_info, pcd_points, pcd_colors = info_tuple
+            pcd = PointCloud(pcd_points)
+            pcd.colors = pcd_colors
+            blank_info.pointcloud = pcd
+            return blank_info
+        self.memory = [conv(it) for it in pklable_memory]
+        self.floors = conv(pklable_floors)
+
+    # ------------------------------------------------------------------------------------------ detection hand-off
+    def _get_object_info(self, rgb_image_path, depth_image_path, consider_floor, outlier_removal_config, depth_factor=1.):
+        """:125-161."""
+        if self.object_finder is None:
+            raise RuntimeError("no object_finder injected: the RAM/GroundingDINO/SAM detector is out of scope here; "
+                               "use localise_arrays(rgb, depth, masks, embeddings) or pass object_finder=")
+        imgs, boxes, masks, phrases = self.object_finder.find(rgb_image_path, consider_floor)
+        if imgs is None:
+            return None, None, None
+        embs = np.stack([np.array(torch.as_tensor(self.get_embeddings_func(
+            current_obj_grounded_img=imgs[i], current_obj_bounding_box=boxes[i], current_obj_mask=masks[i],
+            current_obj_phrase=phrases[i], full_rgb_image=self.load_rgb_image_func(rgb_image_path),
+            full_depth_image=self.load_depth_image_func(depth_image_path), consider_floor=consider_floor,
+            device=self.device)).cpu()) for i in range(len(imgs))])
+        clouds = get_mask_coloured_pointclouds_from_depth(
+            depth_image=self.load_depth_image_func(depth_image_path) / depth_factor,
+            rgb_image=self.load_rgb_image_func(rgb_image_path), masks=masks,
+            focal_length_x=self.camera_focal_lenth_x, focal_length_y=self.camera_focal_lenth_y,
+            outlier_removal_config=outlier_removal_config)
+        assert len(imgs) == len(boxes) == len(masks) == len(phrases) == len(embs)
+        return phrases, embs, clouds
+
+    # ------------------------------------------------------------------------------------------ caches
+    def _memory_cache(self):
+        key = (len(self.memory),) + tuple(id(m.pointcloud._p) for m in self.memory) + \
+              tuple(len(m.embeddings) for m in self.memory)
+        if key != self._cache_key:
+            self._cache_key = key
+            self._cache = {"assn": {}}
+        return self._cache
+
+    def _embedding_bank(self):
+        c = self._memory_cache()
+        if "bank" not in c:
+            rows = [np.asarray(e, np.float32).reshape(1, -1) for m in self.memory for e in m.embeddings]
+            seg = np.cumsum([0] + [len(m.embeddings) for m in self.memory]).astype(np.int32)
+            c["bank"] = (K.to_dev(np.concatenate(rows), torch.float32), K.to_dev(seg, torch.int32))
+        return c["bank"]
+
+    def _all_memory_pcd(self):
+        c = self._memory_cache()
+        if "all" not in c:
+            allp = PointCloud()
+            for obj in self.memory:
+                allp = allp + obj.pointcloud
+            c["all"] = allp
+        return c["all"]
+
+    def _chosen_memory(self, m_indices, fpfh_voxel_size):
+        """centred union of the chosen memory clouds + its FPFH state (identical for every frame)."""
+        c = self._memory_cache()["assn"]
+        key = (tuple(int(i) for i in m_indices), float(fpfh_voxel_size))
+        if key not in c:
+            pcd = PointCloud()
+            for m_index in m_indices:
+                pcd = pcd + self.memory[m_index].pointcloud
+            mean = pcd.get_center()
+            pcd.translate(-mean)
+            try:
+                feats = downsample_and_compute_fpfh(pcd, fpfh_voxel_size)
+            except Exception:
+                feats = None
+            if len(c) > 512:
+                c.pop(next(iter(c)))
+            c[key] = (pcd, mean, feats)
+        return c[key]
+
+    # ------------------------------------------------------------------------------------------ localise
+    def closest_similarities(self, detected_embs):
+        """:913-936: S[i][j] = max over stored embeddings e of object j of <e/|e|, d_i/|d_i|> (float32)."""
+        mem, seg = self._embedding_bank()
+        det = detected_embs if isinstance(detected_embs, torch.Tensor) else torch.from_numpy(
+            np.ascontiguousarray(np.asarray(detected_embs, np.float32)))
+        return K.cosine_segmax(det.to(device=mem.device, dtype=torch.float32).contiguous(), mem, seg)
+
+    def localise(self, image_path, depth_image_path, testname="", subtest_name="", save_point_clouds=False,
+                 outlier_removal_config=None, fpfh_global_dist_factor=2, fpfh_local_dist_factor=0.4,
+                 fpfh_voxel_size=0.05, topK=5, useLora=True, save_localised_pcd_path=None, consider_floor=False,
+                 perform_semantic_icp=True, depth_factor=1., max_detected_object_num=7):
+        """:852-1169."""
+        if outlier_removal_config is None:
+            outlier_removal_config = {"radius_nb_points": 8, "radius": 0.05}
+        consider_floor = False
+        detected_phrases, detected_embs, detected_pointclouds = self._get_object_info(
+            image_path, depth_image_path, consider_floor=consider_floor, outlier_removal_config=outlier_removal_config,
+            depth_factor=depth_factor)
+        return self._localise_core(detected_phrases, detected_embs, detected_pointclouds, outlier_removal_config,
+                                   fpfh_global_dist_factor, fpfh_local_dist_factor, fpfh_voxel_size,
+                                   perform_semantic_icp, max_detected_object_num)
+
+    def localise_arrays(self, rgb_image, depth_image, masks, embeddings, phrases=None, outlier_removal_config=None,
+                        fpfh_global_dist_factor=2, fpfh_local_dist_factor=0.4, fpfh_voxel_size=0.05,
+                        perform_semantic_icp=True, depth_factor=1., max_detected_object_num=7):
+        """localise() from arrays: rgb uint8 [H,W,3], depth [H,W] (float32 metres or raw / depth_factor), masks
+        bool [n,1,H,W] or [n,H,W], embeddings [n,D] -- numpy or CUDA tensors.  Same computation as localise after the
+        detector / encoder hand-off (object_memory.py:147-154 onwards)."""
+        if outlier_removal_config is None:
+            outlier_removal_config = {"radius_nb_points": 8, "radius": 0.05}
+        if masks is None or len(masks) == 0:
+            return self._localise_core(None, None, None, outlier_removal_config, fpfh_global_dist_factor,
+                                       fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
+                                       max_detected_object_num)
+        depth = depth_image
+        if depth_factor != 1.:
+            depth = depth_image / depth_factor
+        clouds = get_mask_coloured_pointclouds_from_depth(depth, rgb_image, masks, self.camera_focal_lenth_x,
+                                                          self.camera_focal_lenth_y, outlier_removal_config)
+        embs = embeddings.detach().cpu().numpy() if isinstance(embeddings, torch.Tensor) else np.array(embeddings)
+        phrases = phrases if phrases is not None else [f"object_{i}" for i in range(len(clouds))]
+        return self._localise_core(phrases, embs, clouds, outlier_removal_config, fpfh_global_dist_factor,
+                                   fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
+                                   max_detected_object_num)
+
+    def _localise_core(self, detected_phrases, detected_embs, detected_pointclouds, outlier_removal_config,
+                       fpfh_global_dist_factor, fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
+                       max_detected_object_num):
+        info = self.last_localise_info = {"assignments": [], "registrations": []}
+        if detected_embs is None:
+            return np.array([0., 0., 0., 0., 0., 0., 1.]), [[], []]           # :895-896
+
+        # take the largest clouds (:900-908; python's sort is stable, reverse keeps ties in input order)
+        if len(detected_pointclouds) > max_detected_object_num:
+            order = sorted(range(len(detected_pointclouds)), key=lambda i: detected_pointclouds[i].n(), reverse=True)
+            order = order[:max_detected_object_num]
+            detected_phrases = [detected_phrases[i] for i in order]
+            detected_embs = np.stack([detected_embs[i] for i in order])
+            detected_pointclouds = [detected_pointclouds[i] for i in order]
+
+        for m in self.memory:
+            m._compute_means()                                                 # :913-914
+        if len(detected_embs) > len(self.memory):                              # :918-920
+            detected_embs = detected_embs[:len(self.memory)]
+
+        closest = self.closest_similarities(detected_embs)                     # :922-936 (device, float32)
+        info["closest_similarities"] = closest
+
+        sv = SimVolume(closest)                                                # :974-984
+        subvolume_size = min(len(detected_pointclouds), 3)
+        sv.fast_construct_volume(subvolume_size)
+        assn_data = list(sv.get_top_indices_from_subvolumes(num_per_length=4))
+        info["assignments"] = copy.deepcopy(assn_data)
+
+        # second outlier removal on every detected cloud (:992-998)
+        detected_pointclouds = [obj.remove_radius_outlier(nb_points=outlier_removal_config["radius_nb_points"],
+                                                          radius=outlier_removal_config["radius"])[0]
+                                for obj in detected_pointclouds]
+        all_memory_pcd = self._all_memory_pcd()                                # :1001-1007
+        all_detected_pcd = PointCloud()
+        for pcd in detected_pointclouds:                                       # :1010-1016
+            all_detected_pcd = all_detected_pcd + pcd
+
+        if perform_semantic_icp and len(assn_data):
+            raise NotImplementedError                                          # :1036-1037, as in the reference
+
+        detected_mean = memory_mean = None
+        assn = None
+        for assn_num, assn in enumerate(assn_data):                            # :1020
+            chosen_detected_pcd = PointCloud()
+            for d_index, _ in assn:
+                chosen_detected_pcd = chosen_detected_pcd + detected_pointclouds[d_index]
+            chosen_memory_pcd, memory_mean, target_feats = self._chosen_memory([m for _, m in assn], fpfh_voxel_size)
+            detected_mean = chosen_detected_pcd.get_center()
+            chosen_detected_pcd.translate(-detected_mean)                      # :1030-1034
+            transform, rmse, fitness = register_point_clouds(
+                chosen_detected_pcd, chosen_memory_pcd, voxel_size=fpfh_voxel_size,
+                global_dist_factor=fpfh_global_dist_factor, local_dist_factor=fpfh_local_dist_factor,
+                target_features=target_feats)
+            global_frame_transform = np.array(transform, dtype=np.float64)     # :1096-1101
+            R = transform[:3, :3]
+            global_frame_transform[:3, 3] = transform[:3, 3] + memory_mean - R @ detected_mean
+            full_rmse, full_fitness = evaluate_transform(all_detected_pcd, all_memory_pcd,
+                                                         trans_init=global_frame_transform)      # :1104
+            assn_data[assn_num] = [assn, transform, rmse, fitness, full_rmse, full_fitness, detected_mean, memory_mean]
+            info["registrations"].append({"assn": assn, "transform": transform, "rmse": rmse, "fitness": fitness,
+                                          "full_rmse": full_rmse, "full_fitness": full_fitness})
+
+        best = sorted(assn_data, key=lambda x: x[5], reverse=True)             # :1111 (stable, by full fitness)
+        best_transform, best_assn = best[0][1], best[0][0]
+        if not self.bug_compatible:
+            detected_mean, memory_mean, assn = best[0][6], best[0][7], best_assn
+        # bug_compatible: means of the LAST loop iteration (:1127 vs :1030-1031) and the last assn (:1169)
+        R = np.array(best_transform[:3, :3])
+        t = np.array(best_transform[:3, 3])
+        tAvg = t + memory_mean - R @ detected_mean
+        qAvg = Rotation.from_matrix(R).as_quat()
+        localised_pose = np.concatenate((tAvg, qAvg))
+        info["best_assn"] = best_assn
+        info["best_transform"] = best_transform
+        return localised_pose, [assn, None]

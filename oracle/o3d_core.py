@@ -284,17 +284,24 @@ def hyp_transform(src, tgt, corres, sample):
 
 
 def ransac(src, tgt, corres, samples, max_d, edge_thr=0.9, confidence=0.99, early_exit=True,
-           checkers=True, block=1 << 16, trace=None):
-    """A.7 with sequential semantics over the host-provided sample array.
+           checkers=True, block=1 << 12, trace=None, max_iteration=None):
+    """A.7 with sequential semantics over the host-provided sample stream.
 
-    samples: int32 [max_iteration, 3] indices into corres.  Returns (RegResult, info dict).
+    samples: int32 [max_iteration, 3] indices into corres, OR a callable (h0, h1) -> int32 [h1-h0, 3] together
+    with max_iteration (the counter-based stream of oracle/sampler.py).  Returns (RegResult, info dict).
     """
     src, tgt = _f64(src), _f64(tgt)
-    corres, samples = _i32(corres), _i32(samples)
+    corres = _i32(corres)
+    if callable(samples):
+        H = int(max_iteration)
+        get = samples
+    else:
+        samples = _i32(samples)
+        H = len(samples)
+        get = lambda a, b: samples[a:b]  # noqa: E731
     best = RegResult()
     best_h = -1
     info = {"drawn": 0, "validated": 0, "best_hyp": -1}
-    H = len(samples)
     if len(corres) < 3 or max_d <= 0 or H == 0:
         return best, info
     tree = cKDTree(tgt)
@@ -302,15 +309,16 @@ def ransac(src, tgt, corres, samples, max_d, edge_thr=0.9, confidence=0.99, earl
     h0 = 0
     while h0 < min(H, est_k):
         h1 = min(H, h0 + block)
+        blk = _i32(get(h0, h1))
         if checkers:
-            ok = ransac_check(src, tgt, corres, samples[h0:h1], edge_thr, max_d)
+            ok = ransac_check(src, tgt, corres, blk, edge_thr, max_d)
         else:
             ok = np.ones(h1 - h0, bool)
         for off in np.nonzero(ok)[0]:
             h = h0 + int(off)
             if h >= est_k:
                 break
-            T = hyp_transform(src, tgt, corres, samples[h])
+            T = hyp_transform(src, tgt, corres, blk[off])
             pts = transform_points(T, src)
             res = score(pts, tgt, tree, max_d, T)
             info["validated"] += 1
@@ -328,7 +336,7 @@ def ransac(src, tgt, corres, samples, max_d, edge_thr=0.9, confidence=0.99, earl
                         kk = math.inf
                     else:
                         kk = math.log(1.0 - confidence) / den
-                    if kk < H:
+                    if kk < est_k:      # Registration.cpp: est_k_local_d < est_k_global ? ceil : keep
                         est_k = int(math.ceil(kk))
         h0 = h1
     info["drawn"] = int(min(H, max(est_k, 0)))

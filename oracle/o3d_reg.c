@@ -182,7 +182,7 @@ ORC_API void orc_ransac_check(const double *src, const double *tgt, const int32_
     }
 }
 
-/* EvaluateInlierCorrespondenceRatio numerator: #{c : |T s_c - t_c| < max_d} */
+/* EvaluateInlierCorrespondenceRatio numerator: #{c : |T s_c - t_c|^2 < max_d^2} (squaredNorm) */
 ORC_API int32_t orc_corres_inliers(const double *T, const double *src, const double *tgt,
                                    const int32_t *corres, int c, double max_d) {
     int32_t cnt = 0;
@@ -191,7 +191,7 @@ ORC_API int32_t orc_corres_inliers(const double *T, const double *src, const dou
         xform(T, src + 3 * (size_t)corres[2 * i], q);
         const double *t = tgt + 3 * (size_t)corres[2 * i + 1];
         double d[3] = {q[0] - t[0], q[1] - t[1], q[2] - t[2]};
-        if (sqrt(dot3(d, d)) < max_d) ++cnt;
+        if (dot3(d, d) < max_d * max_d) ++cnt;
     }
     return cnt;
 }

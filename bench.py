@@ -1,0 +1,286 @@
+#!/usr/bin/env python
+"""bench.py -- localised frames/s of the per-frame object-localisation hot path (BASELINE.json metric) on
+synthetic 8room-style frames (configs[1]: query frames x 40-object memory, DINO-like 768-d embeddings).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            product arm (libibl.so kernels through the C ABI)
+  python bench.py --impl reference ...                           the reference's CPU path (oracle restatement, host cores)
+  torchrun ... bench.py --gpus N ...                             one rank per GPU; frames are sharded by rank (weak scaling)
+
+A step = one pass of ObjectMemory.localise_arrays over a batch of --frames-per-step synthetic frames.
+value  : frames/s, inputs resident in HBM when the timed region starts.
+e2e    : frames/s through the same public call with HOST (pinned) rgb/depth/masks/embeddings, H2D copies and the D2H
+         of the pose inside the timed region.
+One JSON line on stdout (rank 0)."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOAD = dict(name="8room-style: 600x600 f=300 query frames vs 40-object memory (configs[1])", m=40, H=600, W=600,
+                f=300.0, D=768, scene_seed=1002, mem_spacing=0.01, mem_voxel=0.01, fpfh_voxel_size=0.05,
+                fpfh_global_dist_factor=1.5, fpfh_local_dist_factor=1.5, ransac_seed=1002)
+LOCALISE_KW = dict(fpfh_global_dist_factor=WORKLOAD["fpfh_global_dist_factor"],
+                   fpfh_local_dist_factor=WORKLOAD["fpfh_local_dist_factor"],
+                   fpfh_voxel_size=WORKLOAD["fpfh_voxel_size"], perform_semantic_icp=False)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    def __init__(self, gpu_index):
+        self.rows, self.p = [], None
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                       "-i", str(gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) >= 6 and r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def make_inputs(n_frames, rank, device):
+    """Scene + memory arrays + a pool of distinct frames for this rank (host arrays; deterministic per rank)."""
+    from instance_based_loc_b200 import synth
+    w = WORKLOAD
+    scene = synth.make_scene(m=w["m"], seed=w["scene_seed"], D=w["D"])
+    frames = synth.make_frames(scene, n_frames, H=w["H"], W=w["W"], f=w["f"], device=device, seed=100 + rank)
+    return scene, frames
+
+
+def cpu_reference_sample(scene_memory_host, frames, budget_s, seed):
+    """Times the oracle (CPU restatement of the reference path: numpy + scipy cKDTree + C, all host threads the
+    libraries use) on frame 0 until ~budget_s of work is done.  Frames/s is extrapolated from the fraction of the
+    frame's assignments that were registered inside the budget (memory-side FPFH included, as the reference
+    recomputes it per assignment)."""
+    from oracle import o3d_core, ref_pipeline
+    o3d_core.lib()
+    fr = frames[0]
+    w = WORKLOAD
+    cfg = {"radius_nb_points": 8, "radius": 0.05}
+    t0 = time.perf_counter()
+    det = ref_pipeline.detect_clouds(fr["depth"], fr["rgb"], fr["masks"], w["f"], w["f"], cfg)
+    t_front = time.perf_counter() - t0
+    # orchestration up to the assignment list (cheap) -- then time registrations one by one
+    embs = np.array(fr["embs"], np.float32)
+    if len(det) > 7:
+        order = sorted(range(len(det)), key=lambda i: len(det[i][0]), reverse=True)[:7]
+        det, embs = [det[i] for i in order], embs[order]
+    from oracle import ref_port
+    t1 = time.perf_counter()
+    S = ref_port.closest_similarities(embs, [m["embeddings"] for m in scene_memory_host])
+    assns = ref_port.simvolume_assignments(S, 4)
+    det2 = []
+    for p, c in det:
+        keep = o3d_core.remove_radius_outlier_mask(p, 8, 0.05)
+        det2.append((p[keep], c[keep]))
+    all_mem = np.concatenate([m["points"] for m in scene_memory_host])
+    all_det = np.concatenate([p for p, _ in det2])
+    t_mid = time.perf_counter() - t1
+    done, t_reg = 0, 0.0
+    for assn in assns:
+        t2 = time.perf_counter()
+        dp = np.concatenate([det2[d][0] for d, _ in assn]); dc = np.concatenate([det2[d][1] for d, _ in assn])
+        mp = np.concatenate([scene_memory_host[m]["points"] for _, m in assn])
+        mc = np.concatenate([scene_memory_host[m]["colors"] for _, m in assn])
+        mm, dm = mp.mean(0), dp.mean(0)
+        T, _, _ = ref_pipeline.register_point_clouds(dp - dm, dc, mp - mm, mc, w["fpfh_voxel_size"],
+                                                     w["fpfh_global_dist_factor"], w["fpfh_local_dist_factor"], seed=seed)
+        G = np.array(T); G[:3, 3] = T[:3, 3] + mm - T[:3, :3] @ dm
+        ref_pipeline.evaluate_transform(all_det, all_mem, G)
+        t_reg += time.perf_counter() - t2
+        done += 1
+        if t_front + t_mid + t_reg > budget_s:
+            break
+    per_frame = t_front + t_mid + t_reg * (len(assns) / max(done, 1))
+    return {"value": 1.0 / per_frame, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"frame 0 of the workload: front end + {done} of {len(assns)} assignment registrations timed "
+                      f"({t_front + t_mid + t_reg:.1f} s), extrapolated to the whole frame",
+            "seconds_per_frame": per_frame}
+
+
+def run_product(args):
+    import torch
+    import torch.distributed as dist
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from instance_based_loc_b200 import kernels as K
+    from instance_based_loc_b200 import selfcheck
+    from instance_based_loc_b200.o3d import registration as reg
+    w = WORKLOAD
+    B = args.frames_per_step
+    scene, frames = make_inputs(B, rank, "cuda")
+    om, host_mem = selfcheck.build_memory(scene, w["mem_spacing"], w["mem_voxel"], f=w["f"])
+    reg.ransac_seed = w["ransac_seed"]
+    resident = [{k: torch.from_numpy(np.ascontiguousarray(fr[k])).to(dev) for k in ("rgb", "depth", "masks", "embs")}
+                for fr in frames]
+    pinned = [{k: torch.from_numpy(np.ascontiguousarray(fr[k])).pin_memory() for k in ("rgb", "depth", "masks", "embs")}
+              for fr in frames]
+    h2d = sum(t.numel() * t.element_size() for fr in pinned for t in fr.values())
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    gathered = [torch.zeros((B, 7), dtype=torch.float64, device=dev) for _ in range(world)]
+
+    def step(host_inputs):
+        flush.zero_()                                   # L2 flush between iterations (126 MB L2 < 256 MiB)
+        poses = []
+        for i in range(B):
+            if host_inputs:
+                fr = {k: v.to(dev, non_blocking=True) for k, v in pinned[i].items()}
+            else:
+                fr = resident[i]
+            pose, _ = om.localise_arrays(fr["rgb"], fr["depth"], fr["masks"], fr["embs"], **LOCALISE_KW)
+            poses.append(pose)
+        out = torch.from_numpy(np.stack(poses)).to(dev)
+        if world > 1:                                   # the only traffic that crosses NVLink: 56 B per frame
+            dist.all_gather(gathered, out)
+        return out.cpu()                                # D2H of the step's result
+
+    def timed(host_inputs, steps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step(host_inputs)
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(args.warmup):
+        step(False)
+    step(True)
+    clocks = ClockSampler(local)
+    K.prof_enable(True)
+    K.prof_read()
+    l0 = K.launch_count()
+    ms = timed(False, args.steps)
+    launches = K.launch_count() - l0
+    prof = K.prof_read()
+    K.prof_enable(False)
+    ms_e2e = timed(True, args.steps)
+    clk = clocks.stop()
+    total_frames = B * args.steps * world
+    value = total_frames / (ms / 1e3)
+    e2e = total_frames / (ms_e2e / 1e3)
+
+    peak, peak_src = peaks()
+    top = max(prof.items(), key=lambda kv: kv[1]["ms"]) if prof else ("none", {"ms": 0.0, "launches": 0, "work": 0.0})
+    tname, t = top
+    per_launch_ms = t["ms"] / max(t["launches"], 1)
+    achieved = (t["work"] / max(t["launches"], 1)) / (per_launch_ms / 1e3) / 1e9 if per_launch_ms > 0 else 0.0
+    roofline = {"kernel": tname, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "avg_launch_ms": per_launch_ms, "launches": t["launches"], "share_of_step": t["ms"] / ms,
+                "note": "algorithmic bytes model in DESIGN.md; work for feature_nn is f64 flop, reported as GFLOP/s"}
+    kernels = {k: {"ms": round(v["ms"], 3), "launches": v["launches"],
+                   "gwork_per_s": round(v["work"] / max(v["ms"], 1e-9) / 1e6, 2)} for k, v in
+               sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
+    line = {"metric": "localised frames/s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": w["name"], "frames_per_step_per_gpu": B, "memory_objects": w["m"],
+                       "memory_points": int(sum(len(m["points"]) for m in host_mem)), "embedding_dim": w["D"],
+                       "ransac": "max_iteration 4e6, confidence 0.99, counter-based sample stream",
+                       "l2_flush": "256 MiB memset before every step", "parallelism": f"frames sharded over {world} rank(s)"},
+            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 56,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches, "clocks": clk, "roofline": roofline, "kernels": kernels}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_reference_sample(host_mem, frames, args.cpu_budget, w["ransac_seed"])
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle restatement; Open3D itself is not installable here) on the
+    same workload.  Each step is a bounded sample of one frame; rank 0 only."""
+    if int(os.environ.get("RANK", 0)) != 0:
+        return
+    from oracle import ref_port
+    from instance_based_loc_b200 import synth
+    w = WORKLOAD
+    scene, frames = make_inputs(1, 0, "cpu")
+    host_mem = []
+    for j in range(scene.m):
+        p, c = synth.memory_cloud(scene, j, w["mem_spacing"])
+        p2, c2, _, _ = ref_port.voxel_down_sample(p, c, w["mem_voxel"])
+        host_mem.append({"points": p2, "colors": c2, "embeddings": scene.memory_embs[j]})
+    budget = max(5.0, args.cpu_budget / max(args.steps, 1))
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference_sample(host_mem, frames, 2.0, w["ransac_seed"])
+    vals = [cpu_reference_sample(host_mem, frames, budget, w["ransac_seed"]) for _ in range(args.steps)]
+    spf = float(np.mean([v["seconds_per_frame"] for v in vals]))
+    cb = dict(vals[-1], value=1.0 / spf)
+    line = {"impl": "reference", "metric": "localised frames/s", "value": 1.0 / spf, "unit": "frames/s",
+            "n_gpus": int(os.environ.get("WORLD_SIZE", 1)), "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": spf * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": {"workload": w["name"], "memory_objects": w["m"], "embedding_dim": w["D"]},
+            "cpu_baseline": cb, "e2e": {"value": 1.0 / spf, "unit": "frames/s", "h2d_bytes_per_step": 0,
+                                        "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="product", choices=["product", "reference"])
+    ap.add_argument("--frames-per-step", type=int, default=4)
+    ap.add_argument("--cpu-budget", type=float, default=25.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_product(args)
+
+
+if __name__ == "__main__":
+    main()

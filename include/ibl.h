@@ -190,6 +190,17 @@ int ibl_cosine_segmax(const float *det, int32_t nd, const float *mem, int64_t E,
 int ibl_simvolume_topk(const float *S, int32_t nd, int32_t m, int32_t k, int64_t *out_flat, float *out_val,
                        void *stream);
 
+/* ---------------------------------------------------------------- instrumentation ------------ */
+/* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
+int64_t ibl_launch_count(void);
+/* Optional per-kernel timing with cudaEvents on the launching stream.  ibl_prof_read fills arrays of
+ * ibl_prof_num_tags() entries (milliseconds, launches, algorithmic work units: bytes, or f64 flops for
+ * feature_nn) accumulated since the previous read, and synchronises the device. */
+void ibl_prof_enable(int on);
+int ibl_prof_num_tags(void);
+const char *ibl_prof_tag_name(int tag);
+int ibl_prof_read(double *ms, int64_t *launches, double *work);
+
 #ifdef __cplusplus
 }
 #endif

@@ -74,6 +74,11 @@ _PROTOS = {
                         c_double, c_double, POINTER(RegResultT), _V]),
     "ibl_cosine_segmax": (c_int, [_V, c_int32, _V, c_int64, c_int32, _V, c_int32, _V, _V]),
     "ibl_simvolume_topk": (c_int, [_V, c_int32, c_int32, c_int32, _V, _V, _V]),
+    "ibl_launch_count": (c_int64, []),
+    "ibl_prof_enable": (None, [c_int]),
+    "ibl_prof_num_tags": (c_int, []),
+    "ibl_prof_tag_name": (c_char_p, [c_int]),
+    "ibl_prof_read": (c_int, [POINTER(c_double), POINTER(c_int64), POINTER(c_double)]),
 }
 
 EXPORTS = sorted(_PROTOS)

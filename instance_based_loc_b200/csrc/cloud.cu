@@ -109,14 +109,18 @@ static int backproject_impl(const DT *depth, const uint8_t *rgb, const uint8_t *
     IBL_CUDA(ibl_alloc(&offs, nc + 1, st));
     IBL_CUDA(cudaMemsetAsync(counts + nc, 0, sizeof(int), st));
     dim3 grid(ntiles, n_masks);
-    bp_count_kernel<DT><<<grid, 256, 0, st>>>(depth, masks, P, ntiles, vec, counts);
-    IBL_LAUNCH_CHECK();
+    {
+        IBL_PROF(IBL_PROF_BACKPROJECT, st, (double)n_masks * P * (sizeof(DT) + 1));
+        bp_count_kernel<DT><<<grid, 256, 0, st>>>(depth, masks, P, ntiles, vec, counts);
+        IBL_LAUNCH_CHECK();
+    }
     size_t tb = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, tb, counts, offs, (int)(nc + 1), st);
     void *tmp = nullptr;
     IBL_CUDA(cudaMallocAsync(&tmp, tb ? tb : 1, st));
     IBL_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, counts, offs, (int)(nc + 1), st));
     if (out_pts) {
+        IBL_PROF(IBL_PROF_BACKPROJECT, st, (double)n_masks * P * (sizeof(DT) + 1) + 3.0 * P);
         bp_write_kernel<DT><<<grid, 256, 0, st>>>(depth, rgb, masks, P, W, ntiles, vec, hor, ver, fx, fy, offs, out_pts,
                                                   rgb ? out_cols : nullptr);
         IBL_LAUNCH_CHECK();
@@ -255,8 +259,11 @@ IBL_API int ibl_mean3(const double *pts, int64_t n, double *h_mean, void *stream
     cudaStream_t st = ibl_stream(stream);
     double *d = nullptr;
     IBL_CUDA(ibl_alloc(&d, 3, st));
-    seqsum3_kernel<<<1, 256, 0, st>>>(pts, n, d);
-    IBL_LAUNCH_CHECK();
+    {
+        IBL_PROF(IBL_PROF_MEAN, st, 24.0 * n);
+        seqsum3_kernel<<<1, 256, 0, st>>>(pts, n, d);
+        IBL_LAUNCH_CHECK();
+    }
     double hs[3];
     IBL_CUDA(cudaMemcpyAsync(hs, d, sizeof(hs), cudaMemcpyDeviceToHost, st));
     IBL_CUDA(cudaStreamSynchronize(st));

@@ -147,6 +147,7 @@ IBL_API int ibl_normals(const double *pts, int64_t n, const int32_t *nbr_idx, co
     IBL_ARG(n >= 0 && max_nn >= 1);
     if (n == 0) return IBL_OK;
     IBL_ARG(pts && nbr_idx && nbr_cnt && normals);
+    IBL_PROF(IBL_PROF_NORMALS, ibl_stream(stream), (double)n * (24.0 + 28.0 * max_nn + 24.0));
     normals_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ibl_stream(stream)>>>(pts, n, nbr_idx, nbr_cnt, max_nn, normals);
     IBL_LAUNCH_CHECK();
     return IBL_OK;
@@ -236,6 +237,7 @@ IBL_API int ibl_spfh(const double *pts, const double *nrm, int64_t n, const int3
     IBL_ARG(pts && nrm && nbr_idx && nbr_cnt && spfh);
     int64_t blocks = (n + 3) / 4;
     if (blocks > IBL_SMS * 32) blocks = IBL_SMS * 32;
+    IBL_PROF(IBL_PROF_SPFH, ibl_stream(stream), (double)n * (48.0 + 52.0 * max_nn + 264.0));
     spfh_kernel<<<(unsigned)blocks, 128, 0, ibl_stream(stream)>>>(pts, nrm, n, nbr_idx, nbr_cnt, max_nn, spfh);
     IBL_LAUNCH_CHECK();
     return IBL_OK;
@@ -294,6 +296,7 @@ IBL_API int ibl_fpfh(int64_t n, const int32_t *nbr_idx, const double *nbr_d2, co
     IBL_ARG(nbr_idx && nbr_d2 && nbr_cnt && spfh && fpfh);
     int64_t blocks = (n + 3) / 4;
     if (blocks > IBL_SMS * 32) blocks = IBL_SMS * 32;
+    IBL_PROF(IBL_PROF_FPFH, ibl_stream(stream), (double)n * (max_nn * (264.0 + 12.0) + 528.0));
     fpfh_kernel<<<(unsigned)blocks, 128, 0, ibl_stream(stream)>>>(n, nbr_idx, nbr_d2, nbr_cnt, max_nn, spfh, fpfh);
     IBL_LAUNCH_CHECK();
     return IBL_OK;

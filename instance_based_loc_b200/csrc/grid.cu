@@ -97,6 +97,7 @@ IBL_API int ibl_grid_create(const double *pts, int64_t n, double cell, int64_t m
         IBL_CUDA(ibl_alloc(&cid2, (size_t)n, st));
         IBL_CUDA(ibl_alloc(&ord, (size_t)n, st));
         int nb = (int)((n + 255) / 256);
+        IBL_PROF(IBL_PROF_GRID_BUILD, st, 72.0 * n + 8.0 * g->ncells);
         cellid_kernel<<<nb, 256, 0, st>>>(pts, n, g->ox, g->oy, g->oz, g->inv_cell, g->nx, g->ny, g->nz, cid, ord);
         IBL_LAUNCH_CHECK();
         int bits = 1;

@@ -46,6 +46,7 @@ static int radius_launch(const ibl_grid_t *g, double radius, int32_t nb, int32_t
     int blocks = (int)((warps_needed * 32 + 255) / 256);
     int maxb = IBL_SMS * 16;
     if (blocks > maxb) blocks = maxb;
+    IBL_PROF(IBL_PROF_RADIUS, ibl_stream(stream), 33.0 * g->n);
     radius_count_kernel<<<blocks, 256, 0, ibl_stream(stream)>>>(ibl_view(g), g->n, radius * radius, S, nb, count, keep);
     IBL_LAUNCH_CHECK();
     return IBL_OK;
@@ -224,6 +225,7 @@ IBL_API int ibl_knn_hybrid(const ibl_grid_t *g, const double *queries, int64_t n
     int64_t blocks64 = (nq + wpb - 1) / wpb;
     int blocks = (int)(blocks64 > IBL_SMS * 32 ? IBL_SMS * 32 : blocks64);
     double r2 = isfinite(radius) ? radius * radius : INFINITY;
+    IBL_PROF(IBL_PROF_KNN, st, (double)nq * (32.0 + 4.0 + max_nn * (d2 ? 12.0 : 4.0)));
     if (max_nn <= 96) {
         constexpr int CAP = 256;
         size_t sm = (size_t)wpb * CAP * 12;
@@ -295,8 +297,11 @@ IBL_API int ibl_nn_score(const ibl_grid_t *g, const double *src, int64_t n, cons
         IBL_CUDA(ibl_alloc(&pc, (size_t)nb, st));
         IBL_CUDA(ibl_alloc(&pe, (size_t)nb, st));
         IBL_CUDA(ibl_alloc(&dres, 1, st));
-        nn_score_kernel<<<nb, 256, 0, st>>>(ibl_view(g), src, n, T, has_T, max_d, max_d * max_d, nn_idx, nn_d2, pc, pe);
-        IBL_LAUNCH_CHECK();
+        {
+            IBL_PROF(IBL_PROF_NN_SCORE, st, (double)n * (24.0 + (nn_idx ? 4.0 : 0.0) + (nn_d2 ? 8.0 : 0.0)));
+            nn_score_kernel<<<nb, 256, 0, st>>>(ibl_view(g), src, n, T, has_T, max_d, max_d * max_d, nn_idx, nn_d2, pc, pe);
+            IBL_LAUNCH_CHECK();
+        }
         score_final_kernel<<<1, 32, 0, st>>>(pc, pe, nb, dres);
         IBL_LAUNCH_CHECK();
         if (h_result) {

@@ -31,7 +31,26 @@ void ibl_set_error(const char *fmt, ...);
         }                                                                        \
     } while (0)
 
-#define IBL_LAUNCH_CHECK() IBL_CUDA(cudaGetLastError())
+extern unsigned long long g_ibl_launches;
+#define IBL_LAUNCH_CHECK()                              \
+    do {                                                \
+        __sync_fetch_and_add(&g_ibl_launches, 1ull);    \
+        IBL_CUDA(cudaGetLastError());                   \
+    } while (0)
+
+// optional per-kernel event timing (prof.cu); a scope brackets the launches that follow it in the same block
+enum IblProfTag { IBL_PROF_BACKPROJECT = 0, IBL_PROF_RADIUS, IBL_PROF_KNN, IBL_PROF_NORMALS, IBL_PROF_SPFH, IBL_PROF_FPFH,
+                  IBL_PROF_FEATURE_NN, IBL_PROF_RANSAC_CHECK, IBL_PROF_RANSAC_SCORE, IBL_PROF_NN_SCORE, IBL_PROF_ICP_REDUCE,
+                  IBL_PROF_COLOR_GRAD, IBL_PROF_GRID_BUILD, IBL_PROF_SIMVOL, IBL_PROF_COSINE, IBL_PROF_VOXEL, IBL_PROF_MEAN,
+                  IBL_PROF_MISC, IBL_PROF_COUNT };
+int ibl_prof_begin(int tag, cudaStream_t st, double bytes);
+void ibl_prof_end(int slot, cudaStream_t st);
+struct IblProfScope {
+    int slot; cudaStream_t st;
+    IblProfScope(int tag, cudaStream_t s, double bytes) : slot(ibl_prof_begin(tag, s, bytes)), st(s) {}
+    ~IblProfScope() { ibl_prof_end(slot, st); }
+};
+#define IBL_PROF(tag, st, bytes) IblProfScope prof_scope__((tag), (st), (double)(bytes))
 
 static inline cudaStream_t ibl_stream(void *s) { return reinterpret_cast<cudaStream_t>(s); }
 

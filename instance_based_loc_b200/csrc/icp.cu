@@ -46,8 +46,11 @@ static int reduceK(int64_t n, F f, double *h_out, cudaStream_t st) {
     if (nb > IBL_SMS * 2) nb = IBL_SMS * 2;
     double *part = nullptr;
     IBL_CUDA(ibl_alloc(&part, (size_t)nb * K, st));
-    reduceK_kernel<K, F><<<nb, 256, 0, st>>>(n, f, part);
-    IBL_LAUNCH_CHECK();
+    {
+        IBL_PROF(IBL_PROF_ICP_REDUCE, st, (double)n * (28.0 + 8.0 * K));
+        reduceK_kernel<K, F><<<nb, 256, 0, st>>>(n, f, part);
+        IBL_LAUNCH_CHECK();
+    }
     std::vector<double> hp((size_t)nb * K);
     IBL_CUDA(cudaMemcpyAsync(hp.data(), part, sizeof(double) * nb * K, cudaMemcpyDeviceToHost, st));
     IBL_CUDA(cudaStreamSynchronize(st));
@@ -145,6 +148,7 @@ IBL_API int ibl_color_gradient(const double *pts, const double *nrm, const doubl
     IBL_ARG(n >= 0);
     if (n == 0) return IBL_OK;
     IBL_ARG(pts && nrm && col && nbr_idx && nbr_cnt && grad);
+    IBL_PROF(IBL_PROF_COLOR_GRAD, ibl_stream(stream), (double)n * (72.0 + 52.0 * max_nn + 24.0));
     color_gradient_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ibl_stream(stream)>>>(pts, nrm, col, n, nbr_idx, nbr_cnt, max_nn, grad);
     IBL_LAUNCH_CHECK();
     return IBL_OK;

@@ -47,6 +47,7 @@ IBL_API int ibl_feature_nn(const double *fa, int64_t na, const double *fb, int64
     IBL_ARG(na >= 0 && nb >= 0);
     if (na == 0) return IBL_OK;
     IBL_ARG(fa && nn && (nb == 0 || fb));
+    IBL_PROF(IBL_PROF_FEATURE_NN, ibl_stream(stream), 3.0 * 33.0 * (double)na * (double)nb);
     feature_nn_kernel<<<(unsigned)((na + FNN_THREADS - 1) / FNN_THREADS), FNN_THREADS, 0, ibl_stream(stream)>>>(fa, na, fb, nb, nn);
     IBL_LAUNCH_CHECK();
     return IBL_OK;

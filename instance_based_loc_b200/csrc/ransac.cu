@@ -68,6 +68,7 @@ IBL_API int ibl_ransac_check(const double *src, const double *tgt, const int32_t
     IBL_ARG(H >= 0 && n_corres >= 1 && n_corres < (1ll << 31));
     if (H == 0) return IBL_OK;
     IBL_ARG(src && tgt && corres && pass);
+    IBL_PROF(IBL_PROF_RANSAC_CHECK, ibl_stream(stream), 157.0 * (double)H);
     ransac_check_kernel<<<(unsigned)((H + 127) / 128), 128, 0, ibl_stream(stream)>>>(
         src, tgt, corres, n_corres, samples, seed, h0, H, edge_thr, dist_thr, use_checkers, pass, T_out);
     IBL_LAUNCH_CHECK();
@@ -175,8 +176,11 @@ IBL_API int ibl_ransac_score(const ibl_grid_t *tgt_grid, const double *src, int6
     IBL_CUDA(ibl_alloc(&pc, (size_t)nh * ntiles, st));
     IBL_CUDA(ibl_alloc(&pe, (size_t)nh * ntiles, st));
     dim3 grid(ntiles, (unsigned)nh);
-    ransac_score_kernel<<<grid, SCORE_THREADS, 0, st>>>(ibl_view(tgt_grid), src, n_src, T_out, max_d, max_d * max_d, ntiles, pc, pe);
-    IBL_LAUNCH_CHECK();
+    {
+        IBL_PROF(IBL_PROF_RANSAC_SCORE, st, (double)nh * (24.0 * n_src + 128.0));
+        ransac_score_kernel<<<grid, SCORE_THREADS, 0, st>>>(ibl_view(tgt_grid), src, n_src, T_out, max_d, max_d * max_d, ntiles, pc, pe);
+        IBL_LAUNCH_CHECK();
+    }
     ransac_finalize_kernel<<<(unsigned)((nh * 32 + 127) / 128), 128, 0, st>>>(pc, pe, ntiles, nh, T_out, src, tgt, corres, n_corres,
                                                                                max_d, inliers, err2, corres_inliers);
     IBL_LAUNCH_CHECK();

@@ -79,6 +79,7 @@ IBL_API int ibl_cosine_segmax(const float *det, int32_t nd, const float *mem, in
     IBL_CUDA(ibl_alloc(&detn, (size_t)nd * D, st));
     l2norm_rows_kernel<<<(nd + 3) / 4, 128, 0, st>>>(det, nd, D, detn);
     IBL_LAUNCH_CHECK();
+    IBL_PROF(IBL_PROF_COSINE, st, 4.0 * D * ((double)E + nd) + 4.0 * nd * m);
     cosine_segmax_kernel<<<m, 128, 0, st>>>(detn, nd, mem, D, seg, S, m);
     IBL_LAUNCH_CHECK();
     ibl_free(detn, st);
@@ -287,6 +288,7 @@ IBL_API int ibl_simvolume_topk(const float *S, int32_t nd, int32_t m, int32_t k,
     if (bx > cap) bx = cap;
     if (bx < 1) bx = 1;
     dim3 grid(bx, G.ncomb);
+    IBL_PROF(IBL_PROF_SIMVOL, st, 6.0 * (double)G.ncomb * m * G.n1 * G.n2);
     for (int level = 0; level <= 4; ++level) {
         int bins = level <= 1 ? 256 : m + 1;
         sv_pass_kernel<<<grid, 256, 0, st>>>(S, G, level, states, hist, bins, keys, states, k);

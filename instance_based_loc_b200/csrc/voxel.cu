@@ -123,6 +123,7 @@ IBL_API int64_t ibl_voxel_downsample(const double *pts, const double *cols, cons
     IBL_CUDA(ibl_alloc(&flag, (size_t)n, st)); IBL_CUDA(ibl_alloc(&head_pos, (size_t)n, st));
     IBL_CUDA(ibl_alloc(&d_nseg, 1, st));
     int nb = (int)((n + 255) / 256);
+    IBL_PROF(IBL_PROF_VOXEL, st, 72.0 * n);
     vox_key_kernel<<<nb, 256, 0, st>>>(pts, n, voxel, vr, key, idx, out_keys);
     IBL_LAUNCH_CHECK();
     size_t tb = 0, tb2 = 0;

@@ -306,3 +306,22 @@ def simvolume_topk(S, k):
     val = torch.empty((ncomb, k), dtype=torch.float32, device=S.device)
     check(lib().ibl_simvolume_topk(_p(S), nd, m, int(k), _p(flat), _p(val), _stream()), "simvolume_topk")
     return flat, val
+
+
+# ------------------------------------------------------------------------------- instrumentation
+def launch_count():
+    return int(lib().ibl_launch_count())
+
+
+def prof_enable(on=True):
+    lib().ibl_prof_enable(int(bool(on)))
+
+
+def prof_read():
+    """-> {tag: {"ms", "launches", "work"}} accumulated since the last read (device-synchronising)."""
+    L = lib()
+    n = L.ibl_prof_num_tags()
+    ms, la, wk = (c_double * n)(), (c_int64 * n)(), (c_double * n)()
+    check(L.ibl_prof_read(ms, la, wk), "prof_read")
+    return {L.ibl_prof_tag_name(i).decode(): {"ms": ms[i], "launches": int(la[i]), "work": wk[i]} for i in range(n)
+            if la[i] > 0}

@@ -229,7 +229,7 @@ class ObjectMemory():
             depth = depth_image / depth_factor
         clouds = get_mask_coloured_pointclouds_from_depth(depth, rgb_image, masks, self.camera_focal_lenth_x,
                                                           self.camera_focal_lenth_y, outlier_removal_config)
-        embs = embeddings.detach().cpu().numpy() if isinstance(embeddings, torch.Tensor) else np.array(embeddings)
+        embs = embeddings.detach() if isinstance(embeddings, torch.Tensor) else np.array(embeddings)
         phrases = phrases if phrases is not None else [f"object_{i}" for i in range(len(clouds))]
         return self._localise_core(phrases, embs, clouds, outlier_removal_config, fpfh_global_dist_factor,
                                    fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
@@ -247,7 +247,7 @@ class ObjectMemory():
             order = sorted(range(len(detected_pointclouds)), key=lambda i: detected_pointclouds[i].n(), reverse=True)
             order = order[:max_detected_object_num]
             detected_phrases = [detected_phrases[i] for i in order]
-            detected_embs = np.stack([detected_embs[i] for i in order])
+            detected_embs = detected_embs[order]
             detected_pointclouds = [detected_pointclouds[i] for i in order]
 
         for m in self.memory:

@@ -81,6 +81,14 @@ int64_t ibl_grid_occupied(const ibl_grid_t *g);
 /* Chebyshev ring-distance field (uint8 per cell, capped) used to skip empty space in nn queries */
 int ibl_grid_build_ringfield(ibl_grid_t *g, int max_ring, void *stream);
 
+/* Exact nearest-neighbour candidate field for "nearest target point within max_d" queries (replaces the KD-tree of
+ * GetRegistrationResultAndCorrespondences, Registration.cpp, for RANSAC validation / ICP / evaluate_registration):
+ * sparse voxel table (side `voxel`, 0 -> max_d/4) whose entries list every point that can be the answer for a query
+ * inside the voxel.  Once built, ibl_nn_score / ibl_ransac_score / ibl_icp use it whenever their max_d <= this
+ * max_d; results are identical to the ring search.  Syncs (two size read-backs). */
+int ibl_grid_build_nnfield(ibl_grid_t *g, double max_d, double voxel, void *stream);
+int64_t ibl_grid_nnfield_bytes(const ibl_grid_t *g);
+
 /* KDTreeFlann::SearchRadius count for every grid point against the grid (A.2):
  * count[i] = #{j : d2(i,j) < r*r}.  depth_utils.py:41,87, object_memory.py:994. */
 int ibl_radius_count(const ibl_grid_t *g, double radius, int32_t *count, void *stream);

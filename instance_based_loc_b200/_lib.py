@@ -51,6 +51,8 @@ _PROTOS = {
     "ibl_grid_cell": (c_double, [_V]),
     "ibl_grid_occupied": (c_int64, [_V]),
     "ibl_grid_build_ringfield": (c_int, [_V, c_int, _V]),
+    "ibl_grid_build_nnfield": (c_int, [_V, c_double, c_double, _V]),
+    "ibl_grid_nnfield_bytes": (c_int64, [_V]),
     "ibl_radius_count": (c_int, [_V, c_double, _V, _V]),
     "ibl_radius_outlier_mask": (c_int, [_V, c_double, c_int32, _V, _V]),
     "ibl_knn_hybrid": (c_int, [_V, _V, c_int64, c_double, c_int32, _V, _V, _V, _V]),

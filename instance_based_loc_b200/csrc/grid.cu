@@ -138,6 +138,7 @@ IBL_API void ibl_grid_destroy(ibl_grid_t *g) {
     // stream-ordered frees on the creating stream: queries already enqueued there finish first.  (cudaFree on a
     // cudaMallocAsync allocation does NOT synchronise, so it must not be used while kernels may be in flight.)
     cudaStream_t st = g->stream;
+    ibl_grid_free_field(g);
     ibl_free(g->cell_start, st);
     ibl_free(g->sorted, st);
     ibl_free(g->order, st);

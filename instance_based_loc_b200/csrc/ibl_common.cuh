@@ -58,8 +58,22 @@ static inline cudaStream_t ibl_stream(void *s) { return reinterpret_cast<cudaStr
 #define IBL_SMS 148
 
 // stream-ordered scratch allocation (cudaMallocAsync pool: no device sync on free)
+// The default cudaMallocAsync pool releases unused memory back to the driver at every synchronisation (release
+// threshold 0), which makes the next allocation a cuMemMap.  Keep the memory in the pool instead.
+static inline void ibl_pool_init() {
+    static thread_local int done_dev = -1;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev == done_dev) return;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        unsigned long long thr = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    done_dev = dev;
+}
 template <class T>
 static inline cudaError_t ibl_alloc(T **p, size_t count, cudaStream_t st) {
+    ibl_pool_init();
     if (count == 0) count = 1;
     return cudaMallocAsync(reinterpret_cast<void **>(p), count * sizeof(T), st);
 }
@@ -68,6 +82,20 @@ static inline void ibl_free(void *p, cudaStream_t st) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Exact nearest-neighbour candidate field (nnfield.cu): a sparse two-level voxel table over the target, dilated by
+// max_d.  Voxel v (side c, centre c_v, half diagonal h) lists every target point p with
+//     |p - c_v| <= min(D(v) + 2h, max_d + h),   D(v) = min_p |p - c_v|,
+// which is a superset of the possible answers of "nearest neighbour within max_d" for every query inside v
+// (NN distance <= D + h, so the NN lies within D + 2h of the centre).  A query is one table lookup + one short,
+// convergent loop over the list: no ring walk, identical result (lowest original index wins exact ties).
+struct NNFieldView {
+    double ox, oy, oz, inv_c, max_d;
+    int nvx, nvy, nvz, nbx, nby, nbz;
+    const int *block_ptr;        // [nbx*nby*nbz] -> active block id or -1   (blocks are 8x8x8 voxels)
+    const uint2 *entries;        // [nactive*512] (start, count) into cand
+    const int *cand;             // positions into grid.sorted
+};
+
 struct ibl_grid {
     int64_t n;            // points
     double ox, oy, oz;    // origin (min corner)
@@ -82,6 +110,11 @@ struct ibl_grid {
     uint8_t *ring;        // optional Chebyshev ring-distance field [ncells]
     int ring_cap;
     cudaStream_t stream;  // stream the grid was built on (frees are ordered on it)
+    // optional candidate field
+    int has_field;
+    NNFieldView field;
+    int *f_block_ptr; uint2 *f_entries; int *f_cand;
+    int64_t f_nactive, f_ncand;
 };
 
 // device view passed by value to kernels
@@ -92,13 +125,18 @@ struct GridView {
     const double4 *sorted;
     const uint8_t *ring;
     int ring_cap;
+    int has_field;
+    NNFieldView f;
 };
+
+void ibl_grid_free_field(ibl_grid *g);
 
 static inline GridView ibl_view(const ibl_grid *g) {
     GridView v;
     v.ox = g->ox; v.oy = g->oy; v.oz = g->oz; v.cell = g->cell; v.inv_cell = g->inv_cell;
     v.nx = g->nx; v.ny = g->ny; v.nz = g->nz;
     v.cell_start = g->cell_start; v.sorted = g->sorted; v.ring = g->ring; v.ring_cap = g->ring_cap;
+    v.has_field = g->has_field; v.f = g->field;
     return v;
 }
 
@@ -126,8 +164,33 @@ __device__ __forceinline__ void ibl_xform(const double *T, double x, double y, d
 
 // Nearest neighbour of q within max_d (strict d2 < max_d2) by expanding Chebyshev rings.
 // Returns original index or -1; best_d2 out.  Single-thread version (one query per thread).
+__device__ __forceinline__ int ibl_nn1_field(const GridView &g, double qx, double qy, double qz, double max_d2,
+                                             double &best_d2) {
+    const NNFieldView &f = g.f;
+    double best = max_d2;
+    long long best_key = -1;
+    double fx = floor((qx - f.ox) * f.inv_c), fy = floor((qy - f.oy) * f.inv_c), fz = floor((qz - f.oz) * f.inv_c);
+    if (fx >= 0.0 && fy >= 0.0 && fz >= 0.0 && fx < (double)f.nvx && fy < (double)f.nvy && fz < (double)f.nvz) {
+        int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+        int blk = f.block_ptr[((size_t)(iz >> 3) * f.nby + (iy >> 3)) * f.nbx + (ix >> 3)];
+        if (blk >= 0) {
+            uint2 e = f.entries[(size_t)blk * 512 + (((iz & 7) << 6) | ((iy & 7) << 3) | (ix & 7))];
+            const int *c = f.cand + e.x;
+            for (unsigned k = 0; k < e.y; ++k) {
+                double4 t = g.sorted[c[k]];
+                double d2 = ibl_d2(t.x, t.y, t.z, qx, qy, qz);
+                long long oi = (long long)__double_as_longlong(t.w);
+                if (d2 < best || (d2 == best && best_key >= 0 && oi < best_key)) { best = d2; best_key = oi; }
+            }
+        }
+    }
+    best_d2 = best;
+    return (int)best_key;
+}
+
 __device__ __forceinline__ int ibl_nn1_thread(const GridView &g, double qx, double qy, double qz, double max_d,
                                               double max_d2, double &best_d2) {
+    if (g.has_field && max_d <= g.f.max_d) return ibl_nn1_field(g, qx, qy, qz, max_d2, best_d2);
     int cx = ibl_cell_coord(qx, g.ox, g.inv_cell, g.nx);
     int cy = ibl_cell_coord(qy, g.oy, g.inv_cell, g.ny);
     int cz = ibl_cell_coord(qz, g.oz, g.inv_cell, g.nz);

@@ -205,8 +205,13 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
     h_result->n_corres = n_corres;
     if (n_corres < 3 || max_d <= 0 || max_iteration <= 0 || n_src <= 0) { h_result->status = 1; return IBL_OK; }
     cudaStream_t st = ibl_stream(stream);
-    if (block <= 0) block = 1 << 16;
-    const int64_t SCORE_CHUNK = 1024;
+    if (block <= 0) block = 1 << 14;
+    // Blocks grow geometrically (x2 per round, capped): few host round trips for the common 1e5..1e6-draw case while
+    // the work wasted past the adaptive stop stays bounded by one score chunk (survivors are scored in id order).
+    const int64_t MAX_BLOCK = 1 << 20;
+    const int64_t first_block = block;
+    block = MAX_BLOCK;                     // buffers are sized for the largest block
+    const int64_t SCORE_CHUNK = 512;
     uint8_t *pass = nullptr; int64_t *ids = nullptr; int *dcount = nullptr;
     int32_t *inl = nullptr, *cinl = nullptr; double *err = nullptr, *Ts = nullptr;
     IBL_CUDA(ibl_alloc(&pass, (size_t)block, st));
@@ -229,8 +234,9 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
     int64_t est_k = max_iteration;
     double best_fit = 0.0, best_rmse = 0.0;
     int rc = IBL_OK;
-    for (int64_t h0 = 0; h0 < max_iteration && h0 < est_k; h0 += block) {
-        int64_t H = std::min(block, std::min(max_iteration, est_k) - h0);
+    int64_t cur_block = std::min(first_block, MAX_BLOCK);
+    for (int64_t h0 = 0; h0 < max_iteration && h0 < est_k;) {
+        int64_t H = std::min(cur_block, std::min(max_iteration, est_k) - h0);
         if ((rc = ibl_ransac_check(src, tgt, corres, n_corres, samples, seed, h0, H, edge_thr, max_d, use_checkers, pass,
                                    nullptr, stream)) < 0) break;
         cub::CountingInputIterator<int64_t> cit(h0);
@@ -270,6 +276,8 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
             }
         }
         if (rc < 0) break;
+        h0 += H;
+        cur_block = std::min(cur_block * 2, MAX_BLOCK);
     }
     h_result->drawn = std::min(max_iteration, std::max<int64_t>(est_k, 0));
     ibl_free(tmp, st); ibl_free(pass, st); ibl_free(ids, st); ibl_free(dcount, st);

@@ -115,13 +115,19 @@ def mean3(pts):
 class Grid:
     """Owns an ibl_grid_t; keeps the point tensor alive."""
 
-    def __init__(self, pts, cell, max_cells=0, ring=0):
+    def __init__(self, pts, cell, max_cells=0, ring=0, nnfield=0.0, nnfield_voxel=0.0):
         self.pts = pts
         self.h = ctypes.c_void_p()
         check(lib().ibl_grid_create(_p(pts), pts.shape[0], float(cell), int(max_cells), ctypes.byref(self.h), _stream()),
               "grid_create")
         if ring:
             check(lib().ibl_grid_build_ringfield(self.h, int(ring), _stream()), "ringfield")
+        if nnfield:
+            check(lib().ibl_grid_build_nnfield(self.h, float(nnfield), float(nnfield_voxel), _stream()), "nnfield")
+
+    @property
+    def nnfield_bytes(self):
+        return int(lib().ibl_grid_nnfield_bytes(self.h))
 
     @property
     def cell(self):

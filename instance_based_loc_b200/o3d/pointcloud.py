@@ -253,12 +253,13 @@ class PointCloud:
         raise NotImplementedError("cluster_dbscan is memory-build only (SURVEY.md section 8(f) row N2): out of scope")
 
     # ------------------------------------------------------------------ neighbour plumbing
-    def grid(self, cell, ring=0, max_cells=0):
-        """Cached cell-sorted grid for this cloud (invalidated on any mutation)."""
-        key = (float(cell), int(ring), int(max_cells))
+    def grid(self, cell, ring=0, max_cells=0, nnfield=0.0, nnfield_voxel=0.0):
+        """Cached cell-sorted grid (optionally with ring field / exact NN candidate field) for this cloud;
+        invalidated on any mutation."""
+        key = (float(cell), int(ring), int(max_cells), float(nnfield), float(nnfield_voxel))
         g = self._grids.get(key)
         if g is None:
-            g = K.Grid(self._p, cell, max_cells=max_cells, ring=ring)
+            g = K.Grid(self._p, cell, max_cells=max_cells, ring=ring, nnfield=nnfield, nnfield_voxel=nnfield_voxel)
             self._grids[key] = g
         return g
 

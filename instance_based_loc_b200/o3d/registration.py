@@ -109,13 +109,15 @@ class ICPConvergenceCriteria:
         self.max_iteration = int(max_iteration)
 
 
-def nn_cell(max_d):
-    """Grid cell for 1-NN-within-max_d queries: small cells + ring field (empty-space skipping)."""
-    return max(max_d / 4.0, 1e-4)
+def nn_voxel(max_d):
+    """Voxel side of the exact NN candidate field for 1-NN-within-max_d queries (ibl_grid_build_nnfield)."""
+    return max(max_d / 4.0, 0.01)
 
 
 def _nn_grid(target, max_d):
-    return target.grid(nn_cell(max_d), ring=8)
+    """Target-side search structure for GetRegistrationResultAndCorrespondences-style queries.  Cached on the
+    cloud, so a memory-side target pays for it once, not once per frame."""
+    return target.grid(max(max_d, 1e-4), nnfield=max_d, nnfield_voxel=nn_voxel(max_d))
 
 
 def match_features(source_feature, target_feature, mutual_filter=True, ransac_n=3):

@@ -154,11 +154,16 @@ def test_knn_tiny_clouds(K, oc):
         assert np.array_equal(h(idx), ridx) and np.array_equal(h(cnt), rcnt)
 
 
-@pytest.mark.parametrize("max_d,ring", [(0.075, 8), (0.02, 8), (0.075, 0)])
-def test_nn_score(K, oc, max_d, ring):
+@pytest.mark.parametrize("max_d,ring,field", [(0.075, 8, 0), (0.02, 8, 0), (0.075, 0, 0), (0.075, 0, 0.075), (0.02, 0, 0.02),
+                                                (0.02, 0, 0.075), (0.075, 0, 0.02)])
+def test_nn_score(K, oc, max_d, ring, field):
+    """ring search and the exact candidate field (field = the max_d the field was built for; a field built for a
+    SMALLER max_d than the query must be ignored, one built for a larger one must give the same answer)."""
     tgt, _ = surface_cloud(9000, 21)
     src = (random_rigid(2, 0.05, 0.03) @ np.c_[surface_cloud(4000, 22)[0], np.ones(4000)].T).T[:, :3]
-    g = K.Grid(dev(tgt), max(max_d / 4, 1e-4), ring=ring)
+    src = np.concatenate([src, src[:300] + 0.06, src[:50] + 3.0, tgt[:100]])     # far, very far and exact-hit queries
+    g = K.Grid(dev(tgt), max(max_d / 4, 1e-4), ring=ring, nnfield=field, nnfield_voxel=max(field / 4, 0.01))
+    assert (g.nnfield_bytes > 0) == (field > 0)
     T = random_rigid(3, 0.02, 0.01)
     n_in, err2, nn, d2 = K.nn_score(g, dev(src), max_d, T=T, want_idx=True, want_d2=True)
     pts = oc.transform_points(T, src)
@@ -228,6 +233,20 @@ def test_feature_nn_and_mutual(K, oc):
     assert np.array_equal(h(ji), oc.feature_nn(fb, fa))
     cor = h(K.mutual_corres(ij, ji, 3))
     assert np.array_equal(cor, oc.match_features(fa, fb, True, 3))
+    # survivor-list overflow of the fp32 filter: 12 identical targets -> exact slice rescan, lowest index wins
+    fc = fb.copy()
+    fc[:, 100:112] = fa[:, [5]]
+    fc[:, 40] = fa[:, 5] + 1e-9                              # closer than fp32 can resolve, but not the nearest
+    Cc = dev(np.ascontiguousarray(fc.T))
+    got = h(K.feature_nn(A, Cc))
+    assert np.array_equal(got, oc.feature_nn(fa, fc)) and got[5] == 100
+    # large, FPFH-like (non-negative, three blocks summing to ~200) problem that spans several target slices
+    big_a = rng.gamma(0.3, 1.0, (33, 5000)); big_b = rng.gamma(0.3, 1.0, (33, 9000))
+    for blk in range(3):
+        big_a[11 * blk:11 * blk + 11] *= 200.0 / big_a[11 * blk:11 * blk + 11].sum(0)
+        big_b[11 * blk:11 * blk + 11] *= 200.0 / big_b[11 * blk:11 * blk + 11].sum(0)
+    got = h(K.feature_nn(dev(np.ascontiguousarray(big_a.T)), dev(np.ascontiguousarray(big_b.T))))
+    assert np.array_equal(got, oc.feature_nn(big_a, big_b))
     # fallback: fewer than 9 mutual matches -> all of corres_ij
     ij2 = torch.arange(20, dtype=torch.int32, device="cuda") % 4
     ji2 = torch.zeros(4, dtype=torch.int32, device="cuda")
@@ -289,7 +308,7 @@ def test_ransac_score(K, oc, reg_case):
     s = rng.integers(0, len(c["cor"]), (4000, 3), dtype=np.int32)
     rok = oc.ransac_check(c["src"], c["tgt"], c["cor"], s, 0.9, 0.075)
     ids = np.nonzero(rok)[0][:40].astype(np.int64)
-    g = K.Grid(dev(c["tgt"]), 0.075 / 4, ring=8)
+    g = K.Grid(dev(c["tgt"]), 0.075, nnfield=0.075, nnfield_voxel=0.01875)
     inl, err, cin, Ts = K.ransac_score(g, dev(c["src"]), dev(c["tgt"]), dev(c["cor"], torch.int32),
                                        torch.from_numpy(ids).cuda(), 0.075, samples=dev(s, torch.int32))
     from scipy.spatial import cKDTree
@@ -305,12 +324,12 @@ def test_ransac_score(K, oc, reg_case):
         assert int(h(cin)[k]) == ci
 
 
-@pytest.mark.parametrize("early_exit,block", [(True, 4096), (True, 1000), (False, 4096)])
-def test_ransac_run(K, oc, reg_case, early_exit, block):
+@pytest.mark.parametrize("early_exit,block,field", [(True, 4096, True), (True, 1000, False), (False, 4096, True)])
+def test_ransac_run(K, oc, reg_case, early_exit, block, field):
     c = reg_case
     H = 30000
     s = np.random.default_rng(3).integers(0, len(c["cor"]), (H, 3), dtype=np.int32)
-    g = K.Grid(dev(c["tgt"]), 0.075 / 4, ring=8)
+    g = K.Grid(dev(c["tgt"]), 0.075, nnfield=0.075) if field else K.Grid(dev(c["tgt"]), 0.075 / 4, ring=8)
     r = K.ransac_run(g, dev(c["src"]), dev(c["tgt"]), dev(c["cor"], torch.int32), H, 0.99, 0.075, edge_thr=0.9,
                      samples=dev(s, torch.int32), early_exit=early_exit, block=block)
     ref, info = oc.ransac(c["src"], c["tgt"], c["cor"], s, 0.075, 0.9, 0.99, early_exit=early_exit)

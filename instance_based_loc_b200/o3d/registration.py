@@ -219,6 +219,15 @@ def color_gradient(target, max_correspondence_distance):
     return K.color_gradient(target._p, target._n, target._c, idx, cnt)
 
 
+def ensure_color_gradient(target, max_correspondence_distance):
+    """colour gradients of a target, cached on the cloud (they depend only on the target and max_d)."""
+    grad = getattr(target, "_color_grad", None)
+    if grad is None or grad[0] != max_correspondence_distance or grad[1].shape[0] != target.n():
+        grad = (max_correspondence_distance, color_gradient(target, max_correspondence_distance))
+        target._color_grad = grad
+    return grad
+
+
 def registration_colored_icp(source, target, max_correspondence_distance, init=None, estimation_method=None,
                              criteria=None):
     """A.8 (fpfh_register.py:132-135).  Raises like open3d when normals / colours are missing, which is what
@@ -232,10 +241,7 @@ def registration_colored_icp(source, target, max_correspondence_distance, init=N
         raise RuntimeError("ColoredICP requires colored pointclouds.")
     if max_correspondence_distance <= 0:
         raise RuntimeError("Invalid max_correspondence_distance.")
-    grad = getattr(target, "_color_grad", None)
-    if grad is None or grad[0] != max_correspondence_distance or grad[1].shape[0] != target.n():
-        grad = (max_correspondence_distance, color_gradient(target, max_correspondence_distance))
-        target._color_grad = grad
+    grad = ensure_color_gradient(target, max_correspondence_distance)
     g = _nn_grid(target, max_correspondence_distance)
     r = K.icp(g, source._p, target._p, max_correspondence_distance, init, mode=1, scol=source._c, tnrm=target._n,
               tcol=target._c, tgrad=grad[1], max_iteration=criteria.max_iteration,

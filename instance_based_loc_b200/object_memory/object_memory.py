@@ -15,12 +15,15 @@ from __future__ import annotations
 import copy
 import os
 import pickle
+import threading
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 import torch
 from scipy.spatial.transform import Rotation
 
 from .. import kernels as K
+from ..o3d import registration as _reg
 from ..o3d.pointcloud import PointCloud
 from ..utils.depth_utils import get_mask_coloured_pointclouds_from_depth
 from ..utils.fpfh_register import downsample_and_compute_fpfh, evaluate_transform, register_point_clouds
@@ -71,6 +74,9 @@ class ObjectMemory():
         self.floors = None
         self._cache_key = None
         self._cache = {}
+        self._lock = threading.RLock()
+        self._tls = threading.local()
+        self._pool, self._pool_workers = None, 0
         self.last_localise_info = {}
 
     def _log(self, statement):
@@ -145,49 +151,70 @@ class ObjectMemory():
         return phrases, embs, clouds
 
     # ------------------------------------------------------------------------------------------ caches
+    # Memory-side state is identical for every frame, so it is built once (under a lock: localise_batch runs frames
+    # on several host threads / CUDA streams) and only read afterwards.  An entry is published after the building
+    # stream has been synchronised, so readers on other streams never see half-built device data.
     def _memory_cache(self):
         key = (len(self.memory),) + tuple(id(m.pointcloud._p) for m in self.memory) + \
               tuple(len(m.embeddings) for m in self.memory)
-        if key != self._cache_key:
-            self._cache_key = key
-            self._cache = {"assn": {}}
-        return self._cache
+        with self._lock:
+            if key != self._cache_key:
+                self._cache_key = key
+                self._cache = {"assn": {}}
+            return self._cache
 
     def _embedding_bank(self):
-        c = self._memory_cache()
-        if "bank" not in c:
-            rows = [np.asarray(e, np.float32).reshape(1, -1) for m in self.memory for e in m.embeddings]
-            seg = np.cumsum([0] + [len(m.embeddings) for m in self.memory]).astype(np.int32)
-            c["bank"] = (K.to_dev(np.concatenate(rows), torch.float32), K.to_dev(seg, torch.int32))
-        return c["bank"]
+        with self._lock:
+            c = self._memory_cache()
+            if "bank" not in c:
+                rows = [np.asarray(e, np.float32).reshape(1, -1) for m in self.memory for e in m.embeddings]
+                seg = np.cumsum([0] + [len(m.embeddings) for m in self.memory]).astype(np.int32)
+                bank = (K.to_dev(np.concatenate(rows), torch.float32), K.to_dev(seg, torch.int32))
+                for m in self.memory:
+                    m._compute_means()                      # :913-914 (host-side means; nothing reads them here)
+                torch.cuda.current_stream().synchronize()
+                c["bank"] = bank
+            return c["bank"]
 
-    def _all_memory_pcd(self):
-        c = self._memory_cache()
-        if "all" not in c:
-            allp = PointCloud()
-            for obj in self.memory:
-                allp = allp + obj.pointcloud
-            c["all"] = allp
-        return c["all"]
+    def _all_memory_pcd(self, threshold=0.02):
+        with self._lock:
+            c = self._memory_cache()
+            if "all" not in c:
+                allp = PointCloud()
+                for obj in self.memory:
+                    allp = allp + obj.pointcloud
+                _reg._nn_grid(allp, threshold)              # evaluate_transform's search structure (:1104)
+                torch.cuda.current_stream().synchronize()
+                c["all"] = allp
+            return c["all"]
 
-    def _chosen_memory(self, m_indices, fpfh_voxel_size):
-        """centred union of the chosen memory clouds + its FPFH state (identical for every frame)."""
-        c = self._memory_cache()["assn"]
-        key = (tuple(int(i) for i in m_indices), float(fpfh_voxel_size))
-        if key not in c:
-            pcd = PointCloud()
-            for m_index in m_indices:
-                pcd = pcd + self.memory[m_index].pointcloud
-            mean = pcd.get_center()
-            pcd.translate(-mean)
-            try:
-                feats = downsample_and_compute_fpfh(pcd, fpfh_voxel_size)
-            except Exception:
-                feats = None
-            if len(c) > 512:
-                c.pop(next(iter(c)))
-            c[key] = (pcd, mean, feats)
-        return c[key]
+    def _chosen_memory(self, m_indices, fpfh_voxel_size, global_dist_factor, local_dist_factor):
+        """centred union of the chosen memory clouds with everything register_point_clouds derives from it:
+        normals + FPFH, the RANSAC / ICP search structures and the coloured-ICP gradients."""
+        key = (tuple(int(i) for i in m_indices), float(fpfh_voxel_size), float(global_dist_factor),
+               float(local_dist_factor))
+        with self._lock:
+            c = self._memory_cache()["assn"]
+            if key not in c:
+                pcd = PointCloud()
+                for m_index in m_indices:
+                    pcd = pcd + self.memory[m_index].pointcloud
+                mean = pcd.get_center()
+                pcd.translate(-mean)
+                try:
+                    feats = downsample_and_compute_fpfh(pcd, fpfh_voxel_size)
+                    tgt = feats[0]
+                    _reg._nn_grid(tgt, fpfh_voxel_size * global_dist_factor)
+                    _reg._nn_grid(tgt, fpfh_voxel_size * local_dist_factor)
+                    if tgt.has_colors():
+                        _reg.ensure_color_gradient(tgt, fpfh_voxel_size * local_dist_factor)
+                except Exception:
+                    feats = None
+                torch.cuda.current_stream().synchronize()
+                if len(c) > 512:
+                    c.pop(next(iter(c)))
+                c[key] = (pcd, mean, feats)
+            return c[key]
 
     # ------------------------------------------------------------------------------------------ localise
     def closest_similarities(self, detected_embs):
@@ -235,10 +262,46 @@ class ObjectMemory():
                                    fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
                                    max_detected_object_num)
 
+    def localise_batch(self, frames, workers=4, **kw):
+        """localise_arrays over a batch of frames (dicts with rgb / depth / masks / embs), ``workers`` frames in flight
+        at a time, each on its own host thread and CUDA stream: frames are independent, and the
+        path is a long chain of small kernels with host decisions in between, so overlapping frames is what keeps
+        the SMs busy.  Results are identical to calling localise_arrays frame by frame.
+        -> list of (pose, [assn, None], info)."""
+        frames = list(frames)
+        dev_index = torch.cuda.current_device()
+
+        def one(fr, stream=None):
+            pose, assn = self.localise_arrays(fr["rgb"], fr["depth"], fr["masks"], fr["embs"], **kw)
+            return pose, assn, self._tls.info
+
+        if workers <= 1 or len(frames) <= 1:
+            return [one(fr) for fr in frames]
+        ready = torch.cuda.Event()
+        ready.record()                                       # inputs produced on the caller's stream (e.g. H2D copies)
+
+        def run(fr):
+            torch.cuda.set_device(dev_index)
+            st = getattr(self._tls, "stream", None)
+            if st is None:
+                st = self._tls.stream = torch.cuda.Stream()
+            st.wait_event(ready)
+            with torch.cuda.stream(st):
+                out = one(fr)
+                st.synchronize()
+            return out
+
+        if self._pool is None or self._pool_workers != workers:
+            if self._pool is not None:
+                self._pool.shutdown(wait=True)
+            self._pool, self._pool_workers = ThreadPoolExecutor(max_workers=workers), workers
+        return list(self._pool.map(run, frames))
+
     def _localise_core(self, detected_phrases, detected_embs, detected_pointclouds, outlier_removal_config,
                        fpfh_global_dist_factor, fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
                        max_detected_object_num):
         info = self.last_localise_info = {"assignments": [], "registrations": []}
+        self._tls.info = info
         if detected_embs is None:
             return np.array([0., 0., 0., 0., 0., 0., 1.]), [[], []]           # :895-896
 
@@ -250,8 +313,6 @@ class ObjectMemory():
             detected_embs = detected_embs[order]
             detected_pointclouds = [detected_pointclouds[i] for i in order]
 
-        for m in self.memory:
-            m._compute_means()                                                 # :913-914
         if len(detected_embs) > len(self.memory):                              # :918-920
             detected_embs = detected_embs[:len(self.memory)]
 
@@ -282,7 +343,8 @@ class ObjectMemory():
             chosen_detected_pcd = PointCloud()
             for d_index, _ in assn:
                 chosen_detected_pcd = chosen_detected_pcd + detected_pointclouds[d_index]
-            chosen_memory_pcd, memory_mean, target_feats = self._chosen_memory([m for _, m in assn], fpfh_voxel_size)
+            chosen_memory_pcd, memory_mean, target_feats = self._chosen_memory(
+                [m for _, m in assn], fpfh_voxel_size, fpfh_global_dist_factor, fpfh_local_dist_factor)
             detected_mean = chosen_detected_pcd.get_center()
             chosen_detected_pcd.translate(-detected_mean)                      # :1030-1034
             transform, rmse, fitness = register_point_clouds(

@@ -51,3 +51,20 @@ def test_register_fallback_without_colours(cuda):
     rT, rrmse, rfit = ref_pipeline.register_point_clouds(q, None, p, None, 0.05, 1.5, 0.4)
     assert fit == rfit and abs(rmse - rrmse) < 1e-12
     np.testing.assert_allclose(T, rT, atol=1e-9)
+
+
+def test_localise_batch_equals_sequential(cuda):
+    """frames in flight on several host threads / CUDA streams give exactly the per-frame results."""
+    from instance_based_loc_b200 import selfcheck, synth
+    from instance_based_loc_b200.o3d import registration as reg
+    scene = synth.make_scene(m=8, seed=21, D=96, size=(0.35, 0.75))
+    om, _ = selfcheck.build_memory(scene, spacing=0.015, voxel=0.015, f=150.0)
+    frames = synth.make_frames(scene, 5, H=225, W=300, f=150.0, seed=21, min_pixels=200)
+    reg.ransac_seed = 21
+    kw = dict(fpfh_global_dist_factor=1.5, fpfh_local_dist_factor=1.5, fpfh_voxel_size=0.05, perform_semantic_icp=False)
+    seq = [om.localise_arrays(f["rgb"], f["depth"], f["masks"], f["embs"], **kw) for f in frames]
+    frs = [{"rgb": f["rgb"], "depth": f["depth"], "masks": f["masks"], "embs": f["embs"]} for f in frames]
+    for workers in (1, 3):
+        got = om.localise_batch(frs, workers=workers, **kw)
+        for (p0, a0), (p1, a1, _) in zip(seq, got):
+            assert np.array_equal(p0, p1) and a0 == a1

@@ -29,5 +29,12 @@ for rep in range(3):
         p = K.prof_read()
         top = sorted(((v["ms"], k, v["launches"]) for k, v in p.items()), reverse=True)[:6]
         print(rep, mode, f"{ms:.1f} ms", per, [(k, round(m, 1), n) for m, k, n in top], flush=True)
+for workers in (1, 2, 4, 8):
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    res = om.localise_batch(resident * (8 // B), workers=workers, **bench.LOCALISE_KW)
+    torch.cuda.synchronize(); ms = (time.perf_counter() - t0) * 1e3
+    print("batch of", len(res), "workers", workers, f"{ms:.1f} ms  -> {len(res) / ms * 1e3:.2f} frames/s", flush=True)
+ref = [om.localise_arrays(fr["rgb"], fr["depth"], fr["masks"], fr["embs"], **bench.LOCALISE_KW)[0] for fr in resident]
+print("batch == sequential:", all(np.array_equal(a, r[0]) for a, r in zip(ref, res)))
 info = om.last_localise_info
 print([ (r["assn"], round(r["fitness"],3), round(r["full_fitness"],3)) for r in info["registrations"]])

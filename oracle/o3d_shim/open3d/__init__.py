@@ -213,7 +213,8 @@ class ICPConvergenceCriteria:
         self.max_iteration = max_iteration
 
 
-# host-seeded sample source (A.7): tests set this to a callable (C, H) -> int32 [H,3]
+# host-seeded sample source (A.7): tests set this to a callable (C, H) -> int32 [H,3] array, or -> a callable
+# (h0, h1) -> int32 [h1-h0,3] block of the stream (oracle/sampler.py)
 ransac_sampler = lambda C, H: _np.random.default_rng(0).integers(0, C, (H, 3), dtype=_np.int32)  # noqa: E731
 last_ransac_info = {}
 
@@ -238,7 +239,7 @@ def registration_ransac_based_on_feature_matching(source, target, source_feature
     samples = ransac_sampler(len(cor), criteria.max_iteration)
     res, info = _oc.ransac(_np.asarray(source.points), _np.asarray(target.points), cor, samples,
                            max_correspondence_distance, edge_thr=edge, confidence=criteria.confidence,
-                           checkers=use_checkers)
+                           checkers=use_checkers, max_iteration=criteria.max_iteration)
     last_ransac_info.clear()
     last_ransac_info.update(info, n_corres=len(cor))
     return RegistrationResult(res)

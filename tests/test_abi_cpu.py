@@ -1,0 +1,62 @@
+"""CPU checks of the drop-in boundary: libibl.so loads, exports exactly what include/ibl.h declares, and the product
+path fails loudly (never falls back) when there is no GPU."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    src = open(os.path.join(ROOT, "include", "ibl.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(ibl_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    from instance_based_loc_b200 import _lib
+    if not os.path.exists(_lib.LIB_PATH):
+        _lib.build()
+    L = ctypes.CDLL(_lib.LIB_PATH)
+    syms = header_symbols()
+    assert len(syms) >= 35
+    for s in syms:
+        assert hasattr(L, s), f"{s} declared in include/ibl.h but not exported"
+    # and the ctypes prototype table covers the header
+    assert sorted(_lib.EXPORTS) == syms
+
+
+def test_version_and_error_string():
+    from instance_based_loc_b200 import _lib
+    L = _lib.lib()
+    assert L.ibl_version() >= 100
+    assert L.ibl_prof_num_tags() > 10 and L.ibl_launch_count() >= 0
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from instance_based_loc_b200 import kernels
+    from instance_based_loc_b200._lib import IblError
+    from instance_based_loc_b200.o3d.pointcloud import PointCloud
+    with pytest.raises(IblError):
+        kernels.to_dev(np.zeros((4, 3)))
+    with pytest.raises(IblError):
+        PointCloud(np.zeros((4, 3)))
+
+
+def test_product_never_imports_oracle():
+    """the oracle is test infrastructure: no product module may import it (selfcheck.py is the smoke-test checker)."""
+    pkg = os.path.join(ROOT, "instance_based_loc_b200")
+    bad = []
+    for d, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(".py") and f != "selfcheck.py":
+                txt = open(os.path.join(d, f)).read()
+                if re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M):
+                    bad.append(os.path.join(d, f))
+    assert not bad, bad

@@ -122,6 +122,11 @@ int ibl_fpfh(int64_t n, const int32_t *nbr_idx, const double *nbr_d2, const int3
 /* exact 33-d nearest neighbour of every column of fa among the columns of fb (A.5 KDTreeFlann on
  * features, SearchKNN k=1); lowest index wins ties.  fa double[na][33], fb double[nb][33]. */
 int ibl_feature_nn(const double *fa, int64_t na, const double *fb, int64_t nb, int32_t *nn, void *stream);
+/* Debug / test hook of the tensor-core filter inside ibl_feature_nn (csrc/match_tc.cu): the raw tcgen05 tf32 scores
+ * s'(a_i, b_j) = a32_i . b32_j - |b32_j|^2 / 2 as float32 [na][nb] (row-major).  swap_lbo_sbo must be 0 (1 is a
+ * descriptor-layout probe).  Not on the product path. */
+int ibl_feature_scores_debug(const double *fa, int64_t na, const double *fb, int64_t nb, float *scores,
+                             int swap_lbo_sbo, void *stream);
 /* mutual filter + fallback (A.5). ij int32[ns], ji int32[nt] -> corres int32[<=ns][2]; returns C. Syncs. */
 int64_t ibl_mutual_corres(const int32_t *ij, int64_t ns, const int32_t *ji, int64_t nt, int32_t ransac_n,
                           int32_t *corres, void *stream);

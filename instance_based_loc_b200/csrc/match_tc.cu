@@ -1,0 +1,404 @@
+// match_tc.cu -- tensor-core (tcgen05, kind::tf32) filter for the exact 33-d FPFH nearest-neighbour matcher
+// (Open3D RegistrationRANSACBasedOnFeatureMatching front half, utils/fpfh_register.py:110-112).
+//
+// The answer is still the f64 brute-force argmin with lowest-index ties (match.cu: feat_exact); the tensor cores only
+// decide which pairs need that exact evaluation.  For a query a and a target b the kernel computes the score
+//     s'(a,b) = a32.b32 - |b32|^2 / 2            (argmax_b s' == argmin_b |a32 - b32|^2)
+// as ONE tf32 GEMM of depth 104 using the 3xTF32 split  x32 = xh + xl  (xh = RN_tf32(x32), xl = RN_tf32(x32 - xh)):
+//     query row  : [ ah(33) | al(33) | ah(33) |  1    1    1   | 0 0 ]
+//     target row : [ bh(33) | bh(33) | bl(33) | -h0  -h1  -h2  | 0 0 ]      h = |b32|^2/2 = h0 + h1 + h2 (tf32 pieces)
+// so every product is exact in fp32 and only the al.bl term (<= 2^-22 |a||b|) is dropped.
+//   pass 1 : smax[q] = max_b s'(q,b)                                   (epilogue: one FMNMX per pair)
+//   pass 2 : every b with s'(q,b) >= smax[q] - E(q) is evaluated exactly (epilogue: one FSETP per pair; hits are rare)
+// E is a rigorous bound on |(|a32|^2 - 2 s') - d_exact| (see feat_tc_err), so the exact nearest neighbour, and every
+// exact tie with it, is inside the band.
+//
+// Kernel shape (one CTA per SM, 192 threads): warps 0-3 = epilogue (TMEM lane quarter = warp id), warp 4 = bulk-copy
+// producer, warp 5 = MMA issuer.  Operand tiles are pre-packed in global memory in the exact shared-memory image of the
+// no-swizzle K-major UMMA layout (8x16B core matrices, LBO = 128 B along K, SBO = 3328 B along rows), so one
+// cp.async.bulk brings in a whole 128 x 104 tile.  The query tile stays resident; target tiles stream through a
+// 3-stage ring; two 128-column TMEM accumulators overlap the MMA of tile t+1 with the epilogue of tile t.
+#include "ibl_common.cuh"
+
+#define TC_M 128                    // rows per tile (queries and targets)
+#define TC_K 104                    // GEMM depth: 3 x 33 + 3 + 2 pad   (13 MMAs of K = 8)
+#define TC_KCH (TC_K / 4)           // 16-byte chunks per row
+#define TC_LBO 128                  // bytes between K-adjacent core matrices
+#define TC_SBO (TC_KCH * 128)       // bytes between 8-row groups
+#define TC_TILE_BYTES (16 * TC_SBO) // 53,248
+#define TC_STAGES 3
+#define TC_THREADS 192
+#define TC_SMEM (TC_TILE_BYTES * (1 + TC_STAGES) + 256)
+
+struct FSplitOutTC { double d; int idx; int pad; };
+
+// ------------------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, 128 x 128 x 8, tf32 in / f32 accumulate
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 32 consecutive accumulator columns of this thread's TMEM lane
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, float *v) {
+    uint32_t *r = reinterpret_cast<uint32_t *>(v);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// no-swizzle K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout, version 1)
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((addr >> 4) & 0x3fff) | ((uint64_t)((lbo >> 4) & 0x3fff) << 16) |
+           ((uint64_t)((sbo >> 4) & 0x3fff) << 32) | (1ull << 46);
+}
+// cute::UMMA::InstrDescriptor: c = f32 (1 << 4), a = b = tf32 (2 << 7, 2 << 10), K-major both, N >> 3 at 17, M >> 4 at 24
+#define TC_IDESC ((1u << 4) | (2u << 7) | (2u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24))
+
+// ------------------------------------------------------------------------------------------------ operand packing
+__device__ __forceinline__ float tf32_rn(float x) {      // round to nearest (ties away) on the 13 dropped bits
+    uint32_t u = __float_as_uint(x);
+    u = (u + 0x1000u) & 0xffffe000u;
+    return __uint_as_float(u);
+}
+__device__ __forceinline__ size_t tc_elem_offset(int64_t row, int k) {   // float index inside the packed image
+    int64_t tile = row / TC_M;
+    int r = (int)(row % TC_M);
+    return (size_t)tile * (TC_TILE_BYTES / 4) + (size_t)(r >> 3) * (TC_SBO / 4) + (size_t)(k >> 2) * (TC_LBO / 4) + (r & 7) * 4 + (k & 3);
+}
+
+// role 0 = query rows, role 1 = target rows.  Rows in [n, padded) are written too: zeros for queries; for targets a
+// score of -1e30 so that a padding row is never a maximum and never inside a band.  One thread builds one row in
+// registers and stores it as 26 float4 (one per 16-byte K chunk).
+__global__ void __launch_bounds__(128) feat_tc_pack_kernel(const double *__restrict__ f, int64_t n, int64_t n_pad, int role,
+                                                           float *__restrict__ img, float *__restrict__ norm32,
+                                                           unsigned *__restrict__ maxnorm) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n_pad) return;
+    float row[TC_K];
+#pragma unroll
+    for (int k = 0; k < TC_K; ++k) row[k] = 0.f;
+    if (i < n) {
+        double s = 0.0;
+#pragma unroll
+        for (int j = 0; j < 33; ++j) {
+            float v = (float)f[i * 33 + j];
+            float vh = tf32_rn(v);
+            float vl = tf32_rn(v - vh);                   // v - vh is exact in fp32
+            s += (double)v * (double)v;
+            row[j] = vh;
+            row[33 + j] = role == 0 ? vl : vh;
+            row[66 + j] = role == 0 ? vh : vl;
+        }
+        float nf = __double2float_ru(s);
+        if (norm32) norm32[i] = nf;
+        atomicMax(maxnorm, __float_as_uint(nf));
+        if (role == 0) {
+            row[99] = 1.f; row[100] = 1.f; row[101] = 1.f;
+        } else {
+            double h = 0.5 * s;
+            float h0 = tf32_rn((float)h);
+            float h1 = tf32_rn((float)(h - (double)h0));
+            float h2 = tf32_rn((float)(h - (double)h0 - (double)h1));
+            row[99] = -h0; row[100] = -h1; row[101] = -h2;
+        }
+    } else if (role == 1) {
+        row[99] = tf32_rn(-1e30f);
+    }
+    float4 *dst = reinterpret_cast<float4 *>(img + tc_elem_offset(i, 0));
+#pragma unroll
+    for (int c = 0; c < TC_KCH; ++c) dst[c * (TC_LBO / 16)] = make_float4(row[4 * c], row[4 * c + 1], row[4 * c + 2], row[4 * c + 3]);
+}
+
+// ------------------------------------------------------------------------------------------------ error band
+// D32 := an32 - 2 s' (real arithmetic on the computed fp32 values) against the oracle's exact f64 distance d of the f64 rows:
+//   input rounding f64 -> f32          2.4e-7 (an + bn)
+//   an32 rounding                      0.6e-7  an
+//   3xTF32 representation + dropped al.bl   3 * 2^-22 |a_j b_j| per term  ->  7.2e-7 (an + bn)   in D
+//   accumulation: 102 terms, each addition modelled as TRUNCATED at fp32 (1 ulp of the running magnitude, the most
+//   pessimistic behaviour a tensor-core accumulator can have), running magnitude <= (an + 2 bn) / 2
+//                                      2 * 102 * 2^-23 * (an + 2 bn) / 2  =  1.22e-5 an + 2.43e-5 bn
+// => |D32 - d| <= 1.33e-5 an + 2.54e-5 bn.  TC_ERR_A / TC_ERR_B keep a 1.15x margin.  In score space the band is E (s' = -D/2,
+// and nearest-neighbour candidates are those with D32 <= min D32 + 2E).
+#define TC_ERR_A 1.53e-5f
+#define TC_ERR_B 2.92e-5f
+__device__ __forceinline__ float feat_tc_err(float an, float bmax) {
+    return __fadd_ru(__fadd_ru(__fmul_ru(TC_ERR_A, an), __fmul_ru(TC_ERR_B, bmax)), 5e-6f);
+}
+// monotone float <-> int key so that atomicMax(int) orders floats
+__device__ __forceinline__ int f2key(float f) { int b = __float_as_int(f); return b >= 0 ? b : b ^ 0x7fffffff; }
+__device__ __forceinline__ float key2f(int k) { return __int_as_float(k >= 0 ? k : k ^ 0x7fffffff); }
+
+__device__ __noinline__ double feat_tc_exact(const double *__restrict__ a, const double *__restrict__ b) {
+    double s = 0.0;      // the oracle's order: j ascending, one rounding per operation
+#pragma unroll 11
+    for (int j = 0; j < 33; ++j) { double d = __dsub_rn(a[j], b[j]); s = __dadd_rn(s, __dmul_rn(d, d)); }
+    return s;
+}
+
+// MODE 0: dump s' to dump[q][ld] (debug).  MODE 1: smax_key[q] = max over this CTA's target tiles.  MODE 2: band + exact.
+// grid = (query tiles, splits); split y owns target tiles [y * tiles_per_split, ...).
+template <int MODE>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restrict__ Bimg, int64_t nb, int n_btiles,
+               int tiles_per_split, int nsplit, const float *__restrict__ an32, const unsigned *__restrict__ bmax_bits,
+               int *__restrict__ smax_key, const double *__restrict__ fa, const double *__restrict__ fb,
+               FSplitOutTC *__restrict__ out, float *__restrict__ dump, int64_t dump_ld, int swap_lbo_sbo) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint32_t sA = smem_u32(smem);
+    const uint32_t sB0 = sA + TC_TILE_BYTES;
+    uint8_t *tail = smem + TC_TILE_BYTES * (1 + TC_STAGES);
+    const uint32_t bar0 = smem_u32(tail);                 // 8-byte barriers: a_full, full[3], empty[3], tfull[2], tempty[2]
+    const uint32_t BAR_A = bar0, BAR_FULL = bar0 + 8, BAR_EMPTY = bar0 + 8 + 8 * TC_STAGES,
+                   BAR_TFULL = bar0 + 8 + 16 * TC_STAGES, BAR_TEMPTY = BAR_TFULL + 16;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(tail + 128);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qtile = blockIdx.x, split = blockIdx.y;
+    const int t_begin = split * tiles_per_split;
+    const int t_end = min(n_btiles, t_begin + tiles_per_split);
+    const int ntiles = max(0, t_end - t_begin);
+
+    if (threadIdx.x == 0) {
+        mbar_init(BAR_A, 1);
+        for (int s = 0; s < TC_STAGES; ++s) { mbar_init(BAR_FULL + 8 * s, 1); mbar_init(BAR_EMPTY + 8 * s, 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(BAR_TFULL + 8 * s, 1); mbar_init(BAR_TEMPTY + 8 * s, 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 5) {                                      // TMEM: 256 columns = two 128-column accumulators
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32((const void *)tmem_slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 4) {
+        // ===== producer: query tile once, then the target tiles of this split through the ring =====
+        if (lane == 0 && ntiles > 0) {
+            mbar_expect_tx(BAR_A, TC_TILE_BYTES);
+            bulk_g2s(sA, Aimg + (size_t)qtile * (TC_TILE_BYTES / 4), TC_TILE_BYTES, BAR_A);
+            for (int it = 0; it < ntiles; ++it) {
+                int s = it % TC_STAGES;
+                mbar_wait(BAR_EMPTY + 8 * s, ((it / TC_STAGES) & 1) ^ 1);
+                mbar_expect_tx(BAR_FULL + 8 * s, TC_TILE_BYTES);
+                bulk_g2s(sB0 + s * TC_TILE_BYTES, Bimg + (size_t)(t_begin + it) * (TC_TILE_BYTES / 4), TC_TILE_BYTES, BAR_FULL + 8 * s);
+            }
+        }
+    } else if (warp == 5) {
+        // ===== MMA issuer: one thread, 13 tcgen05.mma (128 x 128 x 8) per target tile =====
+        if (lane == 0 && ntiles > 0) {
+            const uint32_t lbo = swap_lbo_sbo ? TC_SBO : TC_LBO, sbo = swap_lbo_sbo ? TC_LBO : TC_SBO;
+            mbar_wait(BAR_A, 0);
+            for (int it = 0; it < ntiles; ++it) {
+                int s = it % TC_STAGES, as = it & 1;
+                mbar_wait(BAR_TEMPTY + 8 * as, ((it >> 1) & 1) ^ 1);
+                mbar_wait(BAR_FULL + 8 * s, (it / TC_STAGES) & 1);
+                tc_fence_after();
+                const uint32_t sB = sB0 + s * TC_TILE_BYTES;
+#pragma unroll
+                for (int k = 0; k < TC_K / 8; ++k) {
+                    uint64_t ad = tc_smem_desc(sA + k * 2 * TC_LBO, lbo, sbo);
+                    uint64_t bd = tc_smem_desc(sB + k * 2 * TC_LBO, lbo, sbo);
+                    tc_mma_tf32(tmem_base + as * 128, ad, bd, TC_IDESC, k > 0);
+                }
+                tc_commit(BAR_EMPTY + 8 * s);             // smem stage free once these MMAs have read it
+                tc_commit(BAR_TFULL + 8 * as);            // accumulator ready for the epilogue
+            }
+        }
+    } else {
+        // ===== epilogue: thread = one query row; TMEM lane = threadIdx.x =====
+        const int64_t q = (int64_t)qtile * TC_M + threadIdx.x;
+        const bool live = q < na;
+        float m = -INFINITY, r = INFINITY;
+        double bestd = INFINITY;
+        int bi = -1;
+        if (MODE == 2 && live) {
+            float E = feat_tc_err(an32[q], __uint_as_float(*bmax_bits));
+            r = __fsub_rd(key2f(smax_key[q]), E);
+        }
+        const uint32_t lane_base = tmem_base + ((uint32_t)(warp * 32) << 16);
+        for (int it = 0; it < ntiles; ++it) {
+            int as = it & 1;
+            mbar_wait(BAR_TFULL + 8 * as, (it >> 1) & 1);
+            tc_fence_after();
+            const int64_t t0 = (int64_t)(t_begin + it) * TC_M;
+#pragma unroll 1
+            for (int ch = 0; ch < 4; ++ch) {
+                float v[32];
+                tc_ld32(lane_base + as * 128 + ch * 32, v);
+                if (MODE == 0) {
+                    if (live) {
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) { int64_t t = t0 + ch * 32 + c; if (t < nb) dump[q * dump_ld + t] = v[c]; }
+                    }
+                } else if (MODE == 1) {
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) m = fmaxf(m, v[c]);
+                } else {
+                    bool hit = false;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) hit |= (v[c] >= r);
+                    if (hit) {                            // rare: only targets inside the error band of the row maximum
+#pragma unroll                                     // static indices keep v[] in registers
+                        for (int c = 0; c < 32; ++c) {
+                            if (v[c] >= r) {
+                                int64_t t = t0 + ch * 32 + c;             // padding rows score -1e30 and never get here
+                                double de = feat_tc_exact(fa + q * 33, fb + t * 33);
+                                if (de < bestd) { bestd = de; bi = (int)t; }   // ascending scan: ties keep the lower index
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(BAR_TEMPTY + 8 * as);
+        }
+        if (live) {
+            if (MODE == 1 && ntiles > 0) atomicMax(smax_key + q, f2key(m));
+            if (MODE == 2) { FSplitOutTC o; o.d = bestd; o.idx = bi; o.pad = 0; out[q * nsplit + split] = o; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 5) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem_base) : "memory");
+    }
+}
+
+__global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int64_t na, int nsplit, int32_t *__restrict__ nn) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= na) return;
+    double bestd = INFINITY;
+    int bi = -1;
+    for (int s = 0; s < nsplit; ++s) {                   // splits are in ascending target order: ties keep the lower index
+        FSplitOutTC p = parts[i * nsplit + s];
+        if (p.idx >= 0 && p.d < bestd) { bestd = p.d; bi = p.idx; }
+    }
+    nn[i] = bi;
+}
+__global__ void feat_tc_fill_key_kernel(int *__restrict__ key, int64_t n) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) key[i] = f2key(-INFINITY);
+}
+
+struct TcPlan { int qtiles, btiles, nsplit, tiles_per_split; int64_t na_pad, nb_pad; };
+static TcPlan tc_plan(int64_t na, int64_t nb) {
+    TcPlan p;
+    p.qtiles = (int)((na + TC_M - 1) / TC_M);
+    p.btiles = (int)((nb + TC_M - 1) / TC_M);
+    p.na_pad = (int64_t)p.qtiles * TC_M;
+    p.nb_pad = (int64_t)p.btiles * TC_M;
+    int want = (IBL_SMS + p.qtiles - 1) / p.qtiles;      // one CTA per SM: fill the 148 SMs when there are few query tiles
+    if (want > p.btiles) want = p.btiles;
+    if (want < 1) want = 1;
+    p.tiles_per_split = (p.btiles + want - 1) / want;
+    p.nsplit = (p.btiles + p.tiles_per_split - 1) / p.tiles_per_split;
+    return p;
+}
+static int tc_configure() {
+    // the attribute is per function and per context; setting it again is cheap
+    IBL_CUDA(cudaFuncSetAttribute(feat_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
+    IBL_CUDA(cudaFuncSetAttribute(feat_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
+    IBL_CUDA(cudaFuncSetAttribute(feat_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
+    return IBL_OK;
+}
+
+// exact 33-d nearest neighbour of every row of fa among the rows of fb (tensor-core filter + exact f64 re-evaluation)
+int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb, int32_t *nn, cudaStream_t st) {
+    int rc = tc_configure();
+    if (rc < 0) return rc;
+    TcPlan p = tc_plan(na, nb);
+    float *A = nullptr, *B = nullptr, *an = nullptr;
+    unsigned *mx = nullptr;
+    int *key = nullptr;
+    FSplitOutTC *parts = nullptr;
+    IBL_CUDA(ibl_alloc(&A, (size_t)p.qtiles * (TC_TILE_BYTES / 4), st));
+    IBL_CUDA(ibl_alloc(&B, (size_t)p.btiles * (TC_TILE_BYTES / 4), st));
+    IBL_CUDA(ibl_alloc(&an, (size_t)p.na_pad, st));
+    IBL_CUDA(ibl_alloc(&mx, 2, st));
+    IBL_CUDA(ibl_alloc(&key, (size_t)p.na_pad, st));
+    IBL_CUDA(ibl_alloc(&parts, (size_t)na * p.nsplit, st));
+    IBL_CUDA(cudaMemsetAsync(mx, 0, 2 * sizeof(unsigned), st));
+    feat_tc_pack_kernel<<<(unsigned)(p.na_pad / 128), 128, 0, st>>>(fa, na, p.na_pad, 0, A, an, mx);
+    IBL_LAUNCH_CHECK();
+    feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, B, nullptr, mx + 1);
+    IBL_LAUNCH_CHECK();
+    feat_tc_fill_key_kernel<<<(unsigned)((p.na_pad + 255) / 256), 256, 0, st>>>(key, p.na_pad);
+    IBL_LAUNCH_CHECK();
+    dim3 grid(p.qtiles, p.nsplit);
+    feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, key,
+                                                        fa, fb, parts, nullptr, 0, 0);
+    IBL_LAUNCH_CHECK();
+    feat_tc_kernel<2><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, key,
+                                                        fa, fb, parts, nullptr, 0, 0);
+    IBL_LAUNCH_CHECK();
+    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, nn);
+    IBL_LAUNCH_CHECK();
+    ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st); ibl_free(key, st); ibl_free(parts, st);
+    return IBL_OK;
+}
+
+// Debug / test hook: the raw tensor-core scores s'(a_i, b_j) = a32.b32 - |b32|^2/2 as float32 [na][nb] (row-major).
+// swap_lbo_sbo = 1 exchanges the two stride fields of the shared-memory descriptors (layout probe; 0 is the product setting).
+IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double *fb, int64_t nb, float *scores,
+                                     int swap_lbo_sbo, void *stream) {
+    IBL_ARG(fa && fb && scores && na > 0 && nb > 0);
+    cudaStream_t st = ibl_stream(stream);
+    int rc = tc_configure();
+    if (rc < 0) return rc;
+    TcPlan p = tc_plan(na, nb);
+    float *A = nullptr, *B = nullptr, *an = nullptr;
+    unsigned *mx = nullptr;
+    IBL_CUDA(ibl_alloc(&A, (size_t)p.qtiles * (TC_TILE_BYTES / 4), st));
+    IBL_CUDA(ibl_alloc(&B, (size_t)p.btiles * (TC_TILE_BYTES / 4), st));
+    IBL_CUDA(ibl_alloc(&an, (size_t)p.na_pad, st));
+    IBL_CUDA(ibl_alloc(&mx, 2, st));
+    IBL_CUDA(cudaMemsetAsync(mx, 0, 2 * sizeof(unsigned), st));
+    feat_tc_pack_kernel<<<(unsigned)(p.na_pad / 128), 128, 0, st>>>(fa, na, p.na_pad, 0, A, an, mx);
+    IBL_LAUNCH_CHECK();
+    feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, B, nullptr, mx + 1);
+    IBL_LAUNCH_CHECK();
+    dim3 grid(p.qtiles, p.nsplit);
+    feat_tc_kernel<0><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, nullptr,
+                                                        fa, fb, nullptr, scores, nb, swap_lbo_sbo);
+    IBL_LAUNCH_CHECK();
+    ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st);
+    return IBL_OK;
+}

@@ -219,6 +219,14 @@ def feature_nn(fa, fb):
     return out
 
 
+def feature_scores_debug(fa, fb, swap_lbo_sbo=0):
+    """Test hook: raw tcgen05 scores a32.b32 - |b32|^2/2 of the matcher's filter, float32 [na, nb]."""
+    out = torch.empty((fa.shape[0], fb.shape[0]), dtype=torch.float32, device=fa.device)
+    check(lib().ibl_feature_scores_debug(_p(fa), fa.shape[0], _p(fb), fb.shape[0], _p(out), int(swap_lbo_sbo), _stream()),
+          "feature_scores_debug")
+    return out
+
+
 def mutual_corres(ij, ji, ransac_n=3):
     cor = torch.empty((ij.shape[0], 2), dtype=torch.int32, device=ij.device)
     c = check(lib().ibl_mutual_corres(_p(ij), ij.shape[0], _p(ji), ji.shape[0], int(ransac_n), _p(cor), _stream()),

@@ -254,6 +254,50 @@ def test_feature_nn_and_mutual(K, oc):
     assert cor2.shape == (20, 2) and np.array_equal(cor2[:, 1], h(ij2))
 
 
+def _fpfh_like(rng, n):
+    f = rng.gamma(0.4, 1.0, (n, 3, 11))
+    return np.ascontiguousarray((200.0 * f / f.sum(-1, keepdims=True)).reshape(n, 33))
+
+
+def test_feature_scores_tensor_core_band(K):
+    """The tcgen05 tf32 scores s' = a32.b32 - |b32|^2/2 (csrc/match_tc.cu) stay inside the error band the matcher assumes:
+    |(an - 2 s') - d_exact| <= 1.33e-5 an + 2.54e-5 bn  (TC_ERR_A / TC_ERR_B carry a further 1.15x margin)."""
+    rng = np.random.default_rng(41)
+    fa, fb = _fpfh_like(rng, 333), _fpfh_like(rng, 517)
+    fb[100] = fa[7]
+    S = h(K.feature_scores_debug(dev(fa), dev(fb))).astype(np.float64)
+    assert S.shape == (333, 517) and np.isfinite(S).all()
+    a32 = fa.astype(np.float32).astype(np.float64)
+    an, bn = (a32 * a32).sum(1), (fb.astype(np.float32).astype(np.float64) ** 2).sum(1)
+    d_exact = ((fa[:, None, :] - fb[None, :, :]) ** 2).sum(-1)
+    err = np.abs((an[:, None] - 2.0 * S) - d_exact)
+    assert (err <= 1.33e-5 * an[:, None] + 2.54e-5 * bn[None, :]).all()
+    assert err.max() / (an.max() + bn.max()) < 5e-6          # measured ~6e-7 on B200: the band is conservative
+
+
+@pytest.mark.parametrize("na,nb", [(1, 1), (127, 129), (128, 128), (129, 127), (3, 1000), (1000, 3)])
+def test_feature_nn_tile_edges(K, oc, na, nb):
+    """Query / target counts around the 128-row tile size of the tensor-core filter (padding rows must never win)."""
+    rng = np.random.default_rng(1000 * na + nb)
+    fa, fb = _fpfh_like(rng, na), _fpfh_like(rng, nb)
+    got = h(K.feature_nn(dev(fa), dev(fb)))
+    assert np.array_equal(got, oc.feature_nn(np.ascontiguousarray(fa.T), np.ascontiguousarray(fb.T)))
+
+
+def test_feature_nn_planar_degenerate(K, oc):
+    """FPFH of planar patches: hundreds of IDENTICAL target rows (all inside the band) -> lowest index, like the oracle."""
+    rng = np.random.default_rng(43)
+    fa, fb = _fpfh_like(rng, 400), _fpfh_like(rng, 900)
+    plane = _fpfh_like(rng, 1)[0]
+    fb[200:700] = plane
+    fb[650] = plane + 1e-7                                    # differs from its 499 neighbours far below fp32 resolution
+    fa[::4] = plane
+    fa[1::4] = plane * (1 + 1e-6)                             # exact nearest is row 650, with 499 rows inside the band
+    got = h(K.feature_nn(dev(fa), dev(fb)))
+    assert np.array_equal(got, oc.feature_nn(np.ascontiguousarray(fa.T), np.ascontiguousarray(fb.T)))
+    assert (got[::4] == 200).all()
+
+
 # ------------------------------------------------------------------------------------------- a9
 @pytest.fixture(scope="module")
 def reg_case():

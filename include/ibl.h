@@ -123,10 +123,13 @@ int ibl_fpfh(int64_t n, const int32_t *nbr_idx, const double *nbr_d2, const int3
  * features, SearchKNN k=1); lowest index wins ties.  fa double[na][33], fb double[nb][33]. */
 int ibl_feature_nn(const double *fa, int64_t na, const double *fb, int64_t nb, int32_t *nn, void *stream);
 /* Debug / test hook of the tensor-core filter inside ibl_feature_nn (csrc/match_tc.cu): the raw tcgen05 tf32 scores
- * s'(a_i, b_j) = a32_i . b32_j - |b32_j|^2 / 2 as float32 [na][nb] (row-major).  swap_lbo_sbo must be 0 (1 is a
+ * s'(a_i, b_j) = a32_i . b32_j - |b32_j|^2 / 2 as float32 [na][nb] (row-major), a32 / b32 being the rows minus the filter's
+ * centre, which is written to center_out (device double[33]) when not NULL.  swap_lbo_sbo must be 0 (1 is a
  * descriptor-layout probe).  Not on the product path. */
 int ibl_feature_scores_debug(const double *fa, int64_t na, const double *fb, int64_t nb, float *scores,
-                             int swap_lbo_sbo, void *stream);
+                             double *center_out, int swap_lbo_sbo, void *stream);
+/* Instrumentation of ibl_feature_nn: h_out2 = {band candidates, exact f64 evaluations} since the last reset.  Syncs. */
+int ibl_feature_nn_stats(int64_t *h_out2, int reset);
 /* mutual filter + fallback (A.5). ij int32[ns], ji int32[nt] -> corres int32[<=ns][2]; returns C. Syncs. */
 int64_t ibl_mutual_corres(const int32_t *ij, int64_t ns, const int32_t *ji, int64_t nt, int32_t ransac_n,
                           int32_t *corres, void *stream);

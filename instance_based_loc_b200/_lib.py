@@ -61,7 +61,8 @@ _PROTOS = {
     "ibl_spfh": (c_int, [_V, _V, c_int64, _V, _V, c_int32, _V, _V]),
     "ibl_fpfh": (c_int, [c_int64, _V, _V, _V, c_int32, _V, _V, _V]),
     "ibl_feature_nn": (c_int, [_V, c_int64, _V, c_int64, _V, _V]),
-    "ibl_feature_scores_debug": (c_int, [_V, c_int64, _V, c_int64, _V, c_int, _V]),
+    "ibl_feature_scores_debug": (c_int, [_V, c_int64, _V, c_int64, _V, _V, c_int, _V]),
+    "ibl_feature_nn_stats": (c_int, [POINTER(c_int64), c_int]),
     "ibl_mutual_corres": (c_int64, [_V, c_int64, _V, c_int64, c_int32, _V, _V]),
     "ibl_ransac_check": (c_int, [_V, _V, _V, c_int64, _V, c_uint64, c_int64, c_int64, c_double, c_double, c_int, _V,
                                  _V, _V]),

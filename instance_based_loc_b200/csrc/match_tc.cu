@@ -9,7 +9,8 @@
 //     target row : [ bh(33) | bh(33) | bl(33) | -h0  -h1  -h2  | 0 0 ]      h = |b32|^2/2 = h0 + h1 + h2 (tf32 pieces)
 // so every product is exact in fp32 and only the al.bl term (<= 2^-22 |a||b|) is dropped.
 //   pass 1 : smax[q] = max_b s'(q,b)                                   (epilogue: one FMNMX per pair)
-//   pass 2 : every b with s'(q,b) >= smax[q] - E(q) is evaluated exactly (epilogue: one FSETP per pair; hits are rare)
+//   pass 2 : every b with s'(q,b) >= smax[q] - E(q) is a candidate (epilogue: one FSETP per pair), remembered in a
+//            thread-private list; feat_tc_eval_kernel then evaluates the candidates exactly, one warp per query row
 // E is a rigorous bound on |(|a32|^2 - 2 s') - d_exact| (see feat_tc_err), so the exact nearest neighbour, and every
 // exact tie with it, is inside the band.
 //
@@ -28,6 +29,7 @@
 #define TC_TILE_BYTES (16 * TC_SBO) // 53,248
 #define TC_STAGES 3
 #define TC_THREADS 192
+#define TC_LCAP 256                 // band candidates remembered per (query, split) row in global memory; the excess is evaluated on the spot
 #define TC_SMEM (TC_TILE_BYTES * (1 + TC_STAGES) + 256)
 
 struct FSplitOutTC { double d; int idx; int pad; };
@@ -102,12 +104,32 @@ __device__ __forceinline__ size_t tc_elem_offset(int64_t row, int k) {   // floa
     return (size_t)tile * (TC_TILE_BYTES / 4) + (size_t)(r >> 3) * (TC_SBO / 4) + (size_t)(k >> 2) * (TC_LBO / 4) + (r & 7) * 4 + (k & 3);
 }
 
+// Centre of the filter's coordinate system: the mean of up to 4096 evenly strided target rows (one CTA, fixed order).
+// ANY centre is valid -- |a - b| does not depend on it -- it only shrinks |a|^2 + |b|^2, which scales the error band;
+// FPFH rows of a scene cluster around a few typical histograms, so the gain is large.
+#define TC_MU_GROUPS 31
+__global__ void __launch_bounds__(33 * TC_MU_GROUPS) feat_tc_center_kernel(const double *__restrict__ f, int64_t n, double *__restrict__ mu) {
+    __shared__ double part[TC_MU_GROUPS][33];
+    const int j = threadIdx.x % 33, g = threadIdx.x / 33;
+    const int64_t S = n < 4096 ? n : 4096;
+    const int64_t stride = n / S;
+    double s = 0.0;
+    for (int64_t k = g; k < S; k += TC_MU_GROUPS) s += f[(k * stride) * 33 + j];
+    part[g][j] = s;
+    __syncthreads();
+    if (g == 0) {
+        double t = 0.0;
+        for (int k = 0; k < TC_MU_GROUPS; ++k) t += part[k][j];
+        mu[j] = t / (double)S;
+    }
+}
+
 // role 0 = query rows, role 1 = target rows.  Rows in [n, padded) are written too: zeros for queries; for targets a
 // score of -1e30 so that a padding row is never a maximum and never inside a band.  One thread builds one row in
 // registers and stores it as 26 float4 (one per 16-byte K chunk).
 __global__ void __launch_bounds__(128) feat_tc_pack_kernel(const double *__restrict__ f, int64_t n, int64_t n_pad, int role,
-                                                           float *__restrict__ img, float *__restrict__ norm32,
-                                                           unsigned *__restrict__ maxnorm) {
+                                                           const double *__restrict__ mu, float *__restrict__ img,
+                                                           float *__restrict__ norm32, unsigned *__restrict__ maxnorm) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n_pad) return;
     float row[TC_K];
@@ -117,7 +139,7 @@ __global__ void __launch_bounds__(128) feat_tc_pack_kernel(const double *__restr
         double s = 0.0;
 #pragma unroll
         for (int j = 0; j < 33; ++j) {
-            float v = (float)f[i * 33 + j];
+            float v = (float)(f[i * 33 + j] - mu[j]);     // centred: distances unchanged, norms (and so the band) shrink
             float vh = tf32_rn(v);
             float vl = tf32_rn(v - vh);                   // v - vh is exact in fp32
             s += (double)v * (double)v;
@@ -171,6 +193,18 @@ __device__ __noinline__ double feat_tc_exact(const double *__restrict__ a, const
     return s;
 }
 
+__device__ unsigned long long g_tc_stats[2];   // band candidates, exact f64 evaluations (instrumentation; see ibl_feature_nn_stats)
+
+// A band candidate of this thread's query: remembered in the row's private list (thread-private, so no atomics and a
+// deterministic layout) for feat_tc_eval_kernel, or, when the list is full, evaluated on the spot.
+__device__ __noinline__ void tc_push(uint32_t *__restrict__ list, int &cnt, int &n_eval, int t, const double *__restrict__ fa_q,
+                                     const double *__restrict__ fb, double &bestd, int &bi) {
+    if (cnt < TC_LCAP) { list[cnt] = (uint32_t)t; ++cnt; return; }
+    double de = feat_tc_exact(fa_q, fb + (size_t)t * 33);
+    if (de < bestd || (de == bestd && t < bi)) { bestd = de; bi = t; }
+    ++cnt; ++n_eval;
+}
+
 // MODE 0: dump s' to dump[q][ld] (debug).  MODE 1: smax_key[q] = max over this CTA's target tiles.  MODE 2: band + exact.
 // grid = (query tiles, splits); split y owns target tiles [y * tiles_per_split, ...).
 template <int MODE>
@@ -178,7 +212,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restrict__ Bimg, int64_t nb, int n_btiles,
                int tiles_per_split, int nsplit, const float *__restrict__ an32, const unsigned *__restrict__ bmax_bits,
                int *__restrict__ smax_key, const double *__restrict__ fa, const double *__restrict__ fb,
-               FSplitOutTC *__restrict__ out, float *__restrict__ dump, int64_t dump_ld, int swap_lbo_sbo) {
+               FSplitOutTC *__restrict__ out, uint32_t *__restrict__ glist, float *__restrict__ dump, int64_t dump_ld,
+               int swap_lbo_sbo) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sA = smem_u32(smem);
     const uint32_t sB0 = sA + TC_TILE_BYTES;
@@ -247,7 +282,8 @@ feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restri
         const bool live = q < na;
         float m = -INFINITY, r = INFINITY;
         double bestd = INFINITY;
-        int bi = -1;
+        int bi = -1, cnt = 0, n_eval = 0;
+        uint32_t *list = (MODE == 2 && live) ? glist + ((size_t)q * nsplit + split) * TC_LCAP : nullptr;
         if (MODE == 2 && live) {
             float E = feat_tc_err(an32[q], __uint_as_float(*bmax_bits));
             r = __fsub_rd(key2f(smax_key[q]), E);
@@ -276,13 +312,8 @@ feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restri
                     for (int c = 0; c < 32; ++c) hit |= (v[c] >= r);
                     if (hit) {                            // rare: only targets inside the error band of the row maximum
 #pragma unroll                                     // static indices keep v[] in registers
-                        for (int c = 0; c < 32; ++c) {
-                            if (v[c] >= r) {
-                                int64_t t = t0 + ch * 32 + c;             // padding rows score -1e30 and never get here
-                                double de = feat_tc_exact(fa + q * 33, fb + t * 33);
-                                if (de < bestd) { bestd = de; bi = (int)t; }   // ascending scan: ties keep the lower index
-                            }
-                        }
+                        for (int c = 0; c < 32; ++c)      // padding rows score -1e30 and never get here
+                            if (v[c] >= r) tc_push(list, cnt, n_eval, (int)(t0 + ch * 32 + c), fa + q * 33, fb, bestd, bi);
                     }
                 }
             }
@@ -291,7 +322,13 @@ feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restri
         }
         if (live) {
             if (MODE == 1 && ntiles > 0) atomicMax(smax_key + q, f2key(m));
-            if (MODE == 2) { FSplitOutTC o; o.d = bestd; o.idx = bi; o.pad = 0; out[q * nsplit + split] = o; }
+        }
+        if (MODE == 2 && live) {                          // pad = candidates of this row; (d, idx) = winner of the on-the-spot excess
+            FSplitOutTC o;
+            o.d = bestd; o.idx = bi; o.pad = cnt;
+            out[q * nsplit + split] = o;
+            if (cnt) atomicAdd(&g_tc_stats[0], (unsigned long long)cnt);
+            if (n_eval) atomicAdd(&g_tc_stats[1], (unsigned long long)n_eval);
         }
     }
     tc_fence_before();
@@ -302,15 +339,73 @@ feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restri
     }
 }
 
-__global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int64_t na, int nsplit, int32_t *__restrict__ nn) {
+// One warp per (query, split) row: the remembered band candidates are evaluated exactly, 32 at a time (the query row is a
+// broadcast load), and reduced with the oracle's order (distance, then lower index).  The band provably holds the exact
+// nearest neighbour, so a row with ONE candidate needs no f64 work here: d = -1 marks "not evaluated", and the merge
+// evaluates it only if another split of the same query also has candidates.
+__global__ void __launch_bounds__(256) feat_tc_eval_kernel(FSplitOutTC *__restrict__ parts, int64_t nrows, int nsplit,
+                                                           const uint32_t *__restrict__ glist, const double *__restrict__ fa,
+                                                           const double *__restrict__ fb) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    unsigned long long n_eval = 0;
+    for (int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < nrows; row += nwarps) {
+        FSplitOutTC p = parts[row];
+        const int cnt = p.pad;
+        if (cnt == 0) continue;
+        const uint32_t *list = glist + (size_t)row * TC_LCAP;
+        if (cnt == 1) {
+            if (lane == 0) { p.d = -1.0; p.idx = (int)list[0]; parts[row] = p; }
+            continue;
+        }
+        const double *a = fa + (row / nsplit) * 33;
+        double bestd = p.d;
+        int bi = p.idx;
+        const int nl = min(cnt, TC_LCAP);
+        for (int base = 0; base < nl; base += 32) {
+            if (base + lane < nl) {
+                int t = (int)list[base + lane];
+                double de = feat_tc_exact(a, fb + (size_t)t * 33);
+                if (de < bestd || (de == bestd && t < bi)) { bestd = de; bi = t; }
+                ++n_eval;
+            }
+        }
+        for (int o = 16; o; o >>= 1) {
+            double od = __shfl_xor_sync(0xffffffffu, bestd, o);
+            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (oi >= 0 && (bi < 0 || od < bestd || (od == bestd && oi < bi))) { bestd = od; bi = oi; }
+        }
+        if (lane == 0) { p.d = bestd; p.idx = bi; parts[row] = p; }
+    }
+    if (n_eval) atomicAdd(&g_tc_stats[1], n_eval);
+}
+
+__global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int64_t na, int nsplit, const double *__restrict__ fa,
+                                     const double *__restrict__ fb, int32_t *__restrict__ nn) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= na) return;
+    int nonempty = 0, only = -1;
+    for (int s = 0; s < nsplit; ++s) {
+        FSplitOutTC p = parts[i * nsplit + s];
+        if (p.idx >= 0) { ++nonempty; only = p.idx; }
+    }
+    if (nonempty == 1 || nonempty == 0) {
+        // one split with candidates: its winner (or its single, unevaluated candidate) is the exact nearest neighbour
+        // unless that split itself held several candidates, in which case it has already been resolved exactly
+        nn[i] = only;
+        return;
+    }
     double bestd = INFINITY;
     int bi = -1;
+    unsigned long long extra = 0;
     for (int s = 0; s < nsplit; ++s) {                   // splits are in ascending target order: ties keep the lower index
         FSplitOutTC p = parts[i * nsplit + s];
-        if (p.idx >= 0 && p.d < bestd) { bestd = p.d; bi = p.idx; }
+        if (p.idx < 0) continue;
+        double d = p.d;
+        if (d < 0.0) { d = feat_tc_exact(fa + i * 33, fb + (size_t)p.idx * 33); ++extra; }
+        if (d < bestd) { bestd = d; bi = p.idx; }
     }
+    if (extra) atomicAdd(&g_tc_stats[1], extra);
     nn[i] = bi;
 }
 __global__ void feat_tc_fill_key_kernel(int *__restrict__ key, int64_t n) {
@@ -355,30 +450,44 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     IBL_CUDA(ibl_alloc(&mx, 2, st));
     IBL_CUDA(ibl_alloc(&key, (size_t)p.na_pad, st));
     IBL_CUDA(ibl_alloc(&parts, (size_t)na * p.nsplit, st));
+    uint32_t *glist = nullptr;
+    IBL_CUDA(ibl_alloc(&glist, (size_t)na * p.nsplit * TC_LCAP, st));
+    double *mu = nullptr;
+    IBL_CUDA(ibl_alloc(&mu, 33, st));
     IBL_CUDA(cudaMemsetAsync(mx, 0, 2 * sizeof(unsigned), st));
-    feat_tc_pack_kernel<<<(unsigned)(p.na_pad / 128), 128, 0, st>>>(fa, na, p.na_pad, 0, A, an, mx);
+    feat_tc_center_kernel<<<1, 33 * TC_MU_GROUPS, 0, st>>>(fb, nb, mu);
     IBL_LAUNCH_CHECK();
-    feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, B, nullptr, mx + 1);
+    feat_tc_pack_kernel<<<(unsigned)(p.na_pad / 128), 128, 0, st>>>(fa, na, p.na_pad, 0, mu, A, an, mx);
+    IBL_LAUNCH_CHECK();
+    feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, B, nullptr, mx + 1);
     IBL_LAUNCH_CHECK();
     feat_tc_fill_key_kernel<<<(unsigned)((p.na_pad + 255) / 256), 256, 0, st>>>(key, p.na_pad);
     IBL_LAUNCH_CHECK();
     dim3 grid(p.qtiles, p.nsplit);
     feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, key,
-                                                        fa, fb, parts, nullptr, 0, 0);
+                                                        fa, fb, parts, glist, nullptr, 0, 0);
     IBL_LAUNCH_CHECK();
     feat_tc_kernel<2><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, key,
-                                                        fa, fb, parts, nullptr, 0, 0);
+                                                        fa, fb, parts, glist, nullptr, 0, 0);
     IBL_LAUNCH_CHECK();
-    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, nn);
+    {
+        int64_t nrows = na * p.nsplit;
+        int64_t blocks = (nrows + 7) / 8;                 // 8 warps per CTA, one row per warp
+        if (blocks > 8 * IBL_SMS) blocks = 8 * IBL_SMS;
+        feat_tc_eval_kernel<<<(unsigned)blocks, 256, 0, st>>>(parts, nrows, p.nsplit, glist, fa, fb);
+        IBL_LAUNCH_CHECK();
+    }
+    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, fa, fb, nn);
     IBL_LAUNCH_CHECK();
-    ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st); ibl_free(key, st); ibl_free(parts, st);
+    ibl_free(glist, st); ibl_free(mu, st); ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st); ibl_free(key, st); ibl_free(parts, st);
     return IBL_OK;
 }
 
-// Debug / test hook: the raw tensor-core scores s'(a_i, b_j) = a32.b32 - |b32|^2/2 as float32 [na][nb] (row-major).
+// Debug / test hook: the raw tensor-core scores s'(a_i, b_j) = a32.b32 - |b32|^2/2 as float32 [na][nb] (row-major), where
+// a32 / b32 are the rows after subtracting the filter's centre (written to center_out, device double[33], if not NULL).
 // swap_lbo_sbo = 1 exchanges the two stride fields of the shared-memory descriptors (layout probe; 0 is the product setting).
 IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double *fb, int64_t nb, float *scores,
-                                     int swap_lbo_sbo, void *stream) {
+                                     double *center_out, int swap_lbo_sbo, void *stream) {
     IBL_ARG(fa && fb && scores && na > 0 && nb > 0);
     cudaStream_t st = ibl_stream(stream);
     int rc = tc_configure();
@@ -391,14 +500,30 @@ IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double 
     IBL_CUDA(ibl_alloc(&an, (size_t)p.na_pad, st));
     IBL_CUDA(ibl_alloc(&mx, 2, st));
     IBL_CUDA(cudaMemsetAsync(mx, 0, 2 * sizeof(unsigned), st));
-    feat_tc_pack_kernel<<<(unsigned)(p.na_pad / 128), 128, 0, st>>>(fa, na, p.na_pad, 0, A, an, mx);
+    double *mu = center_out;
+    if (!mu) IBL_CUDA(ibl_alloc(&mu, 33, st));
+    feat_tc_center_kernel<<<1, 33 * TC_MU_GROUPS, 0, st>>>(fb, nb, mu);
     IBL_LAUNCH_CHECK();
-    feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, B, nullptr, mx + 1);
+    feat_tc_pack_kernel<<<(unsigned)(p.na_pad / 128), 128, 0, st>>>(fa, na, p.na_pad, 0, mu, A, an, mx);
+    IBL_LAUNCH_CHECK();
+    feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, B, nullptr, mx + 1);
     IBL_LAUNCH_CHECK();
     dim3 grid(p.qtiles, p.nsplit);
     feat_tc_kernel<0><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, nullptr,
-                                                        fa, fb, nullptr, scores, nb, swap_lbo_sbo);
+                                                        fa, fb, nullptr, nullptr, scores, nb, swap_lbo_sbo);
     IBL_LAUNCH_CHECK();
+    if (!center_out) ibl_free(mu, st);
     ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st);
+    return IBL_OK;
+}
+
+// Instrumentation: {band candidates, exact f64 evaluations} of ibl_feature_nn accumulated since the last reset.  Syncs.
+IBL_API int ibl_feature_nn_stats(int64_t *h_out2, int reset) {
+    IBL_ARG(h_out2 != nullptr);
+    unsigned long long v[2] = {0, 0};
+    IBL_CUDA(cudaDeviceSynchronize());
+    IBL_CUDA(cudaMemcpyFromSymbol(v, g_tc_stats, sizeof(v)));
+    h_out2[0] = (int64_t)v[0]; h_out2[1] = (int64_t)v[1];
+    if (reset) { unsigned long long z[2] = {0, 0}; IBL_CUDA(cudaMemcpyToSymbol(g_tc_stats, z, sizeof(z))); }
     return IBL_OK;
 }

@@ -89,7 +89,7 @@ __global__ void hyp_transform_kernel(const double *__restrict__ src, const doubl
     for (int e = 0; e < 16; ++e) T_out[16 * k + e] = T[e];
 }
 
-#define SCORE_TILE 2048
+#define SCORE_TILE 512       // source points per CTA: small tiles keep the 148 SMs full when few hypotheses survive the checkers
 #define SCORE_THREADS 256
 
 __global__ void __launch_bounds__(SCORE_THREADS) ransac_score_kernel(GridView g, const double *__restrict__ src,

@@ -220,11 +220,20 @@ def feature_nn(fa, fb):
 
 
 def feature_scores_debug(fa, fb, swap_lbo_sbo=0):
-    """Test hook: raw tcgen05 scores a32.b32 - |b32|^2/2 of the matcher's filter, float32 [na, nb]."""
+    """Test hook: raw tcgen05 scores a32.b32 - |b32|^2/2 of the matcher's filter (rows centred on the returned
+    centre), float32 [na, nb].  -> (scores, centre float64 [33])."""
     out = torch.empty((fa.shape[0], fb.shape[0]), dtype=torch.float32, device=fa.device)
-    check(lib().ibl_feature_scores_debug(_p(fa), fa.shape[0], _p(fb), fb.shape[0], _p(out), int(swap_lbo_sbo), _stream()),
-          "feature_scores_debug")
-    return out
+    mu = torch.empty(33, dtype=torch.float64, device=fa.device)
+    check(lib().ibl_feature_scores_debug(_p(fa), fa.shape[0], _p(fb), fb.shape[0], _p(out), _p(mu), int(swap_lbo_sbo),
+                                         _stream()), "feature_scores_debug")
+    return out, mu
+
+
+def feature_nn_stats(reset=True):
+    """(band candidates, exact f64 evaluations) of feature_nn since the last reset."""
+    v = (ctypes.c_int64 * 2)()
+    check(lib().ibl_feature_nn_stats(v, int(reset)), "feature_nn_stats")
+    return int(v[0]), int(v[1])
 
 
 def mutual_corres(ij, ji, ransac_n=3):

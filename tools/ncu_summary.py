@@ -1,0 +1,77 @@
+"""Summaries of ncu output for profiles/ (read in the build container; ncu -i needs no GPU).
+
+  python tools/ncu_summary.py launches gpurun_out/launches.csv "header text"      per-kernel time table of a launch list
+  python tools/ncu_summary.py full gpurun_out/full_X.ncu-rep [...]                key metrics of --set full captures
+"""
+from __future__ import annotations
+
+import collections
+import csv
+import io
+import re
+import subprocess
+import sys
+
+FULL_METRICS = [
+    "gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+    "dram__bytes_read.sum", "dram__bytes_write.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+    "gpu__compute_memory_throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
+    "smsp__thread_inst_executed_per_inst_executed.ratio", "smsp__inst_executed.sum",
+    "smsp__issue_active.avg.pct_of_peak_sustained_active",
+    "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+    "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct",
+]
+
+
+def launches(path, header=""):
+    with open(path) as f:
+        lines = [l for l in f if not l.startswith("==")]
+    r = csv.reader(lines)
+    hdr = next(r)
+    ki, vi, ui = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Metric Unit")
+    agg = collections.defaultdict(lambda: [0.0, 0])
+    tot, n = 0.0, 0
+    for row in r:
+        if len(row) <= vi:
+            continue
+        try:
+            v = float(row[vi].replace(",", ""))
+        except ValueError:
+            continue
+        u = row[ui]
+        us = v / 1e3 if u in ("ns", "nsecond") else (v if u in ("us", "usecond") else v * 1e3)
+        name = re.sub(r"\(.*", "", row[ki])[:80]
+        agg[name][0] += us
+        agg[name][1] += 1
+        tot += us
+        n += 1
+    if header:
+        print(header)
+    print(f"# total {tot / 1e3:.2f} ms of kernel time in {n} launches (cold-cache, serialised per-launch times: compare SHARES)")
+    for k, (t, c) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:32]:
+        print(f"{t / 1e3:10.3f} ms {100 * t / tot:6.2f}%  n={c:5d} avg={t / c:9.1f} us  {k}")
+
+
+def full(paths):
+    for p in paths:
+        out = subprocess.run(["ncu", "-i", p, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        rows = list(csv.reader(io.StringIO(out)))
+        if len(rows) < 3:
+            print(f"== {p}: no data")
+            continue
+        hdr, units = rows[0], rows[1]
+        kn = hdr.index("Kernel Name")
+        print(f"== {p}")
+        for r in rows[2:]:
+            print("  kernel:", re.sub(r"\(.*", "", r[kn])[:90])
+            for m in FULL_METRICS:
+                if m in hdr:
+                    i = hdr.index(m)
+                    print(f"    {m:78s} {r[i]:>16s} {units[i]}")
+
+
+if __name__ == "__main__":
+    if sys.argv[1] == "launches":
+        launches(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "")
+    else:
+        full(sys.argv[2:])

@@ -30,15 +30,54 @@ def fpfh_like(n, rng, dup=0):
 def stage_scores():
     rng = np.random.default_rng(1)
     fa, fb = fpfh_like(200, rng), fpfh_like(300, rng)
-    a32, b32 = fa.astype(np.float32).astype(np.float64), fb.astype(np.float32).astype(np.float64)
-    ref = a32 @ b32.T - 0.5 * (b32 * b32).sum(1)[None, :]
-    scale = (a32 * a32).sum(1)[:, None] + (b32 * b32).sum(1)[None, :]
     A, B = torch.from_numpy(fa).cuda(), torch.from_numpy(fb).cuda()
     for swap in (0, 1):
-        S = K.feature_scores_debug(A, B, swap).cpu().numpy().astype(np.float64)
+        S, mu = K.feature_scores_debug(A, B, swap)
+        S, mu = S.cpu().numpy().astype(np.float64), mu.cpu().numpy()
+        a32, b32 = (fa - mu).astype(np.float32).astype(np.float64), (fb - mu).astype(np.float32).astype(np.float64)
+        ref = a32 @ b32.T - 0.5 * (b32 * b32).sum(1)[None, :]
+        scale = (a32 * a32).sum(1)[:, None] + (b32 * b32).sum(1)[None, :]
         err = np.abs(S - ref) / scale
         print(f"scores swap={swap}: max rel err {err.max():.3e}  mean {err.mean():.3e}  finite={np.isfinite(S).all()}  "
-              f"S[0,:4]={S[0, :4]} ref[0,:4]={ref[0, :4]}", flush=True)
+              f"mean |a-mu|^2 / |a|^2 = {(a32 * a32).sum() / (fa * fa).sum():.3f}", flush=True)
+
+
+def real_fpfh():
+    """Real FPFH rows: the bench's synthetic scene, a detected-cloud-sized union vs a memory union."""
+    from instance_based_loc_b200 import o3d, synth
+    from instance_based_loc_b200.utils.fpfh_register import downsample_and_compute_fpfh
+    scene = synth.make_scene(m=40, seed=1002, D=768)
+    out = []
+    for objs, spacing in (((0, 1, 2), 0.012), ((0, 1, 2), 0.01)):
+        pts = np.concatenate([synth.memory_cloud(scene, j, spacing)[0] for j in objs])
+        cols = np.concatenate([synth.memory_cloud(scene, j, spacing)[1] for j in objs])
+        pc = o3d.geometry.PointCloud()
+        pc.points = o3d.utility.Vector3dVector(pts - pts.mean(0))
+        pc.colors = o3d.utility.Vector3dVector(cols)
+        _, f = downsample_and_compute_fpfh(pc, 0.05)
+        out.append(f._dev)
+    return out
+
+
+def stage_real():
+    A, B = real_fpfh()
+    na, nb = A.shape[0], B.shape[0]
+    K.feature_nn_stats(True)
+    got = K.feature_nn(A, B).cpu().numpy()
+    cand, ev = K.feature_nn_stats(True)
+    want, dmin = brute_nn(A.cpu().numpy(), B.cpu().numpy())
+    print(f"real na={na} nb={nb}: index match {int((got == want).sum())}/{na}; band candidates/query {cand / na:.2f}, "
+          f"exact evaluations/query {ev / na:.2f}", flush=True)
+    for _ in range(3):
+        K.feature_nn(A, B)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        K.feature_nn(A, B)
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"real time: {e0.elapsed_time(e1) / 10:.3f} ms per call", flush=True)
 
 
 def brute_nn(fa, fb, chunk=256):
@@ -90,4 +129,4 @@ def stage_time():
 
 
 if __name__ == "__main__":
-    {"scores": stage_scores, "nn": stage_nn, "time": stage_time}[sys.argv[1]]()
+    {"scores": stage_scores, "nn": stage_nn, "time": stage_time, "real": stage_real}[sys.argv[1]]()

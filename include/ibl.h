@@ -128,6 +128,9 @@ int ibl_feature_nn(const double *fa, int64_t na, const double *fb, int64_t nb, i
  * descriptor-layout probe).  Not on the product path. */
 int ibl_feature_scores_debug(const double *fa, int64_t na, const double *fb, int64_t nb, float *scores,
                              double *center_out, int swap_lbo_sbo, void *stream);
+/* Test hook: cap ibl_feature_nn's candidate pool at `chunks` chunks of 64 candidates (0 = default sizing) to force the
+ * pool-exhausted path (candidates evaluated on the spot).  Process-wide; results are identical either way. */
+int ibl_feature_nn_set_pool_chunks(int chunks);
 /* Instrumentation of ibl_feature_nn: h_out2 = {band candidates, exact f64 evaluations} since the last reset.  Syncs. */
 int ibl_feature_nn_stats(int64_t *h_out2, int reset);
 /* mutual filter + fallback (A.5). ij int32[ns], ji int32[nt] -> corres int32[<=ns][2]; returns C. Syncs. */

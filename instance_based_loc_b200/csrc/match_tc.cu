@@ -19,6 +19,8 @@
 // no-swizzle K-major UMMA layout (8x16B core matrices, LBO = 128 B along K, SBO = 3328 B along rows), so one
 // cp.async.bulk brings in a whole 128 x 104 tile.  The query tile stays resident; target tiles stream through a
 // 3-stage ring; two 128-column TMEM accumulators overlap the MMA of tile t+1 with the epilogue of tile t.
+#include <algorithm>
+
 #include "ibl_common.cuh"
 
 #define TC_M 128                    // rows per tile (queries and targets)
@@ -29,10 +31,13 @@
 #define TC_TILE_BYTES (16 * TC_SBO) // 53,248
 #define TC_STAGES 3
 #define TC_THREADS 192
-#define TC_LCAP 256                 // band candidates remembered per (query, split) row in global memory; the excess is evaluated on the spot
+#define TC_CHUNK 64                 // band candidates per pool chunk (rows chain as many chunks as they need)
 #define TC_SMEM (TC_TILE_BYTES * (1 + TC_STAGES) + 256)
 
-struct FSplitOutTC { double d; int idx; int pad; };
+// per (query, split) row: winner of the pool-exhausted fallback (d, idx), number of band candidates, first pool chunk
+struct FSplitOutTC { double d; int idx; int cnt; int first; int pad; };
+// candidate pool: chunk c holds entries[c * TC_CHUNK ..), belongs to row[c], has n[c] entries and continues in next[c]
+struct TcPool { uint32_t *entries; int *row, *n, *next; int *counter; int cap; };
 
 // ------------------------------------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -195,14 +200,42 @@ __device__ __noinline__ double feat_tc_exact(const double *__restrict__ a, const
 
 __device__ unsigned long long g_tc_stats[2];   // band candidates, exact f64 evaluations (instrumentation; see ibl_feature_nn_stats)
 
-// A band candidate of this thread's query: remembered in the row's private list (thread-private, so no atomics and a
-// deterministic layout) for feat_tc_eval_kernel, or, when the list is full, evaluated on the spot.
-__device__ __noinline__ void tc_push(uint32_t *__restrict__ list, int &cnt, int &n_eval, int t, const double *__restrict__ fa_q,
-                                     const double *__restrict__ fb, double &bestd, int &bi) {
-    if (cnt < TC_LCAP) { list[cnt] = (uint32_t)t; ++cnt; return; }
-    double de = feat_tc_exact(fa_q, fb + (size_t)t * 33);
-    if (de < bestd || (de == bestd && t < bi)) { bestd = de; bi = t; }
-    ++cnt; ++n_eval;
+// A band candidate of this thread's query goes into the row's chain of pool chunks (one atomicAdd per TC_CHUNK
+// candidates; the chain itself is thread-private) for feat_tc_eval_kernel.  Only if the pool is exhausted is it
+// evaluated on the spot.
+struct TcRowState { int cnt, cur, ccnt, first, n_eval, bi, exhausted; double bestd; };
+// slow path of tc_push: the row needs a (new) chunk, or the pool has run dry
+__device__ __noinline__ TcRowState tc_push_slow(TcRowState st, const TcPool pool, int row, int t,
+                                                const double *__restrict__ fa_q, const double *__restrict__ fb) {
+    if (!st.exhausted) {
+        int c = atomicAdd(pool.counter, 1);
+        if (c >= pool.cap) {
+            st.exhausted = 1;                             // a thread asks the pool at most once after it runs dry
+        } else {
+            if (st.cur >= 0) { pool.n[st.cur] = TC_CHUNK; pool.next[st.cur] = c; } else st.first = c;
+            pool.row[c] = row; pool.next[c] = -1;
+            st.cur = c; st.ccnt = 0;
+        }
+    }
+    if (st.exhausted) {                                   // exact evaluation right here (correct, just slow)
+        double de = feat_tc_exact(fa_q, fb + (size_t)t * 33);
+        if (de < st.bestd || (de == st.bestd && t < st.bi)) { st.bestd = de; st.bi = t; }
+        ++st.n_eval;
+        return st;
+    }
+    pool.entries[(size_t)st.cur * TC_CHUNK + st.ccnt] = (uint32_t)t;
+    ++st.ccnt;
+    return st;                                            // by value: the row state stays in registers on the fast path
+}
+__device__ __forceinline__ void tc_push(TcRowState &st, const TcPool &pool, int row, int t, const double *__restrict__ fa_q,
+                                        const double *__restrict__ fb) {
+    ++st.cnt;
+    if (st.cur >= 0 && st.ccnt < TC_CHUNK) {              // fast path: one store
+        pool.entries[(size_t)st.cur * TC_CHUNK + st.ccnt] = (uint32_t)t;
+        ++st.ccnt;
+    } else {
+        st = tc_push_slow(st, pool, row, t, fa_q, fb);
+    }
 }
 
 // MODE 0: dump s' to dump[q][ld] (debug).  MODE 1: smax_key[q] = max over this CTA's target tiles.  MODE 2: band + exact.
@@ -212,8 +245,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restrict__ Bimg, int64_t nb, int n_btiles,
                int tiles_per_split, int nsplit, const float *__restrict__ an32, const unsigned *__restrict__ bmax_bits,
                int *__restrict__ smax_key, const double *__restrict__ fa, const double *__restrict__ fb,
-               FSplitOutTC *__restrict__ out, uint32_t *__restrict__ glist, float *__restrict__ dump, int64_t dump_ld,
-               int swap_lbo_sbo) {
+               FSplitOutTC *__restrict__ out, TcPool pool, float *__restrict__ dump, int64_t dump_ld, int swap_lbo_sbo) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sA = smem_u32(smem);
     const uint32_t sB0 = sA + TC_TILE_BYTES;
@@ -281,9 +313,9 @@ feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restri
         const int64_t q = (int64_t)qtile * TC_M + threadIdx.x;
         const bool live = q < na;
         float m = -INFINITY, r = INFINITY;
-        double bestd = INFINITY;
-        int bi = -1, cnt = 0, n_eval = 0;
-        uint32_t *list = (MODE == 2 && live) ? glist + ((size_t)q * nsplit + split) * TC_LCAP : nullptr;
+        TcRowState rs;
+        rs.cnt = 0; rs.cur = -1; rs.ccnt = 0; rs.first = -1; rs.n_eval = 0; rs.bi = -1; rs.exhausted = 0; rs.bestd = INFINITY;
+        const int row = (int)(q * nsplit + split);
         if (MODE == 2 && live) {
             float E = feat_tc_err(an32[q], __uint_as_float(*bmax_bits));
             r = __fsub_rd(key2f(smax_key[q]), E);
@@ -310,10 +342,18 @@ feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restri
                     bool hit = false;
 #pragma unroll
                     for (int c = 0; c < 32; ++c) hit |= (v[c] >= r);
-                    if (hit) {                            // rare: only targets inside the error band of the row maximum
-#pragma unroll                                     // static indices keep v[] in registers
-                        for (int c = 0; c < 32; ++c)      // padding rows score -1e30 and never get here
-                            if (v[c] >= r) tc_push(list, cnt, n_eval, (int)(t0 + ch * 32 + c), fa + q * 33, fb, bestd, bi);
+                    if (hit) {                            // only targets inside the error band of the row maximum
+                        // Hit mask with static register indices, then a short loop that the lanes of the warp run in lock
+                        // step (trip count = the largest number of hits any lane has in these 32 columns).
+                        unsigned mask = 0;
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) mask |= (v[c] >= r) ? (1u << c) : 0u;
+                        const int tb = (int)(t0 + ch * 32);           // padding rows score -1e30 and never get here
+                        while (mask) {
+                            int c = __ffs(mask) - 1;
+                            mask &= mask - 1;
+                            tc_push(rs, pool, row, tb + c, fa + q * 33, fb);
+                        }
                     }
                 }
             }
@@ -323,12 +363,13 @@ feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restri
         if (live) {
             if (MODE == 1 && ntiles > 0) atomicMax(smax_key + q, f2key(m));
         }
-        if (MODE == 2 && live) {                          // pad = candidates of this row; (d, idx) = winner of the on-the-spot excess
+        if (MODE == 2 && live) {
+            if (rs.cur >= 0) pool.n[rs.cur] = rs.ccnt;
             FSplitOutTC o;
-            o.d = bestd; o.idx = bi; o.pad = cnt;
-            out[q * nsplit + split] = o;
-            if (cnt) atomicAdd(&g_tc_stats[0], (unsigned long long)cnt);
-            if (n_eval) atomicAdd(&g_tc_stats[1], (unsigned long long)n_eval);
+            o.d = rs.bestd; o.idx = rs.bi; o.cnt = rs.cnt; o.first = rs.first; o.pad = 0;
+            out[row] = o;
+            if (rs.cnt) atomicAdd(&g_tc_stats[0], (unsigned long long)rs.cnt);
+            if (rs.n_eval) atomicAdd(&g_tc_stats[1], (unsigned long long)rs.n_eval);
         }
     }
     tc_fence_before();
@@ -339,34 +380,34 @@ feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restri
     }
 }
 
-// One warp per (query, split) row: the remembered band candidates are evaluated exactly, 32 at a time (the query row is a
-// broadcast load), and reduced with the oracle's order (distance, then lower index).  The band provably holds the exact
-// nearest neighbour, so a row with ONE candidate needs no f64 work here: d = -1 marks "not evaluated", and the merge
-// evaluates it only if another split of the same query also has candidates.
-__global__ void __launch_bounds__(256) feat_tc_eval_kernel(FSplitOutTC *__restrict__ parts, int64_t nrows, int nsplit,
-                                                           const uint32_t *__restrict__ glist, const double *__restrict__ fa,
+// One warp per pool chunk: its candidates are evaluated exactly, 32 at a time (the query row is a broadcast load), and
+// reduced with the oracle's order (distance, then lower index) into res[chunk].  Work is balanced by ENTRY count, however
+// skewed the candidates are over the queries (planar patches: thousands of near-identical rows inside one band).
+// The band provably holds the exact nearest neighbour, so the chunk of a row with ONE candidate needs no f64 work here:
+// d = -1 marks "not evaluated"; the merge evaluates it only if another split of the same query also has candidates.
+struct TcChunkRes { double d; int idx; int pad; };
+__global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__restrict__ parts, TcPool pool, int nsplit,
+                                                           TcChunkRes *__restrict__ res, const double *__restrict__ fa,
                                                            const double *__restrict__ fb) {
     const int lane = threadIdx.x & 31;
-    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int nwarps = gridDim.x * (blockDim.x >> 5);
+    const int nchunks = min(*pool.counter, pool.cap);
     unsigned long long n_eval = 0;
-    for (int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < nrows; row += nwarps) {
-        FSplitOutTC p = parts[row];
-        const int cnt = p.pad;
-        if (cnt == 0) continue;
-        const uint32_t *list = glist + (size_t)row * TC_LCAP;
-        if (cnt == 1) {
-            if (lane == 0) { p.d = -1.0; p.idx = (int)list[0]; parts[row] = p; }
+    for (int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < nchunks; c += nwarps) {
+        const int row = pool.row[c], n = pool.n[c];
+        const uint32_t *e = pool.entries + (size_t)c * TC_CHUNK;
+        if (parts[row].cnt == 1) {
+            if (lane == 0) { TcChunkRes r; r.d = -1.0; r.idx = (int)e[0]; r.pad = 0; res[c] = r; }
             continue;
         }
-        const double *a = fa + (row / nsplit) * 33;
-        double bestd = p.d;
-        int bi = p.idx;
-        const int nl = min(cnt, TC_LCAP);
-        for (int base = 0; base < nl; base += 32) {
-            if (base + lane < nl) {
-                int t = (int)list[base + lane];
+        const double *a = fa + (size_t)(row / nsplit) * 33;
+        double bestd = INFINITY;
+        int bi = -1;
+        for (int base = 0; base < n; base += 32) {
+            if (base + lane < n) {
+                int t = (int)e[base + lane];
                 double de = feat_tc_exact(a, fb + (size_t)t * 33);
-                if (de < bestd || (de == bestd && t < bi)) { bestd = de; bi = t; }
+                if (bi < 0 || de < bestd || (de == bestd && t < bi)) { bestd = de; bi = t; }
                 ++n_eval;
             }
         }
@@ -375,35 +416,41 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(FSplitOutTC *__restri
             int oi = __shfl_xor_sync(0xffffffffu, bi, o);
             if (oi >= 0 && (bi < 0 || od < bestd || (od == bestd && oi < bi))) { bestd = od; bi = oi; }
         }
-        if (lane == 0) { p.d = bestd; p.idx = bi; parts[row] = p; }
+        if (lane == 0) { TcChunkRes r; r.d = bestd; r.idx = bi; r.pad = 0; res[c] = r; }
     }
     if (n_eval) atomicAdd(&g_tc_stats[1], n_eval);
 }
 
-__global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int64_t na, int nsplit, const double *__restrict__ fa,
+// Per query: combine the splits.  Each split row contributes its chain of chunk results and, if the pool ran dry, the
+// winner of its on-the-spot evaluations.
+__global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int64_t na, int nsplit, TcPool pool,
+                                     const TcChunkRes *__restrict__ res, const double *__restrict__ fa,
                                      const double *__restrict__ fb, int32_t *__restrict__ nn) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= na) return;
-    int nonempty = 0, only = -1;
+    long long total = 0;
+    int only = -1;
     for (int s = 0; s < nsplit; ++s) {
-        FSplitOutTC p = parts[i * nsplit + s];
-        if (p.idx >= 0) { ++nonempty; only = p.idx; }
+        const FSplitOutTC p = parts[i * nsplit + s];
+        total += p.cnt;
+        if (p.cnt == 1) only = p.first >= 0 ? (int)pool.entries[(size_t)p.first * TC_CHUNK] : p.idx;
     }
-    if (nonempty == 1 || nonempty == 0) {
-        // one split with candidates: its winner (or its single, unevaluated candidate) is the exact nearest neighbour
-        // unless that split itself held several candidates, in which case it has already been resolved exactly
-        nn[i] = only;
-        return;
-    }
+    if (total == 0) { nn[i] = -1; return; }
+    if (total == 1) { nn[i] = only; return; }            // the single band candidate IS the exact nearest neighbour
     double bestd = INFINITY;
     int bi = -1;
     unsigned long long extra = 0;
-    for (int s = 0; s < nsplit; ++s) {                   // splits are in ascending target order: ties keep the lower index
-        FSplitOutTC p = parts[i * nsplit + s];
-        if (p.idx < 0) continue;
-        double d = p.d;
-        if (d < 0.0) { d = feat_tc_exact(fa + i * 33, fb + (size_t)p.idx * 33); ++extra; }
-        if (d < bestd) { bestd = d; bi = p.idx; }
+    for (int s = 0; s < nsplit; ++s) {
+        const FSplitOutTC p = parts[i * nsplit + s];
+        if (p.cnt == 0) continue;
+        if (p.idx >= 0 && (bi < 0 || p.d < bestd || (p.d == bestd && p.idx < bi))) { bestd = p.d; bi = p.idx; }
+        for (int c = p.first; c >= 0; c = pool.next[c]) {
+            TcChunkRes r = res[c];
+            if (r.idx < 0) continue;
+            double d = r.d;
+            if (d < 0.0) { d = feat_tc_exact(fa + i * 33, fb + (size_t)r.idx * 33); ++extra; }
+            if (bi < 0 || d < bestd || (d == bestd && r.idx < bi)) { bestd = d; bi = r.idx; }
+        }
     }
     if (extra) atomicAdd(&g_tc_stats[1], extra);
     nn[i] = bi;
@@ -435,6 +482,15 @@ static int tc_configure() {
     return IBL_OK;
 }
 
+static int g_tc_pool_cap_override = 0;
+// Test hook: cap the candidate pool at `chunks` chunks of 64 candidates (0 restores the default sizing), so a test can
+// force the pool-exhausted path, where candidates are evaluated on the spot inside pass 2.
+IBL_API int ibl_feature_nn_set_pool_chunks(int chunks) {
+    IBL_ARG(chunks >= 0);
+    g_tc_pool_cap_override = chunks;
+    return IBL_OK;
+}
+
 // exact 33-d nearest neighbour of every row of fa among the rows of fb (tensor-core filter + exact f64 re-evaluation)
 int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb, int32_t *nn, cudaStream_t st) {
     int rc = tc_configure();
@@ -450,8 +506,19 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     IBL_CUDA(ibl_alloc(&mx, 2, st));
     IBL_CUDA(ibl_alloc(&key, (size_t)p.na_pad, st));
     IBL_CUDA(ibl_alloc(&parts, (size_t)na * p.nsplit, st));
-    uint32_t *glist = nullptr;
-    IBL_CUDA(ibl_alloc(&glist, (size_t)na * p.nsplit * TC_LCAP, st));
+    // candidate pool: one chunk for every row that has a candidate at all + 256k chunks (16 M candidates) of headroom
+    TcPool pool;
+    const int64_t nrows = na * p.nsplit;
+    pool.cap = (int)std::min<int64_t>(nrows + (1 << 18), (int64_t)1 << 24);
+    if (g_tc_pool_cap_override > 0) pool.cap = g_tc_pool_cap_override;
+    int *pool_meta = nullptr;
+    TcChunkRes *res = nullptr;
+    IBL_CUDA(ibl_alloc(&pool.entries, (size_t)pool.cap * TC_CHUNK, st));
+    IBL_CUDA(ibl_alloc(&pool_meta, (size_t)pool.cap * 3 + 1, st));
+    IBL_CUDA(ibl_alloc(&res, (size_t)pool.cap, st));
+    pool.row = pool_meta; pool.n = pool_meta + pool.cap; pool.next = pool_meta + 2 * (size_t)pool.cap;
+    pool.counter = pool_meta + 3 * (size_t)pool.cap;
+    IBL_CUDA(cudaMemsetAsync(pool.counter, 0, sizeof(int), st));
     double *mu = nullptr;
     IBL_CUDA(ibl_alloc(&mu, 33, st));
     IBL_CUDA(cudaMemsetAsync(mx, 0, 2 * sizeof(unsigned), st));
@@ -465,21 +532,19 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     IBL_LAUNCH_CHECK();
     dim3 grid(p.qtiles, p.nsplit);
     feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, key,
-                                                        fa, fb, parts, glist, nullptr, 0, 0);
+                                                        fa, fb, parts, pool, nullptr, 0, 0);
     IBL_LAUNCH_CHECK();
     feat_tc_kernel<2><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, key,
-                                                        fa, fb, parts, glist, nullptr, 0, 0);
+                                                        fa, fb, parts, pool, nullptr, 0, 0);
     IBL_LAUNCH_CHECK();
     {
-        int64_t nrows = na * p.nsplit;
-        int64_t blocks = (nrows + 7) / 8;                 // 8 warps per CTA, one row per warp
-        if (blocks > 8 * IBL_SMS) blocks = 8 * IBL_SMS;
-        feat_tc_eval_kernel<<<(unsigned)blocks, 256, 0, st>>>(parts, nrows, p.nsplit, glist, fa, fb);
+        // the chunk count lives on the device (no host sync): a fixed grid strides over it
+        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb);
         IBL_LAUNCH_CHECK();
     }
-    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, fa, fb, nn);
+    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn);
     IBL_LAUNCH_CHECK();
-    ibl_free(glist, st); ibl_free(mu, st); ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st); ibl_free(key, st); ibl_free(parts, st);
+    ibl_free(pool.entries, st); ibl_free(pool_meta, st); ibl_free(res, st); ibl_free(mu, st); ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st); ibl_free(key, st); ibl_free(parts, st);
     return IBL_OK;
 }
 
@@ -510,7 +575,7 @@ IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double 
     IBL_LAUNCH_CHECK();
     dim3 grid(p.qtiles, p.nsplit);
     feat_tc_kernel<0><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, nullptr,
-                                                        fa, fb, nullptr, nullptr, scores, nb, swap_lbo_sbo);
+                                                        fa, fb, nullptr, TcPool{}, scores, nb, swap_lbo_sbo);
     IBL_LAUNCH_CHECK();
     if (!center_out) ibl_free(mu, st);
     ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st);

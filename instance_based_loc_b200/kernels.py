@@ -146,19 +146,30 @@ class Grid:
             pass
 
 
-def knn_cell_for(pts, k, radius):
-    """Pick a grid cell for a k-NN search from the cloud's surface density (two coarse counts)."""
+def surface_spacing(pts, probe_cell):
+    """Mean point spacing of a surface-like cloud from one coarse occupancy count: n points over ~occ * c0^2 of area.
+    Only used to size search grids (performance, never results)."""
     n = pts.shape[0]
     if n == 0:
-        return radius
-    g0 = Grid(pts, max(radius / 4.0, 1e-4))
+        return float(probe_cell)
+    g0 = Grid(pts, max(probe_cell, 1e-4))
     occ = max(1, g0.occupied)
     c0 = g0.cell
     del g0
-    # surface model: n points over ~occ * c0^2 area -> spacing; k points within ~sqrt(k/pi)*spacing
-    spacing = c0 * (occ / n) ** 0.5
+    return float(c0 * (occ / n) ** 0.5)
+
+
+def knn_cell_from_spacing(spacing, k, radius):
+    """Grid cell for a hybrid k-NN search: k points of a surface lie within ~sqrt(k/pi) * spacing."""
     rk = (k / np.pi) ** 0.5 * spacing
     return float(min(max(rk * 0.6, 1e-4), radius))
+
+
+def knn_cell_for(pts, k, radius):
+    """Pick a grid cell for a k-NN search from the cloud's surface density."""
+    if pts.shape[0] == 0:
+        return radius
+    return knn_cell_from_spacing(surface_spacing(pts, radius / 4.0), k, radius)
 
 
 def radius_count(grid, radius):
@@ -234,6 +245,11 @@ def feature_nn_stats(reset=True):
     v = (ctypes.c_int64 * 2)()
     check(lib().ibl_feature_nn_stats(v, int(reset)), "feature_nn_stats")
     return int(v[0]), int(v[1])
+
+
+def feature_nn_set_pool_chunks(chunks=0):
+    """Test hook: cap the matcher's candidate pool (0 = default) to force its pool-exhausted path."""
+    check(lib().ibl_feature_nn_set_pool_chunks(int(chunks)), "feature_nn_set_pool_chunks")
 
 
 def mutual_corres(ij, ji, ransac_n=3):

@@ -264,7 +264,16 @@ class PointCloud:
         return g
 
     def knn(self, radius, max_nn, want_d2=True):
-        cell = K.knn_cell_for(self._p, max_nn, radius if np.isfinite(radius) else 1e30)
+        r = radius if np.isfinite(radius) else 1e30
+        if self.n() == 0:
+            cell = r
+        else:
+            # the spacing estimate costs a probe grid: keep it with the grids (dropped on any mutation), so the
+            # normals / FPFH / colour-gradient searches of one cloud share it
+            sp = self._grids.get("spacing")
+            if sp is None:
+                sp = self._grids["spacing"] = K.surface_spacing(self._p, min(r / 4.0, 0.05))
+            cell = K.knn_cell_from_spacing(sp, max_nn, r)
         return K.knn_hybrid(self.grid(cell), radius, max_nn, want_d2=want_d2)
 
     # ------------------------------------------------------------------ copy / pickle

@@ -296,9 +296,20 @@ def test_feature_nn_planar_degenerate(K, oc):
     fb[650] = plane + 1e-7                                    # differs from its 499 neighbours far below fp32 resolution
     fa[::4] = plane
     fa[1::4] = plane * (1 + 1e-6)                             # exact nearest is row 650, with 499 rows inside the band
+    K.feature_nn_stats(True)
     got = h(K.feature_nn(dev(fa), dev(fb)))
     assert np.array_equal(got, oc.feature_nn(np.ascontiguousarray(fa.T), np.ascontiguousarray(fb.T)))
     assert (got[::4] == 200).all()
+    cand, _ = K.feature_nn_stats(True)
+    # the same problem with the candidate pool capped at 3 chunks: most band candidates take the on-the-spot path
+    K.feature_nn_set_pool_chunks(3)
+    try:
+        got2 = h(K.feature_nn(dev(fa), dev(fb)))
+        cand2, ev2 = K.feature_nn_stats(True)
+    finally:
+        K.feature_nn_set_pool_chunks(0)
+    assert np.array_equal(got2, got)
+    assert cand2 > 200 * 499 and ev2 >= cand2 - 3 * 64 - 400   # everything beyond 3 chunks (and the singles) evaluated exactly
 
 
 # ------------------------------------------------------------------------------------------- a9

@@ -43,6 +43,16 @@ def peaks():
     return 6650.0, 2250.0, "fallback (B200_PROFILING.md: ~6.65 TB/s copy, 2.25 PFLOP/s nominal dense bf16)"
 
 
+def ncu_traffic(tag):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of a kernel group, from the round's `ncu --set full`
+    capture (profiles/ncu_traffic.json: {tag: {"bytes_per_launch": .., "source": .., "launch": ..}}); None if absent."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(p):
+        return None, None
+    e = json.load(open(p)).get(tag)
+    return (e["bytes_per_launch"], f'{e["source"]} ({e["launch"]})') if e else (None, None)
+
+
 # kernels whose IBL_PROF work unit is flops (csrc/match.cu); every other tag counts algorithmic bytes (DESIGN.md section 4)
 TENSOR_KERNELS = {"feature_nn"}
 
@@ -229,8 +239,9 @@ def run_product(args):
     else:
         bound, unit, achieved, peak = "hbm", "GB/s", work_per_s / 1e9, hbm_peak
         note = "achieved = algorithmic bytes per launch (DESIGN.md section 4) / launch time"
+    traffic, traffic_src = ncu_traffic(tname)
     roofline = {"kernel": tname, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit,
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "avg_launch_ms": per_launch_ms, "launches": t["launches"], "share_of_step": t["ms"] / ms_prof, "note": note,
                 "timed_in": "a second pass of the same K steps in this run, with CUDA events around every kernel group "
                             "(the events cost time, so `value` comes from the first, un-instrumented pass)",

@@ -1,4 +1,4 @@
-// match_tc.cu -- tensor-core (tcgen05, kind::tf32) filter for the exact 33-d FPFH nearest-neighbour matcher
+// match_tc.cu -- tensor-core (tcgen05, kind::f16) filter for the exact 33-d FPFH nearest-neighbour matcher
 // (Open3D RegistrationRANSACBasedOnFeatureMatching front half, utils/fpfh_register.py:110-112).
 //
 // The answer is still the f64 brute-force argmin with lowest-index ties (match.cu: feat_exact); the tensor cores only
@@ -20,16 +20,20 @@
 // cp.async.bulk brings in a whole 128 x 104 tile.  The query tile stays resident; target tiles stream through a
 // 3-stage ring; two 128-column TMEM accumulators overlap the MMA of tile t+1 with the epilogue of tile t.
 #include <algorithm>
+#include <cmath>
+
+#include <cuda_fp16.h>
 
 #include "ibl_common.cuh"
 
 #define TC_M 128                    // rows per tile (queries and targets)
-#define TC_K 104                    // GEMM depth: 3 x 33 + 3 + 2 pad   (13 MMAs of K = 8)
-#define TC_KCH (TC_K / 4)           // 16-byte chunks per row
+#define TC_K 112                    // GEMM depth: 3 x 33 + 3 + 10 pad  (7 MMAs of K = 16, fp16 operands)
+#define TC_KCH (TC_K / 8)           // 16-byte chunks (8 halves) per row
 #define TC_LBO 128                  // bytes between K-adjacent core matrices
 #define TC_SBO (TC_KCH * 128)       // bytes between 8-row groups
-#define TC_TILE_BYTES (16 * TC_SBO) // 53,248
-#define TC_STAGES 3
+#define TC_TILE_BYTES (16 * TC_SBO) // 28,672
+#define TC_STAGES 4
+#define TC_RANGE 1024.0             // rows are scaled by a power of two so that |value| <= TC_RANGE (fp16 range / precision)
 #define TC_THREADS 192
 #define TC_CHUNK 64                 // band candidates per pool chunk (rows chain as many chunks as they need)
 #define TC_SMEM (TC_TILE_BYTES * (1 + TC_STAGES) + 256)
@@ -68,12 +72,12 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem]^T, 128 x 128 x 8, tf32 in / f32 accumulate
-__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+// D[tmem] (+)= A[smem] * B[smem]^T, 128 x 128 x 16, fp16 in / f32 accumulate
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 // 32 consecutive accumulator columns of this thread's TMEM lane
@@ -94,19 +98,14 @@ __device__ __forceinline__ uint64_t tc_smem_desc(uint32_t addr, uint32_t lbo, ui
     return (uint64_t)((addr >> 4) & 0x3fff) | ((uint64_t)((lbo >> 4) & 0x3fff) << 16) |
            ((uint64_t)((sbo >> 4) & 0x3fff) << 32) | (1ull << 46);
 }
-// cute::UMMA::InstrDescriptor: c = f32 (1 << 4), a = b = tf32 (2 << 7, 2 << 10), K-major both, N >> 3 at 17, M >> 4 at 24
-#define TC_IDESC ((1u << 4) | (2u << 7) | (2u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24))
+// cute::UMMA::InstrDescriptor: c = f32 (1 << 4), a = b = f16 (format 0 at bits 7 and 10), K-major both, N >> 3 at 17, M >> 4 at 24
+#define TC_IDESC ((1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24))
 
 // ------------------------------------------------------------------------------------------------ operand packing
-__device__ __forceinline__ float tf32_rn(float x) {      // round to nearest (ties away) on the 13 dropped bits
-    uint32_t u = __float_as_uint(x);
-    u = (u + 0x1000u) & 0xffffe000u;
-    return __uint_as_float(u);
-}
-__device__ __forceinline__ size_t tc_elem_offset(int64_t row, int k) {   // float index inside the packed image
+__device__ __forceinline__ size_t tc_row_offset(int64_t row) {   // byte offset of (row, k = 0) inside the packed image
     int64_t tile = row / TC_M;
     int r = (int)(row % TC_M);
-    return (size_t)tile * (TC_TILE_BYTES / 4) + (size_t)(r >> 3) * (TC_SBO / 4) + (size_t)(k >> 2) * (TC_LBO / 4) + (r & 7) * 4 + (k & 3);
+    return (size_t)tile * TC_TILE_BYTES + (size_t)(r >> 3) * TC_SBO + (size_t)(r & 7) * 16;
 }
 
 // Centre of the filter's coordinate system: the mean of up to 4096 evenly strided target rows (one CTA, fixed order).
@@ -129,63 +128,97 @@ __global__ void __launch_bounds__(33 * TC_MU_GROUPS) feat_tc_center_kernel(const
     }
 }
 
+// Largest |f - mu| over all rows of one feature set (atomicMax on the bits of a non-negative float, rounded up).  The pack
+// kernel turns it into a power-of-two scale that brings every value into [-TC_RANGE, TC_RANGE]: scaling by 2^e is exact,
+// so the filter's geometry is unchanged, and fp16 (range 65504, 11-bit significand) is then safe for any input units.
+__global__ void __launch_bounds__(256) feat_tc_range_kernel(const double *__restrict__ f, int64_t n, const double *__restrict__ mu,
+                                                            unsigned *__restrict__ maxabs_bits) {
+    float m = 0.f;
+    for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < n * 33; e += (int64_t)gridDim.x * blockDim.x)
+        m = fmaxf(m, __double2float_ru(fabs(f[e] - mu[e % 33])));
+    for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(maxabs_bits, __float_as_uint(m));
+}
+__device__ __forceinline__ double tc_scale(const unsigned *maxabs_bits) {
+    float m = __uint_as_float(*maxabs_bits);
+    if (!(m > 0.f) || !isfinite(m)) return 1.0;
+    int x;
+    frexp((double)m, &x);                                 // m <= 2^x
+    return ldexp(1.0, 10 - x);                            // m * scale <= 2^10 = TC_RANGE
+}
+
 // role 0 = query rows, role 1 = target rows.  Rows in [n, padded) are written too: zeros for queries; for targets a
-// score of -1e30 so that a padding row is never a maximum and never inside a band.  One thread builds one row in
-// registers and stores it as 26 float4 (one per 16-byte K chunk).
+// score below anything a real row can reach (|a.b| <= 33 * 2^20, h <= 33 * 2^19), so a padding row is never a maximum and
+// never inside a band.  One thread builds one row in registers and stores it as 14 uint4 (one per 16-byte K chunk).
+// The norm term travels as  query 1024 x target -(h / 1024)  in three fp16 pieces (exact power-of-two rescaling).
 __global__ void __launch_bounds__(128) feat_tc_pack_kernel(const double *__restrict__ f, int64_t n, int64_t n_pad, int role,
-                                                           const double *__restrict__ mu, float *__restrict__ img,
-                                                           float *__restrict__ norm32, unsigned *__restrict__ maxnorm) {
+                                                           const double *__restrict__ mu, const unsigned *__restrict__ maxabs_bits,
+                                                           uint8_t *__restrict__ img, float *__restrict__ norm32,
+                                                           unsigned *__restrict__ maxnorm) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n_pad) return;
-    float row[TC_K];
+    unsigned short row[TC_K];
 #pragma unroll
-    for (int k = 0; k < TC_K; ++k) row[k] = 0.f;
+    for (int k = 0; k < TC_K; ++k) row[k] = 0;
     if (i < n) {
+        const double sc = tc_scale(maxabs_bits);
         double s = 0.0;
 #pragma unroll
         for (int j = 0; j < 33; ++j) {
-            float v = (float)(f[i * 33 + j] - mu[j]);     // centred: distances unchanged, norms (and so the band) shrink
-            float vh = tf32_rn(v);
-            float vl = tf32_rn(v - vh);                   // v - vh is exact in fp32
+            float v = (float)((f[i * 33 + j] - mu[j]) * sc);   // centred and scaled: distances scale by sc^2, exactly
+            __half vh = __float2half_rn(v);
+            __half vl = __float2half_rn(v - __half2float(vh));  // v - vh is exact in fp32
             s += (double)v * (double)v;
-            row[j] = vh;
-            row[33 + j] = role == 0 ? vl : vh;
-            row[66 + j] = role == 0 ? vh : vl;
+            row[j] = __half_as_ushort(vh);
+            row[33 + j] = __half_as_ushort(role == 0 ? vl : vh);
+            row[66 + j] = __half_as_ushort(role == 0 ? vh : vl);
         }
         float nf = __double2float_ru(s);
         if (norm32) norm32[i] = nf;
         atomicMax(maxnorm, __float_as_uint(nf));
         if (role == 0) {
-            row[99] = 1.f; row[100] = 1.f; row[101] = 1.f;
+            row[99] = row[100] = row[101] = __half_as_ushort(__float2half_rn(1024.f));
         } else {
-            double h = 0.5 * s;
-            float h0 = tf32_rn((float)h);
-            float h1 = tf32_rn((float)(h - (double)h0));
-            float h2 = tf32_rn((float)(h - (double)h0 - (double)h1));
-            row[99] = -h0; row[100] = -h1; row[101] = -h2;
+            double hq = 0.5 * s / 1024.0;
+            __half h0 = __double2half(hq);
+            __half h1 = __double2half(hq - (double)__half2float(h0));
+            __half h2 = __double2half(hq - (double)__half2float(h0) - (double)__half2float(h1));
+            row[99] = __half_as_ushort(__hneg(h0)); row[100] = __half_as_ushort(__hneg(h1)); row[101] = __half_as_ushort(__hneg(h2));
         }
     } else if (role == 1) {
-        row[99] = tf32_rn(-1e30f);
+        row[99] = row[100] = row[101] = __half_as_ushort(__float2half_rn(-60000.f));   // score -1.8e8
     }
-    float4 *dst = reinterpret_cast<float4 *>(img + tc_elem_offset(i, 0));
+    uint4 *dst = reinterpret_cast<uint4 *>(img + tc_row_offset(i));
 #pragma unroll
-    for (int c = 0; c < TC_KCH; ++c) dst[c * (TC_LBO / 16)] = make_float4(row[4 * c], row[4 * c + 1], row[4 * c + 2], row[4 * c + 3]);
+    for (int c = 0; c < TC_KCH; ++c) {
+        uint4 q;
+        q.x = row[8 * c] | ((unsigned)row[8 * c + 1] << 16); q.y = row[8 * c + 2] | ((unsigned)row[8 * c + 3] << 16);
+        q.z = row[8 * c + 4] | ((unsigned)row[8 * c + 5] << 16); q.w = row[8 * c + 6] | ((unsigned)row[8 * c + 7] << 16);
+        dst[c * (TC_LBO / 16)] = q;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ error band
-// D32 := an32 - 2 s' (real arithmetic on the computed fp32 values) against the oracle's exact f64 distance d of the f64 rows:
+// All quantities are those of the centred, power-of-two-scaled rows (|value| <= 1024); scaling multiplies every distance
+// by the same exact factor, so order and ties are unchanged.
+// D32 := an32 - 2 s' (real arithmetic on the computed fp32 values) against the exact f64 distance d of the (scaled) f64 rows:
 //   input rounding f64 -> f32          2.4e-7 (an + bn)
 //   an32 rounding                      0.6e-7  an
-//   3xTF32 representation + dropped al.bl   3 * 2^-22 |a_j b_j| per term  ->  7.2e-7 (an + bn)   in D
+//   3-term fp16 split (11-bit significands, like tf32): representation + dropped al.bl
+//                                      3 * 2^-22 |a_j b_j| per term  ->  7.2e-7 (an + bn)   in D
+//   fp16 subnormal floor of the low parts: |x - (xh + xl)| <= 2^-25 absolute  ->  3.5e-7 (sqrt an + sqrt bn)   in D
+//   norm pieces h/1024 = h0 + h1 + h2 in fp16, times 1024:  residual <= 2^-25 * 1024  ->  6.2e-5   in D
 //   accumulation: 102 terms, each addition modelled as TRUNCATED at fp32 (1 ulp of the running magnitude, the most
 //   pessimistic behaviour a tensor-core accumulator can have), running magnitude <= (an + 2 bn) / 2
 //                                      2 * 102 * 2^-23 * (an + 2 bn) / 2  =  1.22e-5 an + 2.43e-5 bn
-// => |D32 - d| <= 1.33e-5 an + 2.54e-5 bn.  TC_ERR_A / TC_ERR_B keep a 1.15x margin.  In score space the band is E (s' = -D/2,
-// and nearest-neighbour candidates are those with D32 <= min D32 + 2E).
+// => |D32 - d| <= 1.33e-5 an + 2.54e-5 bn + 3.5e-7 (sqrt an + sqrt bn) + 6.2e-5.  TC_ERR_A / TC_ERR_B keep a 1.15x margin.
+// In score space the band is E (s' = -D/2, and nearest-neighbour candidates are those with D32 <= min D32 + 2E).
 #define TC_ERR_A 1.53e-5f
 #define TC_ERR_B 2.92e-5f
 __device__ __forceinline__ float feat_tc_err(float an, float bmax) {
-    return __fadd_ru(__fadd_ru(__fmul_ru(TC_ERR_A, an), __fmul_ru(TC_ERR_B, bmax)), 5e-6f);
+    float lin = __fadd_ru(__fmul_ru(TC_ERR_A, an), __fmul_ru(TC_ERR_B, bmax));
+    float sq = __fmul_ru(4.0e-7f, __fadd_ru(__fsqrt_ru(an), __fsqrt_ru(bmax)));
+    return __fadd_ru(__fadd_ru(lin, sq), 1.0e-4f);
 }
 // monotone float <-> int key so that atomicMax(int) orders floats
 __device__ __forceinline__ int f2key(float f) { int b = __float_as_int(f); return b >= 0 ? b : b ^ 0x7fffffff; }
@@ -242,7 +275,7 @@ __device__ __forceinline__ void tc_push(TcRowState &st, const TcPool &pool, int 
 // grid = (query tiles, splits); split y owns target tiles [y * tiles_per_split, ...).
 template <int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restrict__ Bimg, int64_t nb, int n_btiles,
+feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__restrict__ Bimg, int64_t nb, int n_btiles,
                int tiles_per_split, int nsplit, const float *__restrict__ an32, const unsigned *__restrict__ bmax_bits,
                int *__restrict__ smax_key, const double *__restrict__ fa, const double *__restrict__ fb,
                FSplitOutTC *__restrict__ out, TcPool pool, float *__restrict__ dump, int64_t dump_ld, int swap_lbo_sbo) {
@@ -279,16 +312,16 @@ feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restri
         // ===== producer: query tile once, then the target tiles of this split through the ring =====
         if (lane == 0 && ntiles > 0) {
             mbar_expect_tx(BAR_A, TC_TILE_BYTES);
-            bulk_g2s(sA, Aimg + (size_t)qtile * (TC_TILE_BYTES / 4), TC_TILE_BYTES, BAR_A);
+            bulk_g2s(sA, Aimg + (size_t)qtile * TC_TILE_BYTES, TC_TILE_BYTES, BAR_A);
             for (int it = 0; it < ntiles; ++it) {
                 int s = it % TC_STAGES;
                 mbar_wait(BAR_EMPTY + 8 * s, ((it / TC_STAGES) & 1) ^ 1);
                 mbar_expect_tx(BAR_FULL + 8 * s, TC_TILE_BYTES);
-                bulk_g2s(sB0 + s * TC_TILE_BYTES, Bimg + (size_t)(t_begin + it) * (TC_TILE_BYTES / 4), TC_TILE_BYTES, BAR_FULL + 8 * s);
+                bulk_g2s(sB0 + s * TC_TILE_BYTES, Bimg + (size_t)(t_begin + it) * TC_TILE_BYTES, TC_TILE_BYTES, BAR_FULL + 8 * s);
             }
         }
     } else if (warp == 5) {
-        // ===== MMA issuer: one thread, 13 tcgen05.mma (128 x 128 x 8) per target tile =====
+        // ===== MMA issuer: one thread, 7 tcgen05.mma (128 x 128 x 16) per target tile =====
         if (lane == 0 && ntiles > 0) {
             const uint32_t lbo = swap_lbo_sbo ? TC_SBO : TC_LBO, sbo = swap_lbo_sbo ? TC_LBO : TC_SBO;
             mbar_wait(BAR_A, 0);
@@ -299,10 +332,10 @@ feat_tc_kernel(const float *__restrict__ Aimg, int64_t na, const float *__restri
                 tc_fence_after();
                 const uint32_t sB = sB0 + s * TC_TILE_BYTES;
 #pragma unroll
-                for (int k = 0; k < TC_K / 8; ++k) {
+                for (int k = 0; k < TC_K / 16; ++k) {          // one MMA consumes K = 16 halves = two 16-byte chunks
                     uint64_t ad = tc_smem_desc(sA + k * 2 * TC_LBO, lbo, sbo);
                     uint64_t bd = tc_smem_desc(sB + k * 2 * TC_LBO, lbo, sbo);
-                    tc_mma_tf32(tmem_base + as * 128, ad, bd, TC_IDESC, k > 0);
+                    tc_mma_f16(tmem_base + as * 128, ad, bd, TC_IDESC, k > 0);
                 }
                 tc_commit(BAR_EMPTY + 8 * s);             // smem stage free once these MMAs have read it
                 tc_commit(BAR_TFULL + 8 * as);            // accumulator ready for the epilogue
@@ -496,14 +529,15 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     int rc = tc_configure();
     if (rc < 0) return rc;
     TcPlan p = tc_plan(na, nb);
-    float *A = nullptr, *B = nullptr, *an = nullptr;
+    uint8_t *A = nullptr, *B = nullptr;
+    float *an = nullptr;
     unsigned *mx = nullptr;
     int *key = nullptr;
     FSplitOutTC *parts = nullptr;
-    IBL_CUDA(ibl_alloc(&A, (size_t)p.qtiles * (TC_TILE_BYTES / 4), st));
-    IBL_CUDA(ibl_alloc(&B, (size_t)p.btiles * (TC_TILE_BYTES / 4), st));
+    IBL_CUDA(ibl_alloc(&A, (size_t)p.qtiles * TC_TILE_BYTES, st));
+    IBL_CUDA(ibl_alloc(&B, (size_t)p.btiles * TC_TILE_BYTES, st));
     IBL_CUDA(ibl_alloc(&an, (size_t)p.na_pad, st));
-    IBL_CUDA(ibl_alloc(&mx, 2, st));
+    IBL_CUDA(ibl_alloc(&mx, 3, st));                       // max |a|^2, max |b|^2, max |f - mu| (float bits)
     IBL_CUDA(ibl_alloc(&key, (size_t)p.na_pad, st));
     IBL_CUDA(ibl_alloc(&parts, (size_t)na * p.nsplit, st));
     // candidate pool: one chunk for every row that has a candidate at all + 256k chunks (16 M candidates) of headroom
@@ -521,12 +555,16 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     IBL_CUDA(cudaMemsetAsync(pool.counter, 0, sizeof(int), st));
     double *mu = nullptr;
     IBL_CUDA(ibl_alloc(&mu, 33, st));
-    IBL_CUDA(cudaMemsetAsync(mx, 0, 2 * sizeof(unsigned), st));
+    IBL_CUDA(cudaMemsetAsync(mx, 0, 3 * sizeof(unsigned), st));
     feat_tc_center_kernel<<<1, 33 * TC_MU_GROUPS, 0, st>>>(fb, nb, mu);
     IBL_LAUNCH_CHECK();
-    feat_tc_pack_kernel<<<(unsigned)(p.na_pad / 128), 128, 0, st>>>(fa, na, p.na_pad, 0, mu, A, an, mx);
+    feat_tc_range_kernel<<<(unsigned)std::min<int64_t>((na * 33 + 255) / 256, 2 * IBL_SMS), 256, 0, st>>>(fa, na, mu, mx + 2);
     IBL_LAUNCH_CHECK();
-    feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, B, nullptr, mx + 1);
+    feat_tc_range_kernel<<<(unsigned)std::min<int64_t>((nb * 33 + 255) / 256, 2 * IBL_SMS), 256, 0, st>>>(fb, nb, mu, mx + 2);
+    IBL_LAUNCH_CHECK();
+    feat_tc_pack_kernel<<<(unsigned)(p.na_pad / 128), 128, 0, st>>>(fa, na, p.na_pad, 0, mu, mx + 2, A, an, mx);
+    IBL_LAUNCH_CHECK();
+    feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, mx + 2, B, nullptr, mx + 1);
     IBL_LAUNCH_CHECK();
     feat_tc_fill_key_kernel<<<(unsigned)((p.na_pad + 255) / 256), 256, 0, st>>>(key, p.na_pad);
     IBL_LAUNCH_CHECK();
@@ -549,7 +587,8 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
 }
 
 // Debug / test hook: the raw tensor-core scores s'(a_i, b_j) = a32.b32 - |b32|^2/2 as float32 [na][nb] (row-major), where
-// a32 / b32 are the rows after subtracting the filter's centre (written to center_out, device double[33], if not NULL).
+// a32 / b32 are the rows after subtracting the filter's centre and multiplying by its power-of-two scale (centre and
+// scale are written to center_out, device double[34], if not NULL).
 // swap_lbo_sbo = 1 exchanges the two stride fields of the shared-memory descriptors (layout probe; 0 is the product setting).
 IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double *fb, int64_t nb, float *scores,
                                      double *center_out, int swap_lbo_sbo, void *stream) {
@@ -558,26 +597,43 @@ IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double 
     int rc = tc_configure();
     if (rc < 0) return rc;
     TcPlan p = tc_plan(na, nb);
-    float *A = nullptr, *B = nullptr, *an = nullptr;
+    uint8_t *A = nullptr, *B = nullptr;
+    float *an = nullptr;
     unsigned *mx = nullptr;
-    IBL_CUDA(ibl_alloc(&A, (size_t)p.qtiles * (TC_TILE_BYTES / 4), st));
-    IBL_CUDA(ibl_alloc(&B, (size_t)p.btiles * (TC_TILE_BYTES / 4), st));
+    IBL_CUDA(ibl_alloc(&A, (size_t)p.qtiles * TC_TILE_BYTES, st));
+    IBL_CUDA(ibl_alloc(&B, (size_t)p.btiles * TC_TILE_BYTES, st));
     IBL_CUDA(ibl_alloc(&an, (size_t)p.na_pad, st));
-    IBL_CUDA(ibl_alloc(&mx, 2, st));
-    IBL_CUDA(cudaMemsetAsync(mx, 0, 2 * sizeof(unsigned), st));
+    IBL_CUDA(ibl_alloc(&mx, 3, st));                       // max |a|^2, max |b|^2, max |f - mu| (float bits)
+    IBL_CUDA(cudaMemsetAsync(mx, 0, 3 * sizeof(unsigned), st));
     double *mu = center_out;
     if (!mu) IBL_CUDA(ibl_alloc(&mu, 33, st));
     feat_tc_center_kernel<<<1, 33 * TC_MU_GROUPS, 0, st>>>(fb, nb, mu);
     IBL_LAUNCH_CHECK();
-    feat_tc_pack_kernel<<<(unsigned)(p.na_pad / 128), 128, 0, st>>>(fa, na, p.na_pad, 0, mu, A, an, mx);
+    feat_tc_range_kernel<<<(unsigned)std::min<int64_t>((na * 33 + 255) / 256, 2 * IBL_SMS), 256, 0, st>>>(fa, na, mu, mx + 2);
     IBL_LAUNCH_CHECK();
-    feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, B, nullptr, mx + 1);
+    feat_tc_range_kernel<<<(unsigned)std::min<int64_t>((nb * 33 + 255) / 256, 2 * IBL_SMS), 256, 0, st>>>(fb, nb, mu, mx + 2);
+    IBL_LAUNCH_CHECK();
+    feat_tc_pack_kernel<<<(unsigned)(p.na_pad / 128), 128, 0, st>>>(fa, na, p.na_pad, 0, mu, mx + 2, A, an, mx);
+    IBL_LAUNCH_CHECK();
+    feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, mx + 2, B, nullptr, mx + 1);
     IBL_LAUNCH_CHECK();
     dim3 grid(p.qtiles, p.nsplit);
     feat_tc_kernel<0><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, nullptr,
                                                         fa, fb, nullptr, TcPool{}, scores, nb, swap_lbo_sbo);
     IBL_LAUNCH_CHECK();
-    if (!center_out) ibl_free(mu, st);
+    if (center_out) {                                     // debug hook only: read the scale back and publish it
+        unsigned bits = 0;
+        IBL_CUDA(cudaMemcpyAsync(&bits, mx + 2, sizeof(bits), cudaMemcpyDeviceToHost, st));
+        IBL_CUDA(cudaStreamSynchronize(st));
+        float m;
+        memcpy(&m, &bits, sizeof(m));
+        double sc = 1.0;
+        if (m > 0.f && std::isfinite(m)) { int x; frexp((double)m, &x); sc = ldexp(1.0, 10 - x); }
+        IBL_CUDA(cudaMemcpyAsync(center_out + 33, &sc, sizeof(sc), cudaMemcpyHostToDevice, st));
+        IBL_CUDA(cudaStreamSynchronize(st));
+    } else {
+        ibl_free(mu, st);
+    }
     ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st);
     return IBL_OK;
 }

@@ -129,35 +129,52 @@ __global__ void __launch_bounds__(SCORE_THREADS) ransac_score_kernel(GridView g,
     }
 }
 
-// one warp per hypothesis: tile partials in index order + correspondence inlier count
-__global__ void __launch_bounds__(128) ransac_finalize_kernel(const int *__restrict__ part_cnt,
-                                                              const double *__restrict__ part_err, int ntiles,
-                                                              int64_t nh, const double *__restrict__ T_all,
-                                                              const double *__restrict__ src,
-                                                              const double *__restrict__ tgt,
-                                                              const int32_t *__restrict__ corres, int64_t n_corres,
-                                                              double max_d, int32_t *__restrict__ inliers,
-                                                              double *__restrict__ err2,
-                                                              int32_t *__restrict__ corres_inliers) {
-    int lane = threadIdx.x & 31;
-    int64_t hyp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-    if (hyp >= nh) return;
+// one CTA per hypothesis: tile partials (fixed order: thread-strided, warp tree, warps in order) + the correspondence
+// inlier count (EvaluateInlierCorrespondenceRatio numerator).  The gathers are latency-bound, so a whole CTA per
+// hypothesis rather than a warp.
+#define FIN_THREADS 128
+__global__ void __launch_bounds__(FIN_THREADS) ransac_finalize_kernel(const int *__restrict__ part_cnt,
+                                                                      const double *__restrict__ part_err, int ntiles,
+                                                                      int64_t nh, const double *__restrict__ T_all,
+                                                                      const double *__restrict__ src,
+                                                                      const double *__restrict__ tgt,
+                                                                      const int32_t *__restrict__ corres, int64_t n_corres,
+                                                                      double max_d, int32_t *__restrict__ inliers,
+                                                                      double *__restrict__ err2,
+                                                                      int32_t *__restrict__ corres_inliers) {
+    __shared__ double se[FIN_THREADS / 32];
+    __shared__ int sc[FIN_THREADS / 32], si[FIN_THREADS / 32];
+    __shared__ double T[16];
+    const int64_t hyp = blockIdx.x;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (threadIdx.x < 16) T[threadIdx.x] = T_all[16 * hyp + threadIdx.x];
+    __syncthreads();
     double e = 0; int c = 0;
-    for (int k = lane; k < ntiles; k += 32) { e += part_err[hyp * ntiles + k]; c += part_cnt[hyp * ntiles + k]; }
-    for (int o = 16; o; o >>= 1) { e += __shfl_down_sync(0xffffffffu, e, o); c += __shfl_down_sync(0xffffffffu, c, o); }
-    double T[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) T[k] = T_all[16 * hyp + k];
+    for (int k = threadIdx.x; k < ntiles; k += FIN_THREADS) { e += part_err[hyp * ntiles + k]; c += part_cnt[hyp * ntiles + k]; }
     int ci = 0;
-    for (int64_t k = lane; k < n_corres; k += 32) {
-        size_t cs = (size_t)corres[2 * k], ct = (size_t)corres[2 * k + 1];
-        double x, y, z;
-        ibl_xform(T, src[3 * cs], src[3 * cs + 1], src[3 * cs + 2], x, y, z);
-        double d[3] = {x - tgt[3 * ct], y - tgt[3 * ct + 1], z - tgt[3 * ct + 2]};
-        ci += ibl_dot(d, d) < max_d * max_d;
+    if (corres_inliers) {
+        const double md2 = max_d * max_d;
+        for (int64_t k = threadIdx.x; k < n_corres; k += FIN_THREADS) {
+            size_t cs = (size_t)corres[2 * k], ct = (size_t)corres[2 * k + 1];
+            double x, y, z;
+            ibl_xform(T, src[3 * cs], src[3 * cs + 1], src[3 * cs + 2], x, y, z);
+            double d[3] = {x - tgt[3 * ct], y - tgt[3 * ct + 1], z - tgt[3 * ct + 2]};
+            ci += ibl_dot(d, d) < md2;
+        }
     }
-    for (int o = 16; o; o >>= 1) ci += __shfl_down_sync(0xffffffffu, ci, o);
-    if (lane == 0) { inliers[hyp] = c; err2[hyp] = e; if (corres_inliers) corres_inliers[hyp] = ci; }
+    for (int o = 16; o; o >>= 1) {
+        e += __shfl_down_sync(0xffffffffu, e, o);
+        c += __shfl_down_sync(0xffffffffu, c, o);
+        ci += __shfl_down_sync(0xffffffffu, ci, o);
+    }
+    if (lane == 0) { se[w] = e; sc[w] = c; si[w] = ci; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double te = 0; int tc = 0, ti = 0;
+        for (int k = 0; k < FIN_THREADS / 32; ++k) { te += se[k]; tc += sc[k]; ti += si[k]; }
+        inliers[hyp] = tc; err2[hyp] = te;
+        if (corres_inliers) corres_inliers[hyp] = ti;
+    }
 }
 
 IBL_API int ibl_ransac_score(const ibl_grid_t *tgt_grid, const double *src, int64_t n_src, const double *tgt,
@@ -181,8 +198,8 @@ IBL_API int ibl_ransac_score(const ibl_grid_t *tgt_grid, const double *src, int6
         ransac_score_kernel<<<grid, SCORE_THREADS, 0, st>>>(ibl_view(tgt_grid), src, n_src, T_out, max_d, max_d * max_d, ntiles, pc, pe);
         IBL_LAUNCH_CHECK();
     }
-    ransac_finalize_kernel<<<(unsigned)((nh * 32 + 127) / 128), 128, 0, st>>>(pc, pe, ntiles, nh, T_out, src, tgt, corres, n_corres,
-                                                                               max_d, inliers, err2, corres_inliers);
+    ransac_finalize_kernel<<<(unsigned)nh, FIN_THREADS, 0, st>>>(pc, pe, ntiles, nh, T_out, src, tgt, corres, n_corres, max_d,
+                                                                 inliers, err2, corres_inliers);
     IBL_LAUNCH_CHECK();
     ibl_free(pc, st); ibl_free(pe, st);
     return IBL_OK;

@@ -231,13 +231,13 @@ def feature_nn(fa, fb):
 
 
 def feature_scores_debug(fa, fb, swap_lbo_sbo=0):
-    """Test hook: raw tcgen05 scores a32.b32 - |b32|^2/2 of the matcher's filter (rows centred on the returned
-    centre), float32 [na, nb].  -> (scores, centre float64 [33])."""
+    """Test hook: raw tcgen05 scores a32.b32 - |b32|^2/2 of the matcher's filter, float32 [na, nb], where a32 / b32 are
+    the rows minus the returned centre, times the returned power-of-two scale.  -> (scores, centre float64 [33], scale)."""
     out = torch.empty((fa.shape[0], fb.shape[0]), dtype=torch.float32, device=fa.device)
-    mu = torch.empty(33, dtype=torch.float64, device=fa.device)
+    mu = torch.empty(34, dtype=torch.float64, device=fa.device)
     check(lib().ibl_feature_scores_debug(_p(fa), fa.shape[0], _p(fb), fb.shape[0], _p(out), _p(mu), int(swap_lbo_sbo),
                                          _stream()), "feature_scores_debug")
-    return out, mu
+    return out, mu[:33], float(mu[33].item())
 
 
 def feature_nn_stats(reset=True):

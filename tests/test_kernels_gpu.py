@@ -265,17 +265,31 @@ def test_feature_scores_tensor_core_band(K):
     rng = np.random.default_rng(41)
     fa, fb = _fpfh_like(rng, 333), _fpfh_like(rng, 517)
     fb[100] = fa[7]
-    S, mu = K.feature_scores_debug(dev(fa), dev(fb))
+    S, mu, sc = K.feature_scores_debug(dev(fa), dev(fb))
     S, mu = h(S).astype(np.float64), h(mu)
     assert S.shape == (333, 517) and np.isfinite(S).all()
-    # the filter works on rows centred on mu (any centre leaves |a - b| unchanged) and rounded to fp32
-    a32 = (fa - mu).astype(np.float32).astype(np.float64)
-    an, bn = (a32 * a32).sum(1), ((fb - mu).astype(np.float32).astype(np.float64) ** 2).sum(1)
-    assert an.mean() < 0.9 * (fa * fa).sum(1).mean()          # centring shrinks the norms the band scales with
-    d_exact = ((fa[:, None, :] - fb[None, :, :]) ** 2).sum(-1)
+    # the filter works on rows centred on mu and scaled by the power of two sc (|value| <= 1024, for fp16), rounded to
+    # fp32; neither changes the order of the distances
+    assert sc == 2.0 ** round(np.log2(sc)) and 512 < np.abs((np.concatenate([fa, fb]) - mu) * sc).max() <= 1024
+    a32 = ((fa - mu) * sc).astype(np.float32).astype(np.float64)
+    an, bn = (a32 * a32).sum(1), (((fb - mu) * sc).astype(np.float32).astype(np.float64) ** 2).sum(1)
+    assert an.mean() < 0.9 * sc * sc * (fa * fa).sum(1).mean()   # centring shrinks the norms the band scales with
+    d_exact = sc * sc * ((fa[:, None, :] - fb[None, :, :]) ** 2).sum(-1)
     err = np.abs((an[:, None] - 2.0 * S) - d_exact)
-    assert (err <= 1.33e-5 * an[:, None] + 2.54e-5 * bn[None, :] + 1e-9).all()
+    bound = 1.33e-5 * an[:, None] + 2.54e-5 * bn[None, :] + 3.5e-7 * (np.sqrt(an)[:, None] + np.sqrt(bn)[None, :]) + 6.2e-5
+    assert (err <= bound).all()
     assert err.max() / (an.max() + bn.max()) < 5e-6          # measured ~6e-7 on B200: the band is conservative
+
+
+def test_feature_nn_any_units(K, oc):
+    """The fp16 filter rescales by a power of two, so features in any units (here x1e6 and x1e-6) match the oracle."""
+    rng = np.random.default_rng(47)
+    fa, fb = _fpfh_like(rng, 300), _fpfh_like(rng, 420)
+    fb[17] = fa[5]
+    for unit in (1e6, 1e-6):
+        got = h(K.feature_nn(dev(fa * unit), dev(fb * unit)))
+        assert np.array_equal(got, oc.feature_nn(np.ascontiguousarray((fa * unit).T), np.ascontiguousarray((fb * unit).T)))
+        assert got[5] == 17
 
 
 @pytest.mark.parametrize("na,nb", [(1, 1), (127, 129), (128, 128), (129, 127), (3, 1000), (1000, 3)])

@@ -32,14 +32,15 @@ def stage_scores():
     fa, fb = fpfh_like(200, rng), fpfh_like(300, rng)
     A, B = torch.from_numpy(fa).cuda(), torch.from_numpy(fb).cuda()
     for swap in (0, 1):
-        S, mu = K.feature_scores_debug(A, B, swap)
+        S, mu, sc = K.feature_scores_debug(A, B, swap)
         S, mu = S.cpu().numpy().astype(np.float64), mu.cpu().numpy()
-        a32, b32 = (fa - mu).astype(np.float32).astype(np.float64), (fb - mu).astype(np.float32).astype(np.float64)
+        a32 = ((fa - mu) * sc).astype(np.float32).astype(np.float64)
+        b32 = ((fb - mu) * sc).astype(np.float32).astype(np.float64)
         ref = a32 @ b32.T - 0.5 * (b32 * b32).sum(1)[None, :]
         scale = (a32 * a32).sum(1)[:, None] + (b32 * b32).sum(1)[None, :]
         err = np.abs(S - ref) / scale
-        print(f"scores swap={swap}: max rel err {err.max():.3e}  mean {err.mean():.3e}  finite={np.isfinite(S).all()}  "
-              f"mean |a-mu|^2 / |a|^2 = {(a32 * a32).sum() / (fa * fa).sum():.3f}", flush=True)
+        print(f"scores swap={swap}: scale {sc}  max rel err {err.max():.3e}  mean {err.mean():.3e}  finite={np.isfinite(S).all()}  "
+              f"mean |a-mu|^2 / |a|^2 = {(a32 * a32).sum() / (sc * sc * (fa * fa).sum()):.3f}", flush=True)
 
 
 def real_fpfh():

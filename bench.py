@@ -162,6 +162,10 @@ def run_product(args):
     from instance_based_loc_b200.o3d import registration as reg
     w = WORKLOAD
     B = args.frames_per_step
+    host_wait = args.host_wait
+    if host_wait == "auto-cores":                       # spinning waits cost > 2 cores per rank with 4 frames in flight
+        host_wait = "block" if (os.cpu_count() or 1) / max(world, 1) < 4 else "auto"
+    K.set_host_wait(host_wait)
     scene, frames = make_inputs(B, rank, "cuda")
     om, host_mem = selfcheck.build_memory(scene, w["mem_spacing"], w["mem_voxel"], f=w["f"])
     reg.ransac_seed = w["ransac_seed"]
@@ -234,8 +238,8 @@ def run_product(args):
     if tname in TENSOR_KERNELS:
         bound, unit, achieved, peak = "tensor", "TFLOP/s", work_per_s / 1e12, tensor_peak
         note = ("achieved = ALGORITHMIC flops 2*33*N_s*N_t of the FPFH distance matrix per launch / launch time (pack, two "
-                "tcgen05 tf32 GEMM passes of depth 104 and the exact f64 re-evaluation are all inside the launch); peak is the "
-                "measured dense bf16 figure, the kernel issues kind::tf32 whose nominal rate is half of it")
+                "one-pass tcgen05 kind::f16 score GEMM of depth 112 (3-way fp16 split) and the exact f64 re-evaluation are all inside "
+                "the launch); peak is the measured dense bf16 figure")
     else:
         bound, unit, achieved, peak = "hbm", "GB/s", work_per_s / 1e9, hbm_peak
         note = "achieved = algorithmic bytes per launch (DESIGN.md section 4) / launch time"
@@ -252,7 +256,8 @@ def run_product(args):
     line = {"metric": "localised frames/s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": w["name"], "frames_per_step_per_gpu": B, "frames_in_flight": args.workers, "memory_objects": w["m"],
+            "config": {"workload": w["name"], "frames_per_step_per_gpu": B, "frames_in_flight": args.workers,
+                       "host_wait": host_wait, "host_cores": os.cpu_count(), "memory_objects": w["m"],
                        "memory_points": int(sum(len(m["points"]) for m in host_mem)), "embedding_dim": w["D"],
                        "ransac": "max_iteration 4e6, confidence 0.99, counter-based sample stream",
                        "l2_flush": "256 MiB memset before every step", "parallelism": f"frames sharded over {world} rank(s)"},
@@ -304,6 +309,8 @@ def main():
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
     ap.add_argument("--frames-per-step", type=int, default=8)
     ap.add_argument("--workers", type=int, default=4, help="frames in flight per GPU (host threads / CUDA streams)")
+    ap.add_argument("--host-wait", default="auto-cores", choices=["auto-cores", "auto", "spin", "yield", "block"],
+                    help="how host threads wait in stream syncs; auto-cores = block when the box has < 4 cores per rank")
     ap.add_argument("--cpu-budget", type=float, default=25.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profiler-range", action="store_true",

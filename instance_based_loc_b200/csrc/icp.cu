@@ -155,13 +155,10 @@ IBL_API int ibl_color_gradient(const double *pts, const double *nrm, const doubl
 }
 
 // ------------------------------------------------------------------------------------------------
-struct ColoredJTJ {   // 21 upper-triangle JTJ + 6 JTr
-    const double *src, *scol; const int32_t *nn; const double *tgt, *tnrm, *tcol, *tgrad; double sg, sp;
-    __device__ bool operator()(int64_t i, double *v) const {
-        int j = nn[i];
-        if (j < 0) return false;
-        size_t ct = (size_t)j;
-        double vs[3] = {src[3 * i], src[3 * i + 1], src[3 * i + 2]};
+// one correspondence (source point vs, its colour row, target index ct) -> 21 upper-triangle JTJ + 6 JTr
+struct ColoredTerms {
+    const double *tgt, *tnrm, *tcol, *tgrad; double sg, sp;
+    __device__ __forceinline__ void operator()(const double *vs, double is, size_t ct, double *v) const {
         double vt[3] = {tgt[3 * ct], tgt[3 * ct + 1], tgt[3 * ct + 2]};
         double nt[3] = {tnrm[3 * ct], tnrm[3 * ct + 1], tnrm[3 * ct + 2]};
         double J[2][6], r[2], cr[3];
@@ -171,7 +168,6 @@ struct ColoredJTJ {   // 21 upper-triangle JTJ + 6 JTr
         double dn = ibl_dot(d, nt);
         r[0] = sg * dn;
         double vp[3] = {vs[0] - dn * nt[0], vs[1] - dn * nt[1], vs[2] - dn * nt[2]};
-        double is = (scol[3 * i] + scol[3 * i + 1] + scol[3 * i + 2]) / 3.0;
         double it = (tcol[3 * ct] + tcol[3 * ct + 1] + tcol[3 * ct + 2]) / 3.0;
         double dit[3] = {tgrad[3 * ct], tgrad[3 * ct + 1], tgrad[3 * ct + 2]};
         double dv[3] = {vp[0] - vt[0], vp[1] - vt[1], vp[2] - vt[2]};
@@ -189,6 +185,16 @@ struct ColoredJTJ {   // 21 upper-triangle JTJ + 6 JTr
         for (int a = 0; a < 6; ++a)
             for (int b = a; b < 6; ++b) v[o++] = J[0][a] * J[0][b] + J[1][a] * J[1][b];
         for (int a = 0; a < 6; ++a) v[21 + a] = J[0][a] * r[0] + J[1][a] * r[1];
+    }
+};
+struct ColoredJTJ {   // reduceK functor over a stored correspondence array
+    const double *src, *scol; const int32_t *nn; ColoredTerms t;
+    __device__ bool operator()(int64_t i, double *v) const {
+        int j = nn[i];
+        if (j < 0) return false;
+        double vs[3] = {src[3 * i], src[3 * i + 1], src[3 * i + 2]};
+        double is = (scol[3 * i] + scol[3 * i + 1] + scol[3 * i + 2]) / 3.0;
+        t(vs, is, (size_t)j, v);
         return true;
     }
 };
@@ -211,7 +217,7 @@ IBL_API int ibl_colored_update(const double *src, const double *scol, const int3
                                const double *tnrm, const double *tcol, const double *tgrad, double lambda_geometric,
                                double *h_out27, double *h_T16, void *stream) {
     IBL_ARG(n >= 0 && h_out27);
-    ColoredJTJ f{src, scol, nn_idx, tgt, tnrm, tcol, tgrad, sqrt(lambda_geometric), sqrt(1.0 - lambda_geometric)};
+    ColoredJTJ f{src, scol, nn_idx, {tgt, tnrm, tcol, tgrad, sqrt(lambda_geometric), sqrt(1.0 - lambda_geometric)}};
     int rc = reduceK<27>(n, f, h_out27, ibl_stream(stream));
     if (rc < 0) return rc;
     if (h_T16) solve_update_host(h_out27, h_T16);
@@ -234,6 +240,129 @@ static bool is_identity(const double *T) {
     return true;
 }
 
+// ------------------------------------------------------------------------------------------------
+// One coloured-ICP iteration in ONE kernel (A.8 loop body): every thread moves its source point by the update of the
+// previous solve, finds its nearest target within max_d (exact NN field / ring search), and contributes to BOTH the
+// registration score of the moved cloud (inlier count, err2 -- reduced in nn_score_kernel's order so fitness and rmse
+// are bit-identical to evaluate_registration) and the normal equations of the NEXT solve.  Per-CTA partials
+// [cnt, err2, 27 x JTJ/JTr] go back in one copy; the host adds them in a fixed order.  Replaces transform + nn_score +
+// score_final + reduceK and one of the two host round trips per iteration.
+#define STEP_W 29
+struct Mat16i { double v[16]; };
+__global__ void __launch_bounds__(256) colored_step_kernel(GridView g, const double *__restrict__ in, double *__restrict__ out,
+                                                           const double *__restrict__ scol, int64_t n, Mat16i U, int has_U,
+                                                           ColoredTerms terms, double max_d, double max_d2,
+                                                           int32_t *__restrict__ nn, double *__restrict__ part) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int hit = 0;
+    double e = 0.0;
+    double v[27];
+#pragma unroll
+    for (int k = 0; k < 27; ++k) v[k] = 0.0;
+    if (i < n) {
+        double p[3] = {in[3 * i], in[3 * i + 1], in[3 * i + 2]};
+        if (has_U) { double a, b, c; ibl_xform(U.v, p[0], p[1], p[2], a, b, c); p[0] = a; p[1] = b; p[2] = c; }
+        out[3 * i] = p[0]; out[3 * i + 1] = p[1]; out[3 * i + 2] = p[2];
+        double bd;
+        int j = ibl_nn1_thread(g, p[0], p[1], p[2], max_d, max_d2, bd);
+        nn[i] = j;
+        if (j >= 0) {
+            hit = 1; e = bd;
+            double is = (scol[3 * i] + scol[3 * i + 1] + scol[3 * i + 2]) / 3.0;
+            terms(p, is, (size_t)j, v);
+        }
+    }
+    __shared__ double se[8];
+    __shared__ int sc[8];
+    __shared__ double sm[8][27];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int o = 16; o; o >>= 1) { e += __shfl_down_sync(0xffffffffu, e, o); hit += __shfl_down_sync(0xffffffffu, hit, o); }
+    if (lane == 0) { se[w] = e; sc[w] = hit; }
+#pragma unroll
+    for (int k = 0; k < 27; ++k) {
+        double x = v[k];
+        for (int o = 16; o; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+        if (lane == 0) sm[w][k] = x;
+    }
+    __syncthreads();
+    double *row = part + (size_t)blockIdx.x * STEP_W;
+    if (threadIdx.x == 0) {
+        double te = 0; long long tc = 0;
+        for (int k = 0; k < 8; ++k) { te += se[k]; tc += sc[k]; }
+        row[0] = (double)tc;
+        row[1] = te;
+    }
+    if (threadIdx.x < 27) {
+        double t = 0;
+        for (int ww = 0; ww < 8; ++ww) t += sm[ww][threadIdx.x];
+        row[2 + threadIdx.x] = t;
+    }
+}
+
+// host side of the fixed-order reductions: score_final_kernel's order for (cnt, err2), index order for the 27 sums
+static void step_reduce_host(const double *hp, int nb, ibl_score_t *sc, double *v27) {
+    double le[32]; long long lc[32];
+    for (int l = 0; l < 32; ++l) { le[l] = 0.0; lc[l] = 0; }
+    for (int k = 0; k < nb; ++k) { le[k & 31] += hp[(size_t)k * STEP_W + 1]; lc[k & 31] += (long long)hp[(size_t)k * STEP_W]; }
+    for (int o = 16; o; o >>= 1)
+        for (int l = 0; l < o; ++l) { le[l] += le[l + o]; lc[l] += lc[l + o]; }
+    sc->n_inliers = lc[0]; sc->err2 = le[0];
+    for (int k = 0; k < 27; ++k) v27[k] = 0.0;
+    for (int b = 0; b < nb; ++b)
+        for (int k = 0; k < 27; ++k) v27[k] += hp[(size_t)b * STEP_W + 2 + k];
+}
+
+static int icp_colored_fused(const ibl_grid_t *tgt_grid, const double *src, const double *scol, int64_t n_src,
+                             const double *tgt, const double *tnrm, const double *tcol, const double *tgrad, double max_d,
+                             double *T, int max_iteration, double rel_fitness, double rel_rmse, double lambda_geometric,
+                             ibl_reg_result_t *h_result, cudaStream_t st) {
+    double *pcd = nullptr, *part = nullptr; int32_t *nn = nullptr;
+    const int nb = (int)((n_src + 255) / 256);
+    IBL_CUDA(ibl_alloc(&pcd, (size_t)n_src * 3, st));
+    IBL_CUDA(ibl_alloc(&nn, (size_t)n_src, st));
+    IBL_CUDA(ibl_alloc(&part, (size_t)nb * STEP_W, st));
+    std::vector<double> hp((size_t)nb * STEP_W);
+    ColoredTerms terms{tgt, tnrm, tcol, tgrad, sqrt(lambda_geometric), sqrt(1.0 - lambda_geometric)};
+    const GridView gv = ibl_view(tgt_grid);
+    ibl_score_t sc = {0, 0.0};
+    double v27[27];
+    auto step = [&](const double *in, const double *U16) -> int {
+        Mat16i U;
+        int has_U = U16 != nullptr && !is_identity(U16);
+        for (int k = 0; k < 16; ++k) U.v[k] = has_U ? U16[k] : ((k % 5 == 0) ? 1.0 : 0.0);
+        {
+            IBL_PROF(IBL_PROF_ICP_REDUCE, st, (double)n_src * (24.0 + 24.0 + 24.0 + 4.0 + 96.0) + 8.0 * STEP_W * nb);
+            colored_step_kernel<<<nb, 256, 0, st>>>(gv, in, pcd, scol, n_src, U, has_U, terms, max_d, max_d * max_d, nn, part);
+            IBL_LAUNCH_CHECK();
+        }
+        IBL_CUDA(cudaMemcpyAsync(hp.data(), part, sizeof(double) * hp.size(), cudaMemcpyDeviceToHost, st));
+        IBL_CUDA(cudaStreamSynchronize(st));
+        if (tgt_grid->n > 0) step_reduce_host(hp.data(), nb, &sc, v27);
+        return IBL_OK;
+    };
+    int rc = step(src, T);
+    if (rc < 0) return rc;
+    double fit = (double)sc.n_inliers / (double)n_src;
+    double rmse = sc.n_inliers > 0 ? sqrt(sc.err2 / (double)sc.n_inliers) : 0.0;
+    int it = 0;
+    for (; it < max_iteration;) {
+        double upd[16];
+        solve_update_host(v27, upd);
+        matmul4(upd, T, T);
+        double pf = fit, pr = rmse;
+        if ((rc = step(pcd, upd)) < 0) return rc;
+        fit = (double)sc.n_inliers / (double)n_src;
+        rmse = sc.n_inliers > 0 ? sqrt(sc.err2 / (double)sc.n_inliers) : 0.0;
+        ++it;
+        if (fabs(pf - fit) < rel_fitness && fabs(pr - rmse) < rel_rmse) break;
+    }
+    memcpy(h_result->T, T, sizeof(double) * 16);
+    h_result->fitness = fit; h_result->inlier_rmse = rmse;
+    h_result->n_inliers = sc.n_inliers; h_result->err2 = sc.err2; h_result->iterations = it;
+    ibl_free(pcd, st); ibl_free(nn, st); ibl_free(part, st);
+    return IBL_OK;
+}
+
 IBL_API int ibl_icp(const ibl_grid_t *tgt_grid, const double *src, const double *scol, int64_t n_src, const double *tgt,
                     const double *tnrm, const double *tcol, const double *tgrad, int mode, double max_d,
                     const double *h_T_init, int max_iteration, double rel_fitness, double rel_rmse, double lambda_geometric,
@@ -246,6 +375,9 @@ IBL_API int ibl_icp(const ibl_grid_t *tgt_grid, const double *src, const double 
     memcpy(h_result->T, T, sizeof(T));
     h_result->best_hyp = -1;
     if (n_src == 0) { h_result->status = 1; return IBL_OK; }
+    if (mode == 1 && tgt_grid->n > 0)
+        return icp_colored_fused(tgt_grid, src, scol, n_src, tgt, tnrm, tcol, tgrad, max_d, T, max_iteration, rel_fitness,
+                                 rel_rmse, lambda_geometric, h_result, st);
     double *pcd = nullptr; int32_t *nn = nullptr;
     IBL_CUDA(ibl_alloc(&pcd, (size_t)n_src * 3, st));
     IBL_CUDA(ibl_alloc(&nn, (size_t)n_src, st));

@@ -8,9 +8,9 @@
 //     query row  : [ ah(33) | al(33) | ah(33) |  1    1    1   | 0 0 ]
 //     target row : [ bh(33) | bh(33) | bl(33) | -h0  -h1  -h2  | 0 0 ]      h = |b32|^2/2 = h0 + h1 + h2 (tf32 pieces)
 // so every product is exact in fp32 and only the al.bl term (<= 2^-22 |a||b|) is dropped.
-//   pass 1 : smax[q] = max_b s'(q,b)                                   (epilogue: one FMNMX per pair)
-//   pass 2 : every b with s'(q,b) >= smax[q] - E(q) is a candidate (epilogue: one FSETP per pair), remembered in a
-//            thread-private list; feat_tc_eval_kernel then evaluates the candidates exactly, one warp per query row
+// ONE pass over the score matrix: every epilogue thread owns a query row, keeps the running maximum m of its scores and
+// records every target b with s'(q,b) >= m - E(q) at the moment it streams by (m only grows, so the recorded set is a
+// superset of the final band [smax - E, smax]); feat_tc_eval_kernel then evaluates the recorded candidates exactly.
 // E is a rigorous bound on |(|a32|^2 - 2 s') - d_exact| (see feat_tc_err), so the exact nearest neighbour, and every
 // exact tie with it, is inside the band.
 //
@@ -92,6 +92,28 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, float *v) {
           "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
         : "r"(taddr) : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// The same load without the wait: the registers are NOT valid until tc_ld_wait32 has been executed on them.  The wait takes
+// the 32 registers as read-write operands, so every use of the values depends on it and cannot be scheduled above it.
+__device__ __forceinline__ void tc_ld32_issue(uint32_t taddr, float *v) {
+    uint32_t *r = reinterpret_cast<uint32_t *>(v);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tc_ld_wait32(float *v) {
+    uint32_t *r = reinterpret_cast<uint32_t *>(v);
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+        : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+          "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]),
+          "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]),
+          "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+        :: "memory");
 }
 // no-swizzle K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout, version 1)
 __device__ __forceinline__ uint64_t tc_smem_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
@@ -271,13 +293,43 @@ __device__ __forceinline__ void tc_push(TcRowState &st, const TcPool &pool, int 
     }
 }
 
-// MODE 0: dump s' to dump[q][ld] (debug).  MODE 1: smax_key[q] = max over this CTA's target tiles.  MODE 2: band + exact.
+// One chunk of 32 scores of this thread's query row, columns tb .. tb+31: raise the running row maximum m (tree of
+// independent FMNMX, not a 32-deep dependent chain), then record every column inside the band E below the maximum SO
+// FAR.  The running maximum only grows, so the final band [m_final - E, m_final] is a subset of what gets recorded; the
+// surplus (targets that were near-records when they streamed by) only costs exact evaluations later.
+__device__ __forceinline__ void tc_band_chunk(const float *v, float &m, float E, int tb, TcRowState &rs, const TcPool &pool,
+                                              int row, const double *__restrict__ fa_q, const double *__restrict__ fb) {
+    float t[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) t[c] = fmaxf(v[2 * c], v[2 * c + 1]);
+#pragma unroll
+    for (int w = 8; w; w >>= 1) {
+#pragma unroll
+        for (int c = 0; c < w; ++c) t[c] = fmaxf(t[c], t[c + w]);
+    }
+    const float cm = t[0];
+    m = fmaxf(m, cm);
+    const float r = __fsub_rd(m, E);                      // E = -inf for rows past the end: r = +inf, nothing is recorded
+    if (cm >= r) {
+        // Hit mask with static register indices, then a short loop that the lanes of the warp run in lock step.
+        unsigned mask = 0;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) mask |= (v[c] >= r) ? (1u << c) : 0u;
+        while (mask) {
+            int c = __ffs(mask) - 1;
+            mask &= mask - 1;
+            tc_push(rs, pool, row, tb + c, fa_q, fb);
+        }
+    }
+}
+
+// MODE 0: dump s' to dump[q][ld] (debug).  MODE 1: running row maximum + band candidates in one pass.
 // grid = (query tiles, splits); split y owns target tiles [y * tiles_per_split, ...).
 template <int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__restrict__ Bimg, int64_t nb, int n_btiles,
                int tiles_per_split, int nsplit, const float *__restrict__ an32, const unsigned *__restrict__ bmax_bits,
-               int *__restrict__ smax_key, const double *__restrict__ fa, const double *__restrict__ fb,
+               const double *__restrict__ fa, const double *__restrict__ fb,
                FSplitOutTC *__restrict__ out, TcPool pool, float *__restrict__ dump, int64_t dump_ld, int swap_lbo_sbo) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sA = smem_u32(smem);
@@ -345,64 +397,70 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
         // ===== epilogue: thread = one query row; TMEM lane = threadIdx.x =====
         const int64_t q = (int64_t)qtile * TC_M + threadIdx.x;
         const bool live = q < na;
-        float m = -INFINITY, r = INFINITY;
-        TcRowState rs;
-        rs.cnt = 0; rs.cur = -1; rs.ccnt = 0; rs.first = -1; rs.n_eval = 0; rs.bi = -1; rs.exhausted = 0; rs.bestd = INFINITY;
-        const int row = (int)(q * nsplit + split);
-        if (MODE == 2 && live) {
-            float E = feat_tc_err(an32[q], __uint_as_float(*bmax_bits));
-            r = __fsub_rd(key2f(smax_key[q]), E);
-        }
         const uint32_t lane_base = tmem_base + ((uint32_t)(warp * 32) << 16);
-        for (int it = 0; it < ntiles; ++it) {
-            int as = it & 1;
-            mbar_wait(BAR_TFULL + 8 * as, (it >> 1) & 1);
-            tc_fence_after();
-            const int64_t t0 = (int64_t)(t_begin + it) * TC_M;
+        if (MODE == 0) {
+            for (int it = 0; it < ntiles; ++it) {
+                int as = it & 1;
+                mbar_wait(BAR_TFULL + 8 * as, (it >> 1) & 1);
+                tc_fence_after();
+                const int64_t t0 = (int64_t)(t_begin + it) * TC_M;
 #pragma unroll 1
-            for (int ch = 0; ch < 4; ++ch) {
-                float v[32];
-                tc_ld32(lane_base + as * 128 + ch * 32, v);
-                if (MODE == 0) {
+                for (int ch = 0; ch < 4; ++ch) {
+                    float v[32];
+                    tc_ld32(lane_base + as * 128 + ch * 32, v);
                     if (live) {
 #pragma unroll
                         for (int c = 0; c < 32; ++c) { int64_t t = t0 + ch * 32 + c; if (t < nb) dump[q * dump_ld + t] = v[c]; }
                     }
-                } else if (MODE == 1) {
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) m = fmaxf(m, v[c]);
-                } else {
-                    bool hit = false;
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) hit |= (v[c] >= r);
-                    if (hit) {                            // only targets inside the error band of the row maximum
-                        // Hit mask with static register indices, then a short loop that the lanes of the warp run in lock
-                        // step (trip count = the largest number of hits any lane has in these 32 columns).
-                        unsigned mask = 0;
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) mask |= (v[c] >= r) ? (1u << c) : 0u;
-                        const int tb = (int)(t0 + ch * 32);           // padding rows score -1e30 and never get here
-                        while (mask) {
-                            int c = __ffs(mask) - 1;
-                            mask &= mask - 1;
-                            tc_push(rs, pool, row, tb + c, fa + q * 33, fb);
-                        }
-                    }
                 }
+                tc_fence_before();
+                mbar_arrive(BAR_TEMPTY + 8 * as);
             }
-            tc_fence_before();
-            mbar_arrive(BAR_TEMPTY + 8 * as);
-        }
-        if (live) {
-            if (MODE == 1 && ntiles > 0) atomicMax(smax_key + q, f2key(m));
-        }
-        if (MODE == 2 && live) {
-            if (rs.cur >= 0) pool.n[rs.cur] = rs.ccnt;
-            FSplitOutTC o;
-            o.d = rs.bestd; o.idx = rs.bi; o.cnt = rs.cnt; o.first = rs.first; o.pad = 0;
-            out[row] = o;
-            if (rs.cnt) atomicAdd(&g_tc_stats[0], (unsigned long long)rs.cnt);
-            if (rs.n_eval) atomicAdd(&g_tc_stats[1], (unsigned long long)rs.n_eval);
+        } else {
+            // Single pass: running maximum + band recording (tc_band_chunk).  The TMEM reads are software-pipelined over two
+            // register buffers -- the load of chunk c+1 is in flight while chunk c is processed -- and the accumulator is handed
+            // back to the MMA warp as soon as its last chunk has been READ, before that chunk is processed.
+            float m = -INFINITY;
+            const float E = live ? feat_tc_err(an32[q], __uint_as_float(*bmax_bits)) : -INFINITY;
+            TcRowState rs;
+            rs.cnt = 0; rs.cur = -1; rs.ccnt = 0; rs.first = -1; rs.n_eval = 0; rs.bi = -1; rs.exhausted = 0; rs.bestd = INFINITY;
+            const int row = (int)(q * nsplit + split);
+            const double *fa_q = fa + q * 33;
+            float va[32], vb[32];
+            if (ntiles > 0) {
+                mbar_wait(BAR_TFULL, 0);
+                tc_fence_after();
+                tc_ld32_issue(lane_base, va);
+            }
+#pragma unroll 1
+            for (int it = 0; it < ntiles; ++it) {
+                const int as = it & 1;
+                const uint32_t acc = lane_base + as * 128;
+                const int tb = (t_begin + it) * TC_M;               // padding rows score far below any band
+                tc_ld_wait32(va); tc_ld32_issue(acc + 32, vb);
+                tc_band_chunk(va, m, E, tb, rs, pool, row, fa_q, fb);
+                tc_ld_wait32(vb); tc_ld32_issue(acc + 64, va);
+                tc_band_chunk(vb, m, E, tb + 32, rs, pool, row, fa_q, fb);
+                tc_ld_wait32(va); tc_ld32_issue(acc + 96, vb);
+                tc_band_chunk(va, m, E, tb + 64, rs, pool, row, fa_q, fb);
+                tc_ld_wait32(vb);
+                tc_fence_before();
+                mbar_arrive(BAR_TEMPTY + 8 * as);
+                if (it + 1 < ntiles) {
+                    mbar_wait(BAR_TFULL + 8 * (as ^ 1), ((it + 1) >> 1) & 1);
+                    tc_fence_after();
+                    tc_ld32_issue(lane_base + (as ^ 1) * 128, va);
+                }
+                tc_band_chunk(vb, m, E, tb + 96, rs, pool, row, fa_q, fb);
+            }
+            if (live) {
+                if (rs.cur >= 0) pool.n[rs.cur] = rs.ccnt;
+                FSplitOutTC o;
+                o.d = rs.bestd; o.idx = rs.bi; o.cnt = rs.cnt; o.first = rs.first; o.pad = 0;
+                out[row] = o;
+                if (rs.cnt) atomicAdd(&g_tc_stats[0], (unsigned long long)rs.cnt);
+                if (rs.n_eval) atomicAdd(&g_tc_stats[1], (unsigned long long)rs.n_eval);
+            }
         }
     }
     tc_fence_before();
@@ -488,22 +546,28 @@ __global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int6
     if (extra) atomicAdd(&g_tc_stats[1], extra);
     nn[i] = bi;
 }
-__global__ void feat_tc_fill_key_kernel(int *__restrict__ key, int64_t n) {
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i < n) key[i] = f2key(-INFINITY);
-}
-
 struct TcPlan { int qtiles, btiles, nsplit, tiles_per_split; int64_t na_pad, nb_pad; };
+// grid = query tiles x splits of the target tiles, one CTA per SM at a time.  The split count is chosen so that the CTAs fill
+// whole waves of 148: cost(ns) = waves x (tiles per CTA + a fixed per-CTA cost of ~6 tile times for TMEM allocation, the
+// query-tile load and the pipeline fill); more splits also mean more partial rows to merge, so ties go to the smaller ns.
 static TcPlan tc_plan(int64_t na, int64_t nb) {
     TcPlan p;
     p.qtiles = (int)((na + TC_M - 1) / TC_M);
     p.btiles = (int)((nb + TC_M - 1) / TC_M);
     p.na_pad = (int64_t)p.qtiles * TC_M;
     p.nb_pad = (int64_t)p.btiles * TC_M;
-    int want = (IBL_SMS + p.qtiles - 1) / p.qtiles;      // one CTA per SM: fill the 148 SMs when there are few query tiles
-    if (want > p.btiles) want = p.btiles;
-    if (want < 1) want = 1;
-    p.tiles_per_split = (p.btiles + want - 1) / want;
+    int best_ns = 1;
+    long long best_cost = -1;
+    for (int ns = 1; ns <= 32 && ns <= p.btiles; ++ns) {
+        int tps = (p.btiles + ns - 1) / ns;
+        int real_ns = (p.btiles + tps - 1) / tps;
+        if (real_ns != ns) continue;
+        if (ns > 1 && tps < 8) break;
+        long long waves = ((long long)p.qtiles * ns + IBL_SMS - 1) / IBL_SMS;
+        long long cost = waves * (tps + 6);
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_ns = ns; }
+    }
+    p.tiles_per_split = (p.btiles + best_ns - 1) / best_ns;
     p.nsplit = (p.btiles + p.tiles_per_split - 1) / p.tiles_per_split;
     return p;
 }
@@ -511,7 +575,6 @@ static int tc_configure() {
     // the attribute is per function and per context; setting it again is cheap
     IBL_CUDA(cudaFuncSetAttribute(feat_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
     IBL_CUDA(cudaFuncSetAttribute(feat_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
-    IBL_CUDA(cudaFuncSetAttribute(feat_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
     return IBL_OK;
 }
 
@@ -532,13 +595,11 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     uint8_t *A = nullptr, *B = nullptr;
     float *an = nullptr;
     unsigned *mx = nullptr;
-    int *key = nullptr;
     FSplitOutTC *parts = nullptr;
     IBL_CUDA(ibl_alloc(&A, (size_t)p.qtiles * TC_TILE_BYTES, st));
     IBL_CUDA(ibl_alloc(&B, (size_t)p.btiles * TC_TILE_BYTES, st));
     IBL_CUDA(ibl_alloc(&an, (size_t)p.na_pad, st));
     IBL_CUDA(ibl_alloc(&mx, 3, st));                       // max |a|^2, max |b|^2, max |f - mu| (float bits)
-    IBL_CUDA(ibl_alloc(&key, (size_t)p.na_pad, st));
     IBL_CUDA(ibl_alloc(&parts, (size_t)na * p.nsplit, st));
     // candidate pool: one chunk for every row that has a candidate at all + 256k chunks (16 M candidates) of headroom
     TcPool pool;
@@ -566,13 +627,8 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     IBL_LAUNCH_CHECK();
     feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, mx + 2, B, nullptr, mx + 1);
     IBL_LAUNCH_CHECK();
-    feat_tc_fill_key_kernel<<<(unsigned)((p.na_pad + 255) / 256), 256, 0, st>>>(key, p.na_pad);
-    IBL_LAUNCH_CHECK();
     dim3 grid(p.qtiles, p.nsplit);
-    feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, key,
-                                                        fa, fb, parts, pool, nullptr, 0, 0);
-    IBL_LAUNCH_CHECK();
-    feat_tc_kernel<2><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, key,
+    feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1,
                                                         fa, fb, parts, pool, nullptr, 0, 0);
     IBL_LAUNCH_CHECK();
     {
@@ -582,7 +638,7 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     }
     feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn);
     IBL_LAUNCH_CHECK();
-    ibl_free(pool.entries, st); ibl_free(pool_meta, st); ibl_free(res, st); ibl_free(mu, st); ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st); ibl_free(key, st); ibl_free(parts, st);
+    ibl_free(pool.entries, st); ibl_free(pool_meta, st); ibl_free(res, st); ibl_free(mu, st); ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st); ibl_free(parts, st);
     return IBL_OK;
 }
 
@@ -618,7 +674,7 @@ IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double 
     feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, mx + 2, B, nullptr, mx + 1);
     IBL_LAUNCH_CHECK();
     dim3 grid(p.qtiles, p.nsplit);
-    feat_tc_kernel<0><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1, nullptr,
+    feat_tc_kernel<0><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1,
                                                         fa, fb, nullptr, TcPool{}, scores, nb, swap_lbo_sbo);
     IBL_LAUNCH_CHECK();
     if (center_out) {                                     // debug hook only: read the scale back and publish it

@@ -38,6 +38,14 @@ void ibl_prof_end(int slot, cudaStream_t st) {
     if (slot < (int)g_recs.size()) cudaEventRecord(g_recs[slot].e1, st);
 }
 
+IBL_API int ibl_set_host_wait(int mode) {
+    IBL_ARG(mode >= 0 && mode <= 3);
+    static const unsigned flags[4] = {cudaDeviceScheduleAuto, cudaDeviceScheduleSpin, cudaDeviceScheduleYield,
+                                      cudaDeviceScheduleBlockingSync};
+    IBL_CUDA(cudaSetDeviceFlags(flags[mode]));
+    return IBL_OK;
+}
+
 IBL_API int64_t ibl_launch_count(void) { return (int64_t)__sync_fetch_and_add(&g_ibl_launches, 0ull); }
 IBL_API int ibl_prof_num_tags(void) { return IBL_PROF_COUNT; }
 IBL_API const char *ibl_prof_tag_name(int tag) { return (tag >= 0 && tag < IBL_PROF_COUNT) ? kTagNames[tag] : ""; }

@@ -13,6 +13,46 @@ import torch
 from .. import kernels as K
 
 
+def assignments_from_topk(flat, val, chosen_objects, m, s, n_det):
+    """The bookkeeping half of get_top_indices_from_subvolumes (:226-270) on the top-k entries of every sub-volume
+    (flat int64 [n_comb,k] indices into (m+1)^s, val float32 [n_comb,k], both in the reference's argmax order).
+
+    The reference walks the n_comb*k entries in order, drops the "unassigned" coordinates, keeps the FIRST occurrence of
+    every distinct assignment with its value, then for each length L takes the max(1, L) best by value (python's
+    stable sort) and removes duplicates.  Same result here without the quadratic ``filtered not in assns`` list scans
+    (21 ms of interpreter time per 7-detection frame): assignments become integer keys, first occurrences come from
+    np.unique, the per-length selection from a stable argsort."""
+    flat = np.asarray(flat, np.int64)
+    val = np.asarray(val)
+    ncomb, k = flat.shape
+    chosen = np.asarray(chosen_objects, np.int64).reshape(ncomb, s)
+    coords = np.stack(np.unravel_index(flat.reshape(-1), (m + 1,) * s), axis=1)          # [ncomb*k, s]
+    det = np.repeat(chosen, k, axis=0)
+    assigned = coords != m
+    code = np.where(assigned, det * (m + 1) + coords + 1, 0)                               # 0 = dropped coordinate
+    # assigned pairs first, in their original (ascending detection) order
+    order = np.argsort(~assigned, axis=1, kind="stable")
+    code = np.take_along_axis(code, order, axis=1)
+    base = int(n_det) * (m + 1) + 2
+    key = np.zeros(len(code), np.int64)
+    for j in range(s):
+        key = key * base + code[:, j]
+    length = assigned.sum(axis=1)
+    rows = np.nonzero(length > 0)[0]
+    _, first = np.unique(key[rows], return_index=True)
+    first = rows[np.sort(first)]                                                           # first occurrences, walk order
+    vals = val.reshape(-1)[first]
+    out = []
+    for L in range(1, n_det + 1):
+        sel = first[length[first] == L]
+        if len(sel) == 0:
+            continue
+        best = sel[np.argsort(-vals[length[first] == L], kind="stable")[:max(1, L)]]
+        for r in best:
+            out.append([[int(det[r, j]), int(coords[r, j])] for j in range(s) if assigned[r, j]])
+    return out
+
+
 class SimVolume():
     def __init__(self, cosine_similarities) -> None:
         """:13-18.  Accepts a numpy array or a CUDA tensor [n_det, m] (float32)."""
@@ -65,32 +105,7 @@ class SimVolume():
         assert self.chosen_objects is not None, "call fast_construct_volume first"
         k = num_per_length * self.n_det * 4
         flat, val = self.top_entries(k)
-        s = self._subvolume_size
-        shape = (self.m + 1,) * s
-        unassigned_ind = self.m
-        all_filtered_topk = []
-        assns = []
-        for ci, chosen in enumerate(self.chosen_objects):
-            coords = np.stack(np.unravel_index(flat[ci], shape), axis=1)
-            for r in range(k):
-                filtered = [[int(i), int(c)] for i, c in zip(chosen, coords[r]) if c != unassigned_ind]
-                if len(filtered) == 0:
-                    continue
-                if filtered not in assns:
-                    assns.append(filtered)
-                    all_filtered_topk.append([filtered, val[ci, r]])
-        filtered_topk = []
-        for i in range(1, self.n_det + 1):
-            to_pick = max(1, i)
-            correct_length = [f for f in all_filtered_topk if len(f[0]) == i]
-            correct_length = sorted(correct_length, key=lambda x: x[-1], reverse=True)[:to_pick]
-            filtered_topk += correct_length
-        assns = [a[0] for a in filtered_topk]
-        no_dupe_assns = []
-        for a in assns:
-            if a not in no_dupe_assns:
-                no_dupe_assns.append(a)
-        return no_dupe_assns
+        return assignments_from_topk(flat, val, self.chosen_objects, self.m, self._subvolume_size, self.n_det)
 
     # ---- legacy API of the reference (not on the localise path) ---------------------------------------------
     def construct_volume(self):

@@ -60,3 +60,30 @@ def test_product_never_imports_oracle():
                 if re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M):
                     bad.append(os.path.join(d, f))
     assert not bad, bad
+
+
+def test_simvolume_bookkeeping_matches_oracle():
+    """Host logic of SimVolume.get_top_indices_from_subvolumes (vectorised first-occurrence / per-length selection) against
+    the oracle's literal restatement of similarity_volume.py:226-270, fed with the oracle's own top-k entries."""
+    import numpy as np
+    from oracle import ref_port
+    from instance_based_loc_b200.utils.similarity_volume import assignments_from_topk
+    rng = np.random.default_rng(5)
+    checked = 0
+    for trial in range(80):
+        n = int(rng.integers(1, 8))
+        m = int(rng.integers(max(n, 3), 24))
+        S = rng.uniform(-0.3, 1, (n, m)).astype(np.float32)
+        if trial % 3 == 0:
+            S = np.round(S, 1)                                  # many exact ties after the fp16 roundings
+        chosen, subs = ref_port.simvolume_subvolumes(S)
+        k = 4 * n * 4
+        if min(v.size for v in subs) < k:
+            continue
+        top = [ref_port.topk_first_index(v, k) for v in subs]
+        flat = np.stack([np.asarray(t[0], np.int64) for t in top])
+        val = np.stack([np.asarray(t[1], np.float32) for t in top])
+        got = assignments_from_topk(flat, val, chosen, m, len(chosen[0]), n)
+        assert got == ref_port.simvolume_assignments(S, 4), (trial, n, m)
+        checked += 1
+    assert checked > 40

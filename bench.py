@@ -163,8 +163,6 @@ def run_product(args):
     w = WORKLOAD
     B = args.frames_per_step
     host_wait = args.host_wait
-    if host_wait == "auto-cores":                       # spinning waits cost > 2 cores per rank with 4 frames in flight
-        host_wait = "block" if (os.cpu_count() or 1) / max(world, 1) < 4 else "auto"
     K.set_host_wait(host_wait)
     scene, frames = make_inputs(B, rank, "cuda")
     om, host_mem = selfcheck.build_memory(scene, w["mem_spacing"], w["mem_voxel"], f=w["f"])
@@ -177,26 +175,26 @@ def run_product(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     gathered = [torch.zeros((B, 7), dtype=torch.float64, device=dev) for _ in range(world)]
 
-    def step(host_inputs):
+    def step(host_inputs, workers=None):
         flush.zero_()                                   # L2 flush between iterations (126 MB L2 < 256 MiB)
         if host_inputs:                                 # H2D of this step's inputs from pinned memory
             batch = [{k: v.to(dev, non_blocking=True) for k, v in pinned[i].items()} for i in range(B)]
         else:
             batch = resident
-        res = om.localise_batch(batch, workers=args.workers, **LOCALISE_KW)
+        res = om.localise_batch(batch, workers=args.workers if workers is None else workers, **LOCALISE_KW)
         out = torch.from_numpy(np.stack([r[0] for r in res])).to(dev)
         if world > 1:                                   # the only traffic that crosses NVLink: 56 B per frame
             dist.all_gather(gathered, out)
         return out.cpu()                                # D2H of the step's result
 
-    def timed(host_inputs, steps):
+    def timed(host_inputs, steps, workers=None):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
-            step(host_inputs)
+            step(host_inputs, workers)
         e1.record()
         torch.cuda.synchronize()
         if world > 1:
@@ -218,10 +216,12 @@ def run_product(args):
         torch.cuda.cudart().cudaProfilerStop()
     launches = K.launch_count() - l0
     # per-kernel breakdown and the roofline kernel's launch time: the same steps again with CUDA events around every
-    # kernel group (csrc/prof.cu).  The events cost time, so this pass is not the one `value` is taken from.
+    # kernel group (csrc/prof.cu), ONE frame in flight -- with several frames in flight an event pair on one stream also
+    # spans whatever the other streams' kernels were doing, so a launch's duration would be over-stated.  The events cost
+    # time and nothing overlaps, so this pass is not the one `value` is taken from.
     K.prof_enable(True)
     K.prof_read()
-    ms_prof = timed(False, args.steps)
+    ms_prof = timed(False, args.steps, workers=1)
     prof = K.prof_read()
     K.prof_enable(False)
     ms_e2e = timed(True, args.steps)
@@ -246,9 +246,11 @@ def run_product(args):
     traffic, traffic_src = ncu_traffic(tname)
     roofline = {"kernel": tname, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit,
                 "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                "avg_launch_ms": per_launch_ms, "launches": t["launches"], "share_of_step": t["ms"] / ms_prof, "note": note,
-                "timed_in": "a second pass of the same K steps in this run, with CUDA events around every kernel group "
-                            "(the events cost time, so `value` comes from the first, un-instrumented pass)",
+                "avg_launch_ms": per_launch_ms, "launches": t["launches"],
+                "share_of_step": t["ms"] / max(sum(v["ms"] for v in prof.values()), 1e-9), "note": note,
+                "timed_in": "a second pass of the same K steps in this run, one frame in flight, with CUDA events around "
+                            "every kernel group (`value` comes from the first, un-instrumented pass); share_of_step = this "
+                            "kernel's event time / the sum over all kernel groups",
                 "ms_per_step_instrumented": ms_prof / args.steps}
     kernels = {k: {"ms": round(v["ms"], 3), "launches": v["launches"],
                    "gwork_per_s": round(v["work"] / max(v["ms"], 1e-9) / 1e6, 2)} for k, v in
@@ -309,8 +311,9 @@ def main():
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
     ap.add_argument("--frames-per-step", type=int, default=8)
     ap.add_argument("--workers", type=int, default=4, help="frames in flight per GPU (host threads / CUDA streams)")
-    ap.add_argument("--host-wait", default="auto-cores", choices=["auto-cores", "auto", "spin", "yield", "block"],
-                    help="how host threads wait in stream syncs; auto-cores = block when the box has < 4 cores per rank")
+    ap.add_argument("--host-wait", default="auto", choices=["auto", "spin", "yield", "block"],
+                    help="how host threads wait in stream syncs (ibl_set_host_wait).  Measured at 8 GPUs / 32 cores: auto "
+                         "(spin) 227-246 frames/s, yield 205, block 70 -- the path syncs hundreds of times per frame")
     ap.add_argument("--cpu-budget", type=float, default=25.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profiler-range", action="store_true",

@@ -214,8 +214,9 @@ int ibl_simvolume_topk(const float *S, int32_t nd, int32_t m, int32_t k, int64_t
 /* How host threads wait inside this library's (and the process's) stream synchronisations on the current device:
  * 0 = driver default (spins when cores outnumber contexts), 1 = spin, 2 = yield, 3 = blocking (sleep on an interrupt).
  * The path synchronises a few hundred times per frame (data-dependent sizes, the RANSAC and ICP host rules), so with
- * several frames in flight spinning costs > 2 cores per GPU; blocking trades ~10 us per wake-up for idle cores, which
- * is what an 8-GPU box with 2 cores per GPU needs.  No reference counterpart (Open3D is CPU-only). */
+ * several frames in flight spinning costs > 2 cores per GPU.  Measured on an 8 x B200 box with 32 cores (DESIGN.md
+ * section 5): blocking waits cost 3.4x in frames/s, yield 1.15x -- spin (the default) stays the right choice there; the
+ * knob exists for boxes with fewer cores per GPU.  No reference counterpart (Open3D is CPU-only). */
 int ibl_set_host_wait(int mode);
 
 /* ---------------------------------------------------------------- instrumentation ------------ */

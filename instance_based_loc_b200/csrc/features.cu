@@ -243,18 +243,29 @@ IBL_API int ibl_spfh(const double *pts, const double *nrm, int64_t n, const int3
     return IBL_OK;
 }
 
-// warp per point: lane j owns bin j (lane 0 also bin 32); the three block sums are accumulated by
-// lanes 0..2 in the reference's (k outer, j inner) order from values staged in shared memory
+// warp per point: lane j owns bin j of every neighbour's SPFH; the three block sums are accumulated by lanes 0..2 in
+// the reference's (k outer, j inner) order from values staged in shared memory.  Bin 32 does not fit the 32 lanes: its
+// quotients are computed for ALL neighbours of the point in a lane-parallel pre-pass (lane = neighbour), so the serial
+// per-neighbour loop issues one f64 division per lane instead of two (a divergent `if (lane == 0)` division costs the
+// whole warp its issue slots).  Every quotient and every sum is the same operation in the same order as before.
+#define FPFH_MAX_NN 224
 __global__ void __launch_bounds__(128) fpfh_kernel(int64_t n, const int32_t *__restrict__ nbr_idx,
                                                    const double *__restrict__ nbr_d2,
                                                    const int32_t *__restrict__ nbr_cnt, int max_nn,
                                                    const double *__restrict__ spfh, double *__restrict__ fpfh) {
-    __shared__ double vals[4][36];
+    __shared__ double vals[4][32];
+    __shared__ double v32s[4][FPFH_MAX_NN];
     int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t i = warp; i < n; i += nwarps) {
         int cnt = nbr_cnt[i];
+        for (int k = 1 + lane; k < cnt; k += 32) {
+            double dist = nbr_d2[i * max_nn + k];
+            size_t q = (size_t)nbr_idx[i * max_nn + k];
+            v32s[wib][k] = (dist == 0.0) ? 0.0 : __ddiv_rn(spfh[q * 33 + 32], dist);
+        }
+        __syncwarp();
         double acc = 0.0, acc32 = 0.0, bsum = 0.0;
         for (int k = 1; k < cnt; ++k) {
             double dist = nbr_d2[i * max_nn + k];
@@ -263,15 +274,14 @@ __global__ void __launch_bounds__(128) fpfh_kernel(int64_t n, const int32_t *__r
             double v = __ddiv_rn(spfh[q * 33 + lane], dist);
             acc = __dadd_rn(acc, v);
             vals[wib][lane] = v;
-            if (lane == 0) {
-                double v32 = __ddiv_rn(spfh[q * 33 + 32], dist);
-                acc32 = __dadd_rn(acc32, v32);
-                vals[wib][32] = v32;
-            }
             __syncwarp();
             if (lane < 3) {
 #pragma unroll
-                for (int t = 0; t < 11; ++t) bsum = __dadd_rn(bsum, vals[wib][lane * 11 + t]);
+                for (int t = 0; t < 10; ++t) bsum = __dadd_rn(bsum, vals[wib][lane * 11 + t]);
+                double last = v32s[wib][k];
+                if (lane < 2) last = vals[wib][lane * 11 + 10];
+                bsum = __dadd_rn(bsum, last);
+                if (lane == 2) acc32 = __dadd_rn(acc32, last);
             }
             __syncwarp();
         }
@@ -281,17 +291,18 @@ __global__ void __launch_bounds__(128) fpfh_kernel(int64_t n, const int32_t *__r
         if (cnt > 1) {
             double sc = lane < 11 ? s0 : (lane < 22 ? s1 : s2);
             fpfh[i * 33 + lane] = __dadd_rn(__dmul_rn(acc, sc), spfh[i * 33 + lane]);
-            if (lane == 0) fpfh[i * 33 + 32] = __dadd_rn(__dmul_rn(acc32, s2), spfh[i * 33 + 32]);
+            if (lane == 2) fpfh[i * 33 + 32] = __dadd_rn(__dmul_rn(acc32, s2), spfh[i * 33 + 32]);
         } else {
             fpfh[i * 33 + lane] = 0.0;
             if (lane == 0) fpfh[i * 33 + 32] = 0.0;
         }
+        __syncwarp();                            // v32s is rewritten by the next point's pre-pass
     }
 }
 
 IBL_API int ibl_fpfh(int64_t n, const int32_t *nbr_idx, const double *nbr_d2, const int32_t *nbr_cnt, int32_t max_nn,
                      const double *spfh, double *fpfh, void *stream) {
-    IBL_ARG(n >= 0 && max_nn >= 1);
+    IBL_ARG(n >= 0 && max_nn >= 1 && max_nn <= FPFH_MAX_NN);
     if (n == 0) return IBL_OK;
     IBL_ARG(nbr_idx && nbr_d2 && nbr_cnt && spfh && fpfh);
     int64_t blocks = (n + 3) / 4;

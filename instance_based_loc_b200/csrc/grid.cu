@@ -117,17 +117,7 @@ IBL_API int ibl_grid_create(const double *pts, int64_t n, double cell, int64_t m
         IBL_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp2, g->cell_start, g->cell_start, (int)(g->ncells + 1), st));
         ibl_free(tmp, st);
         ibl_free(cid, st); ibl_free(cid2, st); ibl_free(ord, st);
-        unsigned long long *occ = nullptr;
-        IBL_CUDA(ibl_alloc(&occ, 1, st));
-        IBL_CUDA(cudaMemsetAsync(occ, 0, 8, st));
-        int64_t nbc = (g->ncells + 255) / 256;
-        count_occupied_kernel<<<(unsigned)nbc, 256, 0, st>>>(g->cell_start, g->ncells, occ);
-        IBL_LAUNCH_CHECK();
-        unsigned long long hocc = 0;
-        IBL_CUDA(cudaMemcpyAsync(&hocc, occ, 8, cudaMemcpyDeviceToHost, st));
-        IBL_CUDA(cudaStreamSynchronize(st));
-        ibl_free(occ, st);
-        g->n_occupied = (int64_t)hocc;
+        g->n_occupied = -1;                                // counted on demand (ibl_grid_occupied): saves a host round trip per build
     }
     *out = g;
     return IBL_OK;
@@ -146,7 +136,25 @@ IBL_API void ibl_grid_destroy(ibl_grid_t *g) {
     delete g;
 }
 IBL_API double ibl_grid_cell(const ibl_grid_t *g) { return g ? g->cell : 0.0; }
-IBL_API int64_t ibl_grid_occupied(const ibl_grid_t *g) { return g ? g->n_occupied : 0; }
+// Number of non-empty cells.  Only the surface-spacing probe asks for it, so it is counted here, on the grid's stream,
+// the first time it is asked for (one small kernel and one host round trip) instead of in every ibl_grid_create.
+IBL_API int64_t ibl_grid_occupied(const ibl_grid_t *gc) {
+    ibl_grid *g = const_cast<ibl_grid *>(gc);
+    if (!g) return 0;
+    if (g->n_occupied >= 0) return g->n_occupied;
+    cudaStream_t st = g->stream;
+    unsigned long long *occ = nullptr, hocc = 0;
+    if (ibl_alloc(&occ, 1, st) != cudaSuccess) return -1;
+    cudaMemsetAsync(occ, 0, 8, st);
+    int64_t nbc = (g->ncells + 255) / 256;
+    count_occupied_kernel<<<(unsigned)nbc, 256, 0, st>>>(g->cell_start, g->ncells, occ);
+    __sync_fetch_and_add(&g_ibl_launches, 1ull);
+    cudaMemcpyAsync(&hocc, occ, 8, cudaMemcpyDeviceToHost, st);
+    cudaStreamSynchronize(st);
+    ibl_free(occ, st);
+    g->n_occupied = (int64_t)hocc;
+    return g->n_occupied;
+}
 
 // ------------------------------------------------------------------------------------------------
 // Chebyshev ring-distance field by level-set dilation

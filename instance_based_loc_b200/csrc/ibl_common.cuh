@@ -188,6 +188,25 @@ __device__ __forceinline__ int ibl_nn1_field(const GridView &g, double qx, doubl
     return (int)best_key;
 }
 
+// Is ANY target strictly within max_d of q?  (== "the nearest neighbour is within max_d", i.e. q is an inlier.)  With the
+// candidate field the voxel's list holds every target that can be the nearest neighbour of a point of the voxel, so the
+// scan stops at the first candidate inside max_d -- usually the first one -- instead of finishing the exact minimum.
+__device__ __forceinline__ bool ibl_any_within_field(const GridView &g, double qx, double qy, double qz, double max_d2) {
+    const NNFieldView &f = g.f;
+    double fx = floor((qx - f.ox) * f.inv_c), fy = floor((qy - f.oy) * f.inv_c), fz = floor((qz - f.oz) * f.inv_c);
+    if (!(fx >= 0.0 && fy >= 0.0 && fz >= 0.0 && fx < (double)f.nvx && fy < (double)f.nvy && fz < (double)f.nvz)) return false;
+    int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    int blk = f.block_ptr[((size_t)(iz >> 3) * f.nby + (iy >> 3)) * f.nbx + (ix >> 3)];
+    if (blk < 0) return false;
+    uint2 e = f.entries[(size_t)blk * 512 + (((iz & 7) << 6) | ((iy & 7) << 3) | (ix & 7))];
+    const int *c = f.cand + e.x;
+    for (unsigned k = 0; k < e.y; ++k) {
+        double4 t = g.sorted[c[k]];
+        if (ibl_d2(t.x, t.y, t.z, qx, qy, qz) < max_d2) return true;
+    }
+    return false;
+}
+
 __device__ __forceinline__ int ibl_nn1_thread(const GridView &g, double qx, double qy, double qz, double max_d,
                                               double max_d2, double &best_d2) {
     if (g.has_field && max_d <= g.f.max_d) return ibl_nn1_field(g, qx, qy, qz, max_d2, best_d2);

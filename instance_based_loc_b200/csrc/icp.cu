@@ -3,6 +3,7 @@
 // utils/fpfh_register.py:132-141).
 // Normal equations are reduced with warp shuffles (fixed tree) -> CTA -> per-CTA partials that the
 // host adds in index order: deterministic run to run.
+#include <algorithm>
 #include <vector>
 
 #include "ibl_common.cuh"
@@ -241,18 +242,52 @@ static bool is_identity(const double *T) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// One coloured-ICP iteration in ONE kernel (A.8 loop body): every thread moves its source point by the update of the
-// previous solve, finds its nearest target within max_d (exact NN field / ring search), and contributes to BOTH the
-// registration score of the moved cloud (inlier count, err2 -- reduced in nn_score_kernel's order so fitness and rmse
-// are bit-identical to evaluate_registration) and the normal equations of the NEXT solve.  Per-CTA partials
-// [cnt, err2, 27 x JTJ/JTr] go back in one copy; the host adds them in a fixed order.  Replaces transform + nn_score +
-// score_final + reduceK and one of the two host round trips per iteration.
+// One coloured-ICP iteration in ONE kernel (A.8 loop body), and the loop's host rule moved onto the device so that
+// iterations can be queued back to back.  Every thread moves its source point by the update of the previous solve, finds
+// its nearest target within max_d (exact NN field / ring search), and contributes to BOTH the registration score of the
+// moved cloud (inlier count, err2 -- reduced in nn_score_kernel / score_final_kernel's order, so fitness and rmse are
+// bit-identical to evaluate_registration) and the normal equations of the NEXT solve.  The last CTA to finish adds the
+// per-CTA partials in a fixed order, applies the convergence rule, solves the 6x6 system and composes the transformation
+// (IcpState).  Kernels launched after convergence return at once, so the host queues a batch of iterations and looks at
+// the state once per batch: 2-4 host round trips per registration instead of two per iteration.
 #define STEP_W 29
-struct Mat16i { double v[16]; };
+struct IcpState {
+    double T[16];            // accumulated transformation (what RegistrationResult reports)
+    double U[16];            // update the next step applies to the moved cloud
+    double fit, rmse, err2;
+    long long n_inliers;
+    int steps;               // steps done; step 0 scores the initial pose, step s >= 1 is ICP iteration s
+    int done;                // converged, or max_iteration reached
+    int has_U;
+    unsigned arrived;        // CTAs that have written their partials in the running step
+};
+
+__device__ void icp_solve_update(const double *v27, double *T16) {
+    double A[36], nb[6], x[6];
+    int o = 0;
+    for (int a = 0; a < 6; ++a)
+        for (int b = a; b < 6; ++b) { A[6 * a + b] = v27[o]; A[6 * b + a] = v27[o]; ++o; }
+    for (int a = 0; a < 6; ++a) nb[a] = -v27[21 + a];
+    for (int k = 0; k < 16; ++k) T16[k] = (k % 5 == 0) ? 1.0 : 0.0;
+    if (!ibl_ldlt_solve<6>(A, nb, x)) return;
+    double cx = cos(x[0]), sx = sin(x[0]), cy = cos(x[1]), sy = sin(x[1]), cz = cos(x[2]), sz = sin(x[2]);
+    T16[0] = cz * cy; T16[1] = cz * sy * sx - sz * cx; T16[2] = cz * sy * cx + sz * sx; T16[3] = x[3];
+    T16[4] = sz * cy; T16[5] = sz * sy * sx + cz * cx; T16[6] = sz * sy * cx - cz * sx; T16[7] = x[4];
+    T16[8] = -sy;     T16[9] = cy * sx;                T16[10] = cy * cx;               T16[11] = x[5];
+}
+
 __global__ void __launch_bounds__(256) colored_step_kernel(GridView g, const double *__restrict__ in, double *__restrict__ out,
-                                                           const double *__restrict__ scol, int64_t n, Mat16i U, int has_U,
+                                                           const double *__restrict__ scol, int64_t n, IcpState *S,
                                                            ColoredTerms terms, double max_d, double max_d2,
-                                                           int32_t *__restrict__ nn, double *__restrict__ part) {
+                                                           int32_t *__restrict__ nn, double *part, int nb,
+                                                           int max_iteration, double rel_fitness, double rel_rmse) {
+    __shared__ double sU[16];
+    __shared__ int s_flag[2];
+    if (threadIdx.x < 16) sU[threadIdx.x] = S->U[threadIdx.x];
+    if (threadIdx.x == 0) { s_flag[0] = S->done; s_flag[1] = S->has_U; }
+    __syncthreads();
+    if (s_flag[0]) return;                                // converged in an earlier step of this batch
+    const int has_U = s_flag[1];
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int hit = 0;
     double e = 0.0;
@@ -261,7 +296,7 @@ __global__ void __launch_bounds__(256) colored_step_kernel(GridView g, const dou
     for (int k = 0; k < 27; ++k) v[k] = 0.0;
     if (i < n) {
         double p[3] = {in[3 * i], in[3 * i + 1], in[3 * i + 2]};
-        if (has_U) { double a, b, c; ibl_xform(U.v, p[0], p[1], p[2], a, b, c); p[0] = a; p[1] = b; p[2] = c; }
+        if (has_U) { double a, b, c; ibl_xform(sU, p[0], p[1], p[2], a, b, c); p[0] = a; p[1] = b; p[2] = c; }
         out[3 * i] = p[0]; out[3 * i + 1] = p[1]; out[3 * i + 2] = p[2];
         double bd;
         int j = ibl_nn1_thread(g, p[0], p[1], p[2], max_d, max_d2, bd);
@@ -297,69 +332,96 @@ __global__ void __launch_bounds__(256) colored_step_kernel(GridView g, const dou
         for (int ww = 0; ww < 8; ++ww) t += sm[ww][threadIdx.x];
         row[2 + threadIdx.x] = t;
     }
-}
-
-// host side of the fixed-order reductions: score_final_kernel's order for (cnt, err2), index order for the 27 sums
-static void step_reduce_host(const double *hp, int nb, ibl_score_t *sc, double *v27) {
-    double le[32]; long long lc[32];
-    for (int l = 0; l < 32; ++l) { le[l] = 0.0; lc[l] = 0; }
-    for (int k = 0; k < nb; ++k) { le[k & 31] += hp[(size_t)k * STEP_W + 1]; lc[k & 31] += (long long)hp[(size_t)k * STEP_W]; }
-    for (int o = 16; o; o >>= 1)
-        for (int l = 0; l < o; ++l) { le[l] += le[l + o]; lc[l] += lc[l + o]; }
-    sc->n_inliers = lc[0]; sc->err2 = le[0];
-    for (int k = 0; k < 27; ++k) v27[k] = 0.0;
-    for (int b = 0; b < nb; ++b)
-        for (int k = 0; k < 27; ++k) v27[k] += hp[(size_t)b * STEP_W + 2 + k];
+    // ---- last CTA: fixed-order reduction of the partials, convergence rule, next update ----
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_flag[0] = (atomicAdd(&S->arrived, 1u) == (unsigned)(nb - 1));
+    __syncthreads();
+    if (!s_flag[0]) return;
+    __threadfence();
+    __shared__ double s_tot[2 + 27];
+    if (w == 0) {                                          // score_final_kernel's order: lane-strided sums, shuffle tree
+        double le = 0; long long lc = 0;
+        for (int k = lane; k < nb; k += 32) { le += __ldcg(part + (size_t)k * STEP_W + 1); lc += (long long)__ldcg(part + (size_t)k * STEP_W); }
+        for (int o = 16; o; o >>= 1) { le += __shfl_down_sync(0xffffffffu, le, o); lc += __shfl_down_sync(0xffffffffu, lc, o); }
+        if (lane == 0) { s_tot[0] = (double)lc; s_tot[1] = le; }
+    } else if (threadIdx.x < 32 + 27) {                    // normal equations: CTA partials in index order
+        int k = threadIdx.x - 32;
+        double t = 0;
+        for (int b = 0; b < nb; ++b) t += __ldcg(part + (size_t)b * STEP_W + 2 + k);
+        s_tot[2 + k] = t;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const long long c = (long long)s_tot[0];
+        const double err2 = s_tot[1];
+        const double fit = (double)c / (double)n;
+        const double rmse = c > 0 ? sqrt(err2 / (double)c) : 0.0;
+        const int steps = S->steps;
+        int done = 0;
+        if (steps >= 1 && fabs(S->fit - fit) < rel_fitness && fabs(S->rmse - rmse) < rel_rmse) done = 1;
+        if (steps >= max_iteration) done = 1;
+        S->fit = fit; S->rmse = rmse; S->err2 = err2; S->n_inliers = c; S->steps = steps + 1;
+        if (!done) {
+            double U[16], T[16], R[16];
+            icp_solve_update(s_tot + 2, U);
+            for (int k = 0; k < 16; ++k) T[k] = S->T[k];
+            for (int a = 0; a < 4; ++a)
+                for (int b = 0; b < 4; ++b) {
+                    double t = 0;
+                    for (int k = 0; k < 4; ++k) t += U[4 * a + k] * T[4 * k + b];
+                    R[4 * a + b] = t;
+                }
+            bool ident = true;
+            for (int k = 0; k < 16; ++k) { S->T[k] = R[k]; S->U[k] = U[k]; ident = ident && (U[k] == ((k % 5 == 0) ? 1.0 : 0.0)); }
+            S->has_U = ident ? 0 : 1;
+        }
+        S->arrived = 0;
+        S->done = done;
+    }
 }
 
 static int icp_colored_fused(const ibl_grid_t *tgt_grid, const double *src, const double *scol, int64_t n_src,
                              const double *tgt, const double *tnrm, const double *tcol, const double *tgrad, double max_d,
                              double *T, int max_iteration, double rel_fitness, double rel_rmse, double lambda_geometric,
                              ibl_reg_result_t *h_result, cudaStream_t st) {
-    double *pcd = nullptr, *part = nullptr; int32_t *nn = nullptr;
+    double *pcd = nullptr, *part = nullptr; int32_t *nn = nullptr; IcpState *dS = nullptr;
     const int nb = (int)((n_src + 255) / 256);
     IBL_CUDA(ibl_alloc(&pcd, (size_t)n_src * 3, st));
     IBL_CUDA(ibl_alloc(&nn, (size_t)n_src, st));
     IBL_CUDA(ibl_alloc(&part, (size_t)nb * STEP_W, st));
-    std::vector<double> hp((size_t)nb * STEP_W);
+    IBL_CUDA(ibl_alloc(&dS, 1, st));
+    IcpState hS;
+    memset(&hS, 0, sizeof(hS));
+    memcpy(hS.T, T, sizeof(hS.T));
+    memcpy(hS.U, T, sizeof(hS.U));                         // step 0 moves the source by the initial transformation
+    hS.has_U = is_identity(T) ? 0 : 1;
+    IBL_CUDA(cudaMemcpyAsync(dS, &hS, sizeof(hS), cudaMemcpyHostToDevice, st));
     ColoredTerms terms{tgt, tnrm, tcol, tgrad, sqrt(lambda_geometric), sqrt(1.0 - lambda_geometric)};
     const GridView gv = ibl_view(tgt_grid);
-    ibl_score_t sc = {0, 0.0};
-    double v27[27];
-    auto step = [&](const double *in, const double *U16) -> int {
-        Mat16i U;
-        int has_U = U16 != nullptr && !is_identity(U16);
-        for (int k = 0; k < 16; ++k) U.v[k] = has_U ? U16[k] : ((k % 5 == 0) ? 1.0 : 0.0);
-        {
-            IBL_PROF(IBL_PROF_ICP_REDUCE, st, (double)n_src * (24.0 + 24.0 + 24.0 + 4.0 + 96.0) + 8.0 * STEP_W * nb);
-            colored_step_kernel<<<nb, 256, 0, st>>>(gv, in, pcd, scol, n_src, U, has_U, terms, max_d, max_d * max_d, nn, part);
-            IBL_LAUNCH_CHECK();
-        }
-        IBL_CUDA(cudaMemcpyAsync(hp.data(), part, sizeof(double) * hp.size(), cudaMemcpyDeviceToHost, st));
-        IBL_CUDA(cudaStreamSynchronize(st));
-        if (tgt_grid->n > 0) step_reduce_host(hp.data(), nb, &sc, v27);
+    auto launch = [&](const double *in) -> int {
+        IBL_PROF(IBL_PROF_ICP_REDUCE, st, (double)n_src * (24.0 + 24.0 + 24.0 + 4.0 + 96.0) + 8.0 * STEP_W * nb);
+        colored_step_kernel<<<nb, 256, 0, st>>>(gv, in, pcd, scol, n_src, dS, terms, max_d, max_d * max_d, nn, part, nb,
+                                                max_iteration, rel_fitness, rel_rmse);
+        IBL_LAUNCH_CHECK();
         return IBL_OK;
     };
-    int rc = step(src, T);
+    int rc = launch(src);                                  // step 0: score of the initial pose + first normal equations
     if (rc < 0) return rc;
-    double fit = (double)sc.n_inliers / (double)n_src;
-    double rmse = sc.n_inliers > 0 ? sqrt(sc.err2 / (double)sc.n_inliers) : 0.0;
-    int it = 0;
-    for (; it < max_iteration;) {
-        double upd[16];
-        solve_update_host(v27, upd);
-        matmul4(upd, T, T);
-        double pf = fit, pr = rmse;
-        if ((rc = step(pcd, upd)) < 0) return rc;
-        fit = (double)sc.n_inliers / (double)n_src;
-        rmse = sc.n_inliers > 0 ? sqrt(sc.err2 / (double)sc.n_inliers) : 0.0;
-        ++it;
-        if (fabs(pf - fit) < rel_fitness && fabs(pr - rmse) < rel_rmse) break;
+    int queued = 0;
+    for (;;) {
+        int batch = std::min(queued == 0 ? 7 : 8, max_iteration - queued);
+        for (int k = 0; k < batch; ++k) if ((rc = launch(pcd)) < 0) return rc;
+        queued += batch;
+        IBL_CUDA(cudaMemcpyAsync(&hS, dS, sizeof(hS), cudaMemcpyDeviceToHost, st));
+        IBL_CUDA(cudaStreamSynchronize(st));
+        if (hS.done || queued >= max_iteration) break;
     }
-    memcpy(h_result->T, T, sizeof(double) * 16);
-    h_result->fitness = fit; h_result->inlier_rmse = rmse;
-    h_result->n_inliers = sc.n_inliers; h_result->err2 = sc.err2; h_result->iterations = it;
-    ibl_free(pcd, st); ibl_free(nn, st); ibl_free(part, st);
+    memcpy(T, hS.T, sizeof(hS.T));
+    memcpy(h_result->T, hS.T, sizeof(double) * 16);
+    h_result->fitness = hS.fit; h_result->inlier_rmse = hS.rmse;
+    h_result->n_inliers = hS.n_inliers; h_result->err2 = hS.err2; h_result->iterations = hS.steps - 1;
+    ibl_free(pcd, st); ibl_free(nn, st); ibl_free(part, st); ibl_free(dS, st);
     return IBL_OK;
 }
 

@@ -4,7 +4,9 @@
 //   score  : grid (source tiles x hypotheses); thread per source point does an exact 1-NN within
 //            max_d on the target grid (ring field skips empty space); integer inlier counts and a
 //            fixed-order err2 reduction (warp shuffles -> CTA -> tile partials)
-//   run    : host loop applying the ordered best-update / adaptive-stop rule
+//   count  : same grid as score, inlier counts only (first candidate within max_d ends a point's scan)
+//   run    : host loop applying the ordered best-update / adaptive-stop rule; a chunk of validated hypotheses is
+//            counted first and only those whose count reaches the running maximum get the exact score
 #include <cub/cub.cuh>
 #include <vector>
 
@@ -129,6 +131,42 @@ __global__ void __launch_bounds__(SCORE_THREADS) ransac_score_kernel(GridView g,
     }
 }
 
+// Inlier COUNT only (same grid shape as ransac_score_kernel): "is any target within max_d" stops at the first candidate
+// that qualifies, where the exact score has to finish the minimum over the whole candidate list.  Integer partials are
+// added with atomicAdd (order-independent), so there is no finalize pass.  The counts equal ransac_score_kernel's.
+__global__ void __launch_bounds__(SCORE_THREADS) ransac_count_kernel(GridView g, const double *__restrict__ src, int64_t n_src,
+                                                                     const double *__restrict__ T_all, double max_d,
+                                                                     double max_d2, int32_t *__restrict__ inliers) {
+    __shared__ double T[16];
+    __shared__ int sc[SCORE_THREADS / 32];
+    int tile = blockIdx.x;
+    int64_t hyp = blockIdx.y;
+    if (threadIdx.x < 16) T[threadIdx.x] = T_all[16 * hyp + threadIdx.x];
+    __syncthreads();
+    int cnt = 0;
+    int64_t base = (int64_t)tile * SCORE_TILE;
+    const bool field = g.has_field && max_d <= g.f.max_d;
+#pragma unroll 1
+    for (int r = 0; r < SCORE_TILE / SCORE_THREADS; ++r) {
+        int64_t i = base + r * SCORE_THREADS + threadIdx.x;
+        if (i < n_src) {
+            double x, y, z, bd;
+            ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
+            if (field) cnt += ibl_any_within_field(g, x, y, z, max_d2) ? 1 : 0;
+            else cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
+        }
+    }
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int o = 16; o; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+    if (lane == 0) sc[w] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tc = 0;
+        for (int k = 0; k < SCORE_THREADS / 32; ++k) tc += sc[k];
+        if (tc) atomicAdd(&inliers[hyp], tc);
+    }
+}
+
 // one CTA per hypothesis: tile partials (fixed order: thread-strided, warp tree, warps in order) + the correspondence
 // inlier count (EvaluateInlierCorrespondenceRatio numerator).  The gathers are latency-bound, so a whole CTA per
 // hypothesis rather than a warp.
@@ -230,11 +268,13 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
     block = MAX_BLOCK;                     // buffers are sized for the largest block
     const int64_t SCORE_CHUNK = 512;
     uint8_t *pass = nullptr; int64_t *ids = nullptr; int *dcount = nullptr;
-    int32_t *inl = nullptr, *cinl = nullptr; double *err = nullptr, *Ts = nullptr;
+    int32_t *inl = nullptr, *inl2 = nullptr, *cinl = nullptr; double *err = nullptr, *Ts = nullptr; int64_t *sel_ids = nullptr;
     IBL_CUDA(ibl_alloc(&pass, (size_t)block, st));
     IBL_CUDA(ibl_alloc(&ids, (size_t)block, st));
     IBL_CUDA(ibl_alloc(&dcount, 1, st));
     IBL_CUDA(ibl_alloc(&inl, (size_t)SCORE_CHUNK, st));
+    IBL_CUDA(ibl_alloc(&inl2, (size_t)SCORE_CHUNK, st));
+    IBL_CUDA(ibl_alloc(&sel_ids, (size_t)SCORE_CHUNK, st));
     IBL_CUDA(ibl_alloc(&cinl, (size_t)SCORE_CHUNK, st));
     IBL_CUDA(ibl_alloc(&err, (size_t)SCORE_CHUNK, st));
     IBL_CUDA(ibl_alloc(&Ts, (size_t)SCORE_CHUNK * 16, st));
@@ -245,8 +285,8 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
     }
     void *tmp = nullptr;
     IBL_CUDA(cudaMallocAsync(&tmp, tb ? tb : 1, st));
-    std::vector<int64_t> h_ids(SCORE_CHUNK);
-    std::vector<int32_t> h_inl(SCORE_CHUNK), h_cinl(SCORE_CHUNK);
+    std::vector<int64_t> h_ids(SCORE_CHUNK), h_sel(SCORE_CHUNK), h_sel_ids(SCORE_CHUNK);
+    std::vector<int32_t> h_inl(SCORE_CHUNK), h_inl2(SCORE_CHUNK), h_cinl(SCORE_CHUNK);
     std::vector<double> h_err(SCORE_CHUNK), h_T(SCORE_CHUNK * 16);
     int64_t est_k = max_iteration;
     double best_fit = 0.0, best_rmse = 0.0;
@@ -264,27 +304,58 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
         bool stop = false;
         for (int64_t c0 = 0; c0 < npass && !stop; c0 += SCORE_CHUNK) {
             int64_t nc = std::min<int64_t>(SCORE_CHUNK, npass - c0);
-            if ((rc = ibl_ransac_score(tgt_grid, src, n_src, tgt, corres, n_corres, samples, seed, ids + c0, nc, max_d, inl, err,
-                                       cinl, Ts, stream)) < 0) { stop = true; break; }
+            // stage 1: inlier counts of the whole chunk (cheap: first candidate within max_d ends a point's scan)
+            hyp_transform_kernel<<<(unsigned)((nc + 63) / 64), 64, 0, st>>>(src, tgt, corres, n_corres, samples, seed, ids + c0, nc, Ts);
+            IBL_LAUNCH_CHECK();
+            IBL_CUDA(cudaMemsetAsync(inl, 0, sizeof(int32_t) * nc, st));
+            {
+                int ntiles = (int)((n_src + SCORE_TILE - 1) / SCORE_TILE);
+                dim3 grid(ntiles, (unsigned)nc);
+                IBL_PROF(IBL_PROF_RANSAC_SCORE, st, (double)nc * (24.0 * n_src + 128.0));
+                ransac_count_kernel<<<grid, SCORE_THREADS, 0, st>>>(ibl_view(tgt_grid), src, n_src, Ts, max_d, max_d * max_d, inl);
+                IBL_LAUNCH_CHECK();
+            }
             IBL_CUDA(cudaMemcpyAsync(h_ids.data(), ids + c0, sizeof(int64_t) * nc, cudaMemcpyDeviceToHost, st));
             IBL_CUDA(cudaMemcpyAsync(h_inl.data(), inl, sizeof(int32_t) * nc, cudaMemcpyDeviceToHost, st));
-            IBL_CUDA(cudaMemcpyAsync(h_cinl.data(), cinl, sizeof(int32_t) * nc, cudaMemcpyDeviceToHost, st));
-            IBL_CUDA(cudaMemcpyAsync(h_err.data(), err, sizeof(double) * nc, cudaMemcpyDeviceToHost, st));
-            IBL_CUDA(cudaMemcpyAsync(h_T.data(), Ts, sizeof(double) * 16 * nc, cudaMemcpyDeviceToHost, st));
             IBL_CUDA(cudaStreamSynchronize(st));
+            // A hypothesis can only replace the best if its count reaches the largest count seen before it (the ordered
+            // rule is "fitness greater, or equal with a smaller rmse"; after any hypothesis the best count is the
+            // running maximum).  Only those need the exact err2 / correspondence-inlier pass.
+            int64_t nsel = 0;
+            {
+                int64_t run_max = h_result->best_hyp >= 0 ? h_result->n_inliers : 0;
+                for (int64_t k = 0; k < nc; ++k) {
+                    h_sel[k] = -1;
+                    if (h_ids[k] >= est_k) break;
+                    if (h_inl[k] > 0 && h_inl[k] >= run_max) { h_sel[k] = nsel; h_sel_ids[nsel++] = h_ids[k]; run_max = h_inl[k]; }
+                }
+            }
+            if (nsel > 0) {                                // stage 2: exact score of the few contenders
+                IBL_CUDA(cudaMemcpyAsync(sel_ids, h_sel_ids.data(), sizeof(int64_t) * nsel, cudaMemcpyHostToDevice, st));
+                if ((rc = ibl_ransac_score(tgt_grid, src, n_src, tgt, corres, n_corres, samples, seed, sel_ids, nsel, max_d, inl2,
+                                           err, cinl, Ts, stream)) < 0) { stop = true; break; }
+                IBL_CUDA(cudaMemcpyAsync(h_inl2.data(), inl2, sizeof(int32_t) * nsel, cudaMemcpyDeviceToHost, st));
+                IBL_CUDA(cudaMemcpyAsync(h_cinl.data(), cinl, sizeof(int32_t) * nsel, cudaMemcpyDeviceToHost, st));
+                IBL_CUDA(cudaMemcpyAsync(h_err.data(), err, sizeof(double) * nsel, cudaMemcpyDeviceToHost, st));
+                IBL_CUDA(cudaMemcpyAsync(h_T.data(), Ts, sizeof(double) * 16 * nsel, cudaMemcpyDeviceToHost, st));
+                IBL_CUDA(cudaStreamSynchronize(st));
+            }
             for (int64_t k = 0; k < nc; ++k) {
                 if (h_ids[k] >= est_k) { stop = true; break; }
                 h_result->validated++;
-                double fit = (double)h_inl[k] / (double)n_src;
-                double rmse = h_inl[k] > 0 ? sqrt(h_err[k] / (double)h_inl[k]) : 0.0;
+                const int64_t j = h_sel[k];
+                if (j < 0) continue;                       // cannot beat the best: fewer inliers
+                if (h_inl2[j] != h_inl[k]) { ibl_set_error("ransac: count pass and exact pass disagree"); rc = IBL_E_CUDA; stop = true; break; }
+                double fit = (double)h_inl2[j] / (double)n_src;
+                double rmse = h_inl2[j] > 0 ? sqrt(h_err[j] / (double)h_inl2[j]) : 0.0;
                 if (fit > best_fit || (fit == best_fit && rmse < best_rmse)) {
                     best_fit = fit; best_rmse = rmse;
                     h_result->fitness = fit; h_result->inlier_rmse = rmse;
-                    h_result->n_inliers = h_inl[k]; h_result->err2 = h_err[k];
+                    h_result->n_inliers = h_inl2[j]; h_result->err2 = h_err[j];
                     h_result->best_hyp = h_ids[k];
-                    memcpy(h_result->T, &h_T[16 * k], sizeof(double) * 16);
+                    memcpy(h_result->T, &h_T[16 * j], sizeof(double) * 16);
                     if (early_exit) {
-                        double rho = (double)h_cinl[k] / (double)n_corres;
+                        double rho = (double)h_cinl[j] / (double)n_corres;
                         double den = rho < 1.0 ? log(1.0 - rho * rho * rho) : -INFINITY;
                         double kk = den == 0.0 ? INFINITY : log(1.0 - confidence) / den;
                         if (kk < (double)est_k) est_k = (int64_t)ceil(kk);
@@ -298,6 +369,6 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
     }
     h_result->drawn = std::min(max_iteration, std::max<int64_t>(est_k, 0));
     ibl_free(tmp, st); ibl_free(pass, st); ibl_free(ids, st); ibl_free(dcount, st);
-    ibl_free(inl, st); ibl_free(cinl, st); ibl_free(err, st); ibl_free(Ts, st);
+    ibl_free(inl, st); ibl_free(inl2, st); ibl_free(sel_ids, st); ibl_free(cinl, st); ibl_free(err, st); ibl_free(Ts, st);
     return rc;
 }

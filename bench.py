@@ -309,9 +309,9 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
-    ap.add_argument("--frames-per-step", type=int, default=8)
+    ap.add_argument("--frames-per-step", type=int, default=16)
     ap.add_argument("--workers", type=int, default=4, help="frames in flight per GPU (host threads / CUDA streams)")
-    ap.add_argument("--host-wait", default="auto", choices=["auto", "spin", "yield", "block"],
+    ap.add_argument("--host-wait", default="auto", choices=["auto", "spin", "yield", "block", "hybrid"],
                     help="how host threads wait in stream syncs (ibl_set_host_wait).  Measured at 8 GPUs / 32 cores: auto "
                          "(spin) 227-246 frames/s, yield 205, block 70 -- the path syncs hundreds of times per frame")
     ap.add_argument("--cpu-budget", type=float, default=25.0)

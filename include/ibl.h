@@ -212,7 +212,8 @@ int ibl_simvolume_topk(const float *S, int32_t nd, int32_t m, int32_t k, int64_t
 
 /* ---------------------------------------------------------------- host wait policy ----------- */
 /* How host threads wait inside this library's (and the process's) stream synchronisations on the current device:
- * 0 = driver default (spins when cores outnumber contexts), 1 = spin, 2 = yield, 3 = blocking (sleep on an interrupt).
+ * 0 = driver default (spins when cores outnumber contexts), 1 = spin, 2 = yield, 3 = blocking (sleep on an interrupt),
+ * 4 = hybrid (this library's waits poll for ~60 us, then sleep in 20-50 us steps; everything else as 0).
  * The path synchronises a few hundred times per frame (data-dependent sizes, the RANSAC and ICP host rules), so with
  * several frames in flight spinning costs > 2 cores per GPU.  Measured on an 8 x B200 box with 32 cores (DESIGN.md
  * section 5): blocking waits cost 3.4x in frames/s, yield 1.15x -- spin (the default) stays the right choice there; the

@@ -128,7 +128,7 @@ static int backproject_impl(const DT *depth, const uint8_t *rgb, const uint8_t *
     // per-mask offsets = offs[mi*ntiles]
     int64_t *hall = (int64_t *)malloc(sizeof(int64_t) * (nc + 1));
     IBL_CUDA(cudaMemcpyAsync(hall, offs, sizeof(int64_t) * (nc + 1), cudaMemcpyDeviceToHost, st));
-    IBL_CUDA(cudaStreamSynchronize(st));
+    IBL_CUDA(ibl_sync(st));
     for (int i = 0; i <= n_masks; ++i) h_offsets[i] = hall[(size_t)i * ntiles];
     free(hall);
     ibl_free(tmp, st); ibl_free(counts, st); ibl_free(offs, st);
@@ -188,7 +188,7 @@ IBL_API int64_t ibl_select_rows(const uint8_t *keep, int64_t n, const double *a,
     int last_pos = 0; uint8_t last_keep = 0;
     IBL_CUDA(cudaMemcpyAsync(&last_pos, pos + (n - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
     IBL_CUDA(cudaMemcpyAsync(&last_keep, keep + (n - 1), 1, cudaMemcpyDeviceToHost, st));
-    IBL_CUDA(cudaStreamSynchronize(st));
+    IBL_CUDA(ibl_sync(st));
     ibl_free(tmp, st); ibl_free(pos, st);
     return (int64_t)last_pos + (last_keep ? 1 : 0);
 }
@@ -266,7 +266,7 @@ IBL_API int ibl_mean3(const double *pts, int64_t n, double *h_mean, void *stream
     }
     double hs[3];
     IBL_CUDA(cudaMemcpyAsync(hs, d, sizeof(hs), cudaMemcpyDeviceToHost, st));
-    IBL_CUDA(cudaStreamSynchronize(st));
+    IBL_CUDA(ibl_sync(st));
     ibl_free(d, st);
     for (int a = 0; a < 3; ++a) h_mean[a] = hs[a] / (double)n;
     return IBL_OK;

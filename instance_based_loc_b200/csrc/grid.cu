@@ -66,7 +66,7 @@ IBL_API int ibl_grid_create(const double *pts, int64_t n, double cell, int64_t m
         IBL_LAUNCH_CHECK();
         double *hp = (double *)malloc(sizeof(double) * nb * 6);
         IBL_CUDA(cudaMemcpyAsync(hp, part, sizeof(double) * nb * 6, cudaMemcpyDeviceToHost, st));
-        IBL_CUDA(cudaStreamSynchronize(st));
+        IBL_CUDA(ibl_sync(st));
         for (int a = 0; a < 3; ++a) { mn[a] = INFINITY; mx[a] = -INFINITY; }
         for (int b = 0; b < nb; ++b)
             for (int a = 0; a < 3; ++a) { mn[a] = fmin(mn[a], hp[b * 6 + a]); mx[a] = fmax(mx[a], hp[b * 6 + 3 + a]); }
@@ -150,7 +150,7 @@ IBL_API int64_t ibl_grid_occupied(const ibl_grid_t *gc) {
     count_occupied_kernel<<<(unsigned)nbc, 256, 0, st>>>(g->cell_start, g->ncells, occ);
     __sync_fetch_and_add(&g_ibl_launches, 1ull);
     cudaMemcpyAsync(&hocc, occ, 8, cudaMemcpyDeviceToHost, st);
-    cudaStreamSynchronize(st);
+    ibl_sync(st);
     ibl_free(occ, st);
     g->n_occupied = (int64_t)hocc;
     return g->n_occupied;

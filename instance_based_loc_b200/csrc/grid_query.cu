@@ -19,17 +19,32 @@ __global__ void __launch_bounds__(256) radius_count_kernel(GridView g, int64_t n
         int x0 = max(cx - S, 0), x1 = min(cx + S, g.nx - 1);
         int y0 = max(cy - S, 0), y1 = min(cy + S, g.ny - 1);
         int z0 = max(cz - S, 0), z1 = min(cz + S, g.nz - 1);
+        // The count is warp-uniform (ballot + popc per batch of 32 candidates).  When only the keep mask is wanted the scan
+        // stops as soon as the count exceeds nb_points -- with ~140 neighbours inside the radius and nb_points = 8 that is
+        // after the first row or two, so rows are visited centre first (dz, dy = 0, -1, +1, -2, +2, ...).
         int c = 0;
-        for (int z = z0; z <= z1; ++z)
-            for (int y = y0; y <= y1; ++y) {
+        const bool early = (count == nullptr);
+        bool done = false;
+        for (int kz = 0; kz <= 2 * S && !done; ++kz) {
+            int z = cz + ((kz & 1) ? -((kz + 1) >> 1) : (kz >> 1));
+            if (z < z0 || z > z1) continue;
+            for (int ky = 0; ky <= 2 * S && !done; ++ky) {
+                int y = cy + ((ky & 1) ? -((ky + 1) >> 1) : (ky >> 1));
+                if (y < y0 || y > y1) continue;
                 size_t rb = ((size_t)z * g.ny + y) * g.nx;
                 int p0 = g.cell_start[rb + x0], p1 = g.cell_start[rb + x1 + 1];
-                for (int p = p0 + lane; p < p1; p += 32) {
-                    double4 t = g.sorted[p];
-                    c += ibl_d2(t.x, t.y, t.z, q.x, q.y, q.z) < r2;
+                for (int pb = p0; pb < p1; pb += 32) {
+                    int p = pb + lane;
+                    bool in = false;
+                    if (p < p1) {
+                        double4 t = g.sorted[p];
+                        in = ibl_d2(t.x, t.y, t.z, q.x, q.y, q.z) < r2;
+                    }
+                    c += __popc(__ballot_sync(0xffffffffu, in));
+                    if (early && c > nb_points) { done = true; break; }
                 }
             }
-        for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        }
         if (lane == 0) {
             int oi = (int)__double_as_longlong(q.w);
             if (count) count[oi] = c;
@@ -93,19 +108,39 @@ __device__ __forceinline__ int next_pow2_ge32(int c) {
     return n2;
 }
 
+// Two passes per query (one warp each).
+//   pass 1 : Chebyshev ring expansion that only COUNTS: every candidate within the radius goes into a histogram of d2
+//            (bins of width cell/16 in distance).  After ring s every point closer than s*cell has been seen, so as soon as the bins
+//            below that bound hold max_nn points the search stops, and the first bin j* whose cumulative count reaches
+//            max_nn is a distance bound that provably contains the max_nn nearest (and every tie with the last one).
+//   pass 2 : the same cells again as whole x-rows of the cube; only candidates in bins <= j* are stored -- about
+//            max_nn + one bin's population instead of everything inside the cube -- then ONE warp bitonic sort on
+//            (d2 bits, index) gives the oracle's ascending (d2, index) order.
+// The histogram replaces the sort-and-compact rounds the one-pass version needed (its buffer held the whole cube, ~3x
+// max_nn on a surface, and the sorts were ~85 % of the instructions).  If the stored set still overflows the buffer
+// (duplicates, a degenerate bin) the old compaction -- sort, keep the best max_nn, remember the threshold -- takes over.
+#define KNN_NB 128
+// histogram bin of a squared distance: float arithmetic is enough -- the only properties used are that the map is monotone
+// non-decreasing in d2 (conversion, correctly rounded sqrt, multiplication by a positive constant and truncation all are)
+// and that both passes use the same map
+__device__ __forceinline__ int knn_bin(double d2, float inv_w) {
+    return (int)fminf(__fmul_rn(__fsqrt_rn((float)d2), inv_w), (float)(KNN_NB - 1));
+}
 template <int CAP>
 __global__ void __launch_bounds__(128) knn_kernel(GridView g, const double *__restrict__ queries, int64_t nq,
                                                   double radius, double r2, int max_nn, int32_t *__restrict__ idx,
                                                   double *__restrict__ d2out, int32_t *__restrict__ cnt) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
     KnnBuf b;
     b.key = reinterpret_cast<unsigned long long *>(smem_raw) + (size_t)wib * CAP;
-    b.val = reinterpret_cast<int *>(smem_raw + sizeof(unsigned long long) * CAP * (blockDim.x >> 5)) + (size_t)wib * CAP;
+    b.val = reinterpret_cast<int *>(smem_raw + sizeof(unsigned long long) * CAP * wpb) + (size_t)wib * CAP;
+    int *hist = reinterpret_cast<int *>(smem_raw + (sizeof(unsigned long long) + sizeof(int)) * CAP * wpb) + (size_t)wib * KNN_NB;
     int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
-    int s_rad = isfinite(radius) ? (int)ceil(radius * g.inv_cell + 1e-6) : 0x3fffffff;
+    const int s_rad = isfinite(radius) ? (int)ceil(radius * g.inv_cell + 1e-6) : 0x3fffffff;
+    const float inv_w = (float)(16.0 * g.inv_cell);       // bins of width cell/16 in DISTANCE: 128 bins reach 8 cells
     for (int64_t qi = warp; qi < nq; qi += nwarps) {
         double qx, qy, qz;
         int64_t row;
@@ -117,19 +152,18 @@ __global__ void __launch_bounds__(128) knn_kernel(GridView g, const double *__re
             qx = queries[3 * qi]; qy = queries[3 * qi + 1]; qz = queries[3 * qi + 2];
             row = qi;
         }
-        int cx = ibl_cell_coord(qx, g.ox, g.inv_cell, g.nx);
-        int cy = ibl_cell_coord(qy, g.oy, g.inv_cell, g.ny);
-        int cz = ibl_cell_coord(qz, g.oz, g.inv_cell, g.nz);
-        int count = 0;
-        bool have_tau = false;
-        unsigned long long tau_k = ~0ull;
-        int tau_v = 0x7fffffff;
-        // rings needed to reach the grid box from an outside query
-        int s_begin;
+        const int cx = ibl_cell_coord(qx, g.ox, g.inv_cell, g.nx);
+        const int cy = ibl_cell_coord(qy, g.oy, g.inv_cell, g.ny);
+        const int cz = ibl_cell_coord(qz, g.oz, g.inv_cell, g.nz);
+        int s_begin;                                       // rings needed to reach the grid box from an outside query
         {
             int kx = ibl_clampi(cx, 0, g.nx - 1), ky = ibl_clampi(cy, 0, g.ny - 1), kz = ibl_clampi(cz, 0, g.nz - 1);
             s_begin = max(max(abs(cx - kx), abs(cy - ky)), abs(cz - kz));
         }
+        // ---------------- pass 1: count ----------------
+        for (int t = lane; t < KNN_NB; t += 32) hist[t] = 0;
+        __syncwarp();
+        int s_end = s_begin, jstar = KNN_NB;               // jstar == KNN_NB: no bin bound (the radius / the whole grid decides)
         for (int s = s_begin;; ++s) {
             int z0 = max(cz - s, 0), z1 = min(cz + s, g.nz - 1);
             int y0 = max(cy - s, 0), y1 = min(cy + s, g.ny - 1);
@@ -147,55 +181,91 @@ __global__ void __launch_bounds__(128) knn_kernel(GridView g, const double *__re
                         xa = max(xa, 0); xb = min(xb, g.nx - 1);
                         if (xa > xb) continue;
                         int p0 = g.cell_start[rb + xa], p1 = g.cell_start[rb + xb + 1];
-                        for (int pb = p0; pb < p1; pb += 32) {
-                            if (count + 32 > CAP) {   // compact: keep the max_nn best, remember threshold
-                                int n2 = next_pow2_ge32(count);
-                                for (int t = count + lane; t < n2; t += 32) { b.key[t] = ~0ull; b.val[t] = 0x7fffffff; }
-                                __syncwarp();
-                                knn_sort(b, n2, lane);
-                                if (count >= max_nn) {
-                                    count = max_nn;
-                                    have_tau = true;
-                                    tau_k = b.key[max_nn - 1];
-                                    tau_v = b.val[max_nn - 1];
-                                }
-                                __syncwarp();
-                            }
-                            int p = pb + lane;
-                            bool ok = false;
-                            unsigned long long kk = 0;
-                            int vv = 0;
-                            if (p < p1) {
-                                double4 t = g.sorted[p];
-                                double d2 = ibl_d2(t.x, t.y, t.z, qx, qy, qz);
-                                kk = (unsigned long long)__double_as_longlong(d2);
-                                vv = (int)__double_as_longlong(t.w);
-                                ok = d2 < r2 && (!have_tau || knn_less(kk, vv, tau_k, tau_v));
-                            }
-                            unsigned m = __ballot_sync(0xffffffffu, ok);
-                            if (ok) {
-                                int pos = count + __popc(m & lt_mask);
-                                b.key[pos] = kk;
-                                b.val[pos] = vv;
-                            }
-                            count += __popc(m);
-                            __syncwarp();
+                        for (int p = p0 + lane; p < p1; p += 32) {
+                            double4 t = g.sorted[p];
+                            double d2 = ibl_d2(t.x, t.y, t.z, qx, qy, qz);
+                            if (d2 < r2) atomicAdd(&hist[knn_bin(d2, inv_w)], 1);
                         }
                     }
                 }
             }
-            // termination tests
+            __syncwarp();
+            s_end = s;
             bool covers = (cx - s <= 0) && (cx + s >= g.nx - 1) && (cy - s <= 0) && (cy + s >= g.ny - 1) &&
                           (cz - s <= 0) && (cz + s >= g.nz - 1);
             if (covers || s >= s_rad) break;
-            if (count >= max_nn) {
-                double gr = ((double)s - 1e-6) * g.cell;
-                if (gr > 0) {
-                    unsigned long long gk = (unsigned long long)__double_as_longlong(gr * gr);
-                    int inside = 0;
-                    for (int t = lane; t < count; t += 32) inside += b.key[t] <= gk;
-                    for (int o = 16; o; o >>= 1) inside += __shfl_xor_sync(0xffffffffu, inside, o);
-                    if (inside >= max_nn) break;
+            double gr = ((double)s - 1e-6) * g.cell;       // every point closer than this has been seen
+            if (gr > 0) {
+                // knn_bin is monotone in d2, so every candidate in a bin below knn_bin(gr^2) is closer than gr (the last bin
+                // is open-ended and is never below anything)
+                int jm = knn_bin(gr * gr, inv_w) - 1;
+                if (jm >= 0) {
+                    int h0 = 4 * lane <= jm ? hist[4 * lane] : 0, h1 = 4 * lane + 1 <= jm ? hist[4 * lane + 1] : 0;
+                    int h2 = 4 * lane + 2 <= jm ? hist[4 * lane + 2] : 0, h3 = 4 * lane + 3 <= jm ? hist[4 * lane + 3] : 0;
+                    int own = h0 + h1 + h2 + h3, incl = own;
+                    for (int o = 1; o < 32; o <<= 1) { int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+                    int total = __shfl_sync(0xffffffffu, incl, 31);
+                    if (total >= max_nn) {
+                        int before = incl - own;
+                        unsigned m = __ballot_sync(0xffffffffu, before < max_nn && incl >= max_nn);
+                        int src_lane = __ffs(m) - 1;
+                        int j = 4 * lane;
+                        if (before + h0 < max_nn) { j = 4 * lane + 1; if (before + h0 + h1 < max_nn) { j = 4 * lane + 2; if (before + h0 + h1 + h2 < max_nn) j = 4 * lane + 3; } }
+                        jstar = __shfl_sync(0xffffffffu, j, src_lane);
+                        break;
+                    }
+                }
+            }
+        }
+        // ---------------- pass 2: store the candidates of bins <= jstar, whole x-rows of the cube ----------------
+        int count = 0;
+        bool have_tau = false;
+        unsigned long long tau_k = ~0ull;
+        int tau_v = 0x7fffffff;
+        {
+            const int s = s_end;
+            int z0 = max(cz - s, 0), z1 = min(cz + s, g.nz - 1);
+            int y0 = max(cy - s, 0), y1 = min(cy + s, g.ny - 1);
+            int xa = max(cx - s, 0), xb = min(cx + s, g.nx - 1);
+            for (int z = z0; z <= z1 && xa <= xb; ++z) {
+                for (int y = y0; y <= y1; ++y) {
+                    size_t rb = ((size_t)z * g.ny + y) * g.nx;
+                    int p0 = g.cell_start[rb + xa], p1 = g.cell_start[rb + xb + 1];
+                    for (int pb = p0; pb < p1; pb += 32) {
+                        if (count + 32 > CAP) {   // overflow: keep the max_nn best, remember the threshold
+                            int n2 = next_pow2_ge32(count);
+                            for (int t = count + lane; t < n2; t += 32) { b.key[t] = ~0ull; b.val[t] = 0x7fffffff; }
+                            __syncwarp();
+                            knn_sort(b, n2, lane);
+                            if (count >= max_nn) {
+                                count = max_nn;
+                                have_tau = true;
+                                tau_k = b.key[max_nn - 1];
+                                tau_v = b.val[max_nn - 1];
+                            }
+                            __syncwarp();
+                        }
+                        int p = pb + lane;
+                        bool ok = false;
+                        unsigned long long kk = 0;
+                        int vv = 0;
+                        if (p < p1) {
+                            double4 t = g.sorted[p];
+                            double d2 = ibl_d2(t.x, t.y, t.z, qx, qy, qz);
+                            kk = (unsigned long long)__double_as_longlong(d2);
+                            vv = (int)__double_as_longlong(t.w);
+                            ok = d2 < r2 && knn_bin(d2, inv_w) <= jstar &&
+                                 (!have_tau || knn_less(kk, vv, tau_k, tau_v));
+                        }
+                        unsigned m = __ballot_sync(0xffffffffu, ok);
+                        if (ok) {
+                            int pos = count + __popc(m & lt_mask);
+                            b.key[pos] = kk;
+                            b.val[pos] = vv;
+                        }
+                        count += __popc(m);
+                        __syncwarp();
+                    }
                 }
             }
         }
@@ -228,11 +298,11 @@ IBL_API int ibl_knn_hybrid(const ibl_grid_t *g, const double *queries, int64_t n
     IBL_PROF(IBL_PROF_KNN, st, (double)nq * (32.0 + 4.0 + max_nn * (d2 ? 12.0 : 4.0)));
     if (max_nn <= 96) {
         constexpr int CAP = 256;
-        size_t sm = (size_t)wpb * CAP * 12;
+        size_t sm = (size_t)wpb * (CAP * 12 + KNN_NB * 4);
         knn_kernel<CAP><<<blocks, threads, sm, st>>>(ibl_view(g), queries, nq, radius, r2, max_nn, idx, d2, cnt);
     } else {
         constexpr int CAP = 512;
-        size_t sm = (size_t)wpb * CAP * 12;
+        size_t sm = (size_t)wpb * (CAP * 12 + KNN_NB * 4);
         knn_kernel<CAP><<<blocks, threads, sm, st>>>(ibl_view(g), queries, nq, radius, r2, max_nn, idx, d2, cnt);
     }
     IBL_LAUNCH_CHECK();
@@ -306,7 +376,7 @@ IBL_API int ibl_nn_score(const ibl_grid_t *g, const double *src, int64_t n, cons
         IBL_LAUNCH_CHECK();
         if (h_result) {
             IBL_CUDA(cudaMemcpyAsync(&res, dres, sizeof(res), cudaMemcpyDeviceToHost, st));
-            IBL_CUDA(cudaStreamSynchronize(st));
+            IBL_CUDA(ibl_sync(st));
         }
         ibl_free(pc, st); ibl_free(pe, st); ibl_free(dres, st);
     } else if (n > 0 && nn_idx) {

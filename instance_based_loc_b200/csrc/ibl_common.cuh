@@ -32,6 +32,7 @@ void ibl_set_error(const char *fmt, ...);
     } while (0)
 
 extern unsigned long long g_ibl_launches;
+cudaError_t ibl_sync(cudaStream_t st);   // host wait on a stream under the ibl_set_host_wait policy (prof.cu)
 #define IBL_LAUNCH_CHECK()                              \
     do {                                                \
         __sync_fetch_and_add(&g_ibl_launches, 1ull);    \

@@ -54,7 +54,7 @@ static int reduceK(int64_t n, F f, double *h_out, cudaStream_t st) {
     }
     std::vector<double> hp((size_t)nb * K);
     IBL_CUDA(cudaMemcpyAsync(hp.data(), part, sizeof(double) * nb * K, cudaMemcpyDeviceToHost, st));
-    IBL_CUDA(cudaStreamSynchronize(st));
+    IBL_CUDA(ibl_sync(st));
     ibl_free(part, st);
     for (int b = 0; b < nb; ++b)
         for (int k = 0; k < K; ++k) h_out[k] += hp[(size_t)b * K + k];
@@ -414,7 +414,7 @@ static int icp_colored_fused(const ibl_grid_t *tgt_grid, const double *src, cons
         for (int k = 0; k < batch; ++k) if ((rc = launch(pcd)) < 0) return rc;
         queued += batch;
         IBL_CUDA(cudaMemcpyAsync(&hS, dS, sizeof(hS), cudaMemcpyDeviceToHost, st));
-        IBL_CUDA(cudaStreamSynchronize(st));
+        IBL_CUDA(ibl_sync(st));
         if (hS.done || queued >= max_iteration) break;
     }
     memcpy(T, hS.T, sizeof(hS.T));

@@ -56,7 +56,7 @@ IBL_API int64_t ibl_mutual_corres(const int32_t *ij, int64_t ns, const int32_t *
     IBL_CUDA(cub::DeviceSelect::Flagged(tmp, tb, cit, flag, sel, dcount, (int)ns, st));
     int c = 0;
     IBL_CUDA(cudaMemcpyAsync(&c, dcount, sizeof(int), cudaMemcpyDeviceToHost, st));
-    IBL_CUDA(cudaStreamSynchronize(st));
+    IBL_CUDA(ibl_sync(st));
     int64_t out_c;
     if (c >= ransac_n * 3) {
         corres_fill_kernel<<<(c + 255) / 256, 256, 0, st>>>(sel, c, ij, corres);

@@ -680,13 +680,13 @@ IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double 
     if (center_out) {                                     // debug hook only: read the scale back and publish it
         unsigned bits = 0;
         IBL_CUDA(cudaMemcpyAsync(&bits, mx + 2, sizeof(bits), cudaMemcpyDeviceToHost, st));
-        IBL_CUDA(cudaStreamSynchronize(st));
+        IBL_CUDA(ibl_sync(st));
         float m;
         memcpy(&m, &bits, sizeof(m));
         double sc = 1.0;
         if (m > 0.f && std::isfinite(m)) { int x; frexp((double)m, &x); sc = ldexp(1.0, 10 - x); }
         IBL_CUDA(cudaMemcpyAsync(center_out + 33, &sc, sizeof(sc), cudaMemcpyHostToDevice, st));
-        IBL_CUDA(cudaStreamSynchronize(st));
+        IBL_CUDA(ibl_sync(st));
     } else {
         ibl_free(mu, st);
     }

@@ -137,7 +137,7 @@ IBL_API int ibl_grid_build_nnfield(ibl_grid_t *g, double max_d, double voxel, vo
     IBL_LAUNCH_CHECK();
     int nactive = 0;
     IBL_CUDA(cudaMemcpyAsync(&nactive, scan + nb, sizeof(int), cudaMemcpyDeviceToHost, st));
-    IBL_CUDA(cudaStreamSynchronize(st));
+    IBL_CUDA(ibl_sync(st));
     ibl_free(tmp, st); ibl_free(flag, st); ibl_free(scan, st);
     int64_t nv = (int64_t)nactive * 512;
     if (nv >= (1ll << 31)) { nf_free(g); ibl_set_error("nnfield: too many active voxels"); return IBL_E_RANGE; }
@@ -164,7 +164,7 @@ IBL_API int ibl_grid_build_nnfield(ibl_grid_t *g, double max_d, double voxel, vo
     IBL_LAUNCH_CHECK();
     unsigned int total = 0;
     IBL_CUDA(cudaMemcpyAsync(&total, start + nv, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
-    IBL_CUDA(cudaStreamSynchronize(st));
+    IBL_CUDA(ibl_sync(st));
     ibl_free(tmp, st);
     if (total >= (1u << 31)) { ibl_free(dmin2, st); ibl_free(cnt, st); ibl_free(start, st); nf_free(g); ibl_set_error("nnfield: too many candidates"); return IBL_E_RANGE; }
     IBL_CUDA(ibl_alloc(&g->f_cand, (size_t)total, st));

@@ -1,6 +1,9 @@
 // prof.cu -- launch counter and optional per-kernel CUDA-event timing (bench.py's roofline object is measured
 // live with these events on the launching stream; see include/ibl.h "instrumentation").
 #include <mutex>
+#include <stdlib.h>
+#include <sys/prctl.h>
+#include <time.h>
 #include <vector>
 
 #include "ibl_common.cuh"
@@ -38,11 +41,36 @@ void ibl_prof_end(int slot, cudaStream_t st) {
     if (slot < (int)g_recs.size()) cudaEventRecord(g_recs[slot].e1, st);
 }
 
+// mode 4 ("hybrid"): this library's own stream waits poll cudaStreamQuery for g_spin_us microseconds -- the ICP / RANSAC
+// round trips are 20-40 us, so they still complete at spin latency -- and then sleep in short steps, so the long waits
+// (feature matching, k-NN: 0.3-2 ms) stop burning a core each.
+static int g_hybrid = 0;
+static int g_spin_us = 60;
+cudaError_t ibl_sync(cudaStream_t st) {
+    if (!g_hybrid) return cudaStreamSynchronize(st);
+    timespec t0, t;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    for (;;) {
+        cudaError_t e = cudaStreamQuery(st);
+        if (e != cudaErrorNotReady) return e;
+        clock_gettime(CLOCK_MONOTONIC, &t);
+        long us = (t.tv_sec - t0.tv_sec) * 1000000L + (t.tv_nsec - t0.tv_nsec) / 1000L;
+        if (us < g_spin_us) { __builtin_ia32_pause(); continue; }
+        timespec nap = {0, us < 400 ? 20000L : 50000L};
+        nanosleep(&nap, nullptr);
+    }
+}
+
 IBL_API int ibl_set_host_wait(int mode) {
-    IBL_ARG(mode >= 0 && mode <= 3);
-    static const unsigned flags[4] = {cudaDeviceScheduleAuto, cudaDeviceScheduleSpin, cudaDeviceScheduleYield,
-                                      cudaDeviceScheduleBlockingSync};
+    IBL_ARG(mode >= 0 && mode <= 4);
+    static const unsigned flags[5] = {cudaDeviceScheduleAuto, cudaDeviceScheduleSpin, cudaDeviceScheduleYield,
+                                      cudaDeviceScheduleBlockingSync, cudaDeviceScheduleAuto};
     IBL_CUDA(cudaSetDeviceFlags(flags[mode]));
+    g_hybrid = mode == 4;
+    if (g_hybrid) {
+        prctl(PR_SET_TIMERSLACK, 1000UL, 0, 0, 0);          // this thread; worker threads set theirs on their first wait
+        if (const char *e = getenv("IBL_WAIT_SPIN_US")) g_spin_us = atoi(e);
+    }
     return IBL_OK;
 }
 

@@ -300,7 +300,7 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
         IBL_CUDA(cub::DeviceSelect::Flagged(tmp, tb, cit, pass, ids, dcount, (int)H, st));
         int npass = 0;
         IBL_CUDA(cudaMemcpyAsync(&npass, dcount, sizeof(int), cudaMemcpyDeviceToHost, st));
-        IBL_CUDA(cudaStreamSynchronize(st));
+        IBL_CUDA(ibl_sync(st));
         bool stop = false;
         for (int64_t c0 = 0; c0 < npass && !stop; c0 += SCORE_CHUNK) {
             int64_t nc = std::min<int64_t>(SCORE_CHUNK, npass - c0);
@@ -317,7 +317,7 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
             }
             IBL_CUDA(cudaMemcpyAsync(h_ids.data(), ids + c0, sizeof(int64_t) * nc, cudaMemcpyDeviceToHost, st));
             IBL_CUDA(cudaMemcpyAsync(h_inl.data(), inl, sizeof(int32_t) * nc, cudaMemcpyDeviceToHost, st));
-            IBL_CUDA(cudaStreamSynchronize(st));
+            IBL_CUDA(ibl_sync(st));
             // A hypothesis can only replace the best if its count reaches the largest count seen before it (the ordered
             // rule is "fitness greater, or equal with a smaller rmse"; after any hypothesis the best count is the
             // running maximum).  Only those need the exact err2 / correspondence-inlier pass.
@@ -338,7 +338,7 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
                 IBL_CUDA(cudaMemcpyAsync(h_cinl.data(), cinl, sizeof(int32_t) * nsel, cudaMemcpyDeviceToHost, st));
                 IBL_CUDA(cudaMemcpyAsync(h_err.data(), err, sizeof(double) * nsel, cudaMemcpyDeviceToHost, st));
                 IBL_CUDA(cudaMemcpyAsync(h_T.data(), Ts, sizeof(double) * 16 * nsel, cudaMemcpyDeviceToHost, st));
-                IBL_CUDA(cudaStreamSynchronize(st));
+                IBL_CUDA(ibl_sync(st));
             }
             for (int64_t k = 0; k < nc; ++k) {
                 if (h_ids[k] >= est_k) { stop = true; break; }

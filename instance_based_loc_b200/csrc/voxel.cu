@@ -87,7 +87,7 @@ IBL_API int64_t ibl_voxel_downsample(const double *pts, const double *cols, cons
     IBL_LAUNCH_CHECK();
     double *hp = (double *)malloc(sizeof(double) * nbb * 6);
     IBL_CUDA(cudaMemcpyAsync(hp, part, sizeof(double) * nbb * 6, cudaMemcpyDeviceToHost, st));
-    IBL_CUDA(cudaStreamSynchronize(st));
+    IBL_CUDA(ibl_sync(st));
     double mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (int b = 0; b < nbb; ++b)
         for (int a = 0; a < 3; ++a) { mn[a] = fmin(mn[a], hp[b * 6 + a]); mx[a] = fmax(mx[a], hp[b * 6 + 3 + a]); }
@@ -139,7 +139,7 @@ IBL_API int64_t ibl_voxel_downsample(const double *pts, const double *cols, cons
     IBL_CUDA(cub::DeviceSelect::Flagged(tmp, tb2, cit, flag, head_pos, d_nseg, (int)n, st));
     int nseg = 0;
     IBL_CUDA(cudaMemcpyAsync(&nseg, d_nseg, sizeof(int), cudaMemcpyDeviceToHost, st));
-    IBL_CUDA(cudaStreamSynchronize(st));
+    IBL_CUDA(ibl_sync(st));
     IBL_CUDA(ibl_alloc(&first_idx, (size_t)nseg, st)); IBL_CUDA(ibl_alloc(&first2, (size_t)nseg, st));
     IBL_CUDA(ibl_alloc(&seg, (size_t)nseg, st)); IBL_CUDA(ibl_alloc(&seg2, (size_t)nseg, st));
     int nbs = (nseg + 255) / 256;

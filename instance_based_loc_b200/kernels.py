@@ -163,9 +163,10 @@ def surface_spacing(pts, probe_cell):
 
 
 # cell = knn_cell_factor * R_k, R_k = radius holding k points of a surface.  The ring search stops at the first ring s with
-# s * cell >= R_k, having gathered the surface inside a cube of half-side (s + 1/2) * cell: a smaller factor means fewer
-# surplus candidates to sort (the dominant cost) against more, emptier cell rows to walk.  IBL_KNN_CELL_FACTOR overrides.
-knn_cell_factor = float(os.environ.get("IBL_KNN_CELL_FACTOR", "0.34"))   # measured on B200 (tools/knn_probe.py): 0.6 -> 1.88 ms, 0.34 -> 1.53 ms at k=100
+# s * cell >= R_k.  With the two-pass kernel (distance histogram, then store only the bins that matter) the sort no longer
+# depends on the cube size, so the balance is cell rows to walk (small cells) against candidates to measure (large cells).
+# IBL_KNN_CELL_FACTOR overrides.
+knn_cell_factor = float(os.environ.get("IBL_KNN_CELL_FACTOR", "0.9"))   # measured on B200 (tools/knn_probe.py, detected clouds of the bench): 0.8-1.0 best
 
 
 def knn_cell_from_spacing(spacing, k, radius):
@@ -357,7 +358,7 @@ def simvolume_topk(S, k):
 
 
 # ------------------------------------------------------------------------------- host wait policy
-HOST_WAIT = {"auto": 0, "spin": 1, "yield": 2, "block": 3}
+HOST_WAIT = {"auto": 0, "spin": 1, "yield": 2, "block": 3, "hybrid": 4}
 
 
 def set_host_wait(mode):

@@ -227,7 +227,9 @@ class PointCloud:
             raise RuntimeError("Illegal input parameters, number of points and radius must be positive")
         if self.is_empty():
             return PointCloud(), []
-        keep = K.radius_outlier_mask(self.grid(radius), radius, nb_points)
+        # cell a hair larger than the radius: the search then needs 1 ring of cells (3^3) instead of the 2 rings (5^3) that
+        # cell == radius costs once the cell-coordinate rounding guard is added (radius_launch's S)
+        keep = K.radius_outlier_mask(self.grid(radius * 1.001), radius, nb_points)
         out, oi = self._select_mask(keep, want_index=True)
         return out, DeviceVec(oi)
 

@@ -2,6 +2,8 @@
 
   python tools/ncu_summary.py launches gpurun_out/launches.csv "header text"      per-kernel time table of a launch list
   python tools/ncu_summary.py full gpurun_out/full_X.ncu-rep [...]                key metrics of --set full captures
+  python tools/ncu_summary.py traffic TAG=gpurun_out/full_X.ncu-rep [...]         profiles/ncu_traffic.json: DRAM bytes per
+                                                                                  launch of a kernel group (bench.py roofline.traffic)
 """
 from __future__ import annotations
 
@@ -70,8 +72,42 @@ def full(paths):
                     print(f"    {m:78s} {r[i]:>16s} {units[i]}")
 
 
+def _bytes(v, unit):
+    v = float(v.replace(",", ""))
+    return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
+
+
+def traffic(specs):
+    """TAG=file.ncu-rep: the capture holds the kernels of ONE launch of the kernel group TAG (e.g. the 8 kernels of one
+    ibl_feature_nn call, or one ransac_score_kernel launch); traffic = sum of dram read + write bytes over them."""
+    import json
+    import os
+    out = {}
+    for spec in specs:
+        tag, path = spec.split("=", 1)
+        txt = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        rows = list(csv.reader(io.StringIO(txt)))
+        if len(rows) < 3:
+            continue
+        hdr, units = rows[0], rows[1]
+        ir, iw, kn, it = (hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("Kernel Name"),
+                          hdr.index("gpu__time_duration.sum"))
+        tot, names, dur = 0.0, [], 0.0
+        for r in rows[2:]:
+            tot += _bytes(r[ir], units[ir]) + _bytes(r[iw], units[iw])
+            names.append(re.sub(r"\(.*", "", r[kn])[:40])
+            dur += float(r[it].replace(",", "")) * {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(units[it], 1.0)
+        out[tag] = {"bytes_per_launch": tot, "source": f"ncu --set full, {os.path.basename(path)}",
+                    "launch": f"{len(names)} kernel(s): {', '.join(names)}; {dur:.1f} us under ncu"}
+    os.makedirs("profiles", exist_ok=True)
+    json.dump(out, open("profiles/ncu_traffic.json", "w"), indent=1)
+    print(json.dumps(out, indent=1))
+
+
 if __name__ == "__main__":
-    if sys.argv[1] == "launches":
+    if sys.argv[1] == "traffic":
+        traffic(sys.argv[2:])
+    elif sys.argv[1] == "launches":
         launches(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "")
     else:
         full(sys.argv[2:])

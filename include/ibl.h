@@ -177,6 +177,12 @@ int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_t n_src,
                    const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
                    int64_t max_iteration, double confidence, double max_d, double edge_thr, int use_checkers,
                    int early_exit, int64_t block, ibl_reg_result_t *h_result, void *stream);
+/* The same loop over hypotheses [h_begin, max_iteration) of the sample stream only: the block one rank owns when a
+ * single registration is sharded by hypothesis over GPUs (secondary axis); `drawn` counts from h_begin. */
+int ibl_ransac_run_range(const ibl_grid_t *tgt_grid, const double *src, int64_t n_src, const double *tgt,
+                   const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
+                   int64_t h_begin, int64_t max_iteration, double confidence, double max_d, double edge_thr, int use_checkers,
+                   int early_exit, int64_t block, ibl_reg_result_t *h_result, void *stream);
 
 /* ---------------------------------------------------------------- ICP ----------------------- */
 /* InitializePointCloudForColoredICP (A.8): grad double[n][3] */

@@ -71,6 +71,8 @@ _PROTOS = {
                                  _V, _V]),
     "ibl_ransac_run": (c_int, [_V, _V, c_int64, _V, _V, c_int64, _V, c_uint64, c_int64, c_double, c_double, c_double,
                                c_int, c_int, c_int64, POINTER(RegResultT), _V]),
+    "ibl_ransac_run_range": (c_int, [_V, _V, c_int64, _V, _V, c_int64, _V, c_uint64, c_int64, c_int64, c_double, c_double,
+                                     c_double, c_int, c_int, c_int64, POINTER(RegResultT), _V]),
     "ibl_color_gradient": (c_int, [_V, _V, _V, c_int64, _V, _V, c_int32, _V, _V]),
     "ibl_p2p_update": (c_int, [_V, _V, c_int64, _V, POINTER(c_double), _V]),
     "ibl_colored_update": (c_int, [_V, _V, _V, c_int64, _V, _V, _V, _V, c_double, POINTER(c_double),

@@ -253,7 +253,17 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
                            const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
                            int64_t max_iteration, double confidence, double max_d, double edge_thr, int use_checkers,
                            int early_exit, int64_t block, ibl_reg_result_t *h_result, void *stream) {
-    IBL_ARG(h_result != nullptr && tgt_grid != nullptr);
+    return ibl_ransac_run_range(tgt_grid, src, n_src, tgt, corres, n_corres, samples, seed, 0, max_iteration, confidence,
+                                max_d, edge_thr, use_checkers, early_exit, block, h_result, stream);
+}
+
+// Hypotheses [h_begin, max_iteration) of the same sample stream: the block one rank owns when a single registration
+// is sharded by hypothesis over GPUs (dist.hypothesis_block).
+IBL_API int ibl_ransac_run_range(const ibl_grid_t *tgt_grid, const double *src, int64_t n_src, const double *tgt,
+                                 const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
+                                 int64_t h_begin, int64_t max_iteration, double confidence, double max_d, double edge_thr,
+                                 int use_checkers, int early_exit, int64_t block, ibl_reg_result_t *h_result, void *stream) {
+    IBL_ARG(h_result != nullptr && tgt_grid != nullptr && h_begin >= 0);
     memset(h_result, 0, sizeof(*h_result));
     for (int k = 0; k < 16; ++k) h_result->T[k] = (k % 5 == 0) ? 1.0 : 0.0;
     h_result->best_hyp = -1;
@@ -292,7 +302,7 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
     double best_fit = 0.0, best_rmse = 0.0;
     int rc = IBL_OK;
     int64_t cur_block = std::min(first_block, MAX_BLOCK);
-    for (int64_t h0 = 0; h0 < max_iteration && h0 < est_k;) {
+    for (int64_t h0 = h_begin; h0 < max_iteration && h0 < est_k;) {
         int64_t H = std::min(cur_block, std::min(max_iteration, est_k) - h0);
         if ((rc = ibl_ransac_check(src, tgt, corres, n_corres, samples, seed, h0, H, edge_thr, max_d, use_checkers, pass,
                                    nullptr, stream)) < 0) break;
@@ -367,7 +377,7 @@ IBL_API int ibl_ransac_run(const ibl_grid_t *tgt_grid, const double *src, int64_
         h0 += H;
         cur_block = std::min(cur_block * 2, MAX_BLOCK);
     }
-    h_result->drawn = std::min(max_iteration, std::max<int64_t>(est_k, 0));
+    h_result->drawn = std::max<int64_t>(std::min(max_iteration, std::max<int64_t>(est_k, 0)) - h_begin, 0);
     ibl_free(tmp, st); ibl_free(pass, st); ibl_free(ids, st); ibl_free(dcount, st);
     ibl_free(inl, st); ibl_free(inl2, st); ibl_free(sel_ids, st); ibl_free(cinl, st); ibl_free(err, st); ibl_free(Ts, st);
     return rc;

@@ -299,11 +299,13 @@ def _reg_dict(r):
 
 
 def ransac_run(grid, src, tgt, corres, max_iteration, confidence, max_d, edge_thr=0.9, samples=None, seed=0,
-               use_checkers=True, early_exit=True, block=1 << 16):
+               use_checkers=True, early_exit=True, block=1 << 16, h0=0):
+    """h0 > 0: only hypotheses [h0, max_iteration) of the sample stream (one rank's block, dist.hypothesis_block)."""
     r = RegResultT()
-    check(lib().ibl_ransac_run(grid.h, _p(src), src.shape[0], _p(tgt), _p(corres), corres.shape[0], _p(samples),
-                               int(seed), int(max_iteration), float(confidence), float(max_d), float(edge_thr),
-                               int(use_checkers), int(early_exit), int(block), ctypes.byref(r), _stream()), "ransac_run")
+    check(lib().ibl_ransac_run_range(grid.h, _p(src), src.shape[0], _p(tgt), _p(corres), corres.shape[0], _p(samples),
+                                     int(seed), int(h0), int(max_iteration), float(confidence), float(max_d),
+                                     float(edge_thr), int(use_checkers), int(early_exit), int(block), ctypes.byref(r),
+                                     _stream()), "ransac_run")
     return _reg_dict(r)
 
 

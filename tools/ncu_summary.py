@@ -85,6 +85,10 @@ def traffic(specs):
     out = {}
     for spec in specs:
         tag, path = spec.split("=", 1)
+        nlaunch = 1                                       # TAG=path:N -- the capture holds N launches of the group
+        if ":" in path and path.rsplit(":", 1)[1].isdigit():
+            path, nl = path.rsplit(":", 1)
+            nlaunch = int(nl)
         txt = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
         rows = list(csv.reader(io.StringIO(txt)))
         if len(rows) < 3:
@@ -97,8 +101,9 @@ def traffic(specs):
             tot += _bytes(r[ir], units[ir]) + _bytes(r[iw], units[iw])
             names.append(re.sub(r"\(.*", "", r[kn])[:40])
             dur += float(r[it].replace(",", "")) * {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(units[it], 1.0)
-        out[tag] = {"bytes_per_launch": tot, "source": f"ncu --set full, {os.path.basename(path)}",
-                    "launch": f"{len(names)} kernel(s): {', '.join(names)}; {dur:.1f} us under ncu"}
+        out[tag] = {"bytes_per_launch": tot / nlaunch, "source": f"ncu --set full, {os.path.basename(path)}",
+                    "launch": f"{nlaunch} launch(es) of the group captured, {len(names)} kernel(s): {', '.join(names)}; "
+                              f"{dur:.1f} us under ncu in total"}
     os.makedirs("profiles", exist_ok=True)
     json.dump(out, open("profiles/ncu_traffic.json", "w"), indent=1)
     print(json.dumps(out, indent=1))

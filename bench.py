@@ -14,6 +14,7 @@ One JSON line on stdout (rank 0)."""
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -188,6 +189,7 @@ def run_product(args):
         return out.cpu()                                # D2H of the step's result
 
     def timed(host_inputs, steps, workers=None):
+        step(host_inputs, workers)                      # untimed: every timed pass starts from the steady state of ITS mode
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -204,10 +206,17 @@ def run_product(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    # nvidia-smi attaches to the driver when it starts, which can stall this process's CUDA calls for a few hundred ms
+    # (tools/stall_probe.py vs tools/host_profile.py): start the sampler BEFORE the warm-up so that its start-up is over
+    # when the timed region begins; it keeps sampling every 200 ms through all timed passes.
+    clocks = ClockSampler(local)
     for _ in range(args.warmup):
         step(False)
     step(True)
-    clocks = ClockSampler(local)
+    # a serving process freezes the heap after warm-up: a gen-2 collection is a 30-40 ms pause with 4 frame threads waiting
+    gc.collect()
+    gc.freeze()
+    gc.disable()
     l0 = K.launch_count()
     if args.profiler_range:                               # ncu --profile-from-start off: capture the timed region only
         torch.cuda.cudart().cudaProfilerStart()
@@ -262,7 +271,7 @@ def run_product(args):
                        "host_wait": host_wait, "host_cores": os.cpu_count(), "memory_objects": w["m"],
                        "memory_points": int(sum(len(m["points"]) for m in host_mem)), "embedding_dim": w["D"],
                        "ransac": "max_iteration 4e6, confidence 0.99, counter-based sample stream",
-                       "l2_flush": "256 MiB memset before every step", "parallelism": f"frames sharded over {world} rank(s)"},
+                       "l2_flush": "256 MiB memset before every step", "python_gc": "frozen and disabled after warm-up", "parallelism": f"frames sharded over {world} rank(s)"},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 56,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "clocks": clk, "roofline": roofline, "kernels": kernels}

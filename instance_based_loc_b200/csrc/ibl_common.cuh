@@ -69,6 +69,12 @@ static inline void ibl_pool_init() {
     if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
         unsigned long long thr = ~0ull;
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+        // Several frames run on several streams.  By default the pool may satisfy an allocation on stream B with memory
+        // whose free is still pending on stream A by making B WAIT for A ("internal dependencies"): that silently chains
+        // independent frames together (sporadic 20-50 % throughput drops at ~50 % GPU utilisation were traced to it).
+        // Grow the pool instead; opportunistic reuse (the free has already completed) stays on.
+        int off = 0;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolReuseAllowInternalDependencies, &off);
     }
     done_dev = dev;
 }
@@ -177,7 +183,8 @@ __device__ __forceinline__ int ibl_nn1_field(const GridView &g, double qx, doubl
         if (blk >= 0) {
             uint2 e = f.entries[(size_t)blk * 512 + (((iz & 7) << 6) | ((iy & 7) << 3) | (ix & 7))];
             const int *c = f.cand + e.x;
-            for (unsigned k = 0; k < e.y; ++k) {
+            const unsigned n = e.y & 0x7fffffffu;          // top bit: NF_SURE (count-only queries)
+            for (unsigned k = 0; k < n; ++k) {
                 double4 t = g.sorted[c[k]];
                 double d2 = ibl_d2(t.x, t.y, t.z, qx, qy, qz);
                 long long oi = (long long)__double_as_longlong(t.w);
@@ -192,7 +199,9 @@ __device__ __forceinline__ int ibl_nn1_field(const GridView &g, double qx, doubl
 // Is ANY target strictly within max_d of q?  (== "the nearest neighbour is within max_d", i.e. q is an inlier.)  With the
 // candidate field the voxel's list holds every target that can be the nearest neighbour of a point of the voxel, so the
 // scan stops at the first candidate inside max_d -- usually the first one -- instead of finishing the exact minimum.
-__device__ __forceinline__ bool ibl_any_within_field(const GridView &g, double qx, double qy, double qz, double max_d2) {
+// sure_ok: the query's max_d IS the max_d the field was built for (the SURE bit is only valid for that distance).
+__device__ __forceinline__ bool ibl_any_within_field(const GridView &g, double qx, double qy, double qz, double max_d2,
+                                                     bool sure_ok) {
     const NNFieldView &f = g.f;
     double fx = floor((qx - f.ox) * f.inv_c), fy = floor((qy - f.oy) * f.inv_c), fz = floor((qz - f.oz) * f.inv_c);
     if (!(fx >= 0.0 && fy >= 0.0 && fz >= 0.0 && fx < (double)f.nvx && fy < (double)f.nvy && fz < (double)f.nvz)) return false;
@@ -200,8 +209,10 @@ __device__ __forceinline__ bool ibl_any_within_field(const GridView &g, double q
     int blk = f.block_ptr[((size_t)(iz >> 3) * f.nby + (iy >> 3)) * f.nbx + (ix >> 3)];
     if (blk < 0) return false;
     uint2 e = f.entries[(size_t)blk * 512 + (((iz & 7) << 6) | ((iy & 7) << 3) | (ix & 7))];
+    if ((e.y & 0x80000000u) && sure_ok) return true;       // whole voxel within max_d of a target (nnfield.cu: NF_SURE)
     const int *c = f.cand + e.x;
-    for (unsigned k = 0; k < e.y; ++k) {
+    const unsigned n = e.y & 0x7fffffffu;
+    for (unsigned k = 0; k < n; ++k) {
         double4 t = g.sorted[c[k]];
         if (ibl_d2(t.x, t.y, t.z, qx, qy, qz) < max_d2) return true;
     }

@@ -80,10 +80,21 @@ __global__ void __launch_bounds__(256) nf_splat_kernel(const double4 *__restrict
     }
 }
 
+// entries[v] = (start, count | SURE bit).  SURE: every point of the voxel is closer than max_d to the target nearest to the
+// voxel centre (|q - c| <= h, |p* - c| = D, so |q - p*| <= D + h), with a 1e-9 relative margin that dwarfs the rounding of
+// the query's squared distance -- an inlier COUNT needs no candidate evaluation there (ibl_any_within_field).
+#define NF_SURE 0x80000000u
 __global__ void nf_entries_kernel(const unsigned int *__restrict__ cnt, const unsigned int *__restrict__ start, int64_t nv,
+                                  const unsigned long long *__restrict__ dmin2, double h, double max_d,
                                   uint2 *__restrict__ entries) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i < nv) entries[i] = make_uint2(start[i], cnt[i]);
+    if (i >= nv) return;
+    unsigned c = cnt[i];
+    if (c) {
+        double D = sqrt(__longlong_as_double((long long)dmin2[i]));
+        if ((D + h) * (1.0 + 1e-9) < max_d) c |= NF_SURE;
+    }
+    entries[i] = make_uint2(start[i], c);
 }
 
 static void nf_free(ibl_grid *g) {
@@ -160,7 +171,7 @@ IBL_API int ibl_grid_build_nnfield(ibl_grid_t *g, double max_d, double voxel, vo
     cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, start, (int)(nv + 1), st);
     IBL_CUDA(cudaMallocAsync(&tmp, tb ? tb : 1, st));
     IBL_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, start, (int)(nv + 1), st));
-    nf_entries_kernel<<<(unsigned)((nv + 255) / 256), 256, 0, st>>>(cnt, start, nv, g->f_entries);
+    nf_entries_kernel<<<(unsigned)((nv + 255) / 256), 256, 0, st>>>(cnt, start, nv, dmin2, G.h, max_d, g->f_entries);
     IBL_LAUNCH_CHECK();
     unsigned int total = 0;
     IBL_CUDA(cudaMemcpyAsync(&total, start + nv, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));

@@ -146,13 +146,14 @@ __global__ void __launch_bounds__(SCORE_THREADS) ransac_count_kernel(GridView g,
     int cnt = 0;
     int64_t base = (int64_t)tile * SCORE_TILE;
     const bool field = g.has_field && max_d <= g.f.max_d;
+    const bool sure_ok = field && max_d == g.f.max_d;
 #pragma unroll 1
     for (int r = 0; r < SCORE_TILE / SCORE_THREADS; ++r) {
         int64_t i = base + r * SCORE_THREADS + threadIdx.x;
         if (i < n_src) {
             double x, y, z, bd;
             ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
-            if (field) cnt += ibl_any_within_field(g, x, y, z, max_d2) ? 1 : 0;
+            if (field) cnt += ibl_any_within_field(g, x, y, z, max_d2, sure_ok) ? 1 : 0;
             else cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
         }
     }

@@ -1,0 +1,40 @@
+"""Diagnostic (GPU box): per-batch wall times of localise_batch at 4 frames in flight, no nvidia-smi running, with GC pauses
+timed -- looks for sporadic stalls."""
+import gc, os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import bench
+from instance_based_loc_b200 import kernels as K, selfcheck
+from instance_based_loc_b200.o3d import registration as reg
+w = bench.WORKLOAD
+dev = torch.device("cuda", 0)
+B = 8
+scene, frames = bench.make_inputs(B, 0, "cuda")
+om, host_mem = selfcheck.build_memory(scene, w["mem_spacing"], w["mem_voxel"], f=w["f"])
+reg.ransac_seed = w["ransac_seed"]
+keys = ("rgb", "depth", "masks", "embs")
+resident = [{k: torch.from_numpy(np.ascontiguousarray(fr[k])).to(dev) for k in keys} for fr in frames]
+gc_t = {"t0": 0.0, "tot": 0.0, "n": 0, "max": 0.0}
+def cb(phase, info):
+    if phase == "start":
+        gc_t["t0"] = time.perf_counter()
+    else:
+        d = time.perf_counter() - gc_t["t0"]
+        gc_t["tot"] += d; gc_t["n"] += 1; gc_t["max"] = max(gc_t["max"], d)
+gc.callbacks.append(cb)
+for mode in ("gc on", "gc off"):
+    if mode == "gc off":
+        gc.collect(); gc.disable()
+    om.localise_batch(resident, workers=4, **bench.LOCALISE_KW)
+    torch.cuda.synchronize()
+    times = []
+    gc_t.update(tot=0.0, n=0, max=0.0)
+    for rep in range(40):
+        t0 = time.perf_counter()
+        om.localise_batch(resident, workers=4, **bench.LOCALISE_KW)
+        torch.cuda.synchronize()
+        times.append((time.perf_counter() - t0) * 1e3)
+    t = np.array(times)
+    print(mode, "batch ms: median %.1f  min %.1f  max %.1f  p90 %.1f" % (np.median(t), t.min(), t.max(), np.percentile(t, 90)),
+          " slow(>1.3x median):", [round(x) for x in t[t > 1.3 * np.median(t)]],
+          " gc: n=%d total %.1f ms max %.1f ms" % (gc_t["n"], gc_t["tot"] * 1e3, gc_t["max"] * 1e3), flush=True)

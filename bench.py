@@ -240,6 +240,7 @@ def run_product(args):
     e2e = total_frames / (ms_e2e / 1e3)
 
     hbm_peak, tensor_peak, peak_src = peaks()
+    gemm = prof.pop("feature_gemm", None)                 # nested inside feature_nn: not a group of its own
     top = max(prof.items(), key=lambda kv: kv[1]["ms"]) if prof else ("none", {"ms": 0.0, "launches": 0, "work": 0.0})
     tname, t = top
     per_launch_ms = t["ms"] / max(t["launches"], 1)
@@ -261,6 +262,18 @@ def run_product(args):
                             "every kernel group (`value` comes from the first, un-instrumented pass); share_of_step = this "
                             "kernel's event time / the sum over all kernel groups",
                 "ms_per_step_instrumented": ms_prof / args.steps}
+    if gemm and gemm["ms"] > 0:
+        # the tcgen05 kernel alone: flops it issues (K = 112 over padded 128 x 128 tiles) against the tensor peak, and its time
+        # against the floor set by reading every fp32 score out of TMEM once (64 B/clk/SM: 1024 clk per 128 x 128 tile)
+        tiles = gemm["work"] / (2.0 * 112 * 128 * 128)
+        floor_ms = tiles * 1024 / 148 / (float(clk["sm_mhz"] or 1965.0) * 1e3)
+        roofline["gemm_kernel"] = {"kernel": "feat_tc_kernel<1> (tcgen05 kind::f16, one pass)", "launches": gemm["launches"],
+                                   "avg_launch_ms": gemm["ms"] / gemm["launches"],
+                                   "issued_tflops": gemm["work"] / gemm["ms"] / 1e9,
+                                   "issued_frac_of_tensor_peak": gemm["work"] / gemm["ms"] / 1e9 / tensor_peak,
+                                   "tmem_read_floor_ms_total": floor_ms, "frac_of_tmem_read_floor": floor_ms / gemm["ms"],
+                                   "note": "MMA floor is 448 clk per tile, TMEM read-back of the accumulator 1024 clk per tile "
+                                           "(DESIGN.md 4.1): the kernel is TMEM-read-bound, so ~0.44 of the tensor peak is its ceiling"}
     kernels = {k: {"ms": round(v["ms"], 3), "launches": v["launches"],
                    "gwork_per_s": round(v["work"] / max(v["ms"], 1e-9) / 1e6, 2)} for k, v in
                sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}

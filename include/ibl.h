@@ -226,6 +226,13 @@ int ibl_simvolume_topk(const float *S, int32_t nd, int32_t m, int32_t k, int64_t
  * knob exists for boxes with fewer cores per GPU.  No reference counterpart (Open3D is CPU-only). */
 int ibl_set_host_wait(int mode);
 
+/* Reserve `bytes` of stream-ordered scratch memory for `stream` (the library's temporaries come from the device's
+ * default cudaMallocAsync pool, which keeps what it has held): call once per frame stream before serving, so no frame
+ * waits for the driver to map memory.  No reference counterpart. */
+int ibl_reserve_scratch(int64_t bytes, void *stream);
+/* {reserved now, reserved high-water, used now, used high-water} bytes of that pool (host array of 4). */
+int ibl_scratch_stats(int64_t *h_out4);
+
 /* ---------------------------------------------------------------- instrumentation ------------ */
 /* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
 int64_t ibl_launch_count(void);

@@ -82,6 +82,8 @@ _PROTOS = {
     "ibl_cosine_segmax": (c_int, [_V, c_int32, _V, c_int64, c_int32, _V, c_int32, _V, _V]),
     "ibl_simvolume_topk": (c_int, [_V, c_int32, c_int32, c_int32, _V, _V, _V]),
     "ibl_set_host_wait": (c_int, [c_int]),
+    "ibl_reserve_scratch": (c_int, [c_int64, _V]),
+    "ibl_scratch_stats": (c_int, [POINTER(c_int64)]),
     "ibl_launch_count": (c_int64, []),
     "ibl_prof_enable": (None, [c_int]),
     "ibl_prof_num_tags": (c_int, []),

@@ -43,7 +43,7 @@ cudaError_t ibl_sync(cudaStream_t st);   // host wait on a stream under the ibl_
 enum IblProfTag { IBL_PROF_BACKPROJECT = 0, IBL_PROF_RADIUS, IBL_PROF_KNN, IBL_PROF_NORMALS, IBL_PROF_SPFH, IBL_PROF_FPFH,
                   IBL_PROF_FEATURE_NN, IBL_PROF_RANSAC_CHECK, IBL_PROF_RANSAC_SCORE, IBL_PROF_NN_SCORE, IBL_PROF_ICP_REDUCE,
                   IBL_PROF_COLOR_GRAD, IBL_PROF_GRID_BUILD, IBL_PROF_SIMVOL, IBL_PROF_COSINE, IBL_PROF_VOXEL, IBL_PROF_MEAN,
-                  IBL_PROF_MISC, IBL_PROF_COUNT };
+                  IBL_PROF_MISC, IBL_PROF_FEATURE_GEMM /* nested inside FEATURE_NN: the tcgen05 kernel alone */, IBL_PROF_COUNT };
 int ibl_prof_begin(int tag, cudaStream_t st, double bytes);
 void ibl_prof_end(int slot, cudaStream_t st);
 struct IblProfScope {

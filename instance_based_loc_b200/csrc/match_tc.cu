@@ -628,9 +628,13 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, mx + 2, B, nullptr, mx + 1);
     IBL_LAUNCH_CHECK();
     dim3 grid(p.qtiles, p.nsplit);
-    feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1,
-                                                        fa, fb, parts, pool, nullptr, 0, 0);
-    IBL_LAUNCH_CHECK();
+    {
+        // nested scope: the tcgen05 kernel alone, with the flops it ISSUES (depth 112 over the padded tiles)
+        IBL_PROF(IBL_PROF_FEATURE_GEMM, st, 2.0 * TC_K * (double)p.na_pad * (double)p.nb_pad);
+        feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1,
+                                                            fa, fb, parts, pool, nullptr, 0, 0);
+        IBL_LAUNCH_CHECK();
+    }
     {
         // the chunk count lives on the device (no host sync): a fixed grid strides over it
         feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb);

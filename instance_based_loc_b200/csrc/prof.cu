@@ -1,5 +1,6 @@
 // prof.cu -- launch counter and optional per-kernel CUDA-event timing (bench.py's roofline object is measured
 // live with these events on the launching stream; see include/ibl.h "instrumentation").
+#include <algorithm>
 #include <mutex>
 #include <stdlib.h>
 #include <sys/prctl.h>
@@ -17,7 +18,8 @@ static std::vector<cudaEvent_t> g_pool;
 
 static const char *kTagNames[IBL_PROF_COUNT] = {
     "backproject", "radius_count", "knn", "normals", "spfh", "fpfh", "feature_nn", "ransac_check", "ransac_score",
-    "nn_score", "icp_reduce", "color_gradient", "grid_build", "simvolume", "cosine_segmax", "voxel", "mean3", "misc"};
+    "nn_score", "icp_reduce", "color_gradient", "grid_build", "simvolume", "cosine_segmax", "voxel", "mean3", "misc",
+    "feature_gemm"};
 
 static cudaEvent_t get_event() {
     if (!g_pool.empty()) { cudaEvent_t e = g_pool.back(); g_pool.pop_back(); return e; }
@@ -70,6 +72,43 @@ IBL_API int ibl_set_host_wait(int mode) {
     if (g_hybrid) {
         prctl(PR_SET_TIMERSLACK, 1000UL, 0, 0, 0);          // this thread; worker threads set theirs on their first wait
         if (const char *e = getenv("IBL_WAIT_SPIN_US")) g_spin_us = atoi(e);
+    }
+    return IBL_OK;
+}
+
+// Grow the stream-ordered scratch pool by `bytes` now (allocate + free on `stream`): the pool keeps what it has ever
+// held (release threshold = max), so a frame stream that reserves its working set once never waits for the driver to
+// map memory in the middle of a frame.  Memory freed on one stream is reused by another only opportunistically, so
+// every frame stream reserves for itself.
+IBL_API int ibl_reserve_scratch(int64_t bytes, void *stream) {
+    IBL_ARG(bytes >= 0);
+    if (bytes == 0) return IBL_OK;
+    cudaStream_t st = ibl_stream(stream);
+    // several blocks rather than one: the allocator splits blocks but does not merge across separate mappings
+    const int64_t piece = 256ll << 20;
+    std::vector<void *> held;
+    for (int64_t left = bytes; left > 0; left -= piece) {
+        unsigned char *p = nullptr;
+        IBL_CUDA(ibl_alloc(&p, (size_t)std::min(left, piece), st));
+        held.push_back(p);
+    }
+    for (void *p : held) ibl_free(p, st);
+    return IBL_OK;
+}
+
+// {reserved now, reserved high-water, used now, used high-water} bytes of the device's default stream-ordered pool
+IBL_API int ibl_scratch_stats(int64_t *h_out4) {
+    IBL_ARG(h_out4 != nullptr);
+    int dev = 0;
+    cudaMemPool_t pool;
+    IBL_CUDA(cudaGetDevice(&dev));
+    IBL_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+    const cudaMemPoolAttr attrs[4] = {cudaMemPoolAttrReservedMemCurrent, cudaMemPoolAttrReservedMemHigh,
+                                      cudaMemPoolAttrUsedMemCurrent, cudaMemPoolAttrUsedMemHigh};
+    for (int k = 0; k < 4; ++k) {
+        unsigned long long v = 0;
+        IBL_CUDA(cudaMemPoolGetAttribute(pool, attrs[k], &v));
+        h_out4[k] = (int64_t)v;
     }
     return IBL_OK;
 }

@@ -369,6 +369,18 @@ def set_host_wait(mode):
     check(lib().ibl_set_host_wait(HOST_WAIT[mode] if isinstance(mode, str) else int(mode)), "set_host_wait")
 
 
+def reserve_scratch(nbytes):
+    """Grow the scratch pool for the current stream by nbytes (ibl_reserve_scratch)."""
+    check(lib().ibl_reserve_scratch(int(nbytes), _stream()), "reserve_scratch")
+
+
+def scratch_stats():
+    """-> dict of the scratch pool's reserved / used bytes (now and high-water)."""
+    v = (c_int64 * 4)()
+    check(lib().ibl_scratch_stats(v), "scratch_stats")
+    return {"reserved": int(v[0]), "reserved_high": int(v[1]), "used": int(v[2]), "used_high": int(v[3])}
+
+
 # ------------------------------------------------------------------------------- instrumentation
 def launch_count():
     return int(lib().ibl_launch_count())

@@ -262,6 +262,8 @@ class ObjectMemory():
                                    fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
                                    max_detected_object_num)
 
+    scratch_bytes_per_stream = 1 << 30                   # matcher candidate pool (~150 MB per call) + grids + k-NN lists
+
     def localise_batch(self, frames, workers=4, **kw):
         """localise_arrays over a batch of frames (dicts with rgb / depth / masks / embs), ``workers`` frames in flight
         at a time, each on its own host thread and CUDA stream: frames are independent, and the
@@ -285,6 +287,8 @@ class ObjectMemory():
             st = getattr(self._tls, "stream", None)
             if st is None:
                 st = self._tls.stream = torch.cuda.Stream()
+                with torch.cuda.stream(st):              # this frame stream's working set, mapped once (see ibl.h)
+                    K.reserve_scratch(self.scratch_bytes_per_stream)
             st.wait_event(ready)
             with torch.cuda.stream(st):
                 out = one(fr)
@@ -295,7 +299,18 @@ class ObjectMemory():
             if self._pool is not None:
                 self._pool.shutdown(wait=True)
             self._pool, self._pool_workers = ThreadPoolExecutor(max_workers=workers), workers
-        return list(self._pool.map(run, frames))
+        # longest first: a frame's cost grows with its detected clouds, i.e. with its mask pixels; handing the heavy
+        # frames out first keeps the last worker from finishing long after the others (results keep the input order)
+        order = list(range(len(frames)))
+        try:
+            px = torch.stack([torch.as_tensor(fr["masks"]).sum() for fr in frames]).cpu().tolist()
+            order.sort(key=lambda i: -px[i])
+        except Exception:
+            pass
+        out = [None] * len(frames)
+        for i, r in zip(order, self._pool.map(run, [frames[i] for i in order])):
+            out[i] = r
+        return out
 
     def _localise_core(self, detected_phrases, detected_embs, detected_pointclouds, outlier_removal_config,
                        fpfh_global_dist_factor, fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,

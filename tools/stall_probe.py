@@ -22,9 +22,11 @@ def cb(phase, info):
         d = time.perf_counter() - gc_t["t0"]
         gc_t["tot"] += d; gc_t["n"] += 1; gc_t["max"] = max(gc_t["max"], d)
 gc.callbacks.append(cb)
-for mode in ("gc on", "gc off"):
+print("pool MB after build", {k: v >> 20 for k, v in K.scratch_stats().items()}, flush=True)
+for mode in ("gc on", "gc off", "gc off again"):
     if mode == "gc off":
         gc.collect(); gc.disable()
+    print("pool MB", mode, {k: v >> 20 for k, v in K.scratch_stats().items()}, flush=True)
     om.localise_batch(resident, workers=4, **bench.LOCALISE_KW)
     torch.cuda.synchronize()
     times = []
@@ -35,6 +37,8 @@ for mode in ("gc on", "gc off"):
         torch.cuda.synchronize()
         times.append((time.perf_counter() - t0) * 1e3)
     t = np.array(times)
+    print("   slow batch indices", [int(i) for i in np.nonzero(t > 1.3 * np.median(t))[0]], "pool MB",
+          {k: v >> 20 for k, v in K.scratch_stats().items()}, flush=True)
     print(mode, "batch ms: median %.1f  min %.1f  max %.1f  p90 %.1f" % (np.median(t), t.min(), t.max(), np.percentile(t, 90)),
           " slow(>1.3x median):", [round(x) for x in t[t > 1.3 * np.median(t)]],
           " gc: n=%d total %.1f ms max %.1f ms" % (gc_t["n"], gc_t["tot"] * 1e3, gc_t["max"] * 1e3), flush=True)

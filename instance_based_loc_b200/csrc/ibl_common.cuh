@@ -3,6 +3,7 @@
 // does not depend on FMA contraction (the library is also built with -fmad=false).
 #pragma once
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -73,7 +74,7 @@ static inline void ibl_pool_init() {
         // whose free is still pending on stream A by making B WAIT for A ("internal dependencies"): that silently chains
         // independent frames together (sporadic 20-50 % throughput drops at ~50 % GPU utilisation were traced to it).
         // Grow the pool instead; opportunistic reuse (the free has already completed) stays on.
-        int off = 0;
+        int off = getenv("IBL_POOL_INTERNAL_DEPS") ? 1 : 0;    // experiment switch; the product setting is 0
         cudaMemPoolSetAttribute(pool, cudaMemPoolReuseAllowInternalDependencies, &off);
     }
     done_dev = dev;

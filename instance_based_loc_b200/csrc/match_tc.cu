@@ -220,6 +220,25 @@ __global__ void __launch_bounds__(128) feat_tc_pack_kernel(const double *__restr
     }
 }
 
+// fp32 copies of the RAW rows (stride TC_R32 floats, 16-byte aligned) and an upper bound of their Euclidean norms, for
+// the second filter in feat_tc_eval_kernel.
+#define TC_R32 36
+__global__ void __launch_bounds__(256) feat_tc_rows32_kernel(const double *__restrict__ f, int64_t n, float *__restrict__ rows32,
+                                                             float *__restrict__ nrm) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double s = 0.0;
+    float *o = rows32 + i * TC_R32;
+#pragma unroll
+    for (int j = 0; j < 33; ++j) {
+        double v = f[i * 33 + j];
+        s += v * v;
+        o[j] = __double2float_rn(v);
+    }
+    o[33] = o[34] = o[35] = 0.f;
+    nrm[i] = __double2float_ru(sqrt(s) * (1.0 + 1e-12));
+}
+
 // ------------------------------------------------------------------------------------------------ error band
 // All quantities are those of the centred, power-of-two-scaled rows (|value| <= 1024); scaling multiplies every distance
 // by the same exact factor, so order and ties are unchanged.
@@ -471,15 +490,49 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
     }
 }
 
-// One warp per pool chunk: its candidates are evaluated exactly, 32 at a time (the query row is a broadcast load), and
-// reduced with the oracle's order (distance, then lower index) into res[chunk].  Work is balanced by ENTRY count, however
-// skewed the candidates are over the queries (planar patches: thousands of near-identical rows inside one band).
-// The band provably holds the exact nearest neighbour, so the chunk of a row with ONE candidate needs no f64 work here:
-// d = -1 marks "not evaluated"; the merge evaluates it only if another split of the same query also has candidates.
 struct TcChunkRes { double d; int idx; int pad; };
+
+// Second filter, on fp32 DIFFERENCES.  s = sum_j fl(fl(a32_j - b32_j)^2) in fp32 (j ascending, every operation rounded to
+// nearest, no FMA) against the exact d = sum_j (a_j - b_j)^2, with u = 2^-24:
+//   input rounding + the subtraction      |delta_j - x_j| <= 2.0000002 u (|a_j| + |b_j|)   =>  ||delta - x|| <= H := 2.0000002 u (|a| + |b|)
+//   squares and the 33-term sum           |s - sum delta_j^2| <= 36 u sum delta_j^2,  sum delta_j^2 <= (1 + 37 u) s
+//   sum delta^2 against d                 |sum delta^2 - d| <= 2 sqrt(d) H + H^2,  sqrt(d) <= sqrt(sum delta^2) + H
+// => |s - d| <= 37 u s + 2.00001 sqrt(s) H + 3 H^2; the kernel uses 40 u s + 2.1 sqrt(s) H + 3.1 H^2 + 1e-30, rounded up.  The
+// error scales with |a| |a - b| instead of the GEMM filter's |a|^2, i.e. it is ~10^3 times tighter for near neighbours.
+__device__ __forceinline__ float feat_tc_err32(float s, float na, float nb) {
+    const float H = __fmul_ru(1.1920932e-7f, __fadd_ru(na, nb));          // 2.0000002 * 2^-24, rounded up
+    float e = __fmul_ru(2.3841864e-6f, s);                                 // 40 u s
+    e = __fadd_ru(e, __fmul_ru(2.1f, __fmul_ru(__fsqrt_ru(s), H)));
+    e = __fadd_ru(e, __fmul_ru(3.1f, __fmul_ru(H, H)));
+    return __fadd_ru(e, 1e-30f);
+}
+__device__ __forceinline__ float feat_tc_d32(const float *__restrict__ a, const float *__restrict__ b) {
+    float s = 0.f;
+#pragma unroll
+    for (int j4 = 0; j4 < 32; j4 += 4) {
+        const float4 x = *reinterpret_cast<const float4 *>(a + j4), y = *reinterpret_cast<const float4 *>(b + j4);
+        float d;
+        d = __fsub_rn(x.x, y.x); s = __fadd_rn(s, __fmul_rn(d, d));
+        d = __fsub_rn(x.y, y.y); s = __fadd_rn(s, __fmul_rn(d, d));
+        d = __fsub_rn(x.z, y.z); s = __fadd_rn(s, __fmul_rn(d, d));
+        d = __fsub_rn(x.w, y.w); s = __fadd_rn(s, __fmul_rn(d, d));
+    }
+    const float d = __fsub_rn(a[32], b[32]);
+    return __fadd_rn(s, __fmul_rn(d, d));
+}
+
+// One warp per pool chunk (<= 64 candidates, two per lane).  Phase 1: the fp32 difference distance of every candidate with
+// its error radius; U = the smallest upper bound in the chunk.  Phase 2: only candidates whose lower bound does not exceed U
+// -- the only ones that can be the chunk's nearest or tie with it -- get the oracle's f64 evaluation, reduced in the oracle's
+// order (distance, then lower index) into res[chunk].  Work is balanced by ENTRY count, however skewed the candidates are
+// over the queries (planar patches: thousands of near-identical rows inside one band).
+// The band provably holds the exact nearest neighbour, so the chunk of a row with ONE candidate needs no work at all here:
+// d = -1 marks "not evaluated"; the merge evaluates it only if another split of the same query also has candidates.
 __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__restrict__ parts, TcPool pool, int nsplit,
                                                            TcChunkRes *__restrict__ res, const double *__restrict__ fa,
-                                                           const double *__restrict__ fb) {
+                                                           const double *__restrict__ fb, const float *__restrict__ a32,
+                                                           const float *__restrict__ b32, const float *__restrict__ na32,
+                                                           const float *__restrict__ nb32) {
     const int lane = threadIdx.x & 31;
     const int nwarps = gridDim.x * (blockDim.x >> 5);
     const int nchunks = min(*pool.counter, pool.cap);
@@ -491,14 +544,32 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__
             if (lane == 0) { TcChunkRes r; r.d = -1.0; r.idx = (int)e[0]; r.pad = 0; res[c] = r; }
             continue;
         }
-        const double *a = fa + (size_t)(row / nsplit) * 33;
+        const int64_t q = row / nsplit;
+        const float *aq = a32 + q * TC_R32;
+        const float naq = na32[q];
+        int t[2] = {-1, -1};
+        float lo[2] = {INFINITY, INFINITY};
+        float U = INFINITY;
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const int k = r * 32 + lane;
+            if (k < n) {
+                t[r] = (int)e[k];
+                const float s = feat_tc_d32(aq, b32 + (size_t)t[r] * TC_R32);
+                const float E2 = feat_tc_err32(s, naq, nb32[t[r]]);
+                lo[r] = __fsub_rd(s, E2);
+                U = fminf(U, __fadd_ru(s, E2));
+            }
+        }
+        for (int o = 16; o; o >>= 1) U = fminf(U, __shfl_xor_sync(0xffffffffu, U, o));
+        const double *a = fa + (size_t)q * 33;
         double bestd = INFINITY;
         int bi = -1;
-        for (int base = 0; base < n; base += 32) {
-            if (base + lane < n) {
-                int t = (int)e[base + lane];
-                double de = feat_tc_exact(a, fb + (size_t)t * 33);
-                if (bi < 0 || de < bestd || (de == bestd && t < bi)) { bestd = de; bi = t; }
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            if (t[r] >= 0 && lo[r] <= U) {
+                double de = feat_tc_exact(a, fb + (size_t)t[r] * 33);
+                if (bi < 0 || de < bestd || (de == bestd && t[r] < bi)) { bestd = de; bi = t[r]; }
                 ++n_eval;
             }
         }
@@ -627,6 +698,15 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     IBL_LAUNCH_CHECK();
     feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, mx + 2, B, nullptr, mx + 1);
     IBL_LAUNCH_CHECK();
+    float *a32 = nullptr, *b32 = nullptr, *na32 = nullptr, *nb32 = nullptr;      // second filter (feat_tc_eval_kernel)
+    IBL_CUDA(ibl_alloc(&a32, (size_t)na * TC_R32, st));
+    IBL_CUDA(ibl_alloc(&b32, (size_t)nb * TC_R32, st));
+    IBL_CUDA(ibl_alloc(&na32, (size_t)na, st));
+    IBL_CUDA(ibl_alloc(&nb32, (size_t)nb, st));
+    feat_tc_rows32_kernel<<<(unsigned)((na + 255) / 256), 256, 0, st>>>(fa, na, a32, na32);
+    IBL_LAUNCH_CHECK();
+    feat_tc_rows32_kernel<<<(unsigned)((nb + 255) / 256), 256, 0, st>>>(fb, nb, b32, nb32);
+    IBL_LAUNCH_CHECK();
     dim3 grid(p.qtiles, p.nsplit);
     {
         // nested scope: the tcgen05 kernel alone, with the flops it ISSUES (depth 112 over the padded tiles)
@@ -637,11 +717,12 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     }
     {
         // the chunk count lives on the device (no host sync): a fixed grid strides over it
-        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb);
+        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32);
         IBL_LAUNCH_CHECK();
     }
     feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn);
     IBL_LAUNCH_CHECK();
+    ibl_free(a32, st); ibl_free(b32, st); ibl_free(na32, st); ibl_free(nb32, st);
     ibl_free(pool.entries, st); ibl_free(pool_meta, st); ibl_free(res, st); ibl_free(mu, st); ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st); ibl_free(parts, st);
     return IBL_OK;
 }

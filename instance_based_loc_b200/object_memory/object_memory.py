@@ -287,8 +287,9 @@ class ObjectMemory():
             st = getattr(self._tls, "stream", None)
             if st is None:
                 st = self._tls.stream = torch.cuda.Stream()
-                with torch.cuda.stream(st):              # this frame stream's working set, mapped once (see ibl.h)
-                    K.reserve_scratch(self.scratch_bytes_per_stream)
+                if self.scratch_bytes_per_stream and not os.environ.get("IBL_NO_RESERVE"):
+                    with torch.cuda.stream(st):          # this frame stream's working set, mapped once (see ibl.h)
+                        K.reserve_scratch(self.scratch_bytes_per_stream)
             st.wait_event(ready)
             with torch.cuda.stream(st):
                 out = one(fr)
@@ -303,8 +304,9 @@ class ObjectMemory():
         # frames out first keeps the last worker from finishing long after the others (results keep the input order)
         order = list(range(len(frames)))
         try:
-            px = torch.stack([torch.as_tensor(fr["masks"]).sum() for fr in frames]).cpu().tolist()
-            order.sort(key=lambda i: -px[i])
+            if not os.environ.get("IBL_NO_LPT"):
+                px = torch.stack([torch.as_tensor(fr["masks"]).sum() for fr in frames]).cpu().tolist()
+                order.sort(key=lambda i: -px[i])
         except Exception:
             pass
         out = [None] * len(frames)

@@ -23,19 +23,23 @@ def cb(phase, info):
         gc_t["tot"] += d; gc_t["n"] += 1; gc_t["max"] = max(gc_t["max"], d)
 gc.callbacks.append(cb)
 print("pool MB after build", {k: v >> 20 for k, v in K.scratch_stats().items()}, flush=True)
-for mode in ("gc on", "gc off", "gc off again"):
-    if mode == "gc off":
-        gc.collect(); gc.disable()
+for mode in ("gc off", "gc off again"):
+    gc.collect(); gc.disable()
     print("pool MB", mode, {k: v >> 20 for k, v in K.scratch_stats().items()}, flush=True)
     om.localise_batch(resident, workers=4, **bench.LOCALISE_KW)
     torch.cuda.synchronize()
     times = []
     gc_t.update(tot=0.0, n=0, max=0.0)
-    for rep in range(40):
-        t0 = time.perf_counter()
+    for rep in range(60):
+        r0, c0, t0 = K.scratch_stats()["reserved"], time.process_time(), time.perf_counter()
         om.localise_batch(resident, workers=4, **bench.LOCALISE_KW)
         torch.cuda.synchronize()
-        times.append((time.perf_counter() - t0) * 1e3)
+        dt = (time.perf_counter() - t0) * 1e3
+        times.append(dt)
+        if len(times) > 5 and dt > 1.25 * np.median(times):
+            print(f"   SLOW batch {rep}: {dt:.0f} ms, process cpu {1e3 * (time.process_time() - c0):.0f} ms, pool reserved "
+                  f"{r0 >> 20} -> {K.scratch_stats()['reserved'] >> 20} MB, torch reserved {torch.cuda.memory_reserved() >> 20} MB, "
+                  f"loadavg {os.getloadavg()}", flush=True)
     t = np.array(times)
     print("   slow batch indices", [int(i) for i in np.nonzero(t > 1.3 * np.median(t))[0]], "pool MB",
           {k: v >> 20 for k, v in K.scratch_stats().items()}, flush=True)

@@ -7,8 +7,8 @@ timeout 700 python -m pytest tests -m gpu -x -q > gpurun_out/gpu_tests.log 2>&1;
 timeout 420 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?" >> gpurun_out/bench.err
 timeout 420 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv \
     --log-file gpurun_out/launches.csv $B > gpurun_out/ncu_launches.log 2>&1; echo "ncu-launches rc=$?" >> gpurun_out/ncu_launches.log
-# feat_tc: the 8 kernels of ONE ibl_feature_nn call (centre, range x2, pack x2, one-pass GEMM, eval, merge), a 3-object call
-for spec in "feat_tc:64:8" "ransac_count_kernel:6:2" "ransac_score_kernel:6:2" "colored_step_kernel:10:2" "knn_kernel:10:2" "fpfh_kernel:5:1"; do
+# feat_tc: the 10 kernels of ONE ibl_feature_nn call (centre, range x2, pack x2, rows32 x2, one-pass GEMM, eval, merge), a 3-object call
+for spec in "feat_tc:80:10" "ransac_count_kernel:6:2" "ransac_score_kernel:6:2" "colored_step_kernel:10:2" "knn_kernel:10:2" "fpfh_kernel:5:1"; do
     IFS=: read k skip cnt <<< "$spec"
     timeout 300 ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:$k \
         --launch-skip $skip -c $cnt -f -o gpurun_out/full_$k $B > gpurun_out/ncu_full_$k.log 2>&1

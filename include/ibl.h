@@ -170,6 +170,12 @@ int ibl_ransac_score(const ibl_grid_t *tgt_grid, const double *src, int64_t n_sr
                      const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
                      const int64_t *hyp_ids, int64_t nh, double max_d, int32_t *inliers, double *err2,
                      int32_t *corres_inliers, double *T_out, void *stream);
+/* Inlier counts only, for hypotheses hyp_ids int64[nh]: inliers[k] equals ibl_ransac_score's inliers[k] (tested), at a
+ * fraction of the cost -- a point's scan stops at the first target within max_d, and voxels of the NN field that lie
+ * wholly within max_d of a target need no scan at all.  T_out double[nh][16]. */
+int ibl_ransac_count(const ibl_grid_t *tgt_grid, const double *src, int64_t n_src, const double *tgt,
+                     const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
+                     const int64_t *hyp_ids, int64_t nh, double max_d, int32_t *inliers, double *T_out, void *stream);
 /* Whole RegistrationRANSACBasedOnCorrespondence loop with sequential semantics (A.7): blocks of
  * `block` hypotheses are checked, the survivors scored, and the ordered update / adaptive stop
  * applied on the host.  Syncs. */

@@ -69,6 +69,7 @@ _PROTOS = {
                                  _V, _V]),
     "ibl_ransac_score": (c_int, [_V, _V, c_int64, _V, _V, c_int64, _V, c_uint64, _V, c_int64, c_double, _V, _V, _V,
                                  _V, _V]),
+    "ibl_ransac_count": (c_int, [_V, _V, c_int64, _V, _V, c_int64, _V, c_uint64, _V, c_int64, c_double, _V, _V, _V]),
     "ibl_ransac_run": (c_int, [_V, _V, c_int64, _V, _V, c_int64, _V, c_uint64, c_int64, c_double, c_double, c_double,
                                c_int, c_int, c_int64, POINTER(RegResultT), _V]),
     "ibl_ransac_run_range": (c_int, [_V, _V, c_int64, _V, _V, c_int64, _V, c_uint64, c_int64, c_int64, c_double, c_double,

@@ -85,7 +85,7 @@ IBL_API int ibl_reserve_scratch(int64_t bytes, void *stream) {
     if (bytes == 0) return IBL_OK;
     cudaStream_t st = ibl_stream(stream);
     // several blocks rather than one: the allocator splits blocks but does not merge across separate mappings
-    const int64_t piece = 256ll << 20;
+    const int64_t piece = 512ll << 20;
     std::vector<void *> held;
     for (int64_t left = bytes; left > 0; left -= piece) {
         unsigned char *p = nullptr;

@@ -244,6 +244,26 @@ IBL_API int ibl_ransac_score(const ibl_grid_t *tgt_grid, const double *src, int6
     return IBL_OK;
 }
 
+// Inlier counts only (the pass ibl_ransac_run uses on whole chunks): inliers[k] == ibl_ransac_score's inliers[k].
+IBL_API int ibl_ransac_count(const ibl_grid_t *tgt_grid, const double *src, int64_t n_src, const double *tgt,
+                             const int32_t *corres, int64_t n_corres, const int32_t *samples, uint64_t seed,
+                             const int64_t *hyp_ids, int64_t nh, double max_d, int32_t *inliers, double *T_out, void *stream) {
+    IBL_ARG(tgt_grid && nh >= 0 && n_src >= 0 && max_d > 0 && nh <= 65535);
+    if (nh == 0) return IBL_OK;
+    IBL_ARG(src && tgt && corres && hyp_ids && inliers && T_out);
+    cudaStream_t st = ibl_stream(stream);
+    hyp_transform_kernel<<<(unsigned)((nh + 63) / 64), 64, 0, st>>>(src, tgt, corres, n_corres, samples, seed, hyp_ids, nh, T_out);
+    IBL_LAUNCH_CHECK();
+    IBL_CUDA(cudaMemsetAsync(inliers, 0, sizeof(int32_t) * nh, st));
+    int ntiles = (int)((n_src + SCORE_TILE - 1) / SCORE_TILE);
+    if (ntiles < 1) ntiles = 1;
+    dim3 grid(ntiles, (unsigned)nh);
+    IBL_PROF(IBL_PROF_RANSAC_SCORE, st, (double)nh * (24.0 * n_src + 128.0));
+    ransac_count_kernel<<<grid, SCORE_THREADS, 0, st>>>(ibl_view(tgt_grid), src, n_src, T_out, max_d, max_d * max_d, inliers);
+    IBL_LAUNCH_CHECK();
+    return IBL_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 struct IotaPlus {
     int64_t h0;
@@ -316,16 +336,8 @@ IBL_API int ibl_ransac_run_range(const ibl_grid_t *tgt_grid, const double *src, 
         for (int64_t c0 = 0; c0 < npass && !stop; c0 += SCORE_CHUNK) {
             int64_t nc = std::min<int64_t>(SCORE_CHUNK, npass - c0);
             // stage 1: inlier counts of the whole chunk (cheap: first candidate within max_d ends a point's scan)
-            hyp_transform_kernel<<<(unsigned)((nc + 63) / 64), 64, 0, st>>>(src, tgt, corres, n_corres, samples, seed, ids + c0, nc, Ts);
-            IBL_LAUNCH_CHECK();
-            IBL_CUDA(cudaMemsetAsync(inl, 0, sizeof(int32_t) * nc, st));
-            {
-                int ntiles = (int)((n_src + SCORE_TILE - 1) / SCORE_TILE);
-                dim3 grid(ntiles, (unsigned)nc);
-                IBL_PROF(IBL_PROF_RANSAC_SCORE, st, (double)nc * (24.0 * n_src + 128.0));
-                ransac_count_kernel<<<grid, SCORE_THREADS, 0, st>>>(ibl_view(tgt_grid), src, n_src, Ts, max_d, max_d * max_d, inl);
-                IBL_LAUNCH_CHECK();
-            }
+            if ((rc = ibl_ransac_count(tgt_grid, src, n_src, tgt, corres, n_corres, samples, seed, ids + c0, nc, max_d, inl, Ts,
+                                       stream)) < 0) { stop = true; break; }
             IBL_CUDA(cudaMemcpyAsync(h_ids.data(), ids + c0, sizeof(int64_t) * nc, cudaMemcpyDeviceToHost, st));
             IBL_CUDA(cudaMemcpyAsync(h_inl.data(), inl, sizeof(int32_t) * nc, cudaMemcpyDeviceToHost, st));
             IBL_CUDA(ibl_sync(st));

@@ -298,6 +298,16 @@ def _reg_dict(r):
             "validated": r.validated, "n_corres": r.n_corres, "iterations": r.iterations, "status": r.status}
 
 
+def ransac_count(grid, src, tgt, corres, hyp_ids, max_d, samples=None, seed=0):
+    """Inlier counts only (ibl_ransac_count) -> (inliers int32 [nh], T [nh,16])."""
+    nh = hyp_ids.shape[0]
+    inl = torch.empty(nh, dtype=torch.int32, device=src.device)
+    Ts = torch.empty((nh, 16), dtype=F64, device=src.device)
+    check(lib().ibl_ransac_count(grid.h, _p(src), src.shape[0], _p(tgt), _p(corres), corres.shape[0], _p(samples),
+                                 int(seed), _p(hyp_ids), nh, float(max_d), _p(inl), _p(Ts), _stream()), "ransac_count")
+    return inl, Ts
+
+
 def ransac_run(grid, src, tgt, corres, max_iteration, confidence, max_d, edge_thr=0.9, samples=None, seed=0,
                use_checkers=True, early_exit=True, block=1 << 16, h0=0):
     """h0 > 0: only hypotheses [h0, max_iteration) of the sample stream (one rank's block, dist.hypothesis_block)."""

@@ -262,7 +262,9 @@ class ObjectMemory():
                                    fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
                                    max_detected_object_num)
 
-    scratch_bytes_per_stream = 1 << 30                   # matcher candidate pool (~150 MB per call) + grids + k-NN lists
+    # per frame stream: matcher candidate pool (~150 MB per call) + grids + k-NN lists, AND whatever memory-side caches
+    # (per-assignment features, grids, NN fields: ~5 GB for the 40-object bank) happen to be built on that stream
+    scratch_bytes_per_stream = 4 << 30
 
     def localise_batch(self, frames, workers=4, **kw):
         """localise_arrays over a batch of frames (dicts with rgb / depth / masks / embs), ``workers`` frames in flight

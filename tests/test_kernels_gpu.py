@@ -396,6 +396,20 @@ def test_ransac_score(K, oc, reg_case):
         assert int(h(cin)[k]) == ci
 
 
+@pytest.mark.parametrize("field,voxel_div,max_d", [(0.075, 8, 0.075), (0.075, 4, 0.075), (0.075, 8, 0.05), (0.0, 0, 0.075)])
+def test_ransac_count_equals_score(K, reg_case, field, voxel_div, max_d):
+    """The count-only pass (first candidate within max_d; SURE voxels of the NN field when the query distance is the
+    field's) must give the exact pass's inlier counts: 600 unchecked hypotheses, good and junk alike."""
+    c = reg_case
+    S, T_, C = dev(c["src"]), dev(c["tgt"]), dev(c["cor"], torch.int32)
+    g = (K.Grid(T_, 0.075, nnfield=field, nnfield_voxel=field / voxel_div) if field else K.Grid(T_, 0.075 / 4, ring=8))
+    ids = torch.arange(600, dtype=torch.int64, device=S.device)
+    inl_c, T_c = K.ransac_count(g, S, T_, C, ids, max_d, seed=99)
+    inl_s, _, _, T_s = K.ransac_score(g, S, T_, C, ids, max_d, seed=99)
+    assert torch.equal(inl_c, inl_s) and torch.equal(T_c, T_s)
+    assert int(inl_s.max()) > 100 and int((inl_s == 0).sum()) >= 0
+
+
 @pytest.mark.parametrize("early_exit,block,field", [(True, 4096, True), (True, 1000, False), (False, 4096, True)])
 def test_ransac_run(K, oc, reg_case, early_exit, block, field):
     c = reg_case
@@ -412,6 +426,27 @@ def test_ransac_run(K, oc, reg_case, early_exit, block, field):
     assert abs(r["fitness"] - ref.fitness) == 0 and abs(r["inlier_rmse"] - ref.inlier_rmse) < 1e-12
     # and the pose is the right one
     assert rot_angle_deg(r["T"][:3, :3], c["T"][:3, :3]) < 2.0
+
+
+def test_scratch_and_host_wait_knobs(K):
+    """ibl_reserve_scratch grows the pool and keeps it; every host-wait mode gives the same results."""
+    before = K.scratch_stats()["reserved"]
+    K.reserve_scratch(64 << 20)
+    torch.cuda.synchronize()
+    assert K.scratch_stats()["reserved"] >= max(before, 64 << 20)
+    p = dev(surface_cloud(4000, 77)[0])
+    want = None
+    try:
+        for mode in ("auto", "spin", "yield", "block", "hybrid", "auto"):
+            K.set_host_wait(mode)
+            g = K.Grid(p, 0.03)
+            idx, d2, cnt = K.knn_hybrid(g, 0.1, 30)
+            got = (h(idx), h(cnt), K.mean3(p))
+            if want is None:
+                want = got
+            assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]) and np.array_equal(got[2], want[2])
+    finally:
+        K.set_host_wait("auto")
 
 
 def test_ransac_too_few_correspondences(K, reg_case):

@@ -16,12 +16,13 @@ def test_smoke_entry(cuda):
 
 @pytest.mark.parametrize("seed", [11, 12])
 def test_localise_frame_parity(cuda, seed):
+    import ibl_selfcheck
     from instance_based_loc_b200 import selfcheck, synth
     scene = synth.make_scene(m=8, seed=seed, D=96, size=(0.35, 0.75))
     om, host = selfcheck.build_memory(scene, spacing=0.015, voxel=0.015, f=150.0)
     frames = synth.make_frames(scene, 2, H=225, W=300, f=150.0, seed=seed, min_pixels=200)
     for fr in frames:
-        rep = selfcheck.compare_frame(om, host, fr, 150.0, seed=seed, fpfh_global_dist_factor=1.5,
+        rep = ibl_selfcheck.compare_frame(om, host, fr, 150.0, seed=seed, fpfh_global_dist_factor=1.5,
                                       fpfh_local_dist_factor=1.5, fpfh_voxel_size=0.05)
         assert rep["assignments_equal"], rep
         assert rep["sim_maxdiff"] < 2e-6, rep

@@ -557,8 +557,12 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__
                 t[r] = (int)e[k];
                 const float s = feat_tc_d32(aq, b32 + (size_t)t[r] * TC_R32);
                 const float E2 = feat_tc_err32(s, naq, nb32[t[r]]);
-                lo[r] = __fsub_rd(s, E2);
-                U = fminf(U, __fadd_ru(s, E2));
+                if (isfinite(s) && isfinite(E2)) {
+                    lo[r] = __fsub_rd(s, E2);
+                    U = fminf(U, __fadd_ru(s, E2));
+                } else {
+                    lo[r] = -INFINITY;                     // units beyond fp32's range: no bound, always evaluated exactly
+                }
             }
         }
         for (int o = 16; o; o >>= 1) U = fminf(U, __shfl_xor_sync(0xffffffffu, U, o));

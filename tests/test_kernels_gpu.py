@@ -282,11 +282,12 @@ def test_feature_scores_tensor_core_band(K):
 
 
 def test_feature_nn_any_units(K, oc):
-    """The fp16 filter rescales by a power of two, so features in any units (here x1e6 and x1e-6) match the oracle."""
+    """The fp16 filter rescales by a power of two, so features in any units match the oracle; at x1e25 the fp32 second
+    filter overflows and must fall back to evaluating every candidate exactly, at x1e-25 its squares underflow."""
     rng = np.random.default_rng(47)
     fa, fb = _fpfh_like(rng, 300), _fpfh_like(rng, 420)
     fb[17] = fa[5]
-    for unit in (1e6, 1e-6):
+    for unit in (1e6, 1e-6, 1e25, 1e-25):
         got = h(K.feature_nn(dev(fa * unit), dev(fb * unit)))
         assert np.array_equal(got, oc.feature_nn(np.ascontiguousarray((fa * unit).T), np.ascontiguousarray((fb * unit).T)))
         assert got[5] == 17

@@ -122,7 +122,7 @@ int ibl_fpfh(int64_t n, const int32_t *nbr_idx, const double *nbr_d2, const int3
 /* exact 33-d nearest neighbour of every column of fa among the columns of fb (A.5 KDTreeFlann on
  * features, SearchKNN k=1); lowest index wins ties.  fa double[na][33], fb double[nb][33]. */
 int ibl_feature_nn(const double *fa, int64_t na, const double *fb, int64_t nb, int32_t *nn, void *stream);
-/* Debug / test hook of the tensor-core filter inside ibl_feature_nn (csrc/match_tc.cu): the raw tcgen05 tf32 scores
+/* Debug / test hook of the tensor-core filter inside ibl_feature_nn (csrc/match_tc.cu): the raw tcgen05 (kind::f16, 3-way fp16 split) scores
  * s'(a_i, b_j) = a32_i . b32_j - |b32_j|^2 / 2 as float32 [na][nb] (row-major), a32 / b32 being the rows minus the filter's
  * centre, times its power-of-two scale; centre (33) and scale (1) are written to center_out (device double[34]) when
  * not NULL.  swap_lbo_sbo must be 0 (1 is a

@@ -1,7 +1,7 @@
 // match.cu -- exact 33-d nearest-neighbour feature matching + mutual filter (Open3D
 // RegistrationRANSACBasedOnFeatureMatching front half, utils/fpfh_register.py:110-112; A.5).
 //
-// The nearest-neighbour search itself is in match_tc.cu (tcgen05 tf32 filter + exact f64 re-evaluation, result identical
+// The nearest-neighbour search itself is in match_tc.cu (tcgen05 fp16-split filter + fp32-difference filter + exact f64 re-evaluation, result identical
 // to an f64 brute force with lowest-index tie-break); this file holds the entry point and the mutual filter.
 #include <cub/cub.cuh>
 

@@ -4,21 +4,25 @@
 // The answer is still the f64 brute-force argmin with lowest-index ties (match.cu: feat_exact); the tensor cores only
 // decide which pairs need that exact evaluation.  For a query a and a target b the kernel computes the score
 //     s'(a,b) = a32.b32 - |b32|^2 / 2            (argmax_b s' == argmin_b |a32 - b32|^2)
-// as ONE tf32 GEMM of depth 104 using the 3xTF32 split  x32 = xh + xl  (xh = RN_tf32(x32), xl = RN_tf32(x32 - xh)):
-//     query row  : [ ah(33) | al(33) | ah(33) |  1    1    1   | 0 0 ]
-//     target row : [ bh(33) | bh(33) | bl(33) | -h0  -h1  -h2  | 0 0 ]      h = |b32|^2/2 = h0 + h1 + h2 (tf32 pieces)
-// so every product is exact in fp32 and only the al.bl term (<= 2^-22 |a||b|) is dropped.
+// as ONE fp16 GEMM of depth 112 (kind::f16, fp32 accumulate) using a 3-way split of the centred, power-of-two-scaled fp32
+// row  x32 = xh + xl  (xh = RN_fp16(x32), xl = RN_fp16(x32 - xh); 11-bit significands, |x32| <= 1024):
+//     query row  : [ ah(33) | al(33) | ah(33) | 1024  1024  1024 | 0 .. ]
+//     target row : [ bh(33) | bh(33) | bl(33) |  -h0   -h1   -h2 | 0 .. ]   h/1024 = |b32|^2/2048 = h0 + h1 + h2 (fp16 pieces)
+// so every product is exact in fp32 and only the al.bl term is dropped.
 // ONE pass over the score matrix: every epilogue thread owns a query row, keeps the running maximum m of its scores and
 // records every target b with s'(q,b) >= m - E(q) at the moment it streams by (m only grows, so the recorded set is a
-// superset of the final band [smax - E, smax]); feat_tc_eval_kernel then evaluates the recorded candidates exactly.
-// E is a rigorous bound on |(|a32|^2 - 2 s') - d_exact| (see feat_tc_err), so the exact nearest neighbour, and every
-// exact tie with it, is inside the band.
+// superset of the final band [smax - E, smax]).  E is a rigorous bound on |(|a32|^2 - 2 s') - d_exact| (see feat_tc_err),
+// so the exact nearest neighbour, and every exact tie with it, is inside the band.  feat_tc_eval_kernel then puts the
+// recorded candidates through a second, ~10^3 times tighter filter on fp32 DIFFERENCES (feat_tc_err32) and evaluates the
+// few that survive exactly in f64.
 //
 // Kernel shape (one CTA per SM, 192 threads): warps 0-3 = epilogue (TMEM lane quarter = warp id), warp 4 = bulk-copy
 // producer, warp 5 = MMA issuer.  Operand tiles are pre-packed in global memory in the exact shared-memory image of the
-// no-swizzle K-major UMMA layout (8x16B core matrices, LBO = 128 B along K, SBO = 3328 B along rows), so one
-// cp.async.bulk brings in a whole 128 x 104 tile.  The query tile stays resident; target tiles stream through a
-// 3-stage ring; two 128-column TMEM accumulators overlap the MMA of tile t+1 with the epilogue of tile t.
+// no-swizzle K-major UMMA layout (8x16B core matrices, LBO = 128 B along K, SBO = 1792 B along rows), so one
+// cp.async.bulk brings in a whole 128 x 112 tile (28 KB).  The query tile stays resident; target tiles stream through a
+// 4-stage ring; two 128-column TMEM accumulators overlap the MMA of tile t+1 with the epilogue of tile t, whose TMEM reads
+// are software-pipelined over two register buffers.  The kernel is bound by reading every fp32 score out of TMEM once
+// (64 B/clk/SM: 1024 clk per 128 x 128 tile against 448 clk of MMAs).
 #include <algorithm>
 #include <cmath>
 

@@ -29,6 +29,14 @@ class ObjectInfo:
         n = 0 if self.pointcloud is None else self.pointcloud.n()
         return f"ObjectInfo == ID: {self.id}, Names: {self.names}, Mean_Emb: {self.mean_emb.shape}, Num. Points: (3, {n})"
 
+    def __setstate__(self, state):
+        """Unpickling (ObjectMemory.load): records written by the reference carry its eager ``pcd`` / ``pcd_colors``
+        host copies (empty for a save_to_pkl record) -- views here, so they are dropped."""
+        state = dict(state)
+        state.pop("pcd", None)
+        state.pop("pcd_colors", None)
+        self.__dict__.update(state)
+
     # the reference keeps eager 3xN host copies; here they are views on demand
     @property
     def pcd(self):

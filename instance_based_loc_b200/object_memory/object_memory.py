@@ -45,6 +45,13 @@ def default_load_depth(path):
     return np.asarray(Image.open(path))
 
 
+class _MemoryUnpickler(pickle.Unpickler):
+    def find_class(self, module, name):
+        if name == "ObjectInfo" and module.split(".")[-1] == "object_info":
+            return ObjectInfo
+        return super().find_class(module, name)
+
+
 class ObjectMemory():
     def __init__(self, device, ram_pretrained_path, sam_checkpoint_path, camera_focal_lenth_x, camera_focal_lenth_y,
                  get_embeddings_func, log_enabled=True, mem_formation_bounding_box_threshold=0.3,
@@ -112,10 +119,17 @@ class ObjectMemory():
         with open(save_directory, "wb") as f:
             pickle.dump((mem, mem[-1] if mem else None), f)
 
+    @staticmethod
+    def read_pkl(load_directory):
+        """The raw content of a ``save_to_pkl`` file: ([(ObjectInfo-without-cloud, points, colors), ...], floors tuple).
+        Files written by the REFERENCE name its own class path (``object_memory.object_info.ObjectInfo``); that path
+        is mapped to this package's ObjectInfo, so a memory bank built with the reference loads without its tree."""
+        with open(load_directory, "rb") as f:
+            return _MemoryUnpickler(f).load()
+
     def load(self, load_directory):
         """:831-846."""
-        with open(load_directory, "rb") as f:
-            pklable_memory, pklable_floors = pickle.load(f)
+        pklable_memory, pklable_floors = self.read_pkl(load_directory)
 
         def conv(info_tuple):
             if info_tuple is None:

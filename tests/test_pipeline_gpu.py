@@ -69,3 +69,29 @@ def test_localise_batch_equals_sequential(cuda):
         got = om.localise_batch(frs, workers=workers, **kw)
         for (p0, a0), (p1, a1, _) in zip(seq, got):
             assert np.array_equal(p0, p1) and a0 == a1
+
+
+def test_load_reference_written_memory(cuda, tmp_path):
+    """a bank written by the reference's own save_to_pkl (tests/golden/make_memory_fixture.py) loads onto
+    the device without the reference tree; this package's writer round-trips it."""
+    import os
+    from instance_based_loc_b200.object_memory.object_memory import ObjectMemory
+    G = os.path.join(os.path.dirname(__file__), "golden")
+    exp = np.load(os.path.join(G, "ref_memory_expect.npz"))
+
+    def check(om):
+        assert len(om.memory) == 3
+        for j, o in enumerate(om.memory):
+            assert o.pointcloud.n() == len(exp[f"p{j}"]) and o.pcd.shape == (3, len(exp[f"p{j}"]))
+            assert np.array_equal(np.asarray(o.pointcloud.points), exp[f"p{j}"])
+            assert np.array_equal(np.asarray(o.pointcloud.colors), exp[f"c{j}"])
+            assert np.array_equal(np.stack(o.embeddings), exp[f"e{j}"]) and np.array_equal(o.mean_emb, exp[f"mean{j}"])
+        assert np.array_equal(np.asarray(om.floors.pointcloud.points), exp["p2"])        # reference quirk :804-824
+
+    om = ObjectMemory("cuda", None, None, 100.0, 100.0, get_embeddings_func=None, log_enabled=False)
+    om.load(os.path.join(G, "ref_memory.pkl"))
+    check(om)
+    om.save_to_pkl(str(tmp_path / "bank.pkl"))
+    om2 = ObjectMemory("cuda", None, None, 100.0, 100.0, get_embeddings_func=None, log_enabled=False)
+    om2.load(str(tmp_path / "bank.pkl"))
+    check(om2)

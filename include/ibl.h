@@ -95,6 +95,16 @@ int ibl_radius_count(const ibl_grid_t *g, double radius, int32_t *count, void *s
 /* keep[i] = count[i] > nb_points fused variant */
 int ibl_radius_outlier_mask(const ibl_grid_t *g, double radius, int32_t nb_points, uint8_t *keep, void *stream);
 
+/* Open3D PointCloud::cluster_dbscan(eps, min_points) (memory build: object_memory/object_memory.py:315,511,632) for the
+ * grid's points: labels int32[n] device, -1 = noise, clusters numbered in the order of their smallest core index (what
+ * Open3D's index-order scan produces); core iff #{j : d2(i,j) < eps*eps} (self included) >= min_points; a border point
+ * takes the smallest cluster number among the core points within eps.  The grid's cell should be >= eps (a hair larger is
+ * cheapest).  h_nclusters (host, may be NULL) receives the number of clusters; syncs when it is given. */
+int ibl_dbscan(const ibl_grid_t *g, double eps, int32_t min_points, int32_t *labels, int32_t *h_nclusters, void *stream);
+/* axis-aligned bounds of a cloud, bit-identical to numpy's pcd.min(axis=-1) / pcd.max(axis=-1) (utils/IoU_ops.py:24-28,
+ * 71-75): h_minmax6 = host double[6] (min xyz, max xyz).  n >= 1.  Syncs. */
+int ibl_bounds3(const double *pts, int64_t n, double *h_minmax6, void *stream);
+
 /* KDTreeFlann::SearchHybrid(q, radius, max_nn) (A.1) for nq queries; queries==NULL means the
  * grid's own points (row i of the output = point i).  idx int32[nq][max_nn] (-1 padded), d2
  * double[nq][max_nn] (may be NULL), cnt int32[nq].  Ascending (d2, index). */

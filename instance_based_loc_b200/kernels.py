@@ -194,6 +194,23 @@ def radius_outlier_mask(grid, radius, nb_points):
     return out
 
 
+def dbscan(grid, eps, min_points):
+    """Open3D cluster_dbscan labels (int32[n] on the device, -1 = noise) and the number of clusters."""
+    out = torch.empty(grid.pts.shape[0], dtype=torch.int32, device=grid.pts.device)
+    nc = ctypes.c_int32(0)
+    check(lib().ibl_dbscan(grid.h, float(eps), int(min_points), _p(out), ctypes.byref(nc), _stream()), "dbscan")
+    return out, int(nc.value)
+
+
+def bounds3(pts):
+    """(min xyz, max xyz) of a device cloud as two host float64[3] arrays; bit-identical to numpy's min / max."""
+    import numpy as np
+    buf = (ctypes.c_double * 6)()
+    check(lib().ibl_bounds3(_p(pts), pts.shape[0], buf, _stream()), "bounds3")
+    a = np.array(buf[:], dtype=np.float64)
+    return a[:3], a[3:]
+
+
 def knn_hybrid(grid, radius, max_nn, queries=None, want_d2=True):
     nq = grid.pts.shape[0] if queries is None else queries.shape[0]
     dev = grid.pts.device

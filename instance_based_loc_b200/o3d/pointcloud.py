@@ -251,8 +251,24 @@ class PointCloud:
         from ..utils.depth_utils import voxel_down_sample_with_colors
         return voxel_down_sample_with_colors(self, voxel_size)
 
-    def cluster_dbscan(self, *a, **k):
-        raise NotImplementedError("cluster_dbscan is memory-build only (SURVEY.md section 8(f) row N2): out of scope")
+    def cluster_dbscan(self, eps, min_points, print_progress=False):
+        """Open3D ClusterDBSCAN (memory build: object_memory.py:315,511,632): one int label per point, -1 = noise, clusters
+        numbered in the order the index-order scan meets them.  Returned as a host int32 array (the reference wraps the
+        IntVector in np.array at once); ``cluster_dbscan_device`` keeps the labels on the device."""
+        return self.cluster_dbscan_device(eps, min_points)[0].cpu().numpy()
+
+    def cluster_dbscan_device(self, eps, min_points):
+        if eps <= 0:
+            raise RuntimeError("eps must be positive")
+        if self.is_empty():
+            return torch.zeros(0, dtype=torch.int32, device=K._dev()), 0
+        return K.dbscan(self.grid(eps * 1.001), eps, min_points)
+
+    def get_min_bound(self):
+        return K.bounds3(self._p)[0] if self.n() else np.zeros(3)
+
+    def get_max_bound(self):
+        return K.bounds3(self._p)[1] if self.n() else np.zeros(3)
 
     # ------------------------------------------------------------------ neighbour plumbing
     def grid(self, cell, ring=0, max_cells=0, nnfield=0.0, nnfield_voxel=0.0):

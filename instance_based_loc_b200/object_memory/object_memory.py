@@ -25,7 +25,7 @@ from scipy.spatial.transform import Rotation
 from .. import kernels as K
 from ..o3d import registration as _reg
 from ..o3d.pointcloud import PointCloud
-from ..utils.depth_utils import get_mask_coloured_pointclouds_from_depth
+from ..utils.depth_utils import DEFAULT_OUTLIER_REMOVAL_CONFIG, get_mask_coloured_pointclouds_from_depth, transform_pointcloud
 from ..utils.fpfh_register import downsample_and_compute_fpfh, evaluate_transform, register_point_clouds
 from ..utils.similarity_volume import SimVolume
 from .object_info import ObjectInfo
@@ -43,6 +43,14 @@ def default_load_depth(path):
         return np.load(path)
     from PIL import Image
     return np.asarray(Image.open(path))
+
+
+def check_if_floor(texts):
+    """object_memory/object_finder_phrases.py:19-35 -- membership of a whole name in the list, not a substring test."""
+    for word in ("floor", "ground", "earth"):
+        if word in texts:
+            return True
+    return False
 
 
 class _MemoryUnpickler(pickle.Unpickler):
@@ -105,8 +113,93 @@ class ObjectMemory():
         return info
 
     def downsample_all_objects(self, voxel_size):
+        """:258-263."""
         for o in self.memory:
             o.downsample(voxel_size)
+        if self.floors is not None:
+            self.floors.downsample(voxel_size)
+
+    # ------------------------------------------------------------------------------------------ memory build (8(f) N2)
+    def process_image(self, rgb_image_path, depth_image_path, pose, consider_floor,
+                      outlier_removal_config=DEFAULT_OUTLIER_REMOVAL_CONFIG, add_noise=False,
+                      pose_noise={'trans': 0.0005, 'rot': 0.0005}, depth_noise=0.003, min_points=500,
+                      will_cluster_later=True, depth_factor=1.):
+        """:163-256 -- detect, back-project and outlier-filter every mask (kernels), move the clouds into the world frame
+        (``transform_pointcloud``) and append one ObjectInfo per object with at least ``min_points`` points; floor-named
+        objects are merged into ``self.floors``.  The noise option draws from numpy's global generator in the reference's
+        order (pose translation, pose rotation, then one draw per cloud), so a seeded run reproduces it."""
+        obj_phrases, embs, obj_pointclouds = self._get_object_info(rgb_image_path, depth_image_path, consider_floor,
+                                                                   outlier_removal_config, depth_factor=depth_factor)
+        if obj_phrases is None:
+            self._log("ObjectMemory.process_image did NOT find any objects")
+            return
+        self._log(f"ObjectMemory.process_image found: {obj_phrases}")
+        if add_noise:
+            pose[:3] = pose[:3] + np.random.normal(0, pose_noise['trans'], pose[:3].shape)
+            q = pose[3:] + np.random.normal(0, pose_noise['rot'], pose[3:].shape)
+            nq = np.linalg.norm(q)
+            pose[3:] = q if nq == 0 else q / nq
+            noisy = []
+            for pc in obj_pointclouds:
+                noise = np.random.normal(0, depth_noise, (pc.n(), 3))
+                noisy.append(PointCloud.from_tensors(pc._p + K.to_dev(noise), pc._c))
+            obj_pointclouds = noisy
+        transformed = [transform_pointcloud(pc, pose) for pc in obj_pointclouds]
+        for obj_phrase, obj_emb, obj_pointcloud in zip(obj_phrases, embs, transformed):
+            if obj_pointcloud.n() < min_points:
+                self._log(f"\t\tSkipping as number of points {obj_pointcloud.n()} < min_points = {min_points}.")
+                continue
+            if not will_cluster_later:
+                raise NotImplementedError("Only final clustering available currently")
+            new_obj_info = ObjectInfo(len(self.memory), obj_phrase, obj_emb, obj_pointcloud,
+                                      self.object_info_max_embeddings_num)
+            if check_if_floor(new_obj_info.names):
+                self.floors = new_obj_info if self.floors is None else self.floors + new_obj_info
+                self._log(f"\tFloor Added: {new_obj_info}")
+            else:
+                self.memory.append(new_obj_info)
+                self._log(f"\tObject Added: {new_obj_info}")
+
+    def remove_points_below_floor(self):
+        """:265-291 -- the lowest y over all objects (min/max kernel per cloud) plus ``dataset_floor_thickness`` is the cut;
+        points at or below it are dropped, objects left empty are removed (while iterating, as in the reference)."""
+        floor_height = float('inf')
+        for info in self.memory:
+            floor_height = min(float(K.bounds3(info.pointcloud._p)[0][1]), floor_height)
+        for info in self.memory:
+            keep = (info.pointcloud._p[:, 1] > floor_height + self.dataset_floor_thickness).to(torch.uint8)
+            info.pointcloud = info.pointcloud._select_mask(keep.contiguous())[0]
+            if info.pointcloud.n() == 0:
+                self.memory.remove(info)
+
+    def recluster_objects_with_dbscan(self, eps=0.2, min_points_per_cluster=300, visualize=False):
+        """:296-372 -- DBSCAN over the union of all memory clouds (``ibl_dbscan``), then every object goes to the cluster of
+        its FIRST point and the objects of one cluster are merged in memory order.  The reference finds that cluster by
+        testing, per label, whether the first point's coordinates occur among the cluster's points, and keeps the LAST
+        label that matches; exact duplicates of that point in another cluster are what the warning there is about.  The
+        same answer comes from the labels directly: the largest label over the points equal to the object's first point."""
+        self._log("Clustering using DBSCAN")
+        clouds = [o.pointcloud._p for o in self.memory]
+        union = PointCloud.from_tensors(torch.cat(clouds, dim=0).contiguous())
+        labels, n_clusters = union.cluster_dbscan_device(eps, min_points_per_cluster)
+        self._log(f"\tUnique clusters: {n_clusters}, Labels shape: {tuple(labels.shape)}")
+        new_object_assignments = np.full(len(self.memory), -1)
+        for index, c in enumerate(clouds):
+            same = (union._p == c[0:1]).all(dim=1)
+            new_object_assignments[index] = int(labels[same].max().item())
+        clustered_objects = []
+        for label in range(n_clusters):
+            objects_to_cluster = [self.memory[i] for i in range(len(self.memory)) if new_object_assignments[i] == label]
+            if not objects_to_cluster:
+                continue
+            clustered_object_info = objects_to_cluster[0]
+            for obj_info in objects_to_cluster[1:]:
+                clustered_object_info = clustered_object_info + obj_info
+            clustered_objects.append(clustered_object_info)
+        self.memory = clustered_objects
+        self._log(f"Updated memory size: {len(self.memory)}")
+        for i, obj_info in enumerate(self.memory):
+            obj_info.id = i
 
     def save_to_pkl(self, save_directory):
         """:779-826 -- [(ObjectInfo-without-cloud, points f64[N,3], colors f64[N,3]), ...], floors tuple.  The

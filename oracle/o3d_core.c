@@ -293,3 +293,51 @@ ORC_API void orc_feature_nn(const double *fa, int na, const double *fb, int nb, 
     }
     free(ta); free(tb);
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * PointCloud::ClusterDBSCAN (upstream cpp/open3d/geometry/PointCloudCluster.cpp; reference call sites
+ * object_memory/object_memory.py:315,511,632 -- memory build).
+ * The sequential loop as published: radius neighbourhoods (d2 < eps^2, self included) are precomputed, labels start
+ * at -2 (unvisited), points are scanned in index order; an unvisited point with fewer than min_points neighbours
+ * becomes noise (-1), otherwise it seeds cluster `cluster_label` and the frontier set is expanded: a noise point met
+ * from a core point is relabelled (border) and not expanded, an unvisited one is labelled and, if it is itself a core
+ * point, its unvisited neighbours join the frontier.  Open3D keeps the frontier in an unordered_set; the labels do not
+ * depend on the order it is drained in, here it is a stack with an "already queued/visited" flag per point.
+ * nbr_ptr: int64[n+1] CSR offsets, nbr_idx: int32 neighbour indices (self included).  Returns the cluster count.
+ * ------------------------------------------------------------------------------------------- */
+ORC_API int orc_dbscan(int n, const int64_t *nbr_ptr, const int32_t *nbr_idx, int min_points, int32_t *labels) {
+    int32_t *stack = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    uint8_t *seen = (uint8_t *)malloc((size_t)(n > 0 ? n : 1));   /* nbs_visited or already in nbs_next, per cluster */
+    int32_t *touched = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < n; ++i) labels[i] = -2;
+    memset(seen, 0, (size_t)(n > 0 ? n : 1));
+    int cluster_label = 0;
+    for (int idx = 0; idx < n; ++idx) {
+        if (labels[idx] != -2) continue;
+        int64_t b = nbr_ptr[idx], e = nbr_ptr[idx + 1];
+        if (e - b < min_points) { labels[idx] = -1; continue; }
+        int top = 0, nt = 0;
+        seen[idx] = 1; touched[nt++] = idx;
+        for (int64_t k = b; k < e; ++k) {
+            int q = nbr_idx[k];
+            if (!seen[q]) { seen[q] = 1; touched[nt++] = q; stack[top++] = q; }
+        }
+        labels[idx] = cluster_label;
+        while (top > 0) {
+            int nb = stack[--top];
+            if (labels[nb] == -1) labels[nb] = cluster_label;
+            if (labels[nb] != -2) continue;
+            labels[nb] = cluster_label;
+            int64_t b2 = nbr_ptr[nb], e2 = nbr_ptr[nb + 1];
+            if (e2 - b2 >= min_points)
+                for (int64_t k = b2; k < e2; ++k) {
+                    int q = nbr_idx[k];
+                    if (!seen[q]) { seen[q] = 1; touched[nt++] = q; stack[top++] = q; }
+                }
+        }
+        for (int k = 0; k < nt; ++k) seen[touched[k]] = 0;
+        cluster_label++;
+    }
+    free(stack); free(seen); free(touched);
+    return cluster_label;
+}

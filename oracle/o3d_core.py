@@ -125,6 +125,38 @@ def radius_count(points, radius, workers=-1):
     return cnt
 
 
+def radius_neighbours(points, radius, workers=-1):
+    """CSR lists of {j : d2(i,j) < r^2} (self included, ascending index) for every point, exact (A.2)."""
+    points = _f64(points)
+    n = len(points)
+    ptr = np.zeros(n + 1, np.int64)
+    if n == 0:
+        return ptr, np.zeros(0, np.int32)
+    tree = cKDTree(points)
+    cand = tree.query_ball_point(points, radius * (1 + 1e-9), workers=workers)
+    r2 = radius * radius
+    out = []
+    for i in range(n):
+        c = np.asarray(cand[i], np.int64)
+        c = np.sort(c[exact_d2(points[c], points[i]) < r2])
+        out.append(c.astype(np.int32))
+        ptr[i + 1] = ptr[i] + len(c)
+    return ptr, (np.concatenate(out) if out else np.zeros(0, np.int32))
+
+
+def cluster_dbscan(points, eps, min_points):
+    """PointCloud.cluster_dbscan (object_memory.py:315,511,632): int32 labels, -1 = noise (sequential C restatement)."""
+    points = _f64(points)
+    n = len(points)
+    labels = np.zeros(n, np.int32)
+    if n == 0:
+        return labels
+    ptr, idx = radius_neighbours(points, eps)
+    idx = _i32(idx)
+    lib().orc_dbscan(ctypes.c_int(n), _p(ptr), _p(idx), ctypes.c_int(int(min_points)), _p(labels))
+    return labels
+
+
 def remove_radius_outlier_mask(points, nb_points, radius):
     return radius_count(points, radius) > nb_points
 

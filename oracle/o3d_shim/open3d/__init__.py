@@ -134,6 +134,9 @@ class PointCloud:
         keep = _np.nonzero(_oc.remove_radius_outlier_mask(_np.asarray(self._p), nb_points, radius))[0]
         return self.select_by_index(keep), list(keep)
 
+    def cluster_dbscan(self, eps, min_points, print_progress=False):  # PointCloudCluster.cpp (memory build)
+        return [int(v) for v in _oc.cluster_dbscan(_np.asarray(self._p), eps, min_points)]
+
     def estimate_normals(self, search_param=None, fast_normal_computation=True):  # A.3
         sp = search_param or KDTreeSearchParamKNN(30)
         self._n = _Vector3dVector(_oc.estimate_normals(_np.asarray(self._p), sp.radius, sp.max_nn))

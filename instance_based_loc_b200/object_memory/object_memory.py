@@ -172,34 +172,119 @@ class ObjectMemory():
             if info.pointcloud.n() == 0:
                 self.memory.remove(info)
 
-    def recluster_objects_with_dbscan(self, eps=0.2, min_points_per_cluster=300, visualize=False):
-        """:296-372 -- DBSCAN over the union of all memory clouds (``ibl_dbscan``), then every object goes to the cluster of
-        its FIRST point and the objects of one cluster are merged in memory order.  The reference finds that cluster by
-        testing, per label, whether the first point's coordinates occur among the cluster's points, and keeps the LAST
-        label that matches; exact duplicates of that point in another cluster are what the warning there is about.  The
-        same answer comes from the labels directly: the largest label over the points equal to the object's first point."""
-        self._log("Clustering using DBSCAN")
-        clouds = [o.pointcloud._p for o in self.memory]
+    def _dbscan_merge(self, objects, eps, min_points_per_cluster):
+        """The block the reference repeats at :306-362, :498-547 and :619-668: DBSCAN over the union of the objects'
+        clouds (``ibl_dbscan``), every object goes to the cluster of its FIRST point, the objects of one cluster are merged
+        in list order, objects whose first point is noise are dropped.  The reference finds that cluster by testing, per
+        label in ascending order, whether the first point's coordinates occur among the cluster's points and keeps the LAST
+        label that matches (its "multiple labels" warning); the same answer read off the labels directly is the largest
+        label over the points equal to the object's first point."""
+        clouds = [o.pointcloud._p for o in objects]
         union = PointCloud.from_tensors(torch.cat(clouds, dim=0).contiguous())
         labels, n_clusters = union.cluster_dbscan_device(eps, min_points_per_cluster)
-        self._log(f"\tUnique clusters: {n_clusters}, Labels shape: {tuple(labels.shape)}")
-        new_object_assignments = np.full(len(self.memory), -1)
+        assignments = np.full(len(objects), -1)
         for index, c in enumerate(clouds):
             same = (union._p == c[0:1]).all(dim=1)
-            new_object_assignments[index] = int(labels[same].max().item())
-        clustered_objects = []
+            assignments[index] = int(labels[same].max().item())
+        merged = []
         for label in range(n_clusters):
-            objects_to_cluster = [self.memory[i] for i in range(len(self.memory)) if new_object_assignments[i] == label]
-            if not objects_to_cluster:
+            to_combine = [objects[i] for i in range(len(objects)) if assignments[i] == label]
+            if not to_combine:
                 continue
-            clustered_object_info = objects_to_cluster[0]
-            for obj_info in objects_to_cluster[1:]:
-                clustered_object_info = clustered_object_info + obj_info
-            clustered_objects.append(clustered_object_info)
-        self.memory = clustered_objects
-        self._log(f"Updated memory size: {len(self.memory)}")
+            combined = to_combine[0]
+            for obj_info in to_combine[1:]:
+                combined = combined + obj_info
+            merged.append(combined)
+        return merged
+
+    def _renumber(self):
         for i, obj_info in enumerate(self.memory):
             obj_info.id = i
+
+    def recluster_objects_with_dbscan(self, eps=0.2, min_points_per_cluster=300, visualize=False):
+        """:296-372."""
+        self._log("Clustering using DBSCAN")
+        self.memory = self._dbscan_merge(self.memory, eps, min_points_per_cluster)
+        self._log(f"Updated memory size: {len(self.memory)}")
+        self._renumber()
+
+    def _embedding_labels(self, embedding_distance_threshold, one_minus):
+        """The m x m part of :379-427 / :444-478: cosine matrix of the objects' mean embeddings (``1 -`` it in the
+        combined variants), shifted and scaled to [0, 1], reversed, then scikit-learn's average-linkage agglomerative
+        clustering on it -- the library and call the reference itself uses; m is the number of objects, host work."""
+        from sklearn.cluster import AgglomerativeClustering
+        all_obj_embs = np.array([obj.mean_emb for obj in self.memory])
+        norms = np.linalg.norm(all_obj_embs, axis=1, keepdims=True)
+        normalized_embeddings = all_obj_embs / norms
+        distance_matrix = np.dot(normalized_embeddings, normalized_embeddings.T)
+        if one_minus:
+            distance_matrix = 1 - distance_matrix
+        distance_matrix -= np.min(distance_matrix)
+        distance_matrix /= np.max(distance_matrix)
+        distance_matrix = 1 - distance_matrix
+        agg = AgglomerativeClustering(n_clusters=None, distance_threshold=embedding_distance_threshold,
+                                      metric='precomputed', linkage='average')
+        agg.fit(distance_matrix)
+        return agg.labels_
+
+    def _merge_by_labels(self, labels):
+        """:419-432 -- the first object of a label absorbs the later ones, result ordered by label."""
+        new_memory = [None for _ in set(labels)]
+        for new_label, old_obj_info in zip(labels, self.memory):
+            if new_memory[new_label] is None:
+                new_memory[new_label] = old_obj_info
+            else:
+                new_memory[new_label] = new_memory[new_label] + old_obj_info
+        self.memory = new_memory
+        self._renumber()
+
+    def recluster_via_agglomerative_clustering(self, distance_func=None, embedding_distance_threshold=0.4,
+                                               distance_threshold=0.1):
+        """:379-432.  Only the default distance function exists in the reference (a custom one is never called there:
+        the matrix always comes from the local ``df``), so ``distance_func`` is accepted and ignored."""
+        self._merge_by_labels(self._embedding_labels(embedding_distance_threshold, one_minus=False))
+
+    def recluster_via_combined(self, distance_func=None, embedding_distance_threshold=0.4, eps=0.4,
+                               min_points_per_cluster=150):
+        """:444-556 -- embedding clusters first, then DBSCAN inside every embedding cluster."""
+        labels = self._embedding_labels(embedding_distance_threshold, one_minus=True)
+        objects_post_dbscan = []
+        for u in set(labels):
+            objs_to_consider = [obj for i, obj in enumerate(self.memory) if labels[i] == u]
+            objects_post_dbscan = objects_post_dbscan + self._dbscan_merge(objs_to_consider, eps, min_points_per_cluster)
+        self.memory = objects_post_dbscan
+        self._renumber()
+
+    def _recluster_IoU(self, IoU_threshold=0.6, iou_func=None):
+        """:710-747 -- average-linkage clustering on 1 - IoU of every pair of objects.  The reference's pair measure is
+        ``calculate_obj_aligned_3d_IoU`` (Qhull oriented boxes + Objectron), which is not built here and raises
+        (utils/IoU_ops.py); ``iou_func(pointcloud_i, pointcloud_j)`` selects another measure, e.g. the axis-aligned
+        ``utils.IoU_ops.calculate_3d_IoU`` -- an explicit choice by the caller, never a silent substitute."""
+        from sklearn.cluster import AgglomerativeClustering
+        from ..utils.IoU_ops import calculate_obj_aligned_3d_IoU
+        f = iou_func or calculate_obj_aligned_3d_IoU
+        m = len(self.memory)
+        IoUs = np.zeros((m, m))
+        for i in range(m):
+            for j in range(i, m):
+                if i == j:
+                    IoUs[i][j] = 1
+                    continue
+                IoUs[i][j] = 1 - f(self.memory[i].pointcloud, self.memory[j].pointcloud)
+                IoUs[j][i] = IoUs[i][j]
+        agg = AgglomerativeClustering(n_clusters=None, distance_threshold=1 - IoU_threshold, metric='precomputed',
+                                      linkage='average')
+        agg.fit(IoUs)
+        self._merge_by_labels(agg.labels_)
+        for o in self.memory:
+            o._compute_means()
+
+    def recluster_via_clustering_and_IoU(self, distance_func=None, embedding_distance_threshold=0.4, eps=0.4,
+                                         min_points_per_cluster=150, IoU_threshold=0.25, iou_func=None):
+        """:562-708 -- ``_recluster_IoU`` first, then exactly ``recluster_via_combined`` (the IoU clustering after the
+        DBSCAN step is commented out in the reference)."""
+        self._recluster_IoU(IoU_threshold, iou_func=iou_func)
+        self.recluster_via_combined(distance_func, embedding_distance_threshold, eps, min_points_per_cluster)
 
     def save_to_pkl(self, save_directory):
         """:779-826 -- [(ObjectInfo-without-cloud, points f64[N,3], colors f64[N,3]), ...], floors tuple.  The

@@ -3,8 +3,10 @@ reference code in the build container on top of the oracle's open3d shim:
 
  * ``utils/IoU_ops.py`` ``calculate_3d_IoU`` / ``calculate_strict_overlap`` on seeded cloud pairs (overlapping, nested,
    touching, disjoint, one empty) -- pure numpy in the reference, so these values ARE the reference's;
- * ``ObjectMemory.remove_points_below_floor``, ``recluster_objects_with_dbscan`` and ``process_image`` (with and without
-   the noise option, numpy's global generator seeded) from object_memory/object_memory.py.  ``cluster_dbscan`` under
+ * ``ObjectMemory.remove_points_below_floor``, ``recluster_objects_with_dbscan``, ``recluster_via_agglomerative_clustering``,
+   ``recluster_via_combined``, ``_recluster_IoU`` / ``recluster_via_clustering_and_IoU`` (pair measure swapped for the
+   reference's axis-aligned ``calculate_3d_IoU``) and ``process_image`` (with and without the noise option, numpy's
+   global generator seeded) from object_memory/object_memory.py.  ``cluster_dbscan`` under
    them is the oracle's restatement of Open3D's loop (oracle/o3d_core.c: orc_dbscan), so the labels themselves are
    "parity unpinned" like the other Open3D rows; the reference's glue around them is what this pins.
 
@@ -108,13 +110,14 @@ def main():
     out["dbscan_eps_minpts"] = np.array([eps, min_pts])
     out["dbscan_labels"] = o3d_core.cluster_dbscan(union, eps, min_pts)
 
-    def dump(prefix, mem):
+    def dump(prefix, mem, colors=True):
         out[f"{prefix}_n"] = np.array(len(mem.memory))
         for j, o in enumerate(mem.memory):
             out[f"{prefix}_names{j}"] = np.array(o.names)
             out[f"{prefix}_id{j}"] = np.array(o.id)
             out[f"{prefix}_p{j}"] = np.asarray(o.pointcloud.points)
-            out[f"{prefix}_c{j}"] = np.asarray(o.pointcloud.colors)
+            if colors:
+                out[f"{prefix}_c{j}"] = np.asarray(o.pointcloud.colors)
             out[f"{prefix}_e{j}"] = np.stack([np.asarray(e) for e in o.embeddings])
 
     with contextlib.redirect_stdout(io.StringIO()):
@@ -127,6 +130,46 @@ def main():
         fill(mem, scene[:6], embs)
         mem.remove_points_below_floor()
         dump("floor", mem)
+
+    # embedding-driven reclustering: three embedding groups {mug, cup, dust}, {sofa}, {shelf, book, vase}
+    plt = sys.modules["matplotlib.pyplot"]
+    plt.imshow = lambda *a, **k: None
+    plt.colorbar = lambda *a, **k: None
+    base = rng.normal(size=(3, 16))
+    grp = [0, 0, 1, 2, 2, 2, 0]
+    embs2 = np.stack([base[k] + 0.05 * rng.normal(size=16) for k in grp]).astype(np.float32)
+    out["scene_embs2"] = embs2
+    aabb_iou = lambda a, b: iou_mod.calculate_3d_IoU(mk(a), mk(b))        # noqa: E731  (the reference's own function)
+    with contextlib.redirect_stdout(io.StringIO()):
+        mem = new_memory()
+        fill(mem, scene, embs2)
+        mem.recluster_via_agglomerative_clustering(embedding_distance_threshold=0.4)
+        dump("agg", mem, colors=False)
+
+        mem = new_memory()
+        fill(mem, scene, embs2)
+        mem.recluster_via_combined(embedding_distance_threshold=0.4, eps=eps, min_points_per_cluster=min_pts)
+        dump("comb", mem, colors=False)
+
+        # _recluster_IoU with the pair measure swapped for the reference's axis-aligned calculate_3d_IoU (the
+        # object-aligned one needs Open3D's Qhull boxes and Objectron, neither available here)
+        saved = om_mod.calculate_obj_aligned_3d_IoU
+        om_mod.calculate_obj_aligned_3d_IoU = aabb_iou
+        try:
+            mem = new_memory()
+            fill(mem, scene, embs2)
+            mem._recluster_IoU(IoU_threshold=0.05)
+            dump("iou", mem, colors=False)
+            for j, o in enumerate(mem.memory):
+                out[f"iou_mean{j}"] = np.asarray(o.mean_emb)
+
+            mem = new_memory()
+            fill(mem, scene, embs2)
+            mem.recluster_via_clustering_and_IoU(embedding_distance_threshold=0.4, eps=eps, min_points_per_cluster=min_pts,
+                                                 IoU_threshold=0.05)
+            dump("cliou", mem, colors=False)
+        finally:
+            om_mod.calculate_obj_aligned_3d_IoU = saved
 
     # process_image: a chair, a floor patch, a lamp that is too small, a second floor patch (merged into .floors)
     det = [("chair", blob(rng, (0.2, 0.1, 1.5), 600, 0.1)), ("floor", blob(rng, (0.0, -0.8, 2.0), 700, 0.3)),
@@ -153,7 +196,9 @@ def main():
 
     np.savez_compressed(OUT, **out)
     print("wrote", OUT, os.path.getsize(OUT), "bytes;", "recluster ->", int(out["recl_n"]), "objects, floor ->",
-          int(out["floor_n"]), "objects, dbscan clusters", int(out["dbscan_labels"].max()) + 1,
+          int(out["floor_n"]), "agg/comb/iou/cliou ->", [[list(out[f"{t}_names{j}"]) for j in range(int(out[f"{t}_n"]))]
+                                                          for t in ("agg", "comb", "iou", "cliou")],
+          "objects, dbscan clusters", int(out["dbscan_labels"].max()) + 1,
           "iou", [out[f"iou_val{k}"].round(4).tolist() for k in range(len(pairs))])
 
 

@@ -91,6 +91,9 @@ def test_build_golden_fixture_consistent():
     assert names == [["mug", "cup"], ["sofa"], ["shelf", "book", "vase"]]
     assert [int(g[f"recl_id{j}"]) for j in range(3)] == [0, 1, 2]
     assert np.array_equal(g["recl_p0"], np.concatenate([g["scene_p0"], g["scene_p1"]]))
+    # embedding-driven variants, as the reference's own methods left the memory
+    assert [list(g[f"agg_names{j}"]) for j in range(int(g["agg_n"]))] == [["sofa", "shelf", "book", "vase"], ["mug", "cup", "dust"]]
+    assert [list(g[f"cliou_names{j}"]) for j in range(int(g["cliou_n"]))] == [["mug", "cup"], ["sofa"], ["shelf", "book", "vase"]]
     # process_image: the small lamp is skipped, both floor patches end up in .floors
     assert [list(g[f"proc_names{j}"]) for j in range(int(g["proc_n"]))] == [["chair"]]
     assert list(g["proc_floor_names"]) == ["floor"] and len(g["proc_floor_p"]) == 700 + 650

@@ -113,13 +113,13 @@ def test_bounds_and_iou_golden(K, g):
             assert np.array_equal(got, g[f"iou_val{k}"], equal_nan=True), (k, got, g[f"iou_val{k}"])
 
 
-def _memory(K, g, n=None):
+def _memory(K, g, n=None, embs="scene_embs"):
     from instance_based_loc_b200.object_memory.object_memory import ObjectMemory
     om = ObjectMemory("cuda", None, None, 300.0, 300.0, get_embeddings_func=None, log_enabled=False,
                       dataset_floor_thickness=0.1)
     for j in range(int(g["scene_n"]) if n is None else n):
         p = g[f"scene_p{j}"]
-        om.add_object(str(g[f"scene_name{j}"]), g["scene_embs"][j], _pc(K, p, np.clip(p * 0.1 + 0.5, 0, 1)))
+        om.add_object(str(g[f"scene_name{j}"]), g[embs][j], _pc(K, p, np.clip(p * 0.1 + 0.5, 0, 1)))
     return om
 
 
@@ -133,7 +133,10 @@ def _check_memory(om, g, prefix, atol=0.0):
             assert np.array_equal(p, g[f"{prefix}_p{j}"])
         else:
             assert np.abs(p - g[f"{prefix}_p{j}"]).max() <= atol
-        assert np.array_equal(c, g[f"{prefix}_c{j}"])
+        if f"{prefix}_c{j}" in g:
+            assert np.array_equal(c, g[f"{prefix}_c{j}"])
+        else:
+            assert c.shape == p.shape
         assert np.array_equal(np.stack([np.asarray(e) for e in o.embeddings]), g[f"{prefix}_e{j}"])
 
 
@@ -169,3 +172,27 @@ def test_process_image_golden(K, g, tag, noise):
     assert np.array_equal(np.stack([np.asarray(e) for e in om.floors.embeddings]), g[f"{tag}_floor_e"])
     om.downsample_all_objects(0.05)                              # floors are down-sampled with the objects (:258-263)
     assert om.floors.pointcloud.n() < len(fp)
+
+
+@pytest.mark.parametrize("tag", ["agg", "comb", "iou", "cliou"])
+def test_embedding_and_iou_reclustering_golden(K, g, tag):
+    """recluster_via_agglomerative_clustering / recluster_via_combined / _recluster_IoU / recluster_via_clustering_and_IoU
+    against the unmodified reference methods (the IoU ones with the pair measure set to the axis-aligned calculate_3d_IoU
+    on both sides: the object-aligned measure is not built and must raise, never fall back)."""
+    from instance_based_loc_b200.utils import IoU_ops
+    eps, mp = float(g["dbscan_eps_minpts"][0]), int(g["dbscan_eps_minpts"][1])
+    om = _memory(K, g, embs="scene_embs2")
+    if tag == "agg":
+        om.recluster_via_agglomerative_clustering(embedding_distance_threshold=0.4)
+    elif tag == "comb":
+        om.recluster_via_combined(embedding_distance_threshold=0.4, eps=eps, min_points_per_cluster=mp)
+    elif tag == "iou":
+        om._recluster_IoU(IoU_threshold=0.05, iou_func=IoU_ops.calculate_3d_IoU)
+        for j, o in enumerate(om.memory):
+            assert np.array_equal(o.mean_emb, g[f"iou_mean{j}"])
+        with pytest.raises(NotImplementedError):
+            _memory(K, g, embs="scene_embs2")._recluster_IoU()
+    else:
+        om.recluster_via_clustering_and_IoU(embedding_distance_threshold=0.4, eps=eps, min_points_per_cluster=mp,
+                                            IoU_threshold=0.05, iou_func=IoU_ops.calculate_3d_IoU)
+    _check_memory(om, g, tag)

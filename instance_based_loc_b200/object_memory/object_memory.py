@@ -286,6 +286,27 @@ class ObjectMemory():
         self._recluster_IoU(IoU_threshold, iou_func=iou_func)
         self.recluster_via_combined(distance_func, embedding_distance_threshold, eps, min_points_per_cluster)
 
+    def save(self, save_directory):
+        """:750-777 -- memory.txt (the repr), combined_pointcloud.ply, combined_pointcloud_with_floor.ply and one directory
+        per object / for the floors (ObjectInfo.save: pointcloud.ply + info.pkl).  Like the reference it needs floors."""
+        from ..o3d import io as _io
+        from ..utils.depth_utils import combine_point_clouds
+        os.makedirs(save_directory, exist_ok=True)
+        individual_obj_save_dir = os.path.join(save_directory, "objects")
+        os.makedirs(individual_obj_save_dir, exist_ok=True)
+        individual_floor_save_dir = os.path.join(save_directory, "floors")
+        os.makedirs(individual_floor_save_dir, exist_ok=True)
+        with open(os.path.join(save_directory, "memory.txt"), "w") as f:
+            f.write(self.__repr__())
+        _io.write_point_cloud(os.path.join(save_directory, "combined_pointcloud.ply"),
+                              combine_point_clouds(obj.pointcloud for obj in self.memory))
+        _io.write_point_cloud(os.path.join(save_directory, "combined_pointcloud_with_floor.ply"),
+                              combine_point_clouds([obj.pointcloud for obj in self.memory] + [self.floors.pointcloud]))
+        for obj in self.memory:
+            obj.save(os.path.join(individual_obj_save_dir, f"{obj.id}"))
+        self.floors.save(os.path.join(individual_floor_save_dir, "all_floors"))
+        self._log(f"Saved memory to {save_directory}")
+
     def save_to_pkl(self, save_directory):
         """:779-826 -- [(ObjectInfo-without-cloud, points f64[N,3], colors f64[N,3]), ...], floors tuple.  The
         reference builds the floors tuple from the LAST object (bug, :804-824); reproduced."""

@@ -154,7 +154,7 @@ def test_remove_points_below_floor_golden(K, g):
 
 
 @pytest.mark.parametrize("tag,noise", [("proc", False), ("procnoise", True)])
-def test_process_image_golden(K, g, tag, noise):
+def test_process_image_golden(K, g, tag, noise, tmp_path):
     """transform_pointcloud is R p + t: BLAS order in the reference, ((R0 x + R1 y) + R2 z) + t in the kernel -> 1e-12."""
     om = _memory(K, g, n=0)
     n = int(g["det_n"])
@@ -170,6 +170,17 @@ def test_process_image_golden(K, g, tag, noise):
     fp = np.asarray(om.floors.pointcloud.points)
     assert fp.shape == g[f"{tag}_floor_p"].shape and np.abs(fp - g[f"{tag}_floor_p"]).max() <= 1e-12
     assert np.array_equal(np.stack([np.asarray(e) for e in om.floors.embeddings]), g[f"{tag}_floor_e"])
+    # ObjectMemory.save (:750-777): memory.txt, the two combined clouds, one directory per object and for the floors
+    from instance_based_loc_b200.o3d import io as o3d_io
+    om.save(str(tmp_path / "mem"))
+    assert open(tmp_path / "mem" / "memory.txt").read() == repr(om)
+    comb = o3d_io.read_point_cloud(str(tmp_path / "mem" / "combined_pointcloud_with_floor.ply"))
+    want = np.concatenate([np.asarray(o.pointcloud.points) for o in om.memory] + [fp])
+    assert np.array_equal(np.asarray(comb.points), want)
+    one = o3d_io.read_point_cloud(str(tmp_path / "mem" / "objects" / "0" / "pointcloud.ply"))
+    assert np.array_equal(np.asarray(one.points), np.asarray(om.memory[0].pointcloud.points))
+    assert os.path.exists(tmp_path / "mem" / "floors" / "all_floors" / "info.pkl")
+    assert os.path.exists(tmp_path / "mem" / "combined_pointcloud.ply")
     om.downsample_all_objects(0.05)                              # floors are down-sampled with the objects (:258-263)
     assert om.floors.pointcloud.n() < len(fp)
 

@@ -101,6 +101,16 @@ int ibl_radius_outlier_mask(const ibl_grid_t *g, double radius, int32_t nb_point
  * takes the smallest cluster number among the core points within eps.  The grid's cell should be >= eps (a hair larger is
  * cheapest).  h_nclusters (host, may be NULL) receives the number of clusters; syncs when it is given. */
 int ibl_dbscan(const ibl_grid_t *g, double eps, int32_t min_points, int32_t *labels, int32_t *h_nclusters, void *stream);
+/* Synthetic RGB-D frames (SURVEY.md 8(d) inputs / 8(f) row S1; stands in for the reference's habitat-sim rendering,
+ * hm3d_data_generation.py): one ray per pixel of an H x W pin-hole frame (focal f, pixel grid = the float32 linspace
+ * values utils/depth_utils.py:57-63 back-projects with) against the room (floor z = 0, ceiling `height`, walls at
+ * +-room) and m oriented boxes (kind 0) / ellipsoids (kind 1): half double[m][3], R double[m][9] object->world
+ * row-major, t double[m][3], all device.  h_Twc16 = HOST row-major camera->world 4x4.  Outputs (device): out_t
+ * double[H*W] camera depth of the first hit (+inf: none), out_inst int32[H*W] object id (-1: room or nothing),
+ * out_nrm double[H*W][3] world-frame surface normal.  Produces inputs only; never timed. */
+int ibl_raycast_scene(const double *h_Twc16, int32_t H, int32_t W, double f, const int32_t *kind, const double *half,
+                      const double *R, const double *t, int32_t m, double room, double height, double *out_t,
+                      int32_t *out_inst, double *out_nrm, void *stream);
 /* axis-aligned bounds of a cloud, bit-identical to numpy's pcd.min(axis=-1) / pcd.max(axis=-1) (utils/IoU_ops.py:24-28,
  * 71-75): h_minmax6 = host double[6] (min xyz, max xyz).  n >= 1.  Syncs. */
 int ibl_bounds3(const double *pts, int64_t n, double *h_minmax6, void *stream);

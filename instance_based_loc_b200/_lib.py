@@ -57,6 +57,8 @@ _PROTOS = {
     "ibl_radius_outlier_mask": (c_int, [_V, c_double, c_int32, _V, _V]),
     "ibl_dbscan": (c_int, [_V, c_double, c_int32, _V, POINTER(c_int32), _V]),
     "ibl_bounds3": (c_int, [_V, c_int64, POINTER(c_double), _V]),
+    "ibl_raycast_scene": (c_int, [POINTER(c_double), c_int32, c_int32, c_double, _V, _V, _V, _V, c_int32, c_double, c_double,
+                                  _V, _V, _V, _V]),
     "ibl_knn_hybrid": (c_int, [_V, _V, c_int64, c_double, c_int32, _V, _V, _V, _V]),
     "ibl_nn_score": (c_int, [_V, _V, c_int64, POINTER(c_double), c_double, _V, _V, POINTER(ScoreT), _V]),
     "ibl_normals": (c_int, [_V, c_int64, _V, _V, c_int32, _V, _V]),

@@ -390,6 +390,20 @@ def simvolume_topk(S, k):
 HOST_WAIT = {"auto": 0, "spin": 1, "yield": 2, "block": 3, "hybrid": 4}
 
 
+def raycast_scene(T_wc, H, W, f, kind, half, R, t, room, height):
+    """First hit per pixel of a synthetic scene: (depth t f64[H*W] (+inf = none), inst int32[H*W], normal f64[H*W,3])."""
+    dev = _dev()
+    P = int(H) * int(W)
+    out_t = torch.empty(P, dtype=F64, device=dev)
+    out_i = torch.empty(P, dtype=torch.int32, device=dev)
+    out_n = torch.empty((P, 3), dtype=F64, device=dev)
+    kind = to_dev(kind, torch.int32)
+    half, R, t = to_dev(half), to_dev(R), to_dev(t)
+    check(lib().ibl_raycast_scene(_T16(T_wc), int(H), int(W), float(f), _p(kind), _p(half), _p(R), _p(t), int(kind.shape[0]),
+                                  float(room), float(height), _p(out_t), _p(out_i), _p(out_n), _stream()), "raycast_scene")
+    return out_t, out_i, out_n
+
+
 def set_host_wait(mode):
     """How host threads wait in stream synchronisations on the current device (ibl_set_host_wait)."""
     _dev()

@@ -107,8 +107,10 @@ def camera_pose(scene, rng, n_try=200):
     raise RuntimeError("could not place a camera")
 
 
-def render(scene, T_wc, H=600, W=600, f=300.0, device="cpu", depth_noise=0.002, seed=0):
-    """Ray cast one frame -> (depth float32 [H,W] metres, rgb uint8 [H,W,3], inst int32 [H,W] (-1 = background))."""
+def render(scene, T_wc, H=600, W=600, f=300.0, device="cpu", depth_noise=0.002, seed=0, use_kernel=False, want_geometry=False):
+    """Ray cast one frame -> (depth float32 [H,W] metres, rgb uint8 [H,W,3], inst int32 [H,W] (-1 = background)).
+    ``use_kernel`` (CUDA only) computes the first hits with the ibl_raycast_scene kernel instead of tensor ops; the two
+    agree to rounding.  ``want_geometry`` returns the noise-free (hit depth f64 [P], inst [P], world normal [P,3]) instead."""
     dev = torch.device(device)
     dt = torch.float64
     hor = torch.as_tensor(np.linspace(-W / 2, W / 2, W, dtype=np.float32), dtype=dt, device=dev)
@@ -118,50 +120,58 @@ def render(scene, T_wc, H=600, W=600, f=300.0, device="cpu", depth_noise=0.002, 
     o_w = Twc[:3, 3]
     d_w = dirs_c.reshape(-1, 3) @ Twc[:3, :3].T                    # NOT normalised: parameter == camera depth Z
     P = d_w.shape[0]
-    Ro = torch.as_tensor(scene.R, dtype=dt, device=dev)            # [m,3,3]
-    to = torch.as_tensor(scene.t, dtype=dt, device=dev)
-    hf = torch.as_tensor(scene.half, dtype=dt, device=dev)
-    best = torch.full((P,), float("inf"), dtype=dt, device=dev)
-    inst = torch.full((P,), -1, dtype=torch.int32, device=dev)
-    nrm = torch.zeros((P, 3), dtype=dt, device=dev)
-    # room: floor z=0, ceiling, 4 walls
-    planes = [((0, 0, 1.0), 0.0), ((0, 0, -1.0), -scene.height), ((1.0, 0, 0), -scene.room), ((-1.0, 0, 0), -scene.room),
-              ((0, 1.0, 0), -scene.room), ((0, -1.0, 0), -scene.room)]
-    for n_, off in planes:
-        n_t = torch.as_tensor(n_, dtype=dt, device=dev)
-        den = d_w @ n_t
-        tt = (off - o_w @ n_t) / den
-        ok = (den < 0) & (tt > 1e-6) & (tt < best)
-        best = torch.where(ok, tt, best)
-        nrm = torch.where(ok[:, None], n_t.expand(P, 3), nrm)
-    for j in range(scene.m):
-        ol = (o_w - to[j]) @ Ro[j]                                  # world -> object: R^T (x - t)
-        dl = d_w @ Ro[j]
-        if scene.kind[j] == 0:                                      # box: slab method
-            inv = 1.0 / dl
-            t0 = (-hf[j] - ol) * inv
-            t1 = (hf[j] - ol) * inv
-            tn, tf = torch.minimum(t0, t1), torch.maximum(t0, t1)
-            tnear, ax = tn.max(dim=1)
-            tfar = tf.min(dim=1).values
-            ok = (tnear < tfar) & (tnear > 1e-6) & (tnear < best)
-            nl = torch.zeros((P, 3), dtype=dt, device=dev)
-            nl.scatter_(1, ax[:, None], -torch.sign(dl.gather(1, ax[:, None])))
-            tt = tnear
-        else:                                                       # ellipsoid: unit sphere in scaled coordinates
-            os_, ds_ = ol / hf[j], dl / hf[j]
-            a = (ds_ * ds_).sum(1)
-            b = (os_[None] * ds_).sum(1)
-            c = (os_ * os_).sum() - 1.0
-            disc = b * b - a * c
-            tt = (-b - torch.sqrt(disc.clamp(min=0))) / a
-            ok = (disc > 0) & (tt > 1e-6) & (tt < best)
-            hit = ol + tt[:, None] * dl
-            nl = hit / (hf[j] * hf[j])
-            nl = nl / nl.norm(dim=1, keepdim=True).clamp(min=1e-12)
-        best = torch.where(ok, tt, best)
-        inst = torch.where(ok, torch.full_like(inst, j), inst)
-        nrm = torch.where(ok[:, None], nl @ Ro[j].T, nrm)
+    if use_kernel:
+        # the same first-hit computation as ONE CUDA kernel (csrc/raycast.cu, ibl_raycast_scene): thread per pixel
+        from . import kernels as K
+        with torch.cuda.device(dev):
+            best, inst, nrm = K.raycast_scene(T_wc, H, W, f, scene.kind, scene.half, scene.R, scene.t, scene.room, scene.height)
+    else:
+        Ro = torch.as_tensor(scene.R, dtype=dt, device=dev)            # [m,3,3]
+        to = torch.as_tensor(scene.t, dtype=dt, device=dev)
+        hf = torch.as_tensor(scene.half, dtype=dt, device=dev)
+        best = torch.full((P,), float("inf"), dtype=dt, device=dev)
+        inst = torch.full((P,), -1, dtype=torch.int32, device=dev)
+        nrm = torch.zeros((P, 3), dtype=dt, device=dev)
+        # room: floor z=0, ceiling, 4 walls
+        planes = [((0, 0, 1.0), 0.0), ((0, 0, -1.0), -scene.height), ((1.0, 0, 0), -scene.room), ((-1.0, 0, 0), -scene.room),
+                  ((0, 1.0, 0), -scene.room), ((0, -1.0, 0), -scene.room)]
+        for n_, off in planes:
+            n_t = torch.as_tensor(n_, dtype=dt, device=dev)
+            den = d_w @ n_t
+            tt = (off - o_w @ n_t) / den
+            ok = (den < 0) & (tt > 1e-6) & (tt < best)
+            best = torch.where(ok, tt, best)
+            nrm = torch.where(ok[:, None], n_t.expand(P, 3), nrm)
+        for j in range(scene.m):
+            ol = (o_w - to[j]) @ Ro[j]                                  # world -> object: R^T (x - t)
+            dl = d_w @ Ro[j]
+            if scene.kind[j] == 0:                                      # box: slab method
+                inv = 1.0 / dl
+                t0 = (-hf[j] - ol) * inv
+                t1 = (hf[j] - ol) * inv
+                tn, tf = torch.minimum(t0, t1), torch.maximum(t0, t1)
+                tnear, ax = tn.max(dim=1)
+                tfar = tf.min(dim=1).values
+                ok = (tnear < tfar) & (tnear > 1e-6) & (tnear < best)
+                nl = torch.zeros((P, 3), dtype=dt, device=dev)
+                nl.scatter_(1, ax[:, None], -torch.sign(dl.gather(1, ax[:, None])))
+                tt = tnear
+            else:                                                       # ellipsoid: unit sphere in scaled coordinates
+                os_, ds_ = ol / hf[j], dl / hf[j]
+                a = (ds_ * ds_).sum(1)
+                b = (os_[None] * ds_).sum(1)
+                c = (os_ * os_).sum() - 1.0
+                disc = b * b - a * c
+                tt = (-b - torch.sqrt(disc.clamp(min=0))) / a
+                ok = (disc > 0) & (tt > 1e-6) & (tt < best)
+                hit = ol + tt[:, None] * dl
+                nl = hit / (hf[j] * hf[j])
+                nl = nl / nl.norm(dim=1, keepdim=True).clamp(min=1e-12)
+            best = torch.where(ok, tt, best)
+            inst = torch.where(ok, torch.full_like(inst, j), inst)
+            nrm = torch.where(ok[:, None], nl @ Ro[j].T, nrm)
+    if want_geometry:
+        return best, inst, nrm
     hit_w = o_w[None] + best[:, None] * d_w
     alb_tab = torch.as_tensor(np.concatenate([scene.albedo, [[0.62, 0.60, 0.57]]]), dtype=dt, device=dev)
     alb = alb_tab[inst.long()]                                      # -1 -> last row (room surfaces)

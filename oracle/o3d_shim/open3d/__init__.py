@@ -297,7 +297,73 @@ def _read_point_cloud(path, **kw):
     return r
 
 
-geometry = _types.SimpleNamespace(PointCloud=PointCloud, KDTreeSearchParamHybrid=KDTreeSearchParamHybrid,
+class OrientedBoundingBox:
+    """open3d.geometry.OrientedBoundingBox as utils/IoU_ops.py:117-135 uses it (create_from_points, get_center,
+    get_box_points) -- upstream cpp/open3d/geometry/BoundingVolume.cpp (0.17): Qhull convex hull of the points (scipy's
+    ConvexHull is the same Qhull with the same 'Qt' option; robust=True adds 'QJ'), mean and covariance of the HULL
+    VERTICES from raw cumulants, eigenvectors sorted by descending eigenvalue, third axis = first x second, extents from
+    the axis-aligned box of the rotated hull vertices.  PARITY UNPINNED like every Open3D row: the eigenvector signs and the
+    hull vertex order (rounding of the sums) are Eigen's / Qhull's upstream; the corner SET does not depend on the signs."""
+
+    def __init__(self):
+        self.center = _np.zeros(3)
+        self.R = _np.eye(3)
+        self.extent = _np.zeros(3)
+
+    @staticmethod
+    def create_from_points(points, robust=False):
+        from scipy.spatial import ConvexHull
+        pts = _np.asarray(points, _np.float64).reshape(-1, 3)
+        if len(pts) < 4:
+            raise RuntimeError("Qhull needs at least 4 points")
+        hull = ConvexHull(pts, qhull_options="QJ" if robust else None)
+        hp = pts[hull.vertices]
+        n = float(len(hp))
+        c = _np.zeros(9)
+        for q in hp:                                               # raw cumulants, accumulated point by point
+            c[0] += q[0]; c[1] += q[1]; c[2] += q[2]
+            c[3] += q[0] * q[0]; c[4] += q[0] * q[1]; c[5] += q[0] * q[2]
+            c[6] += q[1] * q[1]; c[7] += q[1] * q[2]; c[8] += q[2] * q[2]
+        c /= n
+        mean = c[:3].copy()
+        cov = _np.empty((3, 3))
+        cov[0, 0] = c[3] - c[0] * c[0]; cov[1, 1] = c[6] - c[1] * c[1]; cov[2, 2] = c[8] - c[2] * c[2]
+        cov[0, 1] = cov[1, 0] = c[4] - c[0] * c[1]
+        cov[0, 2] = cov[2, 0] = c[5] - c[0] * c[2]
+        cov[1, 2] = cov[2, 1] = c[7] - c[1] * c[2]
+        evals, R = _np.linalg.eigh(cov)                            # ascending, like Eigen's SelfAdjointEigenSolver
+        evals, R = evals.copy(), R.copy()
+        for a, b in ((1, 0), (2, 0), (2, 1)):                      # the three conditional swaps of the upstream code
+            if evals[a] > evals[b]:
+                evals[[a, b]] = evals[[b, a]]
+                R[:, [a, b]] = R[:, [b, a]]
+        R[:, 0] /= _np.linalg.norm(R[:, 0])
+        R[:, 1] /= _np.linalg.norm(R[:, 1])
+        R[:, 2] = _np.cross(R[:, 0], R[:, 1])
+        local = (hp - mean) @ R                                    # R^T (p - mean) per point
+        lo, hi = local.min(axis=0), local.max(axis=0)
+        box = OrientedBoundingBox()
+        box.center = R @ ((lo + hi) * 0.5) + mean
+        box.R = R
+        box.extent = hi - lo
+        return box
+
+    def get_center(self):
+        return self.center
+
+    def volume(self):
+        return float(self.extent[0] * self.extent[1] * self.extent[2])
+
+    def get_box_points(self):
+        x = self.R @ _np.array([self.extent[0] / 2, 0, 0])
+        y = self.R @ _np.array([0, self.extent[1] / 2, 0])
+        z = self.R @ _np.array([0, 0, self.extent[2] / 2])
+        c = self.center
+        return _Vector3dVector(_np.stack([c - x - y - z, c + x - y - z, c - x + y - z, c - x - y + z,
+                                          c + x + y + z, c - x + y + z, c + x - y + z, c + x + y - z]))
+
+
+geometry = _types.SimpleNamespace(PointCloud=PointCloud, OrientedBoundingBox=OrientedBoundingBox, KDTreeSearchParamHybrid=KDTreeSearchParamHybrid,
                                   KDTreeSearchParamKNN=KDTreeSearchParamKNN)
 utility = _types.SimpleNamespace(Vector3dVector=_Vector3dVector, Vector2iVector=_Vector2iVector)
 registration = _types.SimpleNamespace(

@@ -106,3 +106,37 @@ def test_iou_ops_module_has_the_reference_names():
         assert callable(getattr(m, name))
     with pytest.raises(NotImplementedError):
         m.calculate_obj_aligned_3d_IoU(None, None)
+
+
+def test_oracle_oriented_box_properties_and_golden():
+    """The oracle's OrientedBoundingBox (Open3D 0.17's algorithm on scipy's Qhull; oracle/o3d_shim) encloses its points,
+    has a right-handed orthonormal frame with extents in descending-variance order of the hull vertices, and reproduces the
+    fixture that tests/golden/make_obb_golden.py wrote together with the reference's calculate_obj_aligned_3d_IoU values
+    (the target for the not-yet-built GPU measure)."""
+    from oracle import ref_loader
+    o3d = ref_loader.open3d()
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "obb_iou_golden.npz"))
+    for k in range(int(g["n"])):
+        for tag in ("a", "b"):
+            pts = g[f"{tag}{k}"]
+            bb = o3d.geometry.OrientedBoundingBox.create_from_points(o3d.utility.Vector3dVector(pts))
+            assert np.allclose(bb.R.T @ bb.R, np.eye(3), atol=1e-12) and np.linalg.det(bb.R) > 0.999999
+            local = (pts - bb.get_center()) @ bb.R
+            assert (np.abs(local) <= bb.extent / 2 + 1e-9).all()
+            assert np.allclose(np.asarray(bb.get_box_points()), g[f"{tag}{k}_corners"], atol=1e-12)
+            assert np.allclose(bb.extent, g[f"{tag}{k}_extent"], atol=1e-12)
+    iou = [float(g[f"iou{k}"]) for k in range(int(g["n"]))]
+    assert iou[2] == 0.0 and abs(iou[3] - 1.0) < 1e-5 and all(0.0 <= v <= 1.0 + 1e-5 for v in iou)
+    assert 0.25 < iou[0] < 0.45                      # a (1, 2, 3) box shifted by half its short side: 1/3 for exact boxes
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/Objectron/objectron"), reason="reference tree not present")
+def test_reference_obj_aligned_iou_matches_fixture():
+    """Live in the build container: the unmodified reference function (its vendored Objectron + the oracle's boxes)."""
+    import sys
+    from oracle import ref_loader
+    sys.path.insert(0, os.path.join(ref_loader.REF, "Objectron"))
+    iou_mod = ref_loader.load("utils/IoU_ops.py")
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "obb_iou_golden.npz"))
+    for k in range(int(g["n"])):
+        assert float(iou_mod.calculate_obj_aligned_3d_IoU(g[f"a{k}"], g[f"b{k}"])) == float(g[f"iou{k}"])

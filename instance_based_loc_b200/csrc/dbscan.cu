@@ -112,6 +112,20 @@ __global__ void dbscan_label_kernel(int64_t n, const int *__restrict__ root, con
     labels[i] = (r == INT_MAX) ? -1 : rank[r];
 }
 
+// stream-ordered scratch that is returned to the pool on every exit path (the IBL_CUDA / IBL_ARG macros return early)
+struct DbscanScratch {
+    cudaStream_t st;
+    void *ptr[8];
+    int n = 0;
+    ~DbscanScratch() { for (int i = 0; i < n; ++i) ibl_free(ptr[i], st); }
+    template <class T>
+    cudaError_t get(T **out, size_t count) {
+        cudaError_t e = ibl_alloc(out, count, st);
+        if (e == cudaSuccess) ptr[n++] = *out;
+        return e;
+    }
+};
+
 IBL_API int ibl_dbscan(const ibl_grid_t *g, double eps, int32_t min_points, int32_t *labels, int32_t *h_nclusters,
                        void *stream) {
     IBL_ARG(g != nullptr && eps > 0 && (labels != nullptr || g->n == 0));
@@ -120,17 +134,17 @@ IBL_API int ibl_dbscan(const ibl_grid_t *g, double eps, int32_t min_points, int3
     const int64_t n = g->n;
     if (n == 0) return IBL_OK;
     IBL_ARG(n < (int64_t)INT_MAX);
+    DbscanScratch scr{st, {}};                                   // frees everything on every exit path
     int32_t *count = nullptr;
     int *parent = nullptr, *root = nullptr, *flag = nullptr, *rank = nullptr;
-    uint8_t *core = nullptr;
-    void *tmp = nullptr;
+    uint8_t *core = nullptr, *tmp = nullptr;
     size_t tmp_bytes = 0;
-    IBL_CUDA(ibl_alloc(&count, n, st));
-    IBL_CUDA(ibl_alloc(&parent, n, st));
-    IBL_CUDA(ibl_alloc(&root, n, st));
-    IBL_CUDA(ibl_alloc(&flag, n, st));
-    IBL_CUDA(ibl_alloc(&rank, n + 1, st));
-    IBL_CUDA(ibl_alloc(&core, n, st));
+    IBL_CUDA(scr.get(&count, n));
+    IBL_CUDA(scr.get(&parent, n));
+    IBL_CUDA(scr.get(&root, n));
+    IBL_CUDA(scr.get(&flag, n));
+    IBL_CUDA(scr.get(&rank, n + 1));
+    IBL_CUDA(scr.get(&core, n));
     int rc = ibl_radius_count(g, eps, count, stream);
     if (rc != IBL_OK) return rc;
     const int S = (int)ceil(eps * g->inv_cell + 1e-6);
@@ -148,7 +162,7 @@ IBL_API int ibl_dbscan(const ibl_grid_t *g, double eps, int32_t min_points, int3
         dbscan_walk_kernel<1><<<wb, 256, 0, st>>>(ibl_view(g), n, eps * eps, S, core, parent, root);
         IBL_LAUNCH_CHECK();
         IBL_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, flag, rank, (int)n, st));
-        IBL_CUDA(ibl_alloc(reinterpret_cast<uint8_t **>(&tmp), tmp_bytes, st));
+        IBL_CUDA(scr.get(&tmp, tmp_bytes));
         IBL_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, flag, rank, (int)n, st));
         IBL_LAUNCH_CHECK();
         dbscan_label_kernel<<<tb, 256, 0, st>>>(n, root, rank, labels);
@@ -161,8 +175,6 @@ IBL_API int ibl_dbscan(const ibl_grid_t *g, double eps, int32_t min_points, int3
         IBL_CUDA(ibl_sync(st));
         *h_nclusters = last_rank + last_flag;
     }
-    ibl_free(tmp, st); ibl_free(core, st); ibl_free(rank, st); ibl_free(flag, st); ibl_free(root, st);
-    ibl_free(parent, st); ibl_free(count, st);
     return IBL_OK;
 }
 

@@ -142,7 +142,7 @@ class ObjectMemory():
             noisy = []
             for pc in obj_pointclouds:
                 noise = np.random.normal(0, depth_noise, (pc.n(), 3))
-                noisy.append(PointCloud.from_tensors(pc._p + K.to_dev(noise), pc._c))
+                noisy.append(PointCloud.from_tensors(pc._p + K.to_dev(noise), pc._c) if pc.n() else pc)
             obj_pointclouds = noisy
         transformed = [transform_pointcloud(pc, pose) for pc in obj_pointclouds]
         for obj_phrase, obj_emb, obj_pointcloud in zip(obj_phrases, embs, transformed):

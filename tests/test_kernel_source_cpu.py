@@ -1,10 +1,17 @@
-"""CPU check of a CUDA kernel's ARITHMETIC without a GPU: the body of ``raycast_kernel`` (csrc/raycast.cu) is a
-thread-per-pixel loop with no inter-thread communication, so the very same source text compiles as host C++ once the CUDA
-qualifiers are defined away and the _rn intrinsics are mapped to plain IEEE operations (g++ -ffp-contract=off, which is
-what -fmad=false gives on the device).  One "thread" then walks every pixel and the result is compared with the
-tensor-op ray caster of instance_based_loc_b200/synth.py.  The GPU run of the same kernel is
-tests/test_z_memory_build_gpu.py::test_raycast_kernel_vs_tensor_ops.  No product code is involved: nothing here is a
-fallback, the host build lives in a temporary directory."""
+"""CPU check of CUDA kernels' ARITHMETIC without a GPU.  A thread-per-element kernel with no inter-thread communication
+compiles as host C++ from the very same source text once the CUDA qualifiers are defined away and the _rn intrinsics are
+mapped to plain IEEE operations (g++ -ffp-contract=off, which is what -fmad=false gives on the device); one "thread" at a
+time then walks the elements.
+
+ * ``raycast_kernel`` (csrc/raycast.cu) against the tensor-op ray caster of instance_based_loc_b200/synth.py
+   (GPU run of the same kernel: tests/test_z_memory_build_gpu.py::test_raycast_kernel_vs_tensor_ops);
+ * ``normals_kernel`` with ``fast_eigen3x3`` (csrc/features.cu) against the oracle's orc_normals, bit for bit
+   (GPU run: tests/test_kernels_gpu.py::test_normals, test_normals_degenerate);
+ * ``ransac_check_kernel`` (csrc/ransac.cu with rigid.cuh's Jacobi-Kabsch and ibl_common.cuh's ibl_xform) against the
+   oracle's orc_ransac_check: pass mask and transforms bit for bit (GPU run: test_ransac_check).
+
+This is a test of the source, not a fallback: the host builds live in a temporary directory and no product module can
+reach them."""
 import ctypes
 import os
 import subprocess
@@ -25,7 +32,7 @@ PRELUDE = r'''
 static inline double __dadd_rn(double a, double b) { return a + b; }
 static inline double __dsub_rn(double a, double b) { return a - b; }
 static inline double __dmul_rn(double a, double b) { return a * b; }
-struct Dim1 { int x; };
+struct Dim1 { long long x; };
 static Dim1 blockIdx{0}, threadIdx{0}, gridDim{1}, blockDim{1};
 '''
 DRIVER = r'''
@@ -68,3 +75,100 @@ def test_raycast_kernel_source_vs_tensor_ops(host_kernel, m, seed, H, W, f):
     fin = same & np.isfinite(b0)
     assert fin.sum() == 0 or np.abs(b0 - ot)[fin].max() <= 1e-9
     assert np.abs(n0 - on)[same].max() <= 1e-9
+
+
+NORMALS_DRIVER = r'''
+extern "C" void host_normals(const double *pts, long long n, const int32_t *idx, const int32_t *cnt, int max_nn, double *out) {
+    for (long long i = 0; i < n; ++i) { blockIdx.x = i; normals_kernel(pts, n, idx, cnt, max_nn, out); }   // one thread per launch
+}
+'''
+
+
+@pytest.fixture(scope="module")
+def host_normals(tmp_path_factory):
+    src = open(os.path.join(ROOT, "instance_based_loc_b200", "csrc", "features.cu")).read()
+    body = src[src.index("__device__ __forceinline__ void cross3"):src.index("IBL_API int ibl_normals")]
+    d = tmp_path_factory.mktemp("nrm_host")
+    cpp, so = str(d / "nrm_host.cpp"), str(d / "libnrm_host.so")
+    open(cpp, "w").write(PRELUDE + "#include <cstddef>\n" + body + NORMALS_DRIVER)
+    subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-o", so, cpp])
+    return ctypes.CDLL(so)
+
+
+def test_normals_kernel_source_vs_oracle(host_normals):
+    """FastEigen3x3 is branchy (largest cross product, degenerate covariances); the kernel source and the oracle's C must
+    take the same branch everywhere: compared bit for bit on a surface cloud, a plane, a line and tiny neighbourhoods."""
+    from ibl_testutil import surface_cloud
+    from oracle import o3d_core as oc
+    rng = np.random.default_rng(9)
+    plane = np.c_[rng.uniform(-1, 1, (400, 2)), np.zeros(400)]
+    line = np.c_[np.linspace(0, 1, 200), np.zeros(200), np.zeros(200)]
+    sparse = rng.uniform(-5, 5, (50, 3))                                   # < 3 neighbours: identity covariance branch
+    for pts, radius, k in ((surface_cloud(3000, 4)[0], 0.1, 30), (plane, 0.3, 30), (line, 0.05, 30), (sparse, 0.1, 30),
+                           (np.round(surface_cloud(1500, 5)[0], 2), 0.1, 12)):    # snapped to a lattice: exact ties
+        pts = np.ascontiguousarray(pts, np.float64)
+        idx, _, cnt = oc.knn_hybrid(pts, pts, radius, k)
+        idx, cnt = np.ascontiguousarray(idx, np.int32), np.ascontiguousarray(cnt, np.int32)
+        want = np.zeros((len(pts), 3))
+        oc.lib().orc_normals(pts.ctypes.data_as(ctypes.c_void_p), len(pts), idx.ctypes.data_as(ctypes.c_void_p),
+                             cnt.ctypes.data_as(ctypes.c_void_p), k, want.ctypes.data_as(ctypes.c_void_p))
+        got = np.full((len(pts), 3), np.nan)
+        p = lambda a: a.ctypes.data_as(ctypes.c_void_p)      # noqa: E731
+        host_normals.host_normals(p(pts), ctypes.c_longlong(len(pts)), p(idx), p(cnt), k, p(got))
+        assert np.array_equal(got, want)
+
+
+RANSAC_DRIVER = r'''
+extern "C" void host_ransac_check(const double *src, const double *tgt, const int32_t *corres, long long n_corres,
+                                  const int32_t *samples, long long H, double edge_thr, double dist_thr, int use_checkers,
+                                  uint8_t *pass, double *T_out) {
+    for (long long k = 0; k < H; ++k) {
+        blockIdx.x = k;
+        ransac_check_kernel(src, tgt, corres, n_corres, samples, 0ull, 0ll, H, edge_thr, dist_thr, use_checkers, pass, T_out);
+    }
+}
+'''
+
+
+@pytest.fixture(scope="module")
+def host_ransac(tmp_path_factory):
+    csrc = os.path.join(ROOT, "instance_based_loc_b200", "csrc")
+    common = open(os.path.join(csrc, "ibl_common.cuh")).read()
+    xform = common[common.index("// Transform one point with the Open3D/Eigen"):common.index("// Nearest neighbour of q within max_d")]
+    src = open(os.path.join(csrc, "ransac.cu")).read()
+    body = src[src.index("__device__ __forceinline__ void gather_sample"):src.index("IBL_API int ibl_ransac_check")]
+    d = tmp_path_factory.mktemp("ransac_host")
+    cpp, so = str(d / "ransac_host.cpp"), str(d / "libransac_host.so")
+    stub = ("#include <cstddef>\n#include <cstdint>\n"
+            f'#include "{os.path.join(csrc, "rigid.cuh")}"\n')
+    open(cpp, "w").write(PRELUDE + stub + xform + body + RANSAC_DRIVER)
+    subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-o", so, cpp])
+    return ctypes.CDLL(so)
+
+
+def test_ransac_check_kernel_source_vs_oracle(host_ransac):
+    """Edge-length test, Jacobi-Kabsch and distance test of one hypothesis per thread: pass mask and the 4x4 transform of
+    every passing hypothesis bit-equal to the oracle's orc_ransac_check on the same host-seeded triplets."""
+    from ibl_testutil import random_rigid, surface_cloud
+    from oracle import o3d_core as oc
+    rng = np.random.default_rng(21)
+    src = surface_cloud(800, 6)[0]
+    Tgt = random_rigid(3)
+    tgt = src @ Tgt[:3, :3].T + Tgt[:3, 3] + rng.normal(0, 0.002, src.shape)
+    C = 500
+    corres = np.stack([rng.integers(0, len(src), C), rng.integers(0, len(tgt), C)], 1).astype(np.int32)
+    corres[: C // 2, 1] = corres[: C // 2, 0]                          # half of them true matches
+    samples = rng.integers(0, C, (4000, 3)).astype(np.int32)
+    samples[:50, 1] = samples[:50, 0]                                   # degenerate triplets (a repeated correspondence)
+    for edge_thr, dist_thr, use in ((0.9, 0.075, 1), (0.9, 0.02, 1), (0.0, 1e9, 1)):
+        want_ok, want_T = oc.ransac_check(src, tgt, corres, samples, edge_thr, dist_thr, want_T=True)
+        ok = np.zeros(len(samples), np.uint8)
+        Ts = np.zeros((len(samples), 16))
+        p = lambda a: a.ctypes.data_as(ctypes.c_void_p)      # noqa: E731
+        s64, t64 = np.ascontiguousarray(src, np.float64), np.ascontiguousarray(tgt, np.float64)
+        host_ransac.host_ransac_check(p(s64), p(t64), p(corres), ctypes.c_longlong(C), p(samples),
+                                      ctypes.c_longlong(len(samples)), ctypes.c_double(edge_thr), ctypes.c_double(dist_thr),
+                                      use, p(ok), p(Ts))
+        assert np.array_equal(ok.astype(bool), want_ok)
+        assert want_ok.sum() > 0
+        assert np.array_equal(Ts.reshape(-1, 4, 4)[want_ok], want_T[want_ok])

@@ -8,7 +8,9 @@ time then walks the elements.
  * ``normals_kernel`` with ``fast_eigen3x3`` (csrc/features.cu) against the oracle's orc_normals, bit for bit
    (GPU run: tests/test_kernels_gpu.py::test_normals, test_normals_degenerate);
  * ``ransac_check_kernel`` (csrc/ransac.cu with rigid.cuh's Jacobi-Kabsch and ibl_common.cuh's ibl_xform) against the
-   oracle's orc_ransac_check: pass mask and transforms bit for bit (GPU run: test_ransac_check).
+   oracle's orc_ransac_check: pass mask and transforms bit for bit (GPU run: test_ransac_check);
+ * ``color_gradient_kernel`` (csrc/icp.cu with rigid.cuh's LDLT solve) against orc_color_gradient, bit for bit
+   (GPU run: test_colored_icp).
 
 This is a test of the source, not a fallback: the host builds live in a temporary directory and no product module can
 reach them."""
@@ -172,3 +174,42 @@ def test_ransac_check_kernel_source_vs_oracle(host_ransac):
         assert np.array_equal(ok.astype(bool), want_ok)
         assert want_ok.sum() > 0
         assert np.array_equal(Ts.reshape(-1, 4, 4)[want_ok], want_T[want_ok])
+
+
+GRAD_DRIVER = r'''
+extern "C" void host_color_gradient(const double *pts, const double *nrm, const double *col, long long n, const int32_t *idx,
+                                    const int32_t *cnt, int max_nn, double *grad) {
+    for (long long k = 0; k < n; ++k) { blockIdx.x = k; color_gradient_kernel(pts, nrm, col, n, idx, cnt, max_nn, grad); }
+}
+'''
+
+
+@pytest.fixture(scope="module")
+def host_grad(tmp_path_factory):
+    csrc = os.path.join(ROOT, "instance_based_loc_b200", "csrc")
+    src = open(os.path.join(csrc, "icp.cu")).read()
+    body = src[src.index("__global__ void __launch_bounds__(128) color_gradient_kernel"):src.index("IBL_API int ibl_color_gradient")]
+    d = tmp_path_factory.mktemp("grad_host")
+    cpp, so = str(d / "grad_host.cpp"), str(d / "libgrad_host.so")
+    open(cpp, "w").write(PRELUDE + f'#include <cstddef>\n#include "{os.path.join(csrc, "rigid.cuh")}"\n' + body + GRAD_DRIVER)
+    subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-o", so, cpp])
+    return ctypes.CDLL(so)
+
+
+def test_color_gradient_kernel_source_vs_oracle(host_grad):
+    """Coloured-ICP target colour gradients (A.8): 3x3 normal equations per point in neighbour-list order + LDLT solve,
+    bit-equal to the oracle's orc_color_gradient (points with fewer than 4 neighbours keep a zero gradient)."""
+    from ibl_testutil import surface_cloud
+    from oracle import o3d_core as oc
+    pts, col = surface_cloud(2500, 8)
+    pts = np.ascontiguousarray(np.concatenate([pts, [[9.0, 9.0, 9.0]]]))          # an isolated point: nn < 4 branch
+    col = np.ascontiguousarray(np.concatenate([col, [[0.5, 0.5, 0.5]]]))
+    nrm = np.ascontiguousarray(oc.estimate_normals(pts, 0.1, 30))
+    max_d = 0.075
+    want = oc.color_gradient(pts, nrm, col, max_d)
+    idx, _, cnt = oc.knn_hybrid(pts, pts, max_d * 2.0, 30)
+    idx, cnt = np.ascontiguousarray(idx, np.int32), np.ascontiguousarray(cnt, np.int32)
+    got = np.full_like(want, np.nan)
+    p = lambda a: a.ctypes.data_as(ctypes.c_void_p)          # noqa: E731
+    host_grad.host_color_gradient(p(pts), p(nrm), p(col), ctypes.c_longlong(len(pts)), p(idx), p(cnt), 30, p(got))
+    assert np.array_equal(got, want) and np.abs(want).max() > 0 and np.array_equal(want[-1], np.zeros(3))

@@ -14,4 +14,11 @@ for spec in "feat_tc:80:10" "ransac_count_kernel:6:2" "ransac_score_kernel:6:2" 
         --launch-skip $skip -c $cnt -f -o gpurun_out/full_$k $B > gpurun_out/ncu_full_$k.log 2>&1
     echo "ncu-full $k rc=$?" >> gpurun_out/ncu_launches.log
 done
+# memory-build / input kernels (outside the bench's timed region): CUDA-event probes, then one ncu --set full capture each
+timeout 120 python tools/dbscan_probe.py 200000 > gpurun_out/dbscan_probe.jsonl 2> gpurun_out/dbscan_probe.err
+timeout 60 python tools/raycast_probe.py > gpurun_out/raycast_probe.jsonl 2> gpurun_out/raycast_probe.err
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:dbscan_walk_kernel --launch-skip 2 -c 2 -f \
+    -o gpurun_out/full_dbscan_walk python tools/dbscan_probe.py 200000 > gpurun_out/ncu_full_dbscan.log 2>&1
+timeout 120 ncu --set full --clock-control none --import-source on -k regex:raycast_kernel --launch-skip 1 -c 1 -f \
+    -o gpurun_out/full_raycast python tools/raycast_probe.py > gpurun_out/ncu_full_raycast.log 2>&1
 tail -3 gpurun_out/gpu_tests.log; head -c 400 gpurun_out/bench.json; echo; tail -3 gpurun_out/bench.err; tail -6 gpurun_out/ncu_launches.log

@@ -1,0 +1,202 @@
+"""CPU check of WARP-LEVEL CUDA kernels without a GPU: a 32-lane warp is emulated by 32 host threads that run the
+kernel's own source text (csrc/*.cu, CUDA qualifiers defined away) and meet at a barrier inside every warp collective
+(``__ballot_sync``, ``__shfl_xor_sync``); ``atomicCAS`` is the host's compare-exchange, so the lock-free union-find of
+csrc/dbscan.cu runs under real concurrency.  The kernels keep their collectives warp-uniform (the same requirement the
+full-mask intrinsics have on the device), which is what makes the barrier emulation valid.
+
+ * ``radius_count_kernel`` (csrc/grid_query.cu) against the oracle's exact radius counts, counts and keep-mask variants;
+ * ``dbscan_*`` kernels (csrc/dbscan.cu: init, union pass, roots, border pass, labels) against the oracle's sequential
+   restatement of Open3D's ClusterDBSCAN, labels bit for bit.
+
+The cell-sorted grid the kernels walk is built here with numpy in the layout of csrc/grid.cu (origin = min corner,
+cell = floor((p - o) * inv), x fastest, stable order inside a cell, original index in the bits of .w).  A test of the
+source text, not a fallback: the build lives in a temporary directory.  GPU runs of the same kernels:
+tests/test_kernels_gpu.py::test_radius_count_and_outlier, tests/test_z_memory_build_gpu.py::test_dbscan_*."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "instance_based_loc_b200", "csrc")
+
+PRELUDE = r'''
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstddef>
+#include <cstdint>
+#include <cstring>
+#include <pthread.h>
+using std::max;
+using std::min;
+#define __device__
+#define __global__
+#define __forceinline__ inline
+#define __restrict__
+#define __launch_bounds__(x)
+typedef void *cudaStream_t;
+struct uint2 { unsigned x, y; };
+struct double4 { double x, y, z, w; };
+struct ibl_grid;
+static inline double __dadd_rn(double a, double b) { return a + b; }
+static inline double __dsub_rn(double a, double b) { return a - b; }
+static inline double __dmul_rn(double a, double b) { return a * b; }
+static inline long long __double_as_longlong(double d) { long long r; memcpy(&r, &d, 8); return r; }
+static inline int __popc(unsigned x) { return __builtin_popcount(x); }
+static inline int atomicCAS(int *a, int cmp, int val) {
+    __atomic_compare_exchange_n(a, &cmp, val, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST);
+    return cmp;                                            // the old value, like the device intrinsic
+}
+struct Dim1 { long long x; };
+static Dim1 blockIdx{0}, gridDim{1}, blockDim{32};
+static thread_local Dim1 threadIdx{0};
+// ---- one emulated warp: 32 host threads, a barrier inside every collective
+static pthread_barrier_t g_bar;
+static unsigned long long g_slot[32];
+static inline unsigned __ballot_sync(unsigned, bool p) {
+    g_slot[threadIdx.x] = p ? 1ull : 0ull;
+    pthread_barrier_wait(&g_bar);
+    unsigned r = 0;
+    for (int i = 0; i < 32; ++i) r |= (unsigned)g_slot[i] << i;
+    pthread_barrier_wait(&g_bar);
+    return r;
+}
+static inline int __shfl_xor_sync(unsigned, int v, int o) {
+    g_slot[threadIdx.x] = (unsigned long long)(unsigned)v;
+    pthread_barrier_wait(&g_bar);
+    int r = (int)(unsigned)g_slot[threadIdx.x ^ o];
+    pthread_barrier_wait(&g_bar);
+    return r;
+}
+template <class F>
+static void run_warp(F f) {
+    struct Arg { F *f; int lane; };
+    pthread_barrier_init(&g_bar, nullptr, 32);
+    pthread_t th[32];
+    Arg args[32];
+    for (int l = 0; l < 32; ++l) {
+        args[l] = {&f, l};
+        pthread_create(&th[l], nullptr, [](void *p) -> void * { Arg *a = (Arg *)p; threadIdx.x = a->lane; (*a->f)(); return nullptr; }, &args[l]);
+    }
+    for (int l = 0; l < 32; ++l) pthread_join(th[l], nullptr);
+    pthread_barrier_destroy(&g_bar);
+}
+'''
+
+DRIVER = r'''
+static GridView make_view(const double *sorted4, const int *cell_start, const double *o, double cell, const int *dims) {
+    GridView g;
+    memset(&g, 0, sizeof(g));
+    g.ox = o[0]; g.oy = o[1]; g.oz = o[2]; g.cell = cell; g.inv_cell = 1.0 / cell;
+    g.nx = dims[0]; g.ny = dims[1]; g.nz = dims[2];
+    g.cell_start = cell_start; g.sorted = (const double4 *)sorted4;
+    return g;
+}
+extern "C" void host_radius_count(const double *sorted4, const int *cell_start, const double *o, double cell, const int *dims,
+                                  long long n, double radius, int nb_points, int32_t *count, uint8_t *keep) {
+    GridView g = make_view(sorted4, cell_start, o, cell, dims);
+    const int S = (int)ceil(radius * g.inv_cell + 1e-6);
+    run_warp([&] { radius_count_kernel(g, n, radius * radius, S, nb_points, count, keep); });
+}
+extern "C" void host_dbscan(const double *sorted4, const int *cell_start, const double *o, double cell, const int *dims,
+                            long long n, double eps, int min_points, const int32_t *count, int32_t *labels) {
+    GridView g = make_view(sorted4, cell_start, o, cell, dims);
+    const int S = (int)ceil(eps * g.inv_cell + 1e-6);
+    int *parent = new int[n], *root = new int[n], *flag = new int[n], *rank = new int[n + 1];
+    uint8_t *core = new uint8_t[n];
+    blockDim.x = 1;                                        // thread-per-element kernels: one element per "launch"
+    for (long long i = 0; i < n; ++i) { blockIdx.x = i; dbscan_init_kernel(count, n, min_points, parent, core); }
+    blockIdx.x = 0; blockDim.x = 32;
+    run_warp([&] { dbscan_walk_kernel<0>(g, n, eps * eps, S, core, parent, root); });
+    blockDim.x = 1;
+    for (long long i = 0; i < n; ++i) { blockIdx.x = i; dbscan_root_kernel(n, core, parent, root, flag); }
+    blockIdx.x = 0; blockDim.x = 32;
+    run_warp([&] { dbscan_walk_kernel<1>(g, n, eps * eps, S, core, parent, root); });
+    rank[0] = 0;                                           // cub::DeviceScan::ExclusiveSum in the library
+    for (long long i = 0; i < n; ++i) rank[i + 1] = rank[i] + flag[i];
+    blockDim.x = 1;
+    for (long long i = 0; i < n; ++i) { blockIdx.x = i; dbscan_label_kernel(n, root, rank, labels); }
+    blockIdx.x = 0; blockDim.x = 32;
+    delete[] parent; delete[] root; delete[] flag; delete[] rank; delete[] core;
+}
+'''
+
+
+@pytest.fixture(scope="module")
+def warp_lib(tmp_path_factory):
+    common = open(os.path.join(CSRC, "ibl_common.cuh")).read()
+    views = common[common.index("struct NNFieldView {"):common.index("struct ibl_grid {")] + \
+        common[common.index("// device view passed by value to kernels"):common.index("void ibl_grid_free_field")] + \
+        common[common.index("// exact nanoflann L2"):common.index("// Transform one point with the Open3D/Eigen")]
+    gq = open(os.path.join(CSRC, "grid_query.cu")).read()
+    radius = gq[gq.index("__global__ void __launch_bounds__(256) radius_count_kernel"):gq.index("static int radius_launch")]
+    db = open(os.path.join(CSRC, "dbscan.cu")).read()
+    dbscan = db[db.index("__device__ __forceinline__ int uf_find"):db.index("// stream-ordered scratch that is returned")]
+    d = tmp_path_factory.mktemp("warp_host")
+    cpp, so = str(d / "warp_host.cpp"), str(d / "libwarp_host.so")
+    open(cpp, "w").write(PRELUDE + views + radius + dbscan + DRIVER)
+    subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-pthread", "-o", so, cpp])
+    return ctypes.CDLL(so)
+
+
+def host_grid(pts, cell):
+    """The layout of csrc/grid.cu: (sorted double[n][4] with the original index in the bits of .w, cell_start, origin, dims)."""
+    pts = np.ascontiguousarray(pts, np.float64)
+    o = pts.min(axis=0)
+    dims = (np.floor((pts.max(axis=0) - o) / cell) + 1).astype(np.int64)
+    inv = 1.0 / cell
+    c = np.clip(np.floor((pts - o) * inv).astype(np.int64), 0, dims - 1)
+    cid = (c[:, 2] * dims[1] + c[:, 1]) * dims[0] + c[:, 0]
+    order = np.argsort(cid, kind="stable")
+    ncells = int(dims.prod())
+    cell_start = np.searchsorted(cid[order], np.arange(ncells + 1)).astype(np.int32)
+    sorted4 = np.empty((len(pts), 4))
+    sorted4[:, :3] = pts[order]
+    sorted4[:, 3] = order.astype(np.int64).view(np.float64)
+    return np.ascontiguousarray(sorted4), cell_start, np.ascontiguousarray(o), dims.astype(np.int32)
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def _cloud(seed, n_blob=120, n_noise=80):
+    rng = np.random.default_rng(seed)
+    cs = rng.uniform(-1, 1, (4, 3))
+    pts = np.concatenate([c + rng.normal(0, 0.06, (n_blob, 3)) for c in cs] + [rng.uniform(-1.5, 1.5, (n_noise, 3))])
+    return np.ascontiguousarray(pts[rng.permutation(len(pts))])
+
+
+@pytest.mark.parametrize("radius,cell_factor", [(0.1, 1.001), (0.1, 0.5), (0.25, 1.7)])
+def test_radius_count_kernel_source_vs_oracle(warp_lib, radius, cell_factor):
+    from oracle import o3d_core as oc
+    pts = _cloud(1)
+    n = len(pts)
+    sorted4, cell_start, o, dims = host_grid(pts, radius * cell_factor)
+    want = oc.radius_count(pts, radius)
+    count = np.full(n, -1, np.int32)
+    warp_lib.host_radius_count(_p(sorted4), _p(cell_start), _p(o), ctypes.c_double(radius * cell_factor), _p(dims),
+                               ctypes.c_longlong(n), ctypes.c_double(radius), 0, _p(count), None)
+    assert np.array_equal(count, want)
+    keep = np.full(n, 7, np.uint8)                                  # keep-mask variant: early exit, centre-first rows
+    warp_lib.host_radius_count(_p(sorted4), _p(cell_start), _p(o), ctypes.c_double(radius * cell_factor), _p(dims),
+                               ctypes.c_longlong(n), ctypes.c_double(radius), 8, None, _p(keep))
+    assert np.array_equal(keep.astype(bool), want > 8)
+
+
+@pytest.mark.parametrize("eps,min_points,seed", [(0.08, 5, 1), (0.12, 10, 2), (0.1, 1, 3), (0.2, 40, 4)])
+def test_dbscan_kernels_source_vs_oracle(warp_lib, eps, min_points, seed):
+    from oracle import o3d_core as oc
+    pts = _cloud(seed)
+    n = len(pts)
+    sorted4, cell_start, o, dims = host_grid(pts, eps * 1.001)
+    count = oc.radius_count(pts, eps).astype(np.int32)
+    labels = np.full(n, -7, np.int32)
+    warp_lib.host_dbscan(_p(sorted4), _p(cell_start), _p(o), ctypes.c_double(eps * 1.001), _p(dims), ctypes.c_longlong(n),
+                         ctypes.c_double(eps), min_points, _p(count), _p(labels))
+    want = oc.cluster_dbscan(pts, eps, min_points)
+    assert np.array_equal(labels, want)
+    assert want.max() >= 1 or min_points >= 40

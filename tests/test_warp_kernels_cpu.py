@@ -5,6 +5,9 @@ csrc/dbscan.cu runs under real concurrency.  The kernels keep their collectives 
 full-mask intrinsics have on the device), which is what makes the barrier emulation valid.
 
  * ``radius_count_kernel`` (csrc/grid_query.cu) against the oracle's exact radius counts, counts and keep-mask variants;
+ * ``knn_kernel`` (csrc/grid_query.cu: two-pass histogram k-NN with a per-warp shared-memory candidate buffer, warp scans
+   and a warp bitonic sort) against the oracle's hybrid search: neighbour lists, squared distances and counts bit for bit,
+   grid points and external queries, both buffer capacities;
  * ``dbscan_*`` kernels (csrc/dbscan.cu: init, union pass, roots, border pass, labels) against the oracle's sequential
    restatement of Open3D's ClusterDBSCAN, labels bit for bit.
 
@@ -26,6 +29,7 @@ PRELUDE = r'''
 #include <algorithm>
 #include <climits>
 #include <cmath>
+#include <math.h>
 #include <cstddef>
 #include <cstdint>
 #include <cstring>
@@ -71,6 +75,30 @@ static inline int __shfl_xor_sync(unsigned, int v, int o) {
     pthread_barrier_wait(&g_bar);
     return r;
 }
+static inline int __shfl_sync(unsigned, int v, int src) {
+    g_slot[threadIdx.x] = (unsigned long long)(unsigned)v;
+    pthread_barrier_wait(&g_bar);
+    int r = (int)(unsigned)g_slot[src & 31];
+    pthread_barrier_wait(&g_bar);
+    return r;
+}
+static inline int __shfl_up_sync(unsigned, int v, unsigned d) {
+    g_slot[threadIdx.x] = (unsigned long long)(unsigned)v;
+    pthread_barrier_wait(&g_bar);
+    int r = threadIdx.x >= (long long)d ? (int)(unsigned)g_slot[threadIdx.x - d] : v;
+    pthread_barrier_wait(&g_bar);
+    return r;
+}
+static inline void __syncwarp() { pthread_barrier_wait(&g_bar); }
+// "shared memory": one block (= one warp) at a time, so a file-scope buffer stands in for the dynamic allocation
+#define __shared__
+#define __align__(x)
+alignas(16) unsigned char smem_raw[1 << 16];
+static inline int atomicAdd(int *a, int v) { return __atomic_fetch_add(a, v, __ATOMIC_SEQ_CST); }
+static inline int __ffs(unsigned x) { return __builtin_ffs((int)x); }
+static inline double __longlong_as_double(long long v) { double r; memcpy(&r, &v, 8); return r; }
+static inline float __fmul_rn(float a, float b) { return a * b; }
+static inline float __fsqrt_rn(float a) { return sqrtf(a); }
 template <class F>
 static void run_warp(F f) {
     struct Arg { F *f; int lane; };
@@ -100,6 +128,13 @@ extern "C" void host_radius_count(const double *sorted4, const int *cell_start, 
     GridView g = make_view(sorted4, cell_start, o, cell, dims);
     const int S = (int)ceil(radius * g.inv_cell + 1e-6);
     run_warp([&] { radius_count_kernel(g, n, radius * radius, S, nb_points, count, keep); });
+}
+extern "C" void host_knn(const double *sorted4, const int *cell_start, const double *o, double cell, const int *dims,
+                         const double *queries, long long nq, double radius, int max_nn, int32_t *idx, double *d2, int32_t *cnt) {
+    GridView g = make_view(sorted4, cell_start, o, cell, dims);
+    const double r2 = std::isfinite(radius) ? radius * radius : INFINITY;
+    if (max_nn <= 96) run_warp([&] { knn_kernel<256>(g, queries, nq, radius, r2, max_nn, idx, d2, cnt); });
+    else run_warp([&] { knn_kernel<512>(g, queries, nq, radius, r2, max_nn, idx, d2, cnt); });
 }
 extern "C" void host_dbscan(const double *sorted4, const int *cell_start, const double *o, double cell, const int *dims,
                             long long n, double eps, int min_points, const int32_t *count, int32_t *labels) {
@@ -133,11 +168,12 @@ def warp_lib(tmp_path_factory):
         common[common.index("// exact nanoflann L2"):common.index("// Transform one point with the Open3D/Eigen")]
     gq = open(os.path.join(CSRC, "grid_query.cu")).read()
     radius = gq[gq.index("__global__ void __launch_bounds__(256) radius_count_kernel"):gq.index("static int radius_launch")]
+    knn = gq[gq.index("// hybrid k-NN\nstruct KnnBuf"):gq.index("IBL_API int ibl_knn_hybrid")]
     db = open(os.path.join(CSRC, "dbscan.cu")).read()
     dbscan = db[db.index("__device__ __forceinline__ int uf_find"):db.index("// stream-ordered scratch that is returned")]
     d = tmp_path_factory.mktemp("warp_host")
     cpp, so = str(d / "warp_host.cpp"), str(d / "libwarp_host.so")
-    open(cpp, "w").write(PRELUDE + views + radius + dbscan + DRIVER)
+    open(cpp, "w").write(PRELUDE + views + radius + knn + dbscan + DRIVER)
     subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-pthread", "-o", so, cpp])
     return ctypes.CDLL(so)
 
@@ -200,3 +236,27 @@ def test_dbscan_kernels_source_vs_oracle(warp_lib, eps, min_points, seed):
     want = oc.cluster_dbscan(pts, eps, min_points)
     assert np.array_equal(labels, want)
     assert want.max() >= 1 or min_points >= 40
+
+
+@pytest.mark.parametrize("radius,k,cell", [(0.1, 30, 0.05), (0.25, 100, 0.08), (np.inf, 30, 0.1), (0.05, 12, 0.05), (0.3, 224, 0.2)])
+def test_knn_kernel_source_vs_oracle(warp_lib, radius, k, cell):
+    from ibl_testutil import surface_cloud
+    from oracle import o3d_core as oc
+    pts = np.ascontiguousarray(surface_cloud(700, 12)[0])
+    n = len(pts)
+    sorted4, cell_start, o, dims = host_grid(pts, cell)
+    rng = np.random.default_rng(0)
+    ext = np.ascontiguousarray(pts[::9] + rng.normal(0, 0.05, pts[::9].shape))
+    ext[:3] += 10.0                                                  # far outside the grid box
+    for queries in (None, ext):
+        nq = n if queries is None else len(queries)
+        idx = np.full((nq, k), -9, np.int32)
+        d2 = np.full((nq, k), -9.0)
+        cnt = np.full(nq, -9, np.int32)
+        warp_lib.host_knn(_p(sorted4), _p(cell_start), _p(o), ctypes.c_double(cell), _p(dims),
+                          None if queries is None else _p(queries), ctypes.c_longlong(nq), ctypes.c_double(radius), k,
+                          _p(idx), _p(d2), _p(cnt))
+        ridx, rd2, rcnt = oc.knn_hybrid(pts, pts if queries is None else queries, radius, k)
+        assert np.array_equal(cnt, rcnt)
+        assert np.array_equal(idx, ridx)
+        assert np.array_equal(d2, rd2)

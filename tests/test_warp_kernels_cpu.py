@@ -8,6 +8,8 @@ full-mask intrinsics have on the device), which is what makes the barrier emulat
  * ``knn_kernel`` (csrc/grid_query.cu: two-pass histogram k-NN with a per-warp shared-memory candidate buffer, warp scans
    and a warp bitonic sort) against the oracle's hybrid search: neighbour lists, squared distances and counts bit for bit,
    grid points and external queries, both buffer capacities;
+ * ``spfh_kernel`` / ``fpfh_kernel`` (csrc/features.cu: warp per point, bins across lanes, shared-memory staging) against
+   the oracle's orc_spfh / orc_fpfh (SPFH to 1e-12, FPFH within the north-star 1e-4 relative);
  * ``dbscan_*`` kernels (csrc/dbscan.cu: init, union pass, roots, border pass, labels) against the oracle's sequential
    restatement of Open3D's ClusterDBSCAN, labels bit for bit.
 
@@ -89,9 +91,18 @@ static inline int __shfl_up_sync(unsigned, int v, unsigned d) {
     pthread_barrier_wait(&g_bar);
     return r;
 }
+static inline double __shfl_sync(unsigned, double v, int src) {
+    memcpy(&g_slot[threadIdx.x], &v, 8);
+    pthread_barrier_wait(&g_bar);
+    double r;
+    memcpy(&r, &g_slot[src & 31], 8);
+    pthread_barrier_wait(&g_bar);
+    return r;
+}
+static inline double __ddiv_rn(double a, double b) { return a / b; }
 static inline void __syncwarp() { pthread_barrier_wait(&g_bar); }
 // "shared memory": one block (= one warp) at a time, so a file-scope buffer stands in for the dynamic allocation
-#define __shared__
+#define __shared__ static                                   /* one block at a time: a function-static array IS shared by the 32 lanes */
 #define __align__(x)
 alignas(16) unsigned char smem_raw[1 << 16];
 static inline int atomicAdd(int *a, int v) { return __atomic_fetch_add(a, v, __ATOMIC_SEQ_CST); }
@@ -136,6 +147,11 @@ extern "C" void host_knn(const double *sorted4, const int *cell_start, const dou
     if (max_nn <= 96) run_warp([&] { knn_kernel<256>(g, queries, nq, radius, r2, max_nn, idx, d2, cnt); });
     else run_warp([&] { knn_kernel<512>(g, queries, nq, radius, r2, max_nn, idx, d2, cnt); });
 }
+extern "C" void host_spfh_fpfh(const double *pts, const double *nrm, long long n, const int32_t *idx, const double *d2,
+                               const int32_t *cnt, int max_nn, double *spfh, double *fpfh) {
+    run_warp([&] { spfh_kernel(pts, nrm, n, idx, cnt, max_nn, spfh); });
+    run_warp([&] { fpfh_kernel(n, idx, d2, cnt, max_nn, spfh, fpfh); });
+}
 extern "C" void host_dbscan(const double *sorted4, const int *cell_start, const double *o, double cell, const int *dims,
                             long long n, double eps, int min_points, const int32_t *count, int32_t *labels) {
     GridView g = make_view(sorted4, cell_start, o, cell, dims);
@@ -169,11 +185,18 @@ def warp_lib(tmp_path_factory):
     gq = open(os.path.join(CSRC, "grid_query.cu")).read()
     radius = gq[gq.index("__global__ void __launch_bounds__(256) radius_count_kernel"):gq.index("static int radius_launch")]
     knn = gq[gq.index("// hybrid k-NN\nstruct KnnBuf"):gq.index("IBL_API int ibl_knn_hybrid")]
+    dyn = "extern __shared__ __align__(16) unsigned char smem_raw[];"          # dynamic shared memory -> the file-scope buffer
+    assert dyn in knn
+    knn = knn.replace(dyn, "")
+    ft = open(os.path.join(CSRC, "features.cu")).read()
+    feats = ft[ft.index("__device__ __forceinline__ void cross3"):ft.index("__device__ void eigvec0")] + \
+        ft[ft.index("__device__ void pair_features"):ft.index("IBL_API int ibl_spfh")] + \
+        ft[ft.index("#define FPFH_MAX_NN"):ft.index("IBL_API int ibl_fpfh")]
     db = open(os.path.join(CSRC, "dbscan.cu")).read()
     dbscan = db[db.index("__device__ __forceinline__ int uf_find"):db.index("// stream-ordered scratch that is returned")]
     d = tmp_path_factory.mktemp("warp_host")
     cpp, so = str(d / "warp_host.cpp"), str(d / "libwarp_host.so")
-    open(cpp, "w").write(PRELUDE + views + radius + knn + dbscan + DRIVER)
+    open(cpp, "w").write(PRELUDE + views + radius + knn + dbscan + feats + DRIVER)
     subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-pthread", "-o", so, cpp])
     return ctypes.CDLL(so)
 
@@ -260,3 +283,21 @@ def test_knn_kernel_source_vs_oracle(warp_lib, radius, k, cell):
         assert np.array_equal(cnt, rcnt)
         assert np.array_equal(idx, ridx)
         assert np.array_equal(d2, rd2)
+
+
+def test_spfh_fpfh_kernel_source_vs_oracle(warp_lib):
+    from ibl_testutil import surface_cloud
+    from oracle import o3d_core as oc
+    pts = np.ascontiguousarray(surface_cloud(450, 14)[0])
+    n, k, radius = len(pts), 100, 0.25
+    nrm = np.ascontiguousarray(oc.estimate_normals(pts, 0.1, 30))
+    idx, d2, cnt = oc.knn_hybrid(pts, pts, radius, k)
+    idx, d2, cnt = np.ascontiguousarray(idx, np.int32), np.ascontiguousarray(d2), np.ascontiguousarray(cnt, np.int32)
+    spfh = np.full((n, 33), np.nan)                                   # device layout: point-major double[n][33]
+    fpfh = np.full((n, 33), np.nan)
+    warp_lib.host_spfh_fpfh(_p(pts), _p(nrm), ctypes.c_longlong(n), _p(idx), _p(d2), _p(cnt), k, _p(spfh), _p(fpfh))
+    rf, rs = oc.compute_fpfh(pts, nrm, radius, k, return_spfh=True)
+    np.testing.assert_allclose(spfh.T, rs, rtol=1e-12, atol=1e-9)
+    scale = np.maximum(np.abs(rf), 1e-3 * np.abs(rf).max())
+    err = np.max(np.abs(fpfh.T - rf) / scale)
+    assert err <= 1e-4, err

@@ -1,7 +1,7 @@
 """CPU check of WARP-LEVEL CUDA kernels without a GPU: a 32-lane warp is emulated by 32 host threads that run the
 kernel's own source text (csrc/*.cu, CUDA qualifiers defined away) and meet at a barrier inside every warp collective
 (``__ballot_sync``, ``__shfl_xor_sync``); ``atomicCAS`` is the host's compare-exchange, so the lock-free union-find of
-csrc/dbscan.cu runs under real concurrency.  The kernels keep their collectives warp-uniform (the same requirement the
+csrc/dbscan.cu runs under real concurrency (its union pass, which has no collectives, runs as 8 warps = 256 host threads).  The kernels keep their collectives warp-uniform (the same requirement the
 full-mask intrinsics have on the device), which is what makes the barrier emulation valid.
 
  * ``radius_count_kernel`` (csrc/grid_query.cu) against the oracle's exact radius counts, counts and keep-mask variants;
@@ -110,6 +110,19 @@ static inline int __ffs(unsigned x) { return __builtin_ffs((int)x); }
 static inline double __longlong_as_double(long long v) { double r; memcpy(&r, &v, 8); return r; }
 static inline float __fmul_rn(float a, float b) { return a * b; }
 static inline float __fsqrt_rn(float a) { return sqrtf(a); }
+// a block of `nthreads` host threads for kernels WITHOUT collectives (nobody waits at the barrier): several warps at once
+template <class F>
+static void run_block_no_collectives(int nthreads, F f) {
+    struct Arg { F *f; int t; };
+    pthread_t *th = new pthread_t[nthreads];
+    Arg *args = new Arg[nthreads];
+    for (int t = 0; t < nthreads; ++t) {
+        args[t] = {&f, t};
+        pthread_create(&th[t], nullptr, [](void *p) -> void * { Arg *a = (Arg *)p; threadIdx.x = a->t; (*a->f)(); return nullptr; }, &args[t]);
+    }
+    for (int t = 0; t < nthreads; ++t) pthread_join(th[t], nullptr);
+    delete[] th; delete[] args;
+}
 template <class F>
 static void run_warp(F f) {
     struct Arg { F *f; int lane; };
@@ -160,8 +173,8 @@ extern "C" void host_dbscan(const double *sorted4, const int *cell_start, const 
     uint8_t *core = new uint8_t[n];
     blockDim.x = 1;                                        // thread-per-element kernels: one element per "launch"
     for (long long i = 0; i < n; ++i) { blockIdx.x = i; dbscan_init_kernel(count, n, min_points, parent, core); }
-    blockIdx.x = 0; blockDim.x = 32;
-    run_warp([&] { dbscan_walk_kernel<0>(g, n, eps * eps, S, core, parent, root); });
+    blockIdx.x = 0; blockDim.x = 256;                      // the union pass has no collectives: 8 warps race on the union-find
+    run_block_no_collectives(256, [&] { dbscan_walk_kernel<0>(g, n, eps * eps, S, core, parent, root); });
     blockDim.x = 1;
     for (long long i = 0; i < n; ++i) { blockIdx.x = i; dbscan_root_kernel(n, core, parent, root, flag); }
     blockIdx.x = 0; blockDim.x = 32;

@@ -8,6 +8,8 @@ full-mask intrinsics have on the device), which is what makes the barrier emulat
  * ``knn_kernel`` (csrc/grid_query.cu: two-pass histogram k-NN with a per-warp shared-memory candidate buffer, warp scans
    and a warp bitonic sort) against the oracle's hybrid search: neighbour lists, squared distances and counts bit for bit,
    grid points and external queries, both buffer capacities;
+ * ``ibl_nn1_thread`` (csrc/ibl_common.cuh: the per-thread exact nearest neighbour within max_d by Chebyshev ring
+   expansion that nn_score / RANSAC scoring / ICP use when no candidate field is attached) against the oracle's nn1;
  * ``spfh_kernel`` / ``fpfh_kernel`` (csrc/features.cu: warp per point, bins across lanes, shared-memory staging) against
    the oracle's orc_spfh / orc_fpfh (SPFH to 1e-12, FPFH within the north-star 1e-4 relative);
  * ``dbscan_*`` kernels (csrc/dbscan.cu: init, union pass, roots, border pass, labels) against the oracle's sequential
@@ -160,6 +162,12 @@ extern "C" void host_knn(const double *sorted4, const int *cell_start, const dou
     if (max_nn <= 96) run_warp([&] { knn_kernel<256>(g, queries, nq, radius, r2, max_nn, idx, d2, cnt); });
     else run_warp([&] { knn_kernel<512>(g, queries, nq, radius, r2, max_nn, idx, d2, cnt); });
 }
+extern "C" void host_nn1(const double *sorted4, const int *cell_start, const double *o, double cell, const int *dims,
+                         const double *queries, long long nq, double max_d, int32_t *idx, double *d2) {
+    GridView g = make_view(sorted4, cell_start, o, cell, dims);          // no ring field, no candidate field: the ring walk
+    for (long long i = 0; i < nq; ++i)
+        idx[i] = ibl_nn1_thread(g, queries[3 * i], queries[3 * i + 1], queries[3 * i + 2], max_d, max_d * max_d, d2[i]);
+}
 extern "C" void host_spfh_fpfh(const double *pts, const double *nrm, long long n, const int32_t *idx, const double *d2,
                                const int32_t *cnt, int max_nn, double *spfh, double *fpfh) {
     run_warp([&] { spfh_kernel(pts, nrm, n, idx, cnt, max_nn, spfh); });
@@ -194,7 +202,7 @@ def warp_lib(tmp_path_factory):
     common = open(os.path.join(CSRC, "ibl_common.cuh")).read()
     views = common[common.index("struct NNFieldView {"):common.index("struct ibl_grid {")] + \
         common[common.index("// device view passed by value to kernels"):common.index("void ibl_grid_free_field")] + \
-        common[common.index("// exact nanoflann L2"):common.index("// Transform one point with the Open3D/Eigen")]
+        common[common.index("// exact nanoflann L2"):common.index("// bounding box: per-block partial min/max")]
     gq = open(os.path.join(CSRC, "grid_query.cu")).read()
     radius = gq[gq.index("__global__ void __launch_bounds__(256) radius_count_kernel"):gq.index("static int radius_launch")]
     knn = gq[gq.index("// hybrid k-NN\nstruct KnnBuf"):gq.index("IBL_API int ibl_knn_hybrid")]
@@ -314,3 +322,23 @@ def test_spfh_fpfh_kernel_source_vs_oracle(warp_lib):
     scale = np.maximum(np.abs(rf), 1e-3 * np.abs(rf).max())
     err = np.max(np.abs(fpfh.T - rf) / scale)
     assert err <= 1e-4, err
+
+
+@pytest.mark.parametrize("max_d,cell", [(0.075, 0.075), (0.02, 0.05), (0.3, 0.1)])
+def test_nn1_ring_walk_source_vs_oracle(warp_lib, max_d, cell):
+    from ibl_testutil import random_rigid, surface_cloud
+    from oracle import o3d_core as oc
+    tgt = np.ascontiguousarray(surface_cloud(1500, 20)[0])
+    T = random_rigid(4, max_angle=0.05, max_t=0.03)
+    src = surface_cloud(900, 21)[0] @ T[:3, :3].T + T[:3, 3]
+    src = np.ascontiguousarray(np.concatenate([src, tgt[:50], tgt[:5] + 7.0]))       # exact hits and far-away queries
+    sorted4, cell_start, o, dims = host_grid(tgt, cell)
+    idx = np.full(len(src), -9, np.int32)
+    d2 = np.full(len(src), -9.0)
+    warp_lib.host_nn1(_p(sorted4), _p(cell_start), _p(o), ctypes.c_double(cell), _p(dims), _p(src),
+                      ctypes.c_longlong(len(src)), ctypes.c_double(max_d), _p(idx), _p(d2))
+    ridx, rd2 = oc.nn1(tgt, src, max_d)
+    assert np.array_equal(idx, ridx)
+    hit = ridx >= 0
+    assert hit.sum() > 50 and (~hit).sum() >= 5
+    assert np.array_equal(d2[hit], rd2[hit])

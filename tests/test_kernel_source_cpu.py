@@ -10,7 +10,10 @@ time then walks the elements.
  * ``ransac_check_kernel`` (csrc/ransac.cu with rigid.cuh's Jacobi-Kabsch and ibl_common.cuh's ibl_xform) against the
    oracle's orc_ransac_check: pass mask and transforms bit for bit (GPU run: test_ransac_check);
  * ``color_gradient_kernel`` (csrc/icp.cu with rigid.cuh's LDLT solve) against orc_color_gradient, bit for bit
-   (GPU run: test_colored_icp).
+   (GPU run: test_colored_icp);
+ * the four voxel kernels of csrc/voxel.cu (keys, segment heads, first occurrences, sequential means; the device sort and
+   select replaced by std::stable_sort / a loop) against the REFERENCE's own voxel_down_sample_with_colors golden
+   outputs, bit for bit (GPU run: test_voxel_golden, test_voxel_vs_port).
 
 This is a test of the source, not a fallback: the host builds live in a temporary directory and no product module can
 reach them."""
@@ -213,3 +216,96 @@ def test_color_gradient_kernel_source_vs_oracle(host_grad):
     p = lambda a: a.ctypes.data_as(ctypes.c_void_p)          # noqa: E731
     host_grad.host_color_gradient(p(pts), p(nrm), p(col), ctypes.c_longlong(len(pts)), p(idx), p(cnt), 30, p(got))
     assert np.array_equal(got, want) and np.abs(want).max() > 0 and np.array_equal(want[-1], np.zeros(3))
+
+
+VOXEL_DRIVER = r'''
+#include <algorithm>
+#include <numeric>
+#include <vector>
+// the host side of ibl_voxel_downsample (csrc/voxel.cu) with std::stable_sort / a loop in place of the cub device sort and
+// select; the four kernels are the library's source text, one element per "launch"
+extern "C" long long host_voxel(const double *pts, const double *cols, const double *nrm, long long n, double voxel,
+                                double *out_pts, double *out_cols, double *out_nrm, int32_t *vox_id, int64_t *out_keys) {
+    double mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (long long i = 0; i < n; ++i)
+        for (int a = 0; a < 3; ++a) { mn[a] = fmin(mn[a], pts[3 * i + a]); mx[a] = fmax(mx[a], pts[3 * i + a]); }
+    VoxRange vr;
+    unsigned long long r[3];
+    for (int a = 0; a < 3; ++a) {
+        double lo = floor(mn[a] / voxel), hi = floor(mx[a] / voxel);
+        vr.kmin[a] = (long long)lo;
+        r[a] = (unsigned long long)((long long)hi - (long long)lo + 1);
+    }
+    vr.r0 = r[0]; vr.r1 = r[1];
+    std::vector<unsigned long long> key(n), key2(n);
+    std::vector<int> idx(n), idx2(n);
+    std::vector<uint8_t> flag(n);
+    blockDim.x = 1;
+    for (long long i = 0; i < n; ++i) { blockIdx.x = i; vox_key_kernel(pts, n, voxel, vr, key.data(), idx.data(), out_keys); }
+    std::vector<int> perm(n);
+    std::iota(perm.begin(), perm.end(), 0);
+    std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) { return key[a] < key[b]; });      // radix sort is stable
+    for (long long i = 0; i < n; ++i) { key2[i] = key[perm[i]]; idx2[i] = idx[perm[i]]; }
+    for (long long i = 0; i < n; ++i) { blockIdx.x = i; vox_head_kernel(key2.data(), n, flag.data()); }
+    std::vector<int> head_pos;
+    for (long long i = 0; i < n; ++i) if (flag[i]) head_pos.push_back((int)i);                       // DeviceSelect::Flagged
+    const int nseg = (int)head_pos.size();
+    std::vector<int> first_idx(nseg), seg(nseg), seg2(nseg);
+    for (int s = 0; s < nseg; ++s) { blockIdx.x = s; vox_first_kernel(head_pos.data(), nseg, idx2.data(), first_idx.data(), seg.data()); }
+    std::vector<int> p2(nseg);
+    std::iota(p2.begin(), p2.end(), 0);
+    std::stable_sort(p2.begin(), p2.end(), [&](int a, int b) { return first_idx[a] < first_idx[b]; });
+    for (int s = 0; s < nseg; ++s) seg2[s] = seg[p2[s]];
+    for (int v = 0; v < nseg; ++v) {
+        blockIdx.x = v;
+        vox_mean_kernel(seg2.data(), head_pos.data(), nseg, n, idx2.data(), pts, cols, nrm, out_pts, cols ? out_cols : nullptr,
+                        nrm ? out_nrm : nullptr, vox_id);
+    }
+    blockIdx.x = 0;
+    return nseg;
+}
+'''
+
+
+@pytest.fixture(scope="module")
+def host_voxel(tmp_path_factory):
+    src = open(os.path.join(ROOT, "instance_based_loc_b200", "csrc", "voxel.cu")).read()
+    body = src[src.index("struct VoxRange"):src.index("IBL_API int64_t ibl_voxel_downsample")]
+    d = tmp_path_factory.mktemp("vox_host")
+    cpp, so = str(d / "vox_host.cpp"), str(d / "libvox_host.so")
+    pre = PRELUDE + "#include <cstddef>\nstatic inline double __ddiv_rn(double a, double b) { return a / b; }\n"
+    open(cpp, "w").write(pre + body + VOXEL_DRIVER)
+    subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-o", so, cpp])
+    L = ctypes.CDLL(so)
+    L.host_voxel.restype = ctypes.c_longlong
+    return L
+
+
+def _voxel(L, pts, cols, nrm, voxel):
+    p = lambda a: None if a is None else a.ctypes.data_as(ctypes.c_void_p)       # noqa: E731
+    pts = np.ascontiguousarray(pts, np.float64)
+    cols = None if cols is None else np.ascontiguousarray(cols, np.float64)
+    nrm = None if nrm is None else np.ascontiguousarray(nrm, np.float64)
+    n = len(pts)
+    op, oc, on = np.empty_like(pts), np.empty_like(pts), np.empty_like(pts)
+    vid, keys = np.empty(n, np.int32), np.empty((n, 3), np.int64)
+    nv = L.host_voxel(p(pts), p(cols), p(nrm), ctypes.c_longlong(n), ctypes.c_double(voxel), p(op), p(oc), p(on), p(vid), p(keys))
+    return op[:nv], oc[:nv], on[:nv], vid, keys
+
+
+def test_voxel_kernels_source_vs_reference_golden(host_voxel, golden):
+    """Row a3: voxel keys, first-occurrence order and the sequential means of the kernels' source text against the
+    REFERENCE's own voxel_down_sample_with_colors outputs (tests/golden/make_golden.py), bit for bit; then normals and
+    voxel ids against the numpy port on a second cloud."""
+    from ibl_testutil import surface_cloud
+    from oracle import ref_port
+    g = golden
+    op, oc, _, _, keys = _voxel(host_voxel, g["vox_pts"], g["vox_cols"], None, float(g["vox_size"]))
+    assert np.array_equal(keys, g["vox_keys"])
+    assert np.array_equal(op, g["vox_out_pts"]) and np.array_equal(oc, g["vox_out_cols"])
+    p, c = surface_cloud(4000, 31)
+    nr = np.random.default_rng(31).normal(size=p.shape)
+    op, oc, on, vid, _ = _voxel(host_voxel, p, c, nr, 0.03)
+    rp, rc, rn, rvid = ref_port.voxel_down_sample(p, c, 0.03, nr)
+    assert np.array_equal(op, rp) and np.array_equal(oc, rc) and np.array_equal(vid, rvid)
+    assert np.allclose(on, rn, rtol=0, atol=1e-15)

@@ -5,6 +5,9 @@ use them for), the device-wide scan between the two kernels by a host loop.  The
 golden vectors that tests/golden/make_golden.py produced by running the REFERENCE's own numpy
 (utils/depth_utils.py:46-90,176-206) -- so the float32 / float64 rounding sequence of the kernel source is pinned against
 the reference without a GPU.  GPU run of the same kernels: tests/test_kernels_gpu.py::test_backproject_*.
+``seqsum3_kernel`` (the column means of row a4 / a12: double-buffered shared-memory tiles, three serial add chains, __syncthreads)
+is run the same way and compared bit for bit with ``np.mean(points, axis=0)`` itself -- the call the reference makes
+(object_memory/object_memory.py:1030-1031).
 A test of the source text, not a fallback: the build lives in a temporary directory."""
 import ctypes
 import os
@@ -22,6 +25,8 @@ PRELUDE = r'''
 #include <cstdint>
 #include <cstring>
 #include <pthread.h>
+#include <algorithm>
+using std::min;
 #define __device__
 #define __global__
 #define __forceinline__ inline
@@ -34,12 +39,14 @@ struct uchar4 { unsigned char x, y, z, w; };
 static inline float __fmul_rn(float a, float b) { return a * b; }
 static inline float __fdiv_rn(float a, float b) { return a / b; }
 static inline double __dmul_rn(double a, double b) { return a * b; }
+static inline double __dadd_rn(double a, double b) { return a + b; }
 static inline double __ddiv_rn(double a, double b) { return a / b; }
 struct Dim2 { long long x, y; };
 static Dim2 blockIdx{0, 0}, gridDim{1, 1}, blockDim{256, 1};
 static thread_local Dim2 threadIdx{0, 0};
 static pthread_barrier_t g_bar;
 static int g_vals[256];
+static inline void __syncthreads() { pthread_barrier_wait(&g_bar); }
 namespace cub {
 template <class T, int N>
 struct BlockReduce {
@@ -113,6 +120,12 @@ static long long backproject_host(const DT *depth, const uint8_t *rgb, const uin
     delete[] counts; delete[] offs;
     return total;
 }
+extern "C" void host_mean3(const double *pts, long long n, double *mean) {
+    double sums[3] = {0, 0, 0};
+    blockIdx.x = 0; blockIdx.y = 0;
+    run_block([&] { seqsum3_kernel(pts, n, sums); });
+    for (int a = 0; a < 3; ++a) mean[a] = sums[a] / (double)n;          // ibl_mean3's host division
+}
 extern "C" long long host_backproject(const void *depth, int is64, const uint8_t *rgb, const uint8_t *masks, int n_masks, int H,
                                       int W, const float *hor, const float *ver, double fx, double fy, double *out_pts,
                                       double *out_cols, int64_t *h_offsets) {
@@ -128,7 +141,8 @@ def block_lib(tmp_path_factory):
     body = src[src.index("template <typename DT>\n__device__ __forceinline__ void load4"):src.index("template <typename DT>\nstatic int backproject_impl")]
     d = tmp_path_factory.mktemp("block_host")
     cpp, so = str(d / "block_host.cpp"), str(d / "libblock_host.so")
-    open(cpp, "w").write(PRELUDE + body + DRIVER)
+    mean = src[src.index("#define MEAN_TILE 1024"):src.index("IBL_API int ibl_mean3")]
+    open(cpp, "w").write(PRELUDE + body + mean + DRIVER)
     subprocess.check_call(["g++", "-std=c++17", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-pthread", "-o", so, cpp])
     L = ctypes.CDLL(so)
     L.host_backproject.restype = ctypes.c_longlong
@@ -183,3 +197,13 @@ def test_backproject_kernel_source_ragged_sizes(block_lib):
         assert offs == list(np.cumsum([0] + [len(p) for p, _ in ref])) and offs[3] == offs[2]
         assert np.array_equal(pts, np.concatenate([p for p, _ in ref]))
         assert np.array_equal(cols, np.concatenate([q for _, q in ref]))
+
+
+@pytest.mark.parametrize("n", [1, 2, 1023, 1024, 1025, 5000])
+def test_mean_kernel_source_vs_numpy(block_lib, n):
+    """np.mean over axis 0 of a C-contiguous [N,3] array adds the rows one by one; the kernel must give the same bits."""
+    rng = np.random.default_rng(n)
+    pts = np.ascontiguousarray(rng.normal(size=(n, 3)) * np.array([1.0, 1e3, 1e-3]) + np.array([2.0, -700.0, 0.01]))
+    got = np.full(3, np.nan)
+    block_lib.host_mean3(_p(pts), ctypes.c_longlong(n), _p(got))
+    assert np.array_equal(got, np.mean(pts, axis=0))

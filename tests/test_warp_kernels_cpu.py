@@ -10,6 +10,9 @@ full-mask intrinsics have on the device), which is what makes the barrier emulat
    grid points and external queries, both buffer capacities;
  * ``ibl_nn1_thread`` (csrc/ibl_common.cuh: the per-thread exact nearest neighbour within max_d by Chebyshev ring
    expansion that nn_score / RANSAC scoring / ICP use when no candidate field is attached) against the oracle's nn1;
+ * ``nn_score_kernel`` + ``score_final_kernel`` (csrc/grid_query.cu: evaluate_registration -- transform, exact NN, fixed
+   shuffle-tree block reduction over 8 warps, __syncthreads) as a 256-thread block: correspondences and inlier count
+   bit-exact, err2 to 1e-12 (the oracle sums in index order);
  * ``spfh_kernel`` / ``fpfh_kernel`` (csrc/features.cu: warp per point, bins across lanes, shared-memory staging) against
    the oracle's orc_spfh / orc_fpfh (SPFH to 1e-12, FPFH within the north-star 1e-4 relative);
  * ``dbscan_*`` kernels (csrc/dbscan.cu: init, union pass, roots, border pass, labels) against the oracle's sequential
@@ -62,47 +65,68 @@ struct Dim1 { long long x; };
 static Dim1 blockIdx{0}, gridDim{1}, blockDim{32};
 static thread_local Dim1 threadIdx{0};
 // ---- one emulated warp: 32 host threads, a barrier inside every collective
-static pthread_barrier_t g_bar;
+static pthread_barrier_t g_bar;                            // the single emulated warp of run_warp
 static unsigned long long g_slot[32];
+static pthread_barrier_t g_wbar[8], g_bbar;                // run_block256: one barrier per warp + the block barrier
+static unsigned long long g_wslot[8][32];
+static thread_local pthread_barrier_t *t_bar = &g_bar;     // the barrier / exchange slots of the calling lane's warp
+static thread_local unsigned long long *t_slot = g_slot;
+#define LANE ((int)(threadIdx.x & 31))
 static inline unsigned __ballot_sync(unsigned, bool p) {
-    g_slot[threadIdx.x] = p ? 1ull : 0ull;
-    pthread_barrier_wait(&g_bar);
+    t_slot[LANE] = p ? 1ull : 0ull;
+    pthread_barrier_wait(t_bar);
     unsigned r = 0;
-    for (int i = 0; i < 32; ++i) r |= (unsigned)g_slot[i] << i;
-    pthread_barrier_wait(&g_bar);
+    for (int i = 0; i < 32; ++i) r |= (unsigned)t_slot[i] << i;
+    pthread_barrier_wait(t_bar);
     return r;
 }
 static inline int __shfl_xor_sync(unsigned, int v, int o) {
-    g_slot[threadIdx.x] = (unsigned long long)(unsigned)v;
-    pthread_barrier_wait(&g_bar);
-    int r = (int)(unsigned)g_slot[threadIdx.x ^ o];
-    pthread_barrier_wait(&g_bar);
+    t_slot[LANE] = (unsigned long long)(unsigned)v;
+    pthread_barrier_wait(t_bar);
+    int r = (int)(unsigned)t_slot[LANE ^ o];
+    pthread_barrier_wait(t_bar);
     return r;
 }
 static inline int __shfl_sync(unsigned, int v, int src) {
-    g_slot[threadIdx.x] = (unsigned long long)(unsigned)v;
-    pthread_barrier_wait(&g_bar);
-    int r = (int)(unsigned)g_slot[src & 31];
-    pthread_barrier_wait(&g_bar);
+    t_slot[LANE] = (unsigned long long)(unsigned)v;
+    pthread_barrier_wait(t_bar);
+    int r = (int)(unsigned)t_slot[src & 31];
+    pthread_barrier_wait(t_bar);
     return r;
 }
 static inline int __shfl_up_sync(unsigned, int v, unsigned d) {
-    g_slot[threadIdx.x] = (unsigned long long)(unsigned)v;
-    pthread_barrier_wait(&g_bar);
-    int r = threadIdx.x >= (long long)d ? (int)(unsigned)g_slot[threadIdx.x - d] : v;
-    pthread_barrier_wait(&g_bar);
+    t_slot[LANE] = (unsigned long long)(unsigned)v;
+    pthread_barrier_wait(t_bar);
+    int r = LANE >= (int)d ? (int)(unsigned)t_slot[LANE - d] : v;
+    pthread_barrier_wait(t_bar);
     return r;
 }
 static inline double __shfl_sync(unsigned, double v, int src) {
-    memcpy(&g_slot[threadIdx.x], &v, 8);
-    pthread_barrier_wait(&g_bar);
+    memcpy(&t_slot[LANE], &v, 8);
+    pthread_barrier_wait(t_bar);
     double r;
-    memcpy(&r, &g_slot[src & 31], 8);
-    pthread_barrier_wait(&g_bar);
+    memcpy(&r, &t_slot[src & 31], 8);
+    pthread_barrier_wait(t_bar);
     return r;
 }
+template <class T>
+static inline T shfl_down_any(T v, int o) {
+    static_assert(sizeof(T) <= 8, "");
+    unsigned long long bits = 0;
+    memcpy(&bits, &v, sizeof(T));
+    t_slot[LANE] = bits;
+    pthread_barrier_wait(t_bar);
+    T r = v;
+    if (LANE + o < 32) memcpy(&r, &t_slot[LANE + o], sizeof(T));
+    pthread_barrier_wait(t_bar);
+    return r;
+}
+static inline double __shfl_down_sync(unsigned, double v, int o) { return shfl_down_any(v, o); }
+static inline int __shfl_down_sync(unsigned, int v, int o) { return shfl_down_any(v, o); }
+static inline long long __shfl_down_sync(unsigned, long long v, int o) { return shfl_down_any(v, o); }
+static inline void __syncthreads() { pthread_barrier_wait(&g_bbar); }
 static inline double __ddiv_rn(double a, double b) { return a / b; }
-static inline void __syncwarp() { pthread_barrier_wait(&g_bar); }
+static inline void __syncwarp() { pthread_barrier_wait(t_bar); }
 // "shared memory": one block (= one warp) at a time, so a file-scope buffer stands in for the dynamic allocation
 #define __shared__ static                                   /* one block at a time: a function-static array IS shared by the 32 lanes */
 #define __align__(x)
@@ -124,6 +148,26 @@ static void run_block_no_collectives(int nthreads, F f) {
     }
     for (int t = 0; t < nthreads; ++t) pthread_join(th[t], nullptr);
     delete[] th; delete[] args;
+}
+// a 256-thread block: 8 warps with their own collective barriers, __syncthreads on the block barrier
+template <class F>
+static void run_block256(F f) {
+    struct Arg { F *f; int t; };
+    for (int w = 0; w < 8; ++w) pthread_barrier_init(&g_wbar[w], nullptr, 32);
+    pthread_barrier_init(&g_bbar, nullptr, 256);
+    static pthread_t th[256];
+    static Arg args[256];
+    for (int t = 0; t < 256; ++t) {
+        args[t] = {&f, t};
+        pthread_create(&th[t], nullptr, [](void *p) -> void * {
+            Arg *a = (Arg *)p;
+            threadIdx.x = a->t; t_bar = &g_wbar[a->t >> 5]; t_slot = g_wslot[a->t >> 5];
+            (*a->f)();
+            return nullptr; }, &args[t]);
+    }
+    for (int t = 0; t < 256; ++t) pthread_join(th[t], nullptr);
+    for (int w = 0; w < 8; ++w) pthread_barrier_destroy(&g_wbar[w]);
+    pthread_barrier_destroy(&g_bbar);
 }
 template <class F>
 static void run_warp(F f) {
@@ -167,6 +211,26 @@ extern "C" void host_nn1(const double *sorted4, const int *cell_start, const dou
     GridView g = make_view(sorted4, cell_start, o, cell, dims);          // no ring field, no candidate field: the ring walk
     for (long long i = 0; i < nq; ++i)
         idx[i] = ibl_nn1_thread(g, queries[3 * i], queries[3 * i + 1], queries[3 * i + 2], max_d, max_d * max_d, d2[i]);
+}
+extern "C" void host_nn_score(const double *sorted4, const int *cell_start, const double *o, double cell, const int *dims,
+                              const double *src, long long n, const double *T16, double max_d, int32_t *nn_idx, double *nn_d2,
+                              long long *n_inliers, double *err2) {
+    GridView g = make_view(sorted4, cell_start, o, cell, dims);
+    Mat16 T;
+    for (int k = 0; k < 16; ++k) T.v[k] = T16[k];
+    const int nb = (int)((n + 255) / 256);
+    long long *pc = new long long[nb];
+    double *pe = new double[nb];
+    blockDim.x = 256;
+    for (int b = 0; b < nb; ++b) {
+        blockIdx.x = b;
+        run_block256([&] { nn_score_kernel(g, src, n, T, 1, max_d, max_d * max_d, nn_idx, nn_d2, pc, pe); });
+    }
+    blockIdx.x = 0; blockDim.x = 32;
+    ibl_score_t res;
+    run_warp([&] { score_final_kernel(pc, pe, nb, &res); });
+    *n_inliers = res.n_inliers; *err2 = res.err2;
+    delete[] pc; delete[] pe;
 }
 extern "C" void host_spfh_fpfh(const double *pts, const double *nrm, long long n, const int32_t *idx, const double *d2,
                                const int32_t *cnt, int max_nn, double *spfh, double *fpfh) {
@@ -213,11 +277,13 @@ def warp_lib(tmp_path_factory):
     feats = ft[ft.index("__device__ __forceinline__ void cross3"):ft.index("__device__ void eigvec0")] + \
         ft[ft.index("__device__ void pair_features"):ft.index("IBL_API int ibl_spfh")] + \
         ft[ft.index("#define FPFH_MAX_NN"):ft.index("IBL_API int ibl_fpfh")]
+    score = gq[gq.index("struct Mat16 { double v[16]; };"):gq.index("IBL_API int ibl_nn_score")]
+    score = "typedef struct { int64_t n_inliers; double err2; } ibl_score_t;\n" + score
     db = open(os.path.join(CSRC, "dbscan.cu")).read()
     dbscan = db[db.index("__device__ __forceinline__ int uf_find"):db.index("// stream-ordered scratch that is returned")]
     d = tmp_path_factory.mktemp("warp_host")
     cpp, so = str(d / "warp_host.cpp"), str(d / "libwarp_host.so")
-    open(cpp, "w").write(PRELUDE + views + radius + knn + dbscan + feats + DRIVER)
+    open(cpp, "w").write(PRELUDE + views + radius + knn + score + dbscan + feats + DRIVER)
     subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-pthread", "-o", so, cpp])
     return ctypes.CDLL(so)
 
@@ -342,3 +408,25 @@ def test_nn1_ring_walk_source_vs_oracle(warp_lib, max_d, cell):
     hit = ridx >= 0
     assert hit.sum() > 50 and (~hit).sum() >= 5
     assert np.array_equal(d2[hit], rd2[hit])
+
+
+@pytest.mark.parametrize("max_d", [0.02, 0.075])
+def test_nn_score_kernels_source_vs_oracle(warp_lib, max_d):
+    from ibl_testutil import random_rigid, surface_cloud
+    from oracle import o3d_core as oc
+    tgt = np.ascontiguousarray(surface_cloud(1500, 20)[0])
+    T = np.ascontiguousarray(random_rigid(5, max_angle=0.03, max_t=0.01))
+    src = np.ascontiguousarray(surface_cloud(1500, 20)[0][:700] + np.random.default_rng(1).normal(0, 0.004, (700, 3)))
+    sorted4, cell_start, o, dims = host_grid(tgt, max_d)
+    n = len(src)
+    idx, d2 = np.full(n, -9, np.int32), np.full(n, -9.0)
+    cnt, err = ctypes.c_longlong(-1), ctypes.c_double(-1.0)
+    warp_lib.host_nn_score(_p(sorted4), _p(cell_start), _p(o), ctypes.c_double(max_d), _p(dims), _p(src), ctypes.c_longlong(n),
+                           _p(T), ctypes.c_double(max_d), _p(idx), _p(d2), ctypes.byref(cnt), ctypes.byref(err))
+    moved = oc.transform_points(T, src)
+    ridx, rd2 = oc.nn1(tgt, moved, max_d)
+    assert np.array_equal(idx, ridx)
+    hit = ridx >= 0
+    assert 50 < hit.sum() and np.array_equal(d2[hit], rd2[hit]) and np.isinf(d2[~hit]).all()
+    assert cnt.value == int(hit.sum())
+    assert abs(err.value - rd2[hit].sum()) <= 1e-12 * rd2[hit].sum()

@@ -13,6 +13,8 @@ full-mask intrinsics have on the device), which is what makes the barrier emulat
  * ``nn_score_kernel`` + ``score_final_kernel`` (csrc/grid_query.cu: evaluate_registration -- transform, exact NN, fixed
    shuffle-tree block reduction over 8 warps, __syncthreads) as a 256-thread block: correspondences and inlier count
    bit-exact, err2 to 1e-12 (the oracle sums in index order);
+ * ``ransac_count_kernel`` / ``ransac_score_kernel`` (csrc/ransac.cu: one block per (source tile, hypothesis)) on the
+   plain grid: per-hypothesis inlier counts of both kernels equal to the oracle's, err2 to 1e-12;
  * ``spfh_kernel`` / ``fpfh_kernel`` (csrc/features.cu: warp per point, bins across lanes, shared-memory staging) against
    the oracle's orc_spfh / orc_fpfh (SPFH to 1e-12, FPFH within the north-star 1e-4 relative);
  * ``dbscan_*`` kernels (csrc/dbscan.cu: init, union pass, roots, border pass, labels) against the oracle's sequential
@@ -61,9 +63,9 @@ static inline int atomicCAS(int *a, int cmp, int val) {
     __atomic_compare_exchange_n(a, &cmp, val, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST);
     return cmp;                                            // the old value, like the device intrinsic
 }
-struct Dim1 { long long x; };
-static Dim1 blockIdx{0}, gridDim{1}, blockDim{32};
-static thread_local Dim1 threadIdx{0};
+struct Dim1 { long long x, y; };
+static Dim1 blockIdx{0, 0}, gridDim{1, 1}, blockDim{32, 1};
+static thread_local Dim1 threadIdx{0, 0};
 // ---- one emulated warp: 32 host threads, a barrier inside every collective
 static pthread_barrier_t g_bar;                            // the single emulated warp of run_warp
 static unsigned long long g_slot[32];
@@ -232,6 +234,27 @@ extern "C" void host_nn_score(const double *sorted4, const int *cell_start, cons
     *n_inliers = res.n_inliers; *err2 = res.err2;
     delete[] pc; delete[] pe;
 }
+extern "C" void host_ransac_score(const double *sorted4, const int *cell_start, const double *o, double cell, const int *dims,
+                                  const double *src, long long n_src, const double *T_all, int nh, double max_d,
+                                  int32_t *count_only, int32_t *score_cnt, double *score_err) {
+    GridView g = make_view(sorted4, cell_start, o, cell, dims);
+    const int ntiles = (int)((n_src + SCORE_TILE - 1) / SCORE_TILE);
+    int *pc = new int[(size_t)nh * ntiles];
+    double *pe = new double[(size_t)nh * ntiles];
+    blockDim.x = SCORE_THREADS;
+    for (int h = 0; h < nh; ++h) {
+        count_only[h] = 0;
+        for (int t = 0; t < ntiles; ++t) {
+            blockIdx.x = t; blockIdx.y = h;
+            run_block256([&] { ransac_count_kernel(g, src, n_src, T_all, max_d, max_d * max_d, count_only); });
+            run_block256([&] { ransac_score_kernel(g, src, n_src, T_all, max_d, max_d * max_d, ntiles, pc, pe); });
+        }
+        score_cnt[h] = 0; score_err[h] = 0.0;
+        for (int t = 0; t < ntiles; ++t) { score_cnt[h] += pc[(size_t)h * ntiles + t]; score_err[h] += pe[(size_t)h * ntiles + t]; }
+    }
+    blockIdx.x = 0; blockIdx.y = 0; blockDim.x = 32;
+    delete[] pc; delete[] pe;
+}
 extern "C" void host_spfh_fpfh(const double *pts, const double *nrm, long long n, const int32_t *idx, const double *d2,
                                const int32_t *cnt, int max_nn, double *spfh, double *fpfh) {
     run_warp([&] { spfh_kernel(pts, nrm, n, idx, cnt, max_nn, spfh); });
@@ -279,11 +302,13 @@ def warp_lib(tmp_path_factory):
         ft[ft.index("#define FPFH_MAX_NN"):ft.index("IBL_API int ibl_fpfh")]
     score = gq[gq.index("struct Mat16 { double v[16]; };"):gq.index("IBL_API int ibl_nn_score")]
     score = "typedef struct { int64_t n_inliers; double err2; } ibl_score_t;\n" + score
+    rs = open(os.path.join(CSRC, "ransac.cu")).read()
+    rscore = rs[rs.index("#define SCORE_TILE 512"):rs.index("// one CTA per hypothesis: tile partials")]
     db = open(os.path.join(CSRC, "dbscan.cu")).read()
     dbscan = db[db.index("__device__ __forceinline__ int uf_find"):db.index("// stream-ordered scratch that is returned")]
     d = tmp_path_factory.mktemp("warp_host")
     cpp, so = str(d / "warp_host.cpp"), str(d / "libwarp_host.so")
-    open(cpp, "w").write(PRELUDE + views + radius + knn + score + dbscan + feats + DRIVER)
+    open(cpp, "w").write(PRELUDE + views + radius + knn + score + rscore + dbscan + feats + DRIVER)
     subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-shared", "-fPIC", "-pthread", "-o", so, cpp])
     return ctypes.CDLL(so)
 
@@ -430,3 +455,26 @@ def test_nn_score_kernels_source_vs_oracle(warp_lib, max_d):
     assert 50 < hit.sum() and np.array_equal(d2[hit], rd2[hit]) and np.isinf(d2[~hit]).all()
     assert cnt.value == int(hit.sum())
     assert abs(err.value - rd2[hit].sum()) <= 1e-12 * rd2[hit].sum()
+
+
+def test_ransac_score_kernels_source_vs_oracle(warp_lib):
+    from ibl_testutil import random_rigid, surface_cloud
+    from oracle import o3d_core as oc
+    tgt = np.ascontiguousarray(surface_cloud(1500, 20)[0])
+    src = np.ascontiguousarray(surface_cloud(1500, 20)[0][:900] + np.random.default_rng(2).normal(0, 0.01, (900, 3)))
+    max_d = 0.075
+    # a good hypothesis, two mediocre ones and one that moves everything away (zero inliers)
+    Ts = np.stack([np.eye(4), random_rigid(6, max_angle=0.05, max_t=0.02), random_rigid(7, max_angle=0.3, max_t=0.1),
+                   np.array([[1, 0, 0, 50.0], [0, 1, 0, 0], [0, 0, 1, 0], [0, 0, 0, 1.0]])])
+    Ts = np.ascontiguousarray(Ts.reshape(len(Ts), 16))
+    sorted4, cell_start, o, dims = host_grid(tgt, max_d)
+    nh = len(Ts)
+    c0, c1, e1 = np.full(nh, -9, np.int32), np.full(nh, -9, np.int32), np.full(nh, -9.0)
+    warp_lib.host_ransac_score(_p(sorted4), _p(cell_start), _p(o), ctypes.c_double(max_d), _p(dims), _p(src),
+                               ctypes.c_longlong(len(src)), _p(Ts), nh, ctypes.c_double(max_d), _p(c0), _p(c1), _p(e1))
+    for h in range(nh):
+        ridx, rd2 = oc.nn1(tgt, oc.transform_points(Ts[h].reshape(4, 4), src), max_d)
+        hit = ridx >= 0
+        assert c0[h] == c1[h] == int(hit.sum())
+        assert abs(e1[h] - rd2[hit].sum()) <= 1e-12 * max(rd2[hit].sum(), 1e-300)
+    assert c0[0] > c0[2] and c0[3] == 0

@@ -17,20 +17,39 @@ import torch
 
 @dataclass
 class Scene:
-    kind: np.ndarray          # [m] 0 = box, 1 = ellipsoid
-    half: np.ndarray          # [m,3] half extents / semi axes
-    R: np.ndarray             # [m,3,3] object -> world
-    t: np.ndarray             # [m,3]
-    albedo: np.ndarray        # [m,3]
+    """An object is a union of primitives (oriented boxes / ellipsoids): a base standing on the floor plus parts attached
+    to its surface at random 3-d orientations, so that objects have edges, corners and junctions (FPFH has something to
+    match) and no rotational symmetry (a pose is identifiable).  Arrays are per PRIMITIVE; ``obj`` maps a primitive to
+    its object."""
+    kind: np.ndarray          # [n_prim] 0 = box, 1 = ellipsoid
+    half: np.ndarray          # [n_prim,3] half extents / semi axes
+    R: np.ndarray             # [n_prim,3,3] primitive -> world
+    t: np.ndarray             # [n_prim,3]
+    albedo: np.ndarray        # [n_prim,3]
     room: float               # half side of the square room
     height: float             # ceiling height
     emb_centres: np.ndarray   # [m,D]
     memory_embs: list = field(default_factory=list)   # list of [n_e, D] float32
     seed: int = 0
+    obj: np.ndarray = None    # [n_prim] object of each primitive
+    centre: np.ndarray = None  # [m,3] object centres (base primitive)
+
+    def __post_init__(self):
+        if self.obj is None:
+            self.obj = np.arange(len(self.kind))
+        if self.centre is None:
+            self.centre = np.array([self.t[self.obj == j][0] for j in range(self.m)])
 
     @property
     def m(self):
+        return int(self.obj.max()) + 1 if len(self.obj) else 0
+
+    @property
+    def n_prim(self):
         return len(self.kind)
+
+    def prims_of(self, j):
+        return np.nonzero(self.obj == j)[0]
 
 
 LIGHT = np.array([0.35, 0.45, 0.82]) / np.linalg.norm([0.35, 0.45, 0.82])
@@ -41,8 +60,25 @@ def _yaw(a):
     return np.array([[c, -s, 0], [s, c, 0], [0, 0, 1.0]])
 
 
-def make_scene(m=40, seed=1002, D=768, size=(0.3, 0.9), n_emb=(5, 20), sigma=0.0175, common=0.65):
-    """m objects on a jittered floor grid inside a square room (world frame: z up)."""
+def _random_rotation(rng):
+    q = rng.normal(size=4)
+    q /= np.linalg.norm(q)
+    w, x, y, z = q
+    return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                     [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                     [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+
+
+def _prim_min_z(kind, half, R, t):
+    """lowest world z of a primitive."""
+    if kind == 0:
+        return t[2] - np.abs(R[2]) @ half
+    return t[2] - np.sqrt(((R[2] * half) ** 2).sum())
+
+
+def make_scene(m=40, seed=1002, D=768, size=(0.3, 0.9), n_emb=(5, 20), sigma=0.0175, common=0.65, parts=(2, 4)):
+    """m objects on a jittered floor grid inside a square room (world frame: z up).  ``parts`` = (min, max) number of
+    primitives attached to every object's base; (0, 0) gives the single-primitive objects of round 1."""
     rng = np.random.default_rng(seed)
     g = int(np.ceil(np.sqrt(m)))
     pitch = 1.9
@@ -56,6 +92,36 @@ def make_scene(m=40, seed=1002, D=768, size=(0.3, 0.9), n_emb=(5, 20), sigma=0.0
     t[:, 1] = (cells // g - (g - 1) / 2) * pitch + rng.uniform(-0.25, 0.25, m)
     t[:, 2] = half[:, 2]
     albedo = rng.uniform(0.25, 0.95, (m, 3))
+    obj = np.arange(m)
+    centre = t.copy()
+    if parts[1] > 0:
+        prng = np.random.default_rng(seed * 9176 + 11)        # own stream: the base layout above is unchanged by `parts`
+        ek, eh, eR, et, ea, eo = [], [], [], [], [], []
+        for j in range(m):
+            for _ in range(int(prng.integers(parts[0], parts[1] + 1))):
+                k = int(prng.random() < 0.35)
+                h = half[j].mean() * prng.uniform(0.3, 0.75, 3)
+                Rp = _random_rotation(prng)
+                u = prng.normal(size=3)                        # anchor on the base's surface, upper half preferred
+                u[2] = abs(u[2]) * 0.8
+                u /= np.linalg.norm(u)
+                if kind[j] == 0:
+                    a = u / np.abs(u / half[j]).max()           # point of the box surface along u
+                else:
+                    a = u / np.linalg.norm(u / half[j])
+                tp = t[j] + R[j] @ a
+                lift = 0.01 - _prim_min_z(k, h, Rp, tp)
+                if lift > 0:
+                    tp = tp + np.array([0, 0, lift])
+                ek.append(k); eh.append(h); eR.append(Rp); et.append(tp)
+                ea.append(np.clip(albedo[j] + prng.uniform(-0.22, 0.22, 3), 0.15, 0.98)); eo.append(j)
+        if ek:
+            kind = np.concatenate([kind, np.array(ek, dtype=np.int64)])
+            half = np.concatenate([half, np.array(eh)])
+            R = np.concatenate([R, np.array(eR)])
+            t = np.concatenate([t, np.array(et)])
+            albedo = np.concatenate([albedo, np.array(ea)])
+            obj = np.concatenate([obj, np.array(eo)])
     gdir = rng.normal(size=D)
     gdir /= np.linalg.norm(gdir)
     cent = rng.normal(size=(m, D))
@@ -67,7 +133,7 @@ def make_scene(m=40, seed=1002, D=768, size=(0.3, 0.9), n_emb=(5, 20), sigma=0.0
         ne = int(rng.integers(n_emb[0], n_emb[1] + 1))
         e = cent[j][None] + rng.normal(0, sigma, (ne, D))
         mem.append((e * rng.uniform(5, 40, (ne, 1))).astype(np.float32))     # DINOv2 outputs are not normalised
-    return Scene(kind, half, R, t, albedo, room, 2.8, cent, mem, seed)
+    return Scene(kind, half, R, t, albedo, room, 2.8, cent, mem, seed, obj, centre)
 
 
 def _texture(p):
@@ -83,26 +149,30 @@ def _shade(albedo, normal_w, p_w):
 
 def camera_pose(scene, rng, n_try=200):
     """Random camera inside the room looking at an object from 1.6-3.2 m.  Returns T_wc (camera -> world) with the
-    reference's camera axes: +X right, +Y up, +Z forward (depth)."""
+    reference's back-projection axes: +X along image columns, +Y up (decreasing row), +Z forward (depth); det = +1."""
     for _ in range(n_try):
         j = int(rng.integers(0, scene.m))
         ang = rng.uniform(0, 2 * np.pi)
         dist = rng.uniform(1.6, 3.2)
-        eye = scene.t[j] + np.array([np.cos(ang) * dist, np.sin(ang) * dist, 0.0])
+        eye = scene.centre[j] + np.array([np.cos(ang) * dist, np.sin(ang) * dist, 0.0])
         eye[2] = rng.uniform(1.1, 1.6)
         if np.abs(eye[:2]).max() > scene.room - 0.3:
             continue
-        d2 = np.linalg.norm(scene.t[:, :2] - eye[None, :2], axis=1)
+        d2 = np.linalg.norm(scene.centre[:, :2] - eye[None, :2], axis=1)
         if d2.min() < 0.9:
             continue
-        tgt = scene.t[j] + rng.uniform(-0.15, 0.15, 3)
+        tgt = scene.centre[j] + rng.uniform(-0.15, 0.15, 3)
         fwd = tgt - eye
         fwd /= np.linalg.norm(fwd)
-        right = np.cross(fwd, np.array([0, 0, 1.0]))
-        right /= np.linalg.norm(right)
-        up = np.cross(right, fwd)
+        # The reference's back-projection (X grows with the column, Y with decreasing row, Z = depth) reads pixels into a
+        # frame (x, y, z); for the recovered pose to be a rotation, (x, y, z) must be RIGHT-handed: x = up x fwd
+        # (image columns run towards the camera's left), y = fwd x x.  Round 1 used x = fwd x up, a reflection: every
+        # detected cloud was the mirror image of its memory cloud and no rigid registration could match the true pose.
+        xc = np.cross(np.array([0, 0, 1.0]), fwd)
+        xc /= np.linalg.norm(xc)
+        yc = np.cross(fwd, xc)
         T = np.eye(4)
-        T[:3, 0], T[:3, 1], T[:3, 2], T[:3, 3] = right, up, fwd, eye
+        T[:3, 0], T[:3, 1], T[:3, 2], T[:3, 3] = xc, yc, fwd, eye
         return T
     raise RuntimeError("could not place a camera")
 
@@ -142,7 +212,7 @@ def render(scene, T_wc, H=600, W=600, f=300.0, device="cpu", depth_noise=0.002, 
             ok = (den < 0) & (tt > 1e-6) & (tt < best)
             best = torch.where(ok, tt, best)
             nrm = torch.where(ok[:, None], n_t.expand(P, 3), nrm)
-        for j in range(scene.m):
+        for j in range(scene.n_prim):
             ol = (o_w - to[j]) @ Ro[j]                                  # world -> object: R^T (x - t)
             dl = d_w @ Ro[j]
             if scene.kind[j] == 0:                                      # box: slab method
@@ -174,7 +244,9 @@ def render(scene, T_wc, H=600, W=600, f=300.0, device="cpu", depth_noise=0.002, 
         return best, inst, nrm
     hit_w = o_w[None] + best[:, None] * d_w
     alb_tab = torch.as_tensor(np.concatenate([scene.albedo, [[0.62, 0.60, 0.57]]]), dtype=dt, device=dev)
-    alb = alb_tab[inst.long()]                                      # -1 -> last row (room surfaces)
+    alb = alb_tab[inst.long()]                                      # -1 -> last row (room surfaces); per primitive
+    obj_tab = torch.as_tensor(np.concatenate([scene.obj, [-1]]), dtype=torch.int32, device=dev)
+    inst = obj_tab[inst.long()]                                     # primitive -> object id
     col = _shade(alb, nrm, hit_w)
     gen = torch.Generator(device="cpu").manual_seed(int(seed))
     col = (col + 0.01 * torch.randn((P, 3), generator=gen, dtype=dt).to(dev)).clamp(0, 1)
@@ -215,33 +287,68 @@ def query_embeddings(scene, obj_ids, rng, sigma=0.0175):
     return (e * rng.uniform(5, 40, (len(obj_ids), 1))).astype(np.float32)
 
 
-def memory_cloud(scene, j, spacing=0.01, seed=0):
-    """World-frame surface samples of object j with the same shading model as render() -> (pts f64, cols f64)."""
-    rng = np.random.default_rng(seed * 100003 + j)
-    h = scene.half[j]
-    if scene.kind[j] == 0:
-        areas = 4 * np.array([h[1] * h[2], h[1] * h[2], h[0] * h[2], h[0] * h[2], h[0] * h[1]])   # no bottom face
-        n = int(areas.sum() / spacing ** 2)
-        face = rng.choice(5, n, p=areas / areas.sum())
+def _prim_surface(kind, h, n, rng, skip_bottom):
+    """n random surface samples of a primitive in its own frame -> (points, outward normals)."""
+    if kind == 0:
+        areas = 4 * np.array([h[1] * h[2], h[1] * h[2], h[0] * h[2], h[0] * h[2], h[0] * h[1], h[0] * h[1]])
+        if skip_bottom:
+            areas = areas[:5]
+        nf = len(areas)
+        face = rng.choice(nf, n, p=areas / areas.sum())
         pl = rng.uniform(-1, 1, (n, 3)) * h
         nl = np.zeros((n, 3))
-        ax = np.array([0, 0, 1, 1, 2])[face]
-        sg = np.array([1, -1, 1, -1, 1.0])[face]
+        ax = np.array([0, 0, 1, 1, 2, 2])[face]
+        sg = np.array([1, -1, 1, -1, 1.0, -1.0])[face]
         pl[np.arange(n), ax] = sg * h[ax]
         nl[np.arange(n), ax] = sg
-    else:
-        area = 4 * np.pi * ((((h[0] * h[1]) ** 1.6 + (h[0] * h[2]) ** 1.6 + (h[1] * h[2]) ** 1.6) / 3) ** (1 / 1.6))
-        n = int(area / spacing ** 2)
-        u = rng.normal(size=(n, 3))
-        u /= np.linalg.norm(u, axis=1, keepdims=True)
-        pl = u * h
-        nl = pl / (h * h)
-        nl /= np.linalg.norm(nl, axis=1, keepdims=True)
-    pw = pl @ scene.R[j].T + scene.t[j] + rng.normal(0, 0.001, (n, 3))
-    nw = nl @ scene.R[j].T
-    col = _shade(torch.as_tensor(scene.albedo[j]), torch.as_tensor(nw), torch.as_tensor(pw)).numpy()
-    col = np.clip(col + rng.normal(0, 0.01, col.shape), 0, 1)
-    return np.ascontiguousarray(pw), np.ascontiguousarray(col)
+        return pl, nl
+    u = rng.normal(size=(n, 3))
+    u /= np.linalg.norm(u, axis=1, keepdims=True)
+    pl = u * h
+    nl = pl / (h * h)
+    nl /= np.linalg.norm(nl, axis=1, keepdims=True)
+    return pl, nl
+
+
+def _prim_area(kind, h, skip_bottom):
+    if kind == 0:
+        a = 8 * (h[1] * h[2] + h[0] * h[2] + h[0] * h[1])
+        return a - (4 * h[0] * h[1] if skip_bottom else 0.0)
+    return 4 * np.pi * ((((h[0] * h[1]) ** 1.6 + (h[0] * h[2]) ** 1.6 + (h[1] * h[2]) ** 1.6) / 3) ** (1 / 1.6))
+
+
+def _inside(kind, h, R, t, pw, margin=1e-9):
+    pl = (pw - t) @ R
+    if kind == 0:
+        return (np.abs(pl) < h - margin).all(axis=1)
+    return ((pl / h) ** 2).sum(axis=1) < 1.0 - margin
+
+
+def memory_cloud(scene, j, spacing=0.01, seed=0):
+    """World-frame surface samples of object j (the visible surface of the union of its primitives: samples inside
+    another primitive of the object or under the floor are dropped) with the same shading model as render()
+    -> (pts f64, cols f64)."""
+    rng = np.random.default_rng(seed * 100003 + j)
+    prims = scene.prims_of(j)
+    P, C = [], []
+    for a, q in enumerate(prims):
+        h = scene.half[q]
+        skip_bottom = bool(a == 0 and scene.kind[q] == 0)         # the base box stands on the floor
+        n = int(_prim_area(scene.kind[q], h, skip_bottom) / spacing ** 2)
+        pl, nl = _prim_surface(scene.kind[q], h, n, rng, skip_bottom)
+        pw = pl @ scene.R[q].T + scene.t[q]
+        nw = nl @ scene.R[q].T
+        keep = pw[:, 2] > 0.0
+        for q2 in prims:
+            if q2 != q:
+                keep &= ~_inside(scene.kind[q2], scene.half[q2], scene.R[q2], scene.t[q2], pw)
+        pw, nw = pw[keep], nw[keep]
+        pw = pw + rng.normal(0, 0.001, pw.shape)
+        col = _shade(torch.as_tensor(scene.albedo[q]), torch.as_tensor(nw), torch.as_tensor(pw)).numpy()
+        col = np.clip(col + rng.normal(0, 0.01, col.shape), 0, 1)
+        P.append(pw)
+        C.append(col)
+    return np.ascontiguousarray(np.concatenate(P)), np.ascontiguousarray(np.concatenate(C))
 
 
 def make_frames(scene, n_frames, H=600, W=600, f=300.0, device="cpu", seed=0, max_objects=12, min_pixels=300):

@@ -72,7 +72,7 @@ def test_raycast_kernel_source_vs_tensor_ops(host_kernel, m, seed, H, W, f):
     ot, oi, on = np.empty(P), np.empty(P, np.int32), np.empty((P, 3))
     kind, half, R, t = sc.kind.astype(np.int32), np.ascontiguousarray(sc.half), np.ascontiguousarray(sc.R), np.ascontiguousarray(sc.t)
     p = lambda a: a.ctypes.data_as(ctypes.c_void_p)          # noqa: E731
-    host_kernel.host_raycast(p(T), H, W, ctypes.c_double(f), p(kind), p(half), p(R), p(t), m, ctypes.c_double(sc.room),
+    host_kernel.host_raycast(p(T), H, W, ctypes.c_double(f), p(kind), p(half), p(R), p(t), sc.n_prim, ctypes.c_double(sc.room),
                              ctypes.c_double(sc.height), p(ot), p(oi), p(on))
     same = i0 == oi
     assert same.mean() >= 0.9999

@@ -228,4 +228,4 @@ def test_raycast_kernel_vs_tensor_ops(K, m, seed, H, W, f):
         assert (i1 >= 0).sum() > 0
         d, rgb, inst = synth.render(sc, T, H=H, W=W, f=f, device="cuda", use_kernel=True)
         assert d.shape == (H, W) and d.dtype == torch.float32 and rgb.shape == (H, W, 3) and rgb.dtype == torch.uint8
-        assert np.array_equal(inst.cpu().numpy().reshape(-1), i1)
+        assert np.array_equal(inst.cpu().numpy().reshape(-1), np.concatenate([sc.obj, [-1]])[i1])   # primitive -> object

@@ -210,6 +210,42 @@ int ibl_ransac_run_range(const ibl_grid_t *tgt_grid, const double *src, int64_t 
                    int64_t h_begin, int64_t max_iteration, double confidence, double max_d, double edge_thr, int use_checkers,
                    int early_exit, int64_t block, ibl_reg_result_t *h_result, void *stream);
 
+/* ---- batched registration: every (frame, assignment) problem of a step advances together ---- */
+/* One register_point_clouds problem (utils/fpfh_register.py:100-143) after feature matching.  All pointers are device
+ * memory; src / src_col is the centred detected union, tgt* the cached memory-side union with its normals, colours and
+ * colour gradients; the two grids carry the exact-NN candidate fields for the RANSAC and the ICP distances. */
+typedef struct {
+    const double *src;               /* [n_src][3] */
+    const double *src_col;           /* [n_src][3] (coloured ICP) */
+    int64_t n_src;
+    const double *tgt;               /* [n_tgt][3] */
+    const double *tgt_nrm, *tgt_col, *tgt_grad;   /* [n_tgt][3] (coloured ICP) */
+    int64_t n_tgt;
+    const ibl_grid_t *grid_ransac;   /* target grid, NN field built for the RANSAC max_d */
+    const ibl_grid_t *grid_icp;      /* target grid, NN field built for the ICP max_d */
+    const int32_t *corres;           /* [n_corres][2] (source index, target index) */
+    int64_t n_corres;
+    uint64_t seed;                   /* counter-based sample stream ibl_sample(seed, h, j, n_corres) */
+} ibl_reg_problem_t;
+/* ibl_ransac_run for n_problems independent problems at once (object_memory.py:1020-1108 registers up to 6 assignments
+ * per frame one after the other): per round one block of hypotheses per active problem, ONE launch per stage for the whole
+ * batch and three host synchronisations (validated counts, inlier counts, exact scores of the contenders).  Every field of
+ * h_results[p] equals what ibl_ransac_run returns for problem p alone.  Syncs. */
+int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_problems, int64_t max_iteration, double confidence,
+                         double max_d, double edge_thr, int use_checkers, int early_exit, int64_t first_block,
+                         ibl_reg_result_t *h_results, void *stream);
+/* ibl_icp(mode 1) for n_problems problems at once, from h_T_init[p] (host double[n_problems][16]): one launch per ICP
+ * iteration for the whole batch, convergence rule and 6x6 solve per problem on the device, one state read-back per 8
+ * queued iterations.  Results equal ibl_icp's.  Syncs. */
+int ibl_icp_colored_batch(const ibl_reg_problem_t *problems, int32_t n_problems, const double *h_T_init, double max_d,
+                          int max_iteration, double rel_fitness, double rel_rmse, double lambda_geometric,
+                          ibl_reg_result_t *h_results, void *stream);
+/* ibl_nn_score (evaluate_registration, fpfh_register.py:145-150) of n_queries (source, transform) pairs against ONE target
+ * grid: srcs / ns / h_T16 are host arrays of device pointers, point counts and row-major 4x4 transforms.  One launch and
+ * one synchronisation for all of them; h_results[q] equals ibl_nn_score's result for query q. */
+int ibl_nn_score_batch(const ibl_grid_t *g, const double *const *srcs, const int64_t *ns, const double *h_T16,
+                       int32_t n_queries, double max_d, ibl_score_t *h_results, void *stream);
+
 /* ---------------------------------------------------------------- ICP ----------------------- */
 /* InitializePointCloudForColoredICP (A.8): grad double[n][3] */
 int ibl_color_gradient(const double *pts, const double *nrm, const double *col, int64_t n, const int32_t *nbr_idx,

@@ -26,6 +26,14 @@ class RegResultT(ctypes.Structure):
                 ("n_corres", c_int64), ("iterations", c_int32), ("status", c_int32)]
 
 
+class RegProblemT(ctypes.Structure):
+    """ibl_reg_problem_t (include/ibl.h): one registration problem of a batch, device pointers."""
+    _fields_ = [("src", c_void_p), ("src_col", c_void_p), ("n_src", c_int64),
+                ("tgt", c_void_p), ("tgt_nrm", c_void_p), ("tgt_col", c_void_p), ("tgt_grad", c_void_p), ("n_tgt", c_int64),
+                ("grid_ransac", c_void_p), ("grid_icp", c_void_p), ("corres", c_void_p), ("n_corres", c_int64),
+                ("seed", c_uint64)]
+
+
 def build(verbose: bool = False) -> str:
     """Compile libibl.so in-tree with nvcc for sm_100a (csrc/Makefile)."""
     out = subprocess.run(["make", "-j8", "-C", os.path.join(_HERE, "csrc")], capture_output=True, text=True)
@@ -78,6 +86,12 @@ _PROTOS = {
                                c_int, c_int, c_int64, POINTER(RegResultT), _V]),
     "ibl_ransac_run_range": (c_int, [_V, _V, c_int64, _V, _V, c_int64, _V, c_uint64, c_int64, c_int64, c_double, c_double,
                                      c_double, c_int, c_int, c_int64, POINTER(RegResultT), _V]),
+    "ibl_ransac_run_batch": (c_int, [POINTER(RegProblemT), c_int32, c_int64, c_double, c_double, c_double, c_int, c_int,
+                                     c_int64, POINTER(RegResultT), _V]),
+    "ibl_icp_colored_batch": (c_int, [POINTER(RegProblemT), c_int32, POINTER(c_double), c_double, c_int, c_double, c_double,
+                                      c_double, POINTER(RegResultT), _V]),
+    "ibl_nn_score_batch": (c_int, [_V, POINTER(c_void_p), POINTER(c_int64), POINTER(c_double), c_int32, c_double,
+                                   POINTER(ScoreT), _V]),
     "ibl_color_gradient": (c_int, [_V, _V, _V, c_int64, _V, _V, c_int32, _V, _V]),
     "ibl_p2p_update": (c_int, [_V, _V, c_int64, _V, POINTER(c_double), _V]),
     "ibl_colored_update": (c_int, [_V, _V, _V, c_int64, _V, _V, _V, _V, c_double, POINTER(c_double),

@@ -3,6 +3,8 @@
 //   hybrid k-NN   : warp per query, Chebyshev ring expansion, shared-memory candidate buffer,
 //                   warp bitonic sort on (d2 bits, index) -> ascending (d2, index) like the oracle
 //   1-NN + score  : thread per query (ring field skips empty space), deterministic block reduce
+#include <vector>
+
 #include "ibl_common.cuh"
 
 // ------------------------------------------------------------------------------------------------
@@ -383,5 +385,100 @@ IBL_API int ibl_nn_score(const ibl_grid_t *g, const double *src, int64_t n, cons
         IBL_CUDA(cudaMemsetAsync(nn_idx, 0xff, sizeof(int32_t) * (size_t)n, st));
     }
     if (h_result) *h_result = res;
+    return IBL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// evaluate_registration for many (source, transform) pairs against one target grid in ONE launch: CTA `b` of query q is
+// nn_score_kernel's block b (same per-CTA reduction), and one warp per query adds the CTA partials in score_final_kernel's
+// order, so every result equals ibl_nn_score's.
+struct NnsQuery { const double *src; int64_t n; double T[16]; int has_T; int pad; };
+
+__global__ void __launch_bounds__(256) nn_score_batch_kernel(GridView g, const NnsQuery *__restrict__ qs, int nq,
+                                                             const int64_t *__restrict__ blk_prefix, double max_d, double max_d2,
+                                                             long long *__restrict__ part_cnt, double *__restrict__ part_err) {
+    __shared__ int s_q;
+    __shared__ double T[16];
+    if (threadIdx.x == 0) {
+        int lo = 0, hi = nq;
+        const int64_t item = (int64_t)blockIdx.x;
+        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (blk_prefix[mid] <= item) lo = mid; else hi = mid; }
+        s_q = lo;
+    }
+    __syncthreads();
+    const NnsQuery *Q = qs + s_q;
+    if (threadIdx.x < 16) T[threadIdx.x] = Q->T[threadIdx.x];
+    __syncthreads();
+    const int64_t i = ((int64_t)blockIdx.x - blk_prefix[s_q]) * 256 + threadIdx.x;
+    int hit = 0;
+    double e = 0.0;
+    if (i < Q->n) {
+        const double *__restrict__ src = Q->src;
+        double x = src[3 * i], y = src[3 * i + 1], z = src[3 * i + 2];
+        if (Q->has_T) { double a, b, c; ibl_xform(T, x, y, z, a, b, c); x = a; y = b; z = c; }
+        double bd;
+        int j = ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd);
+        if (j >= 0) { hit = 1; e = bd; }
+    }
+    __shared__ double se[8];
+    __shared__ int sc[8];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int o = 16; o; o >>= 1) { e += __shfl_down_sync(0xffffffffu, e, o); hit += __shfl_down_sync(0xffffffffu, hit, o); }
+    if (lane == 0) { se[w] = e; sc[w] = hit; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double te = 0; long long tc = 0;
+        for (int k = 0; k < 8; ++k) { te += se[k]; tc += sc[k]; }
+        part_cnt[blockIdx.x] = tc;
+        part_err[blockIdx.x] = te;
+    }
+}
+
+__global__ void score_final_batch_kernel(const long long *part_cnt, const double *part_err, const int64_t *blk_prefix, ibl_score_t *out) {
+    const int q = blockIdx.x, lane = threadIdx.x;
+    const int64_t b0 = blk_prefix[q];
+    const int nb = (int)(blk_prefix[q + 1] - b0);
+    double e = 0; long long c = 0;
+    for (int k = lane; k < nb; k += 32) { e += part_err[b0 + k]; c += part_cnt[b0 + k]; }
+    for (int o = 16; o; o >>= 1) { e += __shfl_down_sync(0xffffffffu, e, o); c += __shfl_down_sync(0xffffffffu, c, o); }
+    if (lane == 0) { out[q].n_inliers = c; out[q].err2 = e; }
+}
+
+IBL_API int ibl_nn_score_batch(const ibl_grid_t *g, const double *const *srcs, const int64_t *ns, const double *h_T16,
+                               int32_t n_queries, double max_d, ibl_score_t *h_results, void *stream) {
+    IBL_ARG(g != nullptr && n_queries >= 0 && max_d > 0 && (n_queries == 0 || (srcs && ns && h_results)));
+    if (n_queries == 0) return IBL_OK;
+    cudaStream_t st = ibl_stream(stream);
+    std::vector<NnsQuery> hq(n_queries);
+    std::vector<int64_t> prefix(n_queries + 1, 0);
+    double work = 0;
+    for (int q = 0; q < n_queries; ++q) {
+        IBL_ARG(ns[q] >= 0 && (ns[q] == 0 || srcs[q]));
+        hq[q].src = srcs[q]; hq[q].n = g->n > 0 ? ns[q] : 0; hq[q].has_T = h_T16 != nullptr; hq[q].pad = 0;
+        for (int k = 0; k < 16; ++k) hq[q].T[k] = h_T16 ? h_T16[16 * (size_t)q + k] : ((k % 5 == 0) ? 1.0 : 0.0);
+        prefix[q + 1] = prefix[q] + (hq[q].n + 255) / 256;
+        work += (double)hq[q].n * 24.0;
+        h_results[q].n_inliers = 0; h_results[q].err2 = 0.0;
+    }
+    const int64_t nb = prefix[n_queries];
+    if (nb == 0) return IBL_OK;
+    NnsQuery *dq = nullptr; int64_t *dpre = nullptr; long long *pc = nullptr; double *pe = nullptr; ibl_score_t *dres = nullptr;
+    IBL_CUDA(ibl_alloc(&dq, (size_t)n_queries, st));
+    IBL_CUDA(ibl_alloc(&dpre, (size_t)n_queries + 1, st));
+    IBL_CUDA(ibl_alloc(&pc, (size_t)nb, st));
+    IBL_CUDA(ibl_alloc(&pe, (size_t)nb, st));
+    IBL_CUDA(ibl_alloc(&dres, (size_t)n_queries, st));
+    IBL_CUDA(cudaMemcpyAsync(dq, hq.data(), sizeof(NnsQuery) * n_queries, cudaMemcpyHostToDevice, st));
+    IBL_CUDA(cudaMemcpyAsync(dpre, prefix.data(), sizeof(int64_t) * (n_queries + 1), cudaMemcpyHostToDevice, st));
+    {
+        IBL_PROF(IBL_PROF_NN_SCORE, st, work);
+        nn_score_batch_kernel<<<(unsigned)nb, 256, 0, st>>>(ibl_view(g), dq, n_queries, dpre, max_d, max_d * max_d, pc, pe);
+        IBL_LAUNCH_CHECK();
+    }
+    score_final_batch_kernel<<<(unsigned)n_queries, 32, 0, st>>>(pc, pe, dpre, dres);
+    IBL_LAUNCH_CHECK();
+    IBL_CUDA(cudaMemcpyAsync(h_results, dres, sizeof(ibl_score_t) * n_queries, cudaMemcpyDeviceToHost, st));
+    IBL_CUDA(ibl_sync(st));
+    ibl_free(dq, st); ibl_free(dpre, st); ibl_free(pc, st); ibl_free(pe, st); ibl_free(dres, st);
     return IBL_OK;
 }

@@ -276,19 +276,22 @@ __device__ void icp_solve_update(const double *v27, double *T16) {
     T16[8] = -sy;     T16[9] = cy * sx;                T16[10] = cy * cx;               T16[11] = x[5];
 }
 
-__global__ void __launch_bounds__(256) colored_step_kernel(GridView g, const double *__restrict__ in, double *__restrict__ out,
-                                                           const double *__restrict__ scol, int64_t n, IcpState *S,
-                                                           ColoredTerms terms, double max_d, double max_d2,
-                                                           int32_t *__restrict__ nn, double *part, int nb,
-                                                           int max_iteration, double rel_fitness, double rel_rmse) {
+// The body of one CTA (256 threads) of a coloured-ICP step: block `blk` of the problem's `nb` blocks.  in == nullptr: read
+// the problem's own source on step 0 and the moved cloud `out` afterwards (batched launches: the choice is per problem).
+__device__ __forceinline__ void colored_step_block(const GridView &g, const double *__restrict__ in, const double *__restrict__ src0,
+                                                   double *__restrict__ out, const double *__restrict__ scol, int64_t n, IcpState *S,
+                                                   const ColoredTerms &terms, double max_d, double max_d2,
+                                                   int32_t *__restrict__ nn, double *part, int nb, int blk,
+                                                   int max_iteration, double rel_fitness, double rel_rmse) {
     __shared__ double sU[16];
-    __shared__ int s_flag[2];
+    __shared__ int s_flag[3];
     if (threadIdx.x < 16) sU[threadIdx.x] = S->U[threadIdx.x];
-    if (threadIdx.x == 0) { s_flag[0] = S->done; s_flag[1] = S->has_U; }
+    if (threadIdx.x == 0) { s_flag[0] = S->done; s_flag[1] = S->has_U; s_flag[2] = S->steps; }
     __syncthreads();
     if (s_flag[0]) return;                                // converged in an earlier step of this batch
     const int has_U = s_flag[1];
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (in == nullptr) in = s_flag[2] == 0 ? src0 : out;
+    int64_t i = blk * (int64_t)blockDim.x + threadIdx.x;
     int hit = 0;
     double e = 0.0;
     double v[27];
@@ -300,7 +303,7 @@ __global__ void __launch_bounds__(256) colored_step_kernel(GridView g, const dou
         out[3 * i] = p[0]; out[3 * i + 1] = p[1]; out[3 * i + 2] = p[2];
         double bd;
         int j = ibl_nn1_thread(g, p[0], p[1], p[2], max_d, max_d2, bd);
-        nn[i] = j;
+        if (nn) nn[i] = j;
         if (j >= 0) {
             hit = 1; e = bd;
             double is = (scol[3 * i] + scol[3 * i + 1] + scol[3 * i + 2]) / 3.0;
@@ -320,7 +323,7 @@ __global__ void __launch_bounds__(256) colored_step_kernel(GridView g, const dou
         if (lane == 0) sm[w][k] = x;
     }
     __syncthreads();
-    double *row = part + (size_t)blockIdx.x * STEP_W;
+    double *row = part + (size_t)blk * STEP_W;
     if (threadIdx.x == 0) {
         double te = 0; long long tc = 0;
         for (int k = 0; k < 8; ++k) { te += se[k]; tc += sc[k]; }
@@ -379,6 +382,47 @@ __global__ void __launch_bounds__(256) colored_step_kernel(GridView g, const dou
         S->arrived = 0;
         S->done = done;
     }
+}
+
+__global__ void __launch_bounds__(256) colored_step_kernel(GridView g, const double *__restrict__ in, double *__restrict__ out,
+                                                           const double *__restrict__ scol, int64_t n, IcpState *S,
+                                                           ColoredTerms terms, double max_d, double max_d2,
+                                                           int32_t *__restrict__ nn, double *part, int nb,
+                                                           int max_iteration, double rel_fitness, double rel_rmse) {
+    colored_step_block(g, in, in, out, scol, n, S, terms, max_d, max_d2, nn, part, nb, (int)blockIdx.x, max_iteration, rel_fitness,
+                       rel_rmse);
+}
+
+// ---- batched: all coloured-ICP problems of a step advance by one iteration per launch ----
+struct IcpProb {
+    GridView g;
+    const double *src; double *cur; const double *scol;
+    int64_t n;
+    ColoredTerms terms;
+    IcpState *S;
+    double *part;
+    int nb;
+};
+
+__global__ void __launch_bounds__(256) colored_step_batch_kernel(const IcpProb *__restrict__ probs, int nprob,
+                                                                 const int64_t *__restrict__ blk_prefix, double max_d,
+                                                                 double max_d2, int max_iteration, double rel_fitness,
+                                                                 double rel_rmse) {
+    __shared__ GridView g;
+    __shared__ int s_p;
+    if (threadIdx.x == 0) {
+        int lo = 0, hi = nprob;
+        const int64_t item = (int64_t)blockIdx.x;
+        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (blk_prefix[mid] <= item) lo = mid; else hi = mid; }
+        s_p = lo;
+    }
+    __syncthreads();
+    const IcpProb *P = probs + s_p;
+    for (int k = threadIdx.x; k < (int)(sizeof(GridView) / 4); k += 256)
+        reinterpret_cast<int *>(&g)[k] = reinterpret_cast<const int *>(&P->g)[k];
+    __syncthreads();
+    colored_step_block(g, nullptr, P->src, P->cur, P->scol, P->n, P->S, P->terms, max_d, max_d2, nullptr, P->part, P->nb,
+                       (int)((int64_t)blockIdx.x - blk_prefix[s_p]), max_iteration, rel_fitness, rel_rmse);
 }
 
 static int icp_colored_fused(const ibl_grid_t *tgt_grid, const double *src, const double *scol, int64_t n_src,
@@ -470,5 +514,96 @@ IBL_API int ibl_icp(const ibl_grid_t *tgt_grid, const double *src, const double 
     h_result->fitness = fit; h_result->inlier_rmse = rmse;
     h_result->n_inliers = sc.n_inliers; h_result->err2 = sc.err2; h_result->iterations = it;
     ibl_free(pcd, st); ibl_free(nn, st);
+    return IBL_OK;
+}
+
+// All coloured-ICP problems of a step (object_memory.py:1020-1108: one per assignment and frame) iterate together: one
+// launch per ICP iteration for the whole batch, the per-problem convergence rule and 6x6 solve on the device (the last CTA
+// of every problem), and one read-back of the problem states per 8 queued iterations -- instead of 2-4 host round trips
+// per problem.  The per-problem arithmetic and reduction order are colored_step_kernel's, so results equal ibl_icp(mode 1).
+IBL_API int ibl_icp_colored_batch(const ibl_reg_problem_t *problems, int32_t n_problems, const double *h_T_init, double max_d,
+                                  int max_iteration, double rel_fitness, double rel_rmse, double lambda_geometric,
+                                  ibl_reg_result_t *h_results, void *stream) {
+    IBL_ARG(n_problems >= 0 && (n_problems == 0 || (problems && h_results && h_T_init)) && max_d > 0 && max_iteration >= 0);
+    if (n_problems == 0) return IBL_OK;
+    cudaStream_t st = ibl_stream(stream);
+    const int P = n_problems;
+    std::vector<IcpState> hS(P);
+    std::vector<IcpProb> hp(P);
+    std::vector<int> live;
+    int64_t npts = 0, nblk = 0;
+    for (int p = 0; p < P; ++p) {
+        const ibl_reg_problem_t &q = problems[p];
+        ibl_reg_result_t &r = h_results[p];
+        memset(&r, 0, sizeof(r));
+        memcpy(r.T, h_T_init + 16 * (size_t)p, sizeof(double) * 16);
+        r.best_hyp = -1;
+        if (q.n_src <= 0) { r.status = 1; continue; }
+        IBL_ARG(q.grid_icp && q.src && q.src_col && q.tgt && q.tgt_nrm && q.tgt_col && q.tgt_grad && q.n_tgt > 0);
+        live.push_back(p);
+        npts += q.n_src; nblk += (q.n_src + 255) / 256;
+    }
+    if (live.empty()) return IBL_OK;
+    double *cur = nullptr, *part = nullptr; IcpState *dS = nullptr; IcpProb *d_probs = nullptr; int64_t *d_prefix = nullptr;
+    IBL_CUDA(ibl_alloc(&cur, (size_t)npts * 3, st));
+    IBL_CUDA(ibl_alloc(&part, (size_t)nblk * STEP_W, st));
+    IBL_CUDA(ibl_alloc(&dS, (size_t)P, st));
+    IBL_CUDA(ibl_alloc(&d_probs, (size_t)P, st));
+    IBL_CUDA(ibl_alloc(&d_prefix, (size_t)P + 1, st));
+    memset(hS.data(), 0, sizeof(IcpState) * P);
+    {
+        int64_t po = 0, bo = 0;
+        for (int p : live) {
+            const ibl_reg_problem_t &q = problems[p];
+            IcpProb &d = hp[p];
+            d.g = ibl_view(q.grid_icp);
+            d.src = q.src; d.cur = cur + 3 * po; d.scol = q.src_col; d.n = q.n_src;
+            d.terms = ColoredTerms{q.tgt, q.tgt_nrm, q.tgt_col, q.tgt_grad, sqrt(lambda_geometric), sqrt(1.0 - lambda_geometric)};
+            d.S = dS + p; d.nb = (int)((q.n_src + 255) / 256); d.part = part + (size_t)bo * STEP_W;
+            po += q.n_src; bo += d.nb;
+            memcpy(hS[p].T, h_T_init + 16 * (size_t)p, sizeof(double) * 16);
+            memcpy(hS[p].U, h_T_init + 16 * (size_t)p, sizeof(double) * 16);      // step 0 moves the source by the initial pose
+            hS[p].has_U = is_identity(hS[p].T) ? 0 : 1;
+        }
+    }
+    IBL_CUDA(cudaMemcpyAsync(dS, hS.data(), sizeof(IcpState) * P, cudaMemcpyHostToDevice, st));
+    std::vector<IcpProb> table;
+    std::vector<int64_t> prefix;
+    int queued = -1;                                       // ICP iterations queued so far (step 0 = the initial score)
+    while (!live.empty()) {
+        table.clear(); prefix.assign(1, 0);
+        double work = 0;
+        for (int p : live) {
+            table.push_back(hp[p]);
+            prefix.push_back(prefix.back() + hp[p].nb);
+            work += (double)hp[p].n * (24.0 + 24.0 + 24.0 + 4.0 + 96.0) + 8.0 * STEP_W * hp[p].nb;
+        }
+        const int L = (int)live.size();
+        IBL_CUDA(cudaMemcpyAsync(d_probs, table.data(), sizeof(IcpProb) * L, cudaMemcpyHostToDevice, st));
+        IBL_CUDA(cudaMemcpyAsync(d_prefix, prefix.data(), sizeof(int64_t) * (L + 1), cudaMemcpyHostToDevice, st));
+        const int batch = queued < 0 ? std::min(8, max_iteration + 1) : std::min(8, max_iteration - queued);
+        for (int k = 0; k < batch; ++k) {
+            IBL_PROF(IBL_PROF_ICP_REDUCE, st, work);
+            colored_step_batch_kernel<<<(unsigned)prefix.back(), 256, 0, st>>>(d_probs, L, d_prefix, max_d, max_d * max_d,
+                                                                             max_iteration, rel_fitness, rel_rmse);
+            IBL_LAUNCH_CHECK();
+        }
+        queued = queued < 0 ? batch - 1 : queued + batch;
+        IBL_CUDA(cudaMemcpyAsync(hS.data(), dS, sizeof(IcpState) * P, cudaMemcpyDeviceToHost, st));
+        IBL_CUDA(ibl_sync(st));
+        std::vector<int> next;
+        for (int p : live) {
+            if (hS[p].done || queued >= max_iteration) {
+                ibl_reg_result_t &r = h_results[p];
+                memcpy(r.T, hS[p].T, sizeof(double) * 16);
+                r.fitness = hS[p].fit; r.inlier_rmse = hS[p].rmse; r.n_inliers = hS[p].n_inliers; r.err2 = hS[p].err2;
+                r.iterations = hS[p].steps - 1;
+            } else {
+                next.push_back(p);
+            }
+        }
+        live.swap(next);
+    }
+    ibl_free(cur, st); ibl_free(part, st); ibl_free(dS, st); ibl_free(d_probs, st); ibl_free(d_prefix, st);
     return IBL_OK;
 }

@@ -8,6 +8,7 @@
 //   run    : host loop applying the ordered best-update / adaptive-stop rule; a chunk of validated hypotheses is
 //            counted first and only those whose count reaches the running maximum get the exact score
 #include <cub/cub.cuh>
+#include <algorithm>
 #include <vector>
 
 #include "ibl_common.cuh"
@@ -26,6 +27,34 @@ __device__ __forceinline__ void gather_sample(const double *__restrict__ src, co
     }
 }
 
+// one hypothesis: EdgeLength test (needs no transform), Jacobi-Kabsch, Distance test.  T is valid when true is returned.
+__device__ __forceinline__ bool ransac_check_one(const double *__restrict__ src, const double *__restrict__ tgt,
+                                                 const int32_t *__restrict__ corres, int64_t n_corres,
+                                                 const int32_t *__restrict__ samples, uint64_t seed, int64_t h,
+                                                 double edge_thr, double dist_thr, int use_checkers, double *T) {
+    double s[9], t[9];
+    gather_sample(src, tgt, corres, n_corres, samples, seed, h, s, t);
+    if (use_checkers) {
+        for (int i = 0; i < 3; ++i)
+            for (int j = i + 1; j < 3; ++j) {
+                double a[3] = {s[3 * i] - s[3 * j], s[3 * i + 1] - s[3 * j + 1], s[3 * i + 2] - s[3 * j + 2]};
+                double b[3] = {t[3 * i] - t[3 * j], t[3 * i + 1] - t[3 * j + 1], t[3 * i + 2] - t[3 * j + 2]};
+                double ds = sqrt(ibl_dot(a, a)), dt = sqrt(ibl_dot(b, b));
+                if (ds < dt * edge_thr || dt < ds * edge_thr) return false;
+            }
+    }
+    ibl_kabsch3(s, t, T);
+    if (use_checkers) {
+        for (int j = 0; j < 3; ++j) {
+            double qx, qy, qz;
+            ibl_xform(T, s[3 * j], s[3 * j + 1], s[3 * j + 2], qx, qy, qz);
+            double d[3] = {t[3 * j] - qx, t[3 * j + 1] - qy, t[3 * j + 2] - qz};
+            if (sqrt(ibl_dot(d, d)) > dist_thr) return false;
+        }
+    }
+    return true;
+}
+
 __global__ void __launch_bounds__(128) ransac_check_kernel(const double *__restrict__ src, const double *__restrict__ tgt,
                                                            const int32_t *__restrict__ corres, int64_t n_corres,
                                                            const int32_t *__restrict__ samples, uint64_t seed, int64_t h0,
@@ -33,33 +62,11 @@ __global__ void __launch_bounds__(128) ransac_check_kernel(const double *__restr
                                                            uint8_t *__restrict__ pass, double *__restrict__ T_out) {
     int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (k >= H) return;
-    int64_t h = h0 + k;
-    double s[9], t[9], T[16];
-    gather_sample(src, tgt, corres, n_corres, samples, seed, h, s, t);
-    bool ok = true;
-    if (use_checkers) {
-        for (int i = 0; i < 3 && ok; ++i)
-            for (int j = i + 1; j < 3; ++j) {
-                double a[3] = {s[3 * i] - s[3 * j], s[3 * i + 1] - s[3 * j + 1], s[3 * i + 2] - s[3 * j + 2]};
-                double b[3] = {t[3 * i] - t[3 * j], t[3 * i + 1] - t[3 * j + 1], t[3 * i + 2] - t[3 * j + 2]};
-                double ds = sqrt(ibl_dot(a, a)), dt = sqrt(ibl_dot(b, b));
-                if (ds < dt * edge_thr || dt < ds * edge_thr) { ok = false; break; }
-            }
-    }
-    if (ok) {
-        ibl_kabsch3(s, t, T);
-        if (use_checkers) {
-            for (int j = 0; j < 3; ++j) {
-                double qx, qy, qz;
-                ibl_xform(T, s[3 * j], s[3 * j + 1], s[3 * j + 2], qx, qy, qz);
-                double d[3] = {t[3 * j] - qx, t[3 * j + 1] - qy, t[3 * j + 2] - qz};
-                if (sqrt(ibl_dot(d, d)) > dist_thr) { ok = false; break; }
-            }
-        }
-        if (ok && T_out) {
+    double T[16];
+    bool ok = ransac_check_one(src, tgt, corres, n_corres, samples, seed, h0 + k, edge_thr, dist_thr, use_checkers, T);
+    if (ok && T_out) {
 #pragma unroll
-            for (int e = 0; e < 16; ++e) T_out[16 * k + e] = T[e];
-        }
+        for (int e = 0; e < 16; ++e) T_out[16 * k + e] = T[e];
     }
     pass[k] = ok;
 }
@@ -393,5 +400,424 @@ IBL_API int ibl_ransac_run_range(const ibl_grid_t *tgt_grid, const double *src, 
     h_result->drawn = std::max<int64_t>(std::min(max_iteration, std::max<int64_t>(est_k, 0)) - h_begin, 0);
     ibl_free(tmp, st); ibl_free(pass, st); ibl_free(ids, st); ibl_free(dcount, st);
     ibl_free(inl, st); ibl_free(inl2, st); ibl_free(sel_ids, st); ibl_free(cinl, st); ibl_free(err, st); ibl_free(Ts, st);
+    return rc;
+}
+
+// ================================================================================================
+// Batched RANSAC: ALL registration problems of a step advance together (object_memory.py:1020-1108 runs <= 6 of these
+// per frame, one after the other; a step of B frames holds <= 6 B independent problems).  Every round handles one block
+// of hypotheses per active problem with ONE launch per stage for the whole batch and THREE host synchronisations in total
+// (validated counts; inlier counts; exact scores of the contenders), instead of three per 512 validated hypotheses per
+// problem.  The per-problem arithmetic, the hypothesis stream and the ordered best-update / adaptive-stop rule are those
+// of ibl_ransac_run_range, so every result field is identical to running the problems one by one.
+struct RbProb {
+    GridView g;
+    const double *src, *tgt;
+    const int32_t *corres;
+    int64_t n_src, n_corres;
+    uint64_t seed;
+    int64_t h0;         // first hypothesis of this round's block
+    int64_t list_off;   // this problem's slice of ids[] (capacity H)
+    int64_t val_off;    // first validated entry of this problem in Ts[] / inl[] (valid after the count read-back)
+    int32_t H;          // hypotheses in this round's block (0 = not active this round)
+    int32_t ntiles;
+};
+
+// grid (ceil(max H / 128), problems).  Validated hypotheses are appended to the problem's id list (block-relative ids;
+// order within the list is arbitrary, the host sorts): one atomicAdd per warp.
+__global__ void __launch_bounds__(128) ransac_check_batch_kernel(const RbProb *__restrict__ probs, double edge_thr,
+                                                                 double dist_thr, int use_checkers,
+                                                                 int32_t *__restrict__ ids, int32_t *__restrict__ npass) {
+    const RbProb *P = probs + blockIdx.y;
+    const int H = P->H;
+    if ((int64_t)blockIdx.x * 128 >= H) return;
+    const int k = blockIdx.x * 128 + threadIdx.x;
+    bool ok = false;
+    if (k < H) {
+        double T[16];
+        ok = ransac_check_one(P->src, P->tgt, P->corres, P->n_corres, nullptr, P->seed, P->h0 + k, edge_thr, dist_thr,
+                              use_checkers, T);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, ok);
+    if (m == 0) return;
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(&npass[blockIdx.y], __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (ok) ids[P->list_off + base + __popc(m & ((1u << lane) - 1u))] = k;
+}
+
+// transforms of the validated hypotheses: grid (ceil(max npass / 64), problems)
+__global__ void __launch_bounds__(64) hyp_transform_batch_kernel(const RbProb *__restrict__ probs, const int32_t *__restrict__ ids,
+                                                                 const int32_t *__restrict__ npass, double *__restrict__ T_out) {
+    const RbProb *P = probs + blockIdx.y;
+    const int j = blockIdx.x * 64 + threadIdx.x;
+    if (j >= npass[blockIdx.y]) return;
+    double s[9], t[9], T[16];
+    gather_sample(P->src, P->tgt, P->corres, P->n_corres, nullptr, P->seed, P->h0 + ids[P->list_off + j], s, t);
+    ibl_kabsch3(s, t, T);
+    double *o = T_out + (size_t)(P->val_off + j) * 16;
+#pragma unroll
+    for (int e = 0; e < 16; ++e) o[e] = T[e];
+}
+
+// which problem does work item `item` belong to: prefix[p] <= item < prefix[p+1]
+__device__ __forceinline__ int rb_find(const int64_t *__restrict__ prefix, int n, int64_t item) {
+    int lo = 0, hi = n;
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (prefix[mid] <= item) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// One CTA = one (problem, validated hypothesis, source tile) of the round; the same per-point test and the same integer
+// accumulation as ransac_count_kernel.
+__global__ void __launch_bounds__(SCORE_THREADS) ransac_count_batch_kernel(const RbProb *__restrict__ probs, int nprob,
+                                                                           const int64_t *__restrict__ item_prefix,
+                                                                           const double *__restrict__ T_all, double max_d,
+                                                                           double max_d2, int32_t *__restrict__ inliers) {
+    __shared__ GridView g;
+    __shared__ double T[16];
+    __shared__ int sc[SCORE_THREADS / 32];
+    __shared__ int s_p;
+    __shared__ int64_t s_entry, s_tile;
+    if (threadIdx.x == 0) {
+        const int p = rb_find(item_prefix, nprob, (int64_t)blockIdx.x);
+        const int64_t local = (int64_t)blockIdx.x - item_prefix[p];
+        const int nt = probs[p].ntiles;
+        s_p = p; s_entry = probs[p].val_off + local / nt; s_tile = local % nt;
+    }
+    __syncthreads();
+    const RbProb *P = probs + s_p;
+    for (int k = threadIdx.x; k < (int)(sizeof(GridView) / 4); k += SCORE_THREADS)
+        reinterpret_cast<int *>(&g)[k] = reinterpret_cast<const int *>(&P->g)[k];
+    if (threadIdx.x < 16) T[threadIdx.x] = T_all[(size_t)s_entry * 16 + threadIdx.x];
+    __syncthreads();
+    const double *__restrict__ src = P->src;
+    const int64_t n_src = P->n_src;
+    int cnt = 0;
+    const int64_t base = s_tile * SCORE_TILE;
+    const bool field = g.has_field && max_d <= g.f.max_d;
+    const bool sure_ok = field && max_d == g.f.max_d;
+#pragma unroll 1
+    for (int r = 0; r < SCORE_TILE / SCORE_THREADS; ++r) {
+        int64_t i = base + r * SCORE_THREADS + threadIdx.x;
+        if (i < n_src) {
+            double x, y, z, bd;
+            ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
+            if (field) cnt += ibl_any_within_field(g, x, y, z, max_d2, sure_ok) ? 1 : 0;
+            else cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
+        }
+    }
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int o = 16; o; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+    if (lane == 0) sc[w] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tc = 0;
+        for (int k = 0; k < SCORE_THREADS / 32; ++k) tc += sc[k];
+        if (tc) atomicAdd(&inliers[s_entry], tc);
+    }
+}
+
+// exact score of the contenders: one CTA = (contender, source tile); contender c of the batch refers to validated entry
+// sel_entry[c] (its transform) and problem sel_prob[c]; tile partials go to part[part_off[c] + tile] (ransac_score_kernel's
+// reduction order inside the CTA).
+__global__ void __launch_bounds__(SCORE_THREADS) ransac_score_batch_kernel(const RbProb *__restrict__ probs,
+                                                                           const int64_t *__restrict__ item_prefix, int nsel,
+                                                                           const int32_t *__restrict__ sel_prob,
+                                                                           const int64_t *__restrict__ sel_entry,
+                                                                           const double *__restrict__ T_all, double max_d,
+                                                                           double max_d2, int *__restrict__ part_cnt,
+                                                                           double *__restrict__ part_err) {
+    __shared__ GridView g;
+    __shared__ double T[16];
+    __shared__ double se[SCORE_THREADS / 32];
+    __shared__ int sc[SCORE_THREADS / 32];
+    __shared__ int s_c;
+    if (threadIdx.x == 0) s_c = rb_find(item_prefix, nsel, (int64_t)blockIdx.x);
+    __syncthreads();
+    const int c = s_c;
+    const int64_t tile = (int64_t)blockIdx.x - item_prefix[c];
+    const RbProb *P = probs + sel_prob[c];
+    for (int k = threadIdx.x; k < (int)(sizeof(GridView) / 4); k += SCORE_THREADS)
+        reinterpret_cast<int *>(&g)[k] = reinterpret_cast<const int *>(&P->g)[k];
+    if (threadIdx.x < 16) T[threadIdx.x] = T_all[(size_t)sel_entry[c] * 16 + threadIdx.x];
+    __syncthreads();
+    const double *__restrict__ src = P->src;
+    const int64_t n_src = P->n_src;
+    int cnt = 0;
+    double err = 0.0;
+    const int64_t base = tile * SCORE_TILE;
+#pragma unroll 1
+    for (int r = 0; r < SCORE_TILE / SCORE_THREADS; ++r) {
+        int64_t i = base + r * SCORE_THREADS + threadIdx.x;
+        if (i < n_src) {
+            double x, y, z, bd;
+            ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
+            int j = ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd);
+            if (j >= 0) { ++cnt; err = __dadd_rn(err, bd); }
+        }
+    }
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int o = 16; o; o >>= 1) { err += __shfl_down_sync(0xffffffffu, err, o); cnt += __shfl_down_sync(0xffffffffu, cnt, o); }
+    if (lane == 0) { se[w] = err; sc[w] = cnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double te = 0; int tc = 0;
+        for (int k = 0; k < SCORE_THREADS / 32; ++k) { te += se[k]; tc += sc[k]; }
+        part_cnt[blockIdx.x] = tc;
+        part_err[blockIdx.x] = te;
+    }
+}
+
+// one CTA per contender: tile partials in ransac_finalize_kernel's order + the correspondence inlier count
+__global__ void __launch_bounds__(FIN_THREADS) ransac_finalize_batch_kernel(const RbProb *__restrict__ probs,
+                                                                            const int64_t *__restrict__ item_prefix,
+                                                                            const int32_t *__restrict__ sel_prob,
+                                                                            const int64_t *__restrict__ sel_entry,
+                                                                            const int *__restrict__ part_cnt,
+                                                                            const double *__restrict__ part_err,
+                                                                            const double *__restrict__ T_all, double max_d,
+                                                                            int32_t *__restrict__ inliers, double *__restrict__ err2,
+                                                                            int32_t *__restrict__ corres_inliers) {
+    __shared__ double se[FIN_THREADS / 32];
+    __shared__ int sc[FIN_THREADS / 32], si[FIN_THREADS / 32];
+    __shared__ double T[16];
+    const int c = blockIdx.x;
+    const RbProb *P = probs + sel_prob[c];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (threadIdx.x < 16) T[threadIdx.x] = T_all[(size_t)sel_entry[c] * 16 + threadIdx.x];
+    __syncthreads();
+    const int64_t p0 = item_prefix[c];
+    const int ntiles = (int)(item_prefix[c + 1] - p0);
+    double e = 0; int cn = 0;
+    for (int k = threadIdx.x; k < ntiles; k += FIN_THREADS) { e += part_err[p0 + k]; cn += part_cnt[p0 + k]; }
+    int ci = 0;
+    {
+        const double *__restrict__ src = P->src, *__restrict__ tgt = P->tgt;
+        const int32_t *__restrict__ corres = P->corres;
+        const double md2 = max_d * max_d;
+        for (int64_t k = threadIdx.x; k < P->n_corres; k += FIN_THREADS) {
+            size_t cs = (size_t)corres[2 * k], ct = (size_t)corres[2 * k + 1];
+            double x, y, z;
+            ibl_xform(T, src[3 * cs], src[3 * cs + 1], src[3 * cs + 2], x, y, z);
+            double d[3] = {x - tgt[3 * ct], y - tgt[3 * ct + 1], z - tgt[3 * ct + 2]};
+            ci += ibl_dot(d, d) < md2;
+        }
+    }
+    for (int o = 16; o; o >>= 1) {
+        e += __shfl_down_sync(0xffffffffu, e, o);
+        cn += __shfl_down_sync(0xffffffffu, cn, o);
+        ci += __shfl_down_sync(0xffffffffu, ci, o);
+    }
+    if (lane == 0) { se[w] = e; sc[w] = cn; si[w] = ci; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double te = 0; int tc = 0, ti = 0;
+        for (int k = 0; k < FIN_THREADS / 32; ++k) { te += se[k]; tc += sc[k]; ti += si[k]; }
+        inliers[c] = tc; err2[c] = te; corres_inliers[c] = ti;
+    }
+}
+
+#define RB_MAX_BLOCK (1 << 19)     // hypotheses per problem per round, at most (bounds the id lists: 2 MB per problem)
+
+IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_problems, int64_t max_iteration,
+                                 double confidence, double max_d, double edge_thr, int use_checkers, int early_exit,
+                                 int64_t first_block, ibl_reg_result_t *h_results, void *stream) {
+    IBL_ARG(n_problems >= 0 && (n_problems == 0 || (problems && h_results)) && max_d > 0 && n_problems <= 65535);
+    if (n_problems == 0) return IBL_OK;
+    cudaStream_t st = ibl_stream(stream);
+    const int P = n_problems;
+    if (first_block <= 0) first_block = 1 << 14;
+    struct Host { int64_t est_k, h0, cur_block; double best_fit, best_rmse; bool active; };
+    std::vector<Host> hs(P);
+    std::vector<RbProb> hp(P);
+    for (int p = 0; p < P; ++p) {
+        const ibl_reg_problem_t &q = problems[p];
+        ibl_reg_result_t &r = h_results[p];
+        memset(&r, 0, sizeof(r));
+        for (int k = 0; k < 16; ++k) r.T[k] = (k % 5 == 0) ? 1.0 : 0.0;
+        r.best_hyp = -1;
+        r.n_corres = q.n_corres;
+        hs[p] = Host{max_iteration, 0, std::min<int64_t>(first_block, RB_MAX_BLOCK), 0.0, 0.0, true};
+        if (q.n_corres < 3 || max_iteration <= 0 || q.n_src <= 0 || !q.grid_ransac) { r.status = 1; hs[p].active = false; }
+        IBL_ARG(!hs[p].active || (q.src && q.tgt && q.corres && q.n_corres < (1ll << 31)));
+        RbProb &d = hp[p];
+        memset(&d, 0, sizeof(d));
+        if (hs[p].active) d.g = ibl_view(q.grid_ransac);
+        d.src = q.src; d.tgt = q.tgt; d.corres = q.corres; d.n_src = q.n_src; d.n_corres = q.n_corres; d.seed = q.seed;
+        d.ntiles = (int)std::max<int64_t>(1, (q.n_src + SCORE_TILE - 1) / SCORE_TILE);
+    }
+    RbProb *d_probs = nullptr; int32_t *d_npass = nullptr;
+    IBL_CUDA(ibl_alloc(&d_probs, (size_t)P, st));
+    IBL_CUDA(ibl_alloc(&d_npass, (size_t)P, st));
+    std::vector<int32_t> h_npass(P), h_ids, h_inl, h_inl2, h_cinl, sel_prob;
+    std::vector<int64_t> item_prefix(P + 1), sel_entry, sel_prefix;
+    std::vector<double> h_err, h_T;
+    struct Cand { int32_t id; int32_t inl; int64_t entry; int sel; };
+    std::vector<std::vector<Cand>> cands(P);
+    int rc = IBL_OK;
+    for (;;) {
+        // ---- this round's block per problem
+        int64_t cap = 0; int maxH = 0; bool any = false;
+        for (int p = 0; p < P; ++p) {
+            RbProb &d = hp[p];
+            d.H = 0;
+            Host &h = hs[p];
+            if (h.active && !(h.h0 < max_iteration && h.h0 < h.est_k)) h.active = false;
+            if (!h.active) continue;
+            int64_t H = std::min(h.cur_block, std::min(max_iteration, h.est_k) - h.h0);
+            d.H = (int32_t)H; d.h0 = h.h0; d.list_off = cap;
+            cap += H; maxH = std::max(maxH, (int)H); any = true;
+        }
+        if (!any) break;
+        int32_t *d_ids = nullptr;
+        IBL_CUDA(ibl_alloc(&d_ids, (size_t)cap, st));
+        IBL_CUDA(cudaMemcpyAsync(d_probs, hp.data(), sizeof(RbProb) * P, cudaMemcpyHostToDevice, st));
+        IBL_CUDA(cudaMemsetAsync(d_npass, 0, sizeof(int32_t) * P, st));
+        {
+            IBL_PROF(IBL_PROF_RANSAC_CHECK, st, 157.0 * (double)cap);
+            ransac_check_batch_kernel<<<dim3((unsigned)((maxH + 127) / 128), (unsigned)P), 128, 0, st>>>(d_probs, edge_thr, max_d,
+                                                                                                      use_checkers, d_ids, d_npass);
+            IBL_LAUNCH_CHECK();
+        }
+        IBL_CUDA(cudaMemcpyAsync(h_npass.data(), d_npass, sizeof(int32_t) * P, cudaMemcpyDeviceToHost, st));
+        IBL_CUDA(ibl_sync(st));                                                              // sync 1: validated counts
+        int64_t nval = 0, items = 0; int maxpass = 0;
+        for (int p = 0; p < P; ++p) {
+            RbProb &d = hp[p];
+            int np = d.H > 0 ? h_npass[p] : 0;
+            h_npass[p] = np;
+            d.val_off = nval;
+            item_prefix[p] = items;
+            nval += np; items += (int64_t)np * d.ntiles; maxpass = std::max(maxpass, np);
+        }
+        item_prefix[P] = items;
+        if (nval > 0) {
+            if (items >= (1ll << 31)) { ibl_set_error("ransac batch: %lld count work items in one round", (long long)items); rc = IBL_E_ARG; ibl_free(d_ids, st); break; }
+            double *d_Ts = nullptr; int32_t *d_inl = nullptr; int64_t *d_prefix = nullptr;
+            IBL_CUDA(ibl_alloc(&d_Ts, (size_t)nval * 16, st));
+            IBL_CUDA(ibl_alloc(&d_inl, (size_t)nval, st));
+            IBL_CUDA(ibl_alloc(&d_prefix, (size_t)P + 1, st));
+            IBL_CUDA(cudaMemcpyAsync(d_probs, hp.data(), sizeof(RbProb) * P, cudaMemcpyHostToDevice, st));   // val_off
+            IBL_CUDA(cudaMemcpyAsync(d_prefix, item_prefix.data(), sizeof(int64_t) * (P + 1), cudaMemcpyHostToDevice, st));
+            IBL_CUDA(cudaMemsetAsync(d_inl, 0, sizeof(int32_t) * nval, st));
+            hyp_transform_batch_kernel<<<dim3((unsigned)((maxpass + 63) / 64), (unsigned)P), 64, 0, st>>>(d_probs, d_ids, d_npass, d_Ts);
+            IBL_LAUNCH_CHECK();
+            {
+                double work = 0;
+                for (int p = 0; p < P; ++p) work += (double)h_npass[p] * (24.0 * hp[p].n_src + 128.0);
+                IBL_PROF(IBL_PROF_RANSAC_SCORE, st, work);
+                ransac_count_batch_kernel<<<(unsigned)items, SCORE_THREADS, 0, st>>>(d_probs, P, d_prefix, d_Ts, max_d, max_d * max_d, d_inl);
+                IBL_LAUNCH_CHECK();
+            }
+            h_ids.resize(cap); h_inl.resize(nval);
+            // the id lists are sparse inside ids[] (capacity H per problem): copy each problem's used prefix
+            for (int p = 0; p < P; ++p)
+                if (h_npass[p] > 0)
+                    IBL_CUDA(cudaMemcpyAsync(h_ids.data() + hp[p].list_off, d_ids + hp[p].list_off, sizeof(int32_t) * h_npass[p],
+                                             cudaMemcpyDeviceToHost, st));
+            IBL_CUDA(cudaMemcpyAsync(h_inl.data(), d_inl, sizeof(int32_t) * nval, cudaMemcpyDeviceToHost, st));
+            IBL_CUDA(ibl_sync(st));                                                          // sync 2: inlier counts
+            // ---- contenders: in id order, a hypothesis whose count reaches the running maximum before it
+            sel_prob.clear(); sel_entry.clear(); sel_prefix.assign(1, 0);
+            for (int p = 0; p < P; ++p) {
+                std::vector<Cand> &cv = cands[p];
+                cv.clear();
+                const int np = h_npass[p];
+                if (np == 0) continue;
+                cv.resize(np);
+                for (int j = 0; j < np; ++j) cv[j] = Cand{h_ids[hp[p].list_off + j], h_inl[hp[p].val_off + j], hp[p].val_off + j, -1};
+                std::sort(cv.begin(), cv.end(), [](const Cand &a, const Cand &b) { return a.id < b.id; });
+                int64_t run_max = h_results[p].best_hyp >= 0 ? h_results[p].n_inliers : 0;
+                for (Cand &c : cv) {
+                    if (hp[p].h0 + c.id >= hs[p].est_k) break;
+                    if (c.inl > 0 && c.inl >= run_max) {
+                        c.sel = (int)sel_prob.size();
+                        sel_prob.push_back(p); sel_entry.push_back(c.entry);
+                        sel_prefix.push_back(sel_prefix.back() + hp[p].ntiles);
+                        run_max = c.inl;
+                    }
+                }
+            }
+            const int nsel = (int)sel_prob.size();
+            if (nsel > 0) {
+                int32_t *d_sp = nullptr, *d_i2 = nullptr, *d_ci = nullptr; int64_t *d_se = nullptr, *d_spre = nullptr;
+                int *d_pc = nullptr; double *d_pe = nullptr, *d_err = nullptr;
+                const int64_t sitems = sel_prefix.back();
+                IBL_CUDA(ibl_alloc(&d_sp, (size_t)nsel, st)); IBL_CUDA(ibl_alloc(&d_se, (size_t)nsel, st));
+                IBL_CUDA(ibl_alloc(&d_spre, (size_t)nsel + 1, st));
+                IBL_CUDA(ibl_alloc(&d_pc, (size_t)sitems, st)); IBL_CUDA(ibl_alloc(&d_pe, (size_t)sitems, st));
+                IBL_CUDA(ibl_alloc(&d_i2, (size_t)nsel, st)); IBL_CUDA(ibl_alloc(&d_ci, (size_t)nsel, st));
+                IBL_CUDA(ibl_alloc(&d_err, (size_t)nsel, st));
+                IBL_CUDA(cudaMemcpyAsync(d_sp, sel_prob.data(), sizeof(int32_t) * nsel, cudaMemcpyHostToDevice, st));
+                IBL_CUDA(cudaMemcpyAsync(d_se, sel_entry.data(), sizeof(int64_t) * nsel, cudaMemcpyHostToDevice, st));
+                IBL_CUDA(cudaMemcpyAsync(d_spre, sel_prefix.data(), sizeof(int64_t) * (nsel + 1), cudaMemcpyHostToDevice, st));
+                {
+                    double work = 0;
+                    for (int c = 0; c < nsel; ++c) work += 24.0 * hp[sel_prob[c]].n_src + 128.0;
+                    IBL_PROF(IBL_PROF_RANSAC_SCORE, st, work);
+                    ransac_score_batch_kernel<<<(unsigned)sitems, SCORE_THREADS, 0, st>>>(d_probs, d_spre, nsel, d_sp, d_se, d_Ts, max_d,
+                                                                                        max_d * max_d, d_pc, d_pe);
+                    IBL_LAUNCH_CHECK();
+                }
+                ransac_finalize_batch_kernel<<<(unsigned)nsel, FIN_THREADS, 0, st>>>(d_probs, d_spre, d_sp, d_se, d_pc, d_pe, d_Ts, max_d,
+                                                                                   d_i2, d_err, d_ci);
+                IBL_LAUNCH_CHECK();
+                h_inl2.resize(nsel); h_cinl.resize(nsel); h_err.resize(nsel); h_T.resize((size_t)nsel * 16);
+                IBL_CUDA(cudaMemcpyAsync(h_inl2.data(), d_i2, sizeof(int32_t) * nsel, cudaMemcpyDeviceToHost, st));
+                IBL_CUDA(cudaMemcpyAsync(h_cinl.data(), d_ci, sizeof(int32_t) * nsel, cudaMemcpyDeviceToHost, st));
+                IBL_CUDA(cudaMemcpyAsync(h_err.data(), d_err, sizeof(double) * nsel, cudaMemcpyDeviceToHost, st));
+                for (int c = 0; c < nsel; ++c)
+                    IBL_CUDA(cudaMemcpyAsync(&h_T[(size_t)c * 16], d_Ts + (size_t)sel_entry[c] * 16, sizeof(double) * 16,
+                                             cudaMemcpyDeviceToHost, st));
+                IBL_CUDA(ibl_sync(st));                                                      // sync 3: exact scores
+                ibl_free(d_sp, st); ibl_free(d_se, st); ibl_free(d_spre, st); ibl_free(d_pc, st); ibl_free(d_pe, st);
+                ibl_free(d_i2, st); ibl_free(d_ci, st); ibl_free(d_err, st);
+            }
+            // ---- the ordered rule, per problem (ibl_ransac_run_range's loop body)
+            for (int p = 0; p < P && rc == IBL_OK; ++p) {
+                ibl_reg_result_t &r = h_results[p];
+                Host &h = hs[p];
+                for (const Cand &c : cands[p]) {
+                    const int64_t hid = hp[p].h0 + c.id;
+                    if (hid >= h.est_k) break;
+                    r.validated++;
+                    const int j = c.sel;
+                    if (j < 0) continue;
+                    if (h_inl2[j] != c.inl) { ibl_set_error("ransac batch: count pass and exact pass disagree"); rc = IBL_E_CUDA; break; }
+                    const double n_src = (double)hp[p].n_src;
+                    double fit = (double)h_inl2[j] / n_src;
+                    double rmse = h_inl2[j] > 0 ? sqrt(h_err[j] / (double)h_inl2[j]) : 0.0;
+                    if (fit > h.best_fit || (fit == h.best_fit && rmse < h.best_rmse)) {
+                        h.best_fit = fit; h.best_rmse = rmse;
+                        r.fitness = fit; r.inlier_rmse = rmse; r.n_inliers = h_inl2[j]; r.err2 = h_err[j]; r.best_hyp = hid;
+                        memcpy(r.T, &h_T[(size_t)j * 16], sizeof(double) * 16);
+                        if (early_exit) {
+                            double rho = (double)h_cinl[j] / (double)hp[p].n_corres;
+                            double den = rho < 1.0 ? log(1.0 - rho * rho * rho) : -INFINITY;
+                            double kk = den == 0.0 ? INFINITY : log(1.0 - confidence) / den;
+                            if (kk < (double)h.est_k) h.est_k = (int64_t)ceil(kk);
+                        }
+                    }
+                }
+                cands[p].clear();
+            }
+            ibl_free(d_Ts, st); ibl_free(d_inl, st); ibl_free(d_prefix, st);
+        }
+        ibl_free(d_ids, st);
+        if (rc < 0) break;
+        for (int p = 0; p < P; ++p) {
+            if (hp[p].H == 0) continue;
+            hs[p].h0 += hp[p].H;
+            hs[p].cur_block = std::min<int64_t>(hs[p].cur_block * 2, RB_MAX_BLOCK);
+        }
+    }
+    for (int p = 0; p < P; ++p)
+        if (h_results[p].status == 0)
+            h_results[p].drawn = std::max<int64_t>(std::min(max_iteration, std::max<int64_t>(hs[p].est_k, 0)), 0);
+    ibl_free(d_probs, st); ibl_free(d_npass, st);
     return rc;
 }

@@ -10,7 +10,7 @@ from ctypes import c_double, c_int64
 import numpy as np
 import torch
 
-from ._lib import IblError, RegResultT, ScoreT, check, lib
+from ._lib import IblError, RegProblemT, RegResultT, ScoreT, check, lib
 
 F64 = torch.float64
 
@@ -365,6 +365,60 @@ def icp(grid, src, tgt, max_d, init=None, mode=0, scol=None, tnrm=None, tcol=Non
                         float(max_d), _T16(init), int(max_iteration), float(rel_fitness), float(rel_rmse),
                         float(lambda_geometric), ctypes.byref(r), _stream()), "icp")
     return _reg_dict(r)
+
+
+# --------------------------------------------------------------------------- batched registration
+def reg_problems(specs):
+    """specs: list of dicts {src, src_col, tgt, tgt_nrm, tgt_col, tgt_grad (CUDA f64 [n,3] or None), grid_ransac, grid_icp
+    (Grid or None), corres (CUDA int32 [C,2] or None), seed} -> ctypes array of ibl_reg_problem_t.  The caller keeps the
+    tensors alive."""
+    arr = (RegProblemT * len(specs))()
+    for q, sp in zip(arr, specs):
+        src, cor = sp["src"], sp.get("corres")
+        q.src, q.src_col, q.n_src = src.data_ptr(), (sp["src_col"].data_ptr() if sp.get("src_col") is not None else None), src.shape[0]
+        tgt = sp["tgt"]
+        q.tgt, q.n_tgt = tgt.data_ptr(), tgt.shape[0]
+        for k in ("tgt_nrm", "tgt_col", "tgt_grad"):
+            setattr(q, k, sp[k].data_ptr() if sp.get(k) is not None else None)
+        q.grid_ransac = sp["grid_ransac"].h if sp.get("grid_ransac") is not None else None
+        q.grid_icp = sp["grid_icp"].h if sp.get("grid_icp") is not None else None
+        q.corres, q.n_corres = (cor.data_ptr(), cor.shape[0]) if cor is not None else (None, 0)
+        q.seed = int(sp.get("seed", 0))
+    return arr
+
+
+def ransac_run_batch(problems, max_iteration, confidence, max_d, edge_thr=0.9, use_checkers=True, early_exit=True,
+                     block=1 << 14):
+    """ibl_ransac_run_batch over a reg_problems() array -> list of result dicts (one per problem, ransac_run's fields)."""
+    n = len(problems)
+    res = (RegResultT * n)()
+    check(lib().ibl_ransac_run_batch(problems, n, int(max_iteration), float(confidence), float(max_d), float(edge_thr),
+                                     int(use_checkers), int(early_exit), int(block), res, _stream()), "ransac_run_batch")
+    return [_reg_dict(r) for r in res]
+
+
+def icp_colored_batch(problems, T_init, max_d, max_iteration=30, rel_fitness=1e-6, rel_rmse=1e-6, lambda_geometric=0.968):
+    """ibl_icp_colored_batch: T_init host [n,4,4] -> list of result dicts."""
+    n = len(problems)
+    res = (RegResultT * n)()
+    Ti = np.ascontiguousarray(np.asarray(T_init, np.float64).reshape(n, 16))
+    check(lib().ibl_icp_colored_batch(problems, n, Ti.ctypes.data_as(ctypes.POINTER(c_double)), float(max_d), int(max_iteration),
+                                      float(rel_fitness), float(rel_rmse), float(lambda_geometric), res, _stream()),
+          "icp_colored_batch")
+    return [_reg_dict(r) for r in res]
+
+
+def nn_score_batch(grid, srcs, Ts, max_d):
+    """evaluate_registration of many (source tensor, 4x4 transform) pairs against one target grid
+    -> list of (n_inliers, err2)."""
+    n = len(srcs)
+    ptrs = (ctypes.c_void_p * n)(*[s.data_ptr() if s.shape[0] else None for s in srcs])
+    ns = (c_int64 * n)(*[int(s.shape[0]) for s in srcs])
+    Th = np.ascontiguousarray(np.asarray(Ts, np.float64).reshape(n, 16))
+    res = (ScoreT * n)()
+    check(lib().ibl_nn_score_batch(grid.h, ptrs, ns, Th.ctypes.data_as(ctypes.POINTER(c_double)), n, float(max_d), res,
+                                   _stream()), "nn_score_batch")
+    return [(int(r.n_inliers), float(r.err2)) for r in res]
 
 
 # ------------------------------------------------------------------------------------ similarity

@@ -9,6 +9,7 @@ RANSAC sampling: Open3D 0.17 draws correspondence triplets from a thread-local m
 from __future__ import annotations
 
 import os
+import threading
 
 import numpy as np
 import torch
@@ -20,7 +21,19 @@ from .pointcloud import DeviceVec, PointCloud
 ransac_seed = 0                  # seed of the counter-based sample stream
 ransac_sampler = None            # optional callable (C, H) -> int32 [H,3] host array (overrides the seed)
 ransac_block = 1 << 14           # hypotheses checked per device block before the ordered host scan
-last_ransac_info = {}
+ransac_max_iteration = None      # benchmark knob: overrides criteria.max_iteration (configs[2]/[4]: a FIXED hypothesis count)
+ransac_early_exit = True         # benchmark knob: False disables the adaptive stop (every hypothesis of the stream is drawn)
+last_ransac_info = {}            # most recent RANSAC of ANY thread (kept for tools); per-thread copy: last_info()
+_tls = threading.local()
+
+
+def last_info():
+    """What the calling thread's most recent registration did: RANSAC {drawn, validated, n_corres, ...} and ICP
+    {iterations, ...}.  Thread-local, because localise_batch registers frames on several host threads."""
+    d = getattr(_tls, "info", None)
+    if d is None:
+        d = _tls.info = {}
+    return d
 
 
 class Feature:
@@ -169,15 +182,20 @@ def registration_ransac_based_on_correspondence(source, target, corres, max_corr
             use_checkers = True
     C = int(corres.shape[0])
     if C < ransac_n:
+        last_info()["ransac"] = {"drawn": 0, "validated": 0, "best_hyp": -1, "n_corres": C, "n_inliers": 0, "err2": 0.0}
         return RegistrationResult()
     samples = None
     if ransac_sampler is not None:
         samples = K.to_dev(np.ascontiguousarray(ransac_sampler(C, criteria.max_iteration), np.int32), torch.int32)
+    max_it = criteria.max_iteration if ransac_max_iteration is None else int(ransac_max_iteration)
     r = K.ransac_run(_nn_grid(target, max_correspondence_distance), source._p, target._p, corres,
-                     criteria.max_iteration, criteria.confidence, max_correspondence_distance, edge_thr=edge,
-                     samples=samples, seed=ransac_seed, use_checkers=use_checkers, early_exit=True, block=ransac_block)
+                     max_it, criteria.confidence, max_correspondence_distance, edge_thr=edge,
+                     samples=samples, seed=ransac_seed, use_checkers=use_checkers, early_exit=bool(ransac_early_exit),
+                     block=ransac_block)
+    rinfo = {k: r[k] for k in ("drawn", "validated", "best_hyp", "n_corres", "n_inliers", "err2")}
     last_ransac_info.clear()
-    last_ransac_info.update({k: r[k] for k in ("drawn", "validated", "best_hyp", "n_corres", "n_inliers", "err2")})
+    last_ransac_info.update(rinfo)
+    last_info()["ransac"] = rinfo
     return RegistrationResult(r["T"], r["fitness"], r["inlier_rmse"], info=r)
 
 
@@ -219,6 +237,7 @@ def registration_icp(source, target, max_correspondence_distance, init=None, est
     r = K.icp(g, source._p, target._p, max_correspondence_distance, init, mode=0,
               max_iteration=criteria.max_iteration, rel_fitness=criteria.relative_fitness,
               rel_rmse=criteria.relative_rmse)
+    last_info()["icp"] = {"mode": "p2p", "iterations": r["iterations"], "n_inliers": r["n_inliers"]}
     return RegistrationResult(r["T"], r["fitness"], r["inlier_rmse"], info=r)
 
 
@@ -256,4 +275,5 @@ def registration_colored_icp(source, target, max_correspondence_distance, init=N
               tcol=target._c, tgrad=grad[1], max_iteration=criteria.max_iteration,
               rel_fitness=criteria.relative_fitness, rel_rmse=criteria.relative_rmse,
               lambda_geometric=est.lambda_geometric)
+    last_info()["icp"] = {"mode": "colored", "iterations": r["iterations"], "n_inliers": r["n_inliers"]}
     return RegistrationResult(r["T"], r["fitness"], r["inlier_rmse"], info=r)

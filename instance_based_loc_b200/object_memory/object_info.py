@@ -15,7 +15,12 @@ from ..utils.depth_utils import voxel_down_sample_with_colors
 
 
 class ObjectInfo:
+    # Pickles name the reference's class path (object_memory/object_info.py:7), so a memory bank written here loads in the
+    # unmodified reference and vice versa (ObjectMemory.read_pkl maps the path back to this class).
+    __module__ = "object_memory.object_info"
+
     def __init__(self, id, name, emb, pointcloud, max_embeddings_num):
+        self._version = 0                       # bumped by every mutation; ObjectMemory's caches key on it
         self.id = id
         self.names = [name]
         self.embeddings = [emb]
@@ -36,6 +41,23 @@ class ObjectInfo:
         state.pop("pcd", None)
         state.pop("pcd_colors", None)
         self.__dict__.update(state)
+        self.__dict__.setdefault("_version", 0)
+
+    def __getstate__(self):
+        """What the reference's ObjectInfo holds (:9-19, :72-74): public attributes plus the eager 3xN host copies."""
+        state = {k: v for k, v in self.__dict__.items() if not k.startswith("_")}
+        empty = np.zeros((3, 0))
+        state["pcd"] = empty if self.pointcloud is None else self.pcd
+        state["pcd_colors"] = empty if self.pointcloud is None else self.pcd_colors
+        return state
+
+    def __setattr__(self, key, value):
+        if key in ("pointcloud", "embeddings"):
+            self.__dict__["_version"] = self.__dict__.get("_version", 0) + 1
+        object.__setattr__(self, key, value)
+
+    def _touch(self):
+        self._version = self.__dict__.get("_version", 0) + 1
 
     # the reference keeps eager 3xN host copies; here they are views on demand
     @property
@@ -59,6 +81,7 @@ class ObjectInfo:
 
     def _add_embedding(self, new_emb):
         """:38-57 (memory build only)."""
+        self._touch()
         if len(self.embeddings) < self.max_embeddings_num:
             self.embeddings.append(new_emb)
             return
@@ -71,7 +94,7 @@ class ObjectInfo:
             self.embeddings[j] = new_emb
 
     def _add_embeddings(self, new_embs):
-        self.embeddings += new_embs
+        self.embeddings += new_embs          # (an assignment: __setattr__ bumps the version)
 
     def _add_pointcloud(self, new_pointcloud):
         merged = PointCloud()

@@ -12,6 +12,7 @@ What is new relative to the reference (none of it changes results):
 """
 from __future__ import annotations
 
+import contextlib
 import copy
 import os
 import pickle
@@ -51,6 +52,27 @@ def check_if_floor(texts):
         if word in texts:
             return True
     return False
+
+
+@contextlib.contextmanager
+def _reference_class_path():
+    """ObjectInfo pickles under the reference's path ``object_memory.object_info`` (so the unmodified reference can load
+    the file); pickle insists that the path resolves while dumping, so it is aliased for the duration of the dump unless
+    the caller already installed the drop-in aliases."""
+    from . import object_info as _oi
+    import sys
+    added = []
+    for name, mod in (("object_memory", sys.modules[__package__]), ("object_memory.object_info", _oi)):
+        if name not in sys.modules:
+            sys.modules[name] = mod
+            added.append(name)
+    try:
+        if getattr(sys.modules["object_memory.object_info"], "ObjectInfo", None) is not ObjectInfo:
+            raise pickle.PicklingError("another object_memory.object_info is imported in this process")
+        yield
+    finally:
+        for name in added:
+            sys.modules.pop(name, None)
 
 
 class _MemoryUnpickler(pickle.Unpickler):
@@ -93,6 +115,7 @@ class ObjectMemory():
         self._tls = threading.local()
         self._pool, self._pool_workers = None, 0
         self.last_localise_info = {}
+        self.cache_stats = {"lookups": 0, "misses": 0}   # _chosen_memory: per-assignment-tuple memory-side features
 
     def _log(self, statement):
         if self.log_enabled:
@@ -308,15 +331,24 @@ class ObjectMemory():
         self._log(f"Saved memory to {save_directory}")
 
     def save_to_pkl(self, save_directory):
-        """:779-826 -- [(ObjectInfo-without-cloud, points f64[N,3], colors f64[N,3]), ...], floors tuple.  The
-        reference builds the floors tuple from the LAST object (bug, :804-824); reproduced."""
-        def strip(o):
-            b = copy.copy(o)
+        """:779-826 -- [(blank ObjectInfo, points f64[N,3], colors f64[N,3]), ...] plus a floors tuple.  As in the
+        reference every record is a FRESH blank ObjectInfo (id = the builtin ``id``, :790; names / embeddings /
+        means copied, no cloud), and the floors tuple is a separate record built from the LAST object (the reference's
+        loop variable leaks, :804-824) -- not the floors and not the same Python object as the last memory record."""
+        def blank(o):
+            b = ObjectInfo(0, "", o.embeddings[0], None, 1e5)
+            b.id = id
+            b.names = o.names
+            b.embeddings = o.embeddings
+            b.max_embeddings_num = o.max_embeddings_num
+            b.mean_emb = o.mean_emb
+            b.centroid = o.centroid
             b.pointcloud = None
             return (b, np.asarray(o.pointcloud.points), np.asarray(o.pointcloud.colors))
-        mem = [strip(o) for o in self.memory]
-        with open(save_directory, "wb") as f:
-            pickle.dump((mem, mem[-1] if mem else None), f)
+        mem = [blank(o) for o in self.memory]
+        floors = blank(self.memory[-1]) if self.memory else None
+        with open(save_directory, "wb") as f, _reference_class_path():
+            pickle.dump((mem, floors), f)
 
     @staticmethod
     def read_pkl(load_directory):
@@ -368,13 +400,22 @@ class ObjectMemory():
     # on several host threads / CUDA streams) and only read afterwards.  An entry is published after the building
     # stream has been synchronised, so readers on other streams never see half-built device data.
     def _memory_cache(self):
-        key = (len(self.memory),) + tuple(id(m.pointcloud._p) for m in self.memory) + \
-              tuple(len(m.embeddings) for m in self.memory)
+        # identity AND version of every record: ObjectInfo bumps ``_version`` on every mutation (cloud replaced or merged,
+        # embedding appended or swapped in place at capacity), so neither a recycled id() nor an unchanged length can
+        # leave stale device state behind
+        key = (len(self.memory),) + tuple((id(m), m._version, id(m.pointcloud._p)) for m in self.memory)
         with self._lock:
             if key != self._cache_key:
                 self._cache_key = key
                 self._cache = {"assn": {}}
             return self._cache
+
+    def clear_assignment_cache(self):
+        """Drop the per-assignment-tuple memory-side state (centred union cloud, normals, FPFH, NN fields, colour
+        gradients); per-object clouds, the embedding bank and the all-memory search grid stay."""
+        with self._lock:
+            torch.cuda.synchronize()
+            self._memory_cache()["assn"].clear()
 
     def _embedding_bank(self):
         with self._lock:
@@ -408,7 +449,9 @@ class ObjectMemory():
                float(local_dist_factor))
         with self._lock:
             c = self._memory_cache()["assn"]
+            self.cache_stats["lookups"] += 1
             if key not in c:
+                self.cache_stats["misses"] += 1
                 pcd = PointCloud()
                 for m_index in m_indices:
                     pcd = pcd + self.memory[m_index].pointcloud
@@ -421,8 +464,10 @@ class ObjectMemory():
                     _reg._nn_grid(tgt, fpfh_voxel_size * local_dist_factor)
                     if tgt.has_colors():
                         _reg.ensure_color_gradient(tgt, fpfh_voxel_size * local_dist_factor)
+                except K.IblError:
+                    raise                                  # a device / ABI error is not Open3D's "no normals" case
                 except Exception:
-                    feats = None
+                    feats = None                           # register_point_clouds then takes its own fallback branch
                 torch.cuda.current_stream().synchronize()
                 if len(c) > 512:
                     c.pop(next(iter(c)))
@@ -479,63 +524,107 @@ class ObjectMemory():
     # (per-assignment features, grids, NN fields: ~5 GB for the 40-object bank) happen to be built on that stream
     scratch_bytes_per_stream = 4 << 30
 
-    def localise_batch(self, frames, workers=4, **kw):
-        """localise_arrays over a batch of frames (dicts with rgb / depth / masks / embs), ``workers`` frames in flight
-        at a time, each on its own host thread and CUDA stream: frames are independent, and the
-        path is a long chain of small kernels with host decisions in between, so overlapping frames is what keeps
-        the SMs busy.  Results are identical to calling localise_arrays frame by frame.
+    def localise_batch(self, frames, workers=4, batched_registration=True, **kw):
+        """localise_arrays over a batch of frames (dicts with rgb / depth / masks / embs).  Frames are independent
+        (SURVEY.md 8(e)); the work is organised in two stages:
+
+          1. per frame, ``workers`` frames in flight on their own host threads / CUDA streams: back-projection, outlier
+             filters, similarities, SimVolume assignments, and per assignment the centred detected union with its normals,
+             FPFH features and feature correspondences (``_plan`` + ``_prepare_registrations``);
+          2. on the caller's stream, ALL (frame, assignment) registration problems of the batch together: one batched
+             RANSAC (``ibl_ransac_run_batch``), one batched coloured ICP (``ibl_icp_colored_batch``) and one batched
+             evaluate_transform (``ibl_nn_score_batch``) -- a handful of launches and host round trips per stage for the
+             whole batch instead of hundreds per frame.
+
+        ``batched_registration=False`` runs stage 2 frame by frame inside the workers (the round-1 organisation).
+        Results are identical to calling localise_arrays frame by frame either way.
         -> list of (pose, [assn, None], info)."""
         frames = list(frames)
         dev_index = torch.cuda.current_device()
+        batched = bool(batched_registration) and _reg.ransac_sampler is None
 
-        def one(fr, stream=None):
-            pose, assn = self.localise_arrays(fr["rgb"], fr["depth"], fr["masks"], fr["embs"], **kw)
-            return pose, assn, self._tls.info
+        def one(fr):
+            if not batched:
+                pose, assn = self.localise_arrays(fr["rgb"], fr["depth"], fr["masks"], fr["embs"], **kw)
+                return pose, assn, self._tls.info
+            plan = self._plan_arrays(fr["rgb"], fr["depth"], fr["masks"], fr["embs"], **kw)
+            if plan.get("registrations") is not None:
+                self._prepare_registrations(plan)
+            return plan
 
         if workers <= 1 or len(frames) <= 1:
-            return [one(fr) for fr in frames]
-        ready = torch.cuda.Event()
-        ready.record()                                       # inputs produced on the caller's stream (e.g. H2D copies)
+            out = [one(fr) for fr in frames]
+        else:
+            ready = torch.cuda.Event()
+            ready.record()                                   # inputs produced on the caller's stream (e.g. H2D copies)
 
-        def run(fr):
-            torch.cuda.set_device(dev_index)
-            st = getattr(self._tls, "stream", None)
-            if st is None:
-                st = self._tls.stream = torch.cuda.Stream()
-                if self.scratch_bytes_per_stream and not os.environ.get("IBL_NO_RESERVE"):
-                    with torch.cuda.stream(st):          # this frame stream's working set, mapped once (see ibl.h)
-                        K.reserve_scratch(self.scratch_bytes_per_stream)
-            st.wait_event(ready)
-            with torch.cuda.stream(st):
-                out = one(fr)
-                st.synchronize()
-            return out
+            def run(fr):
+                torch.cuda.set_device(dev_index)
+                st = getattr(self._tls, "stream", None)
+                if st is None:
+                    st = self._tls.stream = torch.cuda.Stream()
+                    if self.scratch_bytes_per_stream and not os.environ.get("IBL_NO_RESERVE"):
+                        with torch.cuda.stream(st):      # this frame stream's working set, mapped once (see ibl.h)
+                            K.reserve_scratch(self.scratch_bytes_per_stream)
+                st.wait_event(ready)
+                with torch.cuda.stream(st):
+                    r = one(fr)
+                    st.synchronize()
+                return r
 
-        if self._pool is None or self._pool_workers != workers:
-            if self._pool is not None:
-                self._pool.shutdown(wait=True)
-            self._pool, self._pool_workers = ThreadPoolExecutor(max_workers=workers), workers
-        # longest first: a frame's cost grows with its detected clouds, i.e. with its mask pixels; handing the heavy
-        # frames out first keeps the last worker from finishing long after the others (results keep the input order)
-        order = list(range(len(frames)))
-        try:
+            if self._pool is None or self._pool_workers != workers:
+                if self._pool is not None:
+                    self._pool.shutdown(wait=True)
+                self._pool, self._pool_workers = ThreadPoolExecutor(max_workers=workers), workers
+            # longest first: a frame's cost grows with its detected clouds, i.e. with its mask pixels; handing the heavy
+            # frames out first keeps the last worker from finishing long after the others (results keep the input order).
+            # Mask sizes come from the arrays' shapes and dtypes only -- no device read-back here.
+            order = list(range(len(frames)))
             if not os.environ.get("IBL_NO_LPT"):
-                px = torch.stack([torch.as_tensor(fr["masks"]).sum() for fr in frames]).cpu().tolist()
-                order.sort(key=lambda i: -px[i])
-        except Exception:
-            pass
-        out = [None] * len(frames)
-        for i, r in zip(order, self._pool.map(run, [frames[i] for i in order])):
-            out[i] = r
-        return out
+                order.sort(key=lambda i: -int(np.prod(np.shape(frames[i]["masks"]))))
+            out = [None] * len(frames)
+            for i, r in zip(order, self._pool.map(run, [frames[i] for i in order])):
+                out[i] = r
+        if not batched:
+            return out
+        self._register_batch([p for p in out if p.get("registrations") is not None])
+        res = []
+        for plan in out:
+            pose, assn = self._finish(plan)
+            res.append((pose, assn, plan["info"]))
+        return res
 
-    def _localise_core(self, detected_phrases, detected_embs, detected_pointclouds, outlier_removal_config,
-                       fpfh_global_dist_factor, fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
-                       max_detected_object_num):
-        info = self.last_localise_info = {"assignments": [], "registrations": []}
-        self._tls.info = info
+    # ------------------------------------------------------------------------------------------ plan / register / finish
+    def _plan_arrays(self, rgb_image, depth_image, masks, embeddings, phrases=None, outlier_removal_config=None,
+                     fpfh_global_dist_factor=2, fpfh_local_dist_factor=0.4, fpfh_voxel_size=0.05,
+                     perform_semantic_icp=True, depth_factor=1., max_detected_object_num=7):
+        """localise_arrays up to (not including) the registrations."""
+        if outlier_removal_config is None:
+            outlier_removal_config = {"radius_nb_points": 8, "radius": 0.05}
+        if masks is None or len(masks) == 0:
+            return self._plan(None, None, None, outlier_removal_config, fpfh_global_dist_factor, fpfh_local_dist_factor,
+                              fpfh_voxel_size, perform_semantic_icp, max_detected_object_num)
+        depth = depth_image
+        if depth_factor != 1.:
+            depth = depth_image / depth_factor
+        clouds = get_mask_coloured_pointclouds_from_depth(depth, rgb_image, masks, self.camera_focal_lenth_x,
+                                                          self.camera_focal_lenth_y, outlier_removal_config)
+        embs = embeddings.detach() if isinstance(embeddings, torch.Tensor) else np.array(embeddings)
+        phrases = phrases if phrases is not None else [f"object_{i}" for i in range(len(clouds))]
+        return self._plan(phrases, embs, clouds, outlier_removal_config, fpfh_global_dist_factor, fpfh_local_dist_factor,
+                          fpfh_voxel_size, perform_semantic_icp, max_detected_object_num)
+
+    def _plan(self, detected_phrases, detected_embs, detected_pointclouds, outlier_removal_config,
+              fpfh_global_dist_factor, fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
+              max_detected_object_num):
+        """:895-1034 -- everything of localise() before register_point_clouds: top-7 selection, closest similarities,
+        SimVolume assignments, second outlier filter, and per assignment the centred detected / memory unions.
+        -> plan dict; plan["registrations"] is None when nothing was detected (sentinel pose, :895-896)."""
+        info = {"assignments": [], "registrations": []}
+        plan = {"info": info, "registrations": None, "voxel": fpfh_voxel_size, "gfac": fpfh_global_dist_factor,
+                "lfac": fpfh_local_dist_factor}
         if detected_embs is None:
-            return np.array([0., 0., 0., 0., 0., 0., 1.]), [[], []]           # :895-896
+            return plan
 
         # take the largest clouds (:900-908; python's sort is stable, reverse keeps ties in input order)
         if len(detected_pointclouds) > max_detected_object_num:
@@ -561,7 +650,6 @@ class ObjectMemory():
         detected_pointclouds = [obj.remove_radius_outlier(nb_points=outlier_removal_config["radius_nb_points"],
                                                           radius=outlier_removal_config["radius"])[0]
                                 for obj in detected_pointclouds]
-        all_memory_pcd = self._all_memory_pcd()                                # :1001-1007
         all_detected_pcd = PointCloud()
         for pcd in detected_pointclouds:                                       # :1010-1016
             all_detected_pcd = all_detected_pcd + pcd
@@ -569,9 +657,8 @@ class ObjectMemory():
         if perform_semantic_icp and len(assn_data):
             raise NotImplementedError                                          # :1036-1037, as in the reference
 
-        detected_mean = memory_mean = None
-        assn = None
-        for assn_num, assn in enumerate(assn_data):                            # :1020
+        regs = []
+        for assn in assn_data:                                                 # :1020
             chosen_detected_pcd = PointCloud()
             for d_index, _ in assn:
                 chosen_detected_pcd = chosen_detected_pcd + detected_pointclouds[d_index]
@@ -579,19 +666,136 @@ class ObjectMemory():
                 [m for _, m in assn], fpfh_voxel_size, fpfh_global_dist_factor, fpfh_local_dist_factor)
             detected_mean = chosen_detected_pcd.get_center()
             chosen_detected_pcd.translate(-detected_mean)                      # :1030-1034
-            transform, rmse, fitness = register_point_clouds(
-                chosen_detected_pcd, chosen_memory_pcd, voxel_size=fpfh_voxel_size,
-                global_dist_factor=fpfh_global_dist_factor, local_dist_factor=fpfh_local_dist_factor,
-                target_features=target_feats)
-            global_frame_transform = np.array(transform, dtype=np.float64)     # :1096-1101
-            R = transform[:3, :3]
-            global_frame_transform[:3, 3] = transform[:3, 3] + memory_mean - R @ detected_mean
-            full_rmse, full_fitness = evaluate_transform(all_detected_pcd, all_memory_pcd,
-                                                         trans_init=global_frame_transform)      # :1104
-            assn_data[assn_num] = [assn, transform, rmse, fitness, full_rmse, full_fitness, detected_mean, memory_mean]
-            info["registrations"].append({"assn": assn, "transform": transform, "rmse": rmse, "fitness": fitness,
-                                          "full_rmse": full_rmse, "full_fitness": full_fitness})
+            regs.append({"assn": assn, "source": chosen_detected_pcd, "target": chosen_memory_pcd,
+                         "target_feats": target_feats, "detected_mean": detected_mean, "memory_mean": memory_mean})
+        plan["registrations"] = regs
+        plan["all_detected"] = all_detected_pcd
+        return plan
 
+    def _register_sequential(self, plan):
+        """:1036-1108 one assignment after the other: register_point_clouds, then evaluate_transform of the composed
+        global-frame transform over all detected points against the whole memory."""
+        all_memory_pcd = self._all_memory_pcd()                                # :1001-1007
+        for g in plan["registrations"]:
+            rinfo = _reg.last_info()
+            rinfo.clear()
+            transform, rmse, fitness = register_point_clouds(
+                g["source"], g["target"], voxel_size=plan["voxel"], global_dist_factor=plan["gfac"],
+                local_dist_factor=plan["lfac"], target_features=g["target_feats"])
+            G = self._global_transform(transform, g)
+            full_rmse, full_fitness = evaluate_transform(plan["all_detected"], all_memory_pcd, trans_init=G)   # :1104
+            g.update(transform=transform, rmse=rmse, fitness=fitness, full_rmse=full_rmse, full_fitness=full_fitness,
+                     ransac=dict(rinfo.get("ransac", {})), icp=dict(rinfo.get("icp", {})))
+
+    @staticmethod
+    def _global_transform(transform, g):
+        """:1096-1101 -- the centred registration expressed in the memory / camera frames."""
+        G = np.array(transform, dtype=np.float64)
+        G[:3, 3] = transform[:3, 3] + g["memory_mean"] - transform[:3, :3] @ g["detected_mean"]
+        return G
+
+    def _prepare_registrations(self, plan):
+        """The per-problem front half of register_point_clouds (fpfh_register.py:100-112) for every assignment of a
+        frame: source normals + FPFH and the mutual feature correspondences against the cached target features.  A failure
+        Open3D would raise (no normals, empty cloud) marks the problem for the reference's fallback branch."""
+        for g in plan["registrations"]:
+            g["fallback"] = None
+            try:
+                src_down, src_fpfh = downsample_and_compute_fpfh(g["source"], plan["voxel"])
+                if g["target_feats"] is not None:
+                    tgt_down, tgt_fpfh = g["target_feats"]
+                else:
+                    tgt_down, tgt_fpfh = downsample_and_compute_fpfh(g["target"], plan["voxel"])
+                g["src_down"], g["tgt_down"] = src_down, tgt_down
+                g["corres"] = _reg.match_features(src_fpfh, tgt_fpfh, True, 3)
+            except K.IblError:
+                raise
+            except Exception as e:                             # the reference's bare except (fpfh_register.py:137)
+                g["fallback"] = repr(e)
+
+    def _register_batch(self, plans):
+        """Stage 2 of localise_batch: RANSAC, coloured ICP and evaluate_transform of every (frame, assignment) problem of
+        the batch, each as ONE batched library call (fpfh_register.py:106-143,145-150 per problem)."""
+        probs = [(plan, g) for plan in plans for g in plan["registrations"]]
+        if not probs:
+            return
+        all_memory_pcd = self._all_memory_pcd()
+        by_cfg = {}
+        for plan, g in probs:
+            by_cfg.setdefault((plan["voxel"], plan["gfac"], plan["lfac"]), []).append((plan, g))
+        for (voxel, gfac, lfac), group in by_cfg.items():
+            max_d_r, max_d_i = voxel * gfac, voxel * lfac
+            live = [(plan, g) for plan, g in group if g["fallback"] is None]
+            # ---- RANSAC (fpfh_register.py:106-119)
+            specs = []
+            for plan, g in live:
+                sd, td = g["src_down"], g["tgt_down"]
+                colored = td.has_normals() and sd.has_colors() and td.has_colors()
+                g["colored"] = colored
+                grad = _reg.ensure_color_gradient(td, max_d_i)[1] if colored else None
+                specs.append({"src": sd._p, "src_col": sd._c if colored else None, "tgt": td._p,
+                              "tgt_nrm": td._n if colored else None, "tgt_col": td._c if colored else None, "tgt_grad": grad,
+                              "grid_ransac": _reg._nn_grid(td, max_d_r), "grid_icp": _reg._nn_grid(td, max_d_i),
+                              "corres": g["corres"], "seed": _reg.ransac_seed})
+            if live:
+                arr = K.reg_problems(specs)
+                max_it = 4000000 if _reg.ransac_max_iteration is None else int(_reg.ransac_max_iteration)   # :119
+                rr = K.ransac_run_batch(arr, max_it, 0.99, max_d_r, edge_thr=0.9, use_checkers=True,
+                                        early_exit=bool(_reg.ransac_early_exit), block=_reg.ransac_block)
+                for (plan, g), r in zip(live, rr):
+                    g["ransac"] = {k: r[k] for k in ("drawn", "validated", "best_hyp", "n_corres", "n_inliers", "err2")}
+                    g["ransac_T"] = r["T"]
+                # ---- coloured ICP from the RANSAC pose (:132-135); problems without colours / normals raise in Open3D
+                ci = [k for k, (plan, g) in enumerate(live) if g["colored"]]
+                if ci:
+                    sub = K.reg_problems([specs[k] for k in ci])
+                    ri = K.icp_colored_batch(sub, np.stack([live[k][1]["ransac_T"] for k in ci]), max_d_i)
+                    for k, r in zip(ci, ri):
+                        g = live[k][1]
+                        g.update(transform=r["T"], rmse=r["inlier_rmse"], fitness=r["fitness"],
+                                 icp={"mode": "colored", "iterations": r["iterations"], "n_inliers": r["n_inliers"]})
+                for plan, g in live:
+                    if not g["colored"]:
+                        g["fallback"] = "ColoredICP requires colored pointclouds with target normals."
+            # ---- the reference's except branch (:137-141): identity-initialised point-to-point ICP on the raw clouds
+            for plan, g in group:
+                if g["fallback"] is not None:
+                    r = _reg.registration_icp(g["source"], g["target"], max_d_i, np.eye(4),
+                                              _reg.TransformationEstimationPointToPoint())
+                    g.update(transform=r.transformation, rmse=r.inlier_rmse, fitness=r.fitness,
+                             icp=dict(_reg.last_info().get("icp", {})))
+                    g.setdefault("ransac", {})
+        # ---- evaluate_transform of every candidate over all detected points against the whole memory (:1104)
+        Gs = [self._global_transform(g["transform"], g) for plan, g in probs]
+        grid = _reg._nn_grid(all_memory_pcd, 0.02)
+        scores = K.nn_score_batch(grid, [plan["all_detected"]._p if plan["all_detected"].n() else
+                                         torch.zeros((0, 3), dtype=torch.float64, device=all_memory_pcd._p.device)
+                                         for plan, g in probs], Gs, 0.02)
+        for (plan, g), (n_in, err2) in zip(probs, scores):
+            n = plan["all_detected"].n()
+            g["full_fitness"] = (n_in / n) if n else 0.0
+            g["full_rmse"] = float(np.sqrt(err2 / n_in)) if n_in else 0.0
+
+    def _finish(self, plan):
+        """:1111-1169 -- best assignment by full-memory fitness, pose assembly."""
+        info = plan["info"]
+        self.last_localise_info = info
+        self._tls.info = info
+        if plan["registrations"] is None:
+            return np.array([0., 0., 0., 0., 0., 0., 1.]), [[], []]           # :895-896
+        assn_data = []
+        detected_mean = memory_mean = None
+        assn = None
+        for g in plan["registrations"]:
+            assn = g["assn"]
+            detected_mean, memory_mean = g["detected_mean"], g["memory_mean"]
+            assn_data.append([assn, g["transform"], g["rmse"], g["fitness"], g["full_rmse"], g["full_fitness"],
+                              detected_mean, memory_mean])
+            info["registrations"].append({"assn": assn, "transform": g["transform"], "rmse": g["rmse"], "fitness": g["fitness"],
+                                          "full_rmse": g["full_rmse"], "full_fitness": g["full_fitness"],
+                                          "detected_mean": detected_mean, "memory_mean": memory_mean,
+                                          "n_source": g["source"].n(), "n_target": g["target"].n(),
+                                          "ransac": dict(g.get("ransac", {})), "icp": dict(g.get("icp", {}))})
         best = sorted(assn_data, key=lambda x: x[5], reverse=True)             # :1111 (stable, by full fitness)
         best_transform, best_assn = best[0][1], best[0][0]
         if not self.bug_compatible:
@@ -604,4 +808,17 @@ class ObjectMemory():
         localised_pose = np.concatenate((tAvg, qAvg))
         info["best_assn"] = best_assn
         info["best_transform"] = best_transform
+        # the pose composed with the BEST assignment's own means (what :1127 intends); equals localised_pose whenever
+        # the best assignment is also the last one, or with bug_compatible=False
+        info["pose_best_means"] = np.concatenate((t + best[0][7] - R @ best[0][6], qAvg))
         return localised_pose, [assn, None]
+
+    def _localise_core(self, detected_phrases, detected_embs, detected_pointclouds, outlier_removal_config,
+                       fpfh_global_dist_factor, fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
+                       max_detected_object_num):
+        plan = self._plan(detected_phrases, detected_embs, detected_pointclouds, outlier_removal_config,
+                          fpfh_global_dist_factor, fpfh_local_dist_factor, fpfh_voxel_size, perform_semantic_icp,
+                          max_detected_object_num)
+        if plan["registrations"] is not None:
+            self._register_sequential(plan)
+        return self._finish(plan)

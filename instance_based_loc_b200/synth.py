@@ -357,7 +357,8 @@ def make_frames(scene, n_frames, H=600, W=600, f=300.0, device="cpu", seed=0, ma
     frames = []
     while len(frames) < n_frames:
         T = camera_pose(scene, rng)
-        depth, rgb, inst = render(scene, T, H, W, f, device, seed=int(rng.integers(1 << 31)))
+        depth, rgb, inst = render(scene, T, H, W, f, device, seed=int(rng.integers(1 << 31)),
+                                  use_kernel=torch.device(device).type == "cuda")
         masks, ids = instance_masks(inst, max_objects, min_pixels)
         if len(ids) == 0:
             continue

@@ -9,6 +9,7 @@ import copy
 import numpy as np
 
 from .. import o3d
+from .._lib import IblError
 
 
 def get_SVD_transform(p, q):
@@ -74,9 +75,9 @@ def register_point_clouds(source, target, voxel_size, global_dist_factor=1.5, lo
             source_down, target_down, voxel_size * local_dist_factor, result_ransac.transformation,
             reg.TransformationEstimationForColoredICP()
         )
-    except (KeyboardInterrupt, SystemExit):
-        raise
-    except Exception:
+    except (KeyboardInterrupt, SystemExit, IblError):
+        raise           # a CUDA / ABI failure must not turn into a plausible fallback pose
+    except Exception:   # Open3D's own failures (no normals, no colours, empty clouds): the reference's bare except
         result_icp = reg.registration_icp(
             source, target, voxel_size * local_dist_factor, np.eye(4),
             reg.TransformationEstimationPointToPoint()

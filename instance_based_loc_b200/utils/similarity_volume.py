@@ -53,6 +53,31 @@ def assignments_from_topk(flat, val, chosen_objects, m, s, n_det):
     return out
 
 
+def _outer_chain(rows):
+    """einsum('i,j') followed by einsum('...i,j') per further row on float16 arrays (:47-53, :172-179): every product is
+    rounded to fp16 once, left to right."""
+    vol = np.multiply.outer(rows[0], rows[1])
+    for r in rows[2:]:
+        vol = np.multiply.outer(vol, r)
+    return vol
+
+
+def _validity_mask(m, d):
+    """Which entries of an (m+1)^d volume the reference's mask loops leave finite (:56-90, :127-154): the assigned
+    coordinates (!= m) are pairwise distinct, any subset may be unassigned -- except that the closing
+    ``mask[[-1] * (d + 1)] = -inf`` is numpy LIST indexing on axis 0, i.e. the whole slab ``vol[m]``: the first detection
+    can never be unassigned."""
+    if d > m:          # the loops start from permutations of d DISTINCT objects out of m: none exist, nothing is allowed
+        return np.zeros((m + 1,) * d, dtype=bool)
+    idx = np.indices((m + 1,) * d)
+    ok = np.ones((m + 1,) * d, dtype=bool)
+    for a in range(d):
+        for b in range(a + 1, d):
+            ok &= ~((idx[a] == idx[b]) & (idx[a] != m))
+    ok[m] = False
+    return ok
+
+
 class SimVolume():
     def __init__(self, cosine_similarities) -> None:
         """:13-18.  Accepts a numpy array or a CUDA tensor [n_det, m] (float32)."""
@@ -92,8 +117,21 @@ class SimVolume():
 
     @property
     def subvolumes(self):
-        raise NotImplementedError("sub-volumes are not materialised on the device path; use "
-                                  "get_top_indices_from_subvolumes (the only consumer in localise)")
+        """:156-164 -- the masked fp16 sub-volumes themselves, one per entry of ``chosen_objects``.  The localise path
+        never builds them (get_top_indices_from_subvolumes streams their top entries from the kernel); this
+        materialises them on the host for callers of the legacy attribute."""
+        assert self.chosen_objects is not None, "call fast_construct_volume first"
+        aug = self.aug
+        if self.n_det == 1:
+            v = aug[0].copy()
+            v[-1] = -np.inf                                    # :105-110
+            return [v]
+        allowed = _validity_mask(self.m, self._subvolume_size)
+        out = []
+        for chosen in self.chosen_objects:
+            vol = _outer_chain([aug[c] for c in chosen])
+            out.append(np.where(allowed, vol, np.float16(-np.inf)))
+        return out
 
     def top_entries(self, k):
         """-> (flat int64 [n_comb,k], val float32 [n_comb,k]) host arrays, reference argmax order."""
@@ -107,15 +145,33 @@ class SimVolume():
         flat, val = self.top_entries(k)
         return assignments_from_topk(flat, val, self.chosen_objects, self.m, self._subvolume_size, self.n_det)
 
-    # ---- legacy API of the reference (not on the localise path) ---------------------------------------------
+    # ---- legacy API of the reference (not on the localise path; small dense host arrays) --------------------
     def construct_volume(self):
-        raise NotImplementedError("legacy full-volume path (similarity_volume.py:30-96) is not on the localise path")
+        """:30-96 -- the full (m+1)^n_det volume over ALL detections and its masked copy -> (volume, rep_volume).
+        With fewer than two detections the reference prints and returns ``aug`` alone (:33-35)."""
+        if self.n_det < 2:
+            print("Too few detected embs")
+            return self.aug
+        volume = _outer_chain(list(self.aug))
+        rep = np.where(_validity_mask(self.m, self.n_det), volume, np.float16(-np.inf))
+        rep[np.isnan(rep)] = -np.inf
+        return volume, rep
 
     def construct_volume_choose_e(self, chosen_e):
-        raise NotImplementedError("legacy path (similarity_volume.py:169-180) is not on the localise path")
+        """:169-180 -- unmasked product volume of the chosen detection rows."""
+        assert len(chosen_e) <= self.n_det
+        aug = self.aug
+        return _outer_chain([aug[c] for c in chosen_e])
 
     def get_top_indices(self, vol, k):
-        raise NotImplementedError("legacy path (similarity_volume.py:182-194) is not on the localise path")
+        """:182-194 -- k rounds of argmax over the flattened volume (first flat index on ties); the volume is
+        modified in place like the reference's."""
+        top_k = []
+        for _ in range(k):
+            ind = np.unravel_index(np.argmax(vol, axis=None), vol.shape)
+            top_k.append([ind, vol[ind]])
+            vol[ind] = -np.inf
+        return top_k
 
     def conv_coords_to_pairs(self, vol, coords):
         """:196-209 (pure bookkeeping, kept for API parity)."""

@@ -336,9 +336,9 @@ def ransac(src, tgt, corres, samples, max_d, edge_thr=0.9, confidence=0.99, earl
     info = {"drawn": 0, "validated": 0, "best_hyp": -1}
     if len(corres) < 3 or max_d <= 0 or H == 0:
         return best, info
-    tree = cKDTree(tgt)
     est_k = H
     h0 = 0
+    L = lib()
     while h0 < min(H, est_k):
         h1 = min(H, h0 + block)
         blk = _i32(get(h0, h1))
@@ -346,13 +346,29 @@ def ransac(src, tgt, corres, samples, max_d, edge_thr=0.9, confidence=0.99, earl
             ok = ransac_check(src, tgt, corres, blk, edge_thr, max_d)
         else:
             ok = np.ones(h1 - h0, bool)
-        for off in np.nonzero(ok)[0]:
+        offs = np.nonzero(ok)[0]
+        offs = offs[offs + h0 < est_k]
+        if len(offs):
+            # every validated hypothesis of the block is scored over the whole source (A.6) -- in parallel over the
+            # hypotheses, like Open3D's OpenMP loop; the ordered best-update below consumes them in stream order
+            sel = _i32(blk[offs])
+            Ts = np.zeros((len(offs), 4, 4))
+            L.orc_hyp_transforms(_p(src), _p(tgt), _p(corres), _p(sel), ctypes.c_int64(len(offs)), _p(Ts))
+            cnt = np.zeros(len(offs), np.int64)
+            err = np.zeros(len(offs))
+            L.orc_score_many(_p(tgt), ctypes.c_int64(len(tgt)), _p(src), ctypes.c_int64(len(src)), _p(Ts),
+                             ctypes.c_int64(len(offs)), ctypes.c_double(max_d), _p(cnt), _p(err))
+        for k, off in enumerate(offs):
             h = h0 + int(off)
             if h >= est_k:
                 break
-            T = hyp_transform(src, tgt, corres, blk[off])
-            pts = transform_points(T, src)
-            res = score(pts, tgt, tree, max_d, T)
+            T = Ts[k]
+            res = RegResult(T)
+            res.n_inliers = int(cnt[k])
+            if res.n_inliers:
+                res.err2 = float(err[k])
+                res.fitness = res.n_inliers / len(src)
+                res.inlier_rmse = math.sqrt(res.err2 / res.n_inliers)
             info["validated"] += 1
             if trace is not None:
                 trace.append((h, res.n_inliers, res.err2))
@@ -360,8 +376,8 @@ def ransac(src, tgt, corres, samples, max_d, edge_thr=0.9, confidence=0.99, earl
                 best = res
                 best_h = h
                 if early_exit:
-                    inl = lib().orc_corres_inliers(_p(_f64(T)), _p(src), _p(tgt), _p(corres), len(corres),
-                                                   ctypes.c_double(max_d))
+                    inl = L.orc_corres_inliers(_p(_f64(T)), _p(src), _p(tgt), _p(corres), len(corres),
+                                               ctypes.c_double(max_d))
                     rho = inl / len(corres)
                     den = math.log(1.0 - rho ** 3) if rho < 1.0 else -math.inf
                     if den == 0.0:
@@ -371,6 +387,12 @@ def ransac(src, tgt, corres, samples, max_d, edge_thr=0.9, confidence=0.99, earl
                     if kk < est_k:      # Registration.cpp: est_k_local_d < est_k_global ? ceil : keep
                         est_k = int(math.ceil(kk))
         h0 = h1
+    if best_h >= 0:
+        # the winner's correspondence set (RegistrationResult.correspondence_set_), by the one-at-a-time scorer; its
+        # count and err2 must be what the batched scorer said
+        full = score(transform_points(best.transformation, src), tgt, cKDTree(tgt), max_d, best.transformation)
+        assert full.n_inliers == best.n_inliers and full.err2 == best.err2, "batched and single scorers disagree"
+        best = full
     info["drawn"] = int(min(H, max(est_k, 0)))
     info["best_hyp"] = best_h
     return best, info

@@ -305,3 +305,128 @@ ORC_API int orc_solve_update(const double *JTJ36, const double *JTr6, double *T1
     T16[8] = -sy;     T16[9] = cy * sx;                T16[10] = cy * cx;               T16[11] = x[5];
     return 1;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * A.6 scoring of MANY hypotheses at once (GetRegistrationResultAndCorrespondences per hypothesis).  Open3D 0.17 runs the
+ * RANSAC iterations under `#pragma omp parallel` (Registration.cpp); this is the same parallelism: one hypothesis per
+ * thread, every source point looked up in a uniform grid over the target (cell = max_d: the 27 surrounding cells hold
+ * every point within max_d).  Per hypothesis: the number of source points with a target strictly within max_d and the
+ * sum of their squared nearest distances, added in numpy's pairwise order (o3d_core.py `score` uses np.sum), so the
+ * figures are bit-identical to the one-at-a-time path. */
+static double pairwise_sum(const double *a, int64_t n) {
+    if (n < 8) {
+        double res = 0.;
+        for (int64_t i = 0; i < n; ++i) res += a[i];
+        return res;
+    } else if (n <= 128) {
+        double r[8];
+        for (int k = 0; k < 8; ++k) r[k] = a[k];
+        int64_t i;
+        for (i = 8; i < n - (n % 8); i += 8)
+            for (int k = 0; k < 8; ++k) r[k] += a[i + k];
+        double res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+        for (; i < n; ++i) res += a[i];
+        return res;
+    } else {
+        int64_t n2 = n / 2;
+        n2 -= n2 % 8;
+        return pairwise_sum(a, n2) + pairwise_sum(a + n2, n - n2);
+    }
+}
+
+ORC_API void orc_score_many(const double *tgt, int64_t n_tgt, const double *src, int64_t n_src, const double *Ts, int64_t nh,
+                            double max_d, int64_t *out_cnt, double *out_err2) {
+    for (int64_t h = 0; h < nh; ++h) { out_cnt[h] = 0; out_err2[h] = 0.0; }
+    if (n_tgt == 0 || n_src == 0 || nh == 0 || !(max_d > 0)) return;
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int64_t i = 0; i < n_tgt; ++i)
+        for (int a = 0; a < 3; ++a) { double v = tgt[3 * i + a]; if (v < lo[a]) lo[a] = v; if (v > hi[a]) hi[a] = v; }
+    double cell = max_d;
+    int64_t dim[3];
+    for (;;) {
+        for (int a = 0; a < 3; ++a) dim[a] = (int64_t)floor((hi[a] - lo[a]) / cell) + 1;
+        if ((double)dim[0] * (double)dim[1] * (double)dim[2] <= 6.4e7) break;
+        cell *= 1.5;
+    }
+    const int64_t ncell = dim[0] * dim[1] * dim[2];
+    int32_t *start = (int32_t *)calloc((size_t)ncell + 1, sizeof(int32_t));
+    int32_t *cidx = (int32_t *)malloc(sizeof(int32_t) * (size_t)n_tgt);
+    int32_t *order = (int32_t *)malloc(sizeof(int32_t) * (size_t)n_tgt);
+    for (int64_t i = 0; i < n_tgt; ++i) {
+        int64_t c[3];
+        for (int a = 0; a < 3; ++a) { c[a] = (int64_t)floor((tgt[3 * i + a] - lo[a]) / cell); if (c[a] >= dim[a]) c[a] = dim[a] - 1; if (c[a] < 0) c[a] = 0; }
+        cidx[i] = (int32_t)((c[2] * dim[1] + c[1]) * dim[0] + c[0]);
+        start[cidx[i] + 1]++;
+    }
+    for (int64_t c = 0; c < ncell; ++c) start[c + 1] += start[c];
+    {
+        int32_t *fill = (int32_t *)malloc(sizeof(int32_t) * (size_t)ncell);
+        memcpy(fill, start, sizeof(int32_t) * (size_t)ncell);
+        for (int64_t i = 0; i < n_tgt; ++i) order[fill[cidx[i]]++] = (int32_t)i;      /* ascending index inside a cell */
+        free(fill);
+    }
+    const int reach = (int)ceil(max_d / cell);
+    const double md2 = max_d * max_d;
+#pragma omp parallel
+    {
+        double *buf = (double *)malloc(sizeof(double) * (size_t)n_src);
+#pragma omp for schedule(dynamic, 1)
+        for (int64_t h = 0; h < nh; ++h) {
+            const double *T = Ts + 16 * h;
+            int64_t cnt = 0;
+            for (int64_t i = 0; i < n_src; ++i) {
+                double q[3];
+                xform(T, src + 3 * i, q);
+                int64_t c[3];
+                int outside = 0;
+                for (int a = 0; a < 3; ++a) {
+                    double f = floor((q[a] - lo[a]) / cell);
+                    if (f < -(double)reach - 1 || f > (double)(dim[a] + reach)) { outside = 1; break; }
+                    c[a] = (int64_t)f;
+                }
+                if (outside) continue;
+                double best = INFINITY;
+                int32_t bi = -1;
+                for (int64_t z = c[2] - reach; z <= c[2] + reach; ++z) {
+                    if (z < 0 || z >= dim[2]) continue;
+                    for (int64_t y = c[1] - reach; y <= c[1] + reach; ++y) {
+                        if (y < 0 || y >= dim[1]) continue;
+                        int64_t x0 = c[0] - reach, x1 = c[0] + reach;
+                        if (x0 < 0) x0 = 0;
+                        if (x1 >= dim[0]) x1 = dim[0] - 1;
+                        if (x0 > x1) continue;
+                        const int64_t row = (z * dim[1] + y) * dim[0];
+                        for (int32_t k = start[row + x0]; k < start[row + x1 + 1]; ++k) {
+                            const double *t = tgt + 3 * (size_t)order[k];
+                            double dx = t[0] - q[0], dy = t[1] - q[1], dz = t[2] - q[2];
+                            double d2 = (dx * dx + dy * dy) + dz * dz;
+                            if (d2 < best || (d2 == best && order[k] < bi)) { best = d2; bi = order[k]; }
+                        }
+                    }
+                }
+                if (bi >= 0 && best < md2) buf[cnt++] = best;
+            }
+            out_cnt[h] = cnt;
+            out_err2[h] = pairwise_sum(buf, cnt);
+        }
+        free(buf);
+    }
+    free(start); free(cidx); free(order);
+}
+
+/* transforms of hypotheses given by samples[nh][3] (indices into corres) */
+ORC_API void orc_hyp_transforms(const double *src, const double *tgt, const int32_t *corres, const int32_t *samples, int64_t nh,
+                                double *T_out) {
+#pragma omp parallel for
+    for (int64_t h = 0; h < nh; ++h) {
+        double s[9], t[9];
+        for (int j = 0; j < 3; ++j) {
+            int c = samples[3 * h + j];
+            for (int a = 0; a < 3; ++a) {
+                s[3 * j + a] = src[3 * (size_t)corres[2 * c] + a];
+                t[3 * j + a] = tgt[3 * (size_t)corres[2 * c + 1] + a];
+            }
+        }
+        kabsch(s, t, 3, T_out + 16 * h);
+    }
+}

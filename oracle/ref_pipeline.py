@@ -40,8 +40,9 @@ def fpfh_features(pts, voxel_size):
 
 
 def register_point_clouds(src_p, src_c, tgt_p, tgt_c, voxel_size, global_dist_factor=1.5, local_dist_factor=0.4,
-                          seed=0, tgt_feats=None, info=None):
-    """fpfh_register.py:100-143 -> (T, inlier_rmse, fitness)."""
+                          seed=0, tgt_feats=None, info=None, max_iteration=MAX_ITERATION, early_exit=True):
+    """fpfh_register.py:100-143 -> (T, inlier_rmse, fitness).  ``max_iteration`` / ``early_exit`` only differ from the
+    reference's RANSACConvergenceCriteria(4000000, 0.99) in the fixed-hypothesis benchmark configurations."""
     info = info if info is not None else {}
     try:
         if len(src_p) == 0 or len(tgt_p) == 0:
@@ -52,7 +53,7 @@ def register_point_clouds(src_p, src_c, tgt_p, tgt_c, voxel_size, global_dist_fa
         cor = oc.match_features(sf, tf, True, 3)
         C = len(cor)
         res, rinfo = oc.ransac(src_p, tgt_p, cor, lambda a, b: sampler.samples(seed, a, b - a, C), thr, 0.9, CONFIDENCE,
-                               max_iteration=MAX_ITERATION)
+                               early_exit=early_exit, max_iteration=max_iteration)
         info.update(rinfo, n_corres=C, ransac_T=res.transformation, ransac_inliers=res.n_inliers, corres=cor)
         if src_c is None or tgt_c is None:
             raise RuntimeError("ColoredICP requires colored pointclouds.")

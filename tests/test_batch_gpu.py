@@ -1,0 +1,143 @@
+"""Batched registration entry points (ibl_ransac_run_batch, ibl_icp_colored_batch, ibl_nn_score_batch) against the
+single-problem calls they replace: every result field must be IDENTICAL -- the batch only changes how many problems share
+a launch and a host round trip, never a problem's arithmetic, hypothesis stream or reduction order.  The single-problem
+calls are the ones the oracle parity tests pin (test_kernels_gpu.py: test_ransac_run, test_colored_icp, test_nn_score)."""
+import numpy as np
+import pytest
+import torch
+
+from ibl_testutil import random_rigid, surface_cloud
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def K(cuda):
+    from instance_based_loc_b200 import kernels
+    return kernels
+
+
+def dev(a, dtype=torch.float64):
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).cuda()
+
+
+def _case(seed, n_tgt, n_src, C, outlier):
+    tgt, tcol = surface_cloud(n_tgt, seed)
+    T = random_rigid(seed + 1, 0.6, 0.3)
+    rng = np.random.default_rng(seed + 2)
+    sel = np.sort(rng.choice(n_tgt, n_src, replace=False))
+    src = (np.linalg.inv(T) @ np.c_[tgt[sel], np.ones(len(sel))].T).T[:, :3] + rng.normal(0, 0.001, (n_src, 3))
+    ci = rng.choice(n_src, C, replace=False)
+    cor = np.stack([ci, sel[ci]], axis=1).astype(np.int32)
+    bad = rng.random(C) < outlier
+    cor[bad, 1] = rng.integers(0, n_tgt, bad.sum())
+    return dict(src=src, scol=tcol[sel], tgt=tgt, tcol=tcol, cor=cor, T=T)
+
+
+@pytest.fixture(scope="module")
+def problems(K):
+    """five problems of different sizes / difficulty (one with too few correspondences, one tiny)."""
+    from oracle import o3d_core as oc
+    out = []
+    for seed, n_tgt, n_src, C, outl in ((100, 6000, 3500, 1200, 0.7), (200, 9000, 5100, 900, 0.85), (300, 2500, 700, 300, 0.5),
+                                        (400, 4000, 2000, 2, 0.0), (500, 5000, 513, 400, 0.9)):
+        c = _case(seed, n_tgt, n_src, C, outl)
+        tn = oc.estimate_normals(c["tgt"], 0.1, 30)
+        P, N, Cc = dev(c["tgt"]), dev(tn), dev(c["tcol"])
+        idx, _, cnt = K.knn_hybrid(K.Grid(P, K.knn_cell_for(P, 30, 0.15)), 0.15, 30, want_d2=False)
+        grad = K.color_gradient(P, N, Cc, idx, cnt)
+        g = K.Grid(P, 0.075, nnfield=0.075, nnfield_voxel=0.075 / 8)
+        out.append(dict(c, d_src=dev(c["src"]), d_scol=dev(c["scol"]), d_tgt=P, d_tnrm=N, d_tcol=Cc, d_grad=grad, grid=g,
+                        d_cor=dev(c["cor"], torch.int32), seed=seed))
+    return out
+
+
+def _specs(problems):
+    return [dict(src=p["d_src"], src_col=p["d_scol"], tgt=p["d_tgt"], tgt_nrm=p["d_tnrm"], tgt_col=p["d_tcol"],
+                 tgt_grad=p["d_grad"], grid_ransac=p["grid"], grid_icp=p["grid"], corres=p["d_cor"], seed=p["seed"])
+            for p in problems]
+
+
+@pytest.mark.parametrize("early_exit,H,block", [(True, 60000, 4096), (False, 20000, 1000), (True, 300000, 1 << 14)])
+def test_ransac_batch_equals_single(K, problems, early_exit, H, block):
+    arr = K.reg_problems(_specs(problems))
+    got = K.ransac_run_batch(arr, H, 0.99, 0.075, edge_thr=0.9, use_checkers=True, early_exit=early_exit, block=block)
+    for p, r in zip(problems, got):
+        one = K.ransac_run(p["grid"], p["d_src"], p["d_tgt"], p["d_cor"], H, 0.99, 0.075, edge_thr=0.9, seed=p["seed"],
+                           use_checkers=True, early_exit=early_exit, block=block)
+        for k in ("best_hyp", "n_inliers", "validated", "drawn", "n_corres", "status", "fitness", "inlier_rmse", "err2"):
+            assert r[k] == one[k], (k, r[k], one[k])
+        assert np.array_equal(r["T"], one["T"])
+    assert got[3]["status"] == 1 and np.array_equal(got[3]["T"], np.eye(4))      # 2 correspondences: empty result
+    assert got[0]["fitness"] > 0.5
+
+
+def test_ransac_batch_checkers_off(K, problems):
+    """configs[4]'s forced H_v = H: every hypothesis is scored."""
+    sub = [problems[2], problems[4]]
+    arr = K.reg_problems(_specs(sub))
+    got = K.ransac_run_batch(arr, 3000, 0.99, 0.075, use_checkers=False, early_exit=False, block=1024)
+    for p, r in zip(sub, got):
+        one = K.ransac_run(p["grid"], p["d_src"], p["d_tgt"], p["d_cor"], 3000, 0.99, 0.075, seed=p["seed"],
+                           use_checkers=False, early_exit=False, block=1024)
+        assert r["validated"] == one["validated"] == 3000
+        assert r["best_hyp"] == one["best_hyp"] and r["n_inliers"] == one["n_inliers"] and np.array_equal(r["T"], one["T"])
+        assert r["inlier_rmse"] == one["inlier_rmse"]
+
+
+def test_icp_colored_batch_equals_single(K, problems):
+    live = [p for p in problems if len(p["cor"]) > 3]
+    arr = K.reg_problems(_specs(live))
+    inits = [p["T"] @ random_rigid(40 + k, 0.03, 0.01) for k, p in enumerate(live)]
+    inits[1] = np.eye(4)                                          # a hopeless start: runs all 30 iterations or stalls
+    got = K.icp_colored_batch(arr, np.stack(inits), 0.075)
+    for p, T0, r in zip(live, inits, got):
+        one = K.icp(p["grid"], p["d_src"], p["d_tgt"], 0.075, T0, mode=1, scol=p["d_scol"], tnrm=p["d_tnrm"], tcol=p["d_tcol"],
+                    tgrad=p["d_grad"])
+        for k in ("iterations", "n_inliers", "fitness", "inlier_rmse", "err2"):
+            assert r[k] == one[k], (k, r[k], one[k])
+        assert np.array_equal(r["T"], one["T"])
+    assert len({r["iterations"] for r in got}) > 1                # problems converge after different numbers of steps
+
+
+def test_nn_score_batch_equals_single(K, problems):
+    g = problems[1]["grid"]
+    srcs = [problems[0]["d_src"], problems[1]["d_src"], torch.zeros((0, 3), dtype=torch.float64, device="cuda"),
+            problems[4]["d_src"], problems[1]["d_src"]]
+    Ts = [problems[0]["T"], problems[1]["T"], np.eye(4), random_rigid(9, 0.2, 0.1), np.eye(4)]
+    got = K.nn_score_batch(g, srcs, Ts, 0.02)
+    for s, T, (n_in, err2) in zip(srcs, Ts, got):
+        if s.shape[0] == 0:
+            assert (n_in, err2) == (0, 0.0)
+            continue
+        a, b, _, _ = K.nn_score(g, s, 0.02, T=T)
+        assert (n_in, err2) == (a, b)
+    assert got[1][0] > 0.9 * srcs[1].shape[0]
+
+
+def test_localise_batch_modes_agree(cuda):
+    """localise_batch with the batched registration stage == the per-frame organisation == localise_arrays, frame by
+    frame (poses bit-equal), including the RANSAC bookkeeping (drawn / validated) per registration."""
+    from instance_based_loc_b200 import selfcheck, synth
+    from instance_based_loc_b200.o3d import registration as reg
+    scene = synth.make_scene(m=8, seed=23, D=96, size=(0.35, 0.75))
+    om, _ = selfcheck.build_memory(scene, spacing=0.015, voxel=0.015, f=150.0)
+    frames = synth.make_frames(scene, 6, H=225, W=300, f=150.0, seed=23, min_pixels=200)
+    reg.ransac_seed = 23
+    kw = dict(fpfh_global_dist_factor=1.5, fpfh_local_dist_factor=1.5, fpfh_voxel_size=0.05, perform_semantic_icp=False)
+    frs = [{k: f[k] for k in ("rgb", "depth", "masks", "embs")} for f in frames]
+    seq = []
+    for f in frs:
+        pose, assn = om.localise_arrays(f["rgb"], f["depth"], f["masks"], f["embs"], **kw)
+        seq.append((pose, assn, om.last_localise_info))
+    for workers, batched in ((1, True), (3, True), (3, False)):
+        got = om.localise_batch(frs, workers=workers, batched_registration=batched, **kw)
+        for (p0, a0, i0), (p1, a1, i1) in zip(seq, got):
+            assert np.array_equal(p0, p1) and a0 == a1
+            assert len(i0["registrations"]) == len(i1["registrations"])
+            for g0, g1 in zip(i0["registrations"], i1["registrations"]):
+                assert np.array_equal(g0["transform"], g1["transform"])
+                assert g0["full_fitness"] == g1["full_fitness"] and g0["fitness"] == g1["fitness"]
+                assert g0["ransac"].get("drawn") == g1["ransac"].get("drawn")
+                assert g0["ransac"].get("validated") == g1["ransac"].get("validated")
+                assert g0["icp"].get("iterations") == g1["icp"].get("iterations")

@@ -98,3 +98,32 @@ def test_reference_localise_vs_oracle_pipeline():
     np.testing.assert_allclose(pose, rpose, atol=1e-9)
     assert "Best assn" in buf.getvalue()
     assert not any("fallback" in r["detail"] for r in rinfo["registrations"])
+
+
+@pytest.mark.parametrize("nd,m", [(2, 5), (3, 4), (4, 3)])
+def test_reference_simvolume_legacy_api_vs_mirror_helpers(nd, m):
+    """The legacy SimVolume surface of SURVEY 8(b).1 (construct_volume, construct_volume_choose_e, .subvolumes,
+    get_top_indices; similarity_volume.py:30-96,156-194): the mirror's host helpers against the unmodified reference."""
+    from instance_based_loc_b200.utils import similarity_volume as mine
+    sv = ref_loader.load("utils/similarity_volume.py")
+    S = np.random.default_rng(nd * 7 + m).uniform(-0.2, 0.95, (nd, m)).astype(np.float32)
+    with contextlib.redirect_stderr(io.StringIO()), contextlib.redirect_stdout(io.StringIO()):
+        v = sv.SimVolume(S.copy())
+        vol, rep = v.construct_volume()
+        v.fast_construct_volume(min(nd, 3))
+        subs = [np.array(s) for s in v.subvolumes]
+        chosen = [list(c) for c in v.chosen_objects]
+        ce = v.construct_volume_choose_e(list(range(nd))[::-1])
+        top = v.get_top_indices(np.array(rep, copy=True), 5)
+    aug = np.ones((nd, m + 1), np.float16)
+    aug[:, :-1] = S
+    mvol = mine._outer_chain(list(aug))
+    assert mvol.dtype == vol.dtype and np.array_equal(mvol, vol)
+    mrep = np.where(mine._validity_mask(m, nd), mvol, np.float16(-np.inf))
+    assert np.array_equal(mrep, rep)
+    allowed = mine._validity_mask(m, min(nd, 3))
+    for c, s in zip(chosen, subs):
+        assert np.array_equal(np.where(allowed, mine._outer_chain([aug[i] for i in c]), np.float16(-np.inf)), s)
+    assert np.array_equal(mine._outer_chain([aug[i] for i in range(nd)][::-1]), ce)
+    got = mine.SimVolume.get_top_indices(None, np.array(mrep, copy=True), 5)
+    assert [tuple(int(x) for x in a) for a, _ in got] == [tuple(int(x) for x in a) for a, _ in top]

@@ -270,28 +270,71 @@ ORC_API void orc_fpfh(int n, const int32_t *nbr_idx, const double *nbr_d2, const
 
 /* A.5 exact brute-force 33-d nearest neighbour: for every column of fa find argmin over fb columns.
  * d2 = sum_j (a_j-b_j)^2 accumulated j=0..32 in order; ties -> lowest index. fa:[33][na] fb:[33][nb] */
+typedef struct { double norm; int32_t idx; } nrm_idx_t;
+static int cmp_nrm(const void *x, const void *y) {
+    const nrm_idx_t *a = (const nrm_idx_t *)x, *b = (const nrm_idx_t *)y;
+    if (a->norm < b->norm) return -1;
+    if (a->norm > b->norm) return 1;
+    return (a->idx > b->idx) - (a->idx < b->idx);
+}
+
+/* exact distance in the defining order (j ascending), abandoned as soon as the partial sum EXCEEDS `best`: the terms are
+ * non-negative and rounded addition is monotone, so such a sum cannot end at or below best.  Returns INFINITY then. */
+static inline double feat_d2_bounded(const double *a, const double *b, double best) {
+    double s = 0.0;
+    for (int j = 0; j < 32; j += 8) {
+        for (int k = 0; k < 8; ++k) { double d = a[j + k] - b[j + k]; s += d * d; }
+        if (s > best) return INFINITY;
+    }
+    double d = a[32] - b[32];
+    return s + d * d;
+}
+
 ORC_API void orc_feature_nn(const double *fa, int na, const double *fb, int nb, int32_t *nn) {
     /* transpose for locality */
-    double *ta = (double *)malloc(sizeof(double) * 33 * (size_t)na);
-    double *tb = (double *)malloc(sizeof(double) * 33 * (size_t)nb);
+    double *ta = (double *)malloc(sizeof(double) * 33 * (size_t)(na ? na : 1));
+    double *tb = (double *)malloc(sizeof(double) * 33 * (size_t)(nb ? nb : 1));
     for (int j = 0; j < 33; ++j) {
         for (int i = 0; i < na; ++i) ta[(size_t)i * 33 + j] = fa[(size_t)j * na + i];
         for (int i = 0; i < nb; ++i) tb[(size_t)i * 33 + j] = fb[(size_t)j * nb + i];
     }
+    /* Search order only (the answer is still the exact argmin, lowest index on ties): targets sorted by Euclidean norm;
+     * a query starts at the targets whose norm is closest to its own and walks outwards in both directions, and a
+     * direction is closed once (|a| - |b|)^2, a lower bound of |a - b|^2, exceeds the best distance so far. */
+    nrm_idx_t *ord = (nrm_idx_t *)malloc(sizeof(nrm_idx_t) * (size_t)(nb ? nb : 1));
+    for (int q = 0; q < nb; ++q) {
+        double s = 0.0;
+        for (int j = 0; j < 33; ++j) s += tb[(size_t)q * 33 + j] * tb[(size_t)q * 33 + j];
+        ord[q].norm = sqrt(s); ord[q].idx = q;
+    }
+    qsort(ord, (size_t)nb, sizeof(nrm_idx_t), cmp_nrm);
 #pragma omp parallel for schedule(dynamic, 64)
     for (int i = 0; i < na; ++i) {
         const double *a = ta + (size_t)i * 33;
+        double an = 0.0;
+        for (int j = 0; j < 33; ++j) an += a[j] * a[j];
+        an = sqrt(an);
+        int lo = 0, hi = nb;                                /* first target with norm >= an */
+        while (lo < hi) { int mid = (lo + hi) >> 1; if (ord[mid].norm < an) lo = mid + 1; else hi = mid; }
+        int up = lo, dn = lo - 1;
         double best = INFINITY;
         int bi = -1;
-        for (int q = 0; q < nb; ++q) {
-            const double *b = tb + (size_t)q * 33;
-            double s = 0.0;
-            for (int j = 0; j < 33; ++j) { double d = a[j] - b[j]; s += d * d; }
-            if (s < best) { best = s; bi = q; }
+        while (up < nb || dn >= 0) {
+            for (int side = 0; side < 2; ++side) {
+                int *pos = side ? &dn : &up;
+                if (side ? (*pos < 0) : (*pos >= nb)) continue;
+                double gap = fabs(ord[*pos].norm - an);
+                gap -= 1e-9 * (ord[*pos].norm + an);        /* the norms themselves carry rounding error */
+                if (gap > 0.0 && gap * gap > best) { *pos = side ? -1 : nb; continue; }    /* nothing closer further out */
+                int q = ord[*pos].idx;
+                double s = feat_d2_bounded(a, tb + (size_t)q * 33, best);
+                if (s < best || (s == best && q < bi)) { best = s; bi = q; }
+                *pos += side ? -1 : 1;
+            }
         }
         nn[i] = bi;
     }
-    free(ta); free(tb);
+    free(ta); free(tb); free(ord);
 }
 
 /* ---------------------------------------------------------------------------------------------

@@ -339,6 +339,9 @@ def ransac(src, tgt, corres, samples, max_d, edge_thr=0.9, confidence=0.99, earl
     est_k = H
     h0 = 0
     L = lib()
+    L.orc_grid_build.restype = ctypes.c_void_p
+    grid = ctypes.c_void_p(L.orc_grid_build(_p(tgt), ctypes.c_int64(len(tgt)), ctypes.c_double(max_d)))
+    block0 = block
     while h0 < min(H, est_k):
         h1 = min(H, h0 + block)
         blk = _i32(get(h0, h1))
@@ -356,8 +359,10 @@ def ransac(src, tgt, corres, samples, max_d, edge_thr=0.9, confidence=0.99, earl
             L.orc_hyp_transforms(_p(src), _p(tgt), _p(corres), _p(sel), ctypes.c_int64(len(offs)), _p(Ts))
             cnt = np.zeros(len(offs), np.int64)
             err = np.zeros(len(offs))
-            L.orc_score_many(_p(tgt), ctypes.c_int64(len(tgt)), _p(src), ctypes.c_int64(len(src)), _p(Ts),
-                             ctypes.c_int64(len(offs)), ctypes.c_double(max_d), _p(cnt), _p(err))
+            for a in range(0, len(offs), 128):                       # bounded scratch: 128 x n_src doubles per call
+                b = min(a + 128, len(offs))
+                L.orc_score_many(grid, _p(src), ctypes.c_int64(len(src)), _p(Ts[a:b]), ctypes.c_int64(b - a),
+                                 ctypes.c_double(max_d), _p(cnt[a:b]), _p(err[a:b]))
         for k, off in enumerate(offs):
             h = h0 + int(off)
             if h >= est_k:
@@ -387,6 +392,8 @@ def ransac(src, tgt, corres, samples, max_d, edge_thr=0.9, confidence=0.99, earl
                     if kk < est_k:      # Registration.cpp: est_k_local_d < est_k_global ? ceil : keep
                         est_k = int(math.ceil(kk))
         h0 = h1
+        block = min(block * 2, max(block0, 1 << 17))                  # fewer, larger blocks once the stream gets long
+    L.orc_grid_free(grid)
     if best_h >= 0:
         # the winner's correspondence set (RegistrationResult.correspondence_set_), by the one-at-a-time scorer; its
         # count and err2 must be what the batched scorer said

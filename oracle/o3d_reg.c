@@ -334,84 +334,134 @@ static double pairwise_sum(const double *a, int64_t n) {
     }
 }
 
-ORC_API void orc_score_many(const double *tgt, int64_t n_tgt, const double *src, int64_t n_src, const double *Ts, int64_t nh,
-                            double max_d, int64_t *out_cnt, double *out_err2) {
-    for (int64_t h = 0; h < nh; ++h) { out_cnt[h] = 0; out_err2[h] = 0.0; }
-    if (n_tgt == 0 || n_src == 0 || nh == 0 || !(max_d > 0)) return;
-    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+typedef struct {
+    int64_t n_tgt, dim[3], ncell;
+    double lo[3], cell;
+    const double *tgt;
+    int32_t *start, *order;
+} orc_grid_t;
+
+/* uniform grid over the target (cells of about max_d / 4) for orc_score_many; the caller keeps `tgt` alive */
+ORC_API void *orc_grid_build(const double *tgt, int64_t n_tgt, double max_d) {
+    orc_grid_t *g = (orc_grid_t *)calloc(1, sizeof(orc_grid_t));
+    g->n_tgt = n_tgt; g->tgt = tgt;
+    double hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int a = 0; a < 3; ++a) g->lo[a] = INFINITY;
     for (int64_t i = 0; i < n_tgt; ++i)
-        for (int a = 0; a < 3; ++a) { double v = tgt[3 * i + a]; if (v < lo[a]) lo[a] = v; if (v > hi[a]) hi[a] = v; }
-    double cell = max_d;
-    int64_t dim[3];
-    for (;;) {
-        for (int a = 0; a < 3; ++a) dim[a] = (int64_t)floor((hi[a] - lo[a]) / cell) + 1;
-        if ((double)dim[0] * (double)dim[1] * (double)dim[2] <= 6.4e7) break;
-        cell *= 1.5;
+        for (int a = 0; a < 3; ++a) { double v = tgt[3 * i + a]; if (v < g->lo[a]) g->lo[a] = v; if (v > hi[a]) hi[a] = v; }
+    g->cell = max_d / 4.0;
+    if (n_tgt == 0) { g->dim[0] = g->dim[1] = g->dim[2] = 1; g->lo[0] = g->lo[1] = g->lo[2] = 0.0; }
+    else for (;;) {
+        for (int a = 0; a < 3; ++a) g->dim[a] = (int64_t)floor((hi[a] - g->lo[a]) / g->cell) + 1;
+        if ((double)g->dim[0] * (double)g->dim[1] * (double)g->dim[2] <= 6.4e7) break;
+        g->cell *= 1.5;
     }
-    const int64_t ncell = dim[0] * dim[1] * dim[2];
-    int32_t *start = (int32_t *)calloc((size_t)ncell + 1, sizeof(int32_t));
-    int32_t *cidx = (int32_t *)malloc(sizeof(int32_t) * (size_t)n_tgt);
-    int32_t *order = (int32_t *)malloc(sizeof(int32_t) * (size_t)n_tgt);
+    g->ncell = g->dim[0] * g->dim[1] * g->dim[2];
+    g->start = (int32_t *)calloc((size_t)g->ncell + 1, sizeof(int32_t));
+    g->order = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n_tgt ? n_tgt : 1));
+    int32_t *cidx = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n_tgt ? n_tgt : 1));
     for (int64_t i = 0; i < n_tgt; ++i) {
         int64_t c[3];
-        for (int a = 0; a < 3; ++a) { c[a] = (int64_t)floor((tgt[3 * i + a] - lo[a]) / cell); if (c[a] >= dim[a]) c[a] = dim[a] - 1; if (c[a] < 0) c[a] = 0; }
-        cidx[i] = (int32_t)((c[2] * dim[1] + c[1]) * dim[0] + c[0]);
-        start[cidx[i] + 1]++;
+        for (int a = 0; a < 3; ++a) {
+            c[a] = (int64_t)floor((tgt[3 * i + a] - g->lo[a]) / g->cell);
+            if (c[a] >= g->dim[a]) c[a] = g->dim[a] - 1;
+            if (c[a] < 0) c[a] = 0;
+        }
+        cidx[i] = (int32_t)((c[2] * g->dim[1] + c[1]) * g->dim[0] + c[0]);
+        g->start[cidx[i] + 1]++;
     }
-    for (int64_t c = 0; c < ncell; ++c) start[c + 1] += start[c];
-    {
-        int32_t *fill = (int32_t *)malloc(sizeof(int32_t) * (size_t)ncell);
-        memcpy(fill, start, sizeof(int32_t) * (size_t)ncell);
-        for (int64_t i = 0; i < n_tgt; ++i) order[fill[cidx[i]]++] = (int32_t)i;      /* ascending index inside a cell */
-        free(fill);
+    for (int64_t c = 0; c < g->ncell; ++c) g->start[c + 1] += g->start[c];
+    int32_t *fill = (int32_t *)malloc(sizeof(int32_t) * (size_t)g->ncell);
+    memcpy(fill, g->start, sizeof(int32_t) * (size_t)g->ncell);
+    for (int64_t i = 0; i < n_tgt; ++i) g->order[fill[cidx[i]]++] = (int32_t)i;      /* ascending index inside a cell */
+    free(fill); free(cidx);
+    return g;
+}
+
+ORC_API void orc_grid_free(void *h) {
+    orc_grid_t *g = (orc_grid_t *)h;
+    if (!g) return;
+    free(g->start); free(g->order); free(g);
+}
+
+/* squared distance to the nearest target strictly within max_d of q (lowest index on exact ties), or -1.  Cells are
+ * searched ring by ring: a target in Chebyshev ring s lies farther than s - 1 cells away, so the search ends before ring s
+ * once the best distance is below (s - 1) * cell -- a good hypothesis finds its neighbour in the first rings, a bad one
+ * only walks empty cells. */
+static double grid_nn_d2(const orc_grid_t *g, const double *q, double max_d, double md2) {
+    const double cell = g->cell;
+    const int reach = (int)ceil(max_d / cell) + 1;     /* +1: a point on a cell face may round to either side */
+    int64_t c[3];
+    for (int a = 0; a < 3; ++a) {
+        double f = floor((q[a] - g->lo[a]) / cell);
+        if (f < -(double)reach - 1 || f > (double)(g->dim[a] + reach)) return -1.0;
+        c[a] = (int64_t)f;
     }
-    const int reach = (int)ceil(max_d / cell);
-    const double md2 = max_d * max_d;
-#pragma omp parallel
-    {
-        double *buf = (double *)malloc(sizeof(double) * (size_t)n_src);
-#pragma omp for schedule(dynamic, 1)
-        for (int64_t h = 0; h < nh; ++h) {
-            const double *T = Ts + 16 * h;
-            int64_t cnt = 0;
-            for (int64_t i = 0; i < n_src; ++i) {
-                double q[3];
-                xform(T, src + 3 * i, q);
-                int64_t c[3];
-                int outside = 0;
-                for (int a = 0; a < 3; ++a) {
-                    double f = floor((q[a] - lo[a]) / cell);
-                    if (f < -(double)reach - 1 || f > (double)(dim[a] + reach)) { outside = 1; break; }
-                    c[a] = (int64_t)f;
-                }
-                if (outside) continue;
-                double best = INFINITY;
-                int32_t bi = -1;
-                for (int64_t z = c[2] - reach; z <= c[2] + reach; ++z) {
-                    if (z < 0 || z >= dim[2]) continue;
-                    for (int64_t y = c[1] - reach; y <= c[1] + reach; ++y) {
-                        if (y < 0 || y >= dim[1]) continue;
-                        int64_t x0 = c[0] - reach, x1 = c[0] + reach;
-                        if (x0 < 0) x0 = 0;
-                        if (x1 >= dim[0]) x1 = dim[0] - 1;
-                        if (x0 > x1) continue;
-                        const int64_t row = (z * dim[1] + y) * dim[0];
-                        for (int32_t k = start[row + x0]; k < start[row + x1 + 1]; ++k) {
-                            const double *t = tgt + 3 * (size_t)order[k];
-                            double dx = t[0] - q[0], dy = t[1] - q[1], dz = t[2] - q[2];
-                            double d2 = (dx * dx + dy * dy) + dz * dz;
-                            if (d2 < best || (d2 == best && order[k] < bi)) { best = d2; bi = order[k]; }
-                        }
+    const int64_t *dim = g->dim;
+    double best = INFINITY;
+    int32_t bi = -1;
+    for (int s = 0; s <= reach; ++s) {
+        if (s >= 2) { double gg = (double)(s - 1) * cell * (1.0 - 1e-9); if (best < gg * gg) break; }
+        for (int64_t z = c[2] - s; z <= c[2] + s; ++z) {
+            if (z < 0 || z >= dim[2]) continue;
+            const int zedge = (z == c[2] - s) || (z == c[2] + s);
+            for (int64_t y = c[1] - s; y <= c[1] + s; ++y) {
+                if (y < 0 || y >= dim[1]) continue;
+                const int edge = zedge || (y == c[1] - s) || (y == c[1] + s);
+                const int64_t row = (z * dim[1] + y) * dim[0];
+                for (int part = 0; part < (edge || s == 0 ? 1 : 2); ++part) {       /* full x-run on the shell's faces */
+                    int64_t x0, x1;
+                    if (edge || s == 0) { x0 = c[0] - s; x1 = c[0] + s; }
+                    else if (part == 0) { x0 = x1 = c[0] - s; }
+                    else { x0 = x1 = c[0] + s; }
+                    if (x0 < 0) x0 = 0;
+                    if (x1 >= dim[0]) x1 = dim[0] - 1;
+                    if (x0 > x1) continue;
+                    for (int32_t k = g->start[row + x0]; k < g->start[row + x1 + 1]; ++k) {
+                        const double *t = g->tgt + 3 * (size_t)g->order[k];
+                        double dx = t[0] - q[0], dy = t[1] - q[1], dz = t[2] - q[2];
+                        double d2 = (dx * dx + dy * dy) + dz * dz;
+                        if (d2 < best || (d2 == best && g->order[k] < bi)) { best = d2; bi = g->order[k]; }
                     }
                 }
-                if (bi >= 0 && best < md2) buf[cnt++] = best;
             }
-            out_cnt[h] = cnt;
-            out_err2[h] = pairwise_sum(buf, cnt);
         }
-        free(buf);
     }
-    free(start); free(cidx); free(order);
+    return (bi >= 0 && best < md2) ? best : -1.0;
+}
+
+/* nh hypotheses Ts[nh][16] scored over the whole source: tasks are (hypothesis, chunk of the source), so a handful of
+ * hypotheses still uses every core; per hypothesis the inlier distances are gathered in source order and added in
+ * numpy's pairwise order. */
+ORC_API void orc_score_many(void *grid, const double *src, int64_t n_src, const double *Ts, int64_t nh, double max_d,
+                            int64_t *out_cnt, double *out_err2) {
+    const orc_grid_t *g = (const orc_grid_t *)grid;
+    for (int64_t h = 0; h < nh; ++h) { out_cnt[h] = 0; out_err2[h] = 0.0; }
+    if (!g || g->n_tgt == 0 || n_src == 0 || nh == 0 || !(max_d > 0)) return;
+    const double md2 = max_d * max_d;
+    const int64_t CH = 4096;
+    const int64_t nchunk = (n_src + CH - 1) / CH;
+    double *d2 = (double *)malloc(sizeof(double) * (size_t)nh * (size_t)n_src);
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t task = 0; task < nh * nchunk; ++task) {
+        const int64_t h = task / nchunk, c0 = (task % nchunk) * CH;
+        const int64_t c1 = c0 + CH < n_src ? c0 + CH : n_src;
+        const double *T = Ts + 16 * h;
+        for (int64_t i = c0; i < c1; ++i) {
+            double q[3];
+            xform(T, src + 3 * i, q);
+            d2[h * n_src + i] = grid_nn_d2(g, q, max_d, md2);
+        }
+    }
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t h = 0; h < nh; ++h) {
+        double *row = d2 + h * n_src;
+        int64_t cnt = 0;
+        for (int64_t i = 0; i < n_src; ++i) if (row[i] >= 0.0) row[cnt++] = row[i];
+        out_cnt[h] = cnt;
+        out_err2[h] = pairwise_sum(row, cnt);
+    }
+    free(d2);
 }
 
 /* transforms of hypotheses given by samples[nh][3] (indices into corres) */

@@ -234,6 +234,11 @@ typedef struct {
 int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_problems, int64_t max_iteration, double confidence,
                          double max_d, double edge_thr, int use_checkers, int early_exit, int64_t first_block,
                          ibl_reg_result_t *h_results, void *stream);
+/* Measurement switch for ibl_ransac_run_batch's count pass: 1 (default) = a hypothesis is dropped as soon as its inliers so
+ * far plus the points not yet looked at cannot reach the best count of the earlier rounds (exact: such a hypothesis can
+ * never be accepted by the ordered rule); 0 = every validated hypothesis is counted over the whole source.  Results are the
+ * same either way. */
+int ibl_ransac_set_prune(int on);
 /* ibl_icp(mode 1) for n_problems problems at once, from h_T_init[p] (host double[n_problems][16]): one launch per ICP
  * iteration for the whole batch, convergence rule and 6x6 solve per problem on the device, one state read-back per 8
  * queued iterations.  Results equal ibl_icp's.  Syncs. */

@@ -88,6 +88,7 @@ _PROTOS = {
                                      c_double, c_int, c_int, c_int64, POINTER(RegResultT), _V]),
     "ibl_ransac_run_batch": (c_int, [POINTER(RegProblemT), c_int32, c_int64, c_double, c_double, c_double, c_int, c_int,
                                      c_int64, POINTER(RegResultT), _V]),
+    "ibl_ransac_set_prune": (c_int, [c_int]),
     "ibl_icp_colored_batch": (c_int, [POINTER(RegProblemT), c_int32, POINTER(c_double), c_double, c_int, c_double, c_double,
                                       c_double, POINTER(RegResultT), _V]),
     "ibl_nn_score_batch": (c_int, [_V, POINTER(c_void_p), POINTER(c_int64), POINTER(c_double), c_int32, c_double,

@@ -421,6 +421,8 @@ struct RbProb {
     int64_t val_off;    // first validated entry of this problem in Ts[] / inl[] (valid after the count read-back)
     int32_t H;          // hypotheses in this round's block (0 = not active this round)
     int32_t ntiles;
+    int32_t thr;        // inlier count of the problem's best hypothesis so far (0 = none yet): the pruning threshold
+    int32_t nchunks, chunk_step;   // pruned count pass: chunks of PRUNE_CHUNK source points, visited in steps of chunk_step
 };
 
 // grid (ceil(max H / 128), problems).  Validated hypotheses are appended to the problem's id list (block-relative ids;
@@ -519,6 +521,70 @@ __global__ void __launch_bounds__(SCORE_THREADS) ransac_count_batch_kernel(const
         for (int k = 0; k < SCORE_THREADS / 32; ++k) tc += sc[k];
         if (tc) atomicAdd(&inliers[s_entry], tc);
     }
+}
+
+// Inlier count of ONE validated hypothesis per CTA, with an exact early exit.  Only a hypothesis whose count reaches the
+// running maximum can change the RANSAC state, and the running maximum never falls below the count `thr` of
+// the best hypothesis of the earlier rounds.  The CTA walks the source in chunks and stops as soon as
+//     inliers so far + points not yet looked at  <  thr,
+// i.e. when even a perfect remainder could not reach thr; such a hypothesis is reported as -1 ("below thr") and is never a
+// contender.  Hypotheses that finish report their exact count.  With a best fitness of 0.9 a hypothesis that fits 10 % of
+// the cloud is dropped after ~11 % of the points.  Chunks are visited with a stride coprime to their number, so the first
+// chunks sample the whole cloud (the source is a concatenation of objects) rather than its first object.
+#define PRUNE_CHUNK 1024
+__global__ void __launch_bounds__(SCORE_THREADS) ransac_count_prune_batch_kernel(const RbProb *__restrict__ probs, int nprob,
+                                                                                 const int64_t *__restrict__ val_prefix,
+                                                                                 const double *__restrict__ T_all, double max_d,
+                                                                                 double max_d2, int32_t *__restrict__ inliers) {
+    __shared__ GridView g;
+    __shared__ double T[16];
+    __shared__ int sc[2][SCORE_THREADS / 32];
+    __shared__ int s_p;
+    const int64_t entry = blockIdx.x;
+    if (threadIdx.x == 0) s_p = rb_find(val_prefix, nprob, entry);
+    __syncthreads();
+    const RbProb *P = probs + s_p;
+    for (int k = threadIdx.x; k < (int)(sizeof(GridView) / 4); k += SCORE_THREADS)
+        reinterpret_cast<int *>(&g)[k] = reinterpret_cast<const int *>(&P->g)[k];
+    if (threadIdx.x < 16) T[threadIdx.x] = T_all[(size_t)entry * 16 + threadIdx.x];
+    __syncthreads();
+    const double *__restrict__ src = P->src;
+    const int64_t n_src = P->n_src;
+    const int thr = P->thr, nchunks = P->nchunks, step = P->chunk_step;
+    const bool field = g.has_field && max_d <= g.f.max_d;
+    const bool sure_ok = field && max_d == g.f.max_d;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int total = 0;
+    int64_t seen = 0;
+    int chunk = 0;
+#pragma unroll 1
+    for (int it = 0; it < nchunks; ++it) {
+        const int64_t base = (int64_t)chunk * PRUNE_CHUNK;
+        int cnt = 0;
+#pragma unroll 1
+        for (int r = 0; r < PRUNE_CHUNK / SCORE_THREADS; ++r) {
+            int64_t i = base + r * SCORE_THREADS + threadIdx.x;
+            if (i < n_src) {
+                double x, y, z, bd;
+                ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
+                if (field) cnt += ibl_any_within_field(g, x, y, z, max_d2, sure_ok) ? 1 : 0;
+                else cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
+            }
+        }
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if (lane == 0) sc[it & 1][w] = cnt;
+        __syncthreads();                                   // one barrier per chunk: the two buffers alternate
+#pragma unroll
+        for (int k = 0; k < SCORE_THREADS / 32; ++k) total += sc[it & 1][k];
+        seen += min((int64_t)PRUNE_CHUNK, n_src - base);
+        if ((int64_t)total + (n_src - seen) < (int64_t)thr) {   // uniform over the CTA
+            if (threadIdx.x == 0) inliers[entry] = -1;
+            return;
+        }
+        chunk += step;
+        if (chunk >= nchunks) chunk -= nchunks;
+    }
+    if (threadIdx.x == 0) inliers[entry] = total;
 }
 
 // exact score of the contenders: one CTA = (contender, source tile); contender c of the batch refers to validated entry
@@ -621,6 +687,11 @@ __global__ void __launch_bounds__(FIN_THREADS) ransac_finalize_batch_kernel(cons
     }
 }
 
+// 1 (default): the count pass stops a hypothesis as soon as it cannot reach the best count so far (exact, see
+// ransac_count_prune_batch_kernel); 0: every validated hypothesis is counted over the whole source (measurement switch).
+static int g_ransac_prune = 1;
+IBL_API int ibl_ransac_set_prune(int on) { g_ransac_prune = on ? 1 : 0; return IBL_OK; }
+
 #define RB_MAX_BLOCK (1 << 19)     // hypotheses per problem per round, at most (bounds the id lists: 2 MB per problem)
 
 IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_problems, int64_t max_iteration,
@@ -649,6 +720,13 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
         if (hs[p].active) d.g = ibl_view(q.grid_ransac);
         d.src = q.src; d.tgt = q.tgt; d.corres = q.corres; d.n_src = q.n_src; d.n_corres = q.n_corres; d.seed = q.seed;
         d.ntiles = (int)std::max<int64_t>(1, (q.n_src + SCORE_TILE - 1) / SCORE_TILE);
+        d.nchunks = (int)std::max<int64_t>(1, (q.n_src + PRUNE_CHUNK - 1) / PRUNE_CHUNK);
+        // a stride near the golden section of the chunk count, made coprime to it: consecutive visits are far apart
+        int step = std::max(1, (int)(0.6180339887 * d.nchunks));
+        auto gcd = [](int a, int b) { while (b) { int t = a % b; a = b; b = t; } return a; };
+        while (gcd(step, d.nchunks) != 1) ++step;
+        d.chunk_step = step % d.nchunks;
+        if (d.nchunks == 1) d.chunk_step = 0;
     }
     RbProb *d_probs = nullptr; int32_t *d_npass = nullptr;
     IBL_CUDA(ibl_alloc(&d_probs, (size_t)P, st));
@@ -670,6 +748,7 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
             if (!h.active) continue;
             int64_t H = std::min(h.cur_block, std::min(max_iteration, h.est_k) - h.h0);
             d.H = (int32_t)H; d.h0 = h.h0; d.list_off = cap;
+            d.thr = h_results[p].best_hyp >= 0 ? (int32_t)h_results[p].n_inliers : 0;
             cap += H; maxH = std::max(maxH, (int)H); any = true;
         }
         if (!any) break;
@@ -703,14 +782,23 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
             IBL_CUDA(ibl_alloc(&d_prefix, (size_t)P + 1, st));
             IBL_CUDA(cudaMemcpyAsync(d_probs, hp.data(), sizeof(RbProb) * P, cudaMemcpyHostToDevice, st));   // val_off
             IBL_CUDA(cudaMemcpyAsync(d_prefix, item_prefix.data(), sizeof(int64_t) * (P + 1), cudaMemcpyHostToDevice, st));
-            IBL_CUDA(cudaMemsetAsync(d_inl, 0, sizeof(int32_t) * nval, st));
             hyp_transform_batch_kernel<<<dim3((unsigned)((maxpass + 63) / 64), (unsigned)P), 64, 0, st>>>(d_probs, d_ids, d_npass, d_Ts);
             IBL_LAUNCH_CHECK();
             {
                 double work = 0;
                 for (int p = 0; p < P; ++p) work += (double)h_npass[p] * (24.0 * hp[p].n_src + 128.0);
                 IBL_PROF(IBL_PROF_RANSAC_SCORE, st, work);
-                ransac_count_batch_kernel<<<(unsigned)items, SCORE_THREADS, 0, st>>>(d_probs, P, d_prefix, d_Ts, max_d, max_d * max_d, d_inl);
+                if (g_ransac_prune) {
+                    // val_prefix: first validated entry of every problem (entries are laid out problem by problem)
+                    for (int p = 0; p < P; ++p) item_prefix[p] = hp[p].val_off;
+                    item_prefix[P] = nval;
+                    IBL_CUDA(cudaMemcpyAsync(d_prefix, item_prefix.data(), sizeof(int64_t) * (P + 1), cudaMemcpyHostToDevice, st));
+                    ransac_count_prune_batch_kernel<<<(unsigned)nval, SCORE_THREADS, 0, st>>>(d_probs, P, d_prefix, d_Ts, max_d,
+                                                                                             max_d * max_d, d_inl);
+                } else {
+                    IBL_CUDA(cudaMemsetAsync(d_inl, 0, sizeof(int32_t) * nval, st));
+                    ransac_count_batch_kernel<<<(unsigned)items, SCORE_THREADS, 0, st>>>(d_probs, P, d_prefix, d_Ts, max_d, max_d * max_d, d_inl);
+                }
                 IBL_LAUNCH_CHECK();
             }
             h_ids.resize(cap); h_inl.resize(nval);

@@ -397,6 +397,11 @@ def ransac_run_batch(problems, max_iteration, confidence, max_d, edge_thr=0.9, u
     return [_reg_dict(r) for r in res]
 
 
+def ransac_set_prune(on=True):
+    """Measurement switch of the batched RANSAC count pass (ibl_ransac_set_prune); results do not depend on it."""
+    check(lib().ibl_ransac_set_prune(int(bool(on))), "ransac_set_prune")
+
+
 def icp_colored_batch(problems, T_init, max_d, max_iteration=30, rel_fitness=1e-6, rel_rmse=1e-6, lambda_geometric=0.968):
     """ibl_icp_colored_batch: T_init host [n,4,4] -> list of result dicts."""
     n = len(problems)

@@ -72,6 +72,21 @@ def test_ransac_batch_equals_single(K, problems, early_exit, H, block):
     assert got[0]["fitness"] > 0.5
 
 
+def test_ransac_batch_prune_switch(K, problems):
+    """the exact early exit of the count pass changes no result field"""
+    arr = K.reg_problems(_specs(problems))
+    try:
+        K.ransac_set_prune(False)
+        a = K.ransac_run_batch(arr, 200000, 0.99, 0.075, early_exit=True, block=2048)
+        K.ransac_set_prune(True)
+        b = K.ransac_run_batch(arr, 200000, 0.99, 0.075, early_exit=True, block=2048)
+    finally:
+        K.ransac_set_prune(True)
+    for x, y in zip(a, b):
+        assert {k: v for k, v in x.items() if k != "T"} == {k: v for k, v in y.items() if k != "T"}
+        assert np.array_equal(x["T"], y["T"])
+
+
 def test_ransac_batch_checkers_off(K, problems):
     """configs[4]'s forced H_v = H: every hypothesis is scored."""
     sub = [problems[2], problems[4]]

@@ -69,6 +69,9 @@ int ibl_transform_points(const double *h_T16, const double *in, int64_t n, int r
 /* column means in numpy's exact order (np.mean(points, axis=0), object_memory.py:1030-1031, adds the rows
  * one by one): bit-identical to the reference's detected_mean / memory_mean.  h_mean host double[3]. Syncs. */
 int ibl_mean3(const double *pts, int64_t n, double *h_mean, void *stream);
+/* ibl_mean3 of k clouds in one launch and one synchronisation (object_memory.py:1030-1031: one mean per assignment union);
+ * ptrs / ns host arrays of device pointers and row counts, h_means host double[k][3]. */
+int ibl_mean3_many(const double *const *ptrs, const int64_t *ns, int32_t k, double *h_means, void *stream);
 
 /* ---------------------------------------------------------------- uniform grid -------------- */
 typedef struct ibl_grid ibl_grid_t;
@@ -142,6 +145,18 @@ int ibl_fpfh(int64_t n, const int32_t *nbr_idx, const double *nbr_d2, const int3
 /* exact 33-d nearest neighbour of every column of fa among the columns of fb (A.5 KDTreeFlann on
  * features, SearchKNN k=1); lowest index wins ties.  fa double[na][33], fb double[nb][33]. */
 int ibl_feature_nn(const double *fa, int64_t na, const double *fb, int64_t nb, int32_t *nn, void *stream);
+/* Cached matcher operands of ONE feature set (a memory-side union's FPFH, matched against a new source cloud every frame):
+ * the filter's centre and power-of-two scale, packed query-role and target-role tile images, norms, fp32 rows.  `f` must
+ * stay alive as long as the pack.  No reference counterpart (Open3D rebuilds its feature KD-trees on every call). */
+typedef struct ibl_feature_pack ibl_feature_pack_t;
+int ibl_feature_pack_create(const double *f, int64_t n, ibl_feature_pack_t **out, void *stream);
+void ibl_feature_pack_destroy(ibl_feature_pack_t *pack);
+/* Both directions of the A.5 search for a fresh set fa double[na][33] against a pack: nn_ab int32[na] (nearest pack row per
+ * row of fa) and nn_ba int32[pack rows] (nearest row of fa per pack row); identical to two ibl_feature_nn calls.  fa is
+ * read once.  d_flag (device uint32, may be NULL) is OR-ed with 1 if fa does not fit the pack's fp16 range: the outputs
+ * are then invalid and the caller must fall back to ibl_feature_nn. */
+int ibl_feature_match_packed(const double *fa, int64_t na, const ibl_feature_pack_t *pack, int32_t *nn_ab, int32_t *nn_ba,
+                             uint32_t *d_flag, void *stream);
 /* Debug / test hook of the tensor-core filter inside ibl_feature_nn (csrc/match_tc.cu): the raw tcgen05 (kind::f16, 3-way fp16 split) scores
  * s'(a_i, b_j) = a32_i . b32_j - |b32_j|^2 / 2 as float32 [na][nb] (row-major), a32 / b32 being the rows minus the filter's
  * centre, times its power-of-two scale; centre (33) and scale (1) are written to center_out (device double[34]) when

@@ -54,6 +54,7 @@ _PROTOS = {
     "ibl_select_rows": (c_int64, [_V, c_int64, _V, _V, _V, _V, _V, _V, _V, _V]),
     "ibl_transform_points": (c_int, [POINTER(c_double), _V, c_int64, c_int, _V, _V]),
     "ibl_mean3": (c_int, [_V, c_int64, POINTER(c_double), _V]),
+    "ibl_mean3_many": (c_int, [POINTER(c_void_p), POINTER(c_int64), c_int32, POINTER(c_double), _V]),
     "ibl_grid_create": (c_int, [_V, c_int64, c_double, c_int64, POINTER(c_void_p), _V]),
     "ibl_grid_destroy": (None, [_V]),
     "ibl_grid_cell": (c_double, [_V]),
@@ -73,6 +74,9 @@ _PROTOS = {
     "ibl_spfh": (c_int, [_V, _V, c_int64, _V, _V, c_int32, _V, _V]),
     "ibl_fpfh": (c_int, [c_int64, _V, _V, _V, c_int32, _V, _V, _V]),
     "ibl_feature_nn": (c_int, [_V, c_int64, _V, c_int64, _V, _V]),
+    "ibl_feature_pack_create": (c_int, [_V, c_int64, POINTER(c_void_p), _V]),
+    "ibl_feature_pack_destroy": (None, [_V]),
+    "ibl_feature_match_packed": (c_int, [_V, c_int64, _V, _V, _V, _V, _V]),
     "ibl_feature_scores_debug": (c_int, [_V, c_int64, _V, c_int64, _V, _V, c_int, _V]),
     "ibl_feature_nn_stats": (c_int, [POINTER(c_int64), c_int]),
     "ibl_feature_nn_set_pool_chunks": (c_int, [c_int]),

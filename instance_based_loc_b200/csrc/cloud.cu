@@ -2,6 +2,8 @@
 // transforms (reference: utils/depth_utils.py:12-116,146-265).
 #include <cub/cub.cuh>
 
+#include <vector>
+
 #include "ibl_common.cuh"
 
 // ------------------------------------------------------------------------------------------------
@@ -226,7 +228,7 @@ IBL_API int ibl_transform_points(const double *h_T16, const double *in, int64_t 
 // per column.  One CTA: all threads stage a tile of rows in shared memory (coalesced), then three threads run the
 // three dependent add chains.  ~8 cycles per row; N = 3e5 rows -> ~1.3 ms, N = 3e4 -> 0.13 ms.
 #define MEAN_TILE 1024
-__global__ void __launch_bounds__(256) seqsum3_kernel(const double *__restrict__ pts, int64_t n, double *__restrict__ out) {
+__device__ __forceinline__ void seqsum3_block(const double *__restrict__ pts, int64_t n, double *__restrict__ out) {
     __shared__ double tile[2][MEAN_TILE * 3];
     double acc = 0.0;
     int64_t ntiles = (n + MEAN_TILE - 1) / MEAN_TILE;
@@ -252,6 +254,15 @@ __global__ void __launch_bounds__(256) seqsum3_kernel(const double *__restrict__
     }
     if (threadIdx.x < 3) out[threadIdx.x] = acc;
 }
+__global__ void __launch_bounds__(256) seqsum3_kernel(const double *__restrict__ pts, int64_t n, double *__restrict__ out) {
+    seqsum3_block(pts, n, out);
+}
+// the same for several clouds at once: CTA c sums cloud c (the chains of different clouds run side by side)
+struct SeqSumJob { const double *pts; int64_t n; };
+__global__ void __launch_bounds__(256) seqsum3_many_kernel(const SeqSumJob *__restrict__ jobs, double *__restrict__ out) {
+    const SeqSumJob j = jobs[blockIdx.x];
+    seqsum3_block(j.pts, j.n, out + 3 * (size_t)blockIdx.x);
+}
 IBL_API int ibl_mean3(const double *pts, int64_t n, double *h_mean, void *stream) {
     IBL_ARG(h_mean && n >= 0);
     h_mean[0] = h_mean[1] = h_mean[2] = 0.0;
@@ -269,5 +280,37 @@ IBL_API int ibl_mean3(const double *pts, int64_t n, double *h_mean, void *stream
     IBL_CUDA(ibl_sync(st));
     ibl_free(d, st);
     for (int a = 0; a < 3; ++a) h_mean[a] = hs[a] / (double)n;
+    return IBL_OK;
+}
+
+// compute_center / get_center of k clouds in ONE launch and ONE synchronisation (object_memory.py:1030-1031 takes the mean
+// of every assignment's detected union): ptrs / ns are host arrays of device pointers and row counts, h_means host
+// double[k][3].  Every mean equals ibl_mean3's.
+IBL_API int ibl_mean3_many(const double *const *ptrs, const int64_t *ns, int32_t k, double *h_means, void *stream) {
+    IBL_ARG(k >= 0 && (k == 0 || (ptrs && ns && h_means)));
+    if (k == 0) return IBL_OK;
+    cudaStream_t st = ibl_stream(stream);
+    std::vector<SeqSumJob> jobs(k);
+    double work = 0;
+    for (int c = 0; c < k; ++c) {
+        IBL_ARG(ns[c] >= 0 && (ns[c] == 0 || ptrs[c]));
+        jobs[c].pts = ptrs[c]; jobs[c].n = ns[c];
+        work += 24.0 * ns[c];
+    }
+    SeqSumJob *dj = nullptr; double *d = nullptr;
+    IBL_CUDA(ibl_alloc(&dj, (size_t)k, st));
+    IBL_CUDA(ibl_alloc(&d, (size_t)3 * k, st));
+    IBL_CUDA(cudaMemcpyAsync(dj, jobs.data(), sizeof(SeqSumJob) * k, cudaMemcpyHostToDevice, st));
+    {
+        IBL_PROF(IBL_PROF_MEAN, st, work);
+        seqsum3_many_kernel<<<(unsigned)k, 256, 0, st>>>(dj, d);
+        IBL_LAUNCH_CHECK();
+    }
+    std::vector<double> hs((size_t)3 * k);
+    IBL_CUDA(cudaMemcpyAsync(hs.data(), d, sizeof(double) * 3 * k, cudaMemcpyDeviceToHost, st));
+    IBL_CUDA(ibl_sync(st));
+    ibl_free(dj, st); ibl_free(d, st);
+    for (int c = 0; c < k; ++c)
+        for (int a = 0; a < 3; ++a) h_means[3 * c + a] = ns[c] > 0 ? hs[3 * c + a] / (double)ns[c] : 0.0;
     return IBL_OK;
 }

@@ -666,19 +666,15 @@ IBL_API int ibl_feature_nn_set_pool_chunks(int chunks) {
     return IBL_OK;
 }
 
-// exact 33-d nearest neighbour of every row of fa among the rows of fb (tensor-core filter + exact f64 re-evaluation)
-int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb, int32_t *nn, cudaStream_t st) {
-    int rc = tc_configure();
-    if (rc < 0) return rc;
+// The search proper on packed operands: one-pass tcgen05 score GEMM with band recording, the fp32-difference filter with
+// exact f64 evaluation of the survivors, and the per-query merge.  A / B are the packed tile images of the queries (role 0)
+// and targets (role 1) in ONE common centred / scaled coordinate system, an the queries' squared norms in it, bmax_bits the
+// float bits of max |b|^2; fa / fb the raw f64 rows, a32 / b32 / na32 / nb32 their fp32 copies and norm bounds.
+static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb, const float *an, const unsigned *bmax_bits,
+                     const double *fa, const double *fb, const float *a32, const float *b32, const float *na32,
+                     const float *nb32, int32_t *nn, cudaStream_t st) {
     TcPlan p = tc_plan(na, nb);
-    uint8_t *A = nullptr, *B = nullptr;
-    float *an = nullptr;
-    unsigned *mx = nullptr;
     FSplitOutTC *parts = nullptr;
-    IBL_CUDA(ibl_alloc(&A, (size_t)p.qtiles * TC_TILE_BYTES, st));
-    IBL_CUDA(ibl_alloc(&B, (size_t)p.btiles * TC_TILE_BYTES, st));
-    IBL_CUDA(ibl_alloc(&an, (size_t)p.na_pad, st));
-    IBL_CUDA(ibl_alloc(&mx, 3, st));                       // max |a|^2, max |b|^2, max |f - mu| (float bits)
     IBL_CUDA(ibl_alloc(&parts, (size_t)na * p.nsplit, st));
     // candidate pool: one chunk for every row that has a candidate at all + 256k chunks (16 M candidates) of headroom
     TcPool pool;
@@ -693,6 +689,37 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     pool.row = pool_meta; pool.n = pool_meta + pool.cap; pool.next = pool_meta + 2 * (size_t)pool.cap;
     pool.counter = pool_meta + 3 * (size_t)pool.cap;
     IBL_CUDA(cudaMemsetAsync(pool.counter, 0, sizeof(int), st));
+    dim3 grid(p.qtiles, p.nsplit);
+    {
+        // nested scope: the tcgen05 kernel alone, with the flops it ISSUES (depth 112 over the padded tiles)
+        IBL_PROF(IBL_PROF_FEATURE_GEMM, st, 2.0 * TC_K * (double)p.na_pad * (double)p.nb_pad);
+        feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, bmax_bits,
+                                                            fa, fb, parts, pool, nullptr, 0, 0);
+        IBL_LAUNCH_CHECK();
+    }
+    {
+        // the chunk count lives on the device (no host sync): a fixed grid strides over it
+        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32);
+        IBL_LAUNCH_CHECK();
+    }
+    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn);
+    IBL_LAUNCH_CHECK();
+    ibl_free(pool.entries, st); ibl_free(pool_meta, st); ibl_free(res, st); ibl_free(parts, st);
+    return IBL_OK;
+}
+
+// exact 33-d nearest neighbour of every row of fa among the rows of fb (tensor-core filter + exact f64 re-evaluation)
+int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb, int32_t *nn, cudaStream_t st) {
+    int rc = tc_configure();
+    if (rc < 0) return rc;
+    TcPlan p = tc_plan(na, nb);
+    uint8_t *A = nullptr, *B = nullptr;
+    float *an = nullptr;
+    unsigned *mx = nullptr;
+    IBL_CUDA(ibl_alloc(&A, (size_t)p.qtiles * TC_TILE_BYTES, st));
+    IBL_CUDA(ibl_alloc(&B, (size_t)p.btiles * TC_TILE_BYTES, st));
+    IBL_CUDA(ibl_alloc(&an, (size_t)p.na_pad, st));
+    IBL_CUDA(ibl_alloc(&mx, 3, st));                       // max |a|^2, max |b|^2, max |f - mu| (float bits)
     double *mu = nullptr;
     IBL_CUDA(ibl_alloc(&mu, 33, st));
     IBL_CUDA(cudaMemsetAsync(mx, 0, 3 * sizeof(unsigned), st));
@@ -715,24 +742,166 @@ int ibl_feature_nn_tc(const double *fa, int64_t na, const double *fb, int64_t nb
     IBL_LAUNCH_CHECK();
     feat_tc_rows32_kernel<<<(unsigned)((nb + 255) / 256), 256, 0, st>>>(fb, nb, b32, nb32);
     IBL_LAUNCH_CHECK();
-    dim3 grid(p.qtiles, p.nsplit);
-    {
-        // nested scope: the tcgen05 kernel alone, with the flops it ISSUES (depth 112 over the padded tiles)
-        IBL_PROF(IBL_PROF_FEATURE_GEMM, st, 2.0 * TC_K * (double)p.na_pad * (double)p.nb_pad);
-        feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1,
-                                                            fa, fb, parts, pool, nullptr, 0, 0);
-        IBL_LAUNCH_CHECK();
-    }
-    {
-        // the chunk count lives on the device (no host sync): a fixed grid strides over it
-        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32);
-        IBL_LAUNCH_CHECK();
-    }
-    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn);
-    IBL_LAUNCH_CHECK();
+    rc = tc_search(A, na, B, nb, an, mx + 1, fa, fb, a32, b32, na32, nb32, nn, st);
     ibl_free(a32, st); ibl_free(b32, st); ibl_free(na32, st); ibl_free(nb32, st);
-    ibl_free(pool.entries, st); ibl_free(pool_meta, st); ibl_free(res, st); ibl_free(mu, st); ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st); ibl_free(parts, st);
+    ibl_free(mu, st); ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st);
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------------------ cached packs
+// Everything the matcher derives from ONE feature set, built once: the filter's centre (its mean) and power-of-two scale
+// (chosen with one spare bit, so rows of the other side may be twice as far from the centre), the packed query-role and
+// target-role tile images, the squared norms, and the fp32 rows / norm bounds of the second filter.  A memory-side
+// feature set is matched against a new source cloud every frame (fpfh_register.py:110-112 in both directions): with its
+// pack cached, a registration reads the memory-side f64 rows only for the few exact evaluations.
+struct ibl_feature_pack {
+    int64_t n, n_pad;
+    const double *f;           // the caller's rows [n][33] (kept alive by the caller)
+    double *mu;                // [33]
+    unsigned *mx;              // [0] max |row|^2 as query, [1] max |row|^2 as target, [2] 2 * max |f - mu| (float bits)
+    uint8_t *img0, *img1;      // role 0 (query) / role 1 (target) tile images
+    float *an32;               // [n_pad] squared norms of the scaled rows
+    float *rows32, *nrm32;     // second filter
+    cudaStream_t stream;
+};
+
+__global__ void feat_tc_headroom_kernel(unsigned *maxabs_bits) {
+    float m = __uint_as_float(*maxabs_bits);
+    *maxabs_bits = __float_as_uint(__fmul_ru(m, 2.0f));
+}
+
+// Both roles, the norms and the fp32 rows of a feature set from ONE read of its f64 rows, in the coordinate system of
+// another set's pack (centre mu, scale from maxabs_bits).  flag is raised if a scaled value leaves fp16's comfortable
+// range (|v| > 16384): the caller then falls back to ibl_feature_nn.
+__global__ void __launch_bounds__(128) feat_tc_pack_both_kernel(const double *__restrict__ f, int64_t n, int64_t n_pad,
+                                                                const double *__restrict__ mu, const unsigned *__restrict__ maxabs_bits,
+                                                                uint8_t *__restrict__ img0, uint8_t *__restrict__ img1,
+                                                                float *__restrict__ an32, unsigned *__restrict__ maxnorm0,
+                                                                unsigned *__restrict__ maxnorm1, float *__restrict__ rows32,
+                                                                float *__restrict__ nrm32, unsigned *__restrict__ flag) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n_pad) return;
+    unsigned short r0[TC_K], r1[TC_K];
+#pragma unroll
+    for (int k = 0; k < TC_K; ++k) { r0[k] = 0; r1[k] = 0; }
+    if (i < n) {
+        const double sc = tc_scale(maxabs_bits);
+        double s = 0.0, sraw = 0.0;
+        bool over = false;
+        float *o32 = rows32 + i * TC_R32;
+#pragma unroll
+        for (int j = 0; j < 33; ++j) {
+            const double raw = f[i * 33 + j];
+            sraw += raw * raw;
+            o32[j] = __double2float_rn(raw);
+            float v = (float)((raw - mu[j]) * sc);
+            over |= !(fabsf(v) <= 16384.f);
+            __half vh = __float2half_rn(v);
+            __half vl = __float2half_rn(v - __half2float(vh));
+            s += (double)v * (double)v;
+            r0[j] = __half_as_ushort(vh); r0[33 + j] = __half_as_ushort(vl); r0[66 + j] = __half_as_ushort(vh);
+            r1[j] = __half_as_ushort(vh); r1[33 + j] = __half_as_ushort(vh); r1[66 + j] = __half_as_ushort(vl);
+        }
+        o32[33] = o32[34] = o32[35] = 0.f;
+        nrm32[i] = __double2float_ru(sqrt(sraw) * (1.0 + 1e-12));
+        float nf = __double2float_ru(s);
+        an32[i] = nf;
+        atomicMax(maxnorm0, __float_as_uint(nf));
+        atomicMax(maxnorm1, __float_as_uint(nf));
+        if (over) atomicOr(flag, 1u);
+        r0[99] = r0[100] = r0[101] = __half_as_ushort(__float2half_rn(1024.f));
+        double hq = 0.5 * s / 1024.0;
+        __half h0 = __double2half(hq);
+        __half h1 = __double2half(hq - (double)__half2float(h0));
+        __half h2 = __double2half(hq - (double)__half2float(h0) - (double)__half2float(h1));
+        r1[99] = __half_as_ushort(__hneg(h0)); r1[100] = __half_as_ushort(__hneg(h1)); r1[101] = __half_as_ushort(__hneg(h2));
+    } else {
+        r1[99] = r1[100] = r1[101] = __half_as_ushort(__float2half_rn(-60000.f));   // a padding target never scores
+        an32[i] = 0.f;
+    }
+    uint4 *d0 = reinterpret_cast<uint4 *>(img0 + tc_row_offset(i));
+    uint4 *d1 = reinterpret_cast<uint4 *>(img1 + tc_row_offset(i));
+#pragma unroll
+    for (int c = 0; c < TC_KCH; ++c) {
+        uint4 q;
+        q.x = r0[8 * c] | ((unsigned)r0[8 * c + 1] << 16); q.y = r0[8 * c + 2] | ((unsigned)r0[8 * c + 3] << 16);
+        q.z = r0[8 * c + 4] | ((unsigned)r0[8 * c + 5] << 16); q.w = r0[8 * c + 6] | ((unsigned)r0[8 * c + 7] << 16);
+        d0[c * (TC_LBO / 16)] = q;
+        q.x = r1[8 * c] | ((unsigned)r1[8 * c + 1] << 16); q.y = r1[8 * c + 2] | ((unsigned)r1[8 * c + 3] << 16);
+        q.z = r1[8 * c + 4] | ((unsigned)r1[8 * c + 5] << 16); q.w = r1[8 * c + 6] | ((unsigned)r1[8 * c + 7] << 16);
+        d1[c * (TC_LBO / 16)] = q;
+    }
+}
+
+IBL_API int ibl_feature_pack_create(const double *f, int64_t n, ibl_feature_pack_t **out, void *stream) {
+    IBL_ARG(out && n > 0 && f && n < (1ll << 31));
+    cudaStream_t st = ibl_stream(stream);
+    int rc = tc_configure();
+    if (rc < 0) return rc;
+    ibl_feature_pack *pk = (ibl_feature_pack *)calloc(1, sizeof(ibl_feature_pack));
+    pk->n = n; pk->n_pad = (n + TC_M - 1) / TC_M * TC_M; pk->f = f; pk->stream = st;
+    const size_t img = (size_t)(pk->n_pad / TC_M) * TC_TILE_BYTES;
+    IBL_CUDA(ibl_alloc(&pk->mu, 33, st));
+    IBL_CUDA(ibl_alloc(&pk->mx, 4, st));
+    IBL_CUDA(ibl_alloc(&pk->img0, img, st));
+    IBL_CUDA(ibl_alloc(&pk->img1, img, st));
+    IBL_CUDA(ibl_alloc(&pk->an32, (size_t)pk->n_pad, st));
+    IBL_CUDA(ibl_alloc(&pk->rows32, (size_t)n * TC_R32, st));
+    IBL_CUDA(ibl_alloc(&pk->nrm32, (size_t)n, st));
+    IBL_CUDA(cudaMemsetAsync(pk->mx, 0, 4 * sizeof(unsigned), st));
+    feat_tc_center_kernel<<<1, 33 * TC_MU_GROUPS, 0, st>>>(f, n, pk->mu);
+    IBL_LAUNCH_CHECK();
+    feat_tc_range_kernel<<<(unsigned)std::min<int64_t>((n * 33 + 255) / 256, 2 * IBL_SMS), 256, 0, st>>>(f, n, pk->mu, pk->mx + 2);
+    IBL_LAUNCH_CHECK();
+    feat_tc_headroom_kernel<<<1, 1, 0, st>>>(pk->mx + 2);
+    IBL_LAUNCH_CHECK();
+    feat_tc_pack_both_kernel<<<(unsigned)(pk->n_pad / 128), 128, 0, st>>>(f, n, pk->n_pad, pk->mu, pk->mx + 2, pk->img0, pk->img1,
+                                                                         pk->an32, pk->mx, pk->mx + 1, pk->rows32, pk->nrm32,
+                                                                         pk->mx + 3);
+    IBL_LAUNCH_CHECK();
+    *out = pk;
     return IBL_OK;
+}
+
+IBL_API void ibl_feature_pack_destroy(ibl_feature_pack_t *pk) {
+    if (!pk) return;
+    cudaStream_t st = pk->stream;
+    ibl_free(pk->mu, st); ibl_free(pk->mx, st); ibl_free(pk->img0, st); ibl_free(pk->img1, st); ibl_free(pk->an32, st);
+    ibl_free(pk->rows32, st); ibl_free(pk->nrm32, st);
+    free(pk);
+}
+
+// Both directions of A.5 for a fresh feature set fa against a cached pack: nn_ab[i] = nearest row of the pack for row i of
+// fa, nn_ba[j] = nearest row of fa for row j of the pack.  fa is read ONCE (feat_tc_pack_both_kernel, in the pack's
+// coordinate system), the pack's rows only for exact evaluations.  d_flag (device uint32, optional) is OR-ed with 1 when fa
+// does not fit the pack's fp16 range -- the results are then unreliable and the caller must use ibl_feature_nn.
+IBL_API int ibl_feature_match_packed(const double *fa, int64_t na, const ibl_feature_pack_t *pk, int32_t *nn_ab, int32_t *nn_ba,
+                                     uint32_t *d_flag, void *stream) {
+    IBL_ARG(pk && na > 0 && fa && nn_ab && nn_ba && na < (1ll << 31));
+    cudaStream_t st = ibl_stream(stream);
+    int rc = tc_configure();
+    if (rc < 0) return rc;
+    const int64_t na_pad = (na + TC_M - 1) / TC_M * TC_M;
+    const size_t img = (size_t)(na_pad / TC_M) * TC_TILE_BYTES;
+    uint8_t *A0 = nullptr, *A1 = nullptr; float *an = nullptr, *a32 = nullptr, *na32 = nullptr; unsigned *mx = nullptr;
+    IBL_CUDA(ibl_alloc(&A0, img, st));
+    IBL_CUDA(ibl_alloc(&A1, img, st));
+    IBL_CUDA(ibl_alloc(&an, (size_t)na_pad, st));
+    IBL_CUDA(ibl_alloc(&a32, (size_t)na * TC_R32, st));
+    IBL_CUDA(ibl_alloc(&na32, (size_t)na, st));
+    IBL_CUDA(ibl_alloc(&mx, 3, st));
+    IBL_CUDA(cudaMemsetAsync(mx, 0, 3 * sizeof(unsigned), st));
+    {
+        IBL_PROF(IBL_PROF_FEATURE_NN, st, 2.0 * 2.0 * 33.0 * (double)na * (double)pk->n);    // both directions
+        feat_tc_pack_both_kernel<<<(unsigned)(na_pad / 128), 128, 0, st>>>(fa, na, na_pad, pk->mu, pk->mx + 2, A0, A1, an, mx, mx + 1,
+                                                                          a32, na32, d_flag ? d_flag : mx + 2);
+        IBL_LAUNCH_CHECK();
+        rc = tc_search(A0, na, pk->img1, pk->n, an, pk->mx + 1, fa, pk->f, a32, pk->rows32, na32, pk->nrm32, nn_ab, st);
+        if (rc == IBL_OK)
+            rc = tc_search(pk->img0, pk->n, A1, na, pk->an32, mx + 1, pk->f, fa, pk->rows32, a32, pk->nrm32, na32, nn_ba, st);
+    }
+    ibl_free(A0, st); ibl_free(A1, st); ibl_free(an, st); ibl_free(a32, st); ibl_free(na32, st); ibl_free(mx, st);
+    return rc;
 }
 
 // Debug / test hook: the raw tensor-core scores s'(a_i, b_j) = a32.b32 - |b32|^2/2 as float32 [na][nb] (row-major), where

@@ -114,6 +114,18 @@ def mean3(pts):
     return np.array([m[0], m[1], m[2]])
 
 
+def mean3_many(clouds):
+    """means of several [n,3] clouds with one launch and one synchronisation -> float64 [k,3]; row c equals mean3(clouds[c])."""
+    k = len(clouds)
+    out = np.zeros((k, 3))
+    if k == 0:
+        return out
+    ptrs = (ctypes.c_void_p * k)(*[c.data_ptr() if c.shape[0] else None for c in clouds])
+    ns = (c_int64 * k)(*[int(c.shape[0]) for c in clouds])
+    check(lib().ibl_mean3_many(ptrs, ns, k, out.ctypes.data_as(ctypes.POINTER(c_double)), _stream()), "mean3_many")
+    return out
+
+
 # ------------------------------------------------------------------------------------------ grid
 class Grid:
     """Owns an ibl_grid_t; keeps the point tensor alive."""
@@ -255,6 +267,35 @@ def feature_nn(fa, fb):
     out = torch.empty(fa.shape[0], dtype=torch.int32, device=fa.device)
     check(lib().ibl_feature_nn(_p(fa), fa.shape[0], _p(fb), fb.shape[0], _p(out), _stream()), "feature_nn")
     return out
+
+
+class FeaturePack:
+    """Owns an ibl_feature_pack_t: the matcher's cached operands of one feature set (keeps the rows alive)."""
+
+    def __init__(self, f):
+        self.f = f
+        self.h = ctypes.c_void_p()
+        check(lib().ibl_feature_pack_create(_p(f), f.shape[0], ctypes.byref(self.h), _stream()), "feature_pack_create")
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().ibl_feature_pack_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+def feature_match_packed(fa, pack):
+    """Both search directions of a fresh set fa against a cached pack -> (nn_ab int32 [na], nn_ba int32 [pack rows],
+    flag uint32 [1] device tensor: non-zero = fa outside the pack's fp16 range, results invalid)."""
+    dev = fa.device
+    ab = torch.empty(fa.shape[0], dtype=torch.int32, device=dev)
+    ba = torch.empty(pack.f.shape[0], dtype=torch.int32, device=dev)
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    check(lib().ibl_feature_match_packed(_p(fa), fa.shape[0], pack.h, _p(ab), _p(ba), _p(flag), _stream()),
+          "feature_match_packed")
+    return ab, ba, flag
 
 
 def feature_scores_debug(fa, fb, swap_lbo_sbo=0):

@@ -42,6 +42,14 @@ class Feature:
     def __init__(self, dev=None):
         self._dev = dev
         self._host = None
+        self._pack = None
+
+    def pack(self):
+        """The matcher's cached operands of this feature set (ibl_feature_pack_create), built on first use.  Worth it for
+        a set that is matched many times -- the memory side; match_features uses it whenever it exists."""
+        if self._pack is None and self._dev is not None and self._dev.shape[0] > 0:
+            self._pack = K.FeaturePack(self._dev)
+        return self._pack
 
     @property
     def data(self):
@@ -53,6 +61,7 @@ class Feature:
     def data(self, v):
         self._host = np.asarray(v, np.float64)
         self._dev = K.to_dev(np.ascontiguousarray(self._host.T))
+        self._pack = None
 
     def dimension(self):
         return 33 if self._dev is None else int(self._dev.shape[1])
@@ -145,6 +154,13 @@ def _nn_grid(target, max_d):
 def match_features(source_feature, target_feature, mutual_filter=True, ransac_n=3):
     """A.5 -> device int32 [C,2]."""
     fa, fb = source_feature._dev, target_feature._dev
+    if mutual_filter and target_feature._pack is not None and fa.shape[0] > 0:
+        # the target's packed operands are cached: both directions from one read of the source rows
+        ij, ji, flag = K.feature_match_packed(fa, target_feature._pack)
+        cor = K.mutual_corres(ij, ji, ransac_n)              # synchronises
+        if int(flag.item()) == 0:
+            return cor
+        # source values outside the pack's fp16 range (never the case for FPFH): the general path below
     ij = K.feature_nn(fa, fb)
     if not mutual_filter:
         ar = torch.arange(fa.shape[0], dtype=torch.int32, device=fa.device)

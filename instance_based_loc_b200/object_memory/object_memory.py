@@ -17,6 +17,7 @@ import copy
 import os
 import pickle
 import threading
+import time
 from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
@@ -459,6 +460,7 @@ class ObjectMemory():
                 pcd.translate(-mean)
                 try:
                     feats = downsample_and_compute_fpfh(pcd, fpfh_voxel_size)
+                    feats[1].pack()                        # matcher operands of the memory side, packed once
                     tgt = feats[0]
                     _reg._nn_grid(tgt, fpfh_voxel_size * global_dist_factor)
                     _reg._nn_grid(tgt, fpfh_voxel_size * local_dist_factor)
@@ -524,7 +526,7 @@ class ObjectMemory():
     # (per-assignment features, grids, NN fields: ~5 GB for the 40-object bank) happen to be built on that stream
     scratch_bytes_per_stream = 4 << 30
 
-    def localise_batch(self, frames, workers=4, batched_registration=True, **kw):
+    def localise_batch(self, frames, workers=4, batched_registration=True, pipeline_chunks=2, **kw):
         """localise_arrays over a batch of frames (dicts with rgb / depth / masks / embs).  Frames are independent
         (SURVEY.md 8(e)); the work is organised in two stages:
 
@@ -536,6 +538,8 @@ class ObjectMemory():
              evaluate_transform (``ibl_nn_score_batch``) -- a handful of launches and host round trips per stage for the
              whole batch instead of hundreds per frame.
 
+        With several workers the two stages overlap: the batch is cut into ``pipeline_chunks`` groups and a group is
+        registered (stage 2) while the workers are still in stage 1 of the next one.
         ``batched_registration=False`` runs stage 2 frame by frame inside the workers (the round-1 organisation).
         Results are identical to calling localise_arrays frame by frame either way.
         -> list of (pose, [assn, None], info)."""
@@ -583,16 +587,33 @@ class ObjectMemory():
             if not os.environ.get("IBL_NO_LPT"):
                 order.sort(key=lambda i: -int(np.prod(np.shape(frames[i]["masks"]))))
             out = [None] * len(frames)
-            for i, r in zip(order, self._pool.map(run, [frames[i] for i in order])):
-                out[i] = r
+            futs = [self._pool.submit(run, frames[i]) for i in order]
+            if not batched:
+                for i, f in zip(order, futs):
+                    out[i] = f.result()
+                return out
+            # Stage 2 of the frames that are ready runs on this thread WHILE the workers are still in stage 1 of the rest:
+            # the batch is cut into ``pipeline_chunks`` groups in submission order, each registered as one batch.
+            nchunks = max(1, min(int(pipeline_chunks), len(frames) // 4))
+            cuts = [round(k * len(frames) / nchunks) for k in range(nchunks + 1)]
+            timing = {"stage1_wait_s": 0.0, "stage2_s": 0.0}
+            for a, b in zip(cuts[:-1], cuts[1:]):
+                t0 = time.perf_counter()
+                plans = [f.result() for f in futs[a:b]]
+                t1 = time.perf_counter()
+                for i, p in zip(order[a:b], plans):
+                    out[i] = p
+                self._register_batch([p for p in plans if p.get("registrations") is not None])
+                timing["stage1_wait_s"] += t1 - t0
+                timing["stage2_s"] += time.perf_counter() - t1
+            self.last_batch_timing = timing
+            return [self._finish(plan) + (plan["info"],) for plan in out]
         if not batched:
             return out
+        t0 = time.perf_counter()
         self._register_batch([p for p in out if p.get("registrations") is not None])
-        res = []
-        for plan in out:
-            pose, assn = self._finish(plan)
-            res.append((pose, assn, plan["info"]))
-        return res
+        self.last_batch_timing = {"stage1_wait_s": 0.0, "stage2_s": time.perf_counter() - t0}
+        return [self._finish(plan) + (plan["info"],) for plan in out]
 
     # ------------------------------------------------------------------------------------------ plan / register / finish
     def _plan_arrays(self, rgb_image, depth_image, masks, embeddings, phrases=None, outlier_removal_config=None,
@@ -658,13 +679,17 @@ class ObjectMemory():
             raise NotImplementedError                                          # :1036-1037, as in the reference
 
         regs = []
+        unions = []
         for assn in assn_data:                                                 # :1020
             chosen_detected_pcd = PointCloud()
             for d_index, _ in assn:
                 chosen_detected_pcd = chosen_detected_pcd + detected_pointclouds[d_index]
+            unions.append(chosen_detected_pcd)
+        # the means of all unions of the frame: one launch, one read-back (each equals get_center() of that union)
+        means = K.mean3_many([u._p for u in unions]) if unions else []
+        for assn, chosen_detected_pcd, detected_mean in zip(assn_data, unions, means):
             chosen_memory_pcd, memory_mean, target_feats = self._chosen_memory(
                 [m for _, m in assn], fpfh_voxel_size, fpfh_global_dist_factor, fpfh_local_dist_factor)
-            detected_mean = chosen_detected_pcd.get_center()
             chosen_detected_pcd.translate(-detected_mean)                      # :1030-1034
             regs.append({"assn": assn, "source": chosen_detected_pcd, "target": chosen_memory_pcd,
                          "target_feats": target_feats, "detected_mean": detected_mean, "memory_mean": memory_mean})

@@ -156,3 +156,28 @@ def test_localise_batch_modes_agree(cuda):
                 assert g0["ransac"].get("drawn") == g1["ransac"].get("drawn")
                 assert g0["ransac"].get("validated") == g1["ransac"].get("validated")
                 assert g0["icp"].get("iterations") == g1["icp"].get("iterations")
+
+
+@pytest.mark.parametrize("na,nb", [(700, 900), (128, 128), (5000, 3000), (1, 300), (300, 1)])
+def test_feature_match_packed_equals_generic(K, na, nb):
+    """cached-pack matcher (both directions, memory-side centre / scale) == two ibl_feature_nn calls, including planted
+    exact duplicates (lowest index wins) and rows far from the pack's centre."""
+    rng = np.random.default_rng(na * 7 + nb)
+    base = rng.gamma(2.0, 12.0, (40, 33))
+    fb = base[rng.integers(0, 40, nb)] + rng.normal(0, 1.5, (nb, 33))
+    fa = base[rng.integers(0, 40, na)] + rng.normal(0, 1.5, (na, 33))
+    if nb > 10:
+        fb[7] = fb[3]                                   # exact duplicates in the pack
+        fa[0] = fb[3]
+    if na > 10:
+        fa[5] = fa[2]
+        fa[9] *= 1.9                                    # outside the pack's own range, inside its spare bit
+    A, B = dev(fa), dev(fb)
+    pack = K.FeaturePack(B)
+    ab, ba, flag = K.feature_match_packed(A, pack)
+    assert int(flag.item()) == 0
+    assert np.array_equal(ab.cpu().numpy(), K.feature_nn(A, B).cpu().numpy())
+    assert np.array_equal(ba.cpu().numpy(), K.feature_nn(B, A).cpu().numpy())
+    # a source far outside the pack's fp16 range raises the flag (the Python mirror then takes the general path)
+    _, _, flag = K.feature_match_packed(A * 1e6, pack)
+    assert int(flag.item()) != 0

@@ -78,6 +78,12 @@ typedef struct ibl_grid ibl_grid_t;
 /* Cell-sorted uniform grid over pts (replaces Open3D KDTreeFlann construction at every call
  * site).  cell is a request: it is enlarged until nx*ny*nz <= max_cells (0 -> 2^24).  Syncs. */
 int ibl_grid_create(const double *pts, int64_t n, double cell, int64_t max_cells, ibl_grid_t **out, void *stream);
+/* One grid over the concatenation of several clouds, seg int32[n] (device) = the cloud of every point.  Radius queries on
+ * it only count neighbours of the query's own cloud: one build + one query replace a build + a query per cloud (the
+ * per-mask outlier filters of a frame, utils/depth_utils.py:85-88, object_memory.py:992-998).  Only ibl_radius_count and
+ * ibl_radius_outlier_mask are defined on a segmented grid.  Syncs. */
+int ibl_grid_create_segmented(const double *pts, int64_t n, const int32_t *seg, double cell, int64_t max_cells,
+                              ibl_grid_t **out, void *stream);
 void ibl_grid_destroy(ibl_grid_t *g);
 double ibl_grid_cell(const ibl_grid_t *g);
 int64_t ibl_grid_occupied(const ibl_grid_t *g);
@@ -244,7 +250,7 @@ typedef struct {
 } ibl_reg_problem_t;
 /* ibl_ransac_run for n_problems independent problems at once (object_memory.py:1020-1108 registers up to 6 assignments
  * per frame one after the other): per round one block of hypotheses per active problem, ONE launch per stage for the whole
- * batch and three host synchronisations (validated counts, inlier counts, exact scores of the contenders).  Every field of
+ * batch and two host synchronisations (inlier counts of the validated hypotheses, exact scores of the contenders).  Every field of
  * h_results[p] equals what ibl_ransac_run returns for problem p alone.  Syncs. */
 int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_problems, int64_t max_iteration, double confidence,
                          double max_d, double edge_thr, int use_checkers, int early_exit, int64_t first_block,
@@ -255,8 +261,8 @@ int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_problems, 
  * same either way. */
 int ibl_ransac_set_prune(int on);
 /* ibl_icp(mode 1) for n_problems problems at once, from h_T_init[p] (host double[n_problems][16]): one launch per ICP
- * iteration for the whole batch, convergence rule and 6x6 solve per problem on the device, one state read-back per 8
- * queued iterations.  Results equal ibl_icp's.  Syncs. */
+ * iteration for the whole batch, convergence rule and 6x6 solve per problem on the device, two state read-backs (after 12 iterations
+ * and at the end).  Results equal ibl_icp's.  Syncs. */
 int ibl_icp_colored_batch(const ibl_reg_problem_t *problems, int32_t n_problems, const double *h_T_init, double max_d,
                           int max_iteration, double rel_fitness, double rel_rmse, double lambda_geometric,
                           ibl_reg_result_t *h_results, void *stream);

@@ -56,6 +56,7 @@ _PROTOS = {
     "ibl_mean3": (c_int, [_V, c_int64, POINTER(c_double), _V]),
     "ibl_mean3_many": (c_int, [POINTER(c_void_p), POINTER(c_int64), c_int32, POINTER(c_double), _V]),
     "ibl_grid_create": (c_int, [_V, c_int64, c_double, c_int64, POINTER(c_void_p), _V]),
+    "ibl_grid_create_segmented": (c_int, [_V, c_int64, _V, c_double, c_int64, POINTER(c_void_p), _V]),
     "ibl_grid_destroy": (None, [_V]),
     "ibl_grid_cell": (c_double, [_V]),
     "ibl_grid_occupied": (c_int64, [_V]),

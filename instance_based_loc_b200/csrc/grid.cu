@@ -30,13 +30,13 @@ __global__ void cellid_kernel(const double *__restrict__ pts, int64_t n, double 
 
 __global__ void gather_sorted_kernel(const double *__restrict__ pts, const int *__restrict__ ord, int64_t n,
                                      const uint32_t *__restrict__ cid_sorted, double4 *__restrict__ sorted,
-                                     int *__restrict__ cell_count) {
+                                     int *__restrict__ cell_count, const int32_t *__restrict__ seg) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     int o = ord[i];
     double4 v;
     v.x = pts[3 * (size_t)o]; v.y = pts[3 * (size_t)o + 1]; v.z = pts[3 * (size_t)o + 2];
-    v.w = __longlong_as_double((long long)o);
+    v.w = __longlong_as_double(seg ? (((long long)seg[o] << 32) | (long long)(unsigned)o) : (long long)o);
     sorted[i] = v;
     atomicAdd(&cell_count[cid_sorted[i]], 1);   // integer histogram: order independent
 }
@@ -48,14 +48,29 @@ __global__ void count_occupied_kernel(const int *__restrict__ cell_start, int64_
     if ((threadIdx.x & 31) == 0 && b) atomicAdd(out, (unsigned long long)__popc(b));
 }
 
+static int grid_create_impl(const double *pts, int64_t n, double cell, int64_t max_cells, const int32_t *seg, ibl_grid_t **out,
+                            void *stream);
 IBL_API int ibl_grid_create(const double *pts, int64_t n, double cell, int64_t max_cells, ibl_grid_t **out,
+                            void *stream) {
+    return grid_create_impl(pts, n, cell, max_cells, nullptr, out, stream);
+}
+// One grid over the concatenation of several clouds; seg int32[n] (device) names the cloud of every point.  Radius
+// queries on such a grid (ibl_radius_count / ibl_radius_outlier_mask) only count neighbours of the query's own cloud, so
+// one build and one query replace a build and a query per cloud (the per-mask outlier filters of a frame,
+// utils/depth_utils.py:85-88 and object_memory.py:992-998).  Other queries are not defined on a segmented grid.
+IBL_API int ibl_grid_create_segmented(const double *pts, int64_t n, const int32_t *seg, double cell, int64_t max_cells,
+                                      ibl_grid_t **out, void *stream) {
+    IBL_ARG(seg != nullptr || n == 0);
+    return grid_create_impl(pts, n, cell, max_cells, seg, out, stream);
+}
+static int grid_create_impl(const double *pts, int64_t n, double cell, int64_t max_cells, const int32_t *seg, ibl_grid_t **out,
                             void *stream) {
     IBL_ARG(out != nullptr && n >= 0 && cell > 0 && n < (1ll << 31));
     cudaStream_t st = ibl_stream(stream);
     if (max_cells <= 0) max_cells = 1ll << 24;
     ibl_grid *g = new ibl_grid();
     memset(g, 0, sizeof(*g));
-    g->n = n; g->pts = pts; g->stream = st;
+    g->n = n; g->pts = pts; g->stream = st; g->segmented = seg != nullptr;
     double mn[3] = {0, 0, 0}, mx[3] = {0, 0, 0};
     if (n > 0) {
         int nb = (int)((n + 255) / 256);
@@ -108,7 +123,7 @@ IBL_API int ibl_grid_create(const double *pts, int64_t n, double cell, int64_t m
         IBL_CUDA(cudaMallocAsync(&tmp, tmp_bytes ? tmp_bytes : 1, st));
         IBL_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, cid, cid2, ord, g->order, (int)n, 0, bits, st));
         // histogram into cell_start[c] then exclusive scan in place
-        gather_sorted_kernel<<<nb, 256, 0, st>>>(pts, g->order, n, cid2, g->sorted, g->cell_start);
+        gather_sorted_kernel<<<nb, 256, 0, st>>>(pts, g->order, n, cid2, g->sorted, g->cell_start, seg);
         IBL_LAUNCH_CHECK();
         ibl_free(tmp, st);
         size_t tmp2 = 0;

@@ -41,6 +41,8 @@ __global__ void __launch_bounds__(256) radius_count_kernel(GridView g, int64_t n
                     if (p < p1) {
                         double4 t = g.sorted[p];
                         in = ibl_d2(t.x, t.y, t.z, q.x, q.y, q.z) < r2;
+                        // segmented grid: only points of the query's own cloud count
+                        if (g.segmented) in = in && ((__double_as_longlong(t.w) >> 32) == (__double_as_longlong(q.w) >> 32));
                     }
                     c += __popc(__ballot_sync(0xffffffffu, in));
                     if (early && c > nb_points) { done = true; break; }

@@ -47,6 +47,7 @@ enum IblProfTag { IBL_PROF_BACKPROJECT = 0, IBL_PROF_RADIUS, IBL_PROF_KNN, IBL_P
                   IBL_PROF_MISC, IBL_PROF_FEATURE_GEMM /* nested inside FEATURE_NN: the tcgen05 kernel alone */, IBL_PROF_COUNT };
 int ibl_prof_begin(int tag, cudaStream_t st, double bytes);
 void ibl_prof_end(int slot, cudaStream_t st);
+void ibl_prof_add_work(int tag, double bytes);
 struct IblProfScope {
     int slot; cudaStream_t st;
     IblProfScope(int tag, cudaStream_t s, double bytes) : slot(ibl_prof_begin(tag, s, bytes)), st(s) {}
@@ -118,6 +119,7 @@ struct ibl_grid {
     uint8_t *ring;        // optional Chebyshev ring-distance field [ncells]
     int ring_cap;
     cudaStream_t stream;  // stream the grid was built on (frees are ordered on it)
+    int segmented;        // sorted[].w carries (segment << 32 | original index): radius queries stay inside a segment
     // optional candidate field
     int has_field;
     NNFieldView field;
@@ -133,6 +135,7 @@ struct GridView {
     const double4 *sorted;
     const uint8_t *ring;
     int ring_cap;
+    int segmented;
     int has_field;
     NNFieldView f;
 };
@@ -144,6 +147,7 @@ static inline GridView ibl_view(const ibl_grid *g) {
     v.ox = g->ox; v.oy = g->oy; v.oz = g->oz; v.cell = g->cell; v.inv_cell = g->inv_cell;
     v.nx = g->nx; v.ny = g->ny; v.nz = g->nz;
     v.cell_start = g->cell_start; v.sorted = g->sorted; v.ring = g->ring; v.ring_cap = g->ring_cap;
+    v.segmented = g->segmented;
     v.has_field = g->has_field; v.f = g->field;
     return v;
 }

@@ -519,7 +519,7 @@ IBL_API int ibl_icp(const ibl_grid_t *tgt_grid, const double *src, const double 
 
 // All coloured-ICP problems of a step (object_memory.py:1020-1108: one per assignment and frame) iterate together: one
 // launch per ICP iteration for the whole batch, the per-problem convergence rule and 6x6 solve on the device (the last CTA
-// of every problem), and one read-back of the problem states per 8 queued iterations -- instead of 2-4 host round trips
+// of every problem), and one read-back of the problem states after 12 iterations and one at the end -- instead of 2-4 host round trips
 // per problem.  The per-problem arithmetic and reduction order are colored_step_kernel's, so results equal ibl_icp(mode 1).
 IBL_API int ibl_icp_colored_batch(const ibl_reg_problem_t *problems, int32_t n_problems, const double *h_T_init, double max_d,
                                   int max_iteration, double rel_fitness, double rel_rmse, double lambda_geometric,
@@ -581,7 +581,10 @@ IBL_API int ibl_icp_colored_batch(const ibl_reg_problem_t *problems, int32_t n_p
         const int L = (int)live.size();
         IBL_CUDA(cudaMemcpyAsync(d_probs, table.data(), sizeof(IcpProb) * L, cudaMemcpyHostToDevice, st));
         IBL_CUDA(cudaMemcpyAsync(d_prefix, prefix.data(), sizeof(int64_t) * (L + 1), cudaMemcpyHostToDevice, st));
-        const int batch = queued < 0 ? std::min(8, max_iteration + 1) : std::min(8, max_iteration - queued);
+        // the first read-back after 12 iterations (coloured ICP usually converges in 5-15), then everything that is left:
+        // kernels of a converged problem return at once, so queueing past convergence costs a few empty launches, while
+        // every read-back is a host round trip for the whole batch
+        const int batch = queued < 0 ? std::min(13, max_iteration + 1) : max_iteration - queued;
         for (int k = 0; k < batch; ++k) {
             IBL_PROF(IBL_PROF_ICP_REDUCE, st, work);
             colored_step_batch_kernel<<<(unsigned)prefix.back(), 256, 0, st>>>(d_probs, L, d_prefix, max_d, max_d * max_d,

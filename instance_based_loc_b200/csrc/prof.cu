@@ -37,6 +37,13 @@ int ibl_prof_begin(int tag, cudaStream_t st, double bytes) {
     g_recs.push_back(r);
     return (int)g_recs.size() - 1;
 }
+// work of a launch whose size was only known on the device when it was queued (added to the tag's total at the next read)
+static double g_extra_work[IBL_PROF_COUNT];
+void ibl_prof_add_work(int tag, double bytes) {
+    if (!g_prof_on || tag < 0 || tag >= IBL_PROF_COUNT) return;
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    g_extra_work[tag] += bytes;
+}
 void ibl_prof_end(int slot, cudaStream_t st) {
     if (slot < 0) return;
     std::lock_guard<std::mutex> lk(g_prof_mu);
@@ -123,7 +130,7 @@ IBL_API int ibl_prof_read(double *ms, int64_t *launches, double *bytes) {
     IBL_ARG(ms && launches && bytes);
     IBL_CUDA(cudaDeviceSynchronize());
     std::lock_guard<std::mutex> lk(g_prof_mu);
-    for (int t = 0; t < IBL_PROF_COUNT; ++t) { ms[t] = 0; launches[t] = 0; bytes[t] = 0; }
+    for (int t = 0; t < IBL_PROF_COUNT; ++t) { ms[t] = 0; launches[t] = 0; bytes[t] = g_extra_work[t]; g_extra_work[t] = 0; }
     for (auto &r : g_recs) {
         float f = 0.f;
         if (cudaEventElapsedTime(&f, r.e0, r.e1) == cudaSuccess) { ms[r.tag] += f; launches[r.tag] += 1; bytes[r.tag] += r.bytes; }

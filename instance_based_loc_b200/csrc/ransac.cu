@@ -406,10 +406,10 @@ IBL_API int ibl_ransac_run_range(const ibl_grid_t *tgt_grid, const double *src, 
 // ================================================================================================
 // Batched RANSAC: ALL registration problems of a step advance together (object_memory.py:1020-1108 runs <= 6 of these
 // per frame, one after the other; a step of B frames holds <= 6 B independent problems).  Every round handles one block
-// of hypotheses per active problem with ONE launch per stage for the whole batch and THREE host synchronisations in total
-// (validated counts; inlier counts; exact scores of the contenders), instead of three per 512 validated hypotheses per
-// problem.  The per-problem arithmetic, the hypothesis stream and the ordered best-update / adaptive-stop rule are those
-// of ibl_ransac_run_range, so every result field is identical to running the problems one by one.
+// of hypotheses per active problem with ONE launch per stage for the whole batch and TWO host synchronisations (the
+// inlier counts of the validated hypotheses; the exact scores of the contenders) -- instead of three per 512 validated
+// hypotheses per problem.  The per-problem arithmetic, the hypothesis stream and the ordered best-update / adaptive-stop
+// rule are those of ibl_ransac_run_range, so every result field is identical to running the problems one by one.
 struct RbProb {
     GridView g;
     const double *src, *tgt;
@@ -417,19 +417,18 @@ struct RbProb {
     int64_t n_src, n_corres;
     uint64_t seed;
     int64_t h0;         // first hypothesis of this round's block
-    int64_t list_off;   // this problem's slice of ids[] (capacity H)
-    int64_t val_off;    // first validated entry of this problem in Ts[] / inl[] (valid after the count read-back)
     int32_t H;          // hypotheses in this round's block (0 = not active this round)
     int32_t ntiles;
     int32_t thr;        // inlier count of the problem's best hypothesis so far (0 = none yet): the pruning threshold
-    int32_t nchunks, chunk_step;   // pruned count pass: chunks of PRUNE_CHUNK source points, visited in steps of chunk_step
+    int32_t nchunks, chunk_step;   // count pass: chunks of PRUNE_CHUNK source points, visited in steps of chunk_step
 };
+struct RbEntry { int32_t p, k; };   // validated hypothesis k (block-relative) of problem p
 
-// grid (ceil(max H / 128), problems).  Validated hypotheses are appended to the problem's id list (block-relative ids;
-// order within the list is arbitrary, the host sorts): one atomicAdd per warp.
+// grid (ceil(max H / 128), problems).  Validated hypotheses of ALL problems are appended to one list (order arbitrary, the
+// host sorts): one atomicAdd per warp.
 __global__ void __launch_bounds__(128) ransac_check_batch_kernel(const RbProb *__restrict__ probs, double edge_thr,
                                                                  double dist_thr, int use_checkers,
-                                                                 int32_t *__restrict__ ids, int32_t *__restrict__ npass) {
+                                                                 RbEntry *__restrict__ entries, int *__restrict__ n_entries) {
     const RbProb *P = probs + blockIdx.y;
     const int H = P->H;
     if ((int64_t)blockIdx.x * 128 >= H) return;
@@ -444,26 +443,88 @@ __global__ void __launch_bounds__(128) ransac_check_batch_kernel(const RbProb *_
     if (m == 0) return;
     const int lane = threadIdx.x & 31;
     int base = 0;
-    if (lane == 0) base = atomicAdd(&npass[blockIdx.y], __popc(m));
+    if (lane == 0) base = atomicAdd(n_entries, __popc(m));
     base = __shfl_sync(0xffffffffu, base, 0);
-    if (ok) ids[P->list_off + base + __popc(m & ((1u << lane) - 1u))] = k;
+    if (ok) { RbEntry e; e.p = (int)blockIdx.y; e.k = k; entries[base + __popc(m & ((1u << lane) - 1u))] = e; }
 }
 
-// transforms of the validated hypotheses: grid (ceil(max npass / 64), problems)
-__global__ void __launch_bounds__(64) hyp_transform_batch_kernel(const RbProb *__restrict__ probs, const int32_t *__restrict__ ids,
-                                                                 const int32_t *__restrict__ npass, double *__restrict__ T_out) {
-    const RbProb *P = probs + blockIdx.y;
-    const int j = blockIdx.x * 64 + threadIdx.x;
-    if (j >= npass[blockIdx.y]) return;
-    double s[9], t[9], T[16];
-    gather_sample(P->src, P->tgt, P->corres, P->n_corres, nullptr, P->seed, P->h0 + ids[P->list_off + j], s, t);
-    ibl_kabsch3(s, t, T);
-    double *o = T_out + (size_t)(P->val_off + j) * 16;
+// Inlier count of the validated hypotheses, with an exact early exit.  Only a hypothesis whose count reaches the running
+// maximum can change the RANSAC state, and the running maximum never falls below the count `thr` of the
+// best hypothesis of the earlier rounds.  A CTA takes one hypothesis at a time (persistent grid over the entry list, whose
+// length lives on the device: no host round trip between the check and the count), computes its transform, walks the
+// source in chunks and stops as soon as
+//     inliers so far + points not yet looked at  <  thr,
+// i.e. when even a perfect remainder could not reach thr; such a hypothesis is reported as -1 ("below thr") and is never a
+// contender.  Hypotheses that finish report their exact count.  With a best fitness of 0.9 a hypothesis that fits 10 % of
+// the cloud is dropped after ~11 % of the points.  Chunks are visited with a stride coprime to their number, so the first
+// chunks sample the whole cloud (the source is a concatenation of objects) rather than its first object.
+#define PRUNE_CHUNK 1024
+__global__ void __launch_bounds__(SCORE_THREADS) ransac_count_batch_kernel(const RbProb *__restrict__ probs,
+                                                                           const RbEntry *__restrict__ entries,
+                                                                           const int *__restrict__ n_entries, double max_d,
+                                                                           double max_d2, int32_t *__restrict__ inliers) {
+    __shared__ GridView g;
+    __shared__ double T[16];
+    __shared__ int sc[2][SCORE_THREADS / 32];
+    const int n = *n_entries;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int cur_p = -1;
+#pragma unroll 1
+    for (int e = blockIdx.x; e < n; e += gridDim.x) {
+        const RbEntry ent = entries[e];
+        const RbProb *P = probs + ent.p;
+        __syncthreads();                                   // the previous hypothesis' readers of g / T / sc are done
+        if (ent.p != cur_p) {
+            for (int k = threadIdx.x; k < (int)(sizeof(GridView) / 4); k += SCORE_THREADS)
+                reinterpret_cast<int *>(&g)[k] = reinterpret_cast<const int *>(&P->g)[k];
+            cur_p = ent.p;
+        }
+        if (threadIdx.x == 0) {
+            double s[9], t[9], Tl[16];
+            gather_sample(P->src, P->tgt, P->corres, P->n_corres, nullptr, P->seed, P->h0 + ent.k, s, t);
+            ibl_kabsch3(s, t, Tl);
 #pragma unroll
-    for (int e = 0; e < 16; ++e) o[e] = T[e];
+            for (int k = 0; k < 16; ++k) T[k] = Tl[k];
+        }
+        __syncthreads();
+        const double *__restrict__ src = P->src;
+        const int64_t n_src = P->n_src;
+        const int thr = P->thr, nchunks = P->nchunks, step = P->chunk_step;
+        const bool field = g.has_field && max_d <= g.f.max_d;
+        const bool sure_ok = field && max_d == g.f.max_d;
+        int total = 0;
+        int64_t seen = 0;
+        int chunk = 0;
+        bool pruned = false;
+#pragma unroll 1
+        for (int it = 0; it < nchunks; ++it) {
+            const int64_t base = (int64_t)chunk * PRUNE_CHUNK;
+            int cnt = 0;
+#pragma unroll 1
+            for (int r = 0; r < PRUNE_CHUNK / SCORE_THREADS; ++r) {
+                int64_t i = base + r * SCORE_THREADS + threadIdx.x;
+                if (i < n_src) {
+                    double x, y, z, bd;
+                    ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
+                    if (field) cnt += ibl_any_within_field(g, x, y, z, max_d2, sure_ok) ? 1 : 0;
+                    else cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
+                }
+            }
+            cnt = __reduce_add_sync(0xffffffffu, cnt);
+            if (lane == 0) sc[it & 1][w] = cnt;
+            __syncthreads();                               // one barrier per chunk: the two buffers alternate
+#pragma unroll
+            for (int k = 0; k < SCORE_THREADS / 32; ++k) total += sc[it & 1][k];
+            seen += min((int64_t)PRUNE_CHUNK, n_src - base);
+            if ((int64_t)total + (n_src - seen) < (int64_t)thr) { pruned = true; break; }   // uniform over the CTA
+            chunk += step;
+            if (chunk >= nchunks) chunk -= nchunks;
+        }
+        if (threadIdx.x == 0) inliers[e] = pruned ? -1 : total;
+    }
 }
 
-// which problem does work item `item` belong to: prefix[p] <= item < prefix[p+1]
+// which contender does work item `item` belong to: prefix[c] <= item < prefix[c+1]
 __device__ __forceinline__ int rb_find(const int64_t *__restrict__ prefix, int n, int64_t item) {
     int lo = 0, hi = n;
     while (hi - lo > 1) {
@@ -473,128 +534,25 @@ __device__ __forceinline__ int rb_find(const int64_t *__restrict__ prefix, int n
     return lo;
 }
 
-// One CTA = one (problem, validated hypothesis, source tile) of the round; the same per-point test and the same integer
-// accumulation as ransac_count_kernel.
-__global__ void __launch_bounds__(SCORE_THREADS) ransac_count_batch_kernel(const RbProb *__restrict__ probs, int nprob,
-                                                                           const int64_t *__restrict__ item_prefix,
-                                                                           const double *__restrict__ T_all, double max_d,
-                                                                           double max_d2, int32_t *__restrict__ inliers) {
-    __shared__ GridView g;
-    __shared__ double T[16];
-    __shared__ int sc[SCORE_THREADS / 32];
-    __shared__ int s_p;
-    __shared__ int64_t s_entry, s_tile;
-    if (threadIdx.x == 0) {
-        const int p = rb_find(item_prefix, nprob, (int64_t)blockIdx.x);
-        const int64_t local = (int64_t)blockIdx.x - item_prefix[p];
-        const int nt = probs[p].ntiles;
-        s_p = p; s_entry = probs[p].val_off + local / nt; s_tile = local % nt;
-    }
-    __syncthreads();
-    const RbProb *P = probs + s_p;
-    for (int k = threadIdx.x; k < (int)(sizeof(GridView) / 4); k += SCORE_THREADS)
-        reinterpret_cast<int *>(&g)[k] = reinterpret_cast<const int *>(&P->g)[k];
-    if (threadIdx.x < 16) T[threadIdx.x] = T_all[(size_t)s_entry * 16 + threadIdx.x];
-    __syncthreads();
-    const double *__restrict__ src = P->src;
-    const int64_t n_src = P->n_src;
-    int cnt = 0;
-    const int64_t base = s_tile * SCORE_TILE;
-    const bool field = g.has_field && max_d <= g.f.max_d;
-    const bool sure_ok = field && max_d == g.f.max_d;
-#pragma unroll 1
-    for (int r = 0; r < SCORE_TILE / SCORE_THREADS; ++r) {
-        int64_t i = base + r * SCORE_THREADS + threadIdx.x;
-        if (i < n_src) {
-            double x, y, z, bd;
-            ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
-            if (field) cnt += ibl_any_within_field(g, x, y, z, max_d2, sure_ok) ? 1 : 0;
-            else cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
-        }
-    }
-    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int o = 16; o; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
-    if (lane == 0) sc[w] = cnt;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int tc = 0;
-        for (int k = 0; k < SCORE_THREADS / 32; ++k) tc += sc[k];
-        if (tc) atomicAdd(&inliers[s_entry], tc);
-    }
-}
-
-// Inlier count of ONE validated hypothesis per CTA, with an exact early exit.  Only a hypothesis whose count reaches the
-// running maximum can change the RANSAC state, and the running maximum never falls below the count `thr` of
-// the best hypothesis of the earlier rounds.  The CTA walks the source in chunks and stops as soon as
-//     inliers so far + points not yet looked at  <  thr,
-// i.e. when even a perfect remainder could not reach thr; such a hypothesis is reported as -1 ("below thr") and is never a
-// contender.  Hypotheses that finish report their exact count.  With a best fitness of 0.9 a hypothesis that fits 10 % of
-// the cloud is dropped after ~11 % of the points.  Chunks are visited with a stride coprime to their number, so the first
-// chunks sample the whole cloud (the source is a concatenation of objects) rather than its first object.
-#define PRUNE_CHUNK 1024
-__global__ void __launch_bounds__(SCORE_THREADS) ransac_count_prune_batch_kernel(const RbProb *__restrict__ probs, int nprob,
-                                                                                 const int64_t *__restrict__ val_prefix,
-                                                                                 const double *__restrict__ T_all, double max_d,
-                                                                                 double max_d2, int32_t *__restrict__ inliers) {
-    __shared__ GridView g;
-    __shared__ double T[16];
-    __shared__ int sc[2][SCORE_THREADS / 32];
-    __shared__ int s_p;
-    const int64_t entry = blockIdx.x;
-    if (threadIdx.x == 0) s_p = rb_find(val_prefix, nprob, entry);
-    __syncthreads();
-    const RbProb *P = probs + s_p;
-    for (int k = threadIdx.x; k < (int)(sizeof(GridView) / 4); k += SCORE_THREADS)
-        reinterpret_cast<int *>(&g)[k] = reinterpret_cast<const int *>(&P->g)[k];
-    if (threadIdx.x < 16) T[threadIdx.x] = T_all[(size_t)entry * 16 + threadIdx.x];
-    __syncthreads();
-    const double *__restrict__ src = P->src;
-    const int64_t n_src = P->n_src;
-    const int thr = P->thr, nchunks = P->nchunks, step = P->chunk_step;
-    const bool field = g.has_field && max_d <= g.f.max_d;
-    const bool sure_ok = field && max_d == g.f.max_d;
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    int total = 0;
-    int64_t seen = 0;
-    int chunk = 0;
-#pragma unroll 1
-    for (int it = 0; it < nchunks; ++it) {
-        const int64_t base = (int64_t)chunk * PRUNE_CHUNK;
-        int cnt = 0;
-#pragma unroll 1
-        for (int r = 0; r < PRUNE_CHUNK / SCORE_THREADS; ++r) {
-            int64_t i = base + r * SCORE_THREADS + threadIdx.x;
-            if (i < n_src) {
-                double x, y, z, bd;
-                ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
-                if (field) cnt += ibl_any_within_field(g, x, y, z, max_d2, sure_ok) ? 1 : 0;
-                else cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
-            }
-        }
-        cnt = __reduce_add_sync(0xffffffffu, cnt);
-        if (lane == 0) sc[it & 1][w] = cnt;
-        __syncthreads();                                   // one barrier per chunk: the two buffers alternate
+// transforms of the contenders (thread per contender)
+__global__ void __launch_bounds__(64) hyp_transform_sel_kernel(const RbProb *__restrict__ probs, const RbEntry *__restrict__ sel,
+                                                               int nsel, double *__restrict__ T_out) {
+    const int c = blockIdx.x * 64 + threadIdx.x;
+    if (c >= nsel) return;
+    const RbProb *P = probs + sel[c].p;
+    double s[9], t[9], T[16];
+    gather_sample(P->src, P->tgt, P->corres, P->n_corres, nullptr, P->seed, P->h0 + sel[c].k, s, t);
+    ibl_kabsch3(s, t, T);
 #pragma unroll
-        for (int k = 0; k < SCORE_THREADS / 32; ++k) total += sc[it & 1][k];
-        seen += min((int64_t)PRUNE_CHUNK, n_src - base);
-        if ((int64_t)total + (n_src - seen) < (int64_t)thr) {   // uniform over the CTA
-            if (threadIdx.x == 0) inliers[entry] = -1;
-            return;
-        }
-        chunk += step;
-        if (chunk >= nchunks) chunk -= nchunks;
-    }
-    if (threadIdx.x == 0) inliers[entry] = total;
+    for (int e = 0; e < 16; ++e) T_out[(size_t)c * 16 + e] = T[e];
 }
 
-// exact score of the contenders: one CTA = (contender, source tile); contender c of the batch refers to validated entry
-// sel_entry[c] (its transform) and problem sel_prob[c]; tile partials go to part[part_off[c] + tile] (ransac_score_kernel's
-// reduction order inside the CTA).
+// exact score of the contenders: one CTA = (contender, source tile); tile partials go to part[item] in
+// ransac_score_kernel's reduction order inside the CTA.
 __global__ void __launch_bounds__(SCORE_THREADS) ransac_score_batch_kernel(const RbProb *__restrict__ probs,
                                                                            const int64_t *__restrict__ item_prefix, int nsel,
-                                                                           const int32_t *__restrict__ sel_prob,
-                                                                           const int64_t *__restrict__ sel_entry,
-                                                                           const double *__restrict__ T_all, double max_d,
+                                                                           const RbEntry *__restrict__ sel,
+                                                                           const double *__restrict__ T_sel, double max_d,
                                                                            double max_d2, int *__restrict__ part_cnt,
                                                                            double *__restrict__ part_err) {
     __shared__ GridView g;
@@ -606,10 +564,10 @@ __global__ void __launch_bounds__(SCORE_THREADS) ransac_score_batch_kernel(const
     __syncthreads();
     const int c = s_c;
     const int64_t tile = (int64_t)blockIdx.x - item_prefix[c];
-    const RbProb *P = probs + sel_prob[c];
+    const RbProb *P = probs + sel[c].p;
     for (int k = threadIdx.x; k < (int)(sizeof(GridView) / 4); k += SCORE_THREADS)
         reinterpret_cast<int *>(&g)[k] = reinterpret_cast<const int *>(&P->g)[k];
-    if (threadIdx.x < 16) T[threadIdx.x] = T_all[(size_t)sel_entry[c] * 16 + threadIdx.x];
+    if (threadIdx.x < 16) T[threadIdx.x] = T_sel[(size_t)c * 16 + threadIdx.x];
     __syncthreads();
     const double *__restrict__ src = P->src;
     const int64_t n_src = P->n_src;
@@ -641,20 +599,19 @@ __global__ void __launch_bounds__(SCORE_THREADS) ransac_score_batch_kernel(const
 // one CTA per contender: tile partials in ransac_finalize_kernel's order + the correspondence inlier count
 __global__ void __launch_bounds__(FIN_THREADS) ransac_finalize_batch_kernel(const RbProb *__restrict__ probs,
                                                                             const int64_t *__restrict__ item_prefix,
-                                                                            const int32_t *__restrict__ sel_prob,
-                                                                            const int64_t *__restrict__ sel_entry,
+                                                                            const RbEntry *__restrict__ sel,
                                                                             const int *__restrict__ part_cnt,
                                                                             const double *__restrict__ part_err,
-                                                                            const double *__restrict__ T_all, double max_d,
+                                                                            const double *__restrict__ T_sel, double max_d,
                                                                             int32_t *__restrict__ inliers, double *__restrict__ err2,
                                                                             int32_t *__restrict__ corres_inliers) {
     __shared__ double se[FIN_THREADS / 32];
     __shared__ int sc[FIN_THREADS / 32], si[FIN_THREADS / 32];
     __shared__ double T[16];
     const int c = blockIdx.x;
-    const RbProb *P = probs + sel_prob[c];
+    const RbProb *P = probs + sel[c].p;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    if (threadIdx.x < 16) T[threadIdx.x] = T_all[(size_t)sel_entry[c] * 16 + threadIdx.x];
+    if (threadIdx.x < 16) T[threadIdx.x] = T_sel[(size_t)c * 16 + threadIdx.x];
     __syncthreads();
     const int64_t p0 = item_prefix[c];
     const int ntiles = (int)(item_prefix[c + 1] - p0);
@@ -688,11 +645,13 @@ __global__ void __launch_bounds__(FIN_THREADS) ransac_finalize_batch_kernel(cons
 }
 
 // 1 (default): the count pass stops a hypothesis as soon as it cannot reach the best count so far (exact, see
-// ransac_count_prune_batch_kernel); 0: every validated hypothesis is counted over the whole source (measurement switch).
+// ransac_count_batch_kernel); 0: every validated hypothesis is counted over the whole source (measurement switch).
 static int g_ransac_prune = 1;
 IBL_API int ibl_ransac_set_prune(int on) { g_ransac_prune = on ? 1 : 0; return IBL_OK; }
 
-#define RB_MAX_BLOCK (1 << 19)     // hypotheses per problem per round, at most (bounds the id lists: 2 MB per problem)
+#define RB_MAX_BLOCK (1 << 20)     // hypotheses per problem per round, at most
+#define RB_GROWTH 4                // block growth per round: 64 k, 256 k, 1 M, 1 M, ... (few rounds = few host round trips)
+#define RB_OPT_ENTRIES (1 << 16)   // validated entries read back together with their number (more need a second copy)
 
 IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_problems, int64_t max_iteration,
                                  double confidence, double max_d, double edge_thr, int use_checkers, int early_exit,
@@ -701,7 +660,7 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
     if (n_problems == 0) return IBL_OK;
     cudaStream_t st = ibl_stream(stream);
     const int P = n_problems;
-    if (first_block <= 0) first_block = 1 << 14;
+    if (first_block <= 0) first_block = 1 << 16;
     struct Host { int64_t est_k, h0, cur_block; double best_fit, best_rmse; bool active; };
     std::vector<Host> hs(P);
     std::vector<RbProb> hp(P);
@@ -725,16 +684,16 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
         int step = std::max(1, (int)(0.6180339887 * d.nchunks));
         auto gcd = [](int a, int b) { while (b) { int t = a % b; a = b; b = t; } return a; };
         while (gcd(step, d.nchunks) != 1) ++step;
-        d.chunk_step = step % d.nchunks;
-        if (d.nchunks == 1) d.chunk_step = 0;
+        d.chunk_step = d.nchunks == 1 ? 0 : step % d.nchunks;
     }
-    RbProb *d_probs = nullptr; int32_t *d_npass = nullptr;
+    RbProb *d_probs = nullptr; int *d_n = nullptr;
     IBL_CUDA(ibl_alloc(&d_probs, (size_t)P, st));
-    IBL_CUDA(ibl_alloc(&d_npass, (size_t)P, st));
-    std::vector<int32_t> h_npass(P), h_ids, h_inl, h_inl2, h_cinl, sel_prob;
-    std::vector<int64_t> item_prefix(P + 1), sel_entry, sel_prefix;
+    IBL_CUDA(ibl_alloc(&d_n, 1, st));
+    std::vector<RbEntry> h_ent, sel;
+    std::vector<int32_t> h_inl, h_inl2, h_cinl;
+    std::vector<int64_t> sel_prefix;
     std::vector<double> h_err, h_T;
-    struct Cand { int32_t id; int32_t inl; int64_t entry; int sel; };
+    struct Cand { int32_t k; int32_t inl; int sel; };
     std::vector<std::vector<Cand>> cands(P);
     int rc = IBL_OK;
     for (;;) {
@@ -747,130 +706,103 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
             if (h.active && !(h.h0 < max_iteration && h.h0 < h.est_k)) h.active = false;
             if (!h.active) continue;
             int64_t H = std::min(h.cur_block, std::min(max_iteration, h.est_k) - h.h0);
-            d.H = (int32_t)H; d.h0 = h.h0; d.list_off = cap;
-            d.thr = h_results[p].best_hyp >= 0 ? (int32_t)h_results[p].n_inliers : 0;
+            d.H = (int32_t)H; d.h0 = h.h0;
+            d.thr = (g_ransac_prune && h_results[p].best_hyp >= 0) ? (int32_t)h_results[p].n_inliers : 0;
             cap += H; maxH = std::max(maxH, (int)H); any = true;
         }
         if (!any) break;
-        int32_t *d_ids = nullptr;
-        IBL_CUDA(ibl_alloc(&d_ids, (size_t)cap, st));
+        if (cap >= (1ll << 31)) { ibl_set_error("ransac batch: %lld hypotheses in one round", (long long)cap); rc = IBL_E_ARG; break; }
+        RbEntry *d_ent = nullptr; int32_t *d_inl = nullptr;
+        IBL_CUDA(ibl_alloc(&d_ent, (size_t)cap, st));       // every hypothesis of the round may validate (checkers off)
+        IBL_CUDA(ibl_alloc(&d_inl, (size_t)cap, st));
         IBL_CUDA(cudaMemcpyAsync(d_probs, hp.data(), sizeof(RbProb) * P, cudaMemcpyHostToDevice, st));
-        IBL_CUDA(cudaMemsetAsync(d_npass, 0, sizeof(int32_t) * P, st));
+        IBL_CUDA(cudaMemsetAsync(d_n, 0, sizeof(int), st));
         {
             IBL_PROF(IBL_PROF_RANSAC_CHECK, st, 157.0 * (double)cap);
             ransac_check_batch_kernel<<<dim3((unsigned)((maxH + 127) / 128), (unsigned)P), 128, 0, st>>>(d_probs, edge_thr, max_d,
-                                                                                                      use_checkers, d_ids, d_npass);
+                                                                                                      use_checkers, d_ent, d_n);
             IBL_LAUNCH_CHECK();
         }
-        IBL_CUDA(cudaMemcpyAsync(h_npass.data(), d_npass, sizeof(int32_t) * P, cudaMemcpyDeviceToHost, st));
-        IBL_CUDA(ibl_sync(st));                                                              // sync 1: validated counts
-        int64_t nval = 0, items = 0; int maxpass = 0;
-        for (int p = 0; p < P; ++p) {
-            RbProb &d = hp[p];
-            int np = d.H > 0 ? h_npass[p] : 0;
-            h_npass[p] = np;
-            d.val_off = nval;
-            item_prefix[p] = items;
-            nval += np; items += (int64_t)np * d.ntiles; maxpass = std::max(maxpass, np);
+        {
+            // work figure: the un-pruned pass (every validated hypothesis over its whole source); the number of validated
+            // hypotheses is only known on the device here, so it is filled in after the read-back
+            IBL_PROF(IBL_PROF_RANSAC_SCORE, st, 0.0);
+            ransac_count_batch_kernel<<<IBL_SMS * 6, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
+            IBL_LAUNCH_CHECK();
         }
-        item_prefix[P] = items;
+        int nval = 0;
+        const int64_t opt = std::min<int64_t>(cap, RB_OPT_ENTRIES);
+        h_ent.resize((size_t)std::max<int64_t>(opt, 1)); h_inl.resize((size_t)std::max<int64_t>(opt, 1));
+        IBL_CUDA(cudaMemcpyAsync(&nval, d_n, sizeof(int), cudaMemcpyDeviceToHost, st));
+        IBL_CUDA(cudaMemcpyAsync(h_ent.data(), d_ent, sizeof(RbEntry) * opt, cudaMemcpyDeviceToHost, st));
+        IBL_CUDA(cudaMemcpyAsync(h_inl.data(), d_inl, sizeof(int32_t) * opt, cudaMemcpyDeviceToHost, st));
+        IBL_CUDA(ibl_sync(st));                                                              // sync 1: counts
+        if (nval > opt) {
+            h_ent.resize((size_t)nval); h_inl.resize((size_t)nval);
+            IBL_CUDA(cudaMemcpyAsync(h_ent.data() + opt, d_ent + opt, sizeof(RbEntry) * (nval - opt), cudaMemcpyDeviceToHost, st));
+            IBL_CUDA(cudaMemcpyAsync(h_inl.data() + opt, d_inl + opt, sizeof(int32_t) * (nval - opt), cudaMemcpyDeviceToHost, st));
+            IBL_CUDA(ibl_sync(st));
+        }
+        ibl_prof_add_work(IBL_PROF_RANSAC_SCORE, [&] { double w = 0; for (int e = 0; e < nval; ++e) w += 24.0 * hp[h_ent[e].p].n_src + 128.0; return w; }());
         if (nval > 0) {
-            if (items >= (1ll << 31)) { ibl_set_error("ransac batch: %lld count work items in one round", (long long)items); rc = IBL_E_ARG; ibl_free(d_ids, st); break; }
-            double *d_Ts = nullptr; int32_t *d_inl = nullptr; int64_t *d_prefix = nullptr;
-            IBL_CUDA(ibl_alloc(&d_Ts, (size_t)nval * 16, st));
-            IBL_CUDA(ibl_alloc(&d_inl, (size_t)nval, st));
-            IBL_CUDA(ibl_alloc(&d_prefix, (size_t)P + 1, st));
-            IBL_CUDA(cudaMemcpyAsync(d_probs, hp.data(), sizeof(RbProb) * P, cudaMemcpyHostToDevice, st));   // val_off
-            IBL_CUDA(cudaMemcpyAsync(d_prefix, item_prefix.data(), sizeof(int64_t) * (P + 1), cudaMemcpyHostToDevice, st));
-            hyp_transform_batch_kernel<<<dim3((unsigned)((maxpass + 63) / 64), (unsigned)P), 64, 0, st>>>(d_probs, d_ids, d_npass, d_Ts);
-            IBL_LAUNCH_CHECK();
-            {
-                double work = 0;
-                for (int p = 0; p < P; ++p) work += (double)h_npass[p] * (24.0 * hp[p].n_src + 128.0);
-                IBL_PROF(IBL_PROF_RANSAC_SCORE, st, work);
-                if (g_ransac_prune) {
-                    // val_prefix: first validated entry of every problem (entries are laid out problem by problem)
-                    for (int p = 0; p < P; ++p) item_prefix[p] = hp[p].val_off;
-                    item_prefix[P] = nval;
-                    IBL_CUDA(cudaMemcpyAsync(d_prefix, item_prefix.data(), sizeof(int64_t) * (P + 1), cudaMemcpyHostToDevice, st));
-                    ransac_count_prune_batch_kernel<<<(unsigned)nval, SCORE_THREADS, 0, st>>>(d_probs, P, d_prefix, d_Ts, max_d,
-                                                                                             max_d * max_d, d_inl);
-                } else {
-                    IBL_CUDA(cudaMemsetAsync(d_inl, 0, sizeof(int32_t) * nval, st));
-                    ransac_count_batch_kernel<<<(unsigned)items, SCORE_THREADS, 0, st>>>(d_probs, P, d_prefix, d_Ts, max_d, max_d * max_d, d_inl);
-                }
-                IBL_LAUNCH_CHECK();
-            }
-            h_ids.resize(cap); h_inl.resize(nval);
-            // the id lists are sparse inside ids[] (capacity H per problem): copy each problem's used prefix
-            for (int p = 0; p < P; ++p)
-                if (h_npass[p] > 0)
-                    IBL_CUDA(cudaMemcpyAsync(h_ids.data() + hp[p].list_off, d_ids + hp[p].list_off, sizeof(int32_t) * h_npass[p],
-                                             cudaMemcpyDeviceToHost, st));
-            IBL_CUDA(cudaMemcpyAsync(h_inl.data(), d_inl, sizeof(int32_t) * nval, cudaMemcpyDeviceToHost, st));
-            IBL_CUDA(ibl_sync(st));                                                          // sync 2: inlier counts
             // ---- contenders: in id order, a hypothesis whose count reaches the running maximum before it
-            sel_prob.clear(); sel_entry.clear(); sel_prefix.assign(1, 0);
+            for (int e = 0; e < nval; ++e) cands[h_ent[e].p].push_back(Cand{h_ent[e].k, h_inl[e], -1});
+            sel.clear(); sel_prefix.assign(1, 0);
             for (int p = 0; p < P; ++p) {
                 std::vector<Cand> &cv = cands[p];
-                cv.clear();
-                const int np = h_npass[p];
-                if (np == 0) continue;
-                cv.resize(np);
-                for (int j = 0; j < np; ++j) cv[j] = Cand{h_ids[hp[p].list_off + j], h_inl[hp[p].val_off + j], hp[p].val_off + j, -1};
-                std::sort(cv.begin(), cv.end(), [](const Cand &a, const Cand &b) { return a.id < b.id; });
+                if (cv.empty()) continue;
+                std::sort(cv.begin(), cv.end(), [](const Cand &a, const Cand &b) { return a.k < b.k; });
                 int64_t run_max = h_results[p].best_hyp >= 0 ? h_results[p].n_inliers : 0;
                 for (Cand &c : cv) {
-                    if (hp[p].h0 + c.id >= hs[p].est_k) break;
+                    if (hp[p].h0 + c.k >= hs[p].est_k) break;
                     if (c.inl > 0 && c.inl >= run_max) {
-                        c.sel = (int)sel_prob.size();
-                        sel_prob.push_back(p); sel_entry.push_back(c.entry);
+                        c.sel = (int)sel.size();
+                        sel.push_back(RbEntry{p, c.k});
                         sel_prefix.push_back(sel_prefix.back() + hp[p].ntiles);
                         run_max = c.inl;
                     }
                 }
             }
-            const int nsel = (int)sel_prob.size();
+            const int nsel = (int)sel.size();
             if (nsel > 0) {
-                int32_t *d_sp = nullptr, *d_i2 = nullptr, *d_ci = nullptr; int64_t *d_se = nullptr, *d_spre = nullptr;
-                int *d_pc = nullptr; double *d_pe = nullptr, *d_err = nullptr;
+                RbEntry *d_sel = nullptr; int32_t *d_i2 = nullptr, *d_ci = nullptr; int64_t *d_spre = nullptr;
+                int *d_pc = nullptr; double *d_pe = nullptr, *d_err = nullptr, *d_T = nullptr;
                 const int64_t sitems = sel_prefix.back();
-                IBL_CUDA(ibl_alloc(&d_sp, (size_t)nsel, st)); IBL_CUDA(ibl_alloc(&d_se, (size_t)nsel, st));
+                IBL_CUDA(ibl_alloc(&d_sel, (size_t)nsel, st));
                 IBL_CUDA(ibl_alloc(&d_spre, (size_t)nsel + 1, st));
                 IBL_CUDA(ibl_alloc(&d_pc, (size_t)sitems, st)); IBL_CUDA(ibl_alloc(&d_pe, (size_t)sitems, st));
                 IBL_CUDA(ibl_alloc(&d_i2, (size_t)nsel, st)); IBL_CUDA(ibl_alloc(&d_ci, (size_t)nsel, st));
-                IBL_CUDA(ibl_alloc(&d_err, (size_t)nsel, st));
-                IBL_CUDA(cudaMemcpyAsync(d_sp, sel_prob.data(), sizeof(int32_t) * nsel, cudaMemcpyHostToDevice, st));
-                IBL_CUDA(cudaMemcpyAsync(d_se, sel_entry.data(), sizeof(int64_t) * nsel, cudaMemcpyHostToDevice, st));
+                IBL_CUDA(ibl_alloc(&d_err, (size_t)nsel, st)); IBL_CUDA(ibl_alloc(&d_T, (size_t)nsel * 16, st));
+                IBL_CUDA(cudaMemcpyAsync(d_sel, sel.data(), sizeof(RbEntry) * nsel, cudaMemcpyHostToDevice, st));
                 IBL_CUDA(cudaMemcpyAsync(d_spre, sel_prefix.data(), sizeof(int64_t) * (nsel + 1), cudaMemcpyHostToDevice, st));
+                hyp_transform_sel_kernel<<<(unsigned)((nsel + 63) / 64), 64, 0, st>>>(d_probs, d_sel, nsel, d_T);
+                IBL_LAUNCH_CHECK();
                 {
                     double work = 0;
-                    for (int c = 0; c < nsel; ++c) work += 24.0 * hp[sel_prob[c]].n_src + 128.0;
+                    for (int c = 0; c < nsel; ++c) work += 24.0 * hp[sel[c].p].n_src + 128.0;
                     IBL_PROF(IBL_PROF_RANSAC_SCORE, st, work);
-                    ransac_score_batch_kernel<<<(unsigned)sitems, SCORE_THREADS, 0, st>>>(d_probs, d_spre, nsel, d_sp, d_se, d_Ts, max_d,
+                    ransac_score_batch_kernel<<<(unsigned)sitems, SCORE_THREADS, 0, st>>>(d_probs, d_spre, nsel, d_sel, d_T, max_d,
                                                                                         max_d * max_d, d_pc, d_pe);
                     IBL_LAUNCH_CHECK();
                 }
-                ransac_finalize_batch_kernel<<<(unsigned)nsel, FIN_THREADS, 0, st>>>(d_probs, d_spre, d_sp, d_se, d_pc, d_pe, d_Ts, max_d,
+                ransac_finalize_batch_kernel<<<(unsigned)nsel, FIN_THREADS, 0, st>>>(d_probs, d_spre, d_sel, d_pc, d_pe, d_T, max_d,
                                                                                    d_i2, d_err, d_ci);
                 IBL_LAUNCH_CHECK();
                 h_inl2.resize(nsel); h_cinl.resize(nsel); h_err.resize(nsel); h_T.resize((size_t)nsel * 16);
                 IBL_CUDA(cudaMemcpyAsync(h_inl2.data(), d_i2, sizeof(int32_t) * nsel, cudaMemcpyDeviceToHost, st));
                 IBL_CUDA(cudaMemcpyAsync(h_cinl.data(), d_ci, sizeof(int32_t) * nsel, cudaMemcpyDeviceToHost, st));
                 IBL_CUDA(cudaMemcpyAsync(h_err.data(), d_err, sizeof(double) * nsel, cudaMemcpyDeviceToHost, st));
-                for (int c = 0; c < nsel; ++c)
-                    IBL_CUDA(cudaMemcpyAsync(&h_T[(size_t)c * 16], d_Ts + (size_t)sel_entry[c] * 16, sizeof(double) * 16,
-                                             cudaMemcpyDeviceToHost, st));
-                IBL_CUDA(ibl_sync(st));                                                      // sync 3: exact scores
-                ibl_free(d_sp, st); ibl_free(d_se, st); ibl_free(d_spre, st); ibl_free(d_pc, st); ibl_free(d_pe, st);
-                ibl_free(d_i2, st); ibl_free(d_ci, st); ibl_free(d_err, st);
+                IBL_CUDA(cudaMemcpyAsync(h_T.data(), d_T, sizeof(double) * 16 * nsel, cudaMemcpyDeviceToHost, st));
+                IBL_CUDA(ibl_sync(st));                                                      // sync 2: exact scores
+                ibl_free(d_sel, st); ibl_free(d_spre, st); ibl_free(d_pc, st); ibl_free(d_pe, st);
+                ibl_free(d_i2, st); ibl_free(d_ci, st); ibl_free(d_err, st); ibl_free(d_T, st);
             }
             // ---- the ordered rule, per problem (ibl_ransac_run_range's loop body)
             for (int p = 0; p < P && rc == IBL_OK; ++p) {
                 ibl_reg_result_t &r = h_results[p];
                 Host &h = hs[p];
                 for (const Cand &c : cands[p]) {
-                    const int64_t hid = hp[p].h0 + c.id;
+                    const int64_t hid = hp[p].h0 + c.k;
                     if (hid >= h.est_k) break;
                     r.validated++;
                     const int j = c.sel;
@@ -893,19 +825,18 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
                 }
                 cands[p].clear();
             }
-            ibl_free(d_Ts, st); ibl_free(d_inl, st); ibl_free(d_prefix, st);
         }
-        ibl_free(d_ids, st);
+        ibl_free(d_ent, st); ibl_free(d_inl, st);
         if (rc < 0) break;
         for (int p = 0; p < P; ++p) {
             if (hp[p].H == 0) continue;
             hs[p].h0 += hp[p].H;
-            hs[p].cur_block = std::min<int64_t>(hs[p].cur_block * 2, RB_MAX_BLOCK);
+            hs[p].cur_block = std::min<int64_t>(hs[p].cur_block * RB_GROWTH, RB_MAX_BLOCK);
         }
     }
     for (int p = 0; p < P; ++p)
         if (h_results[p].status == 0)
             h_results[p].drawn = std::max<int64_t>(std::min(max_iteration, std::max<int64_t>(hs[p].est_k, 0)), 0);
-    ibl_free(d_probs, st); ibl_free(d_npass, st);
+    ibl_free(d_probs, st); ibl_free(d_n, st);
     return rc;
 }

@@ -130,11 +130,18 @@ def mean3_many(clouds):
 class Grid:
     """Owns an ibl_grid_t; keeps the point tensor alive."""
 
-    def __init__(self, pts, cell, max_cells=0, ring=0, nnfield=0.0, nnfield_voxel=0.0):
+    def __init__(self, pts, cell, max_cells=0, ring=0, nnfield=0.0, nnfield_voxel=0.0, seg=None):
+        """seg (int32 [n] CUDA, optional): per-point cloud id -> a SEGMENTED grid over a concatenation of clouds, on which
+        radius queries only count neighbours of the query's own cloud (ibl_grid_create_segmented)."""
         self.pts = pts
+        self.seg = seg
         self.h = ctypes.c_void_p()
-        check(lib().ibl_grid_create(_p(pts), pts.shape[0], float(cell), int(max_cells), ctypes.byref(self.h), _stream()),
-              "grid_create")
+        if seg is not None:
+            check(lib().ibl_grid_create_segmented(_p(pts), pts.shape[0], _p(seg), float(cell), int(max_cells),
+                                                  ctypes.byref(self.h), _stream()), "grid_create_segmented")
+        else:
+            check(lib().ibl_grid_create(_p(pts), pts.shape[0], float(cell), int(max_cells), ctypes.byref(self.h), _stream()),
+                  "grid_create")
         if ring:
             check(lib().ibl_grid_build_ringfield(self.h, int(ring), _stream()), "ringfield")
         if nnfield:

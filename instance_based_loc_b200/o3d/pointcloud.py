@@ -92,6 +92,46 @@ def _as_dev(v):
     return K.to_dev(np.asarray(v, dtype=np.float64).reshape(-1, 3))
 
 
+def remove_radius_outlier_many(clouds, nb_points, radius):
+    """``[c.remove_radius_outlier(nb_points, radius)[0] for c in clouds]`` (A.2) with ONE grid build, ONE count kernel and
+    ONE compaction for all clouds: the clouds are concatenated under a segmented grid whose radius query only counts
+    neighbours of the query's own cloud, so every keep flag is the one the cloud's own grid gives.  The per-mask filters of
+    a frame (utils/depth_utils.py:85-88; object_memory.py:992-998) go from two host round trips per cloud to three per
+    frame."""
+    if nb_points < 1 or radius <= 0:
+        raise RuntimeError("Illegal input parameters, number of points and radius must be positive")
+    live = [i for i, c in enumerate(clouds) if c.n() > 0]
+    out = [PointCloud() for _ in clouds]
+    if not live:
+        return out
+    if len(live) == 1:
+        out[live[0]] = clouds[live[0]].remove_radius_outlier(nb_points, radius)[0]
+        return out
+    dev = clouds[live[0]]._p.device
+    sizes = [clouds[i].n() for i in live]
+    pts = torch.cat([clouds[i]._p for i in live]).contiguous()
+    colored = all(clouds[i].has_colors() for i in live)
+    cols = torch.cat([clouds[i]._c for i in live]).contiguous() if colored else None
+    seg = torch.repeat_interleave(torch.arange(len(live), dtype=torch.int32, device=dev),
+                                  torch.as_tensor(sizes, device=dev), output_size=int(sum(sizes)))
+    grid = K.Grid(pts, radius * 1.001, seg=seg)
+    keep = K.radius_outlier_mask(grid, radius, nb_points)
+    ends = torch.as_tensor(np.cumsum(sizes) - 1, device=dev)
+    kept = torch.cumsum(keep, dim=0, dtype=torch.int64)[ends].cpu().numpy()          # survivors up to the end of every cloud
+    p2, c2, _, _ = K.select_rows(keep, pts, cols, None)
+    a = 0
+    for i, b in zip(live, kept.tolist()):
+        if colored:
+            out[i] = PointCloud.from_tensors(p2[a:b], c2[a:b], spacing=clouds[i]._spacing)
+        else:                                                   # mixed: colours stay with the clouds that have them
+            out[i] = PointCloud.from_tensors(p2[a:b], None, spacing=clouds[i]._spacing)
+        a = b
+    if not colored and any(clouds[i].has_colors() for i in live):
+        for i in live:                                          # rare mixed case: fall back to the per-cloud filter
+            out[i] = clouds[i].remove_radius_outlier(nb_points, radius)[0]
+    return out
+
+
 class PointCloud:
     def __init__(self, points=None):
         self._p = None
@@ -99,14 +139,17 @@ class PointCloud:
         self._n = None
         self._grids = {}
         self._color_grad = None
+        self._spacing = None          # mean point spacing, a PERFORMANCE hint for sizing search grids (never affects results)
+        self._knn_hint = None         # (radius, max_nn) of a larger search that will follow on this cloud (see knn)
         if points is not None:
             self.points = points
 
     # ------------------------------------------------------------------ storage
     @staticmethod
-    def from_tensors(p, c=None, n=None):
+    def from_tensors(p, c=None, n=None, spacing=None):
         r = PointCloud()
         r._p, r._c, r._n = p, c, n
+        r._spacing = spacing
         return r
 
 
@@ -166,6 +209,14 @@ class PointCloud:
     def __iadd__(self, o):
         if o.is_empty():
             return self
+        # spacing hint of the union: areas add (area ~ n * spacing^2)
+        if self.is_empty():
+            self._spacing = o._spacing
+        elif self._spacing and o._spacing:
+            n1, n2 = self.n(), o.n()
+            self._spacing = float(((n1 * self._spacing ** 2 + n2 * o._spacing ** 2) / (n1 + n2)) ** 0.5)
+        else:
+            self._spacing = None
         if (self.is_empty() or self.has_normals()) and o.has_normals():
             self._n = o._n if self.is_empty() else torch.cat([self._n, o._n])
         else:
@@ -219,7 +270,7 @@ class PointCloud:
     def _select_mask(self, keep, want_index=False):
         p, c, nn, oi = K.select_rows(keep, self._p, self._c if self.has_colors() else None,
                                      self._n if self.has_normals() else None, want_index=want_index)
-        return PointCloud.from_tensors(p, c, nn), oi
+        return PointCloud.from_tensors(p, c, nn, spacing=self._spacing), oi
 
     def remove_radius_outlier(self, nb_points, radius, print_progress=False):
         """A.2: keep i iff #{j: d2(i,j) < r^2} (self included) > nb_points; order preserved."""
@@ -282,22 +333,46 @@ class PointCloud:
         return g
 
     def knn(self, radius, max_nn, want_d2=True):
+        """Hybrid search of every point among the cloud's own points -> (idx int32 [n, stride], d2 | None, cnt int32 [n]);
+        row i holds cnt[i] neighbours in ascending (d2, index) order, ``stride = idx.shape[1] >= max_nn``.
+
+        A search is a prefix of every LARGER search on the same cloud: the max_nn nearest within ``radius`` are the first
+        entries of the k' >= max_nn nearest within r' >= radius that lie inside ``radius`` (same order, same tie rule).
+        So when a larger search with distances is already cached -- or announced through ``_knn_hint``, as
+        downsample_and_compute_fpfh does for its FPFH search before it estimates the normals -- the result is derived
+        from it (one comparison kernel) instead of searched again: normals (0.1 / 30) and FPFH (0.25 / 100) share one
+        search per cloud."""
         r = radius if np.isfinite(radius) else 1e30
+        last = self._grids.get("knn_last")
+        hint = self._knn_hint
+        if last is None and hint is not None and hint[0] >= r and hint[1] >= max_nn and (hint[0], hint[1]) != (r, max_nn):
+            self._knn_hint = None
+            self.knn(hint[0], hint[1], want_d2=True)                   # the larger search, cached below
+            last = self._grids.get("knn_last")
+        if last is not None and last[0] >= r and last[1] >= max_nn and self.n() > 0:
+            R, Kmax, idx, d2, cnt = last
+            if (R, Kmax) == (r, max_nn):
+                return idx, (d2 if want_d2 else None), cnt
+            sub = (d2[:, :max_nn] < r * r).sum(dim=1).to(torch.int32)    # d2 ascending, +inf beyond cnt
+            return idx, (d2 if want_d2 else None), sub
         if self.n() == 0:
             cell = r
         else:
-            # the spacing estimate costs a probe grid: keep it with the grids (dropped on any mutation), so the
-            # normals / FPFH / colour-gradient searches of one cloud share it
-            sp = self._grids.get("spacing")
+            # spacing hint: carried from the back-projection (depth / focal length) through filters, unions and rigid
+            # moves; without one it is estimated with a probe grid, kept with the grids (dropped on any mutation)
+            sp = self._spacing or self._grids.get("spacing")
             if sp is None:
                 sp = self._grids["spacing"] = K.surface_spacing(self._p, min(r / 4.0, 0.05))
             cell = K.knn_cell_from_spacing(sp, max_nn, r)
-        return K.knn_hybrid(self.grid(cell), radius, max_nn, want_d2=want_d2)
+        out = K.knn_hybrid(self.grid(cell), radius, max_nn, want_d2=want_d2)
+        if want_d2:
+            self._grids["knn_last"] = (r, max_nn) + tuple(out)
+        return out
 
     # ------------------------------------------------------------------ copy / pickle
     def __deepcopy__(self, memo):
         cl = lambda t: None if t is None else t.clone()  # noqa: E731
-        return PointCloud.from_tensors(cl(self._p), cl(self._c), cl(self._n))
+        return PointCloud.from_tensors(cl(self._p), cl(self._c), cl(self._n), spacing=self._spacing)
 
     def __getstate__(self):
         h = lambda t: None if t is None else t.cpu().numpy()  # noqa: E731

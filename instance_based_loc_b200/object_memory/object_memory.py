@@ -26,7 +26,7 @@ from scipy.spatial.transform import Rotation
 
 from .. import kernels as K
 from ..o3d import registration as _reg
-from ..o3d.pointcloud import PointCloud
+from ..o3d.pointcloud import PointCloud, remove_radius_outlier_many
 from ..utils.depth_utils import DEFAULT_OUTLIER_REMOVAL_CONFIG, get_mask_coloured_pointclouds_from_depth, transform_pointcloud
 from ..utils.fpfh_register import downsample_and_compute_fpfh, evaluate_transform, register_point_clouds
 from ..utils.similarity_volume import SimVolume
@@ -466,6 +466,7 @@ class ObjectMemory():
                     _reg._nn_grid(tgt, fpfh_voxel_size * local_dist_factor)
                     if tgt.has_colors():
                         _reg.ensure_color_gradient(tgt, fpfh_voxel_size * local_dist_factor)
+                    tgt._grids.pop("knn_last", None)       # the shared neighbour lists (~1.2 KB per point) are not needed again
                 except K.IblError:
                     raise                                  # a device / ABI error is not Open3D's "no normals" case
                 except Exception:
@@ -668,9 +669,8 @@ class ObjectMemory():
         info["assignments"] = copy.deepcopy(assn_data)
 
         # second outlier removal on every detected cloud (:992-998)
-        detected_pointclouds = [obj.remove_radius_outlier(nb_points=outlier_removal_config["radius_nb_points"],
-                                                          radius=outlier_removal_config["radius"])[0]
-                                for obj in detected_pointclouds]
+        detected_pointclouds = remove_radius_outlier_many(detected_pointclouds, outlier_removal_config["radius_nb_points"],
+                                                          outlier_removal_config["radius"])
         all_detected_pcd = PointCloud()
         for pcd in detected_pointclouds:                                       # :1010-1016
             all_detected_pcd = all_detected_pcd + pcd
@@ -766,7 +766,7 @@ class ObjectMemory():
                 arr = K.reg_problems(specs)
                 max_it = 4000000 if _reg.ransac_max_iteration is None else int(_reg.ransac_max_iteration)   # :119
                 rr = K.ransac_run_batch(arr, max_it, 0.99, max_d_r, edge_thr=0.9, use_checkers=True,
-                                        early_exit=bool(_reg.ransac_early_exit), block=_reg.ransac_block)
+                                        early_exit=bool(_reg.ransac_early_exit), block=_reg.ransac_batch_block)
                 for (plan, g), r in zip(live, rr):
                     g["ransac"] = {k: r[k] for k in ("drawn", "validated", "best_hyp", "n_corres", "n_inliers", "err2")}
                     g["ransac_T"] = r["T"]

@@ -11,7 +11,7 @@ import torch
 from scipy.spatial.transform import Rotation
 
 from .. import kernels as K
-from ..o3d.pointcloud import PointCloud
+from ..o3d.pointcloud import PointCloud, remove_radius_outlier_many
 
 DEFAULT_OUTLIER_REMOVAL_CONFIG = \
     {
@@ -68,14 +68,22 @@ def _clouds_from_masks(depth_image, rgb_image, masks, fx, fy, outlier_removal_co
     rgb = _rgb_to_dev(rgb_image)
     m = _masks_to_dev(masks, H, W)
     pts, cols, offs = K.backproject_masks(d, rgb, m, fx, fy)
-    out = []
-    for i in range(len(offs) - 1):
-        a, b = offs[i], offs[i + 1]
-        pc = PointCloud.from_tensors(pts[a:b], cols[a:b] if cols is not None else None)
-        if outlier_removal_config is not None:
-            pc, _ = pc.remove_radius_outlier(nb_points=outlier_removal_config["radius_nb_points"],
-                                             radius=outlier_removal_config["radius"])
-        out.append(pc)
+    # point spacing of every mask's cloud ~ mean depth / focal length: a performance hint for the search grids built on
+    # these clouds later (one small read-back per frame instead of a probe grid per cloud)
+    spacing = [None] * (len(offs) - 1)
+    if pts.shape[0]:
+        cz = torch.cumsum(pts[:, 2], dim=0)
+        ends = torch.as_tensor([max(o - 1, 0) for o in offs], device=pts.device)
+        zs = cz[ends].cpu().numpy()
+        for i in range(len(offs) - 1):
+            cnt = offs[i + 1] - offs[i]
+            if cnt > 0:
+                zsum = zs[i + 1] - (zs[i] if offs[i] > 0 else 0.0)
+                spacing[i] = float(max(zsum / cnt, 1e-3) / max(abs(float(fx)), 1e-9))
+    out = [PointCloud.from_tensors(pts[offs[i]:offs[i + 1]], cols[offs[i]:offs[i + 1]] if cols is not None else None,
+                                   spacing=spacing[i]) for i in range(len(offs) - 1)]
+    if outlier_removal_config is not None:                     # :41 / :87, every mask's cloud on its own -- one batched pass
+        out = remove_radius_outlier_many(out, outlier_removal_config["radius_nb_points"], outlier_removal_config["radius"])
     return out
 
 

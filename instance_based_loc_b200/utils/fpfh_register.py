@@ -43,6 +43,8 @@ def get_transformation(source, target):
 def downsample_and_compute_fpfh(pcd, voxel_size):
     """:86-98.  NB the reference does NOT downsample (deep copy only); voxel_size only scales the radii."""
     pcd_down = copy.deepcopy(pcd)
+    # the FPFH search (5 vs / 100) contains the normal search (2 vs / 30): announce it, so ONE search serves both
+    pcd_down._knn_hint = (voxel_size * 5, 100)
     radius_normal = voxel_size * 2
     pcd_down.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(radius=radius_normal, max_nn=30))
     radius_feature = voxel_size * 5

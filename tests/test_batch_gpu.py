@@ -181,3 +181,60 @@ def test_feature_match_packed_equals_generic(K, na, nb):
     # a source far outside the pack's fp16 range raises the flag (the Python mirror then takes the general path)
     _, _, flag = K.feature_match_packed(A * 1e6, pack)
     assert int(flag.item()) != 0
+
+
+def test_shared_knn_search_equals_separate_searches(K):
+    """normals (Hybrid 0.1 / 30), colour gradients (0.15 / 30) and FPFH (0.25 / 100) derived from ONE 0.25 / 100 search are
+    the neighbour lists of their own searches: same counts, same indices in the same order."""
+    from instance_based_loc_b200.o3d.pointcloud import PointCloud
+    p, c = surface_cloud(20000, 3)
+    a, b = PointCloud(p), PointCloud(p)
+    a.colors, b.colors = c, c
+    big = a.knn(0.25, 100, want_d2=True)
+    for r, k in ((0.1, 30), (0.15, 30), (0.25, 100), (0.02, 10)):
+        idx, _, cnt = a.knn(r, k, want_d2=False)                      # derived
+        b._grids.pop("knn_last", None)
+        ridx, rd2, rcnt = b.knn(r, k, want_d2=True)                   # searched
+        b._grids.pop("knn_last", None)
+        assert np.array_equal(cnt.cpu().numpy(), rcnt.cpu().numpy())
+        got, ref, cn = idx.cpu().numpy(), ridx.cpu().numpy(), rcnt.cpu().numpy()
+        mask = np.arange(k)[None, :] < cn[:, None]
+        assert np.array_equal(got[:, :k][mask], ref[mask])
+    # and through the reference-shaped entry point: hint -> one search, identical normals and FPFH
+    from instance_based_loc_b200.utils.fpfh_register import downsample_and_compute_fpfh
+    from instance_based_loc_b200.o3d import KDTreeSearchParamHybrid
+    from instance_based_loc_b200.o3d import registration as reg
+    d1, f1 = downsample_and_compute_fpfh(a, 0.05)
+    d2 = PointCloud(p)
+    d2.estimate_normals(KDTreeSearchParamHybrid(radius=0.1, max_nn=30))
+    d2._grids.pop("knn_last", None)
+    f2 = reg.compute_fpfh_feature(d2, KDTreeSearchParamHybrid(radius=0.25, max_nn=100))
+    assert np.array_equal(np.asarray(d1.normals), np.asarray(d2.normals))
+    assert np.array_equal(f1.data, f2.data)
+
+
+def test_remove_radius_outlier_many_equals_per_cloud(K):
+    """one segmented grid + one count + one compaction for several clouds == the per-cloud filter (A.2), including clouds
+    that touch or overlap each other, an empty one and a cloud without colours in the batch."""
+    from instance_based_loc_b200.o3d.pointcloud import PointCloud, remove_radius_outlier_many
+    rng = np.random.default_rng(4)
+    clouds = []
+    for k, n in enumerate((3000, 1200, 0, 5000, 40)):
+        p, c = surface_cloud(max(n, 1), 10 + k, scale=0.4)
+        p = p[:n] + np.array([0.25 * k, 0.0, 0.0])               # neighbours closer than the radius: clouds interpenetrate
+        p = np.concatenate([p, rng.uniform(-1, 1, (n // 20, 3))]) if n else p
+        pc = PointCloud(p)
+        if n:
+            pc.colors = np.concatenate([c[:n], rng.random((n // 20, 3))])
+        clouds.append(pc)
+    for nb in (8, 12):
+        got = remove_radius_outlier_many(clouds, nb, 0.05)
+        for c, g in zip(clouds, got):
+            ref = c.remove_radius_outlier(nb, 0.05)[0] if c.n() else PointCloud()
+            assert g.n() == ref.n()
+            if ref.n():
+                assert np.array_equal(np.asarray(g.points), np.asarray(ref.points))
+                assert np.array_equal(np.asarray(g.colors), np.asarray(ref.colors))
+    clouds[1] = PointCloud(np.asarray(clouds[1].points))              # no colours: the mixed case
+    got = remove_radius_outlier_many(clouds, 8, 0.05)
+    assert got[1].n() == clouds[1].remove_radius_outlier(8, 0.05)[0].n() and not got[1].has_colors() and got[0].has_colors()

@@ -33,6 +33,11 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# torch's own caching allocator grows by cudaMalloc whenever a frame needs a block size it has not cached for that stream;
+# with several frame streams that happened every few steps and stalled whole steps (measured: 150-220 ms steps with
+# occasional 400-600 ms ones).  The stream-ordered allocator shares the driver pool libibl.so already uses (release
+# threshold = max), so after warm-up nothing on the path calls cudaMalloc.  Must be set before torch touches CUDA.
+os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "backend:cudaMallocAsync")
 
 from instance_based_loc_b200 import workloads as WL  # noqa: E402
 
@@ -307,6 +312,7 @@ def run_frames(args, cfg):
     t_setup = time.perf_counter() - t_setup
     cursor = {"i": 0}
     log = {"on": False, "rows": []}
+    trace = bool(os.environ.get("IBL_BENCH_TRACE"))
 
     def step(host_inputs, nworkers=None):
         flush.zero_()                                   # L2 flush between iterations (126 MB L2 < 256 MiB)
@@ -316,7 +322,22 @@ def run_frames(args, cfg):
             batch = [{k: v.to(dev, non_blocking=True) for k, v in pinned[i].items()} for i in idx]
         else:
             batch = [resident[i] for i in idx]
+        t_call = time.perf_counter()
         res = om.localise_batch(batch, workers=workers if nworkers is None else nworkers, **kw)
+        if trace:
+            ms_ = torch.cuda.memory_stats()
+            sc_ = K.scratch_stats()
+            print(f"[trace] torch segments={ms_.get('num_device_alloc', 0)} frees={ms_.get('num_device_free', 0)} "
+                  f"reserved={ms_.get('reserved_bytes.all.current', 0) >> 20} MiB; pool reserved={sc_['reserved'] >> 20} MiB "
+                  f"used_high={sc_['used_high'] >> 20} MiB", file=sys.stderr, flush=True)
+            print(f"[trace] step host_inputs={bool(host_inputs)} idx0={idx[0]} call_ms={(time.perf_counter() - t_call) * 1e3:.1f} "
+                  f"timing={getattr(om, 'last_batch_timing', None)}", file=sys.stderr, flush=True)
+            for i, r in zip(idx, res):
+                s1 = r[2].get("stage1_ms", (0, 0))
+                if s1[0] + s1[1] > 60:
+                    print(f"[trace]   slow frame {i}: plan {s1[0]:.0f} ms, features+matching {s1[1]:.0f} ms, regs "
+                          f"{[(g['n_source'], g['n_target'], g['ransac'].get('n_corres')) for g in r[2]['registrations']]}",
+                          file=sys.stderr, flush=True)
         out = torch.from_numpy(np.stack([r[0] for r in res])).to(dev)
         if world > 1:                                   # the only traffic that crosses NVLink: 56 B per frame
             dist.all_gather(gathered, out)
@@ -471,7 +492,7 @@ def run_frames(args, cfg):
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 56,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "launches_per_frame": launches / max(B * args.steps, 1), "clocks": clk,
-            "ransac": ransac, "gt": gt, "memory_cache_hit_rate": hit_warm,
+            "ransac": ransac, "gt": gt, "memory_cache_hit_rate": hit_warm, "memory_cache": om.cache_info(),
             "cold": {"value": B * cold_steps * world / (ms_cold / 1e3), "unit": "frames/s", "frames_per_rank": B * cold_steps,
                      "memory_cache_hit_rate": hit_cold,
                      "note": "first pass over the pool with the per-assignment memory-side caches (target normals / FPFH / "

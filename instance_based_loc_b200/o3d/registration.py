@@ -21,7 +21,7 @@ from .pointcloud import DeviceVec, PointCloud
 ransac_seed = 0                  # seed of the counter-based sample stream
 ransac_sampler = None            # optional callable (C, H) -> int32 [H,3] host array (overrides the seed)
 ransac_block = 1 << 14           # hypotheses checked per device block before the ordered host scan
-ransac_batch_block = 1 << 16     # first block per problem of the batched RANSAC (grows x4 per round up to 2^20)
+ransac_batch_block = int(os.environ.get("IBL_RANSAC_BATCH_BLOCK", 1 << 14))     # first block per problem of the batched RANSAC (grows x4 per round up to 2^20; 2^14 measured best on configs[1])
 ransac_max_iteration = None      # benchmark knob: overrides criteria.max_iteration (configs[2]/[4]: a FIXED hypothesis count)
 ransac_early_exit = True         # benchmark knob: False disables the adaptive stop (every hypothesis of the stream is drawn)
 last_ransac_info = {}            # most recent RANSAC of ANY thread (kept for tools); per-thread copy: last_info()

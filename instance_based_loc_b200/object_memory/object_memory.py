@@ -411,6 +411,13 @@ class ObjectMemory():
                 self._cache = {"assn": {}}
             return self._cache
 
+    def cache_info(self):
+        """-> entries / bytes of the per-assignment memory-side cache and its lookup statistics."""
+        with self._lock:
+            c = self._memory_cache()["assn"]
+            return dict(self.cache_stats, entries=len(c), bytes=int(sum(e[3] for e in c.values())),
+                        budget_bytes=int(self.assignment_cache_bytes))
+
     def clear_assignment_cache(self):
         """Drop the per-assignment-tuple memory-side state (centred union cloud, normals, FPFH, NN fields, colour
         gradients); per-object clouds, the embedding bank and the all-memory search grid stay."""
@@ -443,6 +450,24 @@ class ObjectMemory():
                 c["all"] = allp
             return c["all"]
 
+    # Per-assignment memory-side state is kept under a BYTE budget with least-recently-used eviction: an entry is ~1 KB per
+    # memory point (union cloud with normals / colours / gradients, FPFH rows, the matcher's packed operands) plus its two
+    # exact-NN candidate fields -- 50-150 MB for a 50 k-point union.  A frame stream of one environment keeps meeting the same
+    # tuples of co-visible objects; how many of them stay resident is a deployment choice (HBM is 180 GB).
+    assignment_cache_bytes = 96 << 30
+
+    @staticmethod
+    def _assn_entry_bytes(pcd, feats):
+        n = pcd.n()
+        b = n * 24 * 2                                         # union points + colours
+        if feats is not None:
+            tgt, f = feats
+            b += n * (24 * 3 + 264 + 448 + 144 + 16 + 40)      # normals, gradients, a spare row; FPFH; packs; fp32 rows; grid rows
+            for g in tgt._grids.values():
+                if isinstance(g, K.Grid):
+                    b += g.nnfield_bytes
+        return int(b)
+
     def _chosen_memory(self, m_indices, fpfh_voxel_size, global_dist_factor, local_dist_factor):
         """centred union of the chosen memory clouds with everything register_point_clouds derives from it:
         normals + FPFH, the RANSAC / ICP search structures and the coloured-ICP gradients."""
@@ -451,31 +476,40 @@ class ObjectMemory():
         with self._lock:
             c = self._memory_cache()["assn"]
             self.cache_stats["lookups"] += 1
-            if key not in c:
-                self.cache_stats["misses"] += 1
-                pcd = PointCloud()
-                for m_index in m_indices:
-                    pcd = pcd + self.memory[m_index].pointcloud
-                mean = pcd.get_center()
-                pcd.translate(-mean)
-                try:
-                    feats = downsample_and_compute_fpfh(pcd, fpfh_voxel_size)
-                    feats[1].pack()                        # matcher operands of the memory side, packed once
-                    tgt = feats[0]
-                    _reg._nn_grid(tgt, fpfh_voxel_size * global_dist_factor)
-                    _reg._nn_grid(tgt, fpfh_voxel_size * local_dist_factor)
-                    if tgt.has_colors():
-                        _reg.ensure_color_gradient(tgt, fpfh_voxel_size * local_dist_factor)
-                    tgt._grids.pop("knn_last", None)       # the shared neighbour lists (~1.2 KB per point) are not needed again
-                except K.IblError:
-                    raise                                  # a device / ABI error is not Open3D's "no normals" case
-                except Exception:
-                    feats = None                           # register_point_clouds then takes its own fallback branch
-                torch.cuda.current_stream().synchronize()
-                if len(c) > 512:
-                    c.pop(next(iter(c)))
-                c[key] = (pcd, mean, feats)
-            return c[key]
+            hit = c.get(key)
+            if hit is not None:
+                c[key] = c.pop(key)                            # most recently used last (dicts keep insertion order)
+                return hit[:3]
+            self.cache_stats["misses"] += 1
+            pcd = PointCloud()
+            for m_index in m_indices:
+                pcd = pcd + self.memory[m_index].pointcloud
+            mean = pcd.get_center()
+            pcd.translate(-mean)
+            try:
+                feats = downsample_and_compute_fpfh(pcd, fpfh_voxel_size)
+                feats[1].pack()                            # matcher operands of the memory side, packed once
+                tgt = feats[0]
+                g_r = _reg._nn_grid(tgt, fpfh_voxel_size * global_dist_factor)
+                g_i = _reg._nn_grid(tgt, fpfh_voxel_size * local_dist_factor)
+                if tgt.has_colors():
+                    _reg.ensure_color_gradient(tgt, fpfh_voxel_size * local_dist_factor)
+                # what later frames need from the search structures are the two NN-field grids only: the k-NN grid (up to
+                # 2^24 cells) and the shared neighbour lists (~1.2 KB per point) served the features and go
+                tgt._grids = {k: g for k, g in tgt._grids.items() if g is g_r or g is g_i}
+                pcd._p, pcd._c = tgt._p, tgt._c            # the copy the features were computed on holds the same values
+            except K.IblError:
+                raise                                      # a device / ABI error is not Open3D's "no normals" case
+            except Exception:
+                feats = None                               # register_point_clouds then takes its own fallback branch
+            torch.cuda.current_stream().synchronize()
+            nbytes = self._assn_entry_bytes(pcd, feats)
+            used = sum(e[3] for e in c.values())
+            while c and used + nbytes > self.assignment_cache_bytes:
+                used -= c.pop(next(iter(c)))[3]            # least recently used first
+                self.cache_stats["evictions"] = self.cache_stats.get("evictions", 0) + 1
+            c[key] = (pcd, mean, feats, nbytes)
+            return c[key][:3]
 
     # ------------------------------------------------------------------------------------------ localise
     def closest_similarities(self, detected_embs):
@@ -552,9 +586,12 @@ class ObjectMemory():
             if not batched:
                 pose, assn = self.localise_arrays(fr["rgb"], fr["depth"], fr["masks"], fr["embs"], **kw)
                 return pose, assn, self._tls.info
+            t0 = time.perf_counter()
             plan = self._plan_arrays(fr["rgb"], fr["depth"], fr["masks"], fr["embs"], **kw)
+            t1 = time.perf_counter()
             if plan.get("registrations") is not None:
                 self._prepare_registrations(plan)
+            plan["info"]["stage1_ms"] = ((t1 - t0) * 1e3, (time.perf_counter() - t1) * 1e3)   # (plan, features + matching)
             return plan
 
         if workers <= 1 or len(frames) <= 1:
@@ -744,6 +781,12 @@ class ObjectMemory():
         probs = [(plan, g) for plan in plans for g in plan["registrations"]]
         if not probs:
             return
+        if not getattr(self._tls, "stage2_reserved", False) and self.scratch_bytes_per_stream and \
+                not os.environ.get("IBL_NO_RESERVE"):
+            # the batched stage's temporaries (entry lists of up to 2^20 hypotheses per problem, moved clouds, partials)
+            # come from the stream-ordered pool: map this stream's share once instead of growing it step by step
+            K.reserve_scratch(self.scratch_bytes_per_stream)
+            self._tls.stage2_reserved = True
         all_memory_pcd = self._all_memory_pcd()
         by_cfg = {}
         for plan, g in probs:

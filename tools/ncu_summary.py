@@ -22,7 +22,79 @@ FULL_METRICS = [
     "smsp__issue_active.avg.pct_of_peak_sustained_active",
     "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
     "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+    "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_bytes.sum", "l1tex__t_bytes.sum",
+    "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
+    "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_tmem.sum",
+    "sm__inst_executed_pipe_tensor.sum",
 ]
+
+# extra metrics to pass to ncu beside --set full (comma-joined): the pipes the path is actually bound by
+EXTRA_METRICS = ("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active,"
+                 "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active,"
+                 "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active,sm__inst_executed_pipe_tmem.sum,"
+                 "sm__inst_executed_pipe_tensor.sum,lts__t_bytes.sum,l1tex__t_bytes.sum,"
+                 "lts__throughput.avg.pct_of_peak_sustained_elapsed,l1tex__throughput.avg.pct_of_peak_sustained_elapsed,"
+                 "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed")
+
+# kernel function -> bench.py kernel group (csrc IBL_PROF tags)
+GROUPS = [("feat_tc_kernel", "feature_nn"), ("feat_tc_", "feature_nn"), ("knn_kernel", "knn"), ("fpfh_kernel", "fpfh"),
+          ("spfh_kernel", "spfh"), ("normals_kernel", "normals"), ("ransac_count", "ransac_score"), ("ransac_score", "ransac_score"),
+          ("ransac_finalize", "ransac_score"), ("ransac_check", "ransac_check"), ("colored_step", "icp_reduce"),
+          ("reduceK", "icp_reduce"), ("nn_score", "nn_score"), ("score_final", "nn_score"), ("radius_count", "radius_count"),
+          ("cellid", "grid_build"), ("gather_sorted", "grid_build"), ("bbox", "grid_build"), ("DeviceRadixSort", "grid_build"),
+          ("DeviceScan", "grid_build"), ("nf_", "grid_build"), ("seqsum3", "mean3"), ("simvol", "simvolume"),
+          ("cosine", "cosine_segmax"), ("backproject", "backproject"), ("voxel", "voxel"), ("color_gradient", "color_gradient")]
+
+
+def bounds(path, out_json="profiles/r02_kernel_bounds.json"):
+    """Per kernel of a --set full capture: which unit it is bound by.  The candidates are the percent-of-peak counters of
+    DRAM, L2, L1/TEX, the fp64 pipe, the tensor pipe and instruction issue; the largest one names the bound, and anything
+    whose largest counter is below 35 % is latency-bound (dependent loads / small grids).  Writes the table bench.py merges
+    into its `kernels` object (per kernel group: the group's heaviest kernel)."""
+    import json
+    txt = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(txt)))
+    hdr, units = rows[0], rows[1]
+    col = {m: hdr.index(m) for m in hdr}
+    kn = hdr.index("Kernel Name")
+
+    def val(r, m):
+        try:
+            return float(r[col[m]].replace(",", ""))
+        except Exception:
+            return 0.0
+    cand = {"hbm": "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "l2": "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+            "l1": "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "fp64": "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
+            "tensor": "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+            "issue": "smsp__issue_active.avg.pct_of_peak_sustained_active"}
+    per_kernel, groups = [], {}
+    for r in rows[2:]:
+        name = re.sub(r"\(.*", "", r[kn])[:70]
+        pct = {k: val(r, m) for k, m in cand.items() if m in col}
+        top = max(pct, key=pct.get) if pct else "latency"
+        bound = top if pct.get(top, 0) >= 35.0 else "latency"
+        us = val(r, "gpu__time_duration.sum") * {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(units[col["gpu__time_duration.sum"]], 1.0)
+        rec = {"kernel": name, "us": round(us, 1), "grid": int(val(r, "launch__grid_size")), "regs": int(val(r, "launch__registers_per_thread")),
+               "bound": bound, "pct_of_peak": {k: round(v, 1) for k, v in pct.items()},
+               "warps_active_pct": round(val(r, "sm__warps_active.avg.pct_of_peak_sustained_active"), 1),
+               "dram_bytes": val(r, "dram__bytes_read.sum") + val(r, "dram__bytes_write.sum")}
+        per_kernel.append(rec)
+        for pat, grp in GROUPS:
+            if pat in name:
+                if grp not in groups or groups[grp]["_us"] < us:
+                    groups[grp] = {"bound": bound, "frac_of_that_peak": round(pct.get(top, 0) / 100.0, 3), "bound_kernel": name,
+                                   "bound_counters_pct": rec["pct_of_peak"], "_us": us}
+                break
+    for g in groups.values():
+        g.pop("_us")
+    print(f"{'kernel':60s} {'us':>9s} {'grid':>7s} {'bound':>8s}  " + " ".join(f"{k:>6s}" for k in cand))
+    for rec in sorted(per_kernel, key=lambda x: -x["us"]):
+        print(f"{rec['kernel'][:60]:60s} {rec['us']:9.1f} {rec['grid']:7d} {rec['bound']:>8s}  " +
+              " ".join(f"{rec['pct_of_peak'].get(k, 0):6.1f}" for k in cand))
+    json.dump(groups, open(out_json, "w"), indent=1, sort_keys=True)
+    json.dump(per_kernel, open(out_json.replace(".json", "_per_kernel.json"), "w"), indent=1)
+
 
 
 def launches(path, header=""):
@@ -110,7 +182,11 @@ def traffic(specs):
 
 
 if __name__ == "__main__":
-    if sys.argv[1] == "traffic":
+    if sys.argv[1] == "bounds":
+        bounds(*sys.argv[2:4])
+    elif sys.argv[1] == "extra-metrics":
+        print(EXTRA_METRICS)
+    elif sys.argv[1] == "traffic":
         traffic(sys.argv[2:])
     elif sys.argv[1] == "launches":
         launches(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "")

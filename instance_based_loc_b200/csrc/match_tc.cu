@@ -38,7 +38,8 @@
 #define TC_TILE_BYTES (16 * TC_SBO) // 28,672
 #define TC_STAGES 4
 #define TC_RANGE 1024.0             // rows are scaled by a power of two so that |value| <= TC_RANGE (fp16 range / precision)
-#define TC_THREADS 192
+#define TC_EPI_WARPS 16            // epilogue warps: 4 per TMEM lane quarter, each owning 32 of a tile's 128 columns
+#define TC_THREADS (32 * (TC_EPI_WARPS + 2))   // + bulk-copy producer warp + MMA issuer warp
 #define TC_CHUNK 64                 // band candidates per pool chunk (rows chain as many chunks as they need)
 #define TC_SMEM (TC_TILE_BYTES * (1 + TC_STAGES) + 256)
 
@@ -320,7 +321,7 @@ __device__ __forceinline__ void tc_push(TcRowState &st, const TcPool &pool, int 
 // independent FMNMX, not a 32-deep dependent chain), then record every column inside the band E below the maximum SO
 // FAR.  The running maximum only grows, so the final band [m_final - E, m_final] is a subset of what gets recorded; the
 // surplus (targets that were near-records when they streamed by) only costs exact evaluations later.
-__device__ __forceinline__ void tc_band_chunk(const float *v, float &m, float E, int tb, TcRowState &rs, const TcPool &pool,
+__device__ __forceinline__ void tc_band_chunk(const float *v, int *row_max_key, float E, int tb, TcRowState &rs, const TcPool &pool,
                                               int row, const double *__restrict__ fa_q, const double *__restrict__ fb) {
     float t[16];
 #pragma unroll
@@ -331,7 +332,11 @@ __device__ __forceinline__ void tc_band_chunk(const float *v, float &m, float E,
         for (int c = 0; c < w; ++c) t[c] = fmaxf(t[c], t[c + w]);
     }
     const float cm = t[0];
-    m = fmaxf(m, cm);
+    // the query row's running maximum is shared by the four threads that own its four column groups (shared memory,
+    // ordered-int atomicMax): whatever the others have already seen tightens this thread's band too.  Any value that has
+    // been a maximum so far is <= the final maximum, so the recorded set stays a superset of the final band.
+    const int old = atomicMax(row_max_key, f2key(cm));
+    const float m = fmaxf(key2f(old), cm);
     const float r = __fsub_rd(m, E);                      // E = -inf for rows past the end: r = +inf, nothing is recorded
     if (cm >= r) {
         // Hit mask with static register indices, then a short loop that the lanes of the warp run in lock step.
@@ -348,6 +353,14 @@ __device__ __forceinline__ void tc_band_chunk(const float *v, float &m, float E,
 
 // MODE 0: dump s' to dump[q][ld] (debug).  MODE 1: running row maximum + band candidates in one pass.
 // grid = (query tiles, splits); split y owns target tiles [y * tiles_per_split, ...).
+// Epilogue: TC_EPI_WARPS = 16 warps.  A warp may only read the TMEM lanes 32 (warp % 4) .. +31, so warp w serves query
+// rows 32 (w % 4) + lane and the 32 accumulator columns 32 (w / 4) .. +31 of every tile: ONE tcgen05.ld.32x32b.x32 per thread
+// and tile.  tools/probes/tmem_probe.cu (profiles/r02_tmem_probe.jsonl) measured the read-back itself at 450 B/clk/SM with 4
+// reading warps and 720 with 8 -- 90-145 clk per 128 x 128 tile, far below the 448 clk of the tile's 7 MMAs -- and the same
+// loop with a running maximum over the values at 330 clk (4 warps) / 190 clk (8 warps): what bounds the epilogue is its
+// ALU work issued from too few warps (one per scheduler cannot hide its own dependent-issue latency), not TMEM.  Hence
+// four warps per scheduler.  A query row's result row in `out` is (q * nsplit + split) * 4 + column group.
+#define TC_CG 4
 template <int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__restrict__ Bimg, int64_t nb, int n_btiles,
@@ -355,10 +368,11 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
                const double *__restrict__ fa, const double *__restrict__ fb,
                FSplitOutTC *__restrict__ out, TcPool pool, float *__restrict__ dump, int64_t dump_ld, int swap_lbo_sbo) {
     extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ int s_rowmax[TC_M];
     const uint32_t sA = smem_u32(smem);
     const uint32_t sB0 = sA + TC_TILE_BYTES;
     uint8_t *tail = smem + TC_TILE_BYTES * (1 + TC_STAGES);
-    const uint32_t bar0 = smem_u32(tail);                 // 8-byte barriers: a_full, full[3], empty[3], tfull[2], tempty[2]
+    const uint32_t bar0 = smem_u32(tail);                 // 8-byte barriers: a_full, full[4], empty[4], tfull[2], tempty[2]
     const uint32_t BAR_A = bar0, BAR_FULL = bar0 + 8, BAR_EMPTY = bar0 + 8 + 8 * TC_STAGES,
                    BAR_TFULL = bar0 + 8 + 16 * TC_STAGES, BAR_TEMPTY = BAR_TFULL + 16;
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(tail + 128);
@@ -367,14 +381,16 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
     const int t_begin = split * tiles_per_split;
     const int t_end = min(n_btiles, t_begin + tiles_per_split);
     const int ntiles = max(0, t_end - t_begin);
+    constexpr int W_PROD = TC_EPI_WARPS, W_MMA = TC_EPI_WARPS + 1;
 
     if (threadIdx.x == 0) {
         mbar_init(BAR_A, 1);
         for (int s = 0; s < TC_STAGES; ++s) { mbar_init(BAR_FULL + 8 * s, 1); mbar_init(BAR_EMPTY + 8 * s, 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(BAR_TFULL + 8 * s, 1); mbar_init(BAR_TEMPTY + 8 * s, 128); }
+        for (int s = 0; s < 2; ++s) { mbar_init(BAR_TFULL + 8 * s, 1); mbar_init(BAR_TEMPTY + 8 * s, 32 * TC_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 5) {                                      // TMEM: 256 columns = two 128-column accumulators
+    if (threadIdx.x < TC_M) s_rowmax[threadIdx.x] = f2key(-INFINITY);
+    if (warp == W_MMA) {                                  // TMEM: 256 columns = two 128-column accumulators
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32((const void *)tmem_slot)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -383,7 +399,7 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 4) {
+    if (warp == W_PROD) {
         // ===== producer: query tile once, then the target tiles of this split through the ring =====
         if (lane == 0 && ntiles > 0) {
             mbar_expect_tx(BAR_A, TC_TILE_BYTES);
@@ -395,7 +411,7 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
                 bulk_g2s(sB0 + s * TC_TILE_BYTES, Bimg + (size_t)(t_begin + it) * TC_TILE_BYTES, TC_TILE_BYTES, BAR_FULL + 8 * s);
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == W_MMA) {
         // ===== MMA issuer: one thread, 7 tcgen05.mma (128 x 128 x 16) per target tile =====
         if (lane == 0 && ntiles > 0) {
             const uint32_t lbo = swap_lbo_sbo ? TC_SBO : TC_LBO, sbo = swap_lbo_sbo ? TC_LBO : TC_SBO;
@@ -417,38 +433,37 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
             }
         }
     } else {
-        // ===== epilogue: thread = one query row; TMEM lane = threadIdx.x =====
-        const int64_t q = (int64_t)qtile * TC_M + threadIdx.x;
+        // ===== epilogue: thread = (query row, column group); TMEM lane = 32 (warp % 4) + lane =====
+        const int r_in_tile = (warp & 3) * 32 + lane;
+        const int cg = warp >> 2;
+        const int64_t q = (int64_t)qtile * TC_M + r_in_tile;
         const bool live = q < na;
-        const uint32_t lane_base = tmem_base + ((uint32_t)(warp * 32) << 16);
+        const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(cg * 32);
         if (MODE == 0) {
             for (int it = 0; it < ntiles; ++it) {
                 int as = it & 1;
                 mbar_wait(BAR_TFULL + 8 * as, (it >> 1) & 1);
                 tc_fence_after();
-                const int64_t t0 = (int64_t)(t_begin + it) * TC_M;
-#pragma unroll 1
-                for (int ch = 0; ch < 4; ++ch) {
-                    float v[32];
-                    tc_ld32(lane_base + as * 128 + ch * 32, v);
-                    if (live) {
+                const int64_t t0 = (int64_t)(t_begin + it) * TC_M + cg * 32;
+                float v[32];
+                tc_ld32(lane_base + as * 128, v);
+                if (live) {
 #pragma unroll
-                        for (int c = 0; c < 32; ++c) { int64_t t = t0 + ch * 32 + c; if (t < nb) dump[q * dump_ld + t] = v[c]; }
-                    }
+                    for (int c = 0; c < 32; ++c) { int64_t t = t0 + c; if (t < nb) dump[q * dump_ld + t] = v[c]; }
                 }
                 tc_fence_before();
                 mbar_arrive(BAR_TEMPTY + 8 * as);
             }
         } else {
-            // Single pass: running maximum + band recording (tc_band_chunk).  The TMEM reads are software-pipelined over two
-            // register buffers -- the load of chunk c+1 is in flight while chunk c is processed -- and the accumulator is handed
-            // back to the MMA warp as soon as its last chunk has been READ, before that chunk is processed.
-            float m = -INFINITY;
+            // Single pass: running maximum + band recording (tc_band_chunk).  The one TMEM read of tile t+1 is issued before
+            // the values of tile t are processed (two register buffers), and the accumulator is handed back to the MMA warp as
+            // soon as it has been READ.
             const float E = live ? feat_tc_err(an32[q], __uint_as_float(*bmax_bits)) : -INFINITY;
             TcRowState rs;
             rs.cnt = 0; rs.cur = -1; rs.ccnt = 0; rs.first = -1; rs.n_eval = 0; rs.bi = -1; rs.exhausted = 0; rs.bestd = INFINITY;
-            const int row = (int)(q * nsplit + split);
+            const int row = (int)((q * nsplit + split) * TC_CG + cg);
             const double *fa_q = fa + q * 33;
+            int *rmk = &s_rowmax[r_in_tile];
             float va[32], vb[32];
             if (ntiles > 0) {
                 mbar_wait(BAR_TFULL, 0);
@@ -456,25 +471,29 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
                 tc_ld32_issue(lane_base, va);
             }
 #pragma unroll 1
-            for (int it = 0; it < ntiles; ++it) {
-                const int as = it & 1;
-                const uint32_t acc = lane_base + as * 128;
-                const int tb = (t_begin + it) * TC_M;               // padding rows score far below any band
-                tc_ld_wait32(va); tc_ld32_issue(acc + 32, vb);
-                tc_band_chunk(va, m, E, tb, rs, pool, row, fa_q, fb);
-                tc_ld_wait32(vb); tc_ld32_issue(acc + 64, va);
-                tc_band_chunk(vb, m, E, tb + 32, rs, pool, row, fa_q, fb);
-                tc_ld_wait32(va); tc_ld32_issue(acc + 96, vb);
-                tc_band_chunk(va, m, E, tb + 64, rs, pool, row, fa_q, fb);
-                tc_ld_wait32(vb);
-                tc_fence_before();
-                mbar_arrive(BAR_TEMPTY + 8 * as);
-                if (it + 1 < ntiles) {
-                    mbar_wait(BAR_TFULL + 8 * (as ^ 1), ((it + 1) >> 1) & 1);
-                    tc_fence_after();
-                    tc_ld32_issue(lane_base + (as ^ 1) * 128, va);
+            for (int it = 0; it < ntiles; it += 2) {
+                {   // tile `it`: values in va, next tile's read goes to vb
+                    tc_ld_wait32(va);
+                    tc_fence_before();
+                    mbar_arrive(BAR_TEMPTY);
+                    if (it + 1 < ntiles) {
+                        mbar_wait(BAR_TFULL + 8, (it >> 1) & 1);
+                        tc_fence_after();
+                        tc_ld32_issue(lane_base + 128, vb);
+                    }
+                    tc_band_chunk(va, rmk, E, (t_begin + it) * TC_M + cg * 32, rs, pool, row, fa_q, fb);
                 }
-                tc_band_chunk(vb, m, E, tb + 96, rs, pool, row, fa_q, fb);
+                if (it + 1 < ntiles) {   // tile `it + 1`: values in vb, next tile's read goes to va
+                    tc_ld_wait32(vb);
+                    tc_fence_before();
+                    mbar_arrive(BAR_TEMPTY + 8);
+                    if (it + 2 < ntiles) {
+                        mbar_wait(BAR_TFULL, ((it + 2) >> 1) & 1);
+                        tc_fence_after();
+                        tc_ld32_issue(lane_base, va);
+                    }
+                    tc_band_chunk(vb, rmk, E, (t_begin + it + 1) * TC_M + cg * 32, rs, pool, row, fa_q, fb);
+                }
             }
             if (live) {
                 if (rs.cur >= 0) pool.n[rs.cur] = rs.ccnt;
@@ -488,7 +507,7 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 5) {
+    if (warp == W_MMA) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem_base) : "memory");
     }
@@ -674,11 +693,12 @@ static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb,
                      const double *fa, const double *fb, const float *a32, const float *b32, const float *na32,
                      const float *nb32, int32_t *nn, cudaStream_t st) {
     TcPlan p = tc_plan(na, nb);
+    const int nsv = p.nsplit * TC_CG;                    // result rows per query: (target split, column group)
     FSplitOutTC *parts = nullptr;
-    IBL_CUDA(ibl_alloc(&parts, (size_t)na * p.nsplit, st));
+    IBL_CUDA(ibl_alloc(&parts, (size_t)na * nsv, st));
     // candidate pool: one chunk for every row that has a candidate at all + 256k chunks (16 M candidates) of headroom
     TcPool pool;
-    const int64_t nrows = na * p.nsplit;
+    const int64_t nrows = na * nsv;
     pool.cap = (int)std::min<int64_t>(nrows + (1 << 18), (int64_t)1 << 24);
     if (g_tc_pool_cap_override > 0) pool.cap = g_tc_pool_cap_override;
     int *pool_meta = nullptr;
@@ -699,10 +719,10 @@ static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb,
     }
     {
         // the chunk count lives on the device (no host sync): a fixed grid strides over it
-        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32);
+        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, nsv, res, fa, fb, a32, b32, na32, nb32);
         IBL_LAUNCH_CHECK();
     }
-    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn);
+    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, nsv, pool, res, fa, fb, nn);
     IBL_LAUNCH_CHECK();
     ibl_free(pool.entries, st); ibl_free(pool_meta, st); ibl_free(res, st); ibl_free(parts, st);
     return IBL_OK;

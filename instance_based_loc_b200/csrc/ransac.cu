@@ -459,7 +459,11 @@ __global__ void __launch_bounds__(128) ransac_check_batch_kernel(const RbProb *_
 // the cloud is dropped after ~11 % of the points.  Chunks are visited with a stride coprime to their number, so the first
 // chunks sample the whole cloud (the source is a concatenation of objects) rather than its first object.
 #define PRUNE_CHUNK 1024
-__global__ void __launch_bounds__(SCORE_THREADS) ransac_count_batch_kernel(const RbProb *__restrict__ probs,
+// FIELD: every problem's grid carries an NN candidate field that covers max_d (the product path).  The ring-search
+// fallback then is not even compiled in, which halves the registers (128 -> 6x) and doubles the resident warps of a kernel
+// whose time is dependent-load latency.
+template <bool FIELD>
+__global__ void __launch_bounds__(SCORE_THREADS, FIELD ? 3 : 1) ransac_count_batch_kernel(const RbProb *__restrict__ probs,
                                                                            const RbEntry *__restrict__ entries,
                                                                            const int *__restrict__ n_entries, double max_d,
                                                                            double max_d2, int32_t *__restrict__ inliers) {
@@ -490,7 +494,7 @@ __global__ void __launch_bounds__(SCORE_THREADS) ransac_count_batch_kernel(const
         const double *__restrict__ src = P->src;
         const int64_t n_src = P->n_src;
         const int thr = P->thr, nchunks = P->nchunks, step = P->chunk_step;
-        const bool field = g.has_field && max_d <= g.f.max_d;
+        const bool field = FIELD || (g.has_field && max_d <= g.f.max_d);
         const bool sure_ok = field && max_d == g.f.max_d;
         int total = 0;
         int64_t seen = 0;
@@ -506,8 +510,8 @@ __global__ void __launch_bounds__(SCORE_THREADS) ransac_count_batch_kernel(const
                 if (i < n_src) {
                     double x, y, z, bd;
                     ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
-                    if (field) cnt += ibl_any_within_field(g, x, y, z, max_d2, sure_ok) ? 1 : 0;
-                    else cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
+                    if (FIELD || field) cnt += ibl_any_within_field(g, x, y, z, max_d2, sure_ok) ? 1 : 0;
+                    else if (!FIELD) cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
                 }
             }
             cnt = __reduce_add_sync(0xffffffffu, cnt);
@@ -686,6 +690,9 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
         while (gcd(step, d.nchunks) != 1) ++step;
         d.chunk_step = d.nchunks == 1 ? 0 : step % d.nchunks;
     }
+    bool all_field = true;
+    for (int p = 0; p < P; ++p)
+        if (hs[p].active && !(problems[p].grid_ransac->has_field && max_d <= problems[p].grid_ransac->field.max_d)) all_field = false;
     RbProb *d_probs = nullptr; int *d_n = nullptr;
     IBL_CUDA(ibl_alloc(&d_probs, (size_t)P, st));
     IBL_CUDA(ibl_alloc(&d_n, 1, st));
@@ -727,7 +734,10 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
             // work figure: the un-pruned pass (every validated hypothesis over its whole source); the number of validated
             // hypotheses is only known on the device here, so it is filled in after the read-back
             IBL_PROF(IBL_PROF_RANSAC_SCORE, st, 0.0);
-            ransac_count_batch_kernel<<<IBL_SMS * 6, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
+            if (all_field)
+                ransac_count_batch_kernel<true><<<IBL_SMS * 6, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
+            else
+                ransac_count_batch_kernel<false><<<IBL_SMS * 4, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
             IBL_LAUNCH_CHECK();
         }
         int nval = 0;

@@ -38,10 +38,10 @@
 #define TC_TILE_BYTES (16 * TC_SBO) // 28,672
 #define TC_STAGES 4
 #define TC_RANGE 1024.0             // rows are scaled by a power of two so that |value| <= TC_RANGE (fp16 range / precision)
-#define TC_EPI_WARPS 16            // epilogue warps: 4 per TMEM lane quarter, each owning 32 of a tile's 128 columns
-#define TC_THREADS (32 * (TC_EPI_WARPS + 2))   // + bulk-copy producer warp + MMA issuer warp
+#define TC_QT 2                      // query tiles per CTA: 2 x 4 epilogue warps, two warps per scheduler
+#define TC_THREADS (32 * (4 * TC_QT + 2))
 #define TC_CHUNK 64                 // band candidates per pool chunk (rows chain as many chunks as they need)
-#define TC_SMEM (TC_TILE_BYTES * (1 + TC_STAGES) + 256)
+#define TC_SMEM (TC_TILE_BYTES * (TC_QT + TC_STAGES) + 256)
 
 // per (query, split) row: winner of the pool-exhausted fallback (d, idx), number of band candidates, first pool chunk
 struct FSplitOutTC { double d; int idx; int cnt; int first; int pad; };
@@ -321,7 +321,7 @@ __device__ __forceinline__ void tc_push(TcRowState &st, const TcPool &pool, int 
 // independent FMNMX, not a 32-deep dependent chain), then record every column inside the band E below the maximum SO
 // FAR.  The running maximum only grows, so the final band [m_final - E, m_final] is a subset of what gets recorded; the
 // surplus (targets that were near-records when they streamed by) only costs exact evaluations later.
-__device__ __forceinline__ void tc_band_chunk(const float *v, int *row_max_key, float E, int tb, TcRowState &rs, const TcPool &pool,
+__device__ __forceinline__ void tc_band_chunk(const float *v, float &m, float E, int tb, TcRowState &rs, const TcPool &pool,
                                               int row, const double *__restrict__ fa_q, const double *__restrict__ fb) {
     float t[16];
 #pragma unroll
@@ -332,11 +332,7 @@ __device__ __forceinline__ void tc_band_chunk(const float *v, int *row_max_key, 
         for (int c = 0; c < w; ++c) t[c] = fmaxf(t[c], t[c + w]);
     }
     const float cm = t[0];
-    // the query row's running maximum is shared by the four threads that own its four column groups (shared memory,
-    // ordered-int atomicMax): whatever the others have already seen tightens this thread's band too.  Any value that has
-    // been a maximum so far is <= the final maximum, so the recorded set stays a superset of the final band.
-    const int old = atomicMax(row_max_key, f2key(cm));
-    const float m = fmaxf(key2f(old), cm);
+    m = fmaxf(m, cm);
     const float r = __fsub_rd(m, E);                      // E = -inf for rows past the end: r = +inf, nothing is recorded
     if (cm >= r) {
         // Hit mask with static register indices, then a short loop that the lanes of the warp run in lock step.
@@ -352,46 +348,44 @@ __device__ __forceinline__ void tc_band_chunk(const float *v, int *row_max_key, 
 }
 
 // MODE 0: dump s' to dump[q][ld] (debug).  MODE 1: running row maximum + band candidates in one pass.
-// grid = (query tiles, splits); split y owns target tiles [y * tiles_per_split, ...).
-// Epilogue: TC_EPI_WARPS = 16 warps.  A warp may only read the TMEM lanes 32 (warp % 4) .. +31, so warp w serves query
-// rows 32 (w % 4) + lane and the 32 accumulator columns 32 (w / 4) .. +31 of every tile: ONE tcgen05.ld.32x32b.x32 per thread
-// and tile.  tools/probes/tmem_probe.cu (profiles/r02_tmem_probe.jsonl) measured the read-back itself at 450 B/clk/SM with 4
-// reading warps and 720 with 8 -- 90-145 clk per 128 x 128 tile, far below the 448 clk of the tile's 7 MMAs -- and the same
-// loop with a running maximum over the values at 330 clk (4 warps) / 190 clk (8 warps): what bounds the epilogue is its
-// ALU work issued from too few warps (one per scheduler cannot hide its own dependent-issue latency), not TMEM.  Hence
-// four warps per scheduler.  A query row's result row in `out` is (q * nsplit + split) * 4 + column group.
-#define TC_CG 4
+// grid = (ceil(query tiles / TC_QT), splits); split y owns target tiles [y * tiles_per_split, ...).
+// A CTA keeps TC_QT = 2 query tiles resident and gives each its own pair of TMEM accumulators and its own four epilogue
+// warps (a warp may only read the TMEM lanes 32 (warp % 4) .. +31, i.e. a thread is one query row): every streamed target
+// tile feeds 2 x 7 MMAs, and the eight epilogue warps -- two per scheduler -- overlap each other's dependent-issue latency.
+// tools/probes/tmem_probe.cu (profiles/r02_tmem_probe.jsonl) measured the TMEM read-back itself at 450 B/clk/SM with four
+// reading warps and 720 with eight (90-145 clk per 128 x 128 tile, far below the 448 clk of 7 MMAs), and the same loop with
+// a running maximum over the values at 330 clk (four warps) against 190 clk (eight): the epilogue is bound by its ALU work
+// issued from one warp per scheduler, not by TMEM.
 template <int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__restrict__ Bimg, int64_t nb, int n_btiles,
+feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const uint8_t *__restrict__ Bimg, int64_t nb, int n_btiles,
                int tiles_per_split, int nsplit, const float *__restrict__ an32, const unsigned *__restrict__ bmax_bits,
                const double *__restrict__ fa, const double *__restrict__ fb,
                FSplitOutTC *__restrict__ out, TcPool pool, float *__restrict__ dump, int64_t dump_ld, int swap_lbo_sbo) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ int s_rowmax[TC_M];
-    const uint32_t sA = smem_u32(smem);
-    const uint32_t sB0 = sA + TC_TILE_BYTES;
-    uint8_t *tail = smem + TC_TILE_BYTES * (1 + TC_STAGES);
+    const uint32_t sA = smem_u32(smem);                   // TC_QT query tiles
+    const uint32_t sB0 = sA + TC_QT * TC_TILE_BYTES;
+    uint8_t *tail = smem + TC_TILE_BYTES * (TC_QT + TC_STAGES);
     const uint32_t bar0 = smem_u32(tail);                 // 8-byte barriers: a_full, full[4], empty[4], tfull[2], tempty[2]
     const uint32_t BAR_A = bar0, BAR_FULL = bar0 + 8, BAR_EMPTY = bar0 + 8 + 8 * TC_STAGES,
                    BAR_TFULL = bar0 + 8 + 16 * TC_STAGES, BAR_TEMPTY = BAR_TFULL + 16;
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(tail + 128);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int qtile = blockIdx.x, split = blockIdx.y;
+    const int qt0 = blockIdx.x * TC_QT, split = blockIdx.y;
+    const int nq_here = min(TC_QT, n_qtiles - qt0);       // query tiles this CTA really has (the last CTA may have one)
     const int t_begin = split * tiles_per_split;
     const int t_end = min(n_btiles, t_begin + tiles_per_split);
     const int ntiles = max(0, t_end - t_begin);
-    constexpr int W_PROD = TC_EPI_WARPS, W_MMA = TC_EPI_WARPS + 1;
+    constexpr int W_PROD = 4 * TC_QT, W_MMA = 4 * TC_QT + 1;
 
     if (threadIdx.x == 0) {
         mbar_init(BAR_A, 1);
         for (int s = 0; s < TC_STAGES; ++s) { mbar_init(BAR_FULL + 8 * s, 1); mbar_init(BAR_EMPTY + 8 * s, 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(BAR_TFULL + 8 * s, 1); mbar_init(BAR_TEMPTY + 8 * s, 32 * TC_EPI_WARPS); }
+        for (int s = 0; s < 2; ++s) { mbar_init(BAR_TFULL + 8 * s, 1); mbar_init(BAR_TEMPTY + 8 * s, 128 * TC_QT); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (threadIdx.x < TC_M) s_rowmax[threadIdx.x] = f2key(-INFINITY);
-    if (warp == W_MMA) {                                  // TMEM: 256 columns = two 128-column accumulators
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32((const void *)tmem_slot)) : "memory");
+    if (warp == W_MMA) {                                  // TMEM: 512 columns = 2 buffers x TC_QT accumulators x 128 columns
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32((const void *)tmem_slot)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
@@ -400,10 +394,11 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == W_PROD) {
-        // ===== producer: query tile once, then the target tiles of this split through the ring =====
+        // ===== producer: the query tiles once, then the target tiles of this split through the ring =====
         if (lane == 0 && ntiles > 0) {
-            mbar_expect_tx(BAR_A, TC_TILE_BYTES);
-            bulk_g2s(sA, Aimg + (size_t)qtile * TC_TILE_BYTES, TC_TILE_BYTES, BAR_A);
+            mbar_expect_tx(BAR_A, (uint32_t)nq_here * TC_TILE_BYTES);
+            for (int h = 0; h < nq_here; ++h)
+                bulk_g2s(sA + h * TC_TILE_BYTES, Aimg + (size_t)(qt0 + h) * TC_TILE_BYTES, TC_TILE_BYTES, BAR_A);
             for (int it = 0; it < ntiles; ++it) {
                 int s = it % TC_STAGES;
                 mbar_wait(BAR_EMPTY + 8 * s, ((it / TC_STAGES) & 1) ^ 1);
@@ -412,7 +407,7 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
             }
         }
     } else if (warp == W_MMA) {
-        // ===== MMA issuer: one thread, 7 tcgen05.mma (128 x 128 x 16) per target tile =====
+        // ===== MMA issuer: one thread, 7 tcgen05.mma (128 x 128 x 16) per (query tile, target tile) =====
         if (lane == 0 && ntiles > 0) {
             const uint32_t lbo = swap_lbo_sbo ? TC_SBO : TC_LBO, sbo = swap_lbo_sbo ? TC_LBO : TC_SBO;
             mbar_wait(BAR_A, 0);
@@ -422,48 +417,52 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
                 mbar_wait(BAR_FULL + 8 * s, (it / TC_STAGES) & 1);
                 tc_fence_after();
                 const uint32_t sB = sB0 + s * TC_TILE_BYTES;
+                for (int h = 0; h < nq_here; ++h) {
 #pragma unroll
-                for (int k = 0; k < TC_K / 16; ++k) {          // one MMA consumes K = 16 halves = two 16-byte chunks
-                    uint64_t ad = tc_smem_desc(sA + k * 2 * TC_LBO, lbo, sbo);
-                    uint64_t bd = tc_smem_desc(sB + k * 2 * TC_LBO, lbo, sbo);
-                    tc_mma_f16(tmem_base + as * 128, ad, bd, TC_IDESC, k > 0);
+                    for (int k = 0; k < TC_K / 16; ++k) {      // one MMA consumes K = 16 halves = two 16-byte chunks
+                        uint64_t ad = tc_smem_desc(sA + h * TC_TILE_BYTES + k * 2 * TC_LBO, lbo, sbo);
+                        uint64_t bd = tc_smem_desc(sB + k * 2 * TC_LBO, lbo, sbo);
+                        tc_mma_f16(tmem_base + as * (128 * TC_QT) + h * 128, ad, bd, TC_IDESC, k > 0);
+                    }
                 }
                 tc_commit(BAR_EMPTY + 8 * s);             // smem stage free once these MMAs have read it
-                tc_commit(BAR_TFULL + 8 * as);            // accumulator ready for the epilogue
+                tc_commit(BAR_TFULL + 8 * as);            // accumulators ready for the epilogue
             }
         }
     } else {
-        // ===== epilogue: thread = (query row, column group); TMEM lane = 32 (warp % 4) + lane =====
-        const int r_in_tile = (warp & 3) * 32 + lane;
-        const int cg = warp >> 2;
-        const int64_t q = (int64_t)qtile * TC_M + r_in_tile;
-        const bool live = q < na;
-        const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(cg * 32);
+        // ===== epilogue: thread = one query row of query tile h = warp / 4; TMEM lane = 32 (warp % 4) + lane =====
+        const int h = warp >> 2;
+        const int64_t q = (int64_t)(qt0 + h) * TC_M + (warp & 3) * 32 + lane;
+        const bool live = h < nq_here && q < na;
+        const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(h * 128);
         if (MODE == 0) {
             for (int it = 0; it < ntiles; ++it) {
                 int as = it & 1;
                 mbar_wait(BAR_TFULL + 8 * as, (it >> 1) & 1);
                 tc_fence_after();
-                const int64_t t0 = (int64_t)(t_begin + it) * TC_M + cg * 32;
-                float v[32];
-                tc_ld32(lane_base + as * 128, v);
-                if (live) {
+                const int64_t t0 = (int64_t)(t_begin + it) * TC_M;
+#pragma unroll 1
+                for (int ch = 0; ch < 4; ++ch) {
+                    float v[32];
+                    tc_ld32(lane_base + as * (128 * TC_QT) + ch * 32, v);
+                    if (live) {
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) { int64_t t = t0 + c; if (t < nb) dump[q * dump_ld + t] = v[c]; }
+                        for (int c = 0; c < 32; ++c) { int64_t t = t0 + ch * 32 + c; if (t < nb) dump[q * dump_ld + t] = v[c]; }
+                    }
                 }
                 tc_fence_before();
                 mbar_arrive(BAR_TEMPTY + 8 * as);
             }
         } else {
-            // Single pass: running maximum + band recording (tc_band_chunk).  The one TMEM read of tile t+1 is issued before
-            // the values of tile t are processed (two register buffers), and the accumulator is handed back to the MMA warp as
-            // soon as it has been READ.
+            // Single pass: running maximum + band recording (tc_band_chunk).  The TMEM reads are software-pipelined over two
+            // register buffers -- the load of chunk c+1 is in flight while chunk c is processed -- and the accumulator is handed
+            // back to the MMA warp as soon as its last chunk has been READ, before that chunk is processed.
+            float m = -INFINITY;
             const float E = live ? feat_tc_err(an32[q], __uint_as_float(*bmax_bits)) : -INFINITY;
             TcRowState rs;
             rs.cnt = 0; rs.cur = -1; rs.ccnt = 0; rs.first = -1; rs.n_eval = 0; rs.bi = -1; rs.exhausted = 0; rs.bestd = INFINITY;
-            const int row = (int)((q * nsplit + split) * TC_CG + cg);
+            const int row = (int)(q * nsplit + split);
             const double *fa_q = fa + q * 33;
-            int *rmk = &s_rowmax[r_in_tile];
             float va[32], vb[32];
             if (ntiles > 0) {
                 mbar_wait(BAR_TFULL, 0);
@@ -471,29 +470,25 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
                 tc_ld32_issue(lane_base, va);
             }
 #pragma unroll 1
-            for (int it = 0; it < ntiles; it += 2) {
-                {   // tile `it`: values in va, next tile's read goes to vb
-                    tc_ld_wait32(va);
-                    tc_fence_before();
-                    mbar_arrive(BAR_TEMPTY);
-                    if (it + 1 < ntiles) {
-                        mbar_wait(BAR_TFULL + 8, (it >> 1) & 1);
-                        tc_fence_after();
-                        tc_ld32_issue(lane_base + 128, vb);
-                    }
-                    tc_band_chunk(va, rmk, E, (t_begin + it) * TC_M + cg * 32, rs, pool, row, fa_q, fb);
+            for (int it = 0; it < ntiles; ++it) {
+                const int as = it & 1;
+                const uint32_t acc = lane_base + as * (128 * TC_QT);
+                const int tb = (t_begin + it) * TC_M;               // padding rows score far below any band
+                tc_ld_wait32(va); tc_ld32_issue(acc + 32, vb);
+                tc_band_chunk(va, m, E, tb, rs, pool, row, fa_q, fb);
+                tc_ld_wait32(vb); tc_ld32_issue(acc + 64, va);
+                tc_band_chunk(vb, m, E, tb + 32, rs, pool, row, fa_q, fb);
+                tc_ld_wait32(va); tc_ld32_issue(acc + 96, vb);
+                tc_band_chunk(va, m, E, tb + 64, rs, pool, row, fa_q, fb);
+                tc_ld_wait32(vb);
+                tc_fence_before();
+                mbar_arrive(BAR_TEMPTY + 8 * as);
+                if (it + 1 < ntiles) {
+                    mbar_wait(BAR_TFULL + 8 * (as ^ 1), ((it + 1) >> 1) & 1);
+                    tc_fence_after();
+                    tc_ld32_issue(lane_base + (as ^ 1) * (128 * TC_QT), va);
                 }
-                if (it + 1 < ntiles) {   // tile `it + 1`: values in vb, next tile's read goes to va
-                    tc_ld_wait32(vb);
-                    tc_fence_before();
-                    mbar_arrive(BAR_TEMPTY + 8);
-                    if (it + 2 < ntiles) {
-                        mbar_wait(BAR_TFULL, ((it + 2) >> 1) & 1);
-                        tc_fence_after();
-                        tc_ld32_issue(lane_base, va);
-                    }
-                    tc_band_chunk(vb, rmk, E, (t_begin + it + 1) * TC_M + cg * 32, rs, pool, row, fa_q, fb);
-                }
+                tc_band_chunk(vb, m, E, tb + 96, rs, pool, row, fa_q, fb);
             }
             if (live) {
                 if (rs.cur >= 0) pool.n[rs.cur] = rs.ccnt;
@@ -509,7 +504,7 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, const uint8_t *__re
     __syncthreads();
     if (warp == W_MMA) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem_base) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
     }
 }
 
@@ -661,7 +656,7 @@ static TcPlan tc_plan(int64_t na, int64_t nb) {
         int real_ns = (p.btiles + tps - 1) / tps;
         if (real_ns != ns) continue;
         if (ns > 1 && tps < 8) break;
-        long long waves = ((long long)p.qtiles * ns + IBL_SMS - 1) / IBL_SMS;
+        long long waves = ((long long)((p.qtiles + TC_QT - 1) / TC_QT) * ns + IBL_SMS - 1) / IBL_SMS;
         long long cost = waves * (tps + 6);
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_ns = ns; }
     }
@@ -693,12 +688,11 @@ static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb,
                      const double *fa, const double *fb, const float *a32, const float *b32, const float *na32,
                      const float *nb32, int32_t *nn, cudaStream_t st) {
     TcPlan p = tc_plan(na, nb);
-    const int nsv = p.nsplit * TC_CG;                    // result rows per query: (target split, column group)
     FSplitOutTC *parts = nullptr;
-    IBL_CUDA(ibl_alloc(&parts, (size_t)na * nsv, st));
+    IBL_CUDA(ibl_alloc(&parts, (size_t)na * p.nsplit, st));
     // candidate pool: one chunk for every row that has a candidate at all + 256k chunks (16 M candidates) of headroom
     TcPool pool;
-    const int64_t nrows = na * nsv;
+    const int64_t nrows = na * p.nsplit;
     pool.cap = (int)std::min<int64_t>(nrows + (1 << 18), (int64_t)1 << 24);
     if (g_tc_pool_cap_override > 0) pool.cap = g_tc_pool_cap_override;
     int *pool_meta = nullptr;
@@ -709,20 +703,20 @@ static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb,
     pool.row = pool_meta; pool.n = pool_meta + pool.cap; pool.next = pool_meta + 2 * (size_t)pool.cap;
     pool.counter = pool_meta + 3 * (size_t)pool.cap;
     IBL_CUDA(cudaMemsetAsync(pool.counter, 0, sizeof(int), st));
-    dim3 grid(p.qtiles, p.nsplit);
+    dim3 grid((p.qtiles + TC_QT - 1) / TC_QT, p.nsplit);
     {
         // nested scope: the tcgen05 kernel alone, with the flops it ISSUES (depth 112 over the padded tiles)
         IBL_PROF(IBL_PROF_FEATURE_GEMM, st, 2.0 * TC_K * (double)p.na_pad * (double)p.nb_pad);
-        feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, bmax_bits,
+        feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, p.qtiles, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, bmax_bits,
                                                             fa, fb, parts, pool, nullptr, 0, 0);
         IBL_LAUNCH_CHECK();
     }
     {
         // the chunk count lives on the device (no host sync): a fixed grid strides over it
-        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, nsv, res, fa, fb, a32, b32, na32, nb32);
+        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32);
         IBL_LAUNCH_CHECK();
     }
-    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, nsv, pool, res, fa, fb, nn);
+    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn);
     IBL_LAUNCH_CHECK();
     ibl_free(pool.entries, st); ibl_free(pool_meta, st); ibl_free(res, st); ibl_free(parts, st);
     return IBL_OK;
@@ -955,8 +949,8 @@ IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double 
     IBL_LAUNCH_CHECK();
     feat_tc_pack_kernel<<<(unsigned)(p.nb_pad / 128), 128, 0, st>>>(fb, nb, p.nb_pad, 1, mu, mx + 2, B, nullptr, mx + 1);
     IBL_LAUNCH_CHECK();
-    dim3 grid(p.qtiles, p.nsplit);
-    feat_tc_kernel<0><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1,
+    dim3 grid((p.qtiles + TC_QT - 1) / TC_QT, p.nsplit);
+    feat_tc_kernel<0><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, p.qtiles, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1,
                                                         fa, fb, nullptr, TcPool{}, scores, nb, swap_lbo_sbo);
     IBL_LAUNCH_CHECK();
     if (center_out) {                                     // debug hook only: read the scale back and publish it

@@ -303,6 +303,9 @@ int ibl_cosine_segmax(const float *det, int32_t nd, const float *mem, int64_t E,
  * (value = the fp16 product widened, -inf when exhausted with flat index 0). */
 int ibl_simvolume_topk(const float *S, int32_t nd, int32_t m, int32_t k, int64_t *out_flat, float *out_val,
                        void *stream);
+/* Test / measurement switch: 1 (default) = (i, j) pairs whose k-line cannot reach the value of the k-th best entry are
+ * skipped in every pass (exact: fp16 products are monotone in each factor); 0 = every pass walks the whole sub-volume. */
+int ibl_simvolume_set_prune(int on);
 
 /* ---------------------------------------------------------------- host wait policy ----------- */
 /* How host threads wait inside this library's (and the process's) stream synchronisations on the current device:

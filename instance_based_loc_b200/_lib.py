@@ -105,6 +105,7 @@ _PROTOS = {
     "ibl_icp": (c_int, [_V, _V, _V, c_int64, _V, _V, _V, _V, c_int, c_double, POINTER(c_double), c_int, c_double,
                         c_double, c_double, POINTER(RegResultT), _V]),
     "ibl_cosine_segmax": (c_int, [_V, c_int32, _V, c_int64, c_int32, _V, c_int32, _V, _V]),
+    "ibl_simvolume_set_prune": (c_int, [c_int]),
     "ibl_simvolume_topk": (c_int, [_V, c_int32, c_int32, c_int32, _V, _V, _V]),
     "ibl_set_host_wait": (c_int, [c_int]),
     "ibl_reserve_scratch": (c_int, [c_int64, _V]),

@@ -122,11 +122,36 @@ __device__ __forceinline__ void comb_rows(int nd, int s, int c, int *r) {
     r[0] = r[1] = r[2] = 0;
 }
 
+// A lower bound on the k-th largest entry of every sub-volume whose FIRST detection is row d: the entries (i, unassigned,
+// unassigned) are valid for every memory object i and equal row_d[i] exactly (x 1.0 in fp16 changes nothing), so the k-th
+// largest value of the row is reached by at least k entries.  One CTA per detection row: bitonic sort of the row's ordered
+// fp16 keys.  lb[d] = 0 (no bound) when the row has fewer than k entries.
+__global__ void __launch_bounds__(256) sv_lower_bound_kernel(const float *__restrict__ S, int m, int k, unsigned *__restrict__ lb) {
+    __shared__ unsigned key[SV_MAXBINS];
+    const int d = blockIdx.x;
+    int n2 = 32;
+    while (n2 < m) n2 <<= 1;
+    for (int t = threadIdx.x; t < n2; t += blockDim.x) key[t] = t < m ? ord16(__float2half_rn(S[(size_t)d * m + t])) : 0u;
+    __syncthreads();
+    for (int kk = 2; kk <= n2; kk <<= 1)
+        for (int j = kk >> 1; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < (n2 >> 1); t += blockDim.x) {
+                int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                int p = i | j;
+                bool desc = (i & kk) == 0;
+                unsigned a = key[i], b = key[p];
+                if ((a < b) == desc) { key[i] = b; key[p] = a; }
+            }
+            __syncthreads();
+        }
+    if (threadIdx.x == 0) lb[d] = m >= k ? key[k - 1] : 0u;
+}
+
 // level 0..4 histogram passes and level 5 = collect
 __global__ void __launch_bounds__(256) sv_pass_kernel(const float *__restrict__ S, SvGeom G, int level,
                                                       const SvState *states, int *__restrict__ hist, int bins,
                                                       unsigned long long *__restrict__ out_keys, SvState *wstates,
-                                                      int kcap) {
+                                                      int kcap, const unsigned *__restrict__ row_lb) {
     __shared__ __half row0[SV_MAXBINS], row1[SV_MAXBINS], row2[SV_MAXBINS];
     __shared__ int sh[SV_MAXBINS];
     __shared__ unsigned long long stotal;
@@ -142,6 +167,19 @@ __global__ void __launch_bounds__(256) sv_pass_kernel(const float *__restrict__ 
     for (int t = threadIdx.x; t < bins; t += blockDim.x) sh[t] = 0;
     if (threadIdx.x == 0) stotal = 0;
     __syncthreads();
+    // extreme values of the last axis (its "unassigned" entry 1.0 included): with them a pair (i, j) bounds every entry
+    // of its k-line -- fp16 multiplication is monotone in each factor, so max_k f16(p * c_k) is f16(p * max c) for
+    // p >= 0 and f16(p * min c) for p < 0
+    __shared__ float s_ext[2];
+    if (threadIdx.x < 32) {
+        float mx = -INFINITY, mn = INFINITY;
+        for (int t = threadIdx.x; t < G.n2; t += 32) { float v = __half2float(row2[t < m ? t : m]); mx = fmaxf(mx, v); mn = fminf(mn, v); }
+        if (G.s < 3) { mx = 1.0f; mn = 1.0f; }
+        for (int o2 = 16; o2; o2 >>= 1) { mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o2)); mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o2)); }
+        if (threadIdx.x == 0) { s_ext[0] = mx; s_ext[1] = mn; }
+    }
+    __syncthreads();
+    const __half c_max = __float2half_rn(s_ext[0]), c_min = __float2half_rn(s_ext[1]);
     SvState stt = states[sub];
     const bool all_invalid = m < G.s;
     int lane = threadIdx.x & 31;
@@ -149,6 +187,13 @@ __global__ void __launch_bounds__(256) sv_pass_kernel(const float *__restrict__ 
     int nwarps = (gridDim.x * blockDim.x) >> 5;
     int npairs = m * G.n1;   // i in [0,m) (first detection can never be unassigned), j in [0,n1)
     unsigned vstar = ((unsigned)stt.sel[0] << 8) | (unsigned)stt.sel[1];
+    // Entries below `floor_o` cannot matter at this level: levels 0-1 look for the value of the k-th largest entry, which is
+    // at least the row bound (sv_lower_bound_kernel); levels 2-5 only touch entries equal to (or, collecting, at least)
+    // that value.  A pair whose k-line cannot reach the floor is skipped whole -- at m = 500 that leaves a few hundred of
+    // the 250 000 pairs.  (The count of ALL valid entries is only needed when there may be fewer than k of them, i.e. when
+    // there is no row bound; then nothing is skipped at level 0.)
+    const unsigned row_floor = row_lb ? row_lb[r[0]] : 0u;
+    const unsigned floor_o = level <= 1 ? row_floor : vstar;
     unsigned long long local_total = 0;
     for (int pi = warp; pi < npairs && !all_invalid; pi += nwarps) {
         int i = pi / G.n1, j = pi - i * G.n1;
@@ -156,6 +201,10 @@ __global__ void __launch_bounds__(256) sv_pass_kernel(const float *__restrict__ 
         if (level >= 3 && level <= 4) { if (i != stt.sel[2]) continue; }
         if (level == 4 && j != stt.sel[3]) continue;
         __half p = (G.s >= 2) ? __hmul(row0[i], row1[j]) : row0[i];
+        if (floor_o) {
+            const __half best = (G.s >= 3) ? __hmax(__hmul(p, c_max), __hmul(p, c_min)) : p;
+            if (!__hisnan(best) && ord16(best) < floor_o) continue;
+        }
         for (int k0 = 0; k0 < G.n2; k0 += 32) {
             int k = k0 + lane;
             bool valid = k < G.n2;
@@ -209,12 +258,14 @@ __global__ void __launch_bounds__(256) sv_pass_kernel(const float *__restrict__ 
 }
 
 // one thread per sub-volume: walk the histogram from the best bin and fix this digit
-__global__ void sv_select_kernel(int *__restrict__ hist, int bins, int level, int k, SvState *__restrict__ states, int ncomb) {
+__global__ void sv_select_kernel(int *__restrict__ hist, int bins, int level, int k, SvState *__restrict__ states, int ncomb,
+                                 int row_bounded) {
     int sub = blockIdx.x * blockDim.x + threadIdx.x;
     if (sub >= ncomb) return;
     SvState st = states[sub];
     int *h = hist + (size_t)sub * SV_MAXBINS;
     if (level == 0) {
+        if (st.total < (unsigned long long)k && row_bounded) st.total = (unsigned long long)k;   // pruned count: >= k entries exist
         st.k_eff = (int)(st.total < (unsigned long long)k ? st.total : (unsigned long long)k);
         st.remaining = st.k_eff;
         st.out_count = 0;
@@ -268,6 +319,11 @@ __global__ void __launch_bounds__(256) sv_sort_kernel(const unsigned long long *
     }
 }
 
+// 1 (default): pairs whose k-line cannot reach the current floor are skipped (exact); 0: every pass walks the whole
+// sub-volume (measurement / test switch)
+static int g_sv_prune = 1;
+IBL_API int ibl_simvolume_set_prune(int on) { g_sv_prune = on ? 1 : 0; return IBL_OK; }
+
 IBL_API int ibl_simvolume_topk(const float *S, int32_t nd, int32_t m, int32_t k, int64_t *out_flat, float *out_val,
                                void *stream) {
     IBL_ARG(S && out_flat && out_val && nd >= 1 && m >= 1 && k >= 1 && k <= 1024 && m + 1 <= SV_MAXBINS);
@@ -289,15 +345,24 @@ IBL_API int ibl_simvolume_topk(const float *S, int32_t nd, int32_t m, int32_t k,
     if (bx < 1) bx = 1;
     dim3 grid(bx, G.ncomb);
     IBL_PROF(IBL_PROF_SIMVOL, st, 6.0 * (double)G.ncomb * m * G.n1 * G.n2);
-    for (int level = 0; level <= 4; ++level) {
-        int bins = level <= 1 ? 256 : m + 1;
-        sv_pass_kernel<<<grid, 256, 0, st>>>(S, G, level, states, hist, bins, keys, states, k);
-        IBL_LAUNCH_CHECK();
-        sv_select_kernel<<<(G.ncomb + 63) / 64, 64, 0, st>>>(hist, bins, level, k, states, G.ncomb);
+    // row bounds (a pruning floor) exist when every row holds at least k values
+    unsigned *row_lb = nullptr;
+    const int row_bounded = (m >= k && g_sv_prune) ? 1 : 0;
+    if (row_bounded) {
+        IBL_CUDA(ibl_alloc(&row_lb, (size_t)nd, st));
+        sv_lower_bound_kernel<<<nd, 256, 0, st>>>(S, m, k, row_lb);
         IBL_LAUNCH_CHECK();
     }
-    sv_pass_kernel<<<grid, 256, 0, st>>>(S, G, 5, states, hist, 1, keys, states, k);
+    for (int level = 0; level <= 4; ++level) {
+        int bins = level <= 1 ? 256 : m + 1;
+        sv_pass_kernel<<<grid, 256, 0, st>>>(S, G, level, states, hist, bins, keys, states, k, g_sv_prune ? row_lb : nullptr);
+        IBL_LAUNCH_CHECK();
+        sv_select_kernel<<<(G.ncomb + 63) / 64, 64, 0, st>>>(hist, bins, level, k, states, G.ncomb, row_bounded);
+        IBL_LAUNCH_CHECK();
+    }
+    sv_pass_kernel<<<grid, 256, 0, st>>>(S, G, 5, states, hist, 1, keys, states, k, g_sv_prune ? row_lb : nullptr);
     IBL_LAUNCH_CHECK();
+    ibl_free(row_lb, st);
     sv_sort_kernel<<<G.ncomb, 256, 0, st>>>(keys, k, k, states, out_flat, out_val);
     IBL_LAUNCH_CHECK();
     ibl_free(states, st); ibl_free(hist, st); ibl_free(keys, st);

@@ -483,6 +483,11 @@ def cosine_segmax(det, mem, seg):
     return S
 
 
+def simvolume_set_prune(on=True):
+    """Test / measurement switch of ibl_simvolume_topk's exact pair pruning (results do not depend on it)."""
+    check(lib().ibl_simvolume_set_prune(int(bool(on))), "simvolume_set_prune")
+
+
 def simvolume_topk(S, k):
     nd, m = S.shape
     s = min(nd, 3)

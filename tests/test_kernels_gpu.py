@@ -527,7 +527,7 @@ def test_simvolume_golden(cuda, golden):
         assert got == exp, (ci, S.shape, got, exp)
 
 
-@pytest.mark.parametrize("nd,m", [(7, 51), (3, 40), (2, 20), (1, 9), (5, 3)])
+@pytest.mark.parametrize("nd,m", [(7, 51), (3, 40), (2, 20), (1, 9), (5, 3), (3, 130), (2, 300), (1, 64), (4, 120)])
 def test_simvolume_topk_vs_port(K, nd, m):
     from oracle import ref_port
     rng = np.random.default_rng(nd + 100 * m)
@@ -545,3 +545,22 @@ def test_simvolume_topk_vs_port(K, nd, m):
     sv = SimVolume(S)
     sv.fast_construct_volume(min(nd, 3))
     assert sv.get_top_indices_from_subvolumes(4) == ref_port.simvolume_assignments(S, 4)
+
+
+@pytest.mark.parametrize("nd,m,neg", [(7, 500, False), (7, 500, True), (5, 257, True), (3, 1000, False)])
+def test_simvolume_pruning_changes_nothing(K, nd, m, neg):
+    """configs[3] sizes (500-object memory): the exact pair pruning (row lower bound for the value passes, the k-th value
+    for the index passes) gives the entries of the full walk, negative similarities (positive products of two negatives)
+    and many fp16 ties included."""
+    rng = np.random.default_rng(nd * 1000 + m)
+    S = rng.uniform(-0.9 if neg else -0.2, 0.98, (nd, m)).astype(np.float32)
+    S[rng.random((nd, m)) < 0.15] = 0.75
+    k = 4 * nd * 4
+    try:
+        K.simvolume_set_prune(False)
+        f0, v0 = K.simvolume_topk(dev(S, torch.float32), k)
+        K.simvolume_set_prune(True)
+        f1, v1 = K.simvolume_topk(dev(S, torch.float32), k)
+    finally:
+        K.simvolume_set_prune(True)
+    assert np.array_equal(h(f0), h(f1)) and np.array_equal(h(v0), h(v1))

@@ -138,6 +138,22 @@ typedef struct { int64_t n_inliers; double err2; } ibl_score_t;
 int ibl_nn_score(const ibl_grid_t *g, const double *src, int64_t n, const double *h_T16, double max_d,
                  int32_t *nn_idx, double *nn_d2, ibl_score_t *h_result, void *stream);
 
+/* ibl_nn_score without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same kernels and reduction order as ibl_nn_score, so n_inliers / err2 / nn_idx / nn_d2 are bit-identical; the
+ * per-CTA partials live in a file-scope static device array (64 KiB, held by every GPU that loads the library until
+ * exit) instead of stream-ordered scratch.  Limits and rules:
+ *   - n <= IBL_NN_SCORE_STATIC_MAX_POINTS, else IBL_E_RANGE with a message (use ibl_nn_score);
+ *   - d_result is a DEVICE ibl_score_t owned by the caller (required); nothing is copied to the host and the call does
+ *     not synchronise -- everything is ordered on `stream`;
+ *   - calls no cudaMalloc / cudaFree / allocating library routine.  The first call on each device looks the array's
+ *     address up (cudaGetSymbolAddress, that device current): make one call before starting a graph capture;
+ *   - all calls share the one array and it keeps the last call's contents (no part of it needs to start at zero: a call
+ *     overwrites every partial it later reads).  Calls that overlap on the GPU RACE on it: serialise them. */
+#define IBL_NN_SCORE_STATIC_MAX_POINTS (1 << 20)
+int ibl_nn_score_static(const ibl_grid_t *g, const double *src, int64_t n, const double *h_T16, double max_d,
+                        int32_t *nn_idx, double *nn_d2, ibl_score_t *d_result, void *stream);
+
 /* ---------------------------------------------------------------- normals / FPFH ------------ */
 /* PointCloud::EstimateNormals(Hybrid) covariance + FastEigen3x3 (A.3), fpfh_register.py:90-92 */
 int ibl_normals(const double *pts, int64_t n, const int32_t *nbr_idx, const int32_t *nbr_cnt, int32_t max_nn,

@@ -71,6 +71,7 @@ _PROTOS = {
                                   _V, _V, _V, _V]),
     "ibl_knn_hybrid": (c_int, [_V, _V, c_int64, c_double, c_int32, _V, _V, _V, _V]),
     "ibl_nn_score": (c_int, [_V, _V, c_int64, POINTER(c_double), c_double, _V, _V, POINTER(ScoreT), _V]),
+    "ibl_nn_score_static": (c_int, [_V, _V, c_int64, POINTER(c_double), c_double, _V, _V, _V, _V]),
     "ibl_normals": (c_int, [_V, c_int64, _V, _V, c_int32, _V, _V]),
     "ibl_spfh": (c_int, [_V, _V, c_int64, _V, _V, c_int32, _V, _V]),
     "ibl_fpfh": (c_int, [c_int64, _V, _V, _V, c_int32, _V, _V, _V]),

@@ -3,6 +3,7 @@
 //   hybrid k-NN   : warp per query, Chebyshev ring expansion, shared-memory candidate buffer,
 //                   warp bitonic sort on (d2 bits, index) -> ascending (d2, index) like the oracle
 //   1-NN + score  : thread per query (ring field skips empty space), deterministic block reduce
+#include <mutex>
 #include <vector>
 
 #include "ibl_common.cuh"
@@ -482,5 +483,82 @@ IBL_API int ibl_nn_score_batch(const ibl_grid_t *g, const double *const *srcs, c
     IBL_CUDA(cudaMemcpyAsync(h_results, dres, sizeof(ibl_score_t) * n_queries, cudaMemcpyDeviceToHost, st));
     IBL_CUDA(ibl_sync(st));
     ibl_free(dq, st); ibl_free(dpre, st); ibl_free(pc, st); ibl_free(pe, st); ibl_free(dres, st);
+    return IBL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// ibl_nn_score_static: ibl_nn_score for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc).  No counterpart in the reference.
+//
+// The per-CTA partials that ibl_nn_score keeps in stream-ordered scratch live here in ONE file-scope device array of a
+// fixed size, held by every GPU that loads the library until exit: IBL_NN_SCORE_STATIC_MAX_POINTS (2^20) source points
+// -> 4096 CTAs x (int64 count + double squared error) = 64 KiB.  The same two kernels run, in the same order, so the
+// result equals ibl_nn_score's bit for bit.  The result goes to a caller-owned DEVICE ibl_score_t: nothing is read back,
+// nothing synchronises, nothing is allocated or freed.
+//
+// In host code `g_nns_static` is only the host-side stand-in of the symbol; the device address is looked up ONCE per
+// device (with that device current) by cudaGetSymbolAddress and cached.
+//
+// Every call shares the array and the array keeps the last call's contents.  Nothing in it has to start at zero: a call
+// with nb CTAs overwrites partials [0, nb) before its final kernel reads exactly those, so stale values are never read.
+// Calls that OVERLAP on the GPU (different streams, or graph branches without an edge between them) race on the array;
+// the caller serialises them.
+struct NnsStatic {
+    long long cnt[IBL_NN_SCORE_STATIC_MAX_POINTS / 256];
+    double err[IBL_NN_SCORE_STATIC_MAX_POINTS / 256];
+};
+static __device__ __align__(256) NnsStatic g_nns_static;
+
+#define NNS_MAX_DEVICES 64
+static NnsStatic *g_nns_static_ptr[NNS_MAX_DEVICES];      // device address of g_nns_static, per device ordinal
+static std::mutex g_nns_static_mu;
+
+static int nns_static_address(NnsStatic **out) {
+    int dev = -1;
+    IBL_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NNS_MAX_DEVICES) {
+        ibl_set_error("ibl_nn_score_static: device ordinal %d outside [0, %d)", dev, NNS_MAX_DEVICES);
+        return IBL_E_RANGE;
+    }
+    std::lock_guard<std::mutex> lk(g_nns_static_mu);
+    if (g_nns_static_ptr[dev] == nullptr) {
+        NnsStatic *p = nullptr;
+        IBL_CUDA(cudaGetSymbolAddress((void **)&p, g_nns_static));
+        if (p == nullptr) {
+            ibl_set_error("ibl_nn_score_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+            return IBL_E_CUDA;
+        }
+        g_nns_static_ptr[dev] = p;
+    }
+    *out = g_nns_static_ptr[dev];
+    return IBL_OK;
+}
+
+IBL_API int ibl_nn_score_static(const ibl_grid_t *g, const double *src, int64_t n, const double *h_T16, double max_d,
+                                int32_t *nn_idx, double *nn_d2, ibl_score_t *d_result, void *stream) {
+    IBL_ARG(g != nullptr && n >= 0 && max_d > 0 && d_result != nullptr && (n == 0 || src != nullptr));
+    if (n > IBL_NN_SCORE_STATIC_MAX_POINTS) {
+        ibl_set_error("ibl_nn_score_static: n = %lld source points exceeds the static scratch limit of %d "
+                      "(IBL_NN_SCORE_STATIC_MAX_POINTS); use ibl_nn_score", (long long)n, IBL_NN_SCORE_STATIC_MAX_POINTS);
+        return IBL_E_RANGE;
+    }
+    cudaStream_t st = ibl_stream(stream);
+    if (n == 0 || g->n == 0) {        // {0, 0.0} is all-zero bytes; nn_idx = -1, nn_d2 untouched, as in ibl_nn_score
+        IBL_CUDA(cudaMemsetAsync(d_result, 0, sizeof(ibl_score_t), st));
+        if (n > 0 && nn_idx) IBL_CUDA(cudaMemsetAsync(nn_idx, 0xff, sizeof(int32_t) * (size_t)n, st));
+        return IBL_OK;
+    }
+    NnsStatic *scratch = nullptr;
+    int rc = nns_static_address(&scratch);
+    if (rc != IBL_OK) return rc;
+    Mat16 T;
+    const int has_T = h_T16 != nullptr;
+    for (int k = 0; k < 16; ++k) T.v[k] = has_T ? h_T16[k] : ((k % 5 == 0) ? 1.0 : 0.0);
+    const int nb = (int)((n + 255) / 256);
+    nn_score_kernel<<<nb, 256, 0, st>>>(ibl_view(g), src, n, T, has_T, max_d, max_d * max_d, nn_idx, nn_d2,
+                                        scratch->cnt, scratch->err);
+    IBL_LAUNCH_CHECK();
+    score_final_kernel<<<1, 32, 0, st>>>(scratch->cnt, scratch->err, nb, d_result);
+    IBL_LAUNCH_CHECK();
     return IBL_OK;
 }

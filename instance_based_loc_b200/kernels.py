@@ -251,6 +251,16 @@ def nn_score(grid, src, max_d, T=None, want_idx=False, want_d2=False):
     return int(res.n_inliers), float(res.err2), nn, d2
 
 
+def nn_score_static(grid, src, max_d, out, T=None, nn=None, d2=None):
+    """ibl_nn_score_static: nn_score with no allocation and no host sync.  ``out`` is a caller-owned device buffer of
+    16 bytes (int64 n_inliers, float64 err2 -- e.g. torch.empty(2, dtype=torch.int64)); ``nn`` / ``d2`` optional caller-owned
+    outputs.  At most IBL_NN_SCORE_STATIC_MAX_POINTS (2^20) source points; calls that overlap on the GPU race on the
+    library's static scratch array."""
+    assert out.is_cuda and out.numel() * out.element_size() >= 16 and out.is_contiguous()
+    check(lib().ibl_nn_score_static(grid.h, _p(src), src.shape[0], _T16(T), float(max_d), _p(nn), _p(d2), _p(out), _stream()),
+          "nn_score_static")
+
+
 # -------------------------------------------------------------------------------------- features
 def normals(pts, idx, cnt):
     out = torch.empty_like(pts)

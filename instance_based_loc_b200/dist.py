@@ -6,8 +6,11 @@ uses no collective at all; only results cross NVLink:
     (7 f64 per frame);
   * hypothesis-block sharding (single-frame latency / RANSAC microbench): every rank scores its own block of the
     same counter-based sample stream and the winners are combined by ``best_of_ranks`` with Open3D's
-    IsBetterRANSACThan order (fitness desc, inlier_rmse asc) and the lowest hypothesis index on ties, which is what
-    the sequential loop would have kept.
+    IsBetterRANSACThan order (fitness desc, inlier_rmse asc) and the lowest hypothesis index on ties.  That equals
+    what the sequential loop would have kept ONLY with a fixed hypothesis count (``registration.ransac_early_exit =
+    False``, the mode configs[4] and tests/test_scale_gpu.py run): with the adaptive stop each rank's estimated stop
+    index is local to its block, ranks above 0 score hypotheses the sequential run would never have drawn, and the
+    winner then depends on the world size.  Callers of ``hypothesis_block`` must switch the adaptive stop off.
 """
 from __future__ import annotations
 

@@ -191,6 +191,12 @@ int ibl_feature_scores_debug(const double *fa, int64_t na, const double *fb, int
 int ibl_feature_nn_set_pool_chunks(int chunks);
 /* Instrumentation of ibl_feature_nn: h_out2 = {band candidates, exact f64 evaluations} since the last reset.  Syncs. */
 int ibl_feature_nn_stats(int64_t *h_out2, int reset);
+/* instrumentation: who waits for whom inside the tcgen05 matcher kernel.  mode 1 zeroes the counters and switches
+ * collection on, mode 0 reads them and switches it off.  h_out8 = {CTAs, target tiles streamed, MMA thread's loop clocks,
+ * of those waiting for a free accumulator (epilogue-bound), waiting for a target tile (copy-bound), epilogue warp 0's loop
+ * clocks, of those waiting for an accumulator (MMA-bound), producer's clocks waiting for a free stage}.  No reference
+ * counterpart.  Syncs. */
+int ibl_feature_nn_wait_stats(int64_t *h_out8, int mode);
 /* mutual filter + fallback (A.5). ij int32[ns], ji int32[nt] -> corres int32[<=ns][2]; returns C. Syncs. */
 int64_t ibl_mutual_corres(const int32_t *ij, int64_t ns, const int32_t *ji, int64_t nt, int32_t ransac_n,
                           int32_t *corres, void *stream);

@@ -81,6 +81,7 @@ _PROTOS = {
     "ibl_feature_match_packed": (c_int, [_V, c_int64, _V, _V, _V, _V, _V]),
     "ibl_feature_scores_debug": (c_int, [_V, c_int64, _V, c_int64, _V, _V, c_int, _V]),
     "ibl_feature_nn_stats": (c_int, [POINTER(c_int64), c_int]),
+    "ibl_feature_nn_wait_stats": (c_int, [POINTER(c_int64), c_int]),
     "ibl_feature_nn_set_pool_chunks": (c_int, [c_int]),
     "ibl_mutual_corres": (c_int64, [_V, c_int64, _V, c_int64, c_int32, _V, _V]),
     "ibl_ransac_check": (c_int, [_V, _V, _V, c_int64, _V, c_uint64, c_int64, c_int64, c_double, c_double, c_int, _V,

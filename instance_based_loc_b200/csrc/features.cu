@@ -249,6 +249,19 @@ IBL_API int ibl_spfh(const double *pts, const double *nrm, int64_t n, const int3
 // per-neighbour loop issues one f64 division per lane instead of two (a divergent `if (lane == 0)` division costs the
 // whole warp its issue slots).  Every quotient and every sum is the same operation in the same order as before.
 #define FPFH_MAX_NN 224
+// s / dist, correctly rounded, for s >= 0.  SPFH histograms are sparse, and a ZERO numerator sends __ddiv_rn down its
+// slow path (the fast path requires a normal numerator); with one zero lane per warp every iteration paid for the ~100
+// instruction special-case routine (ncu: the slow-path call executed once per neighbour, 47 % of the kernel's
+// instructions).  +0 / dist is +0 for dist > 0, so zero lanes divide 1.0 instead and select 0 afterwards.
+__device__ __forceinline__ double fpfh_quot(double s, double dist) {
+    const bool zero = (s == 0.0);
+    double num = zero ? 1.0 : s;
+#if defined(__CUDA_ARCH__)
+    asm volatile("" : "+d"(num));        // opaque: otherwise the compiler folds the two selects away and divides s itself
+#endif
+    const double q = __ddiv_rn(num, dist);
+    return zero ? 0.0 : q;
+}
 __global__ void __launch_bounds__(128) fpfh_kernel(int64_t n, const int32_t *__restrict__ nbr_idx,
                                                    const double *__restrict__ nbr_d2,
                                                    const int32_t *__restrict__ nbr_cnt, int max_nn,
@@ -263,7 +276,7 @@ __global__ void __launch_bounds__(128) fpfh_kernel(int64_t n, const int32_t *__r
         for (int k = 1 + lane; k < cnt; k += 32) {
             double dist = nbr_d2[i * max_nn + k];
             size_t q = (size_t)nbr_idx[i * max_nn + k];
-            v32s[wib][k] = (dist == 0.0) ? 0.0 : __ddiv_rn(spfh[q * 33 + 32], dist);
+            v32s[wib][k] = (dist == 0.0) ? 0.0 : fpfh_quot(spfh[q * 33 + 32], dist);
         }
         __syncwarp();
         double acc = 0.0, acc32 = 0.0, bsum = 0.0;
@@ -271,7 +284,7 @@ __global__ void __launch_bounds__(128) fpfh_kernel(int64_t n, const int32_t *__r
             double dist = nbr_d2[i * max_nn + k];
             if (dist == 0.0) continue;           // uniform across the warp
             size_t q = (size_t)nbr_idx[i * max_nn + k];
-            double v = __ddiv_rn(spfh[q * 33 + lane], dist);
+            double v = fpfh_quot(spfh[q * 33 + lane], dist);
             acc = __dadd_rn(acc, v);
             vals[wib][lane] = v;
             __syncwarp();

@@ -278,6 +278,12 @@ __device__ __noinline__ double feat_tc_exact(const double *__restrict__ a, const
 }
 
 __device__ unsigned long long g_tc_stats[2];   // band candidates, exact f64 evaluations (instrumentation; see ibl_feature_nn_stats)
+// Who waits for whom inside feat_tc_kernel (instrumentation, off unless ibl_feature_nn_wait_stats(.., 1) switched it on):
+// [0] CTAs, [1] target tiles streamed, [2] MMA thread: clocks in its tile loop, [3] of those waiting for a free accumulator
+// (epilogue-bound), [4] waiting for a target tile in shared memory (copy-bound), [5] epilogue warp 0: clocks in its tile
+// loop, [6] of those waiting for an accumulator (MMA-bound), [7] producer: clocks waiting for a free stage.
+__device__ unsigned long long g_tc_wait[8];
+__device__ int g_tc_wait_on;
 
 // A band candidate of this thread's query goes into the row's chain of pool chunks (one atomicAdd per TC_CHUNK
 // candidates; the chain itself is thread-private) for feat_tc_eval_kernel.  Only if the pool is exhausted is it
@@ -377,6 +383,7 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
     const int t_end = min(n_btiles, t_begin + tiles_per_split);
     const int ntiles = max(0, t_end - t_begin);
     constexpr int W_PROD = 4 * TC_QT, W_MMA = 4 * TC_QT + 1;
+    const bool wait_on = (MODE == 1) && g_tc_wait_on != 0;
 
     if (threadIdx.x == 0) {
         mbar_init(BAR_A, 1);
@@ -399,22 +406,31 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
             mbar_expect_tx(BAR_A, (uint32_t)nq_here * TC_TILE_BYTES);
             for (int h = 0; h < nq_here; ++h)
                 bulk_g2s(sA + h * TC_TILE_BYTES, Aimg + (size_t)(qt0 + h) * TC_TILE_BYTES, TC_TILE_BYTES, BAR_A);
+            long long w_empty = 0;
             for (int it = 0; it < ntiles; ++it) {
                 int s = it % TC_STAGES;
+                const long long c0 = wait_on ? clock64() : 0;
                 mbar_wait(BAR_EMPTY + 8 * s, ((it / TC_STAGES) & 1) ^ 1);
+                if (wait_on) w_empty += clock64() - c0;
                 mbar_expect_tx(BAR_FULL + 8 * s, TC_TILE_BYTES);
                 bulk_g2s(sB0 + s * TC_TILE_BYTES, Bimg + (size_t)(t_begin + it) * TC_TILE_BYTES, TC_TILE_BYTES, BAR_FULL + 8 * s);
             }
+            if (wait_on) atomicAdd(&g_tc_wait[7], (unsigned long long)w_empty);
         }
     } else if (warp == W_MMA) {
         // ===== MMA issuer: one thread, 7 tcgen05.mma (128 x 128 x 16) per (query tile, target tile) =====
         if (lane == 0 && ntiles > 0) {
             const uint32_t lbo = swap_lbo_sbo ? TC_SBO : TC_LBO, sbo = swap_lbo_sbo ? TC_LBO : TC_SBO;
             mbar_wait(BAR_A, 0);
+            long long w_tempty = 0, w_full = 0;
+            const long long loop0 = wait_on ? clock64() : 0;
             for (int it = 0; it < ntiles; ++it) {
                 int s = it % TC_STAGES, as = it & 1;
+                const long long c0 = wait_on ? clock64() : 0;
                 mbar_wait(BAR_TEMPTY + 8 * as, ((it >> 1) & 1) ^ 1);
+                const long long c1 = wait_on ? clock64() : 0;
                 mbar_wait(BAR_FULL + 8 * s, (it / TC_STAGES) & 1);
+                if (wait_on) { w_tempty += c1 - c0; w_full += clock64() - c1; }
                 tc_fence_after();
                 const uint32_t sB = sB0 + s * TC_TILE_BYTES;
                 for (int h = 0; h < nq_here; ++h) {
@@ -427,6 +443,13 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
                 }
                 tc_commit(BAR_EMPTY + 8 * s);             // smem stage free once these MMAs have read it
                 tc_commit(BAR_TFULL + 8 * as);            // accumulators ready for the epilogue
+            }
+            if (wait_on) {
+                atomicAdd(&g_tc_wait[0], 1ull);
+                atomicAdd(&g_tc_wait[1], (unsigned long long)ntiles);
+                atomicAdd(&g_tc_wait[2], (unsigned long long)(clock64() - loop0));
+                atomicAdd(&g_tc_wait[3], (unsigned long long)w_tempty);
+                atomicAdd(&g_tc_wait[4], (unsigned long long)w_full);
             }
         }
     } else {
@@ -464,8 +487,11 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
             const int row = (int)(q * nsplit + split);
             const double *fa_q = fa + q * 33;
             float va[32], vb[32];
+            long long w_tfull = 0;
+            const long long eloop0 = wait_on ? clock64() : 0;
             if (ntiles > 0) {
                 mbar_wait(BAR_TFULL, 0);
+                if (wait_on) w_tfull += clock64() - eloop0;
                 tc_fence_after();
                 tc_ld32_issue(lane_base, va);
             }
@@ -484,11 +510,17 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
                 tc_fence_before();
                 mbar_arrive(BAR_TEMPTY + 8 * as);
                 if (it + 1 < ntiles) {
+                    const long long c0 = wait_on ? clock64() : 0;
                     mbar_wait(BAR_TFULL + 8 * (as ^ 1), ((it + 1) >> 1) & 1);
+                    if (wait_on) w_tfull += clock64() - c0;
                     tc_fence_after();
                     tc_ld32_issue(lane_base + (as ^ 1) * (128 * TC_QT), va);
                 }
                 tc_band_chunk(vb, m, E, tb + 96, rs, pool, row, fa_q, fb);
+            }
+            if (wait_on && threadIdx.x == 0) {
+                atomicAdd(&g_tc_wait[5], (unsigned long long)(clock64() - eloop0));
+                atomicAdd(&g_tc_wait[6], (unsigned long long)w_tfull);
             }
             if (live) {
                 if (rs.cur >= 0) pool.n[rs.cur] = rs.ccnt;
@@ -967,6 +999,23 @@ IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double 
         ibl_free(mu, st);
     }
     ibl_free(A, st); ibl_free(B, st); ibl_free(an, st); ibl_free(mx, st);
+    return IBL_OK;
+}
+
+// Instrumentation: the wait clocks of feat_tc_kernel (g_tc_wait above).  mode 1: zero the counters and switch collection on;
+// mode 0: read them into h_out8 and switch collection off.  Syncs.
+IBL_API int ibl_feature_nn_wait_stats(int64_t *h_out8, int mode) {
+    IBL_CUDA(cudaDeviceSynchronize());
+    unsigned long long v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int on = mode ? 1 : 0;
+    if (mode) {
+        IBL_CUDA(cudaMemcpyToSymbol(g_tc_wait, v, sizeof(v)));
+    } else {
+        IBL_ARG(h_out8 != nullptr);
+        IBL_CUDA(cudaMemcpyFromSymbol(v, g_tc_wait, sizeof(v)));
+        for (int k = 0; k < 8; ++k) h_out8[k] = (int64_t)v[k];
+    }
+    IBL_CUDA(cudaMemcpyToSymbol(g_tc_wait_on, &on, sizeof(on)));
     return IBL_OK;
 }
 

@@ -332,6 +332,18 @@ def feature_nn_stats(reset=True):
     return int(v[0]), int(v[1])
 
 
+def feature_nn_wait_stats(start=False):
+    """Wait clocks inside the tcgen05 matcher kernel (ibl_feature_nn_wait_stats).  start=True zeroes and enables the
+    counters; start=False reads them (dict) and disables collection."""
+    v = (ctypes.c_int64 * 8)()
+    check(lib().ibl_feature_nn_wait_stats(v, 1 if start else 0), "feature_nn_wait_stats")
+    if start:
+        return None
+    keys = ("ctas", "tiles", "mma_loop_clk", "mma_wait_accumulator_clk", "mma_wait_tile_clk", "epilogue_loop_clk",
+            "epilogue_wait_accumulator_clk", "producer_wait_stage_clk")
+    return dict(zip(keys, (int(x) for x in v)))
+
+
 def feature_nn_set_pool_chunks(chunks=0):
     """Test hook: cap the matcher's candidate pool (0 = default) to force its pool-exhausted path."""
     check(lib().ibl_feature_nn_set_pool_chunks(int(chunks)), "feature_nn_set_pool_chunks")

@@ -115,21 +115,43 @@ __device__ __forceinline__ int next_pow2_ge32(int c) {
 
 // Two passes per query (one warp each).
 //   pass 1 : Chebyshev ring expansion that only COUNTS: every candidate within the radius goes into a histogram of d2
-//            (bins of width cell/16 in distance).  After ring s every point closer than s*cell has been seen, so as soon as the bins
-//            below that bound hold max_nn points the search stops, and the first bin j* whose cumulative count reaches
-//            max_nn is a distance bound that provably contains the max_nn nearest (and every tie with the last one).
-//   pass 2 : the same cells again as whole x-rows of the cube; only candidates in bins <= j* are stored -- about
-//            max_nn + one bin's population instead of everything inside the cube -- then ONE warp bitonic sort on
-//            (d2 bits, index) gives the oracle's ascending (d2, index) order.
-// The histogram replaces the sort-and-compact rounds the one-pass version needed (its buffer held the whole cube, ~3x
-// max_nn on a surface, and the sorts were ~85 % of the instructions).  If the stored set still overflows the buffer
-// (duplicates, a degenerate bin) the old compaction -- sort, keep the best max_nn, remember the threshold -- takes over.
+//            (128 bins of equal width cell^2 / 8 in SQUARED distance: float conversion, one multiplication, truncation).
+//            After ring s every point closer than s*cell has been seen, so as soon as the bins below that bound hold max_nn
+//            points the search stops, and the first bin j* whose cumulative count reaches max_nn is a distance bound that
+//            provably contains the max_nn nearest (and every tie with the last one).
+//   pass 2 : the cells of the cube again, but only the part of it that the bound can reach: a row of cells whose rectangle
+//            in (y, z) lies farther than the bound is skipped and the others are clipped in x; only candidates in bins
+//            <= j* are stored -- about max_nn + one bin's population -- then ONE warp bitonic sort on (d2 bits, index)
+//            gives the oracle's ascending (d2, index) order.
+// Both passes first compute the (first, last) positions of up to 32 cell segments in PARALLEL (one lane per segment: two
+// loads of cell_start each), then walk the non-empty ones: the old per-row loop paid two dependent global loads per row of
+// cells before it could touch a point (ncu: 25 % of the samples sat on the first use of a candidate, IPC 2.2), and most
+// rows of a cube around a surface are empty.
+// If the stored set overflows the buffer (duplicates, a degenerate bin) a compaction -- sort, keep the best max_nn,
+// remember the threshold -- takes over.
 #define KNN_NB 128
-// histogram bin of a squared distance: float arithmetic is enough -- the only properties used are that the map is monotone
-// non-decreasing in d2 (conversion, correctly rounded sqrt, multiplication by a positive constant and truncation all are)
-// and that both passes use the same map
-__device__ __forceinline__ int knn_bin(double d2, float inv_w) {
-    return (int)fminf(__fmul_rn(__fsqrt_rn((float)d2), inv_w), (float)(KNN_NB - 1));
+// histogram bin of a squared distance.  The only properties used are that the map is monotone non-decreasing in d2
+// (conversion to float, multiplication by a positive constant and truncation all are) and that both passes use the same map.
+__device__ __forceinline__ int knn_bin(double d2, float inv_w2) {
+    return (int)fminf(__fmul_rn((float)d2, inv_w2), (float)(KNN_NB - 1));
+}
+// positions [p0, p1) in g.sorted of the cells xa..xb of row (y, z); empty if the row or the range is outside the grid
+__device__ __forceinline__ void knn_segment(const GridView &g, int z, int y, int xa, int xb, int &p0, int &p1) {
+    p0 = p1 = 0;
+    xa = max(xa, 0); xb = min(xb, g.nx - 1);
+    if (z < 0 || z >= g.nz || y < 0 || y >= g.ny || xa > xb) return;
+    const size_t rb = ((size_t)z * g.ny + y) * g.nx;
+    p0 = g.cell_start[rb + xa];
+    p1 = g.cell_start[rb + xb + 1];
+}
+// distance from q to the interval of coordinates that cell c of an axis can hold (widened by 1e-6 cell; the two boundary
+// cells are open-ended, because points are clamped into them)
+__device__ __forceinline__ double knn_axis_gap(double q, double o, double cell, int c, int n) {
+    const double lo = o + ((double)c - 1e-6) * cell, hi = o + ((double)c + 1.0 + 1e-6) * cell;
+    double d = 0.0;
+    if (c > 0 && q < lo) d = lo - q;
+    if (c < n - 1 && q > hi) d = q - hi;
+    return d;
 }
 template <int CAP>
 __global__ void __launch_bounds__(128) knn_kernel(GridView g, const double *__restrict__ queries, int64_t nq,
@@ -145,7 +167,7 @@ __global__ void __launch_bounds__(128) knn_kernel(GridView g, const double *__re
     int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int s_rad = isfinite(radius) ? (int)ceil(radius * g.inv_cell + 1e-6) : 0x3fffffff;
-    const float inv_w = (float)(16.0 * g.inv_cell);       // bins of width cell/16 in DISTANCE: 128 bins reach 8 cells
+    const float inv_w2 = (float)(8.0 * g.inv_cell * g.inv_cell);   // bins of cell^2 / 8 in SQUARED distance: 128 bins reach 4 cells
     for (int64_t qi = warp; qi < nq; qi += nwarps) {
         double qx, qy, qz;
         int64_t row;
@@ -170,27 +192,31 @@ __global__ void __launch_bounds__(128) knn_kernel(GridView g, const double *__re
         __syncwarp();
         int s_end = s_begin, jstar = KNN_NB;               // jstar == KNN_NB: no bin bound (the radius / the whole grid decides)
         for (int s = s_begin;; ++s) {
-            int z0 = max(cz - s, 0), z1 = min(cz + s, g.nz - 1);
-            int y0 = max(cy - s, 0), y1 = min(cy + s, g.ny - 1);
-            for (int z = z0; z <= z1; ++z) {
-                bool zedge = (z == cz - s) || (z == cz + s);
-                for (int y = y0; y <= y1; ++y) {
-                    bool edge = zedge || (y == cy - s) || (y == cy + s);
-                    size_t rb = ((size_t)z * g.ny + y) * g.nx;
-                    int nseg = edge ? 1 : 2;
-                    for (int seg = 0; seg < nseg; ++seg) {
-                        int xa, xb;
-                        if (edge) { xa = cx - s; xb = cx + s; }
-                        else if (seg == 0) { xa = xb = cx - s; }
-                        else { xa = xb = cx + s; }
-                        xa = max(xa, 0); xb = min(xb, g.nx - 1);
-                        if (xa > xb) continue;
-                        int p0 = g.cell_start[rb + xa], p1 = g.cell_start[rb + xb + 1];
-                        for (int p = p0 + lane; p < p1; p += 32) {
-                            double4 t = g.sorted[p];
-                            double d2 = ibl_d2(t.x, t.y, t.z, qx, qy, qz);
-                            if (d2 < r2) atomicAdd(&hist[knn_bin(d2, inv_w)], 1);
-                        }
+            // ring s = the cells at Chebyshev distance s.  Slot j = (row of the (2s+1)^2 rows in (z, y), segment 0 / 1): a
+            // row on the shell's faces in z or y is ONE segment cx-s .. cx+s; an inner row is the two single cells cx-s, cx+s.
+            // (rows outside the grid are not enumerated: a query far outside the box would otherwise walk empty slots)
+            const int z0 = max(cz - s, 0), z1 = min(cz + s, g.nz - 1), y0 = max(cy - s, 0), y1 = min(cy + s, g.ny - 1);
+            const int Wy = max(y1 - y0 + 1, 0), Wz = max(z1 - z0 + 1, 0);
+            const long long nslots = 2ll * Wy * Wz;
+            for (long long j0 = 0; j0 < nslots; j0 += 32) {
+                const long long j = j0 + lane;
+                int p0 = 0, p1 = 0;
+                if (j < nslots) {
+                    const int rw = (int)(j >> 1), seg = (int)(j & 1);
+                    const int z = z0 + rw / Wy, y = y0 + rw % Wy;
+                    const bool edge = z == cz - s || z == cz + s || y == cy - s || y == cy + s;
+                    if (edge) { if (seg == 0) knn_segment(g, z, y, cx - s, cx + s, p0, p1); }
+                    else knn_segment(g, z, y, seg ? cx + s : cx - s, seg ? cx + s : cx - s, p0, p1);
+                }
+                unsigned live = __ballot_sync(0xffffffffu, p1 > p0);
+                while (live) {
+                    const int src = __ffs(live) - 1;
+                    live &= live - 1;
+                    const int a = __shfl_sync(0xffffffffu, p0, src), e = __shfl_sync(0xffffffffu, p1, src);
+                    for (int p = a + lane; p < e; p += 32) {
+                        double4 t = g.sorted[p];
+                        double d2 = ibl_d2(t.x, t.y, t.z, qx, qy, qz);
+                        if (d2 < r2) atomicAdd(&hist[knn_bin(d2, inv_w2)], 1);
                     }
                 }
             }
@@ -203,7 +229,7 @@ __global__ void __launch_bounds__(128) knn_kernel(GridView g, const double *__re
             if (gr > 0) {
                 // knn_bin is monotone in d2, so every candidate in a bin below knn_bin(gr^2) is closer than gr (the last bin
                 // is open-ended and is never below anything)
-                int jm = knn_bin(gr * gr, inv_w) - 1;
+                int jm = knn_bin(gr * gr, inv_w2) - 1;
                 if (jm >= 0) {
                     int h0 = 4 * lane <= jm ? hist[4 * lane] : 0, h1 = 4 * lane + 1 <= jm ? hist[4 * lane + 1] : 0;
                     int h2 = 4 * lane + 2 <= jm ? hist[4 * lane + 2] : 0, h3 = 4 * lane + 3 <= jm ? hist[4 * lane + 3] : 0;
@@ -222,21 +248,48 @@ __global__ void __launch_bounds__(128) knn_kernel(GridView g, const double *__re
                 }
             }
         }
-        // ---------------- pass 2: store the candidates of bins <= jstar, whole x-rows of the cube ----------------
+        // ---------------- pass 2: store the candidates of bins <= jstar from the reachable part of the cube ----------------
         int count = 0;
         bool have_tau = false;
         unsigned long long tau_k = ~0ull;
         int tau_v = 0x7fffffff;
         {
             const int s = s_end;
-            int z0 = max(cz - s, 0), z1 = min(cz + s, g.nz - 1);
-            int y0 = max(cy - s, 0), y1 = min(cy + s, g.ny - 1);
-            int xa = max(cx - s, 0), xb = min(cx + s, g.nx - 1);
-            for (int z = z0; z <= z1 && xa <= xb; ++z) {
-                for (int y = y0; y <= y1; ++y) {
-                    size_t rb = ((size_t)z * g.ny + y) * g.nx;
-                    int p0 = g.cell_start[rb + xa], p1 = g.cell_start[rb + xb + 1];
-                    for (int pb = p0; pb < p1; pb += 32) {
+            const int z0 = max(cz - s, 0), z1 = min(cz + s, g.nz - 1), y0 = max(cy - s, 0), y1 = min(cy + s, g.ny - 1);
+            const int Wy = max(y1 - y0 + 1, 0), Wz = max(z1 - z0 + 1, 0);
+            const long long nrows = (long long)Wy * Wz;
+            // every stored candidate has knn_bin(d2) <= jstar, hence d2 below the upper edge of bin jstar (taken 1e-5 wide of
+            // the float arithmetic in knn_bin) and below r2: nothing farther than ub2 can be stored
+            double ub2 = r2;
+            if (jstar < KNN_NB - 1) ub2 = fmin(ub2, ((double)(jstar + 1) / (double)inv_w2) * (1.0 + 1e-5));
+            for (long long j0 = 0; j0 < nrows; j0 += 32) {
+                const long long j = j0 + lane;
+                int p0 = 0, p1 = 0;
+                if (j < nrows) {
+                    const int z = z0 + (int)(j / Wy), y = y0 + (int)(j % Wy);
+                    int xa = cx - s, xb = cx + s;
+                    bool reach = true;
+                    if (isfinite(ub2)) {
+                        const double gy = knn_axis_gap(qy, g.oy, g.cell, y, g.ny), gz = knn_axis_gap(qz, g.oz, g.cell, z, g.nz);
+                        const double rest = ub2 - (gy * gy + gz * gz);
+                        if (rest < 0.0) reach = false;
+                        else {
+                            const double dxm = sqrt(rest) + 1e-6 * g.cell;
+                            xa = max(xa, ibl_cell_coord(qx - dxm, g.ox, g.inv_cell, g.nx));
+                            xb = min(xb, ibl_cell_coord(qx + dxm, g.ox, g.inv_cell, g.nx));
+                            // points are clamped into the boundary cells: a range that ends outside the grid includes them
+                            if (xb < 0) xb = 0;
+                            if (xa > g.nx - 1) xa = g.nx - 1;
+                        }
+                    }
+                    if (reach) knn_segment(g, z, y, xa, xb, p0, p1);
+                }
+                unsigned live = __ballot_sync(0xffffffffu, p1 > p0);
+                while (live) {
+                    const int src = __ffs(live) - 1;
+                    live &= live - 1;
+                    const int a = __shfl_sync(0xffffffffu, p0, src), e = __shfl_sync(0xffffffffu, p1, src);
+                    for (int pb = a; pb < e; pb += 32) {
                         if (count + 32 > CAP) {   // overflow: keep the max_nn best, remember the threshold
                             int n2 = next_pow2_ge32(count);
                             for (int t = count + lane; t < n2; t += 32) { b.key[t] = ~0ull; b.val[t] = 0x7fffffff; }
@@ -254,12 +307,12 @@ __global__ void __launch_bounds__(128) knn_kernel(GridView g, const double *__re
                         bool ok = false;
                         unsigned long long kk = 0;
                         int vv = 0;
-                        if (p < p1) {
+                        if (p < e) {
                             double4 t = g.sorted[p];
                             double d2 = ibl_d2(t.x, t.y, t.z, qx, qy, qz);
                             kk = (unsigned long long)__double_as_longlong(d2);
                             vv = (int)__double_as_longlong(t.w);
-                            ok = d2 < r2 && knn_bin(d2, inv_w) <= jstar &&
+                            ok = d2 < r2 && knn_bin(d2, inv_w2) <= jstar &&
                                  (!have_tau || knn_less(kk, vv, tau_k, tau_v));
                         }
                         unsigned m = __ballot_sync(0xffffffffu, ok);

@@ -46,7 +46,9 @@
 // per (query, split) row: winner of the pool-exhausted fallback (d, idx), number of band candidates, first pool chunk
 struct FSplitOutTC { double d; int idx; int cnt; int first; int pad; };
 // candidate pool: chunk c holds entries[c * TC_CHUNK ..), belongs to row[c], has n[c] entries and continues in next[c]
-struct TcPool { uint32_t *entries; int *row, *n, *next; int *counter; int cap; };
+// Chunks [0, base) are owned statically: chunk r is the FIRST chunk of split-row r (no allocation); the rest of the pool is
+// handed out through `counter`.  base = rows x splits, or 0 when a test hook has capped the pool below that.
+struct TcPool { uint32_t *entries; int *row, *n, *next; int *counter; int cap; int base; };
 
 // ------------------------------------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -57,10 +59,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        // the suspend-time hint lets the warp sleep in hardware instead of re-issuing the test: ten warps share four
+        // schedulers here, and a spinning waiter takes issue slots from the single MMA-issuing thread
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@p bra DONE_%=;\n\t"
         "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity), "r"(2000u) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
@@ -293,7 +297,7 @@ struct TcRowState { int cnt, cur, ccnt, first, n_eval, bi, exhausted; double bes
 __device__ __noinline__ TcRowState tc_push_slow(TcRowState st, const TcPool pool, int row, int t,
                                                 const double *__restrict__ fa_q, const double *__restrict__ fb) {
     if (!st.exhausted) {
-        int c = atomicAdd(pool.counter, 1);
+        int c = pool.base + atomicAdd(pool.counter, 1);
         if (c >= pool.cap) {
             st.exhausted = 1;                             // a thread asks the pool at most once after it runs dry
         } else {
@@ -342,12 +346,16 @@ __device__ __forceinline__ void tc_band_chunk(const float *v, float &m, float E,
     const float r = __fsub_rd(m, E);                      // E = -inf for rows past the end: r = +inf, nothing is recorded
     if (cm >= r) {
         // Hit mask with static register indices, then a short loop that the lanes of the warp run in lock step.
-        unsigned mask = 0;
+        // v[c] >= r  <=>  the sign bit of fl(v[c] - r) is clear (subtraction of finite floats has the exact sign, denormals
+        // are kept).  A funnel shift collects the 32 sign bits, column 0 ending at bit 31: two instructions per column
+        // instead of compare + select + or.
+        unsigned below = 0;
 #pragma unroll
-        for (int c = 0; c < 32; ++c) mask |= (v[c] >= r) ? (1u << c) : 0u;
+        for (int c = 0; c < 32; ++c) below = __funnelshift_l(__float_as_uint(__fsub_rn(v[c], r)), below, 1);
+        unsigned mask = ~below;
         while (mask) {
-            int c = __ffs(mask) - 1;
-            mask &= mask - 1;
+            const int c = __clz(mask);                    // ascending column order
+            mask &= ~(0x80000000u >> c);
             tc_push(rs, pool, row, tb + c, fa_q, fb);
         }
     }
@@ -422,6 +430,7 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
         if (lane == 0 && ntiles > 0) {
             const uint32_t lbo = swap_lbo_sbo ? TC_SBO : TC_LBO, sbo = swap_lbo_sbo ? TC_LBO : TC_SBO;
             mbar_wait(BAR_A, 0);
+            const uint64_t a_desc0 = tc_smem_desc(sA, lbo, sbo), b_desc0 = tc_smem_desc(sB0, lbo, sbo);
             long long w_tempty = 0, w_full = 0;
             const long long loop0 = wait_on ? clock64() : 0;
             for (int it = 0; it < ntiles; ++it) {
@@ -432,13 +441,17 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
                 mbar_wait(BAR_FULL + 8 * s, (it / TC_STAGES) & 1);
                 if (wait_on) { w_tempty += c1 - c0; w_full += clock64() - c1; }
                 tc_fence_after();
-                const uint32_t sB = sB0 + s * TC_TILE_BYTES;
+                // descriptors differ from the precomputed ones only in the 16-byte-unit start address (low 14 bits, no carry
+                // out: shared memory is < 256 KB): one 64-bit add each instead of rebuilding them -- this thread shares its
+                // scheduler with two epilogue warps and every instruction it does not issue is an MMA issued sooner
+                const uint64_t b_off = (uint64_t)((s * TC_TILE_BYTES) >> 4);
                 for (int h = 0; h < nq_here; ++h) {
+                    const uint64_t a_off = (uint64_t)((h * TC_TILE_BYTES) >> 4);
 #pragma unroll
                     for (int k = 0; k < TC_K / 16; ++k) {      // one MMA consumes K = 16 halves = two 16-byte chunks
-                        uint64_t ad = tc_smem_desc(sA + h * TC_TILE_BYTES + k * 2 * TC_LBO, lbo, sbo);
-                        uint64_t bd = tc_smem_desc(sB + k * 2 * TC_LBO, lbo, sbo);
-                        tc_mma_f16(tmem_base + as * (128 * TC_QT) + h * 128, ad, bd, TC_IDESC, k > 0);
+                        const uint64_t k_off = (uint64_t)((k * 2 * TC_LBO) >> 4);
+                        tc_mma_f16(tmem_base + as * (128 * TC_QT) + h * 128, a_desc0 + a_off + k_off, b_desc0 + b_off + k_off,
+                                   TC_IDESC, k > 0);
                     }
                 }
                 tc_commit(BAR_EMPTY + 8 * s);             // smem stage free once these MMAs have read it
@@ -486,6 +499,10 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
             rs.cnt = 0; rs.cur = -1; rs.ccnt = 0; rs.first = -1; rs.n_eval = 0; rs.bi = -1; rs.exhausted = 0; rs.bestd = INFINITY;
             const int row = (int)(q * nsplit + split);
             const double *fa_q = fa + q * 33;
+            if (live && row < pool.base) {                   // this row's first chunk is chunk `row`: no pool traffic for it
+                rs.cur = row; rs.first = row;
+                pool.row[row] = row; pool.next[row] = -1;
+            }
             float va[32], vb[32];
             long long w_tfull = 0;
             const long long eloop0 = wait_on ? clock64() : 0;
@@ -585,7 +602,7 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__
                                                            const float *__restrict__ nb32) {
     const int lane = threadIdx.x & 31;
     const int nwarps = gridDim.x * (blockDim.x >> 5);
-    const int nchunks = min(*pool.counter, pool.cap);
+    const int nchunks = min(pool.base + *pool.counter, pool.cap);
     unsigned long long n_eval = 0;
     for (int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < nchunks; c += nwarps) {
         const int row = pool.row[c], n = pool.n[c];
@@ -727,6 +744,7 @@ static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb,
     const int64_t nrows = na * p.nsplit;
     pool.cap = (int)std::min<int64_t>(nrows + (1 << 18), (int64_t)1 << 24);
     if (g_tc_pool_cap_override > 0) pool.cap = g_tc_pool_cap_override;
+    pool.base = nrows <= pool.cap ? (int)nrows : 0;
     int *pool_meta = nullptr;
     TcChunkRes *res = nullptr;
     IBL_CUDA(ibl_alloc(&pool.entries, (size_t)pool.cap * TC_CHUNK, st));

@@ -462,8 +462,8 @@ __global__ void __launch_bounds__(128) ransac_check_batch_kernel(const RbProb *_
 // FIELD: every problem's grid carries an NN candidate field that covers max_d (the product path).  The ring-search
 // fallback then is not even compiled in, which halves the registers (128 -> 6x) and doubles the resident warps of a kernel
 // whose time is dependent-load latency.
-template <bool FIELD>
-__global__ void __launch_bounds__(SCORE_THREADS, FIELD ? 3 : 1) ransac_count_batch_kernel(const RbProb *__restrict__ probs,
+template <bool FIELD, int MINB>
+__global__ void __launch_bounds__(SCORE_THREADS, MINB) ransac_count_batch_kernel(const RbProb *__restrict__ probs,
                                                                            const RbEntry *__restrict__ entries,
                                                                            const int *__restrict__ n_entries, double max_d,
                                                                            double max_d2, int32_t *__restrict__ inliers) {
@@ -504,14 +504,72 @@ __global__ void __launch_bounds__(SCORE_THREADS, FIELD ? 3 : 1) ransac_count_bat
         for (int it = 0; it < nchunks; ++it) {
             const int64_t base = (int64_t)chunk * PRUNE_CHUNK;
             int cnt = 0;
+            if (FIELD) {
+                // The four points a thread owns in this chunk go through the field lookup TOGETHER, level by level (source
+                // point -> block pointer -> voxel entry -> first candidate -> its coordinates): the kernel's time is the
+                // latency of that dependent chain (ncu: IPC 0.4, 11 warps waiting on a load per issue), and walking the
+                // four chains side by side keeps four loads in flight per thread instead of one.  Same tests in the same
+                // order per point as ibl_any_within_field, so every count is unchanged.
+                constexpr int R = PRUNE_CHUNK / SCORE_THREADS;
+                const NNFieldView &f = g.f;
+                double qx[R], qy[R], qz[R];
+                long long bidx[R];
+                int vox[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const int64_t i = base + r * SCORE_THREADS + threadIdx.x;
+                    bidx[r] = -1; vox[r] = 0;
+                    qx[r] = qy[r] = qz[r] = 0.0;
+                    if (i < n_src) {
+                        ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], qx[r], qy[r], qz[r]);
+                        const double fx = floor((qx[r] - f.ox) * f.inv_c), fy = floor((qy[r] - f.oy) * f.inv_c),
+                                     fz = floor((qz[r] - f.oz) * f.inv_c);
+                        if (fx >= 0.0 && fy >= 0.0 && fz >= 0.0 && fx < (double)f.nvx && fy < (double)f.nvy && fz < (double)f.nvz) {
+                            const int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+                            bidx[r] = ((long long)(iz >> 3) * f.nby + (iy >> 3)) * f.nbx + (ix >> 3);
+                            vox[r] = ((iz & 7) << 6) | ((iy & 7) << 3) | (ix & 7);
+                        }
+                    }
+                }
+                int blk[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) blk[r] = bidx[r] >= 0 ? f.block_ptr[bidx[r]] : -1;
+                uint2 ent4[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) ent4[r] = blk[r] >= 0 ? f.entries[(size_t)blk[r] * 512 + vox[r]] : make_uint2(0u, 0u);
+                int c0[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const bool sure = (ent4[r].y & 0x80000000u) && sure_ok;
+                    const unsigned nc = ent4[r].y & 0x7fffffffu;
+                    c0[r] = (!sure && nc > 0) ? f.cand[ent4[r].x] : -1;
+                    if (sure) { ++cnt; ent4[r].y = 0u; }                  // decided: no candidates left to look at
+                }
+                double4 t0[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) t0[r] = c0[r] >= 0 ? g.sorted[c0[r]] : make_double4(0.0, 0.0, 0.0, 0.0);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    if (c0[r] < 0) continue;
+                    bool hit = ibl_d2(t0[r].x, t0[r].y, t0[r].z, qx[r], qy[r], qz[r]) < max_d2;
+                    const unsigned nc = ent4[r].y & 0x7fffffffu;
+                    const int *c = f.cand + ent4[r].x;
+                    for (unsigned k = 1; k < nc && !hit; ++k) {
+                        const double4 t = g.sorted[c[k]];
+                        hit = ibl_d2(t.x, t.y, t.z, qx[r], qy[r], qz[r]) < max_d2;
+                    }
+                    cnt += hit ? 1 : 0;
+                }
+            } else {
 #pragma unroll 1
-            for (int r = 0; r < PRUNE_CHUNK / SCORE_THREADS; ++r) {
-                int64_t i = base + r * SCORE_THREADS + threadIdx.x;
-                if (i < n_src) {
-                    double x, y, z, bd;
-                    ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
-                    if (FIELD || field) cnt += ibl_any_within_field(g, x, y, z, max_d2, sure_ok) ? 1 : 0;
-                    else if (!FIELD) cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
+                for (int r = 0; r < PRUNE_CHUNK / SCORE_THREADS; ++r) {
+                    int64_t i = base + r * SCORE_THREADS + threadIdx.x;
+                    if (i < n_src) {
+                        double x, y, z, bd;
+                        ibl_xform(T, src[3 * i], src[3 * i + 1], src[3 * i + 2], x, y, z);
+                        if (field) cnt += ibl_any_within_field(g, x, y, z, max_d2, sure_ok) ? 1 : 0;
+                        else cnt += ibl_nn1_thread(g, x, y, z, max_d, max_d2, bd) >= 0 ? 1 : 0;
+                    }
                 }
             }
             cnt = __reduce_add_sync(0xffffffffu, cnt);
@@ -651,6 +709,14 @@ __global__ void __launch_bounds__(FIN_THREADS) ransac_finalize_batch_kernel(cons
 // 1 (default): the count pass stops a hypothesis as soon as it cannot reach the best count so far (exact, see
 // ransac_count_batch_kernel); 0: every validated hypothesis is counted over the whole source (measurement switch).
 static int g_ransac_prune = 1;
+// resident CTAs per SM the field-specialised count kernel is compiled for: 3 (80 registers, a few spills; measured 169 ms per
+// bench pass) or 2 (114 registers, no spills; 231 ms): the extra warps matter more than the spills.
+// IBL_RANSAC_COUNT_MINB overrides (measurement switch).
+static int rb_count_minb() {
+    static int v = 0;
+    if (v == 0) { const char *e = getenv("IBL_RANSAC_COUNT_MINB"); v = (e && atoi(e) == 2) ? 2 : 3; }
+    return v;
+}
 IBL_API int ibl_ransac_set_prune(int on) { g_ransac_prune = on ? 1 : 0; return IBL_OK; }
 
 #define RB_MAX_BLOCK (1 << 20)     // hypotheses per problem per round, at most
@@ -735,9 +801,12 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
             // hypotheses is only known on the device here, so it is filled in after the read-back
             IBL_PROF(IBL_PROF_RANSAC_SCORE, st, 0.0);
             if (all_field)
-                ransac_count_batch_kernel<true><<<IBL_SMS * 6, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
+                if (rb_count_minb() == 2)
+                    ransac_count_batch_kernel<true, 2><<<IBL_SMS * 4, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
+                else
+                    ransac_count_batch_kernel<true, 3><<<IBL_SMS * 6, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
             else
-                ransac_count_batch_kernel<false><<<IBL_SMS * 4, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
+                ransac_count_batch_kernel<false, 1><<<IBL_SMS * 4, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
             IBL_LAUNCH_CHECK();
         }
         int nval = 0;

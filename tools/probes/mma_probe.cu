@@ -77,6 +77,112 @@ __global__ void __launch_bounds__(64, 1) mma_kernel(Variant v, int rounds, int s
     }
 }
 
+
+// ---- part 2: the same MMA stream with the matcher's other traffic running beside it ------------------------------------------
+// warp 0 lane 0: MMAs (kernel's layout).  copy != 0: warp 1 lane 0 streams 28 KB bulk copies global -> shared (a buffer the MMAs
+// do not read), `copy` in flight, like the matcher's producer.  readers: warps 2 .. 2+readers-1 read accumulator columns back
+// with tcgen05.ld.32x32b.x32 in a loop, like the epilogue.  Both run until the MMA thread has finished.
+#define LD_X32(r, taddr)                                                                                                   \
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                  \
+                 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];" \
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),     \
+                   "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),         \
+                   "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),        \
+                   "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])                      \
+                 : "r"(taddr) : "memory")
+
+__global__ void __launch_bounds__(320, 1) mma_mix_kernel(int rounds, int copy, int readers, const uint8_t *gsrc,
+                                                         unsigned long long *clk, unsigned *sink) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint32_t slot;
+    __shared__ __align__(8) unsigned long long bar, cbar[4];
+    __shared__ volatile int done;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t TB = 28672;
+    for (uint32_t i = threadIdx.x; i < 7 * TB / 4; i += blockDim.x) reinterpret_cast<uint32_t *>(smem)[i] = 0;
+    if (threadIdx.x == 0) {
+        done = 0;
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)) : "memory");
+        for (int k = 0; k < 4; ++k) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&cbar[k])) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tm = slot;
+    if (warp == 0) {
+        if (lane == 0) {
+            const uint32_t sA0 = smem_u32(smem), sA1 = sA0 + TB, sB = sA0 + 2 * TB;
+            unsigned long long t0 = clock64();
+            for (int r = 0; r < rounds; ++r) {
+                const uint32_t acc = tm + (r & 1) * 256;
+                for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                    for (int k = 0; k < 7; ++k)
+                        mma_f16(acc + h * 128, smem_desc((h ? sA1 : sA0) + k * 256, 128, 1792, 0), smem_desc(sB + k * 256, 128, 1792, 0), k > 0);
+                }
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
+            asm volatile("{\n\t.reg .pred p;\n\tW_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t@p bra D_%=;\n\tbra W_%=;\n\tD_%=:\n\t}"
+                         ::"r"(smem_u32(&bar)) : "memory");
+            clk[blockIdx.x] = clock64() - t0;
+            done = 1;
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && copy > 0) {
+            // `copy` stages of 28 KB; a stage is re-issued as soon as its previous copy has landed
+            unsigned ph[4] = {0, 0, 0, 0};
+            const uint8_t *src = gsrc + (size_t)blockIdx.x * 4 * TB;
+            for (int k = 0; k < copy; ++k) {
+                asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(&cbar[k])), "r"(TB) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(smem_u32(smem) + (3 + k) * TB), "l"(src + (size_t)k * TB), "r"(TB), "r"(smem_u32(&cbar[k])) : "memory");
+            }
+            unsigned long long n = 0;
+            while (!done) {
+                for (int k = 0; k < copy && !done; ++k) {
+                    asm volatile("{\n\t.reg .pred p;\n\tW_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra D_%=;\n\tbra W_%=;\n\tD_%=:\n\t}"
+                                 ::"r"(smem_u32(&cbar[k])), "r"(ph[k]) : "memory");
+                    ph[k] ^= 1; ++n;
+                    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(&cbar[k])), "r"(TB) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 ::"r"(smem_u32(smem) + (3 + k) * TB), "l"(src + (size_t)k * TB), "r"(TB), "r"(smem_u32(&cbar[k])) : "memory");
+                }
+            }
+            for (int k = 0; k < copy; ++k)      // drain: no copy may be in flight when the CTA exits
+                asm volatile("{\n\t.reg .pred p;\n\tW_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra D_%=;\n\tbra W_%=;\n\tD_%=:\n\t}"
+                             ::"r"(smem_u32(&cbar[k])), "r"(ph[k]) : "memory");
+            clk[gridDim.x + blockIdx.x] = n;
+        }
+    } else if (warp - 2 < readers) {
+        const int w = warp - 2;
+        const uint32_t lane_base = tm + ((uint32_t)((w & 3) * 32) << 16) + (uint32_t)((w >> 2) * 128);
+        uint32_t a[32];
+        unsigned acc = 0, n = 0;
+        while (!done) {
+            for (int c = 0; c < 4; ++c) {
+                LD_X32(a, lane_base + (n & 1) * 256 + c * 32);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                acc ^= a[0] ^ a[31];
+            }
+            ++n;
+        }
+        if (acc == 0x12345678u) sink[0] = acc;
+        if (lane == 0) clk[2 * gridDim.x + blockIdx.x * 8 + w] = n;
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tm) : "memory");
+    }
+}
+
 int main() {
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
@@ -109,6 +215,33 @@ int main() {
             printf("{\"variant\": \"%s\", \"b_operand\": \"%s\", \"rounds\": %d, \"clk_per_mma_avg\": %.1f, \"clk_per_mma_max\": %.1f, "
                    "\"frac_of_64clk_floor\": %.3f}\n", v.name, same_b ? "one tile for both accumulators" : "two tiles",
                    rounds, per, (double)mx / ((double)rounds * 14), 64.0 / per);
+            fflush(stdout);
+        }
+    }
+    // part 2
+    {
+        const int rounds2 = 2000;
+        uint8_t *gsrc; unsigned *sink; unsigned long long *clk2;
+        cudaMalloc(&gsrc, (size_t)sms * 4 * 28672); cudaMemset(gsrc, 0, (size_t)sms * 4 * 28672);
+        cudaMalloc(&sink, 4); cudaMalloc(&clk2, sizeof(*clk2) * sms * 10);
+        size_t smem = 7 * 28672 + 1024;
+        cudaFuncSetAttribute(mma_mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        const int cfgs[][2] = {{0, 0}, {4, 0}, {0, 4}, {0, 8}, {4, 8}, {2, 8}, {1, 8}};
+        for (auto &c : cfgs) {
+            cudaMemset(clk2, 0, sizeof(*clk2) * sms * 10);
+            mma_mix_kernel<<<sms, 320, smem>>>(rounds2, c[0], c[1], gsrc, clk2, sink);
+            cudaError_t e = cudaDeviceSynchronize();
+            if (e != cudaSuccess) { printf("{\"mix\": [%d, %d], \"error\": \"%s\"}\n", c[0], c[1], cudaGetErrorString(e)); return 1; }
+            static unsigned long long h[148 * 10 + 64];
+            cudaMemcpy(h, clk2, sizeof(*clk2) * sms * 10, cudaMemcpyDeviceToHost);
+            double sum = 0, copies = 0, reads = 0;
+            for (int i = 0; i < sms; ++i) { sum += h[i]; copies += h[sms + i]; }
+            for (int i = 0; i < sms * 8; ++i) reads += h[2 * sms + i];
+            double per = sum / sms / (rounds2 * 14.0);
+            double clk_total = sum / sms;
+            printf("{\"mix\": \"MMAs + %d bulk copies of 28 KB in flight + %d TMEM-reading warps\", \"clk_per_mma\": %.1f, "
+                   "\"copy_bytes_per_clk_per_sm\": %.1f, \"tmem_read_bytes_per_clk_per_sm\": %.1f}\n", c[0], c[1], per,
+                   copies / sms * 28672.0 / clk_total, reads / sms * (4 * 32 * 32 * 4.0) / clk_total);
             fflush(stdout);
         }
     }

@@ -364,9 +364,13 @@ def run_frames(args, cfg):
         log["on"], log["rows"] = keep, []
         st0 = dict(om.cache_stats)
         e0.record()
+        walls = []
         for _ in range(steps):
-            step(host_inputs, nworkers)
+            t_s = time.perf_counter()
+            step(host_inputs, nworkers)                 # ends with the D2H read of the step's poses: the host time is the step's
+            walls.append(round((time.perf_counter() - t_s) * 1e3, 1))
         e1.record()
+        counted["step_wall_ms"] = walls
         torch.cuda.synchronize()
         counted["launches"] = K.launch_count() - n0      # libibl.so kernels launched inside this timed region
         log["on"] = False
@@ -398,6 +402,7 @@ def run_frames(args, cfg):
     start = cursor["i"]
     ms, hit_warm = timed(False, args.steps, profiler=args.profiler_range, start=start, keep=True)
     launches = counted["launches"]
+    walls_value = counted["step_wall_ms"]
     rows = log["rows"]
     # per-kernel breakdown and the roofline kernel's launch time: the same steps again with CUDA events around every
     # kernel group (csrc/prof.cu), ONE frame in flight -- with several frames in flight an event pair on one stream also
@@ -408,6 +413,7 @@ def run_frames(args, cfg):
     prof = K.prof_read()
     K.prof_enable(False)
     ms_e2e, _ = timed(True, args.steps, start=start)
+    walls_e2e = counted["step_wall_ms"]
     clk = clocks.stop()
     total_frames = B * args.steps * world
     value = total_frames / (ms / 1e3)
@@ -490,7 +496,8 @@ def run_frames(args, cfg):
                                         "python_gc": "frozen and disabled after warm-up",
                                         "parallelism": f"frames sharded over {world} rank(s)"}),
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 56,
-                    "ms_per_step": ms_e2e / args.steps},
+                    "ms_per_step": ms_e2e / args.steps, "step_wall_ms": walls_e2e},
+            "step_wall_ms": walls_value,                 # host wall time of every timed step (rank 0): outliers are visible
             "gpu_launches": launches, "launches_per_frame": launches / max(B * args.steps, 1), "clocks": clk,
             "ransac": ransac, "gt": gt, "memory_cache_hit_rate": hit_warm, "memory_cache": om.cache_info(),
             "cold": {"value": B * cold_steps * world / (ms_cold / 1e3), "unit": "frames/s", "frames_per_rank": B * cold_steps,

@@ -27,6 +27,7 @@
 #include <cmath>
 
 #include <cuda_fp16.h>
+#include <cub/cub.cuh>
 
 #include "ibl_common.cuh"
 
@@ -265,10 +266,16 @@ __global__ void __launch_bounds__(256) feat_tc_rows32_kernel(const double *__res
 // In score space the band is E (s' = -D/2, and nearest-neighbour candidates are those with D32 <= min D32 + 2E).
 #define TC_ERR_A 1.53e-5f
 #define TC_ERR_B 2.92e-5f
-__device__ __forceinline__ float feat_tc_err(float an, float bmax) {
-    float lin = __fadd_ru(__fmul_ru(TC_ERR_A, an), __fmul_ru(TC_ERR_B, bmax));
-    float sq = __fmul_ru(4.0e-7f, __fadd_ru(__fsqrt_ru(an), __fsqrt_ru(bmax)));
-    return __fadd_ru(__fadd_ru(lin, sq), 1.0e-4f);
+// The bound as a sum of a query part and a target part, every operation rounded up:
+//     |D32 - d|  <=  err_a(an) + err_b(bn),   err_a = A an + 4e-7 sqrt(an),   err_b = B bn + 4e-7 sqrt(bn) + 1e-4.
+// It is monotone in bn, so a target tile whose rows all have |b|^2 <= bn_tile can use err_b(bn_tile) instead of err_b(max over
+// ALL targets): with the targets of a cached pack sorted by norm, most tiles get a band several times narrower (the median
+// centred FPFH norm of a memory cloud is ~9x below the maximum).
+__device__ __forceinline__ float feat_tc_err_a(float an) {
+    return __fadd_ru(__fmul_ru(TC_ERR_A, an), __fmul_ru(4.0e-7f, __fsqrt_ru(an)));
+}
+__device__ __forceinline__ float feat_tc_err_b(float bn) {
+    return __fadd_ru(__fadd_ru(__fmul_ru(TC_ERR_B, bn), __fmul_ru(4.0e-7f, __fsqrt_ru(bn))), 1.0e-4f);
 }
 // monotone float <-> int key so that atomicMax(int) orders floats
 __device__ __forceinline__ int f2key(float f) { int b = __float_as_int(f); return b >= 0 ? b : b ^ 0x7fffffff; }
@@ -295,7 +302,8 @@ __device__ int g_tc_wait_on;
 struct TcRowState { int cnt, cur, ccnt, first, n_eval, bi, exhausted; double bestd; };
 // slow path of tc_push: the row needs a (new) chunk, or the pool has run dry
 __device__ __noinline__ TcRowState tc_push_slow(TcRowState st, const TcPool pool, int row, int t,
-                                                const double *__restrict__ fa_q, const double *__restrict__ fb) {
+                                                const double *__restrict__ fa_q, const double *__restrict__ fb,
+                                                const int *__restrict__ perm) {
     if (!st.exhausted) {
         int c = pool.base + atomicAdd(pool.counter, 1);
         if (c >= pool.cap) {
@@ -307,8 +315,9 @@ __device__ __noinline__ TcRowState tc_push_slow(TcRowState st, const TcPool pool
         }
     }
     if (st.exhausted) {                                   // exact evaluation right here (correct, just slow)
-        double de = feat_tc_exact(fa_q, fb + (size_t)t * 33);
-        if (de < st.bestd || (de == st.bestd && t < st.bi)) { st.bestd = de; st.bi = t; }
+        const int to = perm ? perm[t] : t;              // the target's ORIGINAL index: exact rows and ties go by it
+        double de = feat_tc_exact(fa_q, fb + (size_t)to * 33);
+        if (st.bi < 0 || de < st.bestd || (de == st.bestd && to < st.bi)) { st.bestd = de; st.bi = to; }
         ++st.n_eval;
         return st;
     }
@@ -317,22 +326,25 @@ __device__ __noinline__ TcRowState tc_push_slow(TcRowState st, const TcPool pool
     return st;                                            // by value: the row state stays in registers on the fast path
 }
 __device__ __forceinline__ void tc_push(TcRowState &st, const TcPool &pool, int row, int t, const double *__restrict__ fa_q,
-                                        const double *__restrict__ fb) {
+                                        const double *__restrict__ fb, const int *__restrict__ perm) {
     ++st.cnt;
     if (st.cur >= 0 && st.ccnt < TC_CHUNK) {              // fast path: one store
         pool.entries[(size_t)st.cur * TC_CHUNK + st.ccnt] = (uint32_t)t;
         ++st.ccnt;
     } else {
-        st = tc_push_slow(st, pool, row, t, fa_q, fb);
+        st = tc_push_slow(st, pool, row, t, fa_q, fb, perm);
     }
 }
 
-// One chunk of 32 scores of this thread's query row, columns tb .. tb+31: raise the running row maximum m (tree of
-// independent FMNMX, not a 32-deep dependent chain), then record every column inside the band E below the maximum SO
-// FAR.  The running maximum only grows, so the final band [m_final - E, m_final] is a subset of what gets recorded; the
-// surplus (targets that were near-records when they streamed by) only costs exact evaluations later.
-__device__ __forceinline__ void tc_band_chunk(const float *v, float &m, float E, int tb, TcRowState &rs, const TcPool &pool,
-                                              int row, const double *__restrict__ fa_q, const double *__restrict__ fb) {
+// One chunk of 32 scores of this thread's query row, columns tb .. tb+31.  With S the true score of a column and s' the
+// computed one, |S - s'| <= eh for every column of this tile (eh = half the tile's band).  L = max over the columns seen so
+// far of (s' - their eh) is a lower bound of the best TRUE score, so the best column -- and every exact tie with it -- has
+// s' >= L - eh when it streams by: those are recorded.  L only grows, so the recorded set is a superset of what the final L
+// would select; the surplus only costs exact evaluations later.  With one eh for all tiles this is the plain running
+// maximum m = L + eh and the band [m - 2 eh, m].  The chunk maximum is a tree of independent FMNMX, not a 32-deep chain.
+__device__ __forceinline__ void tc_band_chunk(const float *v, float &L, float eh, int tb, TcRowState &rs, const TcPool &pool,
+                                              int row, const double *__restrict__ fa_q, const double *__restrict__ fb,
+                                              const int *__restrict__ perm) {
     float t[16];
 #pragma unroll
     for (int c = 0; c < 16; ++c) t[c] = fmaxf(v[2 * c], v[2 * c + 1]);
@@ -342,10 +354,9 @@ __device__ __forceinline__ void tc_band_chunk(const float *v, float &m, float E,
         for (int c = 0; c < w; ++c) t[c] = fmaxf(t[c], t[c + w]);
     }
     const float cm = t[0];
-    m = fmaxf(m, cm);
-    const float r = __fsub_rd(m, E);                      // E = -inf for rows past the end: r = +inf, nothing is recorded
+    L = fmaxf(L, __fsub_rd(cm, eh));                      // eh = -inf for rows past the end: L = r = +inf, nothing is recorded
+    const float r = __fsub_rd(L, eh);
     if (cm >= r) {
-        // Hit mask with static register indices, then a short loop that the lanes of the warp run in lock step.
         // v[c] >= r  <=>  the sign bit of fl(v[c] - r) is clear (subtraction of finite floats has the exact sign, denormals
         // are kept).  A funnel shift collects the 32 sign bits, column 0 ending at bit 31: two instructions per column
         // instead of compare + select + or.
@@ -356,13 +367,17 @@ __device__ __forceinline__ void tc_band_chunk(const float *v, float &m, float E,
         while (mask) {
             const int c = __clz(mask);                    // ascending column order
             mask &= ~(0x80000000u >> c);
-            tc_push(rs, pool, row, tb + c, fa_q, fb);
+            tc_push(rs, pool, row, tb + c, fa_q, fb, perm);
         }
     }
 }
 
 // MODE 0: dump s' to dump[q][ld] (debug).  MODE 1: running row maximum + band candidates in one pass.
-// grid = (ceil(query tiles / TC_QT), splits); split y owns target tiles [y * tiles_per_split, ...).
+// grid = (ceil(query tiles / TC_QT), splits); split y owns the target tiles y, y + nsplit, y + 2 nsplit, ... and visits them
+// with a stride coprime to their number (tc_tile_of).  With the targets of a cached pack sorted by norm, a contiguous range
+// walked in order made the scores of a row climb steadily -- every new record is a band candidate -- while interleaved splits
+// and a scattered visiting order show every row a tile from its own norm range within the first few tiles, so its lower
+// bound L is close to final early on.  For unsorted targets the order is irrelevant.
 // A CTA keeps TC_QT = 2 query tiles resident and gives each its own pair of TMEM accumulators and its own four epilogue
 // warps (a warp may only read the TMEM lanes 32 (warp % 4) .. +31, i.e. a thread is one query row): every streamed target
 // tile feeds 2 x 7 MMAs, and the eight epilogue warps -- two per scheduler -- overlap each other's dependent-issue latency.
@@ -375,7 +390,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const uint8_t *__restrict__ Bimg, int64_t nb, int n_btiles,
                int tiles_per_split, int nsplit, const float *__restrict__ an32, const unsigned *__restrict__ bmax_bits,
                const double *__restrict__ fa, const double *__restrict__ fb,
-               FSplitOutTC *__restrict__ out, TcPool pool, float *__restrict__ dump, int64_t dump_ld, int swap_lbo_sbo) {
+               FSplitOutTC *__restrict__ out, TcPool pool, float *__restrict__ dump, int64_t dump_ld, int swap_lbo_sbo,
+               const float *__restrict__ tile_eb, const int *__restrict__ perm) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sA = smem_u32(smem);                   // TC_QT query tiles
     const uint32_t sB0 = sA + TC_QT * TC_TILE_BYTES;
@@ -387,9 +403,18 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int qt0 = blockIdx.x * TC_QT, split = blockIdx.y;
     const int nq_here = min(TC_QT, n_qtiles - qt0);       // query tiles this CTA really has (the last CTA may have one)
-    const int t_begin = split * tiles_per_split;
-    const int t_end = min(n_btiles, t_begin + tiles_per_split);
-    const int ntiles = max(0, t_end - t_begin);
+    (void)tiles_per_split;
+    const int ntiles = split < n_btiles ? (n_btiles - split + nsplit - 1) / nsplit : 0;
+    // visiting stride: ~0.618 ntiles, made coprime to ntiles (then it -> (it * stride) % ntiles is a permutation)
+    int vstride = max(1, (int)(0.6180339887f * (float)ntiles));
+    while (vstride > 1) {
+        int x = vstride, y = ntiles;
+        while (y) { const int r = x % y; x = y; y = r; }
+        if (x == 1) break;
+        --vstride;
+    }
+    // every role walks the same sequence: vcur = (it * vstride) % ntiles, kept incrementally; tile = split + nsplit * vcur
+#define TC_NEXT_TILE(vcur) do { (vcur) += vstride; if ((vcur) >= ntiles) (vcur) -= ntiles; } while (0)
     constexpr int W_PROD = 4 * TC_QT, W_MMA = 4 * TC_QT + 1;
     const bool wait_on = (MODE == 1) && g_tc_wait_on != 0;
 
@@ -415,13 +440,15 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
             for (int h = 0; h < nq_here; ++h)
                 bulk_g2s(sA + h * TC_TILE_BYTES, Aimg + (size_t)(qt0 + h) * TC_TILE_BYTES, TC_TILE_BYTES, BAR_A);
             long long w_empty = 0;
+            int vcur = 0;
             for (int it = 0; it < ntiles; ++it) {
                 int s = it % TC_STAGES;
                 const long long c0 = wait_on ? clock64() : 0;
                 mbar_wait(BAR_EMPTY + 8 * s, ((it / TC_STAGES) & 1) ^ 1);
                 if (wait_on) w_empty += clock64() - c0;
                 mbar_expect_tx(BAR_FULL + 8 * s, TC_TILE_BYTES);
-                bulk_g2s(sB0 + s * TC_TILE_BYTES, Bimg + (size_t)(t_begin + it) * TC_TILE_BYTES, TC_TILE_BYTES, BAR_FULL + 8 * s);
+                bulk_g2s(sB0 + s * TC_TILE_BYTES, Bimg + (size_t)(split + nsplit * vcur) * TC_TILE_BYTES, TC_TILE_BYTES, BAR_FULL + 8 * s);
+                TC_NEXT_TILE(vcur);
             }
             if (wait_on) atomicAdd(&g_tc_wait[7], (unsigned long long)w_empty);
         }
@@ -472,11 +499,13 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
         const bool live = h < nq_here && q < na;
         const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(h * 128);
         if (MODE == 0) {
+            int vcur = 0;
             for (int it = 0; it < ntiles; ++it) {
                 int as = it & 1;
                 mbar_wait(BAR_TFULL + 8 * as, (it >> 1) & 1);
                 tc_fence_after();
-                const int64_t t0 = (int64_t)(t_begin + it) * TC_M;
+                const int64_t t0 = (int64_t)(split + nsplit * vcur) * TC_M;
+                TC_NEXT_TILE(vcur);
 #pragma unroll 1
                 for (int ch = 0; ch < 4; ++ch) {
                     float v[32];
@@ -493,8 +522,11 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
             // Single pass: running maximum + band recording (tc_band_chunk).  The TMEM reads are software-pipelined over two
             // register buffers -- the load of chunk c+1 is in flight while chunk c is processed -- and the accumulator is handed
             // back to the MMA warp as soon as its last chunk has been READ, before that chunk is processed.
-            float m = -INFINITY;
-            const float E = live ? feat_tc_err(an32[q], __uint_as_float(*bmax_bits)) : -INFINITY;
+            // tile_eb (cached packs): the target part of the band per TARGET TILE, from the largest norm inside the tile;
+            // otherwise one value from the largest target norm of all
+            float L = -INFINITY;
+            const float ea = live ? feat_tc_err_a(an32[q]) : -INFINITY;
+            const float eb_all = feat_tc_err_b(__uint_as_float(*bmax_bits));
             TcRowState rs;
             rs.cnt = 0; rs.cur = -1; rs.ccnt = 0; rs.first = -1; rs.n_eval = 0; rs.bi = -1; rs.exhausted = 0; rs.bestd = INFINITY;
             const int row = (int)(q * nsplit + split);
@@ -512,17 +544,21 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
                 tc_fence_after();
                 tc_ld32_issue(lane_base, va);
             }
+            int vcur = 0;
 #pragma unroll 1
             for (int it = 0; it < ntiles; ++it) {
                 const int as = it & 1;
                 const uint32_t acc = lane_base + as * (128 * TC_QT);
-                const int tb = (t_begin + it) * TC_M;               // padding rows score far below any band
+                const int tile = split + nsplit * vcur;
+                TC_NEXT_TILE(vcur);
+                const int tb = tile * TC_M;                         // padding rows score far below any band
+                const float eh = __fmul_ru(0.5f, __fadd_ru(ea, tile_eb ? tile_eb[tile] : eb_all));
                 tc_ld_wait32(va); tc_ld32_issue(acc + 32, vb);
-                tc_band_chunk(va, m, E, tb, rs, pool, row, fa_q, fb);
+                tc_band_chunk(va, L, eh, tb, rs, pool, row, fa_q, fb, perm);
                 tc_ld_wait32(vb); tc_ld32_issue(acc + 64, va);
-                tc_band_chunk(vb, m, E, tb + 32, rs, pool, row, fa_q, fb);
+                tc_band_chunk(vb, L, eh, tb + 32, rs, pool, row, fa_q, fb, perm);
                 tc_ld_wait32(va); tc_ld32_issue(acc + 96, vb);
-                tc_band_chunk(va, m, E, tb + 64, rs, pool, row, fa_q, fb);
+                tc_band_chunk(va, L, eh, tb + 64, rs, pool, row, fa_q, fb, perm);
                 tc_ld_wait32(vb);
                 tc_fence_before();
                 mbar_arrive(BAR_TEMPTY + 8 * as);
@@ -533,7 +569,7 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
                     tc_fence_after();
                     tc_ld32_issue(lane_base + (as ^ 1) * (128 * TC_QT), va);
                 }
-                tc_band_chunk(vb, m, E, tb + 96, rs, pool, row, fa_q, fb);
+                tc_band_chunk(vb, L, eh, tb + 96, rs, pool, row, fa_q, fb, perm);
             }
             if (wait_on && threadIdx.x == 0) {
                 atomicAdd(&g_tc_wait[5], (unsigned long long)(clock64() - eloop0));
@@ -555,6 +591,7 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
     }
+#undef TC_NEXT_TILE
 }
 
 struct TcChunkRes { double d; int idx; int pad; };
@@ -588,38 +625,51 @@ __device__ __forceinline__ float feat_tc_d32(const float *__restrict__ a, const 
     return __fadd_rn(s, __fmul_rn(d, d));
 }
 
-// One warp per pool chunk (<= 64 candidates, two per lane).  Phase 1: the fp32 difference distance of every candidate with
-// its error radius; U = the smallest upper bound in the chunk.  Phase 2: only candidates whose lower bound does not exceed U
-// -- the only ones that can be the chunk's nearest or tie with it -- get the oracle's f64 evaluation, reduced in the oracle's
-// order (distance, then lower index) into res[chunk].  Work is balanced by ENTRY count, however skewed the candidates are
-// over the queries (planar patches: thousands of near-identical rows inside one band).
+// EIGHT LANES per pool chunk (<= 64 candidates, up to eight per lane), four chunks per warp.  Phase 1: the fp32 difference
+// distance of every candidate with its error radius; U = the smallest upper bound in the chunk.  Phase 2: only candidates
+// whose lower bound does not exceed U -- the only ones that can be the chunk's nearest or tie with it -- get the oracle's f64
+// evaluation, reduced in the oracle's order (distance, then lower index) into res[chunk].
+// A chunk holds 8-9 candidates on average (every split-row owns at least one chunk) and about one survivor, and the kernel's
+// time is the latency of its gathers: with a whole warp per chunk a quarter of the lanes worked in phase 1 and one in
+// thirty in phase 2; four chunks side by side put four times as many gathers in flight per warp.
 // The band provably holds the exact nearest neighbour, so the chunk of a row with ONE candidate needs no work at all here:
 // d = -1 marks "not evaluated"; the merge evaluates it only if another split of the same query also has candidates.
+#define TC_EVAL_GS 8                                     // lanes per chunk
+#define TC_EVAL_R (TC_CHUNK / TC_EVAL_GS)                // candidates per lane
 __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__restrict__ parts, TcPool pool, int nsplit,
                                                            TcChunkRes *__restrict__ res, const double *__restrict__ fa,
                                                            const double *__restrict__ fb, const float *__restrict__ a32,
                                                            const float *__restrict__ b32, const float *__restrict__ na32,
-                                                           const float *__restrict__ nb32) {
-    const int lane = threadIdx.x & 31;
+                                                           const float *__restrict__ nb32, const int *__restrict__ perm) {
+    // pool entries, b32 and nb32 are in the TARGET IMAGE's row order; perm (may be NULL = identity) maps such a position to
+    // the target's original index, which addresses fb and decides exact ties
+    const int lane = threadIdx.x & 31, grp = lane / TC_EVAL_GS, gl = lane % TC_EVAL_GS;
+    constexpr int GPW = 32 / TC_EVAL_GS;                  // chunks per warp
     const int nwarps = gridDim.x * (blockDim.x >> 5);
     const int nchunks = min(pool.base + *pool.counter, pool.cap);
     unsigned long long n_eval = 0;
-    for (int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < nchunks; c += nwarps) {
-        const int row = pool.row[c], n = pool.n[c];
+    for (int c0 = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * GPW; c0 < nchunks; c0 += nwarps * GPW) {
+        const int c = c0 + grp;
+        const bool valid = c < nchunks;
+        const int row = valid ? pool.row[c] : 0;
+        int n = valid ? pool.n[c] : 0;
         const uint32_t *e = pool.entries + (size_t)c * TC_CHUNK;
-        if (parts[row].cnt == 1) {
-            if (lane == 0) { TcChunkRes r; r.d = -1.0; r.idx = (int)e[0]; r.pad = 0; res[c] = r; }
-            continue;
+        bool single = false;
+        if (valid && parts[row].cnt == 1) {
+            if (gl == 0) { TcChunkRes r; r.d = -1.0; r.idx = perm ? perm[e[0]] : (int)e[0]; r.pad = 0; res[c] = r; }
+            single = true;
+            n = 0;
         }
         const int64_t q = row / nsplit;
         const float *aq = a32 + q * TC_R32;
-        const float naq = na32[q];
-        int t[2] = {-1, -1};
-        float lo[2] = {INFINITY, INFINITY};
+        const float naq = n > 0 ? na32[q] : 0.f;
+        int t[TC_EVAL_R];
+        float lo[TC_EVAL_R];
         float U = INFINITY;
 #pragma unroll
-        for (int r = 0; r < 2; ++r) {
-            const int k = r * 32 + lane;
+        for (int r = 0; r < TC_EVAL_R; ++r) {
+            t[r] = -1; lo[r] = INFINITY;
+            const int k = r * TC_EVAL_GS + gl;
             if (k < n) {
                 t[r] = (int)e[k];
                 const float s = feat_tc_d32(aq, b32 + (size_t)t[r] * TC_R32);
@@ -632,24 +682,25 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__
                 }
             }
         }
-        for (int o = 16; o; o >>= 1) U = fminf(U, __shfl_xor_sync(0xffffffffu, U, o));
+        for (int o = TC_EVAL_GS / 2; o; o >>= 1) U = fminf(U, __shfl_xor_sync(0xffffffffu, U, o));
         const double *a = fa + (size_t)q * 33;
         double bestd = INFINITY;
         int bi = -1;
 #pragma unroll
-        for (int r = 0; r < 2; ++r) {
+        for (int r = 0; r < TC_EVAL_R; ++r) {
             if (t[r] >= 0 && lo[r] <= U) {
-                double de = feat_tc_exact(a, fb + (size_t)t[r] * 33);
-                if (bi < 0 || de < bestd || (de == bestd && t[r] < bi)) { bestd = de; bi = t[r]; }
+                const int to = perm ? perm[t[r]] : t[r];
+                double de = feat_tc_exact(a, fb + (size_t)to * 33);
+                if (bi < 0 || de < bestd || (de == bestd && to < bi)) { bestd = de; bi = to; }
                 ++n_eval;
             }
         }
-        for (int o = 16; o; o >>= 1) {
+        for (int o = TC_EVAL_GS / 2; o; o >>= 1) {
             double od = __shfl_xor_sync(0xffffffffu, bestd, o);
             int oi = __shfl_xor_sync(0xffffffffu, bi, o);
             if (oi >= 0 && (bi < 0 || od < bestd || (od == bestd && oi < bi))) { bestd = od; bi = oi; }
         }
-        if (lane == 0) { TcChunkRes r; r.d = bestd; r.idx = bi; r.pad = 0; res[c] = r; }
+        if (gl == 0 && valid && !single) { TcChunkRes r; r.d = bestd; r.idx = bi; r.pad = 0; res[c] = r; }
     }
     if (n_eval) atomicAdd(&g_tc_stats[1], n_eval);
 }
@@ -658,7 +709,7 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__
 // winner of its on-the-spot evaluations.
 __global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int64_t na, int nsplit, TcPool pool,
                                      const TcChunkRes *__restrict__ res, const double *__restrict__ fa,
-                                     const double *__restrict__ fb, int32_t *__restrict__ nn) {
+                                     const double *__restrict__ fb, int32_t *__restrict__ nn, const int *__restrict__ perm) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= na) return;
     long long total = 0;
@@ -666,7 +717,10 @@ __global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int6
     for (int s = 0; s < nsplit; ++s) {
         const FSplitOutTC p = parts[i * nsplit + s];
         total += p.cnt;
-        if (p.cnt == 1) only = p.first >= 0 ? (int)pool.entries[(size_t)p.first * TC_CHUNK] : p.idx;
+        if (p.cnt == 1) {
+            if (p.first >= 0) { const int t = (int)pool.entries[(size_t)p.first * TC_CHUNK]; only = perm ? perm[t] : t; }
+            else only = p.idx;                            // evaluated on the spot (pool exhausted): already an original index
+        }
     }
     if (total == 0) { nn[i] = -1; return; }
     if (total == 1) { nn[i] = only; return; }            // the single band candidate IS the exact nearest neighbour
@@ -735,7 +789,9 @@ IBL_API int ibl_feature_nn_set_pool_chunks(int chunks) {
 // float bits of max |b|^2; fa / fb the raw f64 rows, a32 / b32 / na32 / nb32 their fp32 copies and norm bounds.
 static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb, const float *an, const unsigned *bmax_bits,
                      const double *fa, const double *fb, const float *a32, const float *b32, const float *na32,
-                     const float *nb32, int32_t *nn, cudaStream_t st) {
+                     const float *nb32, int32_t *nn, cudaStream_t st, const float *tile_eb = nullptr, const int *perm = nullptr) {
+    // B, b32, nb32 are in the target image's row order; tile_eb / perm (both or neither): a cached pack whose target rows are
+    // sorted by norm -- per-tile band terms and the map from image row to original row (fb is in original order)
     TcPlan p = tc_plan(na, nb);
     FSplitOutTC *parts = nullptr;
     IBL_CUDA(ibl_alloc(&parts, (size_t)na * p.nsplit, st));
@@ -758,15 +814,15 @@ static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb,
         // nested scope: the tcgen05 kernel alone, with the flops it ISSUES (depth 112 over the padded tiles)
         IBL_PROF(IBL_PROF_FEATURE_GEMM, st, 2.0 * TC_K * (double)p.na_pad * (double)p.nb_pad);
         feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, p.qtiles, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, bmax_bits,
-                                                            fa, fb, parts, pool, nullptr, 0, 0);
+                                                            fa, fb, parts, pool, nullptr, 0, 0, tile_eb, perm);
         IBL_LAUNCH_CHECK();
     }
     {
         // the chunk count lives on the device (no host sync): a fixed grid strides over it
-        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32);
+        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm);
         IBL_LAUNCH_CHECK();
     }
-    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn);
+    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn, perm);
     IBL_LAUNCH_CHECK();
     ibl_free(pool.entries, st); ibl_free(pool_meta, st); ibl_free(res, st); ibl_free(parts, st);
     return IBL_OK;
@@ -823,11 +879,47 @@ struct ibl_feature_pack {
     const double *f;           // the caller's rows [n][33] (kept alive by the caller)
     double *mu;                // [33]
     unsigned *mx;              // [0] max |row|^2 as query, [1] max |row|^2 as target, [2] 2 * max |f - mu| (float bits)
-    uint8_t *img0, *img1;      // role 0 (query) / role 1 (target) tile images
-    float *an32;               // [n_pad] squared norms of the scaled rows
-    float *rows32, *nrm32;     // second filter
+    uint8_t *img0, *img1;      // role 0 (query) tile image in ORIGINAL row order / role 1 (target) image SORTED by norm
+    float *an32;               // [n_pad] squared norms of the scaled rows (original order)
+    float *rows32, *nrm32;     // second filter, original order (the pack as the query side)
+    float *rows32s, *nrm32s;   // second filter, sorted order (the pack as the target side)
+    int *perm;                 // [n_pad] sorted position -> original row (identity on the padding rows)
+    float *tile_eb;            // [n_pad / 128] target part of the band of each sorted target tile (feat_tc_err_b of its largest norm)
     cudaStream_t stream;
 };
+
+__global__ void feat_tc_iota_kernel(int *v, int64_t n) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) v[i] = (int)i;
+}
+// Row i of the sorted target image = row perm[i] of the image in original order (padding rows stay where they are), with its
+// fp32 row and norm bound; every tile keeps the largest scaled norm of its rows (float bits, atomicMax).
+__global__ void __launch_bounds__(128) feat_tc_sort_rows_kernel(int64_t n, int64_t n_pad, int *__restrict__ perm,
+                                                                const uint8_t *__restrict__ img1o, uint8_t *__restrict__ img1s,
+                                                                const float *__restrict__ rows32, const float *__restrict__ nrm32,
+                                                                float *__restrict__ rows32s, float *__restrict__ nrm32s,
+                                                                const float *__restrict__ an32, unsigned *__restrict__ tile_bn) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n_pad) return;
+    if (i >= n) perm[i] = (int)i;
+    const int64_t src = perm[i];
+    const uint4 *s = reinterpret_cast<const uint4 *>(img1o + tc_row_offset(src));
+    uint4 *d = reinterpret_cast<uint4 *>(img1s + tc_row_offset(i));
+#pragma unroll
+    for (int c = 0; c < TC_KCH; ++c) d[c * (TC_LBO / 16)] = s[c * (TC_LBO / 16)];
+    if (i < n) {
+        const float4 *rs = reinterpret_cast<const float4 *>(rows32 + src * TC_R32);
+        float4 *rd = reinterpret_cast<float4 *>(rows32s + i * TC_R32);
+#pragma unroll
+        for (int c = 0; c < TC_R32 / 4; ++c) rd[c] = rs[c];
+        nrm32s[i] = nrm32[src];
+        atomicMax(tile_bn + i / TC_M, __float_as_uint(an32[src]));
+    }
+}
+__global__ void feat_tc_tile_eb_kernel(const unsigned *__restrict__ tile_bn, float *__restrict__ tile_eb, int ntiles) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < ntiles) tile_eb[t] = feat_tc_err_b(__uint_as_float(tile_bn[t]));
+}
 
 __global__ void feat_tc_headroom_kernel(unsigned *maxabs_bits) {
     float m = __uint_as_float(*maxabs_bits);
@@ -919,10 +1011,37 @@ IBL_API int ibl_feature_pack_create(const double *f, int64_t n, ibl_feature_pack
     IBL_LAUNCH_CHECK();
     feat_tc_headroom_kernel<<<1, 1, 0, st>>>(pk->mx + 2);
     IBL_LAUNCH_CHECK();
-    feat_tc_pack_both_kernel<<<(unsigned)(pk->n_pad / 128), 128, 0, st>>>(f, n, pk->n_pad, pk->mu, pk->mx + 2, pk->img0, pk->img1,
+    uint8_t *img1o = nullptr;                              // target image in original order: only the source of the sorted one
+    IBL_CUDA(ibl_alloc(&img1o, img, st));
+    feat_tc_pack_both_kernel<<<(unsigned)(pk->n_pad / 128), 128, 0, st>>>(f, n, pk->n_pad, pk->mu, pk->mx + 2, pk->img0, img1o,
                                                                          pk->an32, pk->mx, pk->mx + 1, pk->rows32, pk->nrm32,
                                                                          pk->mx + 3);
     IBL_LAUNCH_CHECK();
+    // target role: rows sorted by their scaled norm (non-negative floats order like their bit patterns), so that the rows of a
+    // tile have similar norms and the tile's band term is tight
+    const int ntiles = (int)(pk->n_pad / TC_M);
+    IBL_CUDA(ibl_alloc(&pk->rows32s, (size_t)n * TC_R32, st));
+    IBL_CUDA(ibl_alloc(&pk->nrm32s, (size_t)n, st));
+    IBL_CUDA(ibl_alloc(&pk->perm, (size_t)pk->n_pad, st));
+    IBL_CUDA(ibl_alloc(&pk->tile_eb, (size_t)ntiles, st));
+    unsigned *keys_out = nullptr, *tile_bn = nullptr; int *iota = nullptr;
+    IBL_CUDA(ibl_alloc(&keys_out, (size_t)n, st));
+    IBL_CUDA(ibl_alloc(&iota, (size_t)n, st));
+    IBL_CUDA(ibl_alloc(&tile_bn, (size_t)ntiles, st));
+    IBL_CUDA(cudaMemsetAsync(tile_bn, 0, sizeof(unsigned) * ntiles, st));
+    feat_tc_iota_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(iota, n);
+    IBL_LAUNCH_CHECK();
+    size_t tmp_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, reinterpret_cast<const unsigned *>(pk->an32), keys_out, iota, pk->perm, (int)n, 0, 32, st);
+    void *tmp = nullptr;
+    IBL_CUDA(cudaMallocAsync(&tmp, tmp_bytes ? tmp_bytes : 1, st));
+    IBL_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, reinterpret_cast<const unsigned *>(pk->an32), keys_out, iota, pk->perm, (int)n, 0, 32, st));
+    feat_tc_sort_rows_kernel<<<(unsigned)(pk->n_pad / 128), 128, 0, st>>>(n, pk->n_pad, pk->perm, img1o, pk->img1, pk->rows32, pk->nrm32,
+                                                                         pk->rows32s, pk->nrm32s, pk->an32, tile_bn);
+    IBL_LAUNCH_CHECK();
+    feat_tc_tile_eb_kernel<<<(unsigned)((ntiles + 127) / 128), 128, 0, st>>>(tile_bn, pk->tile_eb, ntiles);
+    IBL_LAUNCH_CHECK();
+    ibl_free(tmp, st); ibl_free(keys_out, st); ibl_free(iota, st); ibl_free(tile_bn, st); ibl_free(img1o, st);
     *out = pk;
     return IBL_OK;
 }
@@ -931,7 +1050,8 @@ IBL_API void ibl_feature_pack_destroy(ibl_feature_pack_t *pk) {
     if (!pk) return;
     cudaStream_t st = pk->stream;
     ibl_free(pk->mu, st); ibl_free(pk->mx, st); ibl_free(pk->img0, st); ibl_free(pk->img1, st); ibl_free(pk->an32, st);
-    ibl_free(pk->rows32, st); ibl_free(pk->nrm32, st);
+    ibl_free(pk->rows32, st); ibl_free(pk->nrm32, st); ibl_free(pk->rows32s, st); ibl_free(pk->nrm32s, st);
+    ibl_free(pk->perm, st); ibl_free(pk->tile_eb, st);
     free(pk);
 }
 
@@ -960,7 +1080,8 @@ IBL_API int ibl_feature_match_packed(const double *fa, int64_t na, const ibl_fea
         feat_tc_pack_both_kernel<<<(unsigned)(na_pad / 128), 128, 0, st>>>(fa, na, na_pad, pk->mu, pk->mx + 2, A0, A1, an, mx, mx + 1,
                                                                           a32, na32, d_flag ? d_flag : mx + 2);
         IBL_LAUNCH_CHECK();
-        rc = tc_search(A0, na, pk->img1, pk->n, an, pk->mx + 1, fa, pk->f, a32, pk->rows32, na32, pk->nrm32, nn_ab, st);
+        rc = tc_search(A0, na, pk->img1, pk->n, an, pk->mx + 1, fa, pk->f, a32, pk->rows32s, na32, pk->nrm32s, nn_ab, st,
+                       pk->tile_eb, pk->perm);
         if (rc == IBL_OK)
             rc = tc_search(pk->img0, pk->n, A1, na, pk->an32, mx + 1, pk->f, fa, pk->rows32, a32, pk->nrm32, na32, nn_ba, st);
     }
@@ -1001,7 +1122,7 @@ IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double 
     IBL_LAUNCH_CHECK();
     dim3 grid((p.qtiles + TC_QT - 1) / TC_QT, p.nsplit);
     feat_tc_kernel<0><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, p.qtiles, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1,
-                                                        fa, fb, nullptr, TcPool{}, scores, nb, swap_lbo_sbo);
+                                                        fa, fb, nullptr, TcPool{}, scores, nb, swap_lbo_sbo, nullptr, nullptr);
     IBL_LAUNCH_CHECK();
     if (center_out) {                                     // debug hook only: read the scale back and publish it
         unsigned bits = 0;

@@ -586,6 +586,10 @@ __global__ void __launch_bounds__(SCORE_THREADS, MINB) ransac_count_batch_kernel
     }
 }
 
+// Tried and rejected (round 2): a WARP per hypothesis (no block barrier, no idle threads during the Kabsch solve).  A round
+// holds only a few thousand validated hypotheses, whose cost ranges from one chunk (pruned) to the whole source: with 3552
+// resident warps each warp gets about one hypothesis and the launch lasts as long as its single longest one -- 31 ms per
+// bench step against 17 ms for the CTA-per-hypothesis kernel above, which finishes a long hypothesis eight times sooner.
 // which contender does work item `item` belong to: prefix[c] <= item < prefix[c+1]
 __device__ __forceinline__ int rb_find(const int64_t *__restrict__ prefix, int n, int64_t item) {
     int lo = 0, hi = n;

@@ -462,7 +462,7 @@ class ObjectMemory():
         b = n * 24 * 2                                         # union points + colours
         if feats is not None:
             tgt, f = feats
-            b += n * (24 * 3 + 264 + 448 + 144 + 16 + 40)      # normals, gradients, a spare row; FPFH; packs; fp32 rows; grid rows
+            b += n * (24 * 3 + 264 + 448 + 2 * 148 + 4 + 16 + 40)      # normals, gradients, a spare row; FPFH; packs; fp32 rows + norms in both orders, permutation; grid rows
             for g in tgt._grids.values():
                 if isinstance(g, K.Grid):
                     b += g.nnfield_bytes

@@ -634,8 +634,7 @@ __device__ __forceinline__ float feat_tc_d32(const float *__restrict__ a, const 
 // thirty in phase 2; four chunks side by side put four times as many gathers in flight per warp.
 // The band provably holds the exact nearest neighbour, so the chunk of a row with ONE candidate needs no work at all here:
 // d = -1 marks "not evaluated"; the merge evaluates it only if another split of the same query also has candidates.
-#define TC_EVAL_GS 8                                     // lanes per chunk
-#define TC_EVAL_R (TC_CHUNK / TC_EVAL_GS)                // candidates per lane
+template <int TC_EVAL_GS>                                // lanes per chunk
 __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__restrict__ parts, TcPool pool, int nsplit,
                                                            TcChunkRes *__restrict__ res, const double *__restrict__ fa,
                                                            const double *__restrict__ fb, const float *__restrict__ a32,
@@ -643,6 +642,7 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__
                                                            const float *__restrict__ nb32, const int *__restrict__ perm) {
     // pool entries, b32 and nb32 are in the TARGET IMAGE's row order; perm (may be NULL = identity) maps such a position to
     // the target's original index, which addresses fb and decides exact ties
+    constexpr int TC_EVAL_R = TC_CHUNK / TC_EVAL_GS;      // candidates per lane
     const int lane = threadIdx.x & 31, grp = lane / TC_EVAL_GS, gl = lane % TC_EVAL_GS;
     constexpr int GPW = 32 / TC_EVAL_GS;                  // chunks per warp
     const int nwarps = gridDim.x * (blockDim.x >> 5);
@@ -819,7 +819,11 @@ static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb,
     }
     {
         // the chunk count lives on the device (no host sync): a fixed grid strides over it
-        feat_tc_eval_kernel<<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm);
+        static int gs = 0;
+        if (gs == 0) { const char *e = getenv("IBL_TC_EVAL_GS"); gs = e ? atoi(e) : 8; }
+        if (gs == 4) feat_tc_eval_kernel<4><<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm);
+        else if (gs == 16) feat_tc_eval_kernel<16><<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm);
+        else feat_tc_eval_kernel<8><<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm);
         IBL_LAUNCH_CHECK();
     }
     feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn, perm);

@@ -509,6 +509,12 @@ class ObjectMemory():
                 used -= c.pop(next(iter(c)))[3]            # least recently used first
                 self.cache_stats["evictions"] = self.cache_stats.get("evictions", 0) + 1
             c[key] = (pcd, mean, feats, nbytes)
+            # The entry's tensors were carved out of the block this stream had reserved for its transients.  Reserve again
+            # NOW (the cold path: a no-op when enough of the pool is free, otherwise the driver maps memory here): a warm frame
+            # that finds the pool full makes the stream-ordered allocator grow in the middle of a step, which was measured to
+            # stall all four frame streams for ~650 ms (pool 80 192 -> 80 224 MiB, step 150 -> 855 ms).
+            if self.scratch_bytes_per_stream and not os.environ.get("IBL_NO_RESERVE"):
+                K.reserve_scratch(self.scratch_bytes_per_stream)
             return c[key][:3]
 
     # ------------------------------------------------------------------------------------------ localise

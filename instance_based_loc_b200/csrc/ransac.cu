@@ -448,6 +448,72 @@ __global__ void __launch_bounds__(128) ransac_check_batch_kernel(const RbProb *_
     if (ok) { RbEntry e; e.p = (int)blockIdx.y; e.k = k; entries[base + __popc(m & ((1u << lane) - 1u))] = e; }
 }
 
+// The check in two kernels (checkers on).  The fused kernel above needs 140 registers for the inlined Jacobi-Kabsch, so only
+// ~12 % of the warp slots are occupied while 99 % of the hypotheses die in the EdgeLength test, which needs six gathered
+// points and a few square roots (ncu: latency-bound, L1 39 %, issue 23 %).  Kernel A does sample + gather + EdgeLength at
+// full occupancy and appends the survivors to a list; kernel B solves the Kabsch and applies the Distance test for those
+// only, one survivor per thread with every lane of a warp busy.  Same arithmetic per hypothesis, same set of validated
+// hypotheses (the list order is arbitrary in both versions; the host sorts).
+__global__ void __launch_bounds__(256) ransac_edge_batch_kernel(const RbProb *__restrict__ probs, double edge_thr,
+                                                                RbEntry *__restrict__ edge_entries, int *__restrict__ n_edge) {
+    const RbProb *P = probs + blockIdx.y;
+    const int H = P->H;
+    if ((int64_t)blockIdx.x * 256 >= H) return;
+    const int k = blockIdx.x * 256 + threadIdx.x;
+    bool ok = false;
+    if (k < H) {
+        double s[9], t[9];
+        gather_sample(P->src, P->tgt, P->corres, P->n_corres, nullptr, P->seed, P->h0 + k, s, t);
+        ok = true;
+        for (int i = 0; i < 3; ++i)
+            for (int j = i + 1; j < 3; ++j) {
+                double a[3] = {s[3 * i] - s[3 * j], s[3 * i + 1] - s[3 * j + 1], s[3 * i + 2] - s[3 * j + 2]};
+                double b[3] = {t[3 * i] - t[3 * j], t[3 * i + 1] - t[3 * j + 1], t[3 * i + 2] - t[3 * j + 2]};
+                double ds = sqrt(ibl_dot(a, a)), dt = sqrt(ibl_dot(b, b));
+                if (ds < dt * edge_thr || dt < ds * edge_thr) ok = false;
+            }
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, ok);
+    if (m == 0) return;
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(n_edge, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (ok) { RbEntry e; e.p = (int)blockIdx.y; e.k = k; edge_entries[base + __popc(m & ((1u << lane) - 1u))] = e; }
+}
+__global__ void __launch_bounds__(128) ransac_kabsch_batch_kernel(const RbProb *__restrict__ probs, double dist_thr,
+                                                                  const RbEntry *__restrict__ edge_entries,
+                                                                  const int *__restrict__ n_edge, RbEntry *__restrict__ entries,
+                                                                  int *__restrict__ n_entries) {
+    const int n = *n_edge;
+    for (int base_i = blockIdx.x * 128; base_i < n; base_i += gridDim.x * 128) {      // uniform per warp
+        const int i = base_i + threadIdx.x;
+        bool ok = false;
+        RbEntry ent = {0, 0};
+        if (i < n) {
+            ent = edge_entries[i];
+            const RbProb *P = probs + ent.p;
+            double s[9], t[9], T[16];
+            gather_sample(P->src, P->tgt, P->corres, P->n_corres, nullptr, P->seed, P->h0 + ent.k, s, t);
+            ibl_kabsch3(s, t, T);
+            ok = true;
+            for (int j = 0; j < 3; ++j) {
+                double qx, qy, qz;
+                ibl_xform(T, s[3 * j], s[3 * j + 1], s[3 * j + 2], qx, qy, qz);
+                double d[3] = {t[3 * j] - qx, t[3 * j + 1] - qy, t[3 * j + 2] - qz};
+                if (sqrt(ibl_dot(d, d)) > dist_thr) ok = false;
+            }
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (m == 0) continue;
+        const int lane = threadIdx.x & 31;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(n_entries, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (ok) entries[base + __popc(m & ((1u << lane) - 1u))] = ent;
+    }
+}
+
 // Inlier count of the validated hypotheses, with an exact early exit.  Only a hypothesis whose count reaches the running
 // maximum can change the RANSAC state, and the running maximum never falls below the count `thr` of the
 // best hypothesis of the earlier rounds.  A CTA takes one hypothesis at a time (persistent grid over the entry list, whose
@@ -716,6 +782,12 @@ static int g_ransac_prune = 1;
 // resident CTAs per SM the field-specialised count kernel is compiled for: 3 (80 registers, a few spills; measured 169 ms per
 // bench pass) or 2 (114 registers, no spills; 231 ms): the extra warps matter more than the spills.
 // IBL_RANSAC_COUNT_MINB overrides (measurement switch).
+// the check as two kernels (1, default) or fused (0); IBL_RANSAC_CHECK_SPLIT overrides (measurement switch)
+static int rb_check_split() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("IBL_RANSAC_CHECK_SPLIT"); v = (e && atoi(e) == 0) ? 0 : 1; }
+    return v;
+}
 static int rb_count_minb() {
     static int v = 0;
     if (v == 0) { const char *e = getenv("IBL_RANSAC_COUNT_MINB"); v = (e && atoi(e) == 2) ? 2 : 3; }
@@ -763,9 +835,10 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
     bool all_field = true;
     for (int p = 0; p < P; ++p)
         if (hs[p].active && !(problems[p].grid_ransac->has_field && max_d <= problems[p].grid_ransac->field.max_d)) all_field = false;
-    RbProb *d_probs = nullptr; int *d_n = nullptr;
+    RbProb *d_probs = nullptr; int *d_n = nullptr, *d_ne = nullptr;
     IBL_CUDA(ibl_alloc(&d_probs, (size_t)P, st));
     IBL_CUDA(ibl_alloc(&d_n, 1, st));
+    IBL_CUDA(ibl_alloc(&d_ne, 1, st));
     std::vector<RbEntry> h_ent, sel;
     std::vector<int32_t> h_inl, h_inl2, h_cinl;
     std::vector<int64_t> sel_prefix;
@@ -794,11 +867,21 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
         IBL_CUDA(ibl_alloc(&d_inl, (size_t)cap, st));
         IBL_CUDA(cudaMemcpyAsync(d_probs, hp.data(), sizeof(RbProb) * P, cudaMemcpyHostToDevice, st));
         IBL_CUDA(cudaMemsetAsync(d_n, 0, sizeof(int), st));
+        RbEntry *d_edge = nullptr;
         {
             IBL_PROF(IBL_PROF_RANSAC_CHECK, st, 157.0 * (double)cap);
-            ransac_check_batch_kernel<<<dim3((unsigned)((maxH + 127) / 128), (unsigned)P), 128, 0, st>>>(d_probs, edge_thr, max_d,
-                                                                                                      use_checkers, d_ent, d_n);
-            IBL_LAUNCH_CHECK();
+            if (use_checkers && rb_check_split()) {
+                IBL_CUDA(ibl_alloc(&d_edge, (size_t)cap, st));
+                IBL_CUDA(cudaMemsetAsync(d_ne, 0, sizeof(int), st));
+                ransac_edge_batch_kernel<<<dim3((unsigned)((maxH + 255) / 256), (unsigned)P), 256, 0, st>>>(d_probs, edge_thr, d_edge, d_ne);
+                IBL_LAUNCH_CHECK();
+                ransac_kabsch_batch_kernel<<<IBL_SMS * 4, 128, 0, st>>>(d_probs, max_d, d_edge, d_ne, d_ent, d_n);
+                IBL_LAUNCH_CHECK();
+            } else {
+                ransac_check_batch_kernel<<<dim3((unsigned)((maxH + 127) / 128), (unsigned)P), 128, 0, st>>>(d_probs, edge_thr, max_d,
+                                                                                                          use_checkers, d_ent, d_n);
+                IBL_LAUNCH_CHECK();
+            }
         }
         {
             // work figure: the un-pruned pass (every validated hypothesis over its whole source); the number of validated
@@ -909,7 +992,7 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
                 cands[p].clear();
             }
         }
-        ibl_free(d_ent, st); ibl_free(d_inl, st);
+        ibl_free(d_ent, st); ibl_free(d_inl, st); ibl_free(d_edge, st);
         if (rc < 0) break;
         for (int p = 0; p < P; ++p) {
             if (hp[p].H == 0) continue;
@@ -920,6 +1003,6 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
     for (int p = 0; p < P; ++p)
         if (h_results[p].status == 0)
             h_results[p].drawn = std::max<int64_t>(std::min(max_iteration, std::max<int64_t>(hs[p].est_k, 0)), 0);
-    ibl_free(d_probs, st); ibl_free(d_n, st);
+    ibl_free(d_probs, st); ibl_free(d_n, st); ibl_free(d_ne, st);
     return rc;
 }

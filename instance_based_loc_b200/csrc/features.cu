@@ -162,7 +162,13 @@ __device__ void pair_features(const double *p1, const double *n1, const double *
     double na[3] = {n1[0], n1[1], n1[2]}, nb[3] = {n2[0], n2[1], n2[2]};
     double angle1 = dot3(n1, d) / f[3];
     double angle2 = dot3(n2, d) / f[3];
-    if (acos(fabs(angle1)) > acos(fabs(angle2))) {
+    // Open3D compares acos(|angle1|) > acos(|angle2|).  acos falls with slope <= -1 on [0, 1], so when the arguments differ
+    // by more than 1e-12 the two arc cosines differ by more than that too -- far above any rounding of either library's
+    // acos -- and the comparison of the arguments decides; only a near-tie pays for the two f64 arc cosines (25 % of this
+    // kernel's instructions).  (Arguments above 1 give NaN in both forms of the test: NaN > x is false, as is x < NaN.)
+    const double c1 = fabs(angle1), c2 = fabs(angle2);
+    const bool swap = fabs(c1 - c2) > 1e-12 && c1 <= 1.0 && c2 <= 1.0 ? (c1 < c2) : (acos(c1) > acos(c2));
+    if (swap) {
         for (int k = 0; k < 3; ++k) { na[k] = n2[k]; nb[k] = n1[k]; d[k] *= -1.0; }
         f[2] = -angle2;
     } else {
@@ -280,11 +286,21 @@ __global__ void __launch_bounds__(128) fpfh_kernel(int64_t n, const int32_t *__r
         }
         __syncwarp();
         double acc = 0.0, acc32 = 0.0, bsum = 0.0;
+        // Two-deep software pipeline over the neighbours: the distance / index of neighbour k+2 and the SPFH row of neighbour
+        // k+1 are in flight while neighbour k is processed (ncu: 45 % of the stall samples sat on the first use of these
+        // three dependent loads).  Slots past the end read row 0, which is valid memory and never used.
+        const int64_t nb0 = i * (int64_t)max_nn;
+        double d_n1 = 1 < cnt ? nbr_d2[nb0 + 1] : 0.0, d_n2 = 2 < cnt ? nbr_d2[nb0 + 2] : 0.0;
+        int q_n1 = 1 < cnt ? nbr_idx[nb0 + 1] : 0, q_n2 = 2 < cnt ? nbr_idx[nb0 + 2] : 0;
+        double s_n1 = spfh[(size_t)q_n1 * 33 + lane];
         for (int k = 1; k < cnt; ++k) {
-            double dist = nbr_d2[i * max_nn + k];
+            const double dist = d_n1, sk = s_n1;
+            d_n1 = d_n2; q_n1 = q_n2;
+            s_n1 = spfh[(size_t)q_n1 * 33 + lane];
+            d_n2 = k + 2 < cnt ? nbr_d2[nb0 + k + 2] : 0.0;           // after the shift: d_n1 / q_n1 / s_n1 = neighbour k+1, d_n2 / q_n2 = k+2
+            q_n2 = k + 2 < cnt ? nbr_idx[nb0 + k + 2] : 0;
             if (dist == 0.0) continue;           // uniform across the warp
-            size_t q = (size_t)nbr_idx[i * max_nn + k];
-            double v = fpfh_quot(spfh[q * 33 + lane], dist);
+            double v = fpfh_quot(sk, dist);
             acc = __dadd_rn(acc, v);
             vals[wib][lane] = v;
             __syncwarp();

@@ -471,13 +471,18 @@ def run_frames(args, cfg):
                             "kernel's event time / the sum over all kernel groups",
                 "ms_per_step_instrumented": ms_prof / args.steps}
     if gemm and gemm["ms"] > 0:
-        tiles = gemm["work"] / (2.0 * 112 * 128 * 128)
-        floor_ms = tiles * 1024 / 148 / (float(clk["sm_mhz"] or 1965.0) * 1e3)
+        # the kernel's own floor: its 128x128x16 MMAs back to back at the measured dense rate (tools/probes/mma_probe.cu: 64 clk
+        # per MMA on zero operands; the measured bf16 peak corresponds to ~90 clk per MMA on real data, which is what the
+        # kernel's MMA thread sees inside its tile loop, profiles/r02_tc_wait_after.json)
+        floor_ms = gemm["work"] / (tensor_peak * 1e12) * 1e3
         roofline["gemm_kernel"] = {"kernel": "feat_tc_kernel<1> (tcgen05 kind::f16, one pass)", "launches": gemm["launches"],
                                    "avg_launch_ms": gemm["ms"] / gemm["launches"],
                                    "issued_tflops": gemm["work"] / gemm["ms"] / 1e9,
                                    "issued_frac_of_tensor_peak": gemm["work"] / gemm["ms"] / 1e9 / tensor_peak,
-                                   "tmem_read_floor_ms_total": floor_ms, "frac_of_tmem_read_floor": floor_ms / gemm["ms"]}
+                                   "mma_floor_ms_total_at_measured_peak": floor_ms,
+                                   "note": "issued flops = 2 * 112 * padded rows * padded columns (the depth-112 split GEMM); the "
+                                           "rest of the launch time is per-CTA prologue, wave quantisation and the epilogue's "
+                                           "candidate path (DESIGN.md 4.1)"}
     bounds = _profile_json("r02_kernel_bounds.json")      # per kernel group: what it is bound by, from ncu (tools/ncu_summary.py)
     kernels = {}
     for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"]):

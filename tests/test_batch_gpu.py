@@ -183,6 +183,33 @@ def test_feature_match_packed_equals_generic(K, na, nb):
     assert int(flag.item()) != 0
 
 
+def test_feature_match_packed_sorted_targets_ties_and_exhausted_pool(K):
+    """The pack's target rows are sorted by norm inside the library (per-tile bands): ties between exact duplicates must still
+    go to the lowest ORIGINAL index, in the chunked path, in the single-candidate shortcut and when the candidate pool runs
+    dry (exact evaluation on the spot).  Many duplicated rows with very different norms, pool capped to a few chunks."""
+    rng = np.random.default_rng(11)
+    base = rng.gamma(2.0, 12.0, (25, 33)) * rng.uniform(0.2, 3.0, (25, 1))      # prototypes with a 15x spread of norms
+    nb, na = 3000, 700
+    pick_b = rng.integers(0, 25, nb)
+    fb = base[pick_b] + (rng.random((nb, 1)) < 0.5) * rng.normal(0, 0.8, (nb, 33))   # half of the rows are EXACT copies of a prototype
+    fa = base[rng.integers(0, 25, na)] + (rng.random((na, 1)) < 0.5) * rng.normal(0, 0.8, (na, 33))
+    A, B = dev(fa), dev(fb)
+    want_ab = K.feature_nn(A, B).cpu().numpy()
+    want_ba = K.feature_nn(B, A).cpu().numpy()
+    d = ((fa[:, None, :] - fb[None, :, :]) ** 2).sum(-1)
+    assert np.array_equal(want_ab, d.argmin(1))             # numpy's argmin takes the first (lowest) index among exact ties
+    pack = K.FeaturePack(B)
+    try:
+        for chunks in (0, 8):                               # default pool, then one that runs dry at once
+            K.feature_nn_set_pool_chunks(chunks)
+            ab, ba, flag = K.feature_match_packed(A, pack)
+            assert int(flag.item()) == 0
+            assert np.array_equal(ab.cpu().numpy(), want_ab), chunks
+            assert np.array_equal(ba.cpu().numpy(), want_ba), chunks
+    finally:
+        K.feature_nn_set_pool_chunks(0)
+
+
 def test_shared_knn_search_equals_separate_searches(K):
     """normals (Hybrid 0.1 / 30), colour gradients (0.15 / 30) and FPFH (0.25 / 100) derived from ONE 0.25 / 100 search are
     the neighbour lists of their own searches: same counts, same indices in the same order."""

@@ -308,7 +308,12 @@ def run_frames(args, cfg):
     pinned = [{k: torch.from_numpy(np.ascontiguousarray(fr[k])).pin_memory() for k in keys} for fr in frames]
     frame_bytes = [sum(t.numel() * t.element_size() for t in fr.values()) for fr in pinned]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    gathered = [torch.zeros((B, 7), dtype=torch.float64, device=dev) for _ in range(world)]
+    # The poses of a step are all-gathered ASYNCHRONOUSLY (NCCL's own stream) and only waited for at the end of the timed
+    # region: frames are independent, so nothing on the path needs the other ranks' results, and a per-step wait made every
+    # step last as long as the slowest rank's 16 frames (measured at N = 8: steps of ~175 ms against ~150 ms at N = 1, the
+    # mean plus ~1.4 sigma of the per-step spread -- that, not host contention, was the scaling loss; `taskset -c 0-3` at
+    # N = 1 costs nothing).
+    pending = []
     t_setup = time.perf_counter() - t_setup
     cursor = {"i": 0}
     log = {"on": False, "rows": []}
@@ -340,13 +345,19 @@ def run_frames(args, cfg):
                           file=sys.stderr, flush=True)
         out = torch.from_numpy(np.stack([r[0] for r in res])).to(dev)
         if world > 1:                                   # the only traffic that crosses NVLink: 56 B per frame
-            dist.all_gather(gathered, out)
+            bufs = [torch.empty((B, 7), dtype=torch.float64, device=dev) for _ in range(world)]
+            pending.append((dist.all_gather(bufs, out, async_op=True), bufs, out))
         host = out.cpu()                                # D2H of the step's result
         if log["on"]:
             log["rows"].extend(zip(idx, res))
         return host, idx
 
     counted = {"launches": 0}
+
+    def drain():
+        for w_, _, _ in pending:
+            w_.wait()
+        del pending[:]
 
     def timed(host_inputs, steps, nworkers=None, profiler=False, start=0, keep=False, before=None):
         cursor["i"] = (start - B) % n_pool
@@ -356,6 +367,7 @@ def run_frames(args, cfg):
         if profiler:                                    # ncu --profile-from-start off: capture the timed region only
             torch.cuda.synchronize()
             torch.cuda.cudart().cudaProfilerStart()
+        drain()                                         # gathers of the untimed steps before this point
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -369,6 +381,7 @@ def run_frames(args, cfg):
             t_s = time.perf_counter()
             step(host_inputs, nworkers)                 # ends with the D2H read of the step's poses: the host time is the step's
             walls.append(round((time.perf_counter() - t_s) * 1e3, 1))
+        drain()                                         # every rank's poses of every step have arrived: inside the timed region
         e1.record()
         counted["step_wall_ms"] = walls
         torch.cuda.synchronize()

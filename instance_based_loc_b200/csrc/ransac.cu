@@ -532,18 +532,26 @@ template <bool FIELD, int MINB>
 __global__ void __launch_bounds__(SCORE_THREADS, MINB) ransac_count_batch_kernel(const RbProb *__restrict__ probs,
                                                                            const RbEntry *__restrict__ entries,
                                                                            const int *__restrict__ n_entries, double max_d,
-                                                                           double max_d2, int32_t *__restrict__ inliers) {
+                                                                           double max_d2, int32_t *__restrict__ inliers,
+                                                                           int *__restrict__ next_entry) {
     __shared__ GridView g;
     __shared__ double T[16];
     __shared__ int sc[2][SCORE_THREADS / 32];
+    __shared__ int s_e;
     const int n = *n_entries;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     int cur_p = -1;
+    // Entries are handed out through a device counter, not round-robin: a hypothesis costs anything between one chunk (pruned
+    // at once) and the whole source, and with a static assignment the launch lasted as long as its unluckiest CTA.
 #pragma unroll 1
-    for (int e = blockIdx.x; e < n; e += gridDim.x) {
+    for (;;) {
+        __syncthreads();                                   // the previous hypothesis' readers of g / T / sc / s_e are done
+        if (threadIdx.x == 0) s_e = atomicAdd(next_entry, 1);
+        __syncthreads();
+        const int e = s_e;
+        if (e >= n) break;
         const RbEntry ent = entries[e];
         const RbProb *P = probs + ent.p;
-        __syncthreads();                                   // the previous hypothesis' readers of g / T / sc are done
         if (ent.p != cur_p) {
             for (int k = threadIdx.x; k < (int)(sizeof(GridView) / 4); k += SCORE_THREADS)
                 reinterpret_cast<int *>(&g)[k] = reinterpret_cast<const int *>(&P->g)[k];
@@ -835,10 +843,11 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
     bool all_field = true;
     for (int p = 0; p < P; ++p)
         if (hs[p].active && !(problems[p].grid_ransac->has_field && max_d <= problems[p].grid_ransac->field.max_d)) all_field = false;
-    RbProb *d_probs = nullptr; int *d_n = nullptr, *d_ne = nullptr;
+    RbProb *d_probs = nullptr; int *d_n = nullptr, *d_ne = nullptr, *d_next = nullptr;
     IBL_CUDA(ibl_alloc(&d_probs, (size_t)P, st));
     IBL_CUDA(ibl_alloc(&d_n, 1, st));
     IBL_CUDA(ibl_alloc(&d_ne, 1, st));
+    IBL_CUDA(ibl_alloc(&d_next, 1, st));
     std::vector<RbEntry> h_ent, sel;
     std::vector<int32_t> h_inl, h_inl2, h_cinl;
     std::vector<int64_t> sel_prefix;
@@ -887,13 +896,14 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
             // work figure: the un-pruned pass (every validated hypothesis over its whole source); the number of validated
             // hypotheses is only known on the device here, so it is filled in after the read-back
             IBL_PROF(IBL_PROF_RANSAC_SCORE, st, 0.0);
+            IBL_CUDA(cudaMemsetAsync(d_next, 0, sizeof(int), st));
             if (all_field)
                 if (rb_count_minb() == 2)
-                    ransac_count_batch_kernel<true, 2><<<IBL_SMS * 4, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
+                    ransac_count_batch_kernel<true, 2><<<IBL_SMS * 4, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl, d_next);
                 else
-                    ransac_count_batch_kernel<true, 3><<<IBL_SMS * 6, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
+                    ransac_count_batch_kernel<true, 3><<<IBL_SMS * 6, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl, d_next);
             else
-                ransac_count_batch_kernel<false, 1><<<IBL_SMS * 4, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl);
+                ransac_count_batch_kernel<false, 1><<<IBL_SMS * 4, SCORE_THREADS, 0, st>>>(d_probs, d_ent, d_n, max_d, max_d * max_d, d_inl, d_next);
             IBL_LAUNCH_CHECK();
         }
         int nval = 0;
@@ -1003,6 +1013,6 @@ IBL_API int ibl_ransac_run_batch(const ibl_reg_problem_t *problems, int32_t n_pr
     for (int p = 0; p < P; ++p)
         if (h_results[p].status == 0)
             h_results[p].drawn = std::max<int64_t>(std::min(max_iteration, std::max<int64_t>(hs[p].est_k, 0)), 0);
-    ibl_free(d_probs, st); ibl_free(d_n, st); ibl_free(d_ne, st);
+    ibl_free(d_probs, st); ibl_free(d_n, st); ibl_free(d_ne, st); ibl_free(d_next, st);
     return rc;
 }

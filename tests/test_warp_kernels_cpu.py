@@ -373,11 +373,14 @@ def test_dbscan_kernels_source_vs_oracle(warp_lib, eps, min_points, seed):
     assert want.max() >= 1 or min_points >= 40
 
 
-@pytest.mark.parametrize("radius,k,cell", [(0.1, 30, 0.05), (0.25, 100, 0.08), (np.inf, 30, 0.1), (0.05, 12, 0.05), (0.3, 224, 0.2)])
-def test_knn_kernel_source_vs_oracle(warp_lib, radius, k, cell):
+@pytest.mark.parametrize("radius,k,cell,n_pts", [(0.1, 30, 0.05, 130), (0.25, 100, 0.08, 130), (np.inf, 30, 0.1, 130),
+                                                  (0.05, 12, 0.05, 130), (0.3, 224, 0.2, 320)])
+def test_knn_kernel_source_vs_oracle(warp_lib, radius, k, cell, n_pts):
     from ibl_testutil import surface_cloud
     from oracle import o3d_core as oc
-    pts = np.ascontiguousarray(surface_cloud(320, 12)[0])      # every warp collective is two pthread barriers here: keep it small
+    # Every warp collective is two pthread barriers here, and the register sort of <= 128 candidates is 300 shuffles per
+    # query: small clouds.  The k = 224 case keeps 320 points, so that more than 128 candidates reach the shared-memory sort.
+    pts = np.ascontiguousarray(surface_cloud(n_pts, 12)[0])
     n = len(pts)
     sorted4, cell_start, o, dims = host_grid(pts, cell)
     rng = np.random.default_rng(0)

@@ -179,6 +179,12 @@ void ibl_feature_pack_destroy(ibl_feature_pack_t *pack);
  * are then invalid and the caller must fall back to ibl_feature_nn. */
 int ibl_feature_match_packed(const double *fa, int64_t na, const ibl_feature_pack_t *pack, int32_t *nn_ab, int32_t *nn_ba,
                              uint32_t *d_flag, void *stream);
+/* The same for callers that apply the mutual filter (CorrespondencesFromFeatures keeps (i, j = nn_ab[i]) iff nn_ba[j] == i,
+ * fpfh_register.py:110-112 with mutual_filter = True): nn_ab as above; nn_ba[j] is computed for the pack rows j that occur
+ * in nn_ab -- the only ones the filter reads -- and is -1 for every other row.  The reverse search then runs over a few
+ * thousand rows instead of the whole memory side. */
+int ibl_feature_match_packed_mutual(const double *fa, int64_t na, const ibl_feature_pack_t *pack, int32_t *nn_ab,
+                                    int32_t *nn_ba, uint32_t *d_flag, void *stream);
 /* Debug / test hook of the tensor-core filter inside ibl_feature_nn (csrc/match_tc.cu): the raw tcgen05 (kind::f16, 3-way fp16 split) scores
  * s'(a_i, b_j) = a32_i . b32_j - |b32_j|^2 / 2 as float32 [na][nb] (row-major), a32 / b32 being the rows minus the filter's
  * centre, times its power-of-two scale; centre (33) and scale (1) are written to center_out (device double[34]) when

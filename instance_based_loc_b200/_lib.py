@@ -79,6 +79,7 @@ _PROTOS = {
     "ibl_feature_pack_create": (c_int, [_V, c_int64, POINTER(c_void_p), _V]),
     "ibl_feature_pack_destroy": (None, [_V]),
     "ibl_feature_match_packed": (c_int, [_V, c_int64, _V, _V, _V, _V, _V]),
+    "ibl_feature_match_packed_mutual": (c_int, [_V, c_int64, _V, _V, _V, _V, _V]),
     "ibl_feature_scores_debug": (c_int, [_V, c_int64, _V, c_int64, _V, _V, c_int, _V]),
     "ibl_feature_nn_stats": (c_int, [POINTER(c_int64), c_int]),
     "ibl_feature_nn_wait_stats": (c_int, [POINTER(c_int64), c_int]),

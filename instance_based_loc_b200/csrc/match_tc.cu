@@ -345,6 +345,7 @@ __device__ __forceinline__ void tc_push(TcRowState &st, const TcPool &pool, int 
 __device__ __forceinline__ void tc_band_chunk(const float *v, float &L, float eh, int tb, TcRowState &rs, const TcPool &pool,
                                               int row, const double *__restrict__ fa_q, const double *__restrict__ fb,
                                               const int *__restrict__ perm) {
+    if (!(eh > -INFINITY)) return;                        // a row past the end (eh = -inf) records nothing, whatever its scores are
     float t[16];
 #pragma unroll
     for (int c = 0; c < 16; ++c) t[c] = fmaxf(v[2 * c], v[2 * c + 1]);
@@ -391,7 +392,13 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
                int tiles_per_split, int nsplit, const float *__restrict__ an32, const unsigned *__restrict__ bmax_bits,
                const double *__restrict__ fa, const double *__restrict__ fb,
                FSplitOutTC *__restrict__ out, TcPool pool, float *__restrict__ dump, int64_t dump_ld, int swap_lbo_sbo,
-               const float *__restrict__ tile_eb, const int *__restrict__ perm) {
+               const float *__restrict__ tile_eb, const int *__restrict__ perm, const int *__restrict__ n_live_dev,
+               const int *__restrict__ qmap) {
+    // n_live_dev / qmap (both or neither): the query image holds a device-side number of rows, gathered from a larger set;
+    // row q of the image is row qmap[q] of an32 / fa.  na is then only an upper bound (grid and scratch were sized by it),
+    // and a CTA whose query tiles are all past the live rows leaves at once.
+    if (n_live_dev && (int64_t)blockIdx.x * TC_QT * TC_M >= (int64_t)*n_live_dev) return;
+    if (n_live_dev) na = min(na, (int64_t)*n_live_dev);
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sA = smem_u32(smem);                   // TC_QT query tiles
     const uint32_t sB0 = sA + TC_QT * TC_TILE_BYTES;
@@ -525,12 +532,13 @@ feat_tc_kernel(const uint8_t *__restrict__ Aimg, int64_t na, int n_qtiles, const
             // tile_eb (cached packs): the target part of the band per TARGET TILE, from the largest norm inside the tile;
             // otherwise one value from the largest target norm of all
             float L = -INFINITY;
-            const float ea = live ? feat_tc_err_a(an32[q]) : -INFINITY;
+            const int64_t qo = (live && qmap) ? (int64_t)qmap[q] : q;      // the row's index in an32 / fa
+            const float ea = live ? feat_tc_err_a(an32[qo]) : -INFINITY;
             const float eb_all = feat_tc_err_b(__uint_as_float(*bmax_bits));
             TcRowState rs;
             rs.cnt = 0; rs.cur = -1; rs.ccnt = 0; rs.first = -1; rs.n_eval = 0; rs.bi = -1; rs.exhausted = 0; rs.bestd = INFINITY;
             const int row = (int)(q * nsplit + split);
-            const double *fa_q = fa + q * 33;
+            const double *fa_q = fa + qo * 33;
             if (live && row < pool.base) {                   // this row's first chunk is chunk `row`: no pool traffic for it
                 rs.cur = row; rs.first = row;
                 pool.row[row] = row; pool.next[row] = -1;
@@ -639,9 +647,11 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__
                                                            TcChunkRes *__restrict__ res, const double *__restrict__ fa,
                                                            const double *__restrict__ fb, const float *__restrict__ a32,
                                                            const float *__restrict__ b32, const float *__restrict__ na32,
-                                                           const float *__restrict__ nb32, const int *__restrict__ perm) {
+                                                           const float *__restrict__ nb32, const int *__restrict__ perm,
+                                                           const int *__restrict__ n_live_dev, const int *__restrict__ qmap) {
     // pool entries, b32 and nb32 are in the TARGET IMAGE's row order; perm (may be NULL = identity) maps such a position to
-    // the target's original index, which addresses fb and decides exact ties
+    // the target's original index, which addresses fb and decides exact ties.  n_live_dev / qmap: see feat_tc_kernel (a32,
+    // na32 and fa are indexed through qmap; the static chunks of rows past the live ones were never written and are skipped)
     constexpr int TC_EVAL_R = TC_CHUNK / TC_EVAL_GS;      // candidates per lane
     const int lane = threadIdx.x & 31, grp = lane / TC_EVAL_GS, gl = lane % TC_EVAL_GS;
     constexpr int GPW = 32 / TC_EVAL_GS;                  // chunks per warp
@@ -650,7 +660,8 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__
     unsigned long long n_eval = 0;
     for (int c0 = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * GPW; c0 < nchunks; c0 += nwarps * GPW) {
         const int c = c0 + grp;
-        const bool valid = c < nchunks;
+        bool valid = c < nchunks;
+        if (valid && n_live_dev && c < pool.base && c / nsplit >= *n_live_dev) valid = false;   // chunk c < base is split-row c
         const int row = valid ? pool.row[c] : 0;
         int n = valid ? pool.n[c] : 0;
         const uint32_t *e = pool.entries + (size_t)c * TC_CHUNK;
@@ -660,7 +671,7 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__
             single = true;
             n = 0;
         }
-        const int64_t q = row / nsplit;
+        const int64_t q = (valid && qmap) ? (int64_t)qmap[row / nsplit] : (int64_t)(row / nsplit);
         const float *aq = a32 + q * TC_R32;
         const float naq = n > 0 ? na32[q] : 0.f;
         int t[TC_EVAL_R];
@@ -709,9 +720,11 @@ __global__ void __launch_bounds__(256) feat_tc_eval_kernel(const FSplitOutTC *__
 // winner of its on-the-spot evaluations.
 __global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int64_t na, int nsplit, TcPool pool,
                                      const TcChunkRes *__restrict__ res, const double *__restrict__ fa,
-                                     const double *__restrict__ fb, int32_t *__restrict__ nn, const int *__restrict__ perm) {
+                                     const double *__restrict__ fb, int32_t *__restrict__ nn, const int *__restrict__ perm,
+                                     const int *__restrict__ n_live_dev, const int *__restrict__ qmap) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i >= na) return;
+    if (i >= na || (n_live_dev && i >= *n_live_dev)) return;
+    const int64_t io = qmap ? (int64_t)qmap[i] : i;       // row i of the query image is row io of fa / nn
     long long total = 0;
     int only = -1;
     for (int s = 0; s < nsplit; ++s) {
@@ -722,8 +735,8 @@ __global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int6
             else only = p.idx;                            // evaluated on the spot (pool exhausted): already an original index
         }
     }
-    if (total == 0) { nn[i] = -1; return; }
-    if (total == 1) { nn[i] = only; return; }            // the single band candidate IS the exact nearest neighbour
+    if (total == 0) { nn[io] = -1; return; }
+    if (total == 1) { nn[io] = only; return; }            // the single band candidate IS the exact nearest neighbour
     double bestd = INFINITY;
     int bi = -1;
     unsigned long long extra = 0;
@@ -735,12 +748,12 @@ __global__ void feat_tc_merge_kernel(const FSplitOutTC *__restrict__ parts, int6
             TcChunkRes r = res[c];
             if (r.idx < 0) continue;
             double d = r.d;
-            if (d < 0.0) { d = feat_tc_exact(fa + i * 33, fb + (size_t)r.idx * 33); ++extra; }
+            if (d < 0.0) { d = feat_tc_exact(fa + io * 33, fb + (size_t)r.idx * 33); ++extra; }
             if (bi < 0 || d < bestd || (d == bestd && r.idx < bi)) { bestd = d; bi = r.idx; }
         }
     }
     if (extra) atomicAdd(&g_tc_stats[1], extra);
-    nn[i] = bi;
+    nn[io] = bi;
 }
 struct TcPlan { int qtiles, btiles, nsplit, tiles_per_split; int64_t na_pad, nb_pad; };
 // grid = query tiles x splits of the target tiles, one CTA per SM at a time.  The split count is chosen so that the CTAs fill
@@ -789,7 +802,8 @@ IBL_API int ibl_feature_nn_set_pool_chunks(int chunks) {
 // float bits of max |b|^2; fa / fb the raw f64 rows, a32 / b32 / na32 / nb32 their fp32 copies and norm bounds.
 static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb, const float *an, const unsigned *bmax_bits,
                      const double *fa, const double *fb, const float *a32, const float *b32, const float *na32,
-                     const float *nb32, int32_t *nn, cudaStream_t st, const float *tile_eb = nullptr, const int *perm = nullptr) {
+                     const float *nb32, int32_t *nn, cudaStream_t st, const float *tile_eb = nullptr, const int *perm = nullptr,
+                     const int *n_live_dev = nullptr, const int *qmap = nullptr) {
     // B, b32, nb32 are in the target image's row order; tile_eb / perm (both or neither): a cached pack whose target rows are
     // sorted by norm -- per-tile band terms and the map from image row to original row (fb is in original order)
     TcPlan p = tc_plan(na, nb);
@@ -814,19 +828,19 @@ static int tc_search(const uint8_t *A, int64_t na, const uint8_t *B, int64_t nb,
         // nested scope: the tcgen05 kernel alone, with the flops it ISSUES (depth 112 over the padded tiles)
         IBL_PROF(IBL_PROF_FEATURE_GEMM, st, 2.0 * TC_K * (double)p.na_pad * (double)p.nb_pad);
         feat_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, p.qtiles, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, bmax_bits,
-                                                            fa, fb, parts, pool, nullptr, 0, 0, tile_eb, perm);
+                                                            fa, fb, parts, pool, nullptr, 0, 0, tile_eb, perm, n_live_dev, qmap);
         IBL_LAUNCH_CHECK();
     }
     {
         // the chunk count lives on the device (no host sync): a fixed grid strides over it
         static int gs = 0;
         if (gs == 0) { const char *e = getenv("IBL_TC_EVAL_GS"); gs = e ? atoi(e) : 8; }
-        if (gs == 4) feat_tc_eval_kernel<4><<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm);
-        else if (gs == 16) feat_tc_eval_kernel<16><<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm);
-        else feat_tc_eval_kernel<8><<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm);
+        if (gs == 4) feat_tc_eval_kernel<4><<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm, n_live_dev, qmap);
+        else if (gs == 16) feat_tc_eval_kernel<16><<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm, n_live_dev, qmap);
+        else feat_tc_eval_kernel<8><<<8 * IBL_SMS, 256, 0, st>>>(parts, pool, p.nsplit, res, fa, fb, a32, b32, na32, nb32, perm, n_live_dev, qmap);
         IBL_LAUNCH_CHECK();
     }
-    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn, perm);
+    feat_tc_merge_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(parts, na, p.nsplit, pool, res, fa, fb, nn, perm, n_live_dev, qmap);
     IBL_LAUNCH_CHECK();
     ibl_free(pool.entries, st); ibl_free(pool_meta, st); ibl_free(res, st); ibl_free(parts, st);
     return IBL_OK;
@@ -1093,6 +1107,90 @@ IBL_API int ibl_feature_match_packed(const double *fa, int64_t na, const ibl_fea
     return rc;
 }
 
+// ---- mutual matching: the reverse direction only where the mutual filter reads it ----------------------------------------
+// Open3D's mutual filter keeps (i, j = nn_ab[i]) iff nn_ba[j] == i (CorrespondencesFromFeatures): nn_ba is read ONLY at the
+// targets some source row chose.  On the bench a source of ~15 k rows reaches a few thousand distinct rows of a ~37 k-row
+// memory side, so the reverse search runs for those rows only: mark the chosen rows, compact them (device-side count),
+// gather their query-role image rows into whole tiles, and run the search with the live row count on the device.
+__global__ void feat_tc_mark_kernel(const int32_t *__restrict__ nn_ab, int64_t na, int64_t nb, uint8_t *__restrict__ mark) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= na) return;
+    const int j = nn_ab[i];
+    if (j >= 0 && j < nb) mark[j] = 1;
+}
+__global__ void __launch_bounds__(128) feat_tc_gather_rows_kernel(const int *__restrict__ J, const int *__restrict__ nJ,
+                                                                  const uint8_t *__restrict__ img, uint8_t *__restrict__ out) {
+    const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;          // the grid covers every row of the output image
+    uint4 *d = reinterpret_cast<uint4 *>(out + tc_row_offset(k));
+    if (k >= *nJ) {
+        // rows past the live ones are ZERO, like the padding rows of a packed image: recycled scratch may hold fp16 Inf / NaN
+        // patterns, and an infinite score defeats the dead rows' "threshold = +inf" rule (inf >= inf)
+#pragma unroll
+        for (int c = 0; c < TC_KCH; ++c) d[c * (TC_LBO / 16)] = make_uint4(0u, 0u, 0u, 0u);
+        return;
+    }
+    const uint4 *s = reinterpret_cast<const uint4 *>(img + tc_row_offset(J[k]));
+#pragma unroll
+    for (int c = 0; c < TC_KCH; ++c) d[c * (TC_LBO / 16)] = s[c * (TC_LBO / 16)];
+}
+
+// ibl_feature_match_packed for callers that apply the mutual filter: nn_ab as there; nn_ba[j] is the nearest row of fa for
+// every pack row j that occurs in nn_ab and -1 for every other row (the filter never reads those).
+IBL_API int ibl_feature_match_packed_mutual(const double *fa, int64_t na, const ibl_feature_pack_t *pk, int32_t *nn_ab,
+                                            int32_t *nn_ba, uint32_t *d_flag, void *stream) {
+    IBL_ARG(pk && na > 0 && fa && nn_ab && nn_ba && na < (1ll << 31));
+    cudaStream_t st = ibl_stream(stream);
+    int rc = tc_configure();
+    if (rc < 0) return rc;
+    const int64_t na_pad = (na + TC_M - 1) / TC_M * TC_M;
+    const size_t img = (size_t)(na_pad / TC_M) * TC_TILE_BYTES;
+    const int64_t nj_max = std::min<int64_t>(na, pk->n);           // at most one chosen pack row per source row
+    const int64_t nj_pad = (nj_max + TC_M - 1) / TC_M * TC_M;
+    uint8_t *A0 = nullptr, *A1 = nullptr, *Q = nullptr, *mark = nullptr; float *an = nullptr, *a32 = nullptr, *na32 = nullptr;
+    unsigned *mx = nullptr; int *J = nullptr, *nJ = nullptr;
+    IBL_CUDA(ibl_alloc(&A0, img, st));
+    IBL_CUDA(ibl_alloc(&A1, img, st));
+    IBL_CUDA(ibl_alloc(&an, (size_t)na_pad, st));
+    IBL_CUDA(ibl_alloc(&a32, (size_t)na * TC_R32, st));
+    IBL_CUDA(ibl_alloc(&na32, (size_t)na, st));
+    IBL_CUDA(ibl_alloc(&mx, 3, st));
+    IBL_CUDA(ibl_alloc(&Q, (size_t)(nj_pad / TC_M) * TC_TILE_BYTES, st));
+    IBL_CUDA(ibl_alloc(&mark, (size_t)pk->n, st));
+    IBL_CUDA(ibl_alloc(&J, (size_t)pk->n, st));
+    IBL_CUDA(ibl_alloc(&nJ, 1, st));
+    IBL_CUDA(cudaMemsetAsync(mx, 0, 3 * sizeof(unsigned), st));
+    IBL_CUDA(cudaMemsetAsync(mark, 0, (size_t)pk->n, st));
+    IBL_CUDA(cudaMemsetAsync(nn_ba, 0xff, sizeof(int32_t) * (size_t)pk->n, st));
+    void *tmp = nullptr;
+    {
+        // work figure: the forward direction only.  The reverse direction's row count lives on the device, so its flops are
+        // NOT counted although its time is inside the scope: the reported rate is a lower bound.
+        IBL_PROF(IBL_PROF_FEATURE_NN, st, 2.0 * 33.0 * (double)na * (double)pk->n);
+        feat_tc_pack_both_kernel<<<(unsigned)(na_pad / 128), 128, 0, st>>>(fa, na, na_pad, pk->mu, pk->mx + 2, A0, A1, an, mx, mx + 1,
+                                                                          a32, na32, d_flag ? d_flag : mx + 2);
+        IBL_LAUNCH_CHECK();
+        rc = tc_search(A0, na, pk->img1, pk->n, an, pk->mx + 1, fa, pk->f, a32, pk->rows32s, na32, pk->nrm32s, nn_ab, st,
+                       pk->tile_eb, pk->perm);
+        if (rc == IBL_OK) {
+            feat_tc_mark_kernel<<<(unsigned)((na + 255) / 256), 256, 0, st>>>(nn_ab, na, pk->n, mark);
+            IBL_LAUNCH_CHECK();
+            cub::CountingInputIterator<int> cit(0);
+            size_t tb = 0;
+            cub::DeviceSelect::Flagged(nullptr, tb, cit, mark, J, nJ, (int)pk->n, st);
+            IBL_CUDA(cudaMallocAsync(&tmp, tb ? tb : 1, st));
+            IBL_CUDA(cub::DeviceSelect::Flagged(tmp, tb, cit, mark, J, nJ, (int)pk->n, st));
+            feat_tc_gather_rows_kernel<<<(unsigned)(nj_pad / 128), 128, 0, st>>>(J, nJ, pk->img0, Q);
+            IBL_LAUNCH_CHECK();
+            rc = tc_search(Q, nj_max, A1, na, pk->an32, mx + 1, pk->f, fa, pk->rows32, a32, pk->nrm32, na32, nn_ba, st,
+                           nullptr, nullptr, nJ, J);
+        }
+    }
+    ibl_free(tmp, st);
+    ibl_free(A0, st); ibl_free(A1, st); ibl_free(an, st); ibl_free(a32, st); ibl_free(na32, st); ibl_free(mx, st);
+    ibl_free(Q, st); ibl_free(mark, st); ibl_free(J, st); ibl_free(nJ, st);
+    return rc;
+}
+
 // Debug / test hook: the raw tensor-core scores s'(a_i, b_j) = a32.b32 - |b32|^2/2 as float32 [na][nb] (row-major), where
 // a32 / b32 are the rows after subtracting the filter's centre and multiplying by its power-of-two scale (centre and
 // scale are written to center_out, device double[34], if not NULL).
@@ -1126,7 +1224,7 @@ IBL_API int ibl_feature_scores_debug(const double *fa, int64_t na, const double 
     IBL_LAUNCH_CHECK();
     dim3 grid((p.qtiles + TC_QT - 1) / TC_QT, p.nsplit);
     feat_tc_kernel<0><<<grid, TC_THREADS, TC_SMEM, st>>>(A, na, p.qtiles, B, nb, p.btiles, p.tiles_per_split, p.nsplit, an, mx + 1,
-                                                        fa, fb, nullptr, TcPool{}, scores, nb, swap_lbo_sbo, nullptr, nullptr);
+                                                        fa, fb, nullptr, TcPool{}, scores, nb, swap_lbo_sbo, nullptr, nullptr, nullptr, nullptr);
     IBL_LAUNCH_CHECK();
     if (center_out) {                                     // debug hook only: read the scale back and publish it
         unsigned bits = 0;

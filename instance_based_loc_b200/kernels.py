@@ -315,6 +315,18 @@ def feature_match_packed(fa, pack):
     return ab, ba, flag
 
 
+def feature_match_packed_mutual(fa, pack):
+    """feature_match_packed for the mutual filter: nn_ba is computed only for the pack rows that occur in nn_ab (the only
+    entries the filter reads) and is -1 elsewhere (ibl_feature_match_packed_mutual)."""
+    dev = fa.device
+    ab = torch.empty(fa.shape[0], dtype=torch.int32, device=dev)
+    ba = torch.empty(pack.f.shape[0], dtype=torch.int32, device=dev)
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    check(lib().ibl_feature_match_packed_mutual(_p(fa), fa.shape[0], pack.h, _p(ab), _p(ba), _p(flag), _stream()),
+          "feature_match_packed_mutual")
+    return ab, ba, flag
+
+
 def feature_scores_debug(fa, fb, swap_lbo_sbo=0):
     """Test hook: raw tcgen05 scores a32.b32 - |b32|^2/2 of the matcher's filter, float32 [na, nb], where a32 / b32 are
     the rows minus the returned centre, times the returned power-of-two scale.  -> (scores, centre float64 [33], scale)."""

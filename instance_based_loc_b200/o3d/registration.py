@@ -152,12 +152,18 @@ def _nn_grid(target, max_d):
     return target.grid(max(max_d, 1e-4), nnfield=max_d, nnfield_voxel=nn_voxel(max_d))
 
 
+# reverse matching restricted to the rows the mutual filter reads (ibl_feature_match_packed_mutual); IBL_MUTUAL_SUBSET=0
+# runs the full reverse direction again (measurement switch)
+mutual_reverse_subset = os.environ.get("IBL_MUTUAL_SUBSET", "1") != "0"
+
+
 def match_features(source_feature, target_feature, mutual_filter=True, ransac_n=3):
     """A.5 -> device int32 [C,2]."""
     fa, fb = source_feature._dev, target_feature._dev
     if mutual_filter and target_feature._pack is not None and fa.shape[0] > 0:
         # the target's packed operands are cached: both directions from one read of the source rows
-        ij, ji, flag = K.feature_match_packed(fa, target_feature._pack)
+        # (the reverse direction only for the target rows some source row chose: the mutual filter reads no others)
+        ij, ji, flag = (K.feature_match_packed_mutual if mutual_reverse_subset else K.feature_match_packed)(fa, target_feature._pack)
         cor = K.mutual_corres(ij, ji, ransac_n)              # synchronises
         if int(flag.item()) == 0:
             return cor

@@ -210,6 +210,34 @@ def test_feature_match_packed_sorted_targets_ties_and_exhausted_pool(K):
         K.feature_nn_set_pool_chunks(0)
 
 
+@pytest.mark.parametrize("na,nb", [(700, 3000), (3000, 700), (130, 129), (5, 900)])
+def test_feature_match_packed_mutual_subset(K, na, nb):
+    """ibl_feature_match_packed_mutual: nn_ab equal to the full call; nn_ba equal to the full call on every pack row that
+    occurs in nn_ab -- the only rows Open3D's mutual filter reads -- and -1 on the others; the filtered correspondences are
+    therefore identical.  Exact duplicates on both sides, default pool and a pool that runs dry."""
+    rng = np.random.default_rng(na + 3 * nb)
+    base = rng.gamma(2.0, 12.0, (30, 33)) * rng.uniform(0.3, 2.5, (30, 1))
+    fb = base[rng.integers(0, 30, nb)] + (rng.random((nb, 1)) < 0.6) * rng.normal(0, 0.8, (nb, 33))
+    fa = base[rng.integers(0, 30, na)] + (rng.random((na, 1)) < 0.6) * rng.normal(0, 0.8, (na, 33))
+    A, B = dev(fa), dev(fb)
+    pack = K.FeaturePack(B)
+    ab0, ba0, _ = K.feature_match_packed(A, pack)
+    try:
+        for chunks in (0, 8):
+            K.feature_nn_set_pool_chunks(chunks)
+            ab, ba, flag = K.feature_match_packed_mutual(A, pack)
+            assert int(flag.item()) == 0
+            ab_h, ba_h, ab0_h, ba0_h = ab.cpu().numpy(), ba.cpu().numpy(), ab0.cpu().numpy(), ba0.cpu().numpy()
+            assert np.array_equal(ab_h, ab0_h), chunks
+            chosen = np.zeros(nb, bool)
+            chosen[ab0_h] = True
+            assert np.array_equal(ba_h[chosen], ba0_h[chosen]), chunks
+            assert np.all(ba_h[~chosen] == -1), chunks
+            assert np.array_equal(K.mutual_corres(ab, ba, 3).cpu().numpy(), K.mutual_corres(ab0, ba0, 3).cpu().numpy())
+    finally:
+        K.feature_nn_set_pool_chunks(0)
+
+
 def test_shared_knn_search_equals_separate_searches(K):
     """normals (Hybrid 0.1 / 30), colour gradients (0.15 / 30) and FPFH (0.25 / 100) derived from ONE 0.25 / 100 search are
     the neighbour lists of their own searches: same counts, same indices in the same order."""

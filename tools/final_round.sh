@@ -5,6 +5,7 @@
 mkdir -p gpurun_out/final
 O=gpurun_out/final
 timeout 900 python -m pytest tests -m gpu -x -q > $O/gpu_tests.log 2>&1; echo "pytest rc=$?" | tee -a $O/gpu_tests.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "smoke rc=$?" | tee -a $O/smoke.log
 timeout 600 python bench.py --gpus 1 --steps 20 --warmup 5 > $O/bench_cfg1.json 2> $O/bench_cfg1.err; echo "bench cfg1 rc=$?"
 for c in 0 2 3 4; do
     timeout 900 python bench.py --config $c > $O/bench_cfg$c.json 2> $O/bench_cfg$c.err; echo "bench cfg$c rc=$?"
@@ -12,11 +13,13 @@ done
 if [ "$1" != "noref" ]; then
     timeout 900 python bench.py --impl reference --gpus 1 --steps 20 --warmup 5 > $O/ref_cfg1.json 2> $O/ref_cfg1.err; echo "reference rc=$?"
 fi
-B="python bench.py --steps 1 --warmup 1 --frames-per-step 16 --no-cpu-baseline --profiler-range"
+FPS=${FRAMES_PER_STEP:-16}
+B="python bench.py --steps 1 --warmup 1 --frames-per-step $FPS --no-cpu-baseline --profiler-range"
 timeout 600 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv \
     --log-file $O/launches.csv $B > $O/ncu_launches.log 2>&1; echo "ncu-launches rc=$?"
-python tools/ncu_summary.py launches $O/launches.csv "configs[1], one step of 16 frames (bench.py --steps 1 --frames-per-step 16 --profiler-range)" > $O/ncu_launches.txt 2>&1
+python tools/ncu_summary.py launches $O/launches.csv "configs[1], one step of $FPS frames (bench.py --steps 1 --frames-per-step $FPS --profiler-range)" > $O/ncu_launches.txt 2>&1
 gzip -f $O/launches.csv
+if [ "$2" = "notour" ]; then tail -2 $O/gpu_tests.log; tail -1 $O/smoke.log; for c in 1 0 2 3 4; do head -c 200 $O/bench_cfg$c.json; echo; done; head -12 $O/ncu_launches.txt; exit 0; fi
 timeout 300 python tools/kernel_tour.py > $O/tour_plain.log 2>&1 && \
 timeout 1200 ncu --set full --clock-control none --import-source on --metrics $(python tools/ncu_summary.py extra-metrics) \
     --kernel-id "::regex:.*:2" -f -o /tmp/tour python tools/kernel_tour.py > $O/ncu_tour.log 2>&1; echo "ncu-tour rc=$?"

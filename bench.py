@@ -468,7 +468,9 @@ def run_frames(args, cfg):
     work_per_s = (t["work"] / max(t["launches"], 1)) / (per_launch_ms / 1e3) if per_launch_ms > 0 else 0.0
     if tname in TENSOR_KERNELS:
         bound, unit, achieved, peak = "tensor", "TFLOP/s", work_per_s / 1e12, tensor_peak
-        note = ("achieved = ALGORITHMIC flops 2*33*N_s*N_t of the FPFH distance matrix per launch / launch time (operand "
+        note = ("achieved = ALGORITHMIC flops 2*33*N_s*N_t of the FORWARD search per launch / launch time; the reverse search "
+                "runs only for the memory rows the mutual filter reads, its row count lives on the device and its flops are "
+                "not counted although its time is (a lower bound) (operand "
                 "packing, the one-pass tcgen05 kind::f16 score GEMM of depth 112, the fp32-difference filter and the exact "
                 "f64 re-evaluation are all inside the launch); peak is the measured dense bf16 figure")
     else:

@@ -1110,26 +1110,25 @@ IBL_API int ibl_feature_match_packed(const double *fa, int64_t na, const ibl_fea
 // ---- mutual matching: the reverse direction only where the mutual filter reads it ----------------------------------------
 // Open3D's mutual filter keeps (i, j = nn_ab[i]) iff nn_ba[j] == i (CorrespondencesFromFeatures): nn_ba is read ONLY at the
 // targets some source row chose.  On the bench a source of ~15 k rows reaches a few thousand distinct rows of a ~37 k-row
-// memory side, so the reverse search runs for those rows only: mark the chosen rows, compact them (device-side count),
-// gather their query-role image rows into whole tiles, and run the search with the live row count on the device.
-__global__ void feat_tc_mark_kernel(const int32_t *__restrict__ nn_ab, int64_t na, int64_t nb, uint8_t *__restrict__ mark) {
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+// memory side, so the reverse search runs for those rows only: ONE kernel claims the chosen rows, compacts them (device-side
+// count) and gathers their query-role image rows into whole tiles, then the search runs with the live row count on the device.
+// One kernel: the first source row that names pack row j claims it (atomic exchange on a zeroed flag), takes the next slot of
+// the compact list (device counter) and copies j's query-role image row there.  The list's ORDER depends on scheduling; no
+// result does -- a row's search is independent of its slot, and results are scattered back through the list.  Slots past
+// the count keep the zeros the image was cleared to: recycled scratch may hold fp16 Inf / NaN patterns, and an infinite score
+// defeats the dead rows' "threshold = +inf" rule (inf >= inf) -- found as an illegal address under four streams.
+__global__ void __launch_bounds__(128) feat_tc_claim_rows_kernel(const int32_t *__restrict__ nn_ab, int64_t na, int64_t nb,
+                                                                 int *__restrict__ claimed, int *__restrict__ J, int *__restrict__ nJ,
+                                                                 const uint8_t *__restrict__ img, uint8_t *__restrict__ out) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= na) return;
     const int j = nn_ab[i];
-    if (j >= 0 && j < nb) mark[j] = 1;
-}
-__global__ void __launch_bounds__(128) feat_tc_gather_rows_kernel(const int *__restrict__ J, const int *__restrict__ nJ,
-                                                                  const uint8_t *__restrict__ img, uint8_t *__restrict__ out) {
-    const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;          // the grid covers every row of the output image
+    if (j < 0 || j >= nb) return;
+    if (atomicExch(claimed + j, 1) != 0) return;
+    const int k = atomicAdd(nJ, 1);
+    J[k] = j;
+    const uint4 *s = reinterpret_cast<const uint4 *>(img + tc_row_offset(j));
     uint4 *d = reinterpret_cast<uint4 *>(out + tc_row_offset(k));
-    if (k >= *nJ) {
-        // rows past the live ones are ZERO, like the padding rows of a packed image: recycled scratch may hold fp16 Inf / NaN
-        // patterns, and an infinite score defeats the dead rows' "threshold = +inf" rule (inf >= inf)
-#pragma unroll
-        for (int c = 0; c < TC_KCH; ++c) d[c * (TC_LBO / 16)] = make_uint4(0u, 0u, 0u, 0u);
-        return;
-    }
-    const uint4 *s = reinterpret_cast<const uint4 *>(img + tc_row_offset(J[k]));
 #pragma unroll
     for (int c = 0; c < TC_KCH; ++c) d[c * (TC_LBO / 16)] = s[c * (TC_LBO / 16)];
 }
@@ -1146,8 +1145,8 @@ IBL_API int ibl_feature_match_packed_mutual(const double *fa, int64_t na, const 
     const size_t img = (size_t)(na_pad / TC_M) * TC_TILE_BYTES;
     const int64_t nj_max = std::min<int64_t>(na, pk->n);           // at most one chosen pack row per source row
     const int64_t nj_pad = (nj_max + TC_M - 1) / TC_M * TC_M;
-    uint8_t *A0 = nullptr, *A1 = nullptr, *Q = nullptr, *mark = nullptr; float *an = nullptr, *a32 = nullptr, *na32 = nullptr;
-    unsigned *mx = nullptr; int *J = nullptr, *nJ = nullptr;
+    uint8_t *A0 = nullptr, *A1 = nullptr, *Q = nullptr; float *an = nullptr, *a32 = nullptr, *na32 = nullptr;
+    unsigned *mx = nullptr; int *J = nullptr, *nJ = nullptr, *claimed = nullptr;
     IBL_CUDA(ibl_alloc(&A0, img, st));
     IBL_CUDA(ibl_alloc(&A1, img, st));
     IBL_CUDA(ibl_alloc(&an, (size_t)na_pad, st));
@@ -1155,13 +1154,14 @@ IBL_API int ibl_feature_match_packed_mutual(const double *fa, int64_t na, const 
     IBL_CUDA(ibl_alloc(&na32, (size_t)na, st));
     IBL_CUDA(ibl_alloc(&mx, 3, st));
     IBL_CUDA(ibl_alloc(&Q, (size_t)(nj_pad / TC_M) * TC_TILE_BYTES, st));
-    IBL_CUDA(ibl_alloc(&mark, (size_t)pk->n, st));
-    IBL_CUDA(ibl_alloc(&J, (size_t)pk->n, st));
+    IBL_CUDA(ibl_alloc(&claimed, (size_t)pk->n, st));
+    IBL_CUDA(ibl_alloc(&J, (size_t)nj_pad, st));
     IBL_CUDA(ibl_alloc(&nJ, 1, st));
     IBL_CUDA(cudaMemsetAsync(mx, 0, 3 * sizeof(unsigned), st));
-    IBL_CUDA(cudaMemsetAsync(mark, 0, (size_t)pk->n, st));
+    IBL_CUDA(cudaMemsetAsync(claimed, 0, sizeof(int) * (size_t)pk->n, st));
+    IBL_CUDA(cudaMemsetAsync(nJ, 0, sizeof(int), st));
+    IBL_CUDA(cudaMemsetAsync(Q, 0, (size_t)(nj_pad / TC_M) * TC_TILE_BYTES, st));
     IBL_CUDA(cudaMemsetAsync(nn_ba, 0xff, sizeof(int32_t) * (size_t)pk->n, st));
-    void *tmp = nullptr;
     {
         // work figure: the forward direction only.  The reverse direction's row count lives on the device, so its flops are
         // NOT counted although its time is inside the scope: the reported rate is a lower bound.
@@ -1172,22 +1172,14 @@ IBL_API int ibl_feature_match_packed_mutual(const double *fa, int64_t na, const 
         rc = tc_search(A0, na, pk->img1, pk->n, an, pk->mx + 1, fa, pk->f, a32, pk->rows32s, na32, pk->nrm32s, nn_ab, st,
                        pk->tile_eb, pk->perm);
         if (rc == IBL_OK) {
-            feat_tc_mark_kernel<<<(unsigned)((na + 255) / 256), 256, 0, st>>>(nn_ab, na, pk->n, mark);
-            IBL_LAUNCH_CHECK();
-            cub::CountingInputIterator<int> cit(0);
-            size_t tb = 0;
-            cub::DeviceSelect::Flagged(nullptr, tb, cit, mark, J, nJ, (int)pk->n, st);
-            IBL_CUDA(cudaMallocAsync(&tmp, tb ? tb : 1, st));
-            IBL_CUDA(cub::DeviceSelect::Flagged(tmp, tb, cit, mark, J, nJ, (int)pk->n, st));
-            feat_tc_gather_rows_kernel<<<(unsigned)(nj_pad / 128), 128, 0, st>>>(J, nJ, pk->img0, Q);
+            feat_tc_claim_rows_kernel<<<(unsigned)((na + 127) / 128), 128, 0, st>>>(nn_ab, na, pk->n, claimed, J, nJ, pk->img0, Q);
             IBL_LAUNCH_CHECK();
             rc = tc_search(Q, nj_max, A1, na, pk->an32, mx + 1, pk->f, fa, pk->rows32, a32, pk->nrm32, na32, nn_ba, st,
                            nullptr, nullptr, nJ, J);
         }
     }
-    ibl_free(tmp, st);
     ibl_free(A0, st); ibl_free(A1, st); ibl_free(an, st); ibl_free(a32, st); ibl_free(na32, st); ibl_free(mx, st);
-    ibl_free(Q, st); ibl_free(mark, st); ibl_free(J, st); ibl_free(nJ, st);
+    ibl_free(Q, st); ibl_free(claimed, st); ibl_free(J, st); ibl_free(nJ, st);
     return rc;
 }
 
